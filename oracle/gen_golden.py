@@ -1,0 +1,230 @@
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference in the authoring container.
+
+Run from the repo root:  python oracle/gen_golden.py
+Needs /root/reference (absent on the GPU box, which only reads the committed fixtures).
+The reference modules are loaded by file path; `omegaconf` (imported but unused by
+utils/utils.py:10, absent from this image) is stubbed.  Nothing is copied from the reference.
+"""
+import importlib.util
+import pathlib
+import random
+import sys
+import tempfile
+import types
+
+import numpy as np
+import torch
+
+REF = pathlib.Path("/root/reference")
+OUT = pathlib.Path(__file__).resolve().parent.parent / "tests" / "golden"
+
+
+def load_reference():
+    sys.modules.setdefault("omegaconf", types.SimpleNamespace(OmegaConf=object))
+    mods = {}
+    for name, rel in (("ref_utils", "utils/utils.py"), ("ref_replay", "utils/replay_buffer.py")):
+        spec = importlib.util.spec_from_file_location(name, REF / rel)
+        m = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(m)
+        mods[name] = m
+    return mods["ref_utils"], mods["ref_replay"]
+
+
+def reps(seed, b, d):
+    g = torch.Generator().manual_seed(seed)
+    return torch.tanh(torch.randn(b, d, generator=g))
+
+
+def gen_pbe(ref_utils):
+    """PBE / RMS trajectories: every (avg, rms, clip) mode, several k and D, 3 sequential calls.
+    The three input reps of a (b, d) shape are stored once and shared by all of its mode cases."""
+    out = {}
+    case = 0
+    for (b, d) in ((96, 512), (64, 50), (80, 10), (72, 24), (64, 128)):
+        xs = [reps(1000 + 31 * d + call, b, d) for call in range(3)]
+        for call, x in enumerate(xs):
+            out[f"rep_{b}_{d}_{call}"] = x.numpy()
+        for k in (1, 3, 12):
+            for avg in (True, False):
+                for rms_on in (True, False):
+                    for clip in (0.0, 0.0001, 0.5, -1.0):
+                        if d != 512 and clip in (0.0001, -1.0):
+                            continue
+                        rms = ref_utils.RMS("cpu")
+                        pbe = ref_utils.PBE(rms, clip, k, avg, rms_on, "cpu")
+                        tag = f"pbe{case:03d}"
+                        out[f"{tag}_cfg"] = np.array([b, d, k, int(avg), int(rms_on)], np.int64)
+                        out[f"{tag}_clip"] = np.array(clip, np.float64)
+                        for call, x in enumerate(xs):
+                            r = pbe(x.clone())
+                            out[f"{tag}_reward{call}"] = r.numpy()
+                            out[f"{tag}_state{call}"] = np.array(
+                                [float(rms.M), float(rms.S), rms.n], np.float64)
+                        case += 1
+    out["n_cases"] = np.array(case)
+    np.savez_compressed(OUT / "pbe_reference.npz", **out)
+    print("pbe cases:", case)
+
+
+def gen_kat(ref_utils):
+    """The 4-point known-answer vectors of SURVEY.md §8c, re-derived from the reference."""
+    rep = torch.tensor([[0., 0.], [3., 4.], [6., 8.], [0., 1.]])
+    out = {"rep": rep.numpy()}
+    for name, (avg, rms_on, clip) in {
+            "avg_rms_c0": (True, True, 0.0), "avg_rms_c05": (True, True, 0.5),
+            "avg_norms_c0": (True, False, 0.0), "avg_norms_c05": (True, False, 0.5),
+            "kth_rms_c0": (False, True, 0.0), "kth_rms_c05": (False, True, 0.5),
+            "kth_norms_c0": (False, False, 0.0), "avg_rms_cneg": (True, True, -1.0)}.items():
+        rms = ref_utils.RMS("cpu")
+        pbe = ref_utils.PBE(rms, clip, 2, avg, rms_on, "cpu")
+        for call in range(2):
+            out[f"{name}_r{call}"] = pbe(rep.clone()).numpy()
+            out[f"{name}_s{call}"] = np.array([float(rms.M), float(rms.S), rms.n], np.float64)
+    rms = ref_utils.RMS("cpu")
+    rms(torch.tensor([[1.], [2.], [3.], [6.]]))
+    out["rms_a"] = np.array([float(rms.M), float(rms.S), rms.n])
+    rms(torch.tensor([[10.], [20.]]))
+    out["rms_b"] = np.array([float(rms.M), float(rms.S), rms.n])
+    np.savez_compressed(OUT / "pbe_kat.npz", **out)
+
+
+def gen_knn_dists(ref_utils):
+    """Distance/top-k of the reference expression itself (utils.py:293-300) with indices kept,
+    including B1 != B2 (compute_apt_reward form) and a 3-D rep."""
+    out = {}
+    for tag, (b1, b2, d, k) in {"sq512": (128, 128, 512, 12), "rect": (40, 200, 64, 12),
+                                "proto": (64, 256, 128, 3), "tiny": (16, 16, 10, 5)}.items():
+        s = reps(50 + b1, b1, d)
+        t = s if b1 == b2 else reps(51 + b2, b2, d)
+        sim = torch.norm(s[:, None, :].view(b1, 1, -1) - t[None, :, :].view(1, b2, -1),
+                         dim=-1, p=2)
+        dist, idx = sim.topk(k, dim=1, largest=False, sorted=True)
+        kp1 = sim.topk(min(k + 1, b2), dim=1, largest=False, sorted=True)[0]
+        out[f"{tag}_src"], out[f"{tag}_tgt"] = s.numpy(), t.numpy()
+        out[f"{tag}_dist"], out[f"{tag}_idx"] = dist.numpy(), idx.numpy()
+        out[f"{tag}_kp1"] = kp1.numpy()
+    np.savez_compressed(OUT / "knn_reference.npz", **out)
+
+
+def gen_proto():
+    """proto.py:110-118 evaluated verbatim on seeded z / queue (the module itself imports the
+    `utils` package, which needs dm_control, so its five lines are executed here directly)."""
+    out = {}
+    g = torch.Generator().manual_seed(1)
+    z = torch.nn.functional.normalize(torch.randn(96, 128, generator=g), dim=1, p=2)
+    g = torch.Generator().manual_seed(2)
+    full = torch.nn.functional.normalize(torch.randn(256, 128, generator=g), dim=1, p=2)
+    for tag, queue in (("full", full.clone()),
+                       ("warm", torch.cat([full[:64], torch.zeros(192, 128)]))):
+        ptr = 0
+        cand = torch.arange(0, 32)
+        queue[ptr:ptr + 32] = z[cand]
+        ptr = (ptr + 32) % queue.shape[0]
+        z_to_q = torch.norm(z[:, None, :] - queue[None, :, :], dim=2, p=2)
+        all_dists, _ = torch.topk(z_to_q, 3, dim=1, largest=False)
+        out[f"{tag}_queue_after"] = queue.numpy()
+        out[f"{tag}_reward"] = all_dists[:, -1:].numpy()
+        out[f"{tag}_ptr"] = np.array(ptr)
+    out["z"] = z.numpy()
+    out["queue_full"] = full.numpy()
+    np.savez_compressed(OUT / "proto_reference.npz", **out)
+
+
+def synth_episode(rng, eps_len, obs_shape, obs_dtype, terminal, with_meta):
+    n = eps_len + 1
+    if obs_dtype == np.uint8:
+        obs = rng.integers(0, 256, size=(n, *obs_shape), dtype=np.uint8)
+    else:
+        obs = rng.standard_normal((n, *obs_shape)).astype(np.float32)
+    disc = np.ones((n, 1), np.float32)
+    if terminal:
+        disc[-1] = 0.0
+    ep = {"observation": obs,
+          "action": rng.uniform(-1, 1, (n, 6)).astype(np.float32),
+          "reward": rng.uniform(0, 1, (n, 1)).astype(np.float32),
+          "discount": disc}
+    if with_meta:
+        ep["skill"] = rng.standard_normal((n, 16)).astype(np.float32)
+        ep["done"] = (rng.uniform(size=(n,)) < 0.1)
+    return ep
+
+
+def gen_replay(ref_replay):
+    """ReplayBuffer._sample / OfflineReplayBuffer._sample of the reference over synthetic episode
+    directories written with the reference's own save_episode; the (episode, idx) draws are
+    recorded by replaying the same RNG streams."""
+    out = {}
+    for tag, (obs_shape, obs_dtype, with_meta, nstep) in {
+            "state_n3": ((24,), np.float32, False, 3), "state_n1": ((24,), np.float32, False, 1),
+            "meta_n3": ((24,), np.float32, True, 3), "pix_n3": ((9, 12, 12), np.uint8, False, 3),
+            "state_n5": ((24,), np.float32, False, 5)}.items():
+        rng = np.random.default_rng(3)
+        with tempfile.TemporaryDirectory() as td:
+            td = pathlib.Path(td)
+            lens = [20, 7, 33, 12, 9, 50]
+            eps = []
+            for e, L in enumerate(lens):
+                ep = synth_episode(rng, L, obs_shape, obs_dtype, terminal=(e % 2 == 0),
+                                   with_meta=with_meta)
+                ref_replay.save_episode(ep, td / f"episode_{e}_{L}.npz")
+                eps.append(ep)
+            meta_specs = ((types.SimpleNamespace(name="skill"), types.SimpleNamespace(name="done"))
+                          if with_meta else ())
+            storage = types.SimpleNamespace(_replay_dir=td, _meta_specs=meta_specs)
+            buf = ref_replay.ReplayBuffer(storage, 10 ** 6, 1, nstep, 0.99, fetch_every=1000,
+                                          save_snapshot=True)
+            random.seed(11)
+            np.random.seed(11)
+            samples = [buf._sample() for _ in range(64)]
+            # replay the identical draw sequence to recover (episode, idx)
+            random.seed(11)
+            np.random.seed(11)
+            fns = list(buf._episode_fns)
+            draws = []
+            for _ in range(64):
+                fn = random.choice(fns)
+                e = int(fn.stem.split("_")[1])
+                idx = np.random.randint(0, lens[e] - nstep + 1) + 1
+                draws.append((e, idx))
+            out[f"{tag}_draws"] = np.array(draws, np.int64)
+            out[f"{tag}_lens"] = np.array(lens, np.int64)
+            out[f"{tag}_nstep"] = np.array(nstep)
+            for name in eps[0]:
+                for e, ep in enumerate(eps):
+                    out[f"{tag}_ep{e}_{name}"] = ep[name]
+            for j in range(len(samples[0])):
+                out[f"{tag}_out{j}"] = np.stack([np.asarray(s[j]) for s in samples])
+            # boundary positions, evaluated by the reference's own arithmetic through _sample
+            # cannot be forced; they are covered through the oracle (pinned on the draws above).
+            if tag == "state_n3":
+                off = ref_replay.OfflineReplayBuffer(None, td, 10 ** 6, 1, 0.99)
+                off._load(relable=False)
+                off._loaded = True
+                random.seed(5)
+                np.random.seed(5)
+                osamples = [off._sample() for _ in range(64)]
+                random.seed(5)
+                np.random.seed(5)
+                ofns = list(off._episode_fns)
+                odraws = []
+                for _ in range(64):
+                    fn = random.choice(ofns)
+                    e = int(fn.stem.split("_")[1])
+                    odraws.append((e, np.random.randint(0, lens[e]) + 1))
+                out["offline_draws"] = np.array(odraws, np.int64)
+                for j in range(5):
+                    out[f"offline_out{j}"] = np.stack([np.asarray(s[j]) for s in osamples])
+    np.savez_compressed(OUT / "replay_reference.npz", **out)
+
+
+if __name__ == "__main__":
+    torch.set_num_threads(8)
+    OUT.mkdir(parents=True, exist_ok=True)
+    ref_utils, ref_replay = load_reference()
+    gen_kat(ref_utils)
+    gen_pbe(ref_utils)
+    gen_knn_dists(ref_utils)
+    gen_proto()
+    gen_replay(ref_replay)
+    for f in sorted(OUT.glob("*.npz")):
+        print(f.name, f.stat().st_size)
