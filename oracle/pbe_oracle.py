@@ -89,10 +89,12 @@ def pbe_reward(source, target, state: RmsState, knn_k, knn_avg, knn_rms, knn_cli
     """
     b1 = source.size(0)
     dists = knn[0] if knn is not None else knn_smallest(source, target, knn_k)[0]
+    # Views, not copies: in the k-th branch the reference hands RMS a stride-k view
+    # (utils.py:302-304) and ATen's mean/var summation order depends on the strides.
     if knn_avg:
-        r = dists.reshape(-1, 1).clone()
+        r = dists.reshape(-1, 1)
     else:
-        r = dists[:, -1].reshape(-1, 1).clone()
+        r = dists[:, -1].reshape(-1, 1)
     if knn_rms:
         r = r / rms_step(state, r).M
     if knn_clip >= 0.0:
