@@ -1,0 +1,16 @@
+"""exorl_b200 — B200-native particle-based kNN intrinsic reward + n-step replay gather.
+
+Drop-in surface of the reference's hot path:
+  RMS, PBE                      <- utils/utils.py:257-319
+  compute_apt_reward            <- the pre-refactor name of the same computation (source != target)
+  proto_knn_reward, proto_enqueue <- agents/unsupervised_learning/proto.py:110-118
+  make_replay_loader, make_offline_replay_loader <- utils/replay_buffer.py:246-277
+"""
+from .knn import RMS, PBE, compute_apt_reward, knn_topk, proto_knn_reward, proto_enqueue
+from .replay import (DeviceReplayBuffer, DeviceReplayLoader, make_replay_loader,
+                     make_offline_replay_loader)
+from .relabel import relabel_apt_reward
+
+__all__ = ["RMS", "PBE", "compute_apt_reward", "knn_topk", "proto_knn_reward", "proto_enqueue",
+           "DeviceReplayBuffer", "DeviceReplayLoader", "make_replay_loader",
+           "make_offline_replay_loader", "relabel_apt_reward"]

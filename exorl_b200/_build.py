@@ -1,0 +1,66 @@
+"""In-tree build of libexorl_b200.so with nvcc for sm_100a (no torch headers involved)."""
+import concurrent.futures
+import os
+import pathlib
+import subprocess
+
+PKG = pathlib.Path(__file__).resolve().parent
+CSRC = PKG / "csrc"
+LIB_DIR = PKG / "lib"
+LIB = LIB_DIR / "libexorl_b200.so"
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-Wall,-Wno-unknown-pragmas",
+         "--expt-relaxed-constexpr"]
+
+
+def _sources():
+    return sorted(CSRC.glob("*.cu"))
+
+
+def _stale(target, deps):
+    if not target.exists():
+        return True
+    t = target.stat().st_mtime
+    return any(d.stat().st_mtime > t for d in deps)
+
+
+def build_library(force=False, verbose=False):
+    """Compile every csrc/*.cu to an object and link the shared library.  Returns its path."""
+    LIB_DIR.mkdir(exist_ok=True)
+    obj_dir = PKG / "build"
+    obj_dir.mkdir(exist_ok=True)
+    headers = list(CSRC.glob("*.cuh")) + [PKG.parent / "include" / "exorl_b200.h"]
+    jobs = []
+    for src in _sources():
+        obj = obj_dir / (src.stem + ".o")
+        if force or _stale(obj, [src] + headers):
+            jobs.append((src, obj))
+
+    def compile_one(job):
+        src, obj = job
+        cmd = [NVCC, *ARCH, *FLAGS, "-c", str(src), "-o", str(obj)]
+        if verbose:
+            cmd.insert(1, "-Xptxas=-v")
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"nvcc failed for {src.name}:\n{r.stdout}\n{r.stderr}")
+        return r.stderr
+
+    with concurrent.futures.ThreadPoolExecutor(max_workers=8) as ex:
+        logs = list(ex.map(compile_one, jobs))
+    if verbose:
+        for log in logs:
+            print(log)
+    objs = [obj_dir / (s.stem + ".o") for s in _sources()]
+    if force or jobs or _stale(LIB, objs):
+        cmd = [NVCC, *ARCH, "-shared", "-o", str(LIB), *map(str, objs), "-cudart", "static"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    return LIB
+
+
+if __name__ == "__main__":
+    import sys
+    print(build_library(force="--force" in sys.argv, verbose="-v" in sys.argv))

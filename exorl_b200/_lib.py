@@ -1,0 +1,118 @@
+"""ctypes binding of libexorl_b200.so (include/exorl_b200.h).  No CPU fallback: if the library is
+missing and cannot be built, every op raises."""
+import ctypes
+import threading
+
+import torch
+
+from . import _build
+
+_c = ctypes
+_i64, _i32, _f32, _f64, _vp, _sz, _u64 = (_c.c_int64, _c.c_int32, _c.c_float, _c.c_double,
+                                          _c.c_void_p, _c.c_size_t, _c.c_uint64)
+
+
+class GatherCol(_c.Structure):
+    _fields_ = [("src", _vp), ("dst", _vp), ("row_bytes", _i64), ("row_offset", _i32)]
+
+
+# name -> (restype, argtypes); mirrors include/exorl_b200.h one to one
+SIGNATURES = {
+    "exb_abi_version": (_c.c_int, []),
+    "exb_last_error": (_c.c_char_p, []),
+    "exb_device_info": (_c.c_int, [_c.POINTER(_c.c_int), _c.POINTER(_c.c_int)]),
+    "exb_knn_exact_workspace_bytes": (_sz, [_i64, _i64, _c.c_int, _c.c_int]),
+    "exb_knn_exact_f32": (_c.c_int, [_vp, _i64, _vp, _i64, _c.c_int, _c.c_int, _i32, _vp, _vp,
+                                     _vp, _sz, _vp]),
+    "exb_knn_prep_f16": (_c.c_int, [_vp, _i64, _c.c_int, _vp, _vp, _vp, _vp, _vp]),
+    "exb_knn_screened_workspace_bytes": (_sz, [_i64, _i64, _c.c_int, _c.c_int]),
+    "exb_knn_screened_f32": (_c.c_int, [_vp, _i64, _vp, _i64, _c.c_int, _c.c_int, _i32,
+                                        _c.c_int, _vp, _vp, _vp, _sz, _vp]),
+    "exb_knn_screened_status_sync": (_c.c_int, [_vp, _c.POINTER(_i32), _vp]),
+    "exb_topk_merge": (_c.c_int, [_vp, _vp, _c.c_int, _i64, _c.c_int, _vp, _vp, _vp]),
+    "exb_pbe_workspace_bytes": (_sz, [_i64, _c.c_int]),
+    "exb_pbe_workspace_init": (_c.c_int, [_vp, _sz, _vp]),
+    "exb_pbe_reward": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _c.c_int, _f32, _vp, _vp, _f64,
+                                  _vp, _vp, _vp, _vp, _sz, _vp]),
+    "exb_pbe_moments": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _vp, _vp, _sz, _vp]),
+    "exb_pbe_finish": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _c.c_int, _f32, _vp, _vp, _vp,
+                                  _f64, _vp, _vp, _vp, _vp]),
+    "exb_rms_update": (_c.c_int, [_vp, _i64, _vp, _vp, _f64, _vp, _vp, _vp, _sz, _vp]),
+    "exb_take_kth": (_c.c_int, [_vp, _i64, _c.c_int, _vp, _vp]),
+    "exb_replay_gather": (_c.c_int, [_vp, _i64, _c.POINTER(GatherCol), _c.c_int, _vp, _vp,
+                                     _c.c_int, _c.c_int, _f32, _vp, _vp, _vp]),
+    "exb_replay_draw": (_c.c_int, [_u64, _u64, _vp, _vp, _i64, _c.c_int, _i64, _vp, _vp, _vp]),
+}
+
+EXB_OK, EXB_EINVAL, EXB_EKRANGE, EXB_EUNSUPPORTED, EXB_ECUDA, EXB_EFALLBACK = range(6)
+MAX_K = 32
+SCREEN_MAX_K = 16
+SCREEN_MAX_DIM = 512
+
+_lock = threading.Lock()
+_lib = None
+
+
+def load():
+    """Return the loaded library, building it in-tree first if the .so is absent."""
+    global _lib
+    with _lock:
+        if _lib is None:
+            path = _build.LIB
+            if not path.exists():
+                try:
+                    _build.build_library()
+                except Exception as e:  # no nvcc on this machine
+                    raise RuntimeError(
+                        f"exorl_b200: {path} is missing and could not be built ({e}); "
+                        "run `python -c 'import __graft_entry__ as g; g.build()'`") from e
+            lib = _c.CDLL(str(path))
+            for name, (res, args) in SIGNATURES.items():
+                fn = getattr(lib, name)   # AttributeError if the ABI drifted: fail loudly
+                fn.restype, fn.argtypes = res, args
+            _lib = lib
+    return _lib
+
+
+def check(rc):
+    if rc == EXB_OK:
+        return
+    msg = load().exb_last_error().decode("utf-8", "replace")
+    if rc == EXB_EKRANGE:
+        # same exception type/text as torch.topk in the reference (utils/utils.py:297)
+        raise RuntimeError("selected index k out of range")
+    if rc in (EXB_EINVAL, EXB_EUNSUPPORTED):
+        raise ValueError(f"exorl_b200: {msg}")
+    raise RuntimeError(f"exorl_b200 (status {rc}): {msg}")
+
+
+def stream_ptr(device=None):
+    return _c.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def ptr(t):
+    return _c.c_void_p(t.data_ptr()) if t is not None else _c.c_void_p(0)
+
+
+class Workspace:
+    """Grow-only device scratch, one per (device, purpose); reuse is stream-ordered."""
+    _cache = {}
+
+    @classmethod
+    def get(cls, device, key, nbytes, zero_init=False):
+        dev = torch.device(device)
+        k = (dev.index if dev.index is not None else torch.cuda.current_device(), key)
+        buf = cls._cache.get(k)
+        fresh = buf is None or buf.numel() < nbytes
+        if fresh:
+            buf = torch.empty(max(int(nbytes), 1024), dtype=torch.uint8, device=dev)
+            if zero_init:
+                buf.zero_()
+            cls._cache[k] = buf
+        return buf, fresh
+
+
+def require_cuda(t, name):
+    if not (isinstance(t, torch.Tensor) and t.is_cuda):
+        raise RuntimeError(f"exorl_b200: `{name}` must be a CUDA tensor — this implementation has "
+                           "no CPU path (use the reference for CPU tensors)")

@@ -1,0 +1,56 @@
+// Shared helpers for the exorl_b200 CUDA sources (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include "../../include/exorl_b200.h"
+
+namespace exb {
+
+void set_error(const char* fmt, ...);
+
+#define EXB_CHECK_ARG(cond, ...)            \
+  do {                                      \
+    if (!(cond)) {                          \
+      exb::set_error(__VA_ARGS__);          \
+      return EXB_EINVAL;                    \
+    }                                       \
+  } while (0)
+
+#define EXB_CUDA(call)                                                              \
+  do {                                                                              \
+    cudaError_t e_ = (call);                                                        \
+    if (e_ != cudaSuccess) {                                                        \
+      exb::set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call,                   \
+                     cudaGetErrorString(e_));                                       \
+      return EXB_ECUDA;                                                             \
+    }                                                                               \
+  } while (0)
+
+#define EXB_LAUNCH_CHECK() EXB_CUDA(cudaGetLastError())
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// Bump allocator over a caller-provided workspace.
+struct Carver {
+  char* base;
+  size_t off;
+  explicit Carver(void* p) : base(static_cast<char*>(p)), off(0) {}
+  template <typename T>
+  T* take(size_t count) {
+    off = align_up(off, 256);
+    T* r = reinterpret_cast<T*>(base + off);
+    off += count * sizeof(T);
+    return r;
+  }
+};
+
+int sm_count();
+
+// (value, index) ordering used everywhere: smaller value first, then smaller index.
+__device__ __forceinline__ bool pair_less(float va, int ia, float vb, int ib) {
+  return va < vb || (va == vb && ia < ib);
+}
+
+}  // namespace exb

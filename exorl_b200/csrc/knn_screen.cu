@@ -1,0 +1,778 @@
+// Screened kNN for sm_100a: TMA-fed tcgen05 GEMM with the accumulator filtered straight out of
+// TMEM against a per-row running threshold, then an exact fp32 recompute of the survivors.
+//
+// Replaces /root/reference/utils/utils.py:293-300 (and proto.py:115-116) with the same results
+// as the exact kernel (knn_exact.cu) at tensor-core speed.  Nothing of size nq x nb reaches HBM.
+//
+// Math.  With a^ = fp16(a), b^ = fp16(b):  ||a^ - b^||^2 = 2 (ha - s),  s = a^.b^ - hb,
+// ha = ||a^||^2/2, hb = ||b^||^2/2.  The GEMM gives a^.b^ (fp32 accumulate), so "nearest" =
+// "largest s".  The true distance obeys | ||a-b|| - ||a^-b^|| | <= ea + eb with
+// ea = ||a - a^||, eb = ||b - b^|| (triangle inequality), both computed exactly per row by the
+// prep kernel.  While scanning, each query row keeps a descending list of scores; with tk its
+// k-th largest score, every bank row that can still belong to the true top-k satisfies
+//     s >= tkeep = ha - (sqrt(2(ha - tk) + 2 dl) + 2(ea + EB))^2 / 2 - dl          
+// (EB = max eb, dl bounds the fp32 accumulation error).  The list keeps everything >= tkeep; if
+// it would need more than SCREEN_CAP slots the row is marked undecided and recomputed by the
+// exact kernel.  The survivors' distances are then recomputed in fp32 direct-difference form,
+// so the returned distances/indices are those of the exact path.
+//
+// Kernel structure (one CTA per 128 query rows x a range of 256-row bank tiles):
+//   warp 0      TMA producer: query tile once (resident in smem), bank tiles through a ring
+//   warp 1      TMEM allocator + single-thread tcgen05.mma issuer (M=128, N=256, K=16)
+//   warps 2-5   epilogue: tcgen05.ld 32 columns at a time (thread = TMEM lane = query row),
+//               subtract hb, compare with tkeep; inserts are rare and go to a per-thread
+//               sorted list in shared memory
+//   two 256-column TMEM accumulators so the MMA of tile t+1 overlaps the filter of tile t.
+#include "common.cuh"
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <float.h>
+#include <limits.h>
+#include <math.h>
+
+namespace exb {
+
+int exact_splits(int64_t nq, int64_t nb, int k);
+int launch_exact(const float* src, int64_t nq, const float* bank, int64_t nb, int dim, int k,
+                 int idx_base, float* out_dist, int* out_idx, float* part_d2, int* part_idx,
+                 int splits, const int* row_list, const int* row_count, int64_t max_slots,
+                 cudaStream_t st);
+
+constexpr int SCR_M = 128;          // query rows per CTA (UMMA M)
+constexpr int SCR_N = 256;          // bank rows per tile (UMMA N)
+constexpr int SCR_KC = 64;          // fp16 elements per K chunk = one 128-byte swizzle row
+constexpr int SCR_CAP = 24;         // list slots per (row, split)
+constexpr int SCR_MAX_K = 16;       // k supported by the screened path
+constexpr int SCR_THREADS = 192;
+constexpr int SCR_A_CHUNK_BYTES = SCR_M * SCR_KC * 2;   // 16 KB
+constexpr int SCR_B_STAGE_BYTES = SCR_N * SCR_KC * 2;   // 32 KB
+constexpr int SCR_MAX_STAGES = 8;
+constexpr int SCR_SMEM_LIMIT = 232448;                  // 227 KB
+constexpr int FALLBACK_CAP = 16384;
+constexpr int FALLBACK_SPLITS = 16;
+
+// ------------------------------------------------------------------------------------------
+// PTX wrappers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra WAIT_DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1,
+                                            uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
+      "l"(map), "r"(c0), "r"(c1), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc_512(uint32_t smem_dst) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(
+      smem_dst));
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+}
+__device__ __forceinline__ void tmem_dealloc_512(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(taddr));
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                         uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                   bar)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+        "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]),
+        "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]),
+        "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {
+  uint32_t r;
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r) : "r"(taddr)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ void tmem_ld_wait() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major, 128-byte swizzle shared-memory matrix descriptor (cute::UMMA::SmemDescriptor layout):
+// start>>4 [0,14), LBO>>4 [16,30) (unused for swizzled K-major, 1), SBO>>4 [32,46) = 1024 B
+// between 8-row groups, version 1 at [46,48), layout SWIZZLE_128B = 2 at [61,64).
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
+  return (uint64_t)((saddr >> 4) & 0x3FFF) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) |
+         (1ull << 46) | (2ull << 61);
+}
+// kind::f16 instruction descriptor: D=F32 (bit 4), A=B=F16 (0), K-major both, N>>3 at [17,23),
+// M>>4 at [24,29).
+constexpr uint32_t SCR_IDESC = (1u << 4) | ((uint32_t)(SCR_N >> 3) << 17) |
+                               ((uint32_t)(SCR_M >> 4) << 24);
+
+// ------------------------------------------------------------------------------------------
+// prep: fp32 rows -> padded fp16 operand, half squared norm of the rounded row, rounding error
+// ------------------------------------------------------------------------------------------
+struct PrepScalars {   // device struct, zeroed per call
+  float err_max;       // max_j ||x_j - fp16(x_j)||
+  float hn_max;        // max_j ||fp16(x_j)||^2 / 2
+  int range_flag;      // a value does not fit fp16 / is not finite
+  int pad;
+};
+
+__global__ void __launch_bounds__(256)
+knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
+                __half* __restrict__ out, float* __restrict__ half_norm,
+                float* __restrict__ round_err, PrepScalars* __restrict__ sc) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= n) return;
+  const float* xr = x + row * dim;
+  __half* orow = out + row * dpad;
+  double nn = 0.0, ee = 0.0;
+  bool bad = false;
+  for (int c = lane; c < dpad; c += 32) {
+    float v = (c < dim) ? xr[c] : 0.f;
+    bad |= !(fabsf(v) <= 65504.f);
+    const __half h = __float2half_rn(v);
+    const float hf = __half2float(h);
+    orow[c] = h;
+    nn += (double)hf * (double)hf;
+    const double e = (double)v - (double)hf;
+    ee += e * e;
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    nn += __shfl_xor_sync(0xffffffffu, nn, off);
+    ee += __shfl_xor_sync(0xffffffffu, ee, off);
+  }
+  bad = __any_sync(0xffffffffu, bad);
+  if (lane == 0) {
+    const float hn = (float)(0.5 * nn);
+    // round the error norm up so the bound stays rigorous after the fp32 conversion
+    const float er = __double2float_ru(sqrt(ee));
+    half_norm[row] = hn;
+    round_err[row] = er;
+    atomicMax(reinterpret_cast<int*>(&sc->err_max), __float_as_int(er));
+    atomicMax(reinterpret_cast<int*>(&sc->hn_max), __float_as_int(hn));
+    if (bad) atomicExch(&sc->range_flag, 1);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// screening kernel
+// ------------------------------------------------------------------------------------------
+struct ScreenParams {
+  const float* ha;        // [nq] query half norms
+  const float* ea;        // [nq] query rounding errors
+  const float* hb;        // [nb] bank half norms
+  const PrepScalars* bsc; // bank scalars (EB, HBmax)
+  int64_t nq, nb;
+  int nkc;                // K chunks of 64
+  int n_tiles;            // bank tiles of 256
+  int tiles_per_split;
+  int splits;
+  int k;
+  int stages;
+  int* cand_idx;          // [nq, splits, CAP]
+  int* cand_cnt;          // [nq, splits]; -1 = undecided
+};
+
+struct ListState {
+  int n;
+  float tk, tkeep, dropped;
+  float ha, e2, dl;
+};
+
+__device__ __forceinline__ float keep_threshold(const ListState& s) {
+  // DESIGN.md §4; evaluated conservatively (round the kept region outwards)
+  const float dk = sqrtf(fmaxf(2.f * (s.ha - s.tk), 0.f) + 2.f * s.dl);
+  const float bound = dk + s.e2;
+  float t = s.ha - 0.5f * bound * bound - s.dl;
+  t -= 4e-6f * (fabsf(s.ha) + fabsf(s.tk));
+  return t;
+}
+
+__device__ __forceinline__ void list_insert(ListState& s, float* lv, int* li, float v, int j,
+                                            int k) {
+  // lv/li: this thread's column of the [CAP][128] arrays (stride 128), sorted descending
+  int p;
+  if (s.n < SCR_CAP) {
+    p = s.n++;
+  } else {
+    const float last = lv[(SCR_CAP - 1) * SCR_M];
+    if (v <= last) {
+      s.dropped = fmaxf(s.dropped, v);
+      p = -1;
+    } else {
+      s.dropped = fmaxf(s.dropped, last);
+      p = SCR_CAP - 1;
+    }
+  }
+  if (p >= 0) {
+    while (p > 0 && lv[(p - 1) * SCR_M] < v) {
+      lv[p * SCR_M] = lv[(p - 1) * SCR_M];
+      li[p * SCR_M] = li[(p - 1) * SCR_M];
+      --p;
+    }
+    lv[p * SCR_M] = v;
+    li[p * SCR_M] = j;
+  }
+  if (s.n >= k) {
+    s.tk = lv[(k - 1) * SCR_M];
+    s.tkeep = keep_threshold(s);
+    while (s.n > k && lv[(s.n - 1) * SCR_M] < s.tkeep) --s.n;
+  }
+}
+
+__global__ void __launch_bounds__(SCR_THREADS, 1)
+knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
+                  const __grid_constant__ CUtensorMap tmap_b, const ScreenParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  // carve (1024-byte aligned for SWIZZLE_128B)
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t* sm = smem_raw + (base - raw);
+  const int nkc = p.nkc, stages = p.stages;
+  const uint32_t a_off = 0;
+  const uint32_t b_off = a_off + (uint32_t)nkc * SCR_A_CHUNK_BYTES;
+  const uint32_t lv_off = b_off + (uint32_t)stages * SCR_B_STAGE_BYTES;
+  const uint32_t li_off = lv_off + SCR_CAP * SCR_M * 4;
+  const uint32_t hn_off = li_off + SCR_CAP * SCR_M * 4;
+  const uint32_t bar_off = hn_off + 2 * SCR_N * 4;
+  float* s_lv = reinterpret_cast<float*>(sm + lv_off);
+  int* s_li = reinterpret_cast<int*>(sm + li_off);
+  float* s_hn = reinterpret_cast<float*>(sm + hn_off);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sm + bar_off);
+  // barrier slots: [0, S) full, [S, 2S) empty, 2S a_full, 2S+1.. tmem_full[2], tmem_empty[2]
+  const uint32_t bar_base = base + bar_off;
+  auto bar_full = [&](int s) { return bar_base + 8u * s; };
+  auto bar_empty = [&](int s) { return bar_base + 8u * (SCR_MAX_STAGES + s); };
+  const uint32_t bar_a = bar_base + 8u * (2 * SCR_MAX_STAGES);
+  auto bar_tfull = [&](int s) { return bar_base + 8u * (2 * SCR_MAX_STAGES + 1 + s); };
+  auto bar_tempty = [&](int s) { return bar_base + 8u * (2 * SCR_MAX_STAGES + 3 + s); };
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 2 * SCR_MAX_STAGES + 5);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m_tile = blockIdx.x, split = blockIdx.y;
+  const int t_begin = split * p.tiles_per_split;
+  const int t_end = min(p.n_tiles, t_begin + p.tiles_per_split);
+  const int n_local = max(t_end - t_begin, 0);
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmap_q);
+    tma_prefetch_desc(&tmap_b);
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(bar_full(s), 1);
+      mbar_init(bar_empty(s), 1);
+    }
+    mbar_init(bar_a, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar_tfull(s), 1);
+      mbar_init(bar_tempty(s), 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc_512(smem_u32(s_tmem));
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0 && n_local > 0) {
+      mbar_expect_tx(bar_a, (uint32_t)nkc * SCR_A_CHUNK_BYTES);
+      for (int kc = 0; kc < nkc; ++kc)
+        tma_load_2d(base + a_off + kc * SCR_A_CHUNK_BYTES, &tmap_q, kc * SCR_KC,
+                    m_tile * SCR_M, bar_a);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = t_begin; t < t_end; ++t) {
+        for (int kc = 0; kc < nkc; ++kc) {
+          mbar_wait(bar_empty(stage), phase ^ 1u);
+          mbar_expect_tx(bar_full(stage), SCR_B_STAGE_BYTES);
+          tma_load_2d(base + b_off + stage * SCR_B_STAGE_BYTES, &tmap_b, kc * SCR_KC, t * SCR_N,
+                      bar_full(stage));
+          if (++stage == stages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0 && n_local > 0) {
+      mbar_wait(bar_a, 0);
+      tc_fence_after();
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int j = 0; j < n_local; ++j) {
+        const int as = j & 1;
+        mbar_wait(bar_tempty(as), (((uint32_t)j >> 1) & 1u) ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)as * SCR_N;
+        for (int kc = 0; kc < nkc; ++kc) {
+          mbar_wait(bar_full(stage), phase);
+          tc_fence_after();
+          const uint64_t adesc = make_sw128_desc(base + a_off + kc * SCR_A_CHUNK_BYTES);
+          const uint64_t bdesc = make_sw128_desc(base + b_off + stage * SCR_B_STAGE_BYTES);
+#pragma unroll
+          for (int ki = 0; ki < SCR_KC / 16; ++ki) {
+            // advance 16 fp16 = 32 bytes inside the swizzle atom: +2 in the (addr >> 4) field
+            umma_f16(d_tmem, adesc + (uint64_t)(2 * ki), bdesc + (uint64_t)(2 * ki), SCR_IDESC,
+                     (kc | ki) != 0 ? 1u : 0u);
+          }
+          umma_commit(bar_empty(stage));
+          if (++stage == stages) { stage = 0; phase ^= 1u; }
+        }
+        umma_commit(bar_tfull(as));
+      }
+    }
+  } else {
+    // ===================== epilogue: filter accumulators =====================
+    const int quad = warp & 3;                    // TMEM lane quadrant this warp may access
+    const int e = quad * 32 + lane;               // row inside the tile
+    const int et = (warp - 2) * 32 + lane;        // 0..127 linear epilogue thread id
+    const int64_t row = (int64_t)m_tile * SCR_M + e;
+    const bool row_ok = row < p.nq;
+    float* lv = s_lv + e;
+    int* li = s_li + e;
+    ListState st;
+    st.n = 0;
+    st.tk = -FLT_MAX;
+    st.tkeep = -FLT_MAX;
+    st.dropped = -FLT_MAX;
+    st.ha = row_ok ? p.ha[row] : 0.f;
+    const float eb_max = p.bsc->err_max, hb_max = p.bsc->hn_max;
+    st.e2 = 2.f * ((row_ok ? p.ea[row] : 0.f) + eb_max);
+    st.dl = (st.ha + hb_max) * (1.0f / 65536.0f);
+    const int k = p.k;
+
+    auto load_hn = [&](int t, float& h0, float& h1) {
+      const int64_t c0 = (int64_t)t * SCR_N + 2 * et;
+      h0 = (c0 < p.nb) ? p.hb[c0] : INFINITY;
+      h1 = (c0 + 1 < p.nb) ? p.hb[c0 + 1] : INFINITY;
+    };
+    float h0 = 0.f, h1 = 0.f;
+    if (n_local > 0) load_hn(t_begin, h0, h1);
+
+    for (int j = 0; j < n_local; ++j) {
+      const int t = t_begin + j;
+      const int as = j & 1;
+      float* hn = s_hn + as * SCR_N;
+      hn[2 * et] = h0;
+      hn[2 * et + 1] = h1;
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (j + 1 < n_local) load_hn(t + 1, h0, h1);
+      mbar_wait(bar_tfull(as), ((uint32_t)j >> 1) & 1u);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)as * SCR_N;
+#pragma unroll 1
+      for (int ch = 0; ch < SCR_N / 32; ++ch) {
+        uint32_t r[32];
+        tmem_ld32(t_row + ch * 32, r);
+        tmem_ld_wait();
+        const float4* hn4 = reinterpret_cast<const float4*>(hn + ch * 32);
+        float m = -INFINITY;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const float4 h = hn4[q];
+          m = fmaxf(m, fmaxf(fmaxf(__uint_as_float(r[4 * q]) - h.x,
+                                   __uint_as_float(r[4 * q + 1]) - h.y),
+                             fmaxf(__uint_as_float(r[4 * q + 2]) - h.z,
+                                   __uint_as_float(r[4 * q + 3]) - h.w)));
+        }
+        if (__any_sync(0xffffffffu, m >= st.tkeep)) {
+          // slow path: union of hit columns over the warp, revisited with uniform control flow
+          uint32_t mask = 0;
+#pragma unroll
+          for (int c = 0; c < 32; ++c)
+            mask |= ((__uint_as_float(r[c]) - hn[ch * 32 + c]) >= st.tkeep ? 1u : 0u) << c;
+          uint32_t wm = __reduce_or_sync(0xffffffffu, mask);
+          while (wm) {
+            const int c = __ffs(wm) - 1;
+            wm &= wm - 1;
+            const float acc = __uint_as_float(tmem_ld1(t_row + ch * 32 + c));
+            tmem_ld_wait();
+            const float s = acc - hn[ch * 32 + c];
+            if (s >= st.tkeep) list_insert(st, lv, li, s, t * SCR_N + ch * 32 + c, k);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_tempty(as));
+    }
+
+    if (row_ok) {
+      const int64_t o = row * p.splits + split;
+      const bool overflow = st.dropped > -FLT_MAX && st.dropped >= st.tkeep;
+      p.cand_cnt[o] = overflow ? -1 : st.n;
+      for (int c = 0; c < st.n; ++c) p.cand_idx[o * SCR_CAP + c] = li[c * SCR_M];
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_512(tmem_base);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// rerank: exact fp32 direct-difference distance of the survivors, one warp per query row
+// ------------------------------------------------------------------------------------------
+struct RerankStatus {   // device, zeroed per call
+  int n_fallback;
+  int invalid;
+  unsigned long long pairs;
+};
+
+__global__ void __launch_bounds__(256)
+knn_rerank_kernel(const float* __restrict__ Q, int64_t nq, const float* __restrict__ B, int dim,
+                  int k, int idx_base, const int* __restrict__ cand_idx,
+                  const int* __restrict__ cand_cnt, int splits, const PrepScalars* qsc,
+                  const PrepScalars* bsc, float* __restrict__ out_dist, int* __restrict__ out_idx,
+                  int* __restrict__ fallback_rows, int fallback_cap, RerankStatus* status) {
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= nq) return;
+  bool undecided = (qsc->range_flag | bsc->range_flag) != 0;
+
+  float q[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const int c = lane + 32 * i;
+    q[i] = (c < dim) ? Q[row * dim + c] : 0.f;
+  }
+  float lv = FLT_MAX;
+  int li = INT_MAX;
+  int total = 0;
+  for (int s = 0; s < splits && !undecided; ++s) {
+    const int cnt = cand_cnt[row * splits + s];
+    if (cnt < 0) { undecided = true; break; }
+    const int* ci = cand_idx + (row * splits + s) * SCR_CAP;
+    total += cnt;
+    for (int c0 = 0; c0 < cnt; c0 += 2) {
+      const int j0 = ci[c0];
+      const bool two = (c0 + 1) < cnt;
+      const int j1 = two ? ci[c0 + 1] : j0;
+      const float* b0 = B + (int64_t)j0 * dim;
+      const float* b1 = B + (int64_t)j1 * dim;
+      float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const int c = lane + 32 * i;
+        if (c < dim) {
+          const float d0 = q[i] - __ldg(b0 + c);
+          const float d1 = q[i] - __ldg(b1 + c);
+          a0 = fmaf(d0, d0, a0);
+          a1 = fmaf(d1, d1, a1);
+        }
+      }
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) {
+        a0 += __shfl_xor_sync(full, a0, off);
+        a1 += __shfl_xor_sync(full, a1, off);
+      }
+      for (int u = 0; u < (two ? 2 : 1); ++u) {
+        const float v = u ? a1 : a0;
+        const int j = u ? j1 : j0;
+        const float thr_v = __shfl_sync(full, lv, k - 1);
+        const int thr_i = __shfl_sync(full, li, k - 1);
+        if (pair_less(v, j, thr_v, thr_i)) {
+          const int pos = __popc(__ballot_sync(full, pair_less(lv, li, v, j)));
+          const float up_v = __shfl_up_sync(full, lv, 1);
+          const int up_i = __shfl_up_sync(full, li, 1);
+          if (lane == pos) { lv = v; li = j; }
+          else if (lane > pos) { lv = up_v; li = up_i; }
+        }
+      }
+    }
+  }
+  if (!undecided && total < k) undecided = true;
+  if (undecided) {
+    if (lane == 0) {
+      const int pos = atomicAdd(&status->n_fallback, 1);
+      if (pos < fallback_cap) fallback_rows[pos] = (int)row;
+      else status->invalid = 1;
+    }
+    return;
+  }
+  if (lane == 0) atomicAdd(&status->pairs, (unsigned long long)total);
+  if (lane < k) {
+    out_dist[row * k + lane] = sqrtf(lv);
+    out_idx[row * k + lane] = li + idx_base;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) ==
+            cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// fp16 [rows, dpad] row-major -> tiles of box_rows x 64 columns, 128-byte swizzle, zero OOB fill
+static int make_tmap(CUtensorMap* map, const void* ptr, int64_t rows, int dpad, int box_rows) {
+  EncodeTiledFn enc = encode_fn();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled entry point unavailable");
+    return EXB_ECUDA;
+  }
+  const cuuint64_t dims[2] = {(cuuint64_t)dpad, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)dpad * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)SCR_KC, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(ptr), dims,
+                         strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return EXB_ECUDA;
+  }
+  return EXB_OK;
+}
+
+static inline int dim_pad(int dim) { return (dim + SCR_KC - 1) / SCR_KC * SCR_KC; }
+
+struct ScreenPlan {
+  int dpad, nkc, n_tiles, m_tiles, splits, tiles_per_split, stages;
+  size_t smem;
+  int fb_cap, fb_splits;
+};
+
+static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
+  if (dim < 1 || dim > EXB_SCREEN_MAX_DIM || k < 1 || k > SCR_MAX_K || nq < 1 || nb < 1)
+    return false;
+  pl->dpad = dim_pad(dim);
+  pl->nkc = pl->dpad / SCR_KC;
+  pl->n_tiles = (int)((nb + SCR_N - 1) / SCR_N);
+  pl->m_tiles = (int)((nq + SCR_M - 1) / SCR_M);
+  int splits = sm_count() / pl->m_tiles;
+  if (splits > pl->n_tiles) splits = pl->n_tiles;
+  if (splits > 16) splits = 16;
+  if (splits < 1) splits = 1;
+  pl->tiles_per_split = (pl->n_tiles + splits - 1) / splits;
+  pl->splits = (pl->n_tiles + pl->tiles_per_split - 1) / pl->tiles_per_split;
+  const size_t fixed = (size_t)pl->nkc * SCR_A_CHUNK_BYTES + 2 * SCR_CAP * SCR_M * 4 +
+                       2 * SCR_N * 4 + (2 * SCR_MAX_STAGES + 5) * 8 + 16 + 1024;
+  int stages = (int)((SCR_SMEM_LIMIT - fixed) / SCR_B_STAGE_BYTES);
+  if (stages > SCR_MAX_STAGES) stages = SCR_MAX_STAGES;
+  if (stages < 2) return false;
+  pl->stages = stages;
+  pl->smem = fixed + (size_t)stages * SCR_B_STAGE_BYTES;
+  pl->fb_cap = (int)(nq < FALLBACK_CAP ? nq : FALLBACK_CAP);
+  int fbs = (int)((nb + 127) / 128);
+  if (fbs > FALLBACK_SPLITS) fbs = FALLBACK_SPLITS;
+  if (fbs * k > 512) fbs = 512 / k;
+  pl->fb_splits = fbs < 1 ? 1 : fbs;
+  return true;
+}
+
+struct ScreenWs {
+  RerankStatus* status;
+  PrepScalars* qsc;
+  PrepScalars* bsc;
+  __half* q16;
+  __half* b16;
+  float *ha, *ea, *hb, *eb;
+  int *cand_idx, *cand_cnt, *fb_rows;
+  float* fb_d2;
+  int* fb_idx;
+};
+
+static size_t carve_screen(void* ws, int64_t nq, int64_t nb, const ScreenPlan& pl, int k,
+                           bool same, ScreenWs* o) {
+  Carver cv(ws ? ws : reinterpret_cast<void*>(256));  // dry run computes the size only
+  o->status = cv.take<RerankStatus>(1);
+  o->qsc = cv.take<PrepScalars>(1);
+  o->bsc = cv.take<PrepScalars>(1);
+  o->b16 = cv.take<__half>((size_t)nb * pl.dpad);
+  o->q16 = same ? o->b16 : cv.take<__half>((size_t)nq * pl.dpad);
+  o->hb = cv.take<float>(nb);
+  o->eb = cv.take<float>(nb);
+  o->ha = same ? o->hb : cv.take<float>(nq);
+  o->ea = same ? o->eb : cv.take<float>(nq);
+  o->cand_idx = cv.take<int>((size_t)nq * pl.splits * SCR_CAP);
+  o->cand_cnt = cv.take<int>((size_t)nq * pl.splits);
+  o->fb_rows = cv.take<int>(pl.fb_cap);
+  o->fb_d2 = cv.take<float>((size_t)pl.fb_cap * pl.fb_splits * k);
+  o->fb_idx = cv.take<int>((size_t)pl.fb_cap * pl.fb_splits * k);
+  return cv.off + 256;
+}
+
+static int launch_prep(const float* x, int64_t n, int dim, int dpad, __half* out, float* hn,
+                       float* er, PrepScalars* sc, cudaStream_t st) {
+  knn_prep_kernel<<<(unsigned)((n + 7) / 8), 256, 0, st>>>(x, n, dim, dpad, out, hn, er, sc);
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}
+
+}  // namespace exb
+
+using namespace exb;
+
+extern "C" int exb_knn_prep_f16(const float* x, int64_t n, int dim, void* out_f16,
+                                float* half_norm, float* round_err, float* scalars,
+                                exb_stream_t stream) {
+  EXB_CHECK_ARG(x && out_f16 && half_norm && round_err && scalars && n > 0 && dim > 0,
+                "bad arguments");
+  return launch_prep(x, n, dim, dim_pad(dim), static_cast<__half*>(out_f16), half_norm,
+                     round_err, reinterpret_cast<PrepScalars*>(scalars), (cudaStream_t)stream);
+}
+
+extern "C" size_t exb_knn_screened_workspace_bytes(int64_t nq, int64_t nb, int dim, int k) {
+  ScreenPlan pl;
+  if (!make_plan(nq, nb, dim, k, &pl)) return 0;
+  ScreenWs w;
+  // worst case: src and bank distinct
+  return carve_screen(nullptr, nq, nb, pl, k, false, &w);
+}
+
+extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* bank, int64_t nb,
+                                    int dim, int k, int32_t idx_base, int src_is_bank,
+                                    float* out_dist, int32_t* out_idx, void* workspace,
+                                    size_t workspace_bytes, exb_stream_t stream) {
+  EXB_CHECK_ARG(src && bank && out_dist && out_idx, "null pointer");
+  EXB_CHECK_ARG(nq > 0 && nb > 0 && nq < (1LL << 31) && nb < (1LL << 31), "bad row counts");
+  if (k > nb) {
+    set_error("selected index k out of range (k=%d > bank rows=%lld)", k, (long long)nb);
+    return EXB_EKRANGE;
+  }
+  ScreenPlan pl;
+  if (!make_plan(nq, nb, dim, k, &pl)) {
+    set_error("screened kNN supports 1 <= dim <= %d and 1 <= k <= %d (got dim=%d k=%d)",
+              EXB_SCREEN_MAX_DIM, SCR_MAX_K, dim, k);
+    return EXB_EUNSUPPORTED;
+  }
+  const bool same = src_is_bank && src == bank && nq == nb;
+  ScreenWs w;
+  const size_t need = carve_screen(nullptr, nq, nb, pl, k, same, &w);
+  EXB_CHECK_ARG(workspace && workspace_bytes >= need, "workspace too small: %zu < %zu",
+                workspace_bytes, need);
+  EXB_CHECK_ARG(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  carve_screen(workspace, nq, nb, pl, k, same, &w);
+  cudaStream_t st = (cudaStream_t)stream;
+
+  // header (status + scalars) is the first 3 x 256 bytes
+  EXB_CUDA(cudaMemsetAsync(workspace, 0, 768, st));
+  int rc = launch_prep(bank, nb, dim, pl.dpad, w.b16, w.hb, w.eb, w.bsc, st);
+  if (rc) return rc;
+  if (!same) {
+    rc = launch_prep(src, nq, dim, pl.dpad, w.q16, w.ha, w.ea, w.qsc, st);
+    if (rc) return rc;
+  }
+
+  CUtensorMap tq, tb;
+  rc = make_tmap(&tq, w.q16, nq, pl.dpad, SCR_M);
+  if (rc) return rc;
+  rc = make_tmap(&tb, w.b16, nb, pl.dpad, SCR_N);
+  if (rc) return rc;
+
+  static bool attr_set = false;
+  if (!attr_set) {
+    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  SCR_SMEM_LIMIT));
+    attr_set = true;
+  }
+  ScreenParams sp;
+  sp.ha = w.ha; sp.ea = w.ea; sp.hb = w.hb; sp.bsc = w.bsc;
+  sp.nq = nq; sp.nb = nb; sp.nkc = pl.nkc; sp.n_tiles = pl.n_tiles;
+  sp.tiles_per_split = pl.tiles_per_split; sp.splits = pl.splits; sp.k = k;
+  sp.stages = pl.stages; sp.cand_idx = w.cand_idx; sp.cand_cnt = w.cand_cnt;
+  dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
+  knn_screen_kernel<<<grid, SCR_THREADS, pl.smem, st>>>(tq, tb, sp);
+  EXB_LAUNCH_CHECK();
+
+  knn_rerank_kernel<<<(unsigned)((nq + 7) / 8), 256, 0, st>>>(
+      src, nq, bank, dim, k, idx_base, w.cand_idx, w.cand_cnt, pl.splits, same ? w.bsc : w.qsc,
+      w.bsc, out_dist, out_idx, w.fb_rows, pl.fb_cap, w.status);
+  EXB_LAUNCH_CHECK();
+
+  // undecided rows -> exact kernel, indirect through the device-side row list / count
+  return launch_exact(src, nq, bank, nb, dim, k, idx_base, out_dist, out_idx, w.fb_d2, w.fb_idx,
+                      pl.fb_splits, w.fb_rows, &w.status->n_fallback, pl.fb_cap, st);
+}
+
+extern "C" int exb_knn_screened_status_sync(const void* workspace, int32_t host_status[4],
+                                            exb_stream_t stream) {
+  EXB_CHECK_ARG(workspace && host_status, "null pointer");
+  RerankStatus s;
+  EXB_CUDA(cudaMemcpyAsync(&s, workspace, sizeof(s), cudaMemcpyDeviceToHost,
+                           (cudaStream_t)stream));
+  EXB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  host_status[0] = s.n_fallback;
+  host_status[1] = s.invalid;
+  host_status[2] = (int32_t)(s.pairs > 0x7fffffffULL ? 0x7fffffff : s.pairs);
+  host_status[3] = (int32_t)(s.pairs >> 31);
+  return EXB_OK;
+}

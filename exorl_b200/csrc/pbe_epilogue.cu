@@ -1,0 +1,318 @@
+// Running-moment (RMS) update + PBE reward epilogue.
+//
+// Replaces /root/reference/utils/utils.py:264-276 (RMS.__call__: batch mean, unbiased variance,
+// Chan combination with the carried M, S, n) and :301-318 (divide by the UPDATED mean, clip,
+// mean over k, log(1 + r)), which the reference runs as ~25 launch-bound ATen kernels.
+//
+// State convention (include/exorl_b200.h): M and S are the fp32 (1,) tensors the reference
+// exposes, n is the python float passed by value.  Sums are accumulated in fp64 and the updated
+// M, S are rounded to fp32, like the reference's fp32 tensors.
+#include "common.cuh"
+#include <math.h>
+
+namespace exb {
+
+constexpr int PBE_THREADS = 256;
+constexpr int PBE_SMALL_THREADS = 1024;
+constexpr int64_t PBE_SMALL_LIMIT = 16384;  // values handled by the single-block kernel
+
+struct RmsParams {
+  const float* m_in;
+  const float* s_in;
+  double n;
+  float* m_out;
+  float* s_out;
+};
+
+// values entering the moments: avg -> all nq*k, else column k-1 of each row
+__device__ __forceinline__ int64_t value_index(int64_t i, int k, int avg) {
+  return avg ? i : i * k + (k - 1);
+}
+
+__device__ __forceinline__ double2 warp_sum2(double2 v) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    v.x += __shfl_xor_sync(0xffffffffu, v.x, off);
+    v.y += __shfl_xor_sync(0xffffffffu, v.y, off);
+  }
+  return v;
+}
+
+// Block-wide (sum, sumsq); result valid in thread 0.
+template <int THREADS>
+__device__ double2 block_sum2(double2 v, double2* smem) {
+  v = warp_sum2(v);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) smem[warp] = v;
+  __syncthreads();
+  if (warp == 0) {
+    double2 t = (lane < THREADS / 32) ? smem[lane] : make_double2(0.0, 0.0);
+    t = warp_sum2(t);
+    if (lane == 0) smem[0] = t;
+  }
+  __syncthreads();
+  return smem[0];
+}
+
+// utils/utils.py:264-276 on scalars.  sums = {count, sum, sumsq}.
+__device__ void rms_apply(const double* sums, const RmsParams& p) {
+  const double bs = sums[0], sum = sums[1], sumsq = sums[2];
+  const double M = (double)*p.m_in, S = (double)*p.s_in, n = p.n;
+  const double mean = sum / bs;
+  // torch.var(unbiased): NaN for a single element, like the reference.
+  const double var = (bs > 1.0) ? fmax(sumsq - sum * mean, 0.0) / (bs - 1.0) : (double)NAN;
+  const double tot = n + bs;
+  const double delta = mean - M;
+  const double new_m = M + delta * bs / tot;
+  const double new_s = (S * n + var * bs + delta * delta * n * bs / tot) / tot;
+  *p.m_out = (float)new_m;
+  *p.s_out = (float)new_s;
+}
+
+__device__ __forceinline__ float pbe_row(const float* __restrict__ d, int k, int avg, float inv_on,
+                                         float m, int use_clip, float clip) {
+  // r / M (true division, utils.py:304/311), max(r - clip, 0) (:305-308/:312-315),
+  // mean over k (:317), log(r + 1) (:318)
+  float r;
+  if (avg) {
+    float acc = 0.f;
+    for (int j = 0; j < k; ++j) {
+      float v = d[j];
+      if (inv_on != 0.f) v = v / m;
+      if (use_clip) v = fmaxf(v - clip, 0.f);
+      acc += v;
+    }
+    r = acc / (float)k;
+  } else {
+    float v = d[k - 1];
+    if (inv_on != 0.f) v = v / m;
+    if (use_clip) v = fmaxf(v - clip, 0.f);
+    r = v;
+  }
+  return logf(r + 1.0f);
+}
+
+// Partial sums per block, then the last block to finish (ticket) reduces them in a fixed order,
+// optionally applies the RMS update, and re-arms the ticket.
+__global__ void __launch_bounds__(PBE_THREADS)
+pbe_moments_kernel(const float* __restrict__ x, int64_t count, int k, int avg,
+                   double2* __restrict__ partials, unsigned* __restrict__ ticket,
+                   double* __restrict__ out_sums, int apply, RmsParams p) {
+  __shared__ double2 red[PBE_THREADS / 32];
+  __shared__ bool is_last;
+  double2 acc = make_double2(0.0, 0.0);
+  for (int64_t i = (int64_t)blockIdx.x * PBE_THREADS + threadIdx.x; i < count;
+       i += (int64_t)gridDim.x * PBE_THREADS) {
+    const double v = (double)x[value_index(i, k, avg)];
+    acc.x += v;
+    acc.y += v * v;
+  }
+  const double2 tot = block_sum2<PBE_THREADS>(acc, red);
+  if (threadIdx.x == 0) {
+    partials[blockIdx.x] = tot;
+    __threadfence();
+    const unsigned t = atomicAdd(ticket, 1u);
+    is_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  double2 a = make_double2(0.0, 0.0);
+  for (int i = threadIdx.x; i < (int)gridDim.x; i += PBE_THREADS) {
+    const double2 t = partials[i];
+    a.x += t.x;
+    a.y += t.y;
+  }
+  const double2 all = block_sum2<PBE_THREADS>(a, red);
+  if (threadIdx.x == 0) {
+    out_sums[0] = (double)count;
+    out_sums[1] = all.x;
+    out_sums[2] = all.y;
+    if (apply) rms_apply(out_sums, p);
+    *ticket = 0u;
+  }
+}
+
+__global__ void rms_apply_kernel(const double* __restrict__ sums, RmsParams p) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) rms_apply(sums, p);
+}
+
+__global__ void __launch_bounds__(PBE_THREADS)
+pbe_finish_kernel(const float* __restrict__ dist, int64_t nq, int k, int avg, int use_rms,
+                  int use_clip, float clip, const float* __restrict__ m_ptr,
+                  float* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * PBE_THREADS + threadIdx.x;
+  if (i >= nq) return;
+  const float m = use_rms ? *m_ptr : 1.0f;
+  out[i] = pbe_row(dist + i * k, k, avg, use_rms ? 1.f : 0.f, m, use_clip, clip);
+}
+
+// Whole epilogue in one block for the per-update sizes (B = 1024, k = 12).
+__global__ void __launch_bounds__(PBE_SMALL_THREADS)
+pbe_small_kernel(const float* __restrict__ dist, int64_t nq, int k, int avg, int use_rms,
+                 int use_clip, float clip, RmsParams p, float* __restrict__ out) {
+  __shared__ double2 red[PBE_SMALL_THREADS / 32];
+  __shared__ double sums[3];
+  if (use_rms) {
+    const int64_t count = avg ? nq * k : nq;
+    double2 acc = make_double2(0.0, 0.0);
+    for (int64_t i = threadIdx.x; i < count; i += PBE_SMALL_THREADS) {
+      const double v = (double)dist[value_index(i, k, avg)];
+      acc.x += v;
+      acc.y += v * v;
+    }
+    const double2 all = block_sum2<PBE_SMALL_THREADS>(acc, red);
+    if (threadIdx.x == 0) {
+      sums[0] = (double)count;
+      sums[1] = all.x;
+      sums[2] = all.y;
+      rms_apply(sums, p);
+      __threadfence_block();
+    }
+    __syncthreads();
+  }
+  const float m = use_rms ? *p.m_out : 1.0f;
+  for (int64_t i = threadIdx.x; i < nq; i += PBE_SMALL_THREADS)
+    out[i] = pbe_row(dist + i * k, k, avg, use_rms ? 1.f : 0.f, m, use_clip, clip);
+}
+
+__global__ void take_kth_kernel(const float* __restrict__ dist, int64_t nq, int k,
+                                float* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < nq) out[i] = dist[i * k + (k - 1)];
+}
+
+static int moments_blocks(int64_t count) {
+  int64_t b = (count + PBE_THREADS * 8 - 1) / (PBE_THREADS * 8);
+  const int64_t cap = 4LL * sm_count();
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+}  // namespace exb
+
+using namespace exb;
+
+extern "C" size_t exb_pbe_workspace_bytes(int64_t nq, int k) {
+  (void)nq;
+  (void)k;
+  return 256 /*ticket*/ + 256 /*sums*/ + align_up(4 * 160 * sizeof(double2) * 2, 256);
+}
+
+namespace {
+struct PbeWs {
+  unsigned* ticket;
+  double* sums;
+  double2* partials;
+};
+int carve_pbe(void* ws, size_t bytes, PbeWs* o) {
+  EXB_CHECK_ARG(ws && bytes >= exb_pbe_workspace_bytes(0, 0), "pbe workspace too small");
+  EXB_CHECK_ARG(4 * sm_count() <= 4 * 160 * 2, "unexpected SM count");
+  Carver cv(ws);
+  o->ticket = cv.take<unsigned>(1);
+  o->sums = cv.take<double>(4);
+  o->partials = cv.take<double2>(4 * 160 * 2);
+  return EXB_OK;
+}
+}  // namespace
+
+// The ticket word must start at zero: the workspace is zero-initialised once by the caller
+// (exb_pbe_workspace_init) and every launch re-arms it.
+extern "C" int exb_pbe_workspace_init(void* workspace, size_t workspace_bytes,
+                                      exb_stream_t stream) {
+  EXB_CHECK_ARG(workspace && workspace_bytes >= exb_pbe_workspace_bytes(0, 0),
+                "pbe workspace too small");
+  EXB_CUDA(cudaMemsetAsync(workspace, 0, exb_pbe_workspace_bytes(0, 0), (cudaStream_t)stream));
+  return EXB_OK;
+}
+
+extern "C" int exb_pbe_reward(const float* knn_dist, int64_t nq, int k, int avg, int use_rms,
+                              float clip, const float* rms_m_in, const float* rms_s_in,
+                              double rms_n, float* rms_m_out, float* rms_s_out,
+                              float* out_reward, void* workspace, size_t workspace_bytes,
+                              exb_stream_t stream) {
+  EXB_CHECK_ARG(knn_dist && out_reward && nq > 0 && k >= 1, "bad arguments");
+  EXB_CHECK_ARG(!use_rms || (rms_m_in && rms_s_in && rms_m_out && rms_s_out),
+                "use_rms needs the RMS state pointers");
+  cudaStream_t st = (cudaStream_t)stream;
+  RmsParams p{rms_m_in, rms_s_in, rms_n, rms_m_out, rms_s_out};
+  const int use_clip = clip >= 0.0f;
+  const int64_t count = avg ? nq * k : nq;
+  if (nq * k <= PBE_SMALL_LIMIT) {
+    pbe_small_kernel<<<1, PBE_SMALL_THREADS, 0, st>>>(knn_dist, nq, k, avg, use_rms, use_clip,
+                                                      clip, p, out_reward);
+    EXB_LAUNCH_CHECK();
+    return EXB_OK;
+  }
+  if (use_rms) {
+    PbeWs w;
+    int rc = carve_pbe(workspace, workspace_bytes, &w);
+    if (rc) return rc;
+    pbe_moments_kernel<<<moments_blocks(count), PBE_THREADS, 0, st>>>(
+        knn_dist, count, k, avg, w.partials, w.ticket, w.sums, 1, p);
+    EXB_LAUNCH_CHECK();
+  }
+  pbe_finish_kernel<<<(unsigned)((nq + PBE_THREADS - 1) / PBE_THREADS), PBE_THREADS, 0, st>>>(
+      knn_dist, nq, k, avg, use_rms, use_clip, clip, rms_m_out, out_reward);
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}
+
+extern "C" int exb_pbe_moments(const float* knn_dist, int64_t nq, int k, int avg,
+                               double* out_sums, void* workspace, size_t workspace_bytes,
+                               exb_stream_t stream) {
+  EXB_CHECK_ARG(knn_dist && out_sums && nq > 0 && k >= 1, "bad arguments");
+  PbeWs w;
+  int rc = carve_pbe(workspace, workspace_bytes, &w);
+  if (rc) return rc;
+  const int64_t count = avg ? nq * k : nq;
+  RmsParams p{nullptr, nullptr, 0.0, nullptr, nullptr};
+  pbe_moments_kernel<<<moments_blocks(count), PBE_THREADS, 0, (cudaStream_t)stream>>>(
+      knn_dist, count, k, avg, w.partials, w.ticket, out_sums, 0, p);
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}
+
+extern "C" int exb_pbe_finish(const float* knn_dist, int64_t nq, int k, int avg, int use_rms,
+                              float clip, const double* sums, const float* rms_m_in,
+                              const float* rms_s_in, double rms_n, float* rms_m_out,
+                              float* rms_s_out, float* out_reward, exb_stream_t stream) {
+  EXB_CHECK_ARG(knn_dist && out_reward && nq > 0 && k >= 1, "bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (use_rms) {
+    EXB_CHECK_ARG(sums && rms_m_in && rms_s_in && rms_m_out && rms_s_out,
+                  "use_rms needs sums and the RMS state pointers");
+    RmsParams p{rms_m_in, rms_s_in, rms_n, rms_m_out, rms_s_out};
+    rms_apply_kernel<<<1, 32, 0, st>>>(sums, p);
+    EXB_LAUNCH_CHECK();
+  }
+  pbe_finish_kernel<<<(unsigned)((nq + PBE_THREADS - 1) / PBE_THREADS), PBE_THREADS, 0, st>>>(
+      knn_dist, nq, k, avg, use_rms, clip >= 0.0f, clip, rms_m_out, out_reward);
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}
+
+extern "C" int exb_rms_update(const float* x, int64_t n, const float* rms_m_in,
+                              const float* rms_s_in, double rms_n, float* rms_m_out,
+                              float* rms_s_out, void* workspace, size_t workspace_bytes,
+                              exb_stream_t stream) {
+  EXB_CHECK_ARG(x && n > 0 && rms_m_in && rms_s_in && rms_m_out && rms_s_out, "bad arguments");
+  PbeWs w;
+  int rc = carve_pbe(workspace, workspace_bytes, &w);
+  if (rc) return rc;
+  RmsParams p{rms_m_in, rms_s_in, rms_n, rms_m_out, rms_s_out};
+  pbe_moments_kernel<<<moments_blocks(n), PBE_THREADS, 0, (cudaStream_t)stream>>>(
+      x, n, 1, 1, w.partials, w.ticket, w.sums, 1, p);
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}
+
+extern "C" int exb_take_kth(const float* knn_dist, int64_t nq, int k, float* out,
+                            exb_stream_t stream) {
+  EXB_CHECK_ARG(knn_dist && out && nq > 0 && k >= 1, "bad arguments");
+  take_kth_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, (cudaStream_t)stream>>>(knn_dist, nq,
+                                                                                  k, out);
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}

@@ -1,0 +1,215 @@
+"""Host-side mirror of the reference's particle-based reward interface over the C ABI.
+
+Same names, argument meaning and error behaviour as the reference:
+  RMS  <- /root/reference/utils/utils.py:257-276
+  PBE  <- /root/reference/utils/utils.py:279-319
+  compute_apt_reward(source, target, args) <- the same computation with source != target
+  proto_knn_reward / proto_enqueue <- agents/unsupervised_learning/proto.py:110-118
+All arithmetic runs in hand-written sm_100a kernels (exorl_b200/csrc); there is no CPU path.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+
+_MODES = ("auto", "exact", "screened")
+
+
+def _as_rows(x, name):
+    """(b, ...) -> contiguous fp32 (b, c); the reference flattens trailing dims with .view
+    (utils/utils.py:293-294)."""
+    _lib.require_cuda(x, name)
+    x = x.detach()
+    if x.dtype != torch.float32:
+        x = x.float()
+    return x.reshape(x.size(0), -1).contiguous()
+
+
+def knn_topk(source, target, k, idx_base=0, mode="auto"):
+    """k smallest L2 distances (ascending) of every source row to the target rows.
+
+    Returns (dist (b1, k) float32, idx (b1, k) int32), both on source's device.  Replaces the
+    (b1, b2, c) broadcast + torch.norm + topk of utils/utils.py:293-300; raises RuntimeError
+    "selected index k out of range" when k > b2 like the reference's topk.
+    mode: "exact" = fp32 CUDA-core kernel; "screened" = tcgen05 fp16 screening + exact fp32
+    recompute of the survivors (same results); "auto" picks by shape.
+    """
+    if mode not in _MODES:
+        raise ValueError(f"mode must be one of {_MODES}")
+    lib = _lib.load()
+    src = _as_rows(source, "source")
+    same = target is source
+    tgt = src if same else _as_rows(target, "target")
+    if src.size(1) != tgt.size(1):
+        raise RuntimeError(f"feature sizes differ: {src.size(1)} vs {tgt.size(1)}")
+    if src.device != tgt.device:
+        raise RuntimeError("source and target must be on the same device")
+    k = int(k)
+    nq, nb, dim = src.size(0), tgt.size(0), src.size(1)
+    if k > nb:
+        raise RuntimeError("selected index k out of range")
+    if k < 1 or k > _lib.MAX_K:
+        raise ValueError(f"exorl_b200: knn_k={k} outside [1, {_lib.MAX_K}]")
+    dev = src.device
+    with torch.cuda.device(dev):
+        dist = torch.empty(nq, k, dtype=torch.float32, device=dev)
+        idx = torch.empty(nq, k, dtype=torch.int32, device=dev)
+        if nq == 0:
+            return dist, idx
+        use_screen = mode == "screened" or (mode == "auto" and _screen_ok(nq, nb, dim, k))
+        if use_screen:
+            need = lib.exb_knn_screened_workspace_bytes(nq, nb, dim, k)
+            if need == 0:
+                raise ValueError(f"exorl_b200: screened kNN does not support dim={dim}, k={k}")
+            ws, _ = _lib.Workspace.get(dev, "knn_screened", need)
+            _lib.check(lib.exb_knn_screened_f32(
+                _lib.ptr(src), nq, _lib.ptr(tgt), nb, dim, k, int(idx_base), int(same),
+                _lib.ptr(dist), _lib.ptr(idx), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+        else:
+            need = lib.exb_knn_exact_workspace_bytes(nq, nb, dim, k)
+            ws, _ = _lib.Workspace.get(dev, "knn_exact", need)
+            _lib.check(lib.exb_knn_exact_f32(
+                _lib.ptr(src), nq, _lib.ptr(tgt), nb, dim, k, int(idx_base), _lib.ptr(dist),
+                _lib.ptr(idx), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+    return dist, idx
+
+
+def _screen_ok(nq, nb, dim, k):
+    return (dim <= _lib.SCREEN_MAX_DIM and k <= _lib.SCREEN_MAX_K and nq >= 128 and nb >= 256)
+
+
+def screened_status(device=None):
+    """(undecided_rows, invalid_flag, reranked_pairs, _) of the last screened call (syncs)."""
+    lib = _lib.load()
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+    ws, fresh = _lib.Workspace.get(dev, "knn_screened", 1024)
+    if fresh:
+        return (0, 0, 0, 0)
+    out = (ctypes.c_int32 * 4)()
+    _lib.check(lib.exb_knn_screened_status_sync(_lib.ptr(ws), out, _lib.stream_ptr(dev)))
+    return tuple(out)
+
+
+def _pbe_ws(dev):
+    lib = _lib.load()
+    need = lib.exb_pbe_workspace_bytes(0, 0)
+    ws, fresh = _lib.Workspace.get(dev, "pbe", need, zero_init=True)
+    return ws
+
+
+class RMS(object):
+    """running mean and std — drop-in for utils/utils.py:257-276.
+
+    M and S are tensors on `device`, n is a python float; the object is a plain picklable
+    Python object (snapshots pickle the whole agent)."""
+
+    def __init__(self, device, epsilon=1e-4, shape=(1,)):
+        self.M = torch.zeros(shape).to(device)
+        self.S = torch.ones(shape).to(device)
+        self.n = epsilon
+
+    def __call__(self, x):
+        bs = x.size(0)
+        if (self.M.numel() == 1 and x.is_cuda and x.dtype == torch.float32
+                and x.numel() == bs and self.M.is_cuda):
+            lib = _lib.load()
+            dev = x.device
+            xc = x.detach().reshape(-1).contiguous()
+            new_m = torch.empty_like(self.M)
+            new_s = torch.empty_like(self.S)
+            with torch.cuda.device(dev):
+                ws = _pbe_ws(dev)
+                _lib.check(lib.exb_rms_update(
+                    _lib.ptr(xc), bs, _lib.ptr(self.M), _lib.ptr(self.S), float(self.n),
+                    _lib.ptr(new_m), _lib.ptr(new_s), _lib.ptr(ws), ws.numel(),
+                    _lib.stream_ptr(dev)))
+        else:
+            # general-shape states (not on the kNN path): same formula with device torch ops
+            delta = torch.mean(x, dim=0) - self.M
+            new_m = self.M + delta * bs / (self.n + bs)
+            new_s = (self.S * self.n + torch.var(x, dim=0) * bs
+                     + torch.square(delta) * self.n * bs / (self.n + bs)) / (self.n + bs)
+        self.M = new_m
+        self.S = new_s
+        self.n += bs
+        return self.M, self.S
+
+
+def _reward_from_knn(dist, k, knn_avg, knn_rms, knn_clip, rms):
+    lib = _lib.load()
+    dev = dist.device
+    nq = dist.size(0)
+    out = torch.empty(nq, 1, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        ws = _pbe_ws(dev)
+        if knn_rms:
+            if rms is None:
+                raise ValueError("knn_rms=True needs an RMS state object")
+            if rms.M.numel() != 1 or not rms.M.is_cuda:
+                raise ValueError("the RMS state used by PBE must have shape (1,) on the GPU")
+            new_m = torch.empty_like(rms.M)
+            new_s = torch.empty_like(rms.S)
+            args = (_lib.ptr(rms.M), _lib.ptr(rms.S), float(rms.n), _lib.ptr(new_m),
+                    _lib.ptr(new_s))
+        else:
+            args = (None, None, 0.0, None, None)
+        _lib.check(lib.exb_pbe_reward(
+            _lib.ptr(dist), nq, k, int(bool(knn_avg)), int(bool(knn_rms)), float(knn_clip),
+            *args, _lib.ptr(out), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+    if knn_rms:
+        # utils/utils.py:272-274: rebind M, S and advance n by the number of values seen
+        rms.M, rms.S = new_m, new_s
+        rms.n += nq * k if knn_avg else nq
+    return out
+
+
+def compute_apt_reward(source, target, args, rms=None, mode="auto"):
+    """APT particle-based reward of every `source` row against the `target` bank, (b1, 1).
+
+    `args` exposes knn_k, knn_avg, knn_rms, knn_clip (and optionally .rms); this is the
+    signature the computation had before the reference folded it into PBE.__call__
+    (utils/utils.py:289-319, where source = target = rep)."""
+    if rms is None:
+        rms = getattr(args, "rms", None)
+    k = int(args.knn_k)
+    dist, _ = knn_topk(source, target, k, mode=mode)
+    return _reward_from_knn(dist, k, args.knn_avg, args.knn_rms, args.knn_clip, rms)
+
+
+class PBE(object):
+    """particle-based entropy based on knn normalized by running mean — drop-in for
+    utils/utils.py:279-319 (same constructor, same call, same RMS side effects)."""
+
+    def __init__(self, rms, knn_clip, knn_k, knn_avg, knn_rms, device):
+        self.rms = rms
+        self.knn_rms = knn_rms
+        self.knn_k = knn_k
+        self.knn_avg = knn_avg
+        self.knn_clip = knn_clip
+        self.device = device
+        self.mode = "auto"
+
+    def __call__(self, rep):
+        return compute_apt_reward(rep, rep, self, rms=self.rms,
+                                  mode=getattr(self, "mode", "auto"))
+
+
+def proto_enqueue(queue, queue_ptr, z, candidates):
+    """FIFO write of z[candidates] into the queue; returns the new pointer (proto.py:110-112)."""
+    n = candidates.numel()
+    queue[queue_ptr:queue_ptr + n] = z[candidates]
+    return (queue_ptr + n) % queue.shape[0]
+
+
+def proto_knn_reward(z, queue, topk, mode="auto"):
+    """Distance of every z row to its topk-th nearest queue row, (B, 1) — replaces
+    proto.py:115-118 (no RMS, no clip, no log)."""
+    lib = _lib.load()
+    k = int(topk)
+    dist, _ = knn_topk(z, queue, k, mode=mode)
+    out = torch.empty(dist.size(0), 1, dtype=torch.float32, device=dist.device)
+    with torch.cuda.device(dist.device):
+        _lib.check(lib.exb_take_kth(_lib.ptr(dist), dist.size(0), k, _lib.ptr(out),
+                                    _lib.stream_ptr(dist.device)))
+    return out

@@ -1,0 +1,151 @@
+"""Dataset-scale APT relabel: kNN reward of a whole buffer against itself, bank sharded over ranks.
+
+New composition of the reference's PBE semantics (utils/utils.py:289-319) at N ~ 10^6, where the
+reference formula cannot be evaluated (it materialises an (N, N, c) tensor); SURVEY.md §3.5, §8e.
+
+  every rank holds the full query set `rep` (N, c) and owns bank rows [lo, hi) = its shard;
+  1. local:    k nearest bank rows of the shard for every query (exact distances, global ids)
+  2. exchange: "all_gather"  — every rank receives all G per-shard (N, k) lists and merges all
+                               N rows (north_star's formulation), or
+               "all_to_all"  — rank r receives the G lists of query block r only, merges N/G
+                               rows, and the RMS sums are all-reduced (8x less traffic/merge work)
+  3. one global RMS update with bs = N*k (or N), then the epilogue
+  4. all_to_all only: rewards all-gathered so every rank returns the full (N, 1).
+
+The three compute stages are injectable so the partition/exchange logic can be exercised with
+the gloo backend on CPU (tests/test_relabel_gloo.py); the defaults are the CUDA kernels.
+"""
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from .knn import knn_topk, _reward_from_knn, _pbe_ws
+
+
+def shard_bounds(n, world, rank):
+    """Contiguous near-equal row split: rows [lo, hi) of rank `rank`."""
+    base, rem = divmod(n, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def _cuda_local_knn(rep, lo, hi, k, mode):
+    return knn_topk(rep, rep[lo:hi], k, idx_base=lo, mode=mode)
+
+
+def _cuda_merge(dist_lists, idx_lists, k):
+    """dist_lists/idx_lists: (G, n, k) -> (n, k) global k smallest."""
+    lib = _lib.load()
+    g, n, _ = dist_lists.shape
+    dev = dist_lists.device
+    out_d = torch.empty(n, k, dtype=torch.float32, device=dev)
+    out_i = torch.empty(n, k, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(lib.exb_topk_merge(_lib.ptr(dist_lists), _lib.ptr(idx_lists), g, n, k,
+                                      _lib.ptr(out_d), _lib.ptr(out_i), _lib.stream_ptr(dev)))
+    return out_d, out_i
+
+
+def _cuda_sums(knn_dist, k, avg):
+    lib = _lib.load()
+    dev = knn_dist.device
+    out = torch.empty(3, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        ws = _pbe_ws(dev)
+        _lib.check(lib.exb_pbe_moments(_lib.ptr(knn_dist), knn_dist.size(0), k, int(avg),
+                                       _lib.ptr(out), _lib.ptr(ws), ws.numel(),
+                                       _lib.stream_ptr(dev)))
+    return out
+
+
+def _cuda_finish(knn_dist, k, avg, use_rms, clip, sums, rms):
+    lib = _lib.load()
+    dev = knn_dist.device
+    n = knn_dist.size(0)
+    out = torch.empty(n, 1, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        if use_rms:
+            new_m, new_s = torch.empty_like(rms.M), torch.empty_like(rms.S)
+            st = (_lib.ptr(rms.M), _lib.ptr(rms.S), float(rms.n), _lib.ptr(new_m),
+                  _lib.ptr(new_s))
+        else:
+            st = (None, None, 0.0, None, None)
+        _lib.check(lib.exb_pbe_finish(_lib.ptr(knn_dist), n, k, int(avg), int(use_rms),
+                                      float(clip), _lib.ptr(sums) if use_rms else None, *st,
+                                      _lib.ptr(out), _lib.stream_ptr(dev)))
+    if use_rms:
+        rms.M, rms.S = new_m, new_s
+    return out
+
+
+class _CudaStages:
+    local_knn = staticmethod(_cuda_local_knn)
+    merge = staticmethod(_cuda_merge)
+    sums = staticmethod(_cuda_sums)
+    finish = staticmethod(_cuda_finish)
+
+    @staticmethod
+    def reward(knn_dist, k, avg, use_rms, clip, rms):
+        return _reward_from_knn(knn_dist, k, avg, use_rms, clip, rms)
+
+
+def relabel_apt_reward(rep, args, rms=None, group=None, exchange="all_to_all", mode="auto",
+                       return_knn=False, stages=_CudaStages):
+    """APT reward (N, 1) of every row of `rep` against all N rows, identical on every rank.
+
+    `args` exposes knn_k, knn_avg, knn_rms, knn_clip like PBE; `rms` is the running-moment state
+    (updated once with bs = N*k in avg mode, N otherwise).  Works without an initialised process
+    group (single shard)."""
+    if exchange not in ("all_gather", "all_to_all"):
+        raise ValueError("exchange must be 'all_gather' or 'all_to_all'")
+    if rms is None:
+        rms = getattr(args, "rms", None)
+    k, avg, use_rms, clip = int(args.knn_k), bool(args.knn_avg), bool(args.knn_rms), args.knn_clip
+    distributed = dist.is_available() and dist.is_initialized()
+    world = dist.get_world_size(group) if distributed else 1
+    rank = dist.get_rank(group) if distributed else 0
+    n = rep.size(0)
+    lo, hi = shard_bounds(n, world, rank)
+    if hi - lo < k:
+        raise RuntimeError("selected index k out of range")   # a shard smaller than k rows
+
+    d_loc, i_loc = stages.local_knn(rep, lo, hi, k, mode)      # (N, k) exact, global ids
+    if world == 1:
+        reward = stages.reward(d_loc, k, avg, use_rms, clip, rms)
+        return (reward, d_loc, i_loc) if return_knn else reward
+
+    if exchange == "all_gather":
+        d_all = torch.empty((world * n, k), dtype=d_loc.dtype, device=d_loc.device)
+        i_all = torch.empty((world * n, k), dtype=i_loc.dtype, device=i_loc.device)
+        dist.all_gather_into_tensor(d_all, d_loc.contiguous(), group=group)
+        dist.all_gather_into_tensor(i_all, i_loc.contiguous(), group=group)
+        d_glob, i_glob = stages.merge(d_all.view(world, n, k), i_all.view(world, n, k), k)
+        reward = stages.reward(d_glob, k, avg, use_rms, clip, rms)   # same update on every rank
+        return (reward, d_glob, i_glob) if return_knn else reward
+
+    # all_to_all: query block b of every rank's list goes to rank b
+    bounds = [shard_bounds(n, world, r) for r in range(world)]
+    in_split = [(b - a) for a, b in bounds]
+    my_n = hi - lo
+    d_blk = torch.empty((world * my_n, k), dtype=d_loc.dtype, device=d_loc.device)
+    i_blk = torch.empty((world * my_n, k), dtype=i_loc.dtype, device=i_loc.device)
+    dist.all_to_all_single(d_blk, d_loc.contiguous(), [my_n] * world, in_split, group=group)
+    dist.all_to_all_single(i_blk, i_loc.contiguous(), [my_n] * world, in_split, group=group)
+    d_mine, i_mine = stages.merge(d_blk.view(world, my_n, k), i_blk.view(world, my_n, k), k)
+    sums = None
+    if use_rms:
+        sums = stages.sums(d_mine, k, avg)                      # {count, sum, sumsq} of my block
+        dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
+    r_mine = stages.finish(d_mine, k, avg, use_rms, clip, sums, rms)
+    if use_rms:
+        rms.n += n * k if avg else n
+    # variable block sizes: gather padded to the largest block
+    mx = max(in_split)
+    pad = torch.zeros((mx, 1), dtype=r_mine.dtype, device=r_mine.device)
+    pad[:my_n] = r_mine
+    gathered = torch.empty((world * mx, 1), dtype=r_mine.dtype, device=r_mine.device)
+    dist.all_gather_into_tensor(gathered, pad, group=group)
+    reward = torch.cat([gathered[r * mx:r * mx + in_split[r]] for r in range(world)], dim=0)
+    if return_knn:
+        return reward, d_mine, i_mine
+    return reward

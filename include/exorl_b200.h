@@ -1,0 +1,174 @@
+/*
+ * exorl_b200 — C ABI of the B200-native particle-based kNN reward + n-step replay gather path.
+ *
+ * The reference (AOS55/exorl) has no FFI layer: the path is three Python call sites
+ * (SURVEY.md §8b).  This header is the boundary a maintainer binds instead (ctypes stub in
+ * INTEGRATION.md); every entry point cites the reference lines whose work it replaces.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; all pointers are DEVICE pointers unless named host_*;
+ *   - row-major contiguous fp32 inputs, int32 neighbour indices;
+ *   - every call only enqueues work on `stream` (a cudaStream_t) and never synchronises,
+ *     except the explicitly named *_sync helpers;
+ *   - return value: 0 on success, one of EXB_E* otherwise; exb_last_error() gives the text
+ *     (thread-local, valid until the next failing call on that thread);
+ *   - the caller owns every buffer; workspaces are sized by the *_workspace_bytes queries.
+ */
+#ifndef EXORL_B200_H_
+#define EXORL_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EXB_OK 0
+#define EXB_EINVAL 1       /* bad pointer / size / alignment                                   */
+#define EXB_EKRANGE 2      /* k > number of bank rows: reference raises RuntimeError("selected
+                              index k out of range") from topk, utils/utils.py:297            */
+#define EXB_EUNSUPPORTED 3 /* shape outside what the kernel family supports (e.g. rep dim)     */
+#define EXB_ECUDA 4        /* a CUDA runtime/driver call failed                                */
+#define EXB_EFALLBACK 5    /* screening produced more undecided rows than the fallback capacity */
+
+#define EXB_MAX_K 32       /* neighbours per query (reference uses 12 and 3)                   */
+#define EXB_SCREEN_CAP 24  /* candidate slots per (query, split) kept by the screening kernel   */
+#define EXB_SCREEN_MAX_K 16 /* largest k the screened path accepts (else use the exact path)      */
+#define EXB_SCREEN_MAX_DIM 512
+
+typedef void* exb_stream_t; /* cudaStream_t */
+
+int exb_abi_version(void);
+const char* exb_last_error(void);
+/* Device properties the host side needs for grid sizing (SM count, cc major*10+minor). */
+int exb_device_info(int* sm_count, int* cc);
+
+/* --------------------------------------------------------------------------------------------
+ * kNN, exact fp32 path (CUDA cores).  Replaces utils/utils.py:293-300 (PBE distance matrix +
+ * topk) and agents/unsupervised_learning/proto.py:115-116: for every src row the k smallest
+ * direct-difference distances sqrt(sum_c (src[i,c]-bank[j,c])^2), ascending, ties broken by the
+ * smaller bank index, with their bank indices (+ idx_base).  No (nq, nb) matrix is materialised.
+ * Also the fallback for rows the screening kernel cannot decide.
+ * ------------------------------------------------------------------------------------------ */
+size_t exb_knn_exact_workspace_bytes(int64_t nq, int64_t nb, int dim, int k);
+int exb_knn_exact_f32(const float* src, int64_t nq, const float* bank, int64_t nb, int dim,
+                      int k, int32_t idx_base, float* out_dist /* [nq,k] */,
+                      int32_t* out_idx /* [nq,k] */, void* workspace, size_t workspace_bytes,
+                      exb_stream_t stream);
+
+/* --------------------------------------------------------------------------------------------
+ * kNN, screened path (tcgen05 tensor cores + exact recompute) — same results as the exact path.
+ *   1. exb_knn_prep_f16: fp32 rows -> fp16 K-major operand padded to a multiple of 64 columns,
+ *      plus per row  half_norm = ||fp16(x)||^2 / 2  and  round_err = ||x - fp16(x)||_2 ; sets
+ *      a range flag when a value does not fit fp16 (then every row goes to the exact kernel).
+ *   2. exb_knn_screen_f16: TMA-fed tcgen05 GEMM  src16 . bank16^T  with the accumulator read
+ *      back from TMEM and filtered per row against a running k-th-best-plus-margin threshold;
+ *      keeps, per (query, bank split), every bank row whose screened distance is within the
+ *      rigorous rounding margin of the k-th best (<= EXB_SCREEN_CAP of them, else the row is
+ *      flagged undecided).  Nothing of size nq x nb is written to HBM.
+ *   3. exb_knn_rerank_f32: exact fp32 direct-difference distance of the survivors, top-k.
+ *   4. undecided rows are recomputed by the exact kernel.
+ * exb_knn_screened_f32 runs 1-4.  Replaces the same reference lines as exb_knn_exact_f32.
+ * ------------------------------------------------------------------------------------------ */
+/* scalars: device struct {float err_max; float hn_max; int range_flag; int pad}, max-accumulated
+ * over calls; the caller zeroes it. */
+int exb_knn_prep_f16(const float* x, int64_t n, int dim, void* out_f16 /* [n, dim_pad] */,
+                     float* half_norm /* [n] */, float* round_err /* [n] */,
+                     float* scalars /* 16 bytes */, exb_stream_t stream);
+
+size_t exb_knn_screened_workspace_bytes(int64_t nq, int64_t nb, int dim, int k);
+/* src_is_bank != 0 tells the call that src and bank are the same tensor (PBE: source = target,
+ * utils/utils.py:290) so the fp16 operand is prepared once. */
+int exb_knn_screened_f32(const float* src, int64_t nq, const float* bank, int64_t nb, int dim,
+                         int k, int32_t idx_base, int src_is_bank, float* out_dist,
+                         int32_t* out_idx, void* workspace, size_t workspace_bytes,
+                         exb_stream_t stream);
+/* Device-side status word of the last screened call that used `workspace`:
+ *   [0] undecided rows sent to the exact fallback, [1] non-zero if they exceeded capacity or
+ *   the fp16 range check failed (results invalid -> use exb_knn_exact_f32), [2] candidate
+ *   pairs reranked.  Copies 4 ints to host and synchronises `stream`. */
+int exb_knn_screened_status_sync(const void* workspace, int32_t host_status[4],
+                                 exb_stream_t stream);
+
+/* --------------------------------------------------------------------------------------------
+ * Sharded kNN: merge G per-shard (dist, idx) lists (each [nq,k], ascending) into the global
+ * k smallest per row; ties -> smaller index.  lists are laid out [G, nq, k] (the result of an
+ * all-gather of per-rank results).  New composition; semantics of
+ * utils/utils.py:297-300 applied to the union of shards.
+ * ------------------------------------------------------------------------------------------ */
+int exb_topk_merge(const float* dist_lists, const int32_t* idx_lists, int n_lists, int64_t nq,
+                   int k, float* out_dist, int32_t* out_idx, exb_stream_t stream);
+
+/* --------------------------------------------------------------------------------------------
+ * RMS state + PBE epilogue.  Replaces utils/utils.py:264-276 (RMS.__call__) and :301-318.
+ *   knn_dist [nq,k] ascending.  avg != 0: all nq*k values enter the running moments and the
+ *   reward is the mean over k; avg == 0: column k-1 only.  use_rms: update state (M,S,n) then
+ *   divide by the UPDATED mean.  clip >= 0: max(r - clip, 0).  reward = log(r + 1), [nq].
+ *   RMS state: rms_m_in / rms_s_in are the fp32 (1,) tensors RMS.M / RMS.S on the device, rms_n
+ *   is RMS.n (a python float in the reference, passed by value); the updated moments are written
+ *   to rms_m_out / rms_s_out (may alias the inputs).  The caller advances n += count itself,
+ *   like utils/utils.py:274.  When use_rms == 0 the state pointers may be NULL.
+ * exb_pbe_moments exposes a shard's plain sums {count, sum, sum of squares} (fp64) so that ranks
+ * can all-reduce(SUM) them before exb_pbe_finish; exb_pbe_reward does everything on one device.
+ * The workspace carries a ticket word: zero it once with exb_pbe_workspace_init.
+ * ------------------------------------------------------------------------------------------ */
+size_t exb_pbe_workspace_bytes(int64_t nq, int k);
+int exb_pbe_workspace_init(void* workspace, size_t workspace_bytes, exb_stream_t stream);
+int exb_pbe_reward(const float* knn_dist, int64_t nq, int k, int avg, int use_rms, float clip,
+                   const float* rms_m_in, const float* rms_s_in, double rms_n, float* rms_m_out,
+                   float* rms_s_out, float* out_reward /* [nq] */, void* workspace,
+                   size_t workspace_bytes, exb_stream_t stream);
+int exb_pbe_moments(const float* knn_dist, int64_t nq, int k, int avg,
+                    double* out_sums /* device double[3] = count, sum, sumsq */, void* workspace,
+                    size_t workspace_bytes, exb_stream_t stream);
+int exb_pbe_finish(const float* knn_dist, int64_t nq, int k, int avg, int use_rms, float clip,
+                   const double* sums /* device double[3], already combined */,
+                   const float* rms_m_in, const float* rms_s_in, double rms_n, float* rms_m_out,
+                   float* rms_s_out, float* out_reward, exb_stream_t stream);
+/* RMS.__call__ on an (n, 1) fp32 column (utils/utils.py:264-276), e.g. for RND (rnd.py:96). */
+int exb_rms_update(const float* x, int64_t n, const float* rms_m_in, const float* rms_s_in,
+                   double rms_n, float* rms_m_out, float* rms_s_out, void* workspace,
+                   size_t workspace_bytes, exb_stream_t stream);
+
+/* ProtoRL reward: k-th smallest distance only, no RMS/clip/log (proto.py:115-118). */
+int exb_take_kth(const float* knn_dist, int64_t nq, int k, float* out /* [nq] */,
+                 exb_stream_t stream);
+
+/* --------------------------------------------------------------------------------------------
+ * Replay gather over a device-resident flat buffer.  Replaces the per-sample
+ * python of ReplayBuffer._sample, utils/replay_buffer.py:223-235, and
+ * OfflineReplayBuffer._sample, :87-96, plus collate/pin/H2D (:246-277).
+ *   rows[b] = global row of the 1-based in-episode position idx (= episode start row + idx).
+ *   obs      <- observation[rows-1]            (row_bytes_obs bytes per row, any dtype)
+ *   action   <- action[rows]
+ *   next_obs <- observation[rows+nstep-1]
+ *   reward, discount: fp32 (1,) per sample, accumulated exactly in the reference's order:
+ *       r = 0; g = 1; for i<nstep: r += g*reward[row+i]; g *= discount[row+i]*gamma
+ *     offline (nstep_mode == 0): r = reward[row]; g = discount[row]*gamma   (:94-95)
+ *   meta[m]  <- meta_src[m][rows-1]            (n_meta extra columns, :224-225)
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  const void* src;      /* device base of the column                       */
+  void* dst;            /* device output, batch rows                       */
+  int64_t row_bytes;    /* bytes per row                                   */
+  int32_t row_offset;   /* added to rows[b]: -1 obs/meta, 0 action, nstep-1 next_obs */
+} exb_gather_col;
+
+int exb_replay_gather(const int64_t* rows, int64_t batch, const exb_gather_col* host_cols,
+                      int n_cols, const float* reward_src, const float* discount_src, int nstep,
+                      int nstep_mode, float gamma, float* out_reward, float* out_discount,
+                      exb_stream_t stream);
+
+/* Device index draw (fast mode): Philox4x32-10, counter (sample, call_lo, call_hi, 0), key =
+ * seed.  episode = mulhi(r0, n_episodes); idx = mulhi(r1, eps_len[e]-nstep+1)+1 — the range of
+ * utils/replay_buffer.py:222 (nstep = 1 gives the offline range of :90) — rows = start+idx. */
+int exb_replay_draw(uint64_t seed, uint64_t call, const int64_t* eps_start,
+                    const int32_t* eps_len, int64_t n_episodes, int nstep, int64_t batch,
+                    int64_t* out_rows, int32_t* out_episode /* may be NULL */,
+                    exb_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EXORL_B200_H_ */

@@ -1,0 +1,77 @@
+"""CPU checks of the drop-in boundary: the C-ABI library builds/loads and exports every symbol
+include/exorl_b200.h declares; host-side argument errors; no compute without a GPU."""
+import pathlib
+import re
+
+import pytest
+import torch
+
+import exorl_b200
+from exorl_b200 import _lib
+
+HEADER = pathlib.Path(__file__).resolve().parent.parent / "include" / "exorl_b200.h"
+
+
+def _declared_symbols():
+    text = re.sub(r"/\*.*?\*/", "", HEADER.read_text(), flags=re.S)
+    return sorted(set(re.findall(r"\b(exb_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    lib = _lib.load()
+    names = _declared_symbols()
+    assert len(names) >= 15
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in the header but not exported"
+    assert lib.exb_abi_version() == 1
+
+
+def test_binding_table_matches_header():
+    assert sorted(_lib.SIGNATURES) == _declared_symbols()
+
+
+def test_workspace_queries_need_no_gpu():
+    lib = _lib.load()
+    assert lib.exb_pbe_workspace_bytes(1024, 12) > 0
+    assert lib.exb_knn_exact_workspace_bytes(0, 10, 4, 3) == 0      # empty input
+    assert lib.exb_knn_exact_workspace_bytes(10, 10, 4, 99) == 0    # k beyond EXB_MAX_K
+
+
+def test_cpu_tensors_are_rejected_loudly():
+    x = torch.randn(8, 4)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        exorl_b200.knn_topk(x, x, 2)
+    rms = exorl_b200.RMS("cpu")
+    pbe = exorl_b200.PBE(rms, 0.0, 2, True, True, "cpu")
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        pbe(x)
+    with pytest.raises(RuntimeError, match="CUDA device"):
+        exorl_b200.DeviceReplayBuffer("cpu", 100, 3, 0.99)
+
+
+def test_product_does_not_import_oracle():
+    root = pathlib.Path(exorl_b200.__file__).parent
+    for f in root.rglob("*.py"):
+        assert "oracle" not in f.read_text().replace("# oracle", ""), f
+    for f in (root / "csrc").glob("*"):
+        assert "oracle" not in f.read_text(), f
+
+
+def test_shard_bounds_partition():
+    from exorl_b200.relabel import shard_bounds
+    for n, w in ((10, 3), (1_000_000, 8), (7, 7), (5, 2)):
+        b = [shard_bounds(n, w, r) for r in range(w)]
+        assert b[0][0] == 0 and b[-1][1] == n
+        assert all(b[i][1] == b[i + 1][0] for i in range(w - 1))
+        sizes = [hi - lo for lo, hi in b]
+        assert max(sizes) - min(sizes) <= 1
+
+
+def test_rms_general_shape_cpu_formula():
+    """RMS with a non-(1,) shape is not on the kNN path and uses the reference formula with torch
+    ops on whatever device the state lives on."""
+    r = exorl_b200.RMS("cpu", shape=(3,))
+    x = torch.arange(12.).reshape(4, 3)
+    m, s = r(x)
+    assert m.shape == (3,) and r.n == pytest.approx(4.0001)
+    assert torch.allclose(m, x.mean(0) * 4 / 4.0001, rtol=1e-6)

@@ -1,0 +1,280 @@
+"""GPU parity: exorl_b200 (CUDA, through the C ABI) vs the oracle / reference golden vectors.
+
+Tolerances (north_star): kNN index sets bit-exact outside exact/near ties; rewards rel 1e-5."""
+import pickle
+import types
+
+import numpy as np
+import pytest
+import torch
+
+import exorl_b200 as xb
+from exorl_b200 import knn as xknn
+from oracle import RmsState, pbe_reward, knn_smallest, proto_reward, rms_step
+from helpers import reps, assert_knn_matches
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+RTOL = 1e-5
+
+
+def _pbe(clip, k, avg, rms_on, mode="auto"):
+    p = xb.PBE(xb.RMS(DEV), clip, k, avg, rms_on, DEV)
+    p.mode = mode
+    return p
+
+
+def _close(got, want, rtol=RTOL, atol=1e-7):
+    np.testing.assert_allclose(np.asarray(got, np.float64), np.asarray(want, np.float64),
+                               rtol=rtol, atol=atol, equal_nan=True)
+
+
+# ---------------------------------------------------------------- known answers
+REP4 = torch.tensor([[0., 0.], [3., 4.], [6., 8.], [0., 1.]])
+
+
+@pytest.mark.parametrize("avg,rms_on,clip,want", [
+    (True, True, 0.0, [0.30438635, 0.92008394, 1.02207816, 0.30438635]),
+    (True, True, 0.5, [0.10056251, 0.81514400, 0.92780966, 0.10056251]),
+    (True, False, 0.0, [0.40546510, 1.13825607, 1.25276291, 0.40546510]),
+    (True, False, 0.5, [0.22314355, 1.05477190, 1.17865503, 0.22314355]),
+    (False, True, 0.0, [0.30438960, 0.92009133, 1.02208614, 0.30438960]),
+    (False, True, 0.5, [0.0, 0.69789571, 0.82373059, 0.0]),
+    (False, False, 0.0, [0.69314718, 1.65682530, 1.79175949, 0.69314718]),
+])
+def test_kat_rewards(avg, rms_on, clip, want):
+    r = _pbe(clip, 2, avg, rms_on)(REP4.to(DEV))
+    assert r.shape == (4, 1) and r.dtype == torch.float32 and r.is_cuda
+    _close(r.flatten().cpu(), want)
+
+
+def test_kat_state_trajectory():
+    p = _pbe(0.0, 2, True, True)
+    x = REP4.to(DEV)
+    p(x)
+    assert float(p.rms.M) == pytest.approx(1.40531242, rel=1e-6)
+    assert float(p.rms.S) == pytest.approx(4.17146730, rel=1e-6)
+    assert p.rms.n == pytest.approx(8.0001)
+    r2 = p(x)
+    _close(r2.flatten().cpu(), [0.30438468, 0.92008013, 1.02207410, 0.30438468])
+    assert float(p.rms.M) == pytest.approx(1.40532124, rel=1e-6)
+    assert float(p.rms.S) == pytest.approx(4.17147541, rel=1e-6)
+    assert p.rms.n == pytest.approx(16.0001)
+
+
+def test_kat_rms_alone():
+    r = xb.RMS(DEV)
+    r(torch.tensor([[1.], [2.], [3.], [6.]], device=DEV))
+    assert float(r.M) == pytest.approx(2.99992490, rel=1e-6)
+    assert float(r.S) == pytest.approx(4.66679955, rel=1e-6)
+    m, s = r(torch.tensor([[10.], [20.]], device=DEV))
+    assert float(m) == pytest.approx(6.99988317, rel=1e-6)
+    assert float(s) == pytest.approx(51.77775192, rel=1e-6)
+    assert r.n == pytest.approx(6.0001) and m.shape == (1,) and m.is_cuda
+
+
+def test_k_out_of_range_raises_like_reference():
+    with pytest.raises(RuntimeError, match="selected index k out of range"):
+        _pbe(0.0, 5, True, True)(REP4.to(DEV))
+
+
+# ---------------------------------------------------------------- golden fixtures from the reference
+def test_golden_all_modes_three_calls(golden):
+    g = golden("pbe_reference.npz")
+    for c in range(int(g["n_cases"])):
+        tag = f"pbe{c:03d}"
+        b, d, k, avg, rms_on = (int(v) for v in g[f"{tag}_cfg"])
+        clip = float(g[f"{tag}_clip"])
+        p = _pbe(clip, k, bool(avg), bool(rms_on))
+        for call in range(3):
+            x = torch.from_numpy(g[f"rep_{b}_{d}_{call}"]).to(DEV)
+            r = p(x)
+            _close(r.cpu().numpy(), g[f"{tag}_reward{call}"])
+            if rms_on:
+                m, s, n = g[f"{tag}_state{call}"]
+                _close([float(p.rms.M), float(p.rms.S)], [m, s], rtol=2e-5, atol=1e-7)
+                assert p.rms.n == n
+
+
+@pytest.mark.parametrize("mode", ["exact", "screened"])
+def test_golden_knn_index_sets(golden, mode):
+    g = golden("knn_reference.npz")
+    for tag in ("sq512", "rect", "proto", "tiny"):
+        s, t = torch.from_numpy(g[f"{tag}_src"]), torch.from_numpy(g[f"{tag}_tgt"])
+        k = g[f"{tag}_idx"].shape[1]
+        sd = s.to(DEV)
+        td = sd if tag in ("sq512", "tiny") else t.to(DEV)
+        d, i = xb.knn_topk(sd, td, k, mode=mode)
+        torch.cuda.synchronize()
+        oracle = (torch.from_numpy(g[f"{tag}_dist"]), torch.from_numpy(g[f"{tag}_idx"]))
+        assert_knn_matches(s, t, k, d, i, oracle=oracle)
+
+
+def test_golden_proto(golden):
+    g = golden("proto_reference.npz")
+    z = torch.from_numpy(g["z"]).to(DEV)
+    full = torch.from_numpy(g["queue_full"]).to(DEV)
+    for tag, q in (("full", full.clone()),
+                   ("warm", torch.cat([full[:64], torch.zeros(192, 128, device=DEV)]))):
+        ptr = xb.proto_enqueue(q, 0, z, torch.arange(0, 32, device=DEV))
+        assert ptr == int(g[f"{tag}_ptr"])
+        assert np.array_equal(q.cpu().numpy(), g[f"{tag}_queue_after"])
+        for mode in ("exact", "screened"):
+            r = xb.proto_knn_reward(z, q, 3, mode=mode)
+            assert r.shape == (96, 1)
+            _close(r.cpu().numpy(), g[f"{tag}_reward"])
+
+
+# ---------------------------------------------------------------- oracle-diff on random inputs
+@pytest.mark.parametrize("mode", ["exact", "screened"])
+@pytest.mark.parametrize("b1,b2,d,k", [(300, 300, 512, 12), (257, 1000, 50, 12), (128, 2048, 128, 3),
+                                       (1024, 1024, 10, 12), (130, 513, 24, 1), (64, 700, 512, 16),
+                                       (5, 17, 3, 4)])
+def test_knn_vs_oracle(mode, b1, b2, d, k):
+    s = reps(b1 * 7 + d, b1, d)
+    t = s if b1 == b2 else reps(b2 * 3 + d, b2, d)
+    sd = s.to(DEV)
+    td = sd if b1 == b2 else t.to(DEV)
+    dist, idx = xb.knn_topk(sd, td, k, mode=mode)
+    assert_knn_matches(s, t, k, dist, idx)
+    if b1 == b2:   # self-match first, distance exactly 0
+        assert torch.equal(idx[:, 0].cpu().long(), torch.arange(b1))
+        assert torch.all(dist[:, 0] == 0)
+
+
+@pytest.mark.parametrize("mode", ["exact", "screened"])
+def test_c1_full_size_reward_and_indices(mode):
+    """BASELINE config 1: 1024 x 512, k=12, avg + rms, clip 0."""
+    x = reps(0, 1024, 512)
+    xd = x.to(DEV)
+    dist, idx = xb.knn_topk(xd, xd, 12, mode=mode)
+    assert_knn_matches(x, x, 12, dist, idx)
+    p = _pbe(0.0, 12, True, True, mode)
+    st = RmsState()
+    for _ in range(2):
+        want = pbe_reward(x, x, st, 12, True, True, 0.0)
+        got = p(xd)
+        _close(got.cpu().numpy(), want.numpy())
+    _close([float(p.rms.M), float(p.rms.S)], [float(st.M), float(st.S)], rtol=2e-5)
+    assert p.rms.n == st.n
+    if mode == "screened":
+        und, invalid, pairs, _ = xknn.screened_status(torch.device(DEV))
+        assert invalid == 0 and und <= 8 and pairs >= 1024 * 12
+
+
+@pytest.mark.parametrize("mode", ["exact", "screened"])
+def test_c2_proto_full_size(mode):
+    z = reps(1, 1024, 128, "unit")
+    q = reps(2, 2048, 128, "unit")
+    for queue in (q, torch.cat([q[:512], torch.zeros(1536, 128)])):   # full / warm-up state
+        want = proto_reward(z, queue, 3)
+        got = xb.proto_knn_reward(z.to(DEV), queue.to(DEV), 3, mode=mode)
+        _close(got.cpu().numpy(), want.numpy())
+
+
+@pytest.mark.parametrize("mode", ["exact", "screened"])
+def test_duplicates_and_exact_ties(mode):
+    """Duplicate rows (exact ties) are tolerated: distances match, indices valid and distinct."""
+    base = reps(9, 200, 64)
+    x = torch.cat([base, base[:100], base[:50]])          # up to 3 copies
+    xd = x.to(DEV)
+    dist, idx = xb.knn_topk(xd, xd, 5, mode=mode)
+    od, _ = knn_smallest(x, x, 5)
+    _close(dist.cpu().numpy(), od.numpy())
+    assert all(len(set(r)) == 5 for r in idx.cpu().tolist())
+
+
+def test_screened_handles_many_ties_through_fallback():
+    """More tied candidates than list slots: rows must come back exact via the fallback."""
+    z = reps(4, 256, 128, "unit")
+    q = torch.zeros(1024, 128)                            # every queue row at distance 1
+    got = xb.proto_knn_reward(z.to(DEV), q.to(DEV), 3, mode="screened")
+    _close(got.cpu().numpy(), proto_reward(z, q, 3).numpy())
+    und, invalid, _, _ = xknn.screened_status(torch.device(DEV))
+    assert und == 256 and invalid == 0
+
+
+def test_screened_range_fallback_for_unbounded_reps():
+    """Values outside fp16 range cannot be screened; the call must still return exact results."""
+    x = reps(12, 300, 32, "raw") * 1e5
+    xd = x.to(DEV)
+    dist, idx = xb.knn_topk(xd, xd, 4, mode="screened")
+    assert_knn_matches(x, x, 4, dist, idx)
+
+
+@pytest.mark.parametrize("mode", ["exact", "screened"])
+def test_unscaled_and_tiny_reps(mode):
+    for scale in (30.0, 1e-3):
+        x = reps(21, 400, 96, "raw") * scale
+        xd = x.to(DEV)
+        dist, idx = xb.knn_topk(xd, xd, 12, mode=mode)
+        assert_knn_matches(x, x, 12, dist, idx)
+
+
+def test_properties_translation_and_permutation():
+    x = reps(33, 512, 64)
+    xd = x.to(DEV)
+    _, i0 = xb.knn_topk(xd, xd, 8, mode="screened")
+    perm = torch.randperm(512, generator=torch.Generator().manual_seed(1))
+    xp = x[perm].to(DEV)
+    dp, ip = xb.knn_topk(xp, xp, 8, mode="screened")
+    assert_knn_matches(x[perm], x[perm], 8, dp, ip)
+    # permutation equivariance of the neighbour sets
+    inv = torch.empty_like(perm)
+    inv[perm] = torch.arange(512)
+    a = torch.sort(i0.cpu().long(), dim=1).values
+    b = torch.sort(perm[ip.cpu().long()][inv], dim=1).values
+    assert (a != b).any(dim=1).sum() <= 2     # only fp32 near-ties may differ
+
+
+def test_3d_rep_is_flattened_like_reference():
+    x = reps(5, 64, 24).reshape(64, 4, 6)
+    want = pbe_reward(x, x, RmsState(), 3, True, True, 0.0)
+    got = _pbe(0.0, 3, True, True)(x.to(DEV))
+    _close(got.cpu().numpy(), want.numpy())
+
+
+def test_compute_apt_reward_source_ne_target_and_grad_mode():
+    s, t = reps(1, 200, 64), reps(2, 900, 64)
+    args = types.SimpleNamespace(knn_k=12, knn_avg=True, knn_rms=True, knn_clip=0.0001)
+    st = RmsState()
+    want = pbe_reward(s, t, st, 12, True, True, 0.0001)
+    rms = xb.RMS(DEV)
+    sd = s.to(DEV).requires_grad_(True)            # must not fail under grad mode
+    got = xb.compute_apt_reward(sd, t.to(DEV), args, rms=rms)
+    assert not got.requires_grad
+    _close(got.cpu().numpy(), want.numpy())
+    assert rms.n == st.n
+
+
+def test_rms_matches_oracle_trajectory_large_and_strided():
+    r, st = xb.RMS(DEV), RmsState()
+    for i, n in enumerate((50000, 3, 1, 70000)):
+        x = reps(100 + i, n, 1, "raw") * 3 + 20
+        rms_step(st, x)
+        r(x.to(DEV))
+        _close([float(r.M), float(r.S)], [float(st.M), float(st.S)], rtol=2e-5)
+        assert r.n == st.n
+
+
+def test_pbe_and_rms_are_picklable():
+    p = _pbe(0.0, 3, True, True)
+    x = reps(8, 64, 16).to(DEV)
+    p(x)
+    q = pickle.loads(pickle.dumps(p))
+    assert q.rms.n == p.rms.n and torch.equal(q.rms.M, p.rms.M)
+    assert torch.equal(q(x), p(x))
+
+
+def test_large_moments_path():
+    """nq*k above the single-block limit exercises the multi-block moments kernel."""
+    x = reps(77, 4096, 32)
+    st = RmsState()
+    want = pbe_reward(x, x, st, 12, True, True, 0.0)
+    p = _pbe(0.0, 12, True, True)
+    got = p(x.to(DEV))
+    _close(got.cpu().numpy(), want.numpy())
+    _close([float(p.rms.M), float(p.rms.S)], [float(st.M), float(st.S)], rtol=2e-5)
+    st2 = RmsState()
+    want2 = pbe_reward(x, x, st2, 12, False, True, 0.5)
+    _close(_pbe(0.5, 12, False, True)(x.to(DEV)).cpu().numpy(), want2.numpy())

@@ -1,0 +1,70 @@
+"""Sharded relabel on one device: virtual shards + merge kernel == unsharded."""
+import types
+
+import numpy as np
+import pytest
+import torch
+
+import exorl_b200 as xb
+from exorl_b200.relabel import shard_bounds, _cuda_merge
+from oracle import RmsState, pbe_reward, knn_smallest
+from helpers import reps, assert_knn_matches
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+@pytest.mark.parametrize("mode", ["exact", "screened"])
+@pytest.mark.parametrize("world", [2, 8])
+def test_virtual_shards_merge_equals_unsharded(mode, world):
+    n, k = 3000, 12
+    x = reps(5, n, 64)
+    xd = x.to(DEV)
+    ds, is_ = [], []
+    for r in range(world):
+        lo, hi = shard_bounds(n, world, r)
+        d, i = xb.knn_topk(xd, xd[lo:hi], k, idx_base=lo, mode=mode)
+        ds.append(d)
+        is_.append(i)
+    d, i = _cuda_merge(torch.stack(ds), torch.stack(is_), k)
+    assert_knn_matches(x, x, k, d, i)
+
+
+def test_merge_tie_rule_and_padding():
+    d = torch.tensor([[[1., 2., 2.]], [[0.5, 2., 9.]]], device=DEV)          # (G=2, n=1, k=3)
+    i = torch.tensor([[[7, 3, 9]], [[100, 1, 5]]], dtype=torch.int32, device=DEV)
+    od, oi = _cuda_merge(d, i, 3)
+    assert od.flatten().tolist() == [0.5, 1.0, 2.0] and oi.flatten().tolist() == [100, 7, 1]
+
+
+def test_relabel_single_process_matches_oracle():
+    n = 5000
+    x = reps(6, n, 128)
+    args = types.SimpleNamespace(knn_k=12, knn_avg=True, knn_rms=True, knn_clip=0.0)
+    rms = xb.RMS(DEV)
+    got, d, i = xb.relabel_apt_reward(x.to(DEV), args, rms=rms, return_knn=True)
+    st = RmsState()
+    knn = knn_smallest(x, x, 12)
+    want = pbe_reward(x, x, st, 12, True, True, 0.0, knn=knn)
+    np.testing.assert_allclose(got.cpu().numpy(), want.numpy(), rtol=1e-5, atol=1e-7)
+    assert rms.n == st.n
+    assert_knn_matches(x, x, 12, d, i, oracle=knn)
+
+
+def test_medium_bank_screened_equals_exact_kernel():
+    """32 768 x 32 768 x 512 (SURVEY §8c full-N check size): the tcgen05 path and the fp32
+    CUDA-core path agree; a 256-query subset is checked against the oracle."""
+    n = 32768
+    x = reps(5, n, 512)
+    xd = x.to(DEV)
+    d_s, i_s = xb.knn_topk(xd, xd, 12, mode="screened")
+    from exorl_b200 import knn as xknn
+    und, invalid, pairs, _ = xknn.screened_status(torch.device(DEV))
+    assert invalid == 0 and und < n // 100
+    d_e, i_e = xb.knn_topk(xd, xd, 12, mode="exact")
+    np.testing.assert_allclose(d_s.cpu().numpy(), d_e.cpu().numpy(), rtol=1e-6)
+    diff = (i_s.sort(dim=1).values != i_e.sort(dim=1).values).any(dim=1).sum().item()
+    assert diff <= n // 1000          # only fp32 near-ties may differ between summation orders
+    sub = torch.arange(0, n, n // 256)[:256]
+    od, oi = knn_smallest(x[sub], x, 12)
+    assert_knn_matches(x[sub], x, 12, d_s[sub.to(DEV)], i_s[sub.to(DEV)], oracle=(od, oi))

@@ -1,0 +1,193 @@
+"""GPU parity of the replay gather: bit-exact tuples vs the reference's ReplayBuffer._sample /
+OfflineReplayBuffer._sample (golden fixtures) and vs the oracle on boundary positions."""
+import pathlib
+import random
+import types
+
+import numpy as np
+import pytest
+import torch
+
+import exorl_b200 as xb
+from oracle import (nstep_transition, onestep_transition, write_episode_npz,
+                    draw_indices_philox, flatten_episodes)
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _episodes(g, tag):
+    lens = g[f"{tag}_lens"]
+    names = sorted({k.split("_", 3)[3] for k in g.files if k.startswith(f"{tag}_ep0_")})
+    return [{n: g[f"{tag}_ep{e}_{n}"] for n in names} for e in range(len(lens))]
+
+
+def _buffer(eps, nstep, meta=(), max_size=10 ** 6):
+    buf = xb.DeviceReplayBuffer(DEV, max_size, nstep, 0.99, meta_names=meta)
+    for e, ep in enumerate(eps):
+        buf.add_episode(ep, key=f"episode_{e}_{len(ep['reward']) - 1}.npz")
+    return buf
+
+
+@pytest.mark.parametrize("tag", ["state_n3", "state_n1", "meta_n3", "pix_n3", "state_n5"])
+def test_golden_nstep_bit_exact(golden, tag):
+    g = golden("replay_reference.npz")
+    eps = _episodes(g, tag)
+    nstep = int(g[f"{tag}_nstep"])
+    meta = ("skill", "done") if tag.startswith("meta") else ()
+    buf = _buffer(eps, nstep, meta)
+    out = buf.gather(buf.rows_from_draws(g[f"{tag}_draws"]))
+    torch.cuda.synchronize()
+    assert len(out) == 5 + len(meta)
+    for j, t in enumerate(out):
+        want = g[f"{tag}_out{j}"]
+        got = t.cpu().numpy()
+        assert got.dtype == want.dtype and got.shape == want.shape, (tag, j)
+        assert np.array_equal(got, want), (tag, j)
+
+
+def test_golden_offline_bit_exact(golden):
+    g = golden("replay_reference.npz")
+    buf = _buffer(_episodes(g, "state_n3"), 1)
+    out = buf.gather(buf.rows_from_draws(g["offline_draws"]), offline=True)
+    for j, t in enumerate(out):
+        assert np.array_equal(t.cpu().numpy(), g[f"offline_out{j}"]), j
+
+
+def _synth(rng, L, obs_shape=(24,), dtype=np.float32, terminal=False):
+    n = L + 1
+    obs = (rng.integers(0, 256, (n, *obs_shape), dtype=np.uint8) if dtype == np.uint8
+           else rng.standard_normal((n, *obs_shape)).astype(np.float32))
+    d = np.ones((n, 1), np.float32)
+    if terminal:
+        d[-1] = 0
+        d[L // 2] = 0.5
+    return {"observation": obs, "action": rng.uniform(-1, 1, (n, 6)).astype(np.float32),
+            "reward": rng.uniform(0, 1, (n, 1)).astype(np.float32), "discount": d}
+
+
+@pytest.mark.parametrize("nstep", [1, 3, 7])
+def test_boundaries_and_terminal_discounts_vs_oracle(nstep):
+    rng = np.random.default_rng(0)
+    eps = [_synth(rng, L, terminal=(i % 2 == 0)) for i, L in enumerate((nstep, 9, 30, nstep + 1))]
+    buf = _buffer(eps, nstep)
+    draws = []
+    for e, ep in enumerate(eps):
+        L = len(ep["reward"]) - 1
+        draws += [(e, 1), (e, L - nstep + 1)] + [(e, i) for i in range(1, L - nstep + 2)]
+    out = buf.gather(buf.rows_from_draws(draws))
+    for s, (e, idx) in enumerate(draws):
+        want = nstep_transition(eps[e], idx, nstep, 0.99)
+        for j in range(5):
+            assert np.array_equal(out[j][s].cpu().numpy(), np.asarray(want[j])), (e, idx, j)
+
+
+def test_pixel_rows_large_vectorised_copy():
+    rng = np.random.default_rng(4)
+    eps = [_synth(rng, 12, (9, 84, 84), np.uint8) for _ in range(3)]
+    buf = _buffer(eps, 3)
+    draws = [(e, i) for e in range(3) for i in (1, 5, 10)]
+    out = buf.gather(buf.rows_from_draws(draws))
+    assert out[0].dtype == torch.uint8 and out[0].shape == (9, 9, 84, 84)
+    for s, (e, idx) in enumerate(draws):
+        want = nstep_transition(eps[e], idx, 3, 0.99)
+        assert np.array_equal(out[0][s].cpu().numpy(), want[0])
+        assert np.array_equal(out[4][s].cpu().numpy(), want[4])
+
+
+def test_unaligned_rows_take_narrow_vector_paths():
+    rng = np.random.default_rng(5)
+    eps = []
+    for _ in range(2):
+        ep = _synth(rng, 10, (7,))                       # 28-byte obs rows
+        ep["action"] = rng.uniform(-1, 1, (11, 3)).astype(np.float32)   # 12-byte rows
+        ep["flag"] = rng.integers(0, 2, (11, 5)).astype(np.uint8)       # 5-byte rows
+        eps.append(ep)
+    buf = _buffer(eps, 2, meta=("flag",))
+    draws = [(0, 1), (1, 9), (0, 4)]
+    out = buf.gather(buf.rows_from_draws(draws))
+    for s, (e, idx) in enumerate(draws):
+        want = nstep_transition(eps[e], idx, 2, 0.99, ("flag",))
+        for j in range(6):
+            assert np.array_equal(out[j][s].cpu().numpy(), np.asarray(want[j]))
+
+
+def test_philox_draw_matches_oracle_and_ranges():
+    rng = np.random.default_rng(7)
+    lens = [5, 40, 13, 1000, 8]
+    eps = [_synth(rng, L) for L in lens]
+    buf = _buffer(eps, 3)
+    sorted_eps, starts, elen = buf._tables()
+    rows = buf.draw_rows_philox(4096, seed=1234567890123, call=42).cpu().numpy()
+    _, _, want = draw_indices_philox(1234567890123, 42, 4096, starts.cpu().numpy(),
+                                     elen.cpu().numpy(), 3)
+    assert np.array_equal(rows, want)
+    # every draw is a valid start: idx in [1, L-nstep+1]
+    st, ln = starts.cpu().numpy(), elen.cpu().numpy()
+    ep = np.searchsorted(np.sort(st), rows, side="right") - 1
+    order = np.argsort(st)
+    idx = rows - st[order][ep]
+    assert idx.min() >= 1 and np.all(idx <= ln[order][ep] - 3 + 1)
+    # uniform over episodes (not over transitions)
+    counts = np.bincount(ep, minlength=5) / 4096
+    assert np.all(np.abs(counts - 0.2) < 0.03)
+
+
+def test_loader_dropin_signature_and_reference_rng_parity(tmp_path):
+    """make_replay_loader with the reference's positional signature; with sampler
+    'reference_rng' the stream of batches equals the reference algorithm's single-process stream
+    for the same seeds (oracle arithmetic on the reference's own RNG call order)."""
+    rng = np.random.default_rng(3)
+    lens = [20, 7, 33, 12]
+    eps = []
+    for e, L in enumerate(lens):
+        ep = _synth(rng, L, terminal=(e == 1))
+        ep["skill"] = rng.standard_normal((L + 1, 4)).astype(np.float32)
+        write_episode_npz(ep, tmp_path / f"episode_{e}_{L}.npz")
+        eps.append(ep)
+    storage = types.SimpleNamespace(_replay_dir=pathlib.Path(tmp_path),
+                                    _meta_specs=(types.SimpleNamespace(name="skill"),))
+    loader = xb.make_replay_loader(storage, 1000000, 16, 4, True, 3, 0.99, device=DEV,
+                                   sampler="reference_rng")
+    random.seed(11)
+    np.random.seed(11)
+    it = iter(loader)
+    batches = [next(it) for _ in range(3)]
+    random.seed(11)
+    np.random.seed(11)
+    order = sorted(range(4), key=lambda e: f"episode_{e}_{lens[e]}.npz")
+    for batch in batches:
+        assert len(batch) == 6 and all(t.is_cuda for t in batch)
+        for s in range(16):
+            e = random.choice(order)
+            idx = np.random.randint(0, lens[e] - 3 + 1) + 1
+            want = nstep_transition(eps[e], idx, 3, 0.99, ("skill",))
+            for j in range(6):
+                assert np.array_equal(batch[j][s].cpu().numpy(), np.asarray(want[j]))
+    # philox loader: yields forever, right shapes/dtypes
+    loader2 = xb.make_replay_loader(storage, 1000000, 1024, 4, True, 3, 0.99, device=DEV, seed=5)
+    obs, act, rew, disc, nobs, skill = next(iter(loader2))
+    assert obs.shape == (1024, 24) and act.shape == (1024, 6) and rew.shape == (1024, 1)
+    assert disc.shape == (1024, 1) and nobs.shape == (1024, 24) and skill.shape == (1024, 4)
+
+
+def test_offline_loader_and_fifo_eviction(tmp_path):
+    rng = np.random.default_rng(8)
+    eps = []
+    for e in range(6):
+        ep = _synth(rng, 10)
+        write_episode_npz(ep, tmp_path / f"episode_{e}_10.npz")
+        eps.append(ep)
+    loader = xb.make_offline_replay_loader(None, pathlib.Path(tmp_path), 1000, 32, 1, 0.99,
+                                           device=DEV, seed=1)
+    obs, act, rew, disc, nobs = next(iter(loader))
+    assert obs.shape == (32, 24) and torch.all(disc == np.float32(0.99))
+    # FIFO eviction by episode at max_size (utils/replay_buffer.py:178-182)
+    buf = xb.DeviceReplayBuffer(DEV, 35, 3, 0.99)
+    for e, ep in enumerate(eps):
+        buf.add_episode(ep, key=f"episode_{e}_10.npz")
+        assert len(buf) <= 35
+    assert [x["key"] for x in buf.episodes] == [f"episode_{e}_10.npz" for e in (3, 4, 5)]
+    out = buf.gather(buf.rows_from_draws([(0, 1), (2, 8)]))
+    assert np.array_equal(out[0][0].cpu().numpy(), eps[3]["observation"][0])
+    assert np.array_equal(out[4][1].cpu().numpy(), eps[5]["observation"][10])

@@ -1,0 +1,110 @@
+"""World-size-2 gloo test (CPU) of the sharded relabel's partition + exchange logic.  The three
+compute stages are replaced by oracle-backed stand-ins (test infrastructure); what is under test
+is exorl_b200.relabel's shard bounds, all_gather / all_to_all layouts, sums all-reduce and the
+final reward gather."""
+import os
+import socket
+import types
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+class _OracleStages:
+    """CPU stand-ins with the same contracts as the CUDA stages."""
+
+    @staticmethod
+    def local_knn(rep, lo, hi, k, mode):
+        from oracle import knn_smallest
+        d, i = knn_smallest(rep, rep[lo:hi], k)
+        return d, (i + lo).to(torch.int32)
+
+    @staticmethod
+    def merge(d_lists, i_lists, k):
+        g, n, _ = d_lists.shape
+        d = d_lists.permute(1, 0, 2).reshape(n, g * k)
+        i = i_lists.permute(1, 0, 2).reshape(n, g * k)
+        key = d.double() * 1e7 + i.double() * 1e-3          # smaller distance, then smaller index
+        pos = key.argsort(dim=1)[:, :k]
+        return torch.gather(d, 1, pos), torch.gather(i, 1, pos)
+
+    @staticmethod
+    def sums(knn_dist, k, avg):
+        v = (knn_dist if avg else knn_dist[:, -1]).double().reshape(-1)
+        return torch.tensor([v.numel(), v.sum(), (v * v).sum()], dtype=torch.float64)
+
+    @staticmethod
+    def finish(knn_dist, k, avg, use_rms, clip, sums, rms):
+        r = (knn_dist if avg else knn_dist[:, -1:]).clone()
+        if use_rms:
+            bs, s, ss = (float(x) for x in sums)
+            mean = s / bs
+            var = (ss - s * mean) / (bs - 1)
+            m, sv, n = float(rms.M), float(rms.S), rms.n
+            delta = mean - m
+            rms.M = torch.tensor([m + delta * bs / (n + bs)], dtype=torch.float32)
+            rms.S = torch.tensor([(sv * n + var * bs + delta * delta * n * bs / (n + bs))
+                                  / (n + bs)], dtype=torch.float32)
+            r = r / rms.M
+        if clip >= 0:
+            r = torch.clamp(r - clip, min=0)
+        if avg:
+            r = r.mean(dim=1, keepdim=True)
+        return torch.log(r + 1.0)
+
+    @staticmethod
+    def reward(knn_dist, k, avg, use_rms, clip, rms):
+        sums = _OracleStages.sums(knn_dist, k, avg)
+        out = _OracleStages.finish(knn_dist, k, avg, use_rms, clip, sums, rms)
+        if use_rms:
+            rms.n += knn_dist.size(0) * (k if avg else 1)
+        return out
+
+
+def _worker(rank, world, port, exchange, n, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from exorl_b200.relabel import relabel_apt_reward
+        g = torch.Generator().manual_seed(5)
+        rep = torch.tanh(torch.randn(n, 16, generator=g))
+        args = types.SimpleNamespace(knn_k=4, knn_avg=True, knn_rms=True, knn_clip=0.0)
+        rms = types.SimpleNamespace(M=torch.zeros(1), S=torch.ones(1), n=1e-4)
+        r = relabel_apt_reward(rep, args, rms=rms, exchange=exchange, stages=_OracleStages)
+        q.put((rank, r.numpy(), float(rms.M), float(rms.S), rms.n))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("exchange", ["all_gather", "all_to_all"])
+@pytest.mark.parametrize("n", [64, 51])
+def test_two_rank_relabel_equals_unsharded(exchange, n):
+    from oracle import RmsState, pbe_reward
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, exchange, n, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in range(2)], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    g = torch.Generator().manual_seed(5)
+    rep = torch.tanh(torch.randn(n, 16, generator=g))
+    st = RmsState()
+    want = pbe_reward(rep, rep, st, 4, True, True, 0.0).numpy()
+    for rank, r, m, s, cnt in res:
+        assert r.shape == (n, 1)
+        np.testing.assert_allclose(r, want, rtol=1e-5, atol=1e-7)
+        assert m == pytest.approx(float(st.M), rel=1e-5) and s == pytest.approx(float(st.S), rel=1e-4)
+        assert cnt == pytest.approx(st.n)
