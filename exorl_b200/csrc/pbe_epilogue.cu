@@ -69,6 +69,10 @@ __device__ void rms_apply(const double* sums, const RmsParams& p) {
   *p.s_out = (float)new_s;
 }
 
+// torch.maximum(t, 0) propagates NaN (0/0 when every distance is 0, e.g. k = 1 on source =
+// target); fmaxf would not.
+__device__ __forceinline__ float clip_nan(float t) { return (t < 0.f) ? 0.f : t; }
+
 __device__ __forceinline__ float pbe_row(const float* __restrict__ d, int k, int avg, float inv_on,
                                          float m, int use_clip, float clip) {
   // r / M (true division, utils.py:304/311), max(r - clip, 0) (:305-308/:312-315),
@@ -79,14 +83,14 @@ __device__ __forceinline__ float pbe_row(const float* __restrict__ d, int k, int
     for (int j = 0; j < k; ++j) {
       float v = d[j];
       if (inv_on != 0.f) v = v / m;
-      if (use_clip) v = fmaxf(v - clip, 0.f);
+      if (use_clip) v = clip_nan(v - clip);
       acc += v;
     }
     r = acc / (float)k;
   } else {
     float v = d[k - 1];
     if (inv_on != 0.f) v = v / m;
-    if (use_clip) v = fmaxf(v - clip, 0.f);
+    if (use_clip) v = clip_nan(v - clip);
     r = v;
   }
   return logf(r + 1.0f);
