@@ -602,6 +602,15 @@ static int make_tmap(CUtensorMap* map, const void* ptr, int64_t rows, int dpad, 
   return EXB_OK;
 }
 
+// Optional CUDA-event bracket around every screening-kernel launch (bench.py's roofline leg).
+struct ScreenProfile {
+  bool on = false;
+  int n = 0;
+  cudaEvent_t e0[64], e1[64];
+  bool created = false;
+};
+static ScreenProfile g_prof;
+
 static inline int dim_pad(int dim) { return (dim + SCR_KC - 1) / SCR_KC * SCR_KC; }
 
 struct ScreenPlan {
@@ -750,8 +759,11 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
   sp.tiles_per_split = pl.tiles_per_split; sp.splits = pl.splits; sp.k = k;
   sp.stages = pl.stages; sp.cand_idx = w.cand_idx; sp.cand_cnt = w.cand_cnt;
   dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
+  const bool prof = g_prof.on && g_prof.n < 64;
+  if (prof) EXB_CUDA(cudaEventRecord(g_prof.e0[g_prof.n], st));
   knn_screen_kernel<<<grid, SCR_THREADS, pl.smem, st>>>(tq, tb, sp);
   EXB_LAUNCH_CHECK();
+  if (prof) EXB_CUDA(cudaEventRecord(g_prof.e1[g_prof.n++], st));
 
   knn_rerank_kernel<<<(unsigned)((nq + 7) / 8), 256, 0, st>>>(
       src, nq, bank, dim, k, idx_base, w.cand_idx, w.cand_cnt, pl.splits, same ? w.bsc : w.qsc,
@@ -774,5 +786,29 @@ extern "C" int exb_knn_screened_status_sync(const void* workspace, int32_t host_
   host_status[1] = s.invalid;
   host_status[2] = (int32_t)(s.pairs > 0x7fffffffULL ? 0x7fffffff : s.pairs);
   host_status[3] = (int32_t)(s.pairs >> 31);
+  return EXB_OK;
+}
+
+extern "C" int exb_profile_begin(int enable) {
+  if (enable && !g_prof.created) {
+    for (int i = 0; i < 64; ++i) {
+      EXB_CUDA(cudaEventCreate(&g_prof.e0[i]));
+      EXB_CUDA(cudaEventCreate(&g_prof.e1[i]));
+    }
+    g_prof.created = true;
+  }
+  g_prof.on = enable != 0;
+  g_prof.n = 0;
+  return EXB_OK;
+}
+
+extern "C" int exb_profile_collect_sync(float* host_ms, int cap, int* host_n) {
+  EXB_CHECK_ARG(host_ms && host_n && cap >= 0, "bad arguments");
+  int n = g_prof.n < cap ? g_prof.n : cap;
+  for (int i = 0; i < n; ++i) {
+    EXB_CUDA(cudaEventSynchronize(g_prof.e1[i]));
+    EXB_CUDA(cudaEventElapsedTime(&host_ms[i], g_prof.e0[i], g_prof.e1[i]));
+  }
+  *host_n = n;
   return EXB_OK;
 }

@@ -30,7 +30,8 @@ def shard_bounds(n, world, rank):
 
 
 def _cuda_local_knn(rep, lo, hi, k, mode):
-    return knn_topk(rep, rep[lo:hi], k, idx_base=lo, mode=mode)
+    bank = rep if (lo == 0 and hi == rep.size(0)) else rep[lo:hi]   # `is` marks source = target
+    return knn_topk(rep, bank, k, idx_base=lo, mode=mode)
 
 
 def _cuda_merge(dist_lists, idx_lists, k):

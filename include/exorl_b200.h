@@ -91,6 +91,11 @@ int exb_knn_screened_f32(const float* src, int64_t nq, const float* bank, int64_
 int exb_knn_screened_status_sync(const void* workspace, int32_t host_status[4],
                                  exb_stream_t stream);
 
+/* Measurement hook (bench.py): when enabled, every screening-kernel launch is bracketed by CUDA
+ * events on its own stream (up to 64 launches); collect returns their durations in ms. */
+int exb_profile_begin(int enable);
+int exb_profile_collect_sync(float* host_ms, int cap, int* host_n);
+
 /* --------------------------------------------------------------------------------------------
  * Sharded kNN: merge G per-shard (dist, idx) lists (each [nq,k], ascending) into the global
  * k smallest per row; ties -> smaller index.  lists are laid out [G, nq, k] (the result of an
