@@ -29,6 +29,7 @@
 #include <float.h>
 #include <limits.h>
 #include <math.h>
+#include <stdlib.h>
 
 namespace exb {
 
@@ -150,6 +151,59 @@ __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// ---- cta_group::2 (CTA pair) variants.  PEER_MASK clears the CTA-parity bit of a shared-window
+// address so that it names the same offset in the even (leader) CTA of the pair (the convention
+// of cute::Sm100MmaPeerBitMask).
+constexpr uint32_t PEER_MASK = 0xFEFFFFFFu;
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, int c0,
+                                                 int c1, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
+      "l"(map), "r"(c0), "r"(c1), "r"(bar & PEER_MASK)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar & PEER_MASK) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_512_pair(uint32_t smem_dst) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(
+      smem_dst));
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+}
+__device__ __forceinline__ void tmem_dealloc_512_pair(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" ::"r"(taddr));
+}
+__device__ __forceinline__ void umma_f16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                              uint32_t idesc, uint32_t accumulate) {
+  const uint32_t z = 0;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, {%5, %5, %5, %5, %5, %5, %5, %5}, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(z)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
+  const uint16_t mask = 3;
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64"
+      " [%0], %1;" ::"r"(bar),
+      "h"(mask)
+      : "memory");
+}
+
 // K-major, 128-byte swizzle shared-memory matrix descriptor (cute::UMMA::SmemDescriptor layout):
 // start>>4 [0,14), LBO>>4 [16,30) (unused for swizzled K-major, 1), SBO>>4 [32,46) = 1024 B
 // between 8-row groups, version 1 at [46,48), layout SWIZZLE_128B = 2 at [61,64).
@@ -159,8 +213,10 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
 }
 // kind::f16 instruction descriptor: D=F32 (bit 4), A=B=F16 (0), K-major both, N>>3 at [17,23),
 // M>>4 at [24,29).
-constexpr uint32_t SCR_IDESC = (1u << 4) | ((uint32_t)(SCR_N >> 3) << 17) |
-                               ((uint32_t)(SCR_M >> 4) << 24);
+template <int CG>
+constexpr uint32_t scr_idesc() {
+  return (1u << 4) | ((uint32_t)(SCR_N >> 3) << 17) | ((uint32_t)((SCR_M * CG) >> 4) << 24);
+}
 
 // ------------------------------------------------------------------------------------------
 // prep: fp32 rows -> padded fp16 operand, half squared norm of the rounded row, rounding error
@@ -277,6 +333,7 @@ __device__ __forceinline__ void list_insert(ListState& s, float* lv, int* li, fl
   }
 }
 
+template <int CG>
 __global__ void __launch_bounds__(SCR_THREADS, 1)
 knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
                   const __grid_constant__ CUtensorMap tmap_b, const ScreenParams p) {
@@ -285,10 +342,14 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
   uint8_t* sm = smem_raw + (base - raw);
+  constexpr uint32_t B_STAGE = SCR_B_STAGE_BYTES / CG;   // this CTA's share of a bank tile chunk
+  constexpr int B_ROWS = SCR_N / CG;
+  const uint32_t cta_rank = (CG == 2) ? cluster_ctarank() : 0u;
+  const bool leader = cta_rank == 0;
   const int nkc = p.nkc, stages = p.stages;
   const uint32_t a_off = 0;
   const uint32_t b_off = a_off + (uint32_t)nkc * SCR_A_CHUNK_BYTES;
-  const uint32_t lv_off = b_off + (uint32_t)stages * SCR_B_STAGE_BYTES;
+  const uint32_t lv_off = b_off + (uint32_t)stages * B_STAGE;
   const uint32_t li_off = lv_off + SCR_CAP * SCR_M * 4;
   const uint32_t hn_off = li_off + SCR_CAP * SCR_M * 4;
   const uint32_t bar_off = hn_off + 2 * SCR_N * 4;
@@ -321,38 +382,54 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
     mbar_init(bar_a, 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_tfull(s), 1);
-      mbar_init(bar_tempty(s), 4);
+      mbar_init(bar_tempty(s), 4 * CG);
     }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc_512(smem_u32(s_tmem));
+  if (warp == 1) {
+    if constexpr (CG == 2) tmem_alloc_512_pair(smem_u32(s_tmem));
+    else tmem_alloc_512(smem_u32(s_tmem));
+  }
   tc_fence_before();
   __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all();   // peer barriers initialised before any remote signal
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0 && n_local > 0) {
-      mbar_expect_tx(bar_a, (uint32_t)nkc * SCR_A_CHUNK_BYTES);
-      for (int kc = 0; kc < nkc; ++kc)
-        tma_load_2d(base + a_off + kc * SCR_A_CHUNK_BYTES, &tmap_q, kc * SCR_KC,
-                    m_tile * SCR_M, bar_a);
+      // In pair mode both CTAs' loads complete on the LEADER's barriers; only the leader arms them
+      // (with the bytes of both CTAs).
+      if (leader) mbar_expect_tx(bar_a, (uint32_t)nkc * SCR_A_CHUNK_BYTES * CG);
+      for (int kc = 0; kc < nkc; ++kc) {
+        if constexpr (CG == 2)
+          tma_load_2d_pair(base + a_off + kc * SCR_A_CHUNK_BYTES, &tmap_q, kc * SCR_KC,
+                           m_tile * SCR_M, bar_a);
+        else
+          tma_load_2d(base + a_off + kc * SCR_A_CHUNK_BYTES, &tmap_q, kc * SCR_KC,
+                      m_tile * SCR_M, bar_a);
+      }
       int stage = 0;
       uint32_t phase = 0;
       for (int t = t_begin; t < t_end; ++t) {
+        const int brow = t * SCR_N + (int)cta_rank * B_ROWS;
         for (int kc = 0; kc < nkc; ++kc) {
           mbar_wait(bar_empty(stage), phase ^ 1u);
-          mbar_expect_tx(bar_full(stage), SCR_B_STAGE_BYTES);
-          tma_load_2d(base + b_off + stage * SCR_B_STAGE_BYTES, &tmap_b, kc * SCR_KC, t * SCR_N,
-                      bar_full(stage));
+          if (leader) mbar_expect_tx(bar_full(stage), SCR_B_STAGE_BYTES);
+          if constexpr (CG == 2)
+            tma_load_2d_pair(base + b_off + stage * B_STAGE, &tmap_b, kc * SCR_KC, brow,
+                             bar_full(stage));
+          else
+            tma_load_2d(base + b_off + stage * B_STAGE, &tmap_b, kc * SCR_KC, brow,
+                        bar_full(stage));
           if (++stage == stages) { stage = 0; phase ^= 1u; }
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0 && n_local > 0) {
+    if (lane == 0 && n_local > 0 && leader) {
       mbar_wait(bar_a, 0);
       tc_fence_after();
       int stage = 0;
@@ -366,17 +443,23 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
           mbar_wait(bar_full(stage), phase);
           tc_fence_after();
           const uint64_t adesc = make_sw128_desc(base + a_off + kc * SCR_A_CHUNK_BYTES);
-          const uint64_t bdesc = make_sw128_desc(base + b_off + stage * SCR_B_STAGE_BYTES);
+          const uint64_t bdesc = make_sw128_desc(base + b_off + stage * B_STAGE);
 #pragma unroll
           for (int ki = 0; ki < SCR_KC / 16; ++ki) {
             // advance 16 fp16 = 32 bytes inside the swizzle atom: +2 in the (addr >> 4) field
-            umma_f16(d_tmem, adesc + (uint64_t)(2 * ki), bdesc + (uint64_t)(2 * ki), SCR_IDESC,
-                     (kc | ki) != 0 ? 1u : 0u);
+            if constexpr (CG == 2)
+              umma_f16_pair(d_tmem, adesc + (uint64_t)(2 * ki), bdesc + (uint64_t)(2 * ki),
+                            scr_idesc<2>(), (kc | ki) != 0 ? 1u : 0u);
+            else
+              umma_f16(d_tmem, adesc + (uint64_t)(2 * ki), bdesc + (uint64_t)(2 * ki),
+                       scr_idesc<1>(), (kc | ki) != 0 ? 1u : 0u);
           }
-          umma_commit(bar_empty(stage));
+          if constexpr (CG == 2) umma_commit_pair(bar_empty(stage));
+          else umma_commit(bar_empty(stage));
           if (++stage == stages) { stage = 0; phase ^= 1u; }
         }
-        umma_commit(bar_tfull(as));
+        if constexpr (CG == 2) umma_commit_pair(bar_tfull(as));
+        else umma_commit(bar_tfull(as));
       }
     }
   } else {
@@ -452,7 +535,10 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_tempty(as));
+      if (lane == 0) {
+        if constexpr (CG == 2) mbar_arrive_leader(bar_tempty(as));
+        else mbar_arrive(bar_tempty(as));
+      }
     }
 
     if (row_ok) {
@@ -465,9 +551,11 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
 
   tc_fence_before();
   __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all();   // the pair shares TMEM/smem until both are done
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc_512(tmem_base);
+    if constexpr (CG == 2) tmem_dealloc_512_pair(tmem_base);
+    else tmem_dealloc_512(tmem_base);
   }
 }
 
@@ -614,6 +702,7 @@ static ScreenProfile g_prof;
 static inline int dim_pad(int dim) { return (dim + SCR_KC - 1) / SCR_KC * SCR_KC; }
 
 struct ScreenPlan {
+  int cg;   // CTAs cooperating on one MMA (1, or 2 = cta_group::2 pair)
   int dpad, nkc, n_tiles, m_tiles, splits, tiles_per_split, stages;
   size_t smem;
   int fb_cap, fb_splits;
@@ -626,6 +715,14 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
   pl->nkc = pl->dpad / SCR_KC;
   pl->n_tiles = (int)((nb + SCR_N - 1) / SCR_N);
   pl->m_tiles = (int)((nq + SCR_M - 1) / SCR_M);
+  // CTA pairs (cta_group::2) halve each CTA's share of the bank-tile traffic and leave room for a
+  // 4-deep TMA ring; EXB_SCREEN_CG=1 forces the single-CTA kernel (A/B measurements).
+  static const int forced_cg = [] {
+    const char* e = getenv("EXB_SCREEN_CG");
+    return e ? atoi(e) : 0;
+  }();
+  pl->cg = (forced_cg == 1 || forced_cg == 2) ? forced_cg : (pl->m_tiles >= 2 ? 2 : 1);
+  pl->m_tiles = (pl->m_tiles + pl->cg - 1) / pl->cg * pl->cg;
   int splits = sm_count() / pl->m_tiles;
   if (splits > pl->n_tiles) splits = pl->n_tiles;
   if (splits > 16) splits = 16;
@@ -634,11 +731,12 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
   pl->splits = (pl->n_tiles + pl->tiles_per_split - 1) / pl->tiles_per_split;
   const size_t fixed = (size_t)pl->nkc * SCR_A_CHUNK_BYTES + 2 * SCR_CAP * SCR_M * 4 +
                        2 * SCR_N * 4 + (2 * SCR_MAX_STAGES + 5) * 8 + 16 + 1024;
-  int stages = (int)((SCR_SMEM_LIMIT - fixed) / SCR_B_STAGE_BYTES);
+  const int b_stage = SCR_B_STAGE_BYTES / pl->cg;
+  int stages = (int)((SCR_SMEM_LIMIT - fixed) / b_stage);
   if (stages > SCR_MAX_STAGES) stages = SCR_MAX_STAGES;
   if (stages < 2) return false;
   pl->stages = stages;
-  pl->smem = fixed + (size_t)stages * SCR_B_STAGE_BYTES;
+  pl->smem = fixed + (size_t)stages * b_stage;
   pl->fb_cap = (int)(nq < FALLBACK_CAP ? nq : FALLBACK_CAP);
   int fbs = (int)((nb + 127) / 128);
   if (fbs > FALLBACK_SPLITS) fbs = FALLBACK_SPLITS;
@@ -744,13 +842,15 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
   CUtensorMap tq, tb;
   rc = make_tmap(&tq, w.q16, nq, pl.dpad, SCR_M);
   if (rc) return rc;
-  rc = make_tmap(&tb, w.b16, nb, pl.dpad, SCR_N);
+  rc = make_tmap(&tb, w.b16, nb, pl.dpad, SCR_N / pl.cg);
   if (rc) return rc;
 
   static bool attr_set = false;
   if (!attr_set) {
-    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  SCR_SMEM_LIMIT));
+    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<1>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
+    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<2>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
     attr_set = true;
   }
   ScreenParams sp;
@@ -761,7 +861,23 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
   dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
   const bool prof = g_prof.on && g_prof.n < 64;
   if (prof) EXB_CUDA(cudaEventRecord(g_prof.e0[g_prof.n], st));
-  knn_screen_kernel<<<grid, SCR_THREADS, pl.smem, st>>>(tq, tb, sp);
+  if (pl.cg == 2) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(SCR_THREADS);
+    cfg.dynamicSmemBytes = pl.smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    EXB_CUDA(cudaLaunchKernelEx(&cfg, knn_screen_kernel<2>, tq, tb, sp));
+  } else {
+    knn_screen_kernel<1><<<grid, SCR_THREADS, pl.smem, st>>>(tq, tb, sp);
+  }
   EXB_LAUNCH_CHECK();
   if (prof) EXB_CUDA(cudaEventRecord(g_prof.e1[g_prof.n++], st));
 
