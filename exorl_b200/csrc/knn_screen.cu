@@ -95,6 +95,11 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       "l"(map), "r"(c0), "r"(c1), "r"(bar)
       : "memory");
 }
+__device__ __forceinline__ void tma_prefetch_l2_2d(const CUtensorMap* map, int c0, int c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];" ::"l"(map), "r"(c0),
+               "r"(c1)
+               : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
@@ -282,6 +287,8 @@ struct ScreenParams {
   int splits;
   int k;
   int stages;
+  int prefetch;           // L2 prefetch distance in bank tiles (0 = off)
+  int debug;              // measurement only (EXB_SCREEN_DEBUG): 1 = skip filter, 2 = load only
   int* cand_idx;          // [nq, splits, CAP]
   int* cand_cnt;          // [nq, splits]; -1 = undecided
 };
@@ -415,6 +422,9 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
       for (int t = t_begin; t < t_end; ++t) {
         const int brow = t * SCR_N + (int)cta_rank * B_ROWS;
         for (int kc = 0; kc < nkc; ++kc) {
+          // pull this CTA's share of a later tile into L2 so the ring only sees L2 latency
+          if (p.prefetch > 0 && t + p.prefetch < t_end)
+            tma_prefetch_l2_2d(&tmap_b, kc * SCR_KC, brow + p.prefetch * SCR_N);
           mbar_wait(bar_empty(stage), phase ^ 1u);
           if (leader) mbar_expect_tx(bar_full(stage), SCR_B_STAGE_BYTES);
           if constexpr (CG == 2)
@@ -501,11 +511,10 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
       mbar_wait(bar_tfull(as), ((uint32_t)j >> 1) & 1u);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)as * SCR_N;
-#pragma unroll 1
-      for (int ch = 0; ch < SCR_N / 32; ++ch) {
-        uint32_t r[32];
-        tmem_ld32(t_row + ch * 32, r);
-        tmem_ld_wait();
+      // Software-pipelined drain: the TMEM load of chunk c+1 is in flight while chunk c is
+      // filtered (tcgen05.wait::ld waits for every outstanding load of the thread, so the order
+      // is wait -> issue next -> process current, alternating two register buffers).
+      auto process = [&](const uint32_t (&r)[32], int ch) {
         const float4* hn4 = reinterpret_cast<const float4*>(hn + ch * 32);
         float m = -INFINITY;
 #pragma unroll
@@ -531,6 +540,19 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
             const float s = acc - hn[ch * 32 + c];
             if (s >= st.tkeep) list_insert(st, lv, li, s, t * SCR_N + ch * 32 + c, k);
           }
+        }
+      };
+      if (p.debug != 1) {
+        uint32_t ra[32], rb[32];
+        tmem_ld32(t_row, ra);
+#pragma unroll 1
+        for (int ch = 0; ch < SCR_N / 32; ch += 2) {
+          tmem_ld_wait();
+          tmem_ld32(t_row + (ch + 1) * 32, rb);
+          if (p.debug == 0) process(ra, ch);
+          tmem_ld_wait();
+          if (ch + 2 < SCR_N / 32) tmem_ld32(t_row + (ch + 2) * 32, ra);
+          if (p.debug == 0) process(rb, ch + 1);
         }
       }
       tc_fence_before();
@@ -857,6 +879,16 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
   sp.ha = w.ha; sp.ea = w.ea; sp.hb = w.hb; sp.bsc = w.bsc;
   sp.nq = nq; sp.nb = nb; sp.nkc = pl.nkc; sp.n_tiles = pl.n_tiles;
   sp.tiles_per_split = pl.tiles_per_split; sp.splits = pl.splits; sp.k = k;
+  static const int dbg = [] {
+    const char* e = getenv("EXB_SCREEN_DEBUG");
+    return e ? atoi(e) : 0;
+  }();
+  sp.debug = dbg;
+  static const int pf = [] {
+    const char* e = getenv("EXB_SCREEN_PREFETCH");   // measured: hurts (L2->SM bandwidth), so off
+    return e ? atoi(e) : 0;
+  }();
+  sp.prefetch = pf;
   sp.stages = pl.stages; sp.cand_idx = w.cand_idx; sp.cand_cnt = w.cand_cnt;
   dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
   const bool prof = g_prof.on && g_prof.n < 64;
