@@ -49,8 +49,8 @@ constexpr int SCR_A_CHUNK_BYTES = SCR_M * SCR_KC * 2;   // 16 KB
 constexpr int SCR_B_STAGE_BYTES = SCR_N * SCR_KC * 2;   // 32 KB
 constexpr int SCR_MAX_STAGES = 8;
 constexpr int SCR_SMEM_LIMIT = 232448;                  // 227 KB
-constexpr int FALLBACK_CAP = 16384;
-constexpr int FALLBACK_SPLITS = 16;
+constexpr int FALLBACK_CAP = 4096;
+constexpr int FALLBACK_SPLITS = 42;   // x k <= 512 entries, the merge kernel's capacity
 
 // ------------------------------------------------------------------------------------------
 // PTX wrappers
@@ -289,14 +289,25 @@ struct ScreenParams {
   int stages;
   int prefetch;           // L2 prefetch distance in bank tiles (0 = off)
   int debug;              // measurement only (EXB_SCREEN_DEBUG): 1 = skip filter, 2 = load only
+  float* cand_val;        // [nq, splits, CAP] screened scores s = a^.b^ - hb
   int* cand_idx;          // [nq, splits, CAP]
   int* cand_cnt;          // [nq, splits]; -1 = undecided
 };
 
+// Per-row candidate state of one epilogue thread.  The k best scores seen so far are kept sorted
+// (descending) in registers by a branch-free min/max chain, so the running k-th best `tk` costs no
+// memory traffic; the candidates themselves (score, bank index) are appended to an unsorted
+// shared-memory buffer and pruned lazily (entries that fell below the rising `tkeep`).
 struct ListState {
-  int n;
-  float tk, tkeep, dropped;
+  int n;                     // entries in the buffer
+  float dropped;             // largest score ever dropped for lack of room (-FLT_MAX if none);
+                             // the row is undecided iff dropped >= the FINAL tkeep
+  float tk, tkeep;
   float ha, e2, dl;
+  // k best scores, descending, RIGHT-aligned in a fixed 16-slot chain: slots [0, 16-k) hold
+  // +FLT_MAX sentinels (values pass through them unchanged), so the k-th best is always the
+  // static last slot and nothing is ever indexed dynamically (keeps the chain in registers).
+  float tv[SCR_MAX_K];
 };
 
 __device__ __forceinline__ float keep_threshold(const ListState& s) {
@@ -308,35 +319,87 @@ __device__ __forceinline__ float keep_threshold(const ListState& s) {
   return t;
 }
 
-__device__ __forceinline__ void list_insert(ListState& s, float* lv, int* li, float v, int j,
+// bv/bi: this thread's column of the [CAP][128] arrays (stride SCR_M)
+__device__ __forceinline__ void list_compact(ListState& s, float* bv, int* bi) {
+  int w = 0;
+  for (int r = 0; r < s.n; ++r) {
+    const float v = bv[r * SCR_M];
+    const int j = bi[r * SCR_M];
+    if (v >= s.tkeep) {
+      bv[w * SCR_M] = v;
+      bi[w * SCR_M] = j;
+      ++w;
+    }
+  }
+  s.n = w;
+}
+
+__device__ __forceinline__ void list_insert(ListState& s, float* bv, int* bi, float v, int j,
                                             int k) {
-  // lv/li: this thread's column of the [CAP][128] arrays (stride 128), sorted descending
-  int p;
+  // precondition: v >= s.tkeep
+  if (s.n == SCR_CAP) list_compact(s, bv, bi);
   if (s.n < SCR_CAP) {
-    p = s.n++;
+    bv[s.n * SCR_M] = v;
+    bi[s.n * SCR_M] = j;
+    ++s.n;
   } else {
-    const float last = lv[(SCR_CAP - 1) * SCR_M];
-    if (v <= last) {
-      s.dropped = fmaxf(s.dropped, v);
-      p = -1;
+    // still full (only while tkeep is loose, early in a scan): evict the smallest score and
+    // remember it; whether that lost a needed candidate is decided against the final tkeep
+    int pm = 0;
+    float vm = bv[0];
+    for (int r = 1; r < SCR_CAP; ++r) {
+      const float x = bv[r * SCR_M];
+      if (x < vm) { vm = x; pm = r; }
+    }
+    if (v > vm) {
+      bv[pm * SCR_M] = v;
+      bi[pm * SCR_M] = j;
+      s.dropped = fmaxf(s.dropped, vm);
     } else {
-      s.dropped = fmaxf(s.dropped, last);
-      p = SCR_CAP - 1;
+      s.dropped = fmaxf(s.dropped, v);
     }
   }
-  if (p >= 0) {
-    while (p > 0 && lv[(p - 1) * SCR_M] < v) {
-      lv[p * SCR_M] = lv[(p - 1) * SCR_M];
-      li[p * SCR_M] = li[(p - 1) * SCR_M];
-      --p;
+  if (v > s.tk) {            // enters the k best: push through the sorted register chain
+    float x = v;
+#pragma unroll
+    for (int i = 0; i < SCR_MAX_K; ++i) {
+      const float hi = fmaxf(s.tv[i], x);
+      x = fminf(s.tv[i], x);
+      s.tv[i] = hi;
     }
-    lv[p * SCR_M] = v;
-    li[p * SCR_M] = j;
+    s.tk = s.tv[SCR_MAX_K - 1];
+    if (s.tk > -FLT_MAX) s.tkeep = keep_threshold(s);   // k scores seen
   }
-  if (s.n >= k) {
-    s.tk = lv[(k - 1) * SCR_M];
-    s.tkeep = keep_threshold(s);
-    while (s.n > k && lv[(s.n - 1) * SCR_M] < s.tkeep) --s.n;
+}
+
+// Filter one 32-column chunk of the accumulator held in registers (thread = query row).
+__device__ __forceinline__ void filter_chunk(ListState& st, const uint32_t (&r)[32], int ch,
+                                             const float* hn, float* lv, int* li, uint32_t t_row,
+                                             int t, int k) {
+  const float4* hn4 = reinterpret_cast<const float4*>(hn + ch * 32);
+  float m = -INFINITY;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    const float4 h = hn4[q];
+    m = fmaxf(m, fmaxf(fmaxf(__uint_as_float(r[4 * q]) - h.x, __uint_as_float(r[4 * q + 1]) - h.y),
+                       fmaxf(__uint_as_float(r[4 * q + 2]) - h.z,
+                             __uint_as_float(r[4 * q + 3]) - h.w)));
+  }
+  if (__any_sync(0xffffffffu, m >= st.tkeep)) {
+    // slow path: union of hit columns over the warp, revisited with uniform control flow
+    uint32_t mask = 0;
+#pragma unroll
+    for (int c = 0; c < 32; ++c)
+      mask |= ((__uint_as_float(r[c]) - hn[ch * 32 + c]) >= st.tkeep ? 1u : 0u) << c;
+    uint32_t wm = __reduce_or_sync(0xffffffffu, mask);
+    while (wm) {
+      const int c = __ffs(wm) - 1;
+      wm &= wm - 1;
+      const float acc = __uint_as_float(tmem_ld1(t_row + ch * 32 + c));
+      tmem_ld_wait();
+      const float s = acc - hn[ch * 32 + c];
+      if (s >= st.tkeep) list_insert(st, lv, li, s, t * SCR_N + ch * 32 + c, k);
+    }
   }
 }
 
@@ -483,9 +546,11 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
     int* li = s_li + e;
     ListState st;
     st.n = 0;
+    st.dropped = -FLT_MAX;
     st.tk = -FLT_MAX;
     st.tkeep = -FLT_MAX;
-    st.dropped = -FLT_MAX;
+#pragma unroll
+    for (int i = 0; i < SCR_MAX_K; ++i) st.tv[i] = (i < SCR_MAX_K - p.k) ? FLT_MAX : -FLT_MAX;
     st.ha = row_ok ? p.ha[row] : 0.f;
     const float eb_max = p.bsc->err_max, hb_max = p.bsc->hn_max;
     st.e2 = 2.f * ((row_ok ? p.ea[row] : 0.f) + eb_max);
@@ -514,34 +579,6 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
       // Software-pipelined drain: the TMEM load of chunk c+1 is in flight while chunk c is
       // filtered (tcgen05.wait::ld waits for every outstanding load of the thread, so the order
       // is wait -> issue next -> process current, alternating two register buffers).
-      auto process = [&](const uint32_t (&r)[32], int ch) {
-        const float4* hn4 = reinterpret_cast<const float4*>(hn + ch * 32);
-        float m = -INFINITY;
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const float4 h = hn4[q];
-          m = fmaxf(m, fmaxf(fmaxf(__uint_as_float(r[4 * q]) - h.x,
-                                   __uint_as_float(r[4 * q + 1]) - h.y),
-                             fmaxf(__uint_as_float(r[4 * q + 2]) - h.z,
-                                   __uint_as_float(r[4 * q + 3]) - h.w)));
-        }
-        if (__any_sync(0xffffffffu, m >= st.tkeep)) {
-          // slow path: union of hit columns over the warp, revisited with uniform control flow
-          uint32_t mask = 0;
-#pragma unroll
-          for (int c = 0; c < 32; ++c)
-            mask |= ((__uint_as_float(r[c]) - hn[ch * 32 + c]) >= st.tkeep ? 1u : 0u) << c;
-          uint32_t wm = __reduce_or_sync(0xffffffffu, mask);
-          while (wm) {
-            const int c = __ffs(wm) - 1;
-            wm &= wm - 1;
-            const float acc = __uint_as_float(tmem_ld1(t_row + ch * 32 + c));
-            tmem_ld_wait();
-            const float s = acc - hn[ch * 32 + c];
-            if (s >= st.tkeep) list_insert(st, lv, li, s, t * SCR_N + ch * 32 + c, k);
-          }
-        }
-      };
       if (p.debug != 1) {
         uint32_t ra[32], rb[32];
         tmem_ld32(t_row, ra);
@@ -549,10 +586,10 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
         for (int ch = 0; ch < SCR_N / 32; ch += 2) {
           tmem_ld_wait();
           tmem_ld32(t_row + (ch + 1) * 32, rb);
-          if (p.debug == 0) process(ra, ch);
+          if (p.debug == 0) filter_chunk(st, ra, ch, hn, lv, li, t_row, t, k);
           tmem_ld_wait();
           if (ch + 2 < SCR_N / 32) tmem_ld32(t_row + (ch + 2) * 32, ra);
-          if (p.debug == 0) process(rb, ch + 1);
+          if (p.debug == 0) filter_chunk(st, rb, ch + 1, hn, lv, li, t_row, t, k);
         }
       }
       tc_fence_before();
@@ -565,9 +602,13 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
 
     if (row_ok) {
       const int64_t o = row * p.splits + split;
+      list_compact(st, lv, li);
       const bool overflow = st.dropped > -FLT_MAX && st.dropped >= st.tkeep;
       p.cand_cnt[o] = overflow ? -1 : st.n;
-      for (int c = 0; c < st.n; ++c) p.cand_idx[o * SCR_CAP + c] = li[c * SCR_M];
+      for (int c = 0; c < st.n; ++c) {
+        p.cand_idx[o * SCR_CAP + c] = li[c * SCR_M];
+        p.cand_val[o * SCR_CAP + c] = lv[c * SCR_M];
+      }
     }
   }
 
@@ -590,70 +631,88 @@ struct RerankStatus {   // device, zeroed per call
   unsigned long long pairs;
 };
 
+constexpr int RR_PER_LANE = 12;   // 32 * 12 = 384 >= 16 splits * 24 slots
+constexpr int RR_SURV = 64;       // survivors recomputed exactly per row (else undecided)
+
 __global__ void __launch_bounds__(256)
 knn_rerank_kernel(const float* __restrict__ Q, int64_t nq, const float* __restrict__ B, int dim,
-                  int k, int idx_base, const int* __restrict__ cand_idx,
-                  const int* __restrict__ cand_cnt, int splits, const PrepScalars* qsc,
-                  const PrepScalars* bsc, float* __restrict__ out_dist, int* __restrict__ out_idx,
-                  int* __restrict__ fallback_rows, int fallback_cap, RerankStatus* status) {
+                  int k, int idx_base, const float* __restrict__ cand_val,
+                  const int* __restrict__ cand_idx, const int* __restrict__ cand_cnt, int splits,
+                  const float* __restrict__ ha, const float* __restrict__ ea,
+                  const PrepScalars* qsc, const PrepScalars* bsc, float* __restrict__ out_dist,
+                  int* __restrict__ out_idx, int* __restrict__ fallback_rows, int fallback_cap,
+                  RerankStatus* status) {
+  __shared__ int s_surv[8][RR_SURV];
   const unsigned full = 0xffffffffu;
-  const int lane = threadIdx.x & 31;
-  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int64_t row = (int64_t)blockIdx.x * 8 + wib;
   if (row >= nq) return;
   bool undecided = (qsc->range_flag | bsc->range_flag) != 0;
 
-  float q[16];
-#pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    const int c = lane + 32 * i;
-    q[i] = (c < dim) ? Q[row * dim + c] : 0.f;
-  }
-  float lv = FLT_MAX;
-  int li = INT_MAX;
+  // ---- gather the per-split lists of this row into registers (entry e = lane + 32 i)
+  float ev[RR_PER_LANE];
+  int ei[RR_PER_LANE];
   int total = 0;
-  for (int s = 0; s < splits && !undecided; ++s) {
-    const int cnt = cand_cnt[row * splits + s];
-    if (cnt < 0) { undecided = true; break; }
-    const int* ci = cand_idx + (row * splits + s) * SCR_CAP;
-    total += cnt;
-    for (int c0 = 0; c0 < cnt; c0 += 2) {
-      const int j0 = ci[c0];
-      const bool two = (c0 + 1) < cnt;
-      const int j1 = two ? ci[c0 + 1] : j0;
-      const float* b0 = B + (int64_t)j0 * dim;
-      const float* b1 = B + (int64_t)j1 * dim;
-      float a0 = 0.f, a1 = 0.f;
+  for (int sp = 0; sp < splits; ++sp) {
+    const int c = cand_cnt[row * splits + sp];
+    if (c < 0) undecided = true;
+    total += max(c, 0);
+  }
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int c = lane + 32 * i;
-        if (c < dim) {
-          const float d0 = q[i] - __ldg(b0 + c);
-          const float d1 = q[i] - __ldg(b1 + c);
-          a0 = fmaf(d0, d0, a0);
-          a1 = fmaf(d1, d1, a1);
-        }
-      }
-#pragma unroll
-      for (int off = 16; off > 0; off >>= 1) {
-        a0 += __shfl_xor_sync(full, a0, off);
-        a1 += __shfl_xor_sync(full, a1, off);
-      }
-      for (int u = 0; u < (two ? 2 : 1); ++u) {
-        const float v = u ? a1 : a0;
-        const int j = u ? j1 : j0;
-        const float thr_v = __shfl_sync(full, lv, k - 1);
-        const int thr_i = __shfl_sync(full, li, k - 1);
-        if (pair_less(v, j, thr_v, thr_i)) {
-          const int pos = __popc(__ballot_sync(full, pair_less(lv, li, v, j)));
-          const float up_v = __shfl_up_sync(full, lv, 1);
-          const int up_i = __shfl_up_sync(full, li, 1);
-          if (lane == pos) { lv = v; li = j; }
-          else if (lane > pos) { lv = up_v; li = up_i; }
-        }
-      }
+  for (int i = 0; i < RR_PER_LANE; ++i) {
+    const int e = lane + 32 * i;
+    const int sp = e / SCR_CAP, c = e - sp * SCR_CAP;
+    ev[i] = -FLT_MAX;
+    ei[i] = -1;
+    if (sp < splits && c < cand_cnt[row * splits + sp]) {
+      ev[i] = cand_val[(row * splits + sp) * SCR_CAP + c];
+      ei[i] = cand_idx[(row * splits + sp) * SCR_CAP + c];
     }
   }
-  if (!undecided && total < k) undecided = true;
+  if (total < k) undecided = true;
+
+  int n_surv = 0;
+  if (!undecided) {
+    // ---- k-th best screened score over the union of splits (k rounds of warp arg-max)
+    float wv[RR_PER_LANE];
+#pragma unroll
+    for (int i = 0; i < RR_PER_LANE; ++i) wv[i] = ev[i];
+    float kth = -FLT_MAX;
+    for (int round = 0; round < k; ++round) {
+      float lm = wv[0];
+      int ls = 0;
+#pragma unroll
+      for (int i = 1; i < RR_PER_LANE; ++i)
+        if (wv[i] > lm) { lm = wv[i]; ls = i; }
+      float wm = lm;
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) wm = fmaxf(wm, __shfl_xor_sync(full, wm, off));
+      const int owner = __ffs(__ballot_sync(full, lm == wm)) - 1;
+      if (lane == owner) {
+#pragma unroll
+        for (int i = 0; i < RR_PER_LANE; ++i)
+          if (i == ls) wv[i] = -FLT_MAX;
+      }
+      kth = wm;
+    }
+    // same keep rule as the screening kernel, now with the global k-th best
+    ListState st;
+    st.ha = ha[row];
+    st.e2 = 2.f * (ea[row] + bsc->err_max);
+    st.dl = (st.ha + bsc->hn_max) * (1.0f / 65536.0f);
+    st.tk = kth;
+    const float tkeep = keep_threshold(st);
+#pragma unroll
+    for (int i = 0; i < RR_PER_LANE; ++i) {
+      const bool keep = ei[i] >= 0 && ev[i] >= tkeep;
+      const unsigned m = __ballot_sync(full, keep);
+      const int pos = n_surv + __popc(m & ((1u << lane) - 1u));
+      if (keep && pos < RR_SURV) s_surv[wib][pos] = ei[i];
+      n_surv += __popc(m);
+    }
+    if (n_surv > RR_SURV) undecided = true;
+    __syncwarp();
+  }
   if (undecided) {
     if (lane == 0) {
       const int pos = atomicAdd(&status->n_fallback, 1);
@@ -662,7 +721,57 @@ knn_rerank_kernel(const float* __restrict__ Q, int64_t nq, const float* __restri
     }
     return;
   }
-  if (lane == 0) atomicAdd(&status->pairs, (unsigned long long)total);
+
+  // ---- exact fp32 direct-difference distances of the survivors, warp-resident sorted top-k
+  float q[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const int c = lane + 32 * i;
+    q[i] = (c < dim) ? Q[row * dim + c] : 0.f;
+  }
+  float lv = FLT_MAX;
+  int li = INT_MAX;
+  for (int c0 = 0; c0 < n_surv; c0 += 4) {
+    int j[4];
+    const float* bp[4];
+    float a[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      j[u] = s_surv[wib][min(c0 + u, n_surv - 1)];
+      bp[u] = B + (int64_t)j[u] * dim;
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int c = lane + 32 * i;
+      if (c < dim) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const float d = q[i] - __ldg(bp[u] + c);
+          a[u] = fmaf(d, d, a[u]);
+        }
+      }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1)
+#pragma unroll
+      for (int u = 0; u < 4; ++u) a[u] += __shfl_xor_sync(full, a[u], off);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (c0 + u < n_surv) {
+        const float v = a[u];
+        const float thr_v = __shfl_sync(full, lv, k - 1);
+        const int thr_i = __shfl_sync(full, li, k - 1);
+        if (pair_less(v, j[u], thr_v, thr_i)) {
+          const int pos = __popc(__ballot_sync(full, pair_less(lv, li, v, j[u])));
+          const float up_v = __shfl_up_sync(full, lv, 1);
+          const int up_i = __shfl_up_sync(full, li, 1);
+          if (lane == pos) { lv = v; li = j[u]; }
+          else if (lane > pos) { lv = up_v; li = up_i; }
+        }
+      }
+    }
+  }
+  if (lane == 0) atomicAdd(&status->pairs, (unsigned long long)n_surv);
   if (lane < k) {
     out_dist[row * k + lane] = sqrtf(lv);
     out_idx[row * k + lane] = li + idx_base;
@@ -774,6 +883,7 @@ struct ScreenWs {
   __half* q16;
   __half* b16;
   float *ha, *ea, *hb, *eb;
+  float* cand_val;
   int *cand_idx, *cand_cnt, *fb_rows;
   float* fb_d2;
   int* fb_idx;
@@ -791,6 +901,7 @@ static size_t carve_screen(void* ws, int64_t nq, int64_t nb, const ScreenPlan& p
   o->eb = cv.take<float>(nb);
   o->ha = same ? o->hb : cv.take<float>(nq);
   o->ea = same ? o->eb : cv.take<float>(nq);
+  o->cand_val = cv.take<float>((size_t)nq * pl.splits * SCR_CAP);
   o->cand_idx = cv.take<int>((size_t)nq * pl.splits * SCR_CAP);
   o->cand_cnt = cv.take<int>((size_t)nq * pl.splits);
   o->fb_rows = cv.take<int>(pl.fb_cap);
@@ -889,7 +1000,7 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
     return e ? atoi(e) : 0;
   }();
   sp.prefetch = pf;
-  sp.stages = pl.stages; sp.cand_idx = w.cand_idx; sp.cand_cnt = w.cand_cnt;
+  sp.stages = pl.stages; sp.cand_val = w.cand_val; sp.cand_idx = w.cand_idx; sp.cand_cnt = w.cand_cnt;
   dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
   const bool prof = g_prof.on && g_prof.n < 64;
   if (prof) EXB_CUDA(cudaEventRecord(g_prof.e0[g_prof.n], st));
@@ -914,8 +1025,8 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
   if (prof) EXB_CUDA(cudaEventRecord(g_prof.e1[g_prof.n++], st));
 
   knn_rerank_kernel<<<(unsigned)((nq + 7) / 8), 256, 0, st>>>(
-      src, nq, bank, dim, k, idx_base, w.cand_idx, w.cand_cnt, pl.splits, same ? w.bsc : w.qsc,
-      w.bsc, out_dist, out_idx, w.fb_rows, pl.fb_cap, w.status);
+      src, nq, bank, dim, k, idx_base, w.cand_val, w.cand_idx, w.cand_cnt, pl.splits, w.ha, w.ea,
+      same ? w.bsc : w.qsc, w.bsc, out_dist, out_idx, w.fb_rows, pl.fb_cap, w.status);
   EXB_LAUNCH_CHECK();
 
   // undecided rows -> exact kernel, indirect through the device-side row list / count
