@@ -1,6 +1,8 @@
 """ctypes binding of libexorl_b200.so (include/exorl_b200.h).  No CPU fallback: if the library is
 missing and cannot be built, every op raises."""
 import ctypes
+import os
+import pathlib
 import threading
 
 import torch
@@ -61,6 +63,8 @@ def load():
     with _lock:
         if _lib is None:
             path = _build.LIB
+            if os.environ.get("EXORL_B200_LIB"):        # A/B measurements of two builds
+                path = pathlib.Path(os.environ["EXORL_B200_LIB"])
             if not path.exists():
                 try:
                     _build.build_library()

@@ -334,6 +334,86 @@ __device__ __forceinline__ void list_compact(ListState& s, float* bv, int* bi) {
   s.n = w;
 }
 
+// Push one score through the sorted register chain (branch-free).
+__device__ __forceinline__ void chain_push(ListState& s, float x) {
+#pragma unroll
+  for (int i = 0; i < SCR_MAX_K; ++i) {
+    const float hi = fmaxf(s.tv[i], x);
+    x = fminf(s.tv[i], x);
+    s.tv[i] = hi;
+  }
+}
+
+__device__ __forceinline__ void refresh_threshold(ListState& s) {
+  s.tk = s.tv[SCR_MAX_K - 1];
+  if (s.tk > -FLT_MAX) s.tkeep = fmaxf(s.tkeep, keep_threshold(s));   // k scores seen
+}
+
+// Scores of one 32-column chunk (thread = query row) and their maxima over groups of 4 columns.
+__device__ __forceinline__ float chunk_scores(const uint32_t (&r)[32], const float* hn_chunk,
+                                              float (&sc)[32], float (&g)[8]) {
+  const float4* hn4 = reinterpret_cast<const float4*>(hn_chunk);
+  float m = -INFINITY;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    const float4 h = hn4[q];
+    sc[4 * q] = __uint_as_float(r[4 * q]) - h.x;
+    sc[4 * q + 1] = __uint_as_float(r[4 * q + 1]) - h.y;
+    sc[4 * q + 2] = __uint_as_float(r[4 * q + 2]) - h.z;
+    sc[4 * q + 3] = __uint_as_float(r[4 * q + 3]) - h.w;
+    g[q] = fmaxf(fmaxf(sc[4 * q], sc[4 * q + 1]), fmaxf(sc[4 * q + 2], sc[4 * q + 3]));
+    m = fmaxf(m, g[q]);
+  }
+  return m;
+}
+
+// Seed pass (first tile of a CTA): only the running k-th best is updated, from group maxima.
+// Every group maximum is a real score, so the chain's k-th entry never exceeds the true k-th
+// best score: thresholds derived from it are conservative.
+__device__ __forceinline__ void seed_chunk(ListState& st, const uint32_t (&r)[32],
+                                           const float* hn_chunk) {
+  float sc[32], g[8];
+  chunk_scores(r, hn_chunk, sc, g);
+#pragma unroll
+  for (int q = 0; q < 8; ++q)
+    if (g[q] > st.tv[SCR_MAX_K - 1]) chain_push(st, g[q]);
+}
+
+// Filter one 32-column chunk: append every column whose score reaches tkeep (tiny predicated
+// stores), optionally feed the chain with the group maxima, refresh the thresholds once.
+__device__ __forceinline__ void filter_chunk(ListState& st, const uint32_t (&r)[32], int col0,
+                                             const float* hn_chunk, float* bv, int* bi,
+                                             bool feed_chain) {
+  float sc[32], g[8];
+  const float m = chunk_scores(r, hn_chunk, sc, g);
+  if (__any_sync(0xffffffffu, m >= st.tkeep)) {
+    // prune stale entries only when the buffer is nearly full (steady state holds ~k+2 live ones)
+    if (st.n >= SCR_CAP - 4) list_compact(st, bv, bi);
+    const float tkeep = st.tkeep;
+#pragma unroll
+    for (int c = 0; c < 32; ++c) {
+      if (sc[c] >= tkeep) {
+        if (st.n < SCR_CAP) {
+          bv[st.n * SCR_M] = sc[c];
+          bi[st.n * SCR_M] = col0 + c;
+          ++st.n;
+        } else {
+          st.dropped = fmaxf(st.dropped, sc[c]);   // judged against the final tkeep
+        }
+      }
+    }
+    if (feed_chain && m > st.tv[SCR_MAX_K - 1]) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        if (g[q] > st.tv[SCR_MAX_K - 1]) chain_push(st, g[q]);
+      refresh_threshold(st);
+    }
+  }
+}
+
+// ---- steady-state path (every tile after a CTA's first): hits are rare, so the hit columns of
+// the warp are revisited one by one with uniform control flow and inserted individually; every
+// inserted score also goes through the chain, so tk is the exact k-th best of what was kept.
 __device__ __forceinline__ void list_insert(ListState& s, float* bv, int* bi, float v, int j,
                                             int k) {
   // precondition: v >= s.tkeep
@@ -360,20 +440,13 @@ __device__ __forceinline__ void list_insert(ListState& s, float* bv, int* bi, fl
     }
   }
   if (v > s.tk) {            // enters the k best: push through the sorted register chain
-    float x = v;
-#pragma unroll
-    for (int i = 0; i < SCR_MAX_K; ++i) {
-      const float hi = fmaxf(s.tv[i], x);
-      x = fminf(s.tv[i], x);
-      s.tv[i] = hi;
-    }
-    s.tk = s.tv[SCR_MAX_K - 1];
-    if (s.tk > -FLT_MAX) s.tkeep = keep_threshold(s);   // k scores seen
+    chain_push(s, v);
+    refresh_threshold(s);
   }
 }
 
 // Filter one 32-column chunk of the accumulator held in registers (thread = query row).
-__device__ __forceinline__ void filter_chunk(ListState& st, const uint32_t (&r)[32], int ch,
+__device__ __forceinline__ void filter_chunk_visit(ListState& st, const uint32_t (&r)[32], int ch,
                                              const float* hn, float* lv, int* li, uint32_t t_row,
                                              int t, int k) {
   const float4* hn4 = reinterpret_cast<const float4*>(hn + ch * 32);
@@ -403,7 +476,9 @@ __device__ __forceinline__ void filter_chunk(ListState& st, const uint32_t (&r)[
   }
 }
 
-template <int CG>
+// SEED = true: latency mode (each CTA sees only a few bank tiles, the list fill phase dominates):
+// seed pass on the first tile + inline appends.  SEED = false: long scans, visit-based inserts.
+template <int CG, bool SEED>
 __global__ void __launch_bounds__(SCR_THREADS, 1)
 knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
                   const __grid_constant__ CUtensorMap tmap_b, const ScreenParams p) {
@@ -555,7 +630,6 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
     const float eb_max = p.bsc->err_max, hb_max = p.bsc->hn_max;
     st.e2 = 2.f * ((row_ok ? p.ea[row] : 0.f) + eb_max);
     st.dl = (st.ha + hb_max) * (1.0f / 65536.0f);
-    const int k = p.k;
 
     auto load_hn = [&](int t, float& h0, float& h1) {
       const int64_t c0 = (int64_t)t * SCR_N + 2 * et;
@@ -581,15 +655,43 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
       // is wait -> issue next -> process current, alternating two register buffers).
       if (p.debug != 1) {
         uint32_t ra[32], rb[32];
+        const bool first = (j == 0);
+        if (SEED && first && p.debug == 0) {
+          // seed pass over the whole first tile (the accumulator stays in TMEM for the real pass)
+          tmem_ld32(t_row, ra);
+#pragma unroll 1
+          for (int ch = 0; ch < SCR_N / 32; ch += 2) {
+            tmem_ld_wait();
+            tmem_ld32(t_row + (ch + 1) * 32, rb);
+            seed_chunk(st, ra, hn + ch * 32);
+            tmem_ld_wait();
+            if (ch + 2 < SCR_N / 32) tmem_ld32(t_row + (ch + 2) * 32, ra);
+            seed_chunk(st, rb, hn + (ch + 1) * 32);
+          }
+          refresh_threshold(st);
+        }
+        // Software-pipelined drain: the TMEM load of chunk c+1 is in flight while chunk c is
+        // filtered (tcgen05.wait::ld waits for every outstanding load of the thread, so the order
+        // is wait -> issue next -> process current, alternating two register buffers).
         tmem_ld32(t_row, ra);
 #pragma unroll 1
         for (int ch = 0; ch < SCR_N / 32; ch += 2) {
           tmem_ld_wait();
           tmem_ld32(t_row + (ch + 1) * 32, rb);
-          if (p.debug == 0) filter_chunk(st, ra, ch, hn, lv, li, t_row, t, k);
+          if (p.debug == 0) {
+            if constexpr (SEED)
+              filter_chunk(st, ra, t * SCR_N + ch * 32, hn + ch * 32, lv, li, !first);
+            else
+              filter_chunk_visit(st, ra, ch, hn, lv, li, t_row, t, p.k);
+          }
           tmem_ld_wait();
           if (ch + 2 < SCR_N / 32) tmem_ld32(t_row + (ch + 2) * 32, ra);
-          if (p.debug == 0) filter_chunk(st, rb, ch + 1, hn, lv, li, t_row, t, k);
+          if (p.debug == 0) {
+            if constexpr (SEED)
+              filter_chunk(st, rb, t * SCR_N + (ch + 1) * 32, hn + (ch + 1) * 32, lv, li, !first);
+            else
+              filter_chunk_visit(st, rb, ch + 1, hn, lv, li, t_row, t, p.k);
+          }
         }
       }
       tc_fence_before();
@@ -980,9 +1082,13 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
 
   static bool attr_set = false;
   if (!attr_set) {
-    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<1>,
+    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<1, false>,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
-    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<2>,
+    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<2, false>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
+    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<1, true>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
+    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<2, true>,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
     attr_set = true;
   }
@@ -1002,6 +1108,7 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
   sp.prefetch = pf;
   sp.stages = pl.stages; sp.cand_val = w.cand_val; sp.cand_idx = w.cand_idx; sp.cand_cnt = w.cand_cnt;
   dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
+  const bool seed = pl.tiles_per_split <= 16;   // fill phase dominates short scans
   const bool prof = g_prof.on && g_prof.n < 64;
   if (prof) EXB_CUDA(cudaEventRecord(g_prof.e0[g_prof.n], st));
   if (pl.cg == 2) {
@@ -1017,9 +1124,11 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    EXB_CUDA(cudaLaunchKernelEx(&cfg, knn_screen_kernel<2>, tq, tb, sp));
+    if (seed) EXB_CUDA(cudaLaunchKernelEx(&cfg, knn_screen_kernel<2, true>, tq, tb, sp));
+    else EXB_CUDA(cudaLaunchKernelEx(&cfg, knn_screen_kernel<2, false>, tq, tb, sp));
   } else {
-    knn_screen_kernel<1><<<grid, SCR_THREADS, pl.smem, st>>>(tq, tb, sp);
+    if (seed) knn_screen_kernel<1, true><<<grid, SCR_THREADS, pl.smem, st>>>(tq, tb, sp);
+    else knn_screen_kernel<1, false><<<grid, SCR_THREADS, pl.smem, st>>>(tq, tb, sp);
   }
   EXB_LAUNCH_CHECK();
   if (prof) EXB_CUDA(cudaEventRecord(g_prof.e1[g_prof.n++], st));
