@@ -51,6 +51,9 @@ constexpr int SCR_MAX_STAGES = 8;
 constexpr int SCR_SMEM_LIMIT = 232448;                  // 227 KB
 constexpr int FALLBACK_CAP = 4096;
 constexpr int FALLBACK_SPLITS = 42;   // x k <= 512 entries, the merge kernel's capacity
+// fp32 accumulation error of a <= 512-term fp16 dot product, relative to ||a^|| ||b^|| <= ha + hb:
+// 512 additions x 2^-23 per (truncating) add.
+constexpr float SCR_ACC_EPS = 1.0f / 16384.0f;
 
 // ------------------------------------------------------------------------------------------
 // PTX wrappers
@@ -629,7 +632,7 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
     st.ha = row_ok ? p.ha[row] : 0.f;
     const float eb_max = p.bsc->err_max, hb_max = p.bsc->hn_max;
     st.e2 = 2.f * ((row_ok ? p.ea[row] : 0.f) + eb_max);
-    st.dl = (st.ha + hb_max) * (1.0f / 65536.0f);
+    st.dl = (st.ha + hb_max) * SCR_ACC_EPS;
 
     auto load_hn = [&](int t, float& h0, float& h1) {
       const int64_t c0 = (int64_t)t * SCR_N + 2 * et;
@@ -801,7 +804,7 @@ knn_rerank_kernel(const float* __restrict__ Q, int64_t nq, const float* __restri
     ListState st;
     st.ha = ha[row];
     st.e2 = 2.f * (ea[row] + bsc->err_max);
-    st.dl = (st.ha + bsc->hn_max) * (1.0f / 65536.0f);
+    st.dl = (st.ha + bsc->hn_max) * SCR_ACC_EPS;
     st.tk = kth;
     const float tkeep = keep_threshold(st);
 #pragma unroll
