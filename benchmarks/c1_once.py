@@ -1,7 +1,8 @@
-"""Three C1 calls per mode (for an ncu launch list of the per-update path)."""
+"""Three C1 / C2 calls per mode (for an ncu launch list of the per-update path) + screen status."""
 import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import exorl_b200 as xb
+from exorl_b200 import knn as xknn
 dev = "cuda:0"
 g = torch.Generator().manual_seed(0)
 x = torch.tanh(torch.randn(1024, 512, generator=g)).to(dev)
@@ -10,4 +11,25 @@ for mode in ("screened", "exact"):
     for _ in range(3):
         r = p(x)
     torch.cuda.synchronize()
-print("ok", float(r.sum()))
+    if mode == "screened":
+        print("C1 screened status (undecided, invalid, pairs, _):", xknn.screened_status(torch.device(dev)))
+z = torch.nn.functional.normalize(torch.randn(1024, 128, generator=g), dim=1).to(dev)
+q = torch.nn.functional.normalize(torch.randn(2048, 128, generator=g), dim=1).to(dev)
+for _ in range(3):
+    r2 = xb.proto_knn_reward(z, q, 3, mode="screened")
+torch.cuda.synchronize()
+print("C2 screened status:", xknn.screened_status(torch.device(dev)))
+print("ok", float(r.sum()), float(r2.sum()))
+if os.environ.get("EXB_SCREEN_TRACE"):
+    import ctypes
+    from exorl_b200 import _lib
+    lib = _lib.load()
+    for name, fn in (("C1", lambda: xb.knn_topk(x, x, 12, mode="screened")),
+                     ("C2", lambda: xb.knn_topk(z, q, 3, mode="screened"))):
+        fn(); torch.cuda.synchronize()
+        ws, _ = _lib.Workspace.get(torch.device(dev), "knn_screened", 1024)
+        out = (ctypes.c_int64 * 16)()
+        _lib.check(lib.exb_debug_trace_sync(_lib.ptr(ws), out, _lib.stream_ptr(torch.device(dev))))
+        t = list(out)
+        print(name, "trace ns rel. screen start:", [v - t[0] if v else None for v in t[:7]],
+              "rerank:", [v - t[8] if v else None for v in t[8:12]], "gap:", t[8] - t[6])

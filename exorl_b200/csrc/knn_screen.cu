@@ -24,6 +24,7 @@
 //               sorted list in shared memory
 //   two 256-column TMEM accumulators so the MMA of tile t+1 overlaps the filter of tile t.
 #include "common.cuh"
+#include "tc_ptx.cuh"
 #include <cuda.h>
 #include <cuda_fp16.h>
 #include <float.h>
@@ -56,177 +57,6 @@ constexpr int FALLBACK_SPLITS = 42;   // x k <= 512 entries, the merge kernel's 
 constexpr float SCR_ACC_EPS = 1.0f / 16384.0f;
 
 // ------------------------------------------------------------------------------------------
-// PTX wrappers
-// ------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-  return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
-               : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "WAIT_LOOP:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra WAIT_DONE;\n"
-      "bra WAIT_LOOP;\n"
-      "WAIT_DONE:\n"
-      "}\n" ::"r"(bar),
-      "r"(parity)
-      : "memory");
-}
-__device__ __forceinline__ void fence_barrier_init() {
-  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() {
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1,
-                                            uint32_t bar) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
-      " [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
-      "l"(map), "r"(c0), "r"(c1), "r"(bar)
-      : "memory");
-}
-__device__ __forceinline__ void tma_prefetch_l2_2d(const CUtensorMap* map, int c0, int c1) {
-  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];" ::"l"(map), "r"(c0),
-               "r"(c1)
-               : "memory");
-}
-__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
-  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() {
-  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void tc_fence_after() {
-  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_alloc_512(uint32_t smem_dst) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(
-      smem_dst));
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
-}
-__device__ __forceinline__ void tmem_dealloc_512(uint32_t taddr) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(taddr));
-}
-__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
-                                         uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "setp.ne.b32 p, %4, 0;\n"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
-      "}\n" ::"r"(tmem_d),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
-                   bar)
-               : "memory");
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
-        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
-        "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]),
-        "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]),
-        "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr)
-      : "memory");
-}
-__device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {
-  uint32_t r;
-  asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r) : "r"(taddr)
-               : "memory");
-  return r;
-}
-__device__ __forceinline__ void tmem_ld_wait() {
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-
-// ---- cta_group::2 (CTA pair) variants.  PEER_MASK clears the CTA-parity bit of a shared-window
-// address so that it names the same offset in the even (leader) CTA of the pair (the convention
-// of cute::Sm100MmaPeerBitMask).
-constexpr uint32_t PEER_MASK = 0xFEFFFFFFu;
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, int c0,
-                                                 int c1, uint32_t bar) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
-      " [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
-      "l"(map), "r"(c0), "r"(c1), "r"(bar & PEER_MASK)
-      : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar & PEER_MASK) : "memory");
-}
-__device__ __forceinline__ void tmem_alloc_512_pair(uint32_t smem_dst) {
-  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(
-      smem_dst));
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
-}
-__device__ __forceinline__ void tmem_dealloc_512_pair(uint32_t taddr) {
-  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" ::"r"(taddr));
-}
-__device__ __forceinline__ void umma_f16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
-                                              uint32_t idesc, uint32_t accumulate) {
-  const uint32_t z = 0;
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "setp.ne.b32 p, %4, 0;\n"
-      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, {%5, %5, %5, %5, %5, %5, %5, %5}, p;\n"
-      "}\n" ::"r"(tmem_d),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(z)
-      : "memory");
-}
-__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
-  const uint16_t mask = 3;
-  asm volatile(
-      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64"
-      " [%0], %1;" ::"r"(bar),
-      "h"(mask)
-      : "memory");
-}
-
-// K-major, 128-byte swizzle shared-memory matrix descriptor (cute::UMMA::SmemDescriptor layout):
-// start>>4 [0,14), LBO>>4 [16,30) (unused for swizzled K-major, 1), SBO>>4 [32,46) = 1024 B
-// between 8-row groups, version 1 at [46,48), layout SWIZZLE_128B = 2 at [61,64).
-__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
-  return (uint64_t)((saddr >> 4) & 0x3FFF) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) |
-         (1ull << 46) | (2ull << 61);
-}
-// kind::f16 instruction descriptor: D=F32 (bit 4), A=B=F16 (0), K-major both, N>>3 at [17,23),
-// M>>4 at [24,29).
-template <int CG>
-constexpr uint32_t scr_idesc() {
-  return (1u << 4) | ((uint32_t)(SCR_N >> 3) << 17) | ((uint32_t)((SCR_M * CG) >> 4) << 24);
-}
-
-// ------------------------------------------------------------------------------------------
 // prep: fp32 rows -> padded fp16 operand, half squared norm of the rounded row, rounding error
 // ------------------------------------------------------------------------------------------
 struct PrepScalars {   // device struct, zeroed per call
@@ -236,10 +66,17 @@ struct PrepScalars {   // device struct, zeroed per call
   int pad;
 };
 
+// One warp per row.  VEC: dim % 4 == 0 and 16-byte aligned rows -> every lane issues all of its
+// float4 loads up front (<= 4 for dim <= 512) instead of a dependent scalar loop.  A row with a
+// value outside the fp16 range gets round_err = +inf (the screen then keeps nothing certain for
+// it and every row falls to the exact kernel) in addition to the range flag.
+template <bool VEC>
 __global__ void __launch_bounds__(256)
 knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
                 __half* __restrict__ out, float* __restrict__ half_norm,
-                float* __restrict__ round_err, PrepScalars* __restrict__ sc) {
+                float* __restrict__ round_err, PrepScalars* __restrict__ sc,
+                unsigned long long* __restrict__ zero16) {
+  if (zero16 != nullptr && blockIdx.x == 0 && threadIdx.x < 2) zero16[threadIdx.x] = 0ull;
   const int lane = threadIdx.x & 31;
   const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= n) return;
@@ -247,15 +84,48 @@ knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
   __half* orow = out + row * dpad;
   double nn = 0.0, ee = 0.0;
   bool bad = false;
-  for (int c = lane; c < dpad; c += 32) {
-    float v = (c < dim) ? xr[c] : 0.f;
-    bad |= !(fabsf(v) <= 65504.f);
-    const __half h = __float2half_rn(v);
-    const float hf = __half2float(h);
-    orow[c] = h;
-    nn += (double)hf * (double)hf;
-    const double e = (double)v - (double)hf;
-    ee += e * e;
+  if constexpr (VEC) {
+    const float4* x4 = reinterpret_cast<const float4*>(xr);
+    uint2* o2 = reinterpret_cast<uint2*>(orow);
+    const int nv = dim >> 2, nvp = dpad >> 2;
+    float4 v[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int c = lane + 32 * i;
+      v[i] = (c < nv) ? __ldg(x4 + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nvp) {
+        const float f[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+        __half h[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          bad |= !(fabsf(f[j]) <= 65504.f);
+          h[j] = __float2half_rn(f[j]);
+          const float hf = __half2float(h[j]);
+          nn += (double)hf * (double)hf;
+          const double e = (double)f[j] - (double)hf;
+          ee += e * e;
+        }
+        uint2 pk;
+        pk.x = (uint32_t)__half_as_ushort(h[0]) | ((uint32_t)__half_as_ushort(h[1]) << 16);
+        pk.y = (uint32_t)__half_as_ushort(h[2]) | ((uint32_t)__half_as_ushort(h[3]) << 16);
+        o2[c] = pk;
+      }
+    }
+  } else {
+    for (int c = lane; c < dpad; c += 32) {
+      float v = (c < dim) ? xr[c] : 0.f;
+      bad |= !(fabsf(v) <= 65504.f);
+      const __half h = __float2half_rn(v);
+      const float hf = __half2float(h);
+      orow[c] = h;
+      nn += (double)hf * (double)hf;
+      const double e = (double)v - (double)hf;
+      ee += e * e;
+    }
   }
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) {
@@ -264,14 +134,16 @@ knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
   }
   bad = __any_sync(0xffffffffu, bad);
   if (lane == 0) {
-    const float hn = (float)(0.5 * nn);
+    const float hn = bad ? 0.f : (float)(0.5 * nn);
     // round the error norm up so the bound stays rigorous after the fp32 conversion
-    const float er = __double2float_ru(sqrt(ee));
+    const float er = bad ? INFINITY : __double2float_ru(sqrt(ee));
     half_norm[row] = hn;
     round_err[row] = er;
-    atomicMax(reinterpret_cast<int*>(&sc->err_max), __float_as_int(er));
-    atomicMax(reinterpret_cast<int*>(&sc->hn_max), __float_as_int(hn));
-    if (bad) atomicExch(&sc->range_flag, 1);
+    if (sc) {
+      atomicMax(reinterpret_cast<int*>(&sc->err_max), __float_as_int(er));
+      atomicMax(reinterpret_cast<int*>(&sc->hn_max), __float_as_int(hn));
+      if (bad) atomicExch(&sc->range_flag, 1);
+    }
   }
 }
 
@@ -600,10 +472,10 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
             // advance 16 fp16 = 32 bytes inside the swizzle atom: +2 in the (addr >> 4) field
             if constexpr (CG == 2)
               umma_f16_pair(d_tmem, adesc + (uint64_t)(2 * ki), bdesc + (uint64_t)(2 * ki),
-                            scr_idesc<2>(), (kc | ki) != 0 ? 1u : 0u);
+                            umma_idesc_f16(2 * SCR_M, SCR_N), (kc | ki) != 0 ? 1u : 0u);
             else
               umma_f16(d_tmem, adesc + (uint64_t)(2 * ki), bdesc + (uint64_t)(2 * ki),
-                       scr_idesc<1>(), (kc | ki) != 0 ? 1u : 0u);
+                       umma_idesc_f16(SCR_M, SCR_N), (kc | ki) != 0 ? 1u : 0u);
           }
           if constexpr (CG == 2) umma_commit_pair(bar_empty(stage));
           else umma_commit(bar_empty(stage));
@@ -727,161 +599,12 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
   }
 }
 
-// ------------------------------------------------------------------------------------------
-// rerank: exact fp32 direct-difference distance of the survivors, one warp per query row
-// ------------------------------------------------------------------------------------------
-struct RerankStatus {   // device, zeroed per call
-  int n_fallback;
-  int invalid;
-  unsigned long long pairs;
-};
+}  // namespace exb
 
-constexpr int RR_PER_LANE = 12;   // 32 * 12 = 384 >= 16 splits * 24 slots
-constexpr int RR_SURV = 64;       // survivors recomputed exactly per row (else undecided)
+#include "knn_lat.cuh"
+#include "knn_rerank.cuh"
 
-__global__ void __launch_bounds__(256)
-knn_rerank_kernel(const float* __restrict__ Q, int64_t nq, const float* __restrict__ B, int dim,
-                  int k, int idx_base, const float* __restrict__ cand_val,
-                  const int* __restrict__ cand_idx, const int* __restrict__ cand_cnt, int splits,
-                  const float* __restrict__ ha, const float* __restrict__ ea,
-                  const PrepScalars* qsc, const PrepScalars* bsc, float* __restrict__ out_dist,
-                  int* __restrict__ out_idx, int* __restrict__ fallback_rows, int fallback_cap,
-                  RerankStatus* status) {
-  __shared__ int s_surv[8][RR_SURV];
-  const unsigned full = 0xffffffffu;
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  const int64_t row = (int64_t)blockIdx.x * 8 + wib;
-  if (row >= nq) return;
-  bool undecided = (qsc->range_flag | bsc->range_flag) != 0;
-
-  // ---- gather the per-split lists of this row into registers (entry e = lane + 32 i)
-  float ev[RR_PER_LANE];
-  int ei[RR_PER_LANE];
-  int total = 0;
-  for (int sp = 0; sp < splits; ++sp) {
-    const int c = cand_cnt[row * splits + sp];
-    if (c < 0) undecided = true;
-    total += max(c, 0);
-  }
-#pragma unroll
-  for (int i = 0; i < RR_PER_LANE; ++i) {
-    const int e = lane + 32 * i;
-    const int sp = e / SCR_CAP, c = e - sp * SCR_CAP;
-    ev[i] = -FLT_MAX;
-    ei[i] = -1;
-    if (sp < splits && c < cand_cnt[row * splits + sp]) {
-      ev[i] = cand_val[(row * splits + sp) * SCR_CAP + c];
-      ei[i] = cand_idx[(row * splits + sp) * SCR_CAP + c];
-    }
-  }
-  if (total < k) undecided = true;
-
-  int n_surv = 0;
-  if (!undecided) {
-    // ---- k-th best screened score over the union of splits (k rounds of warp arg-max)
-    float wv[RR_PER_LANE];
-#pragma unroll
-    for (int i = 0; i < RR_PER_LANE; ++i) wv[i] = ev[i];
-    float kth = -FLT_MAX;
-    for (int round = 0; round < k; ++round) {
-      float lm = wv[0];
-      int ls = 0;
-#pragma unroll
-      for (int i = 1; i < RR_PER_LANE; ++i)
-        if (wv[i] > lm) { lm = wv[i]; ls = i; }
-      float wm = lm;
-#pragma unroll
-      for (int off = 16; off > 0; off >>= 1) wm = fmaxf(wm, __shfl_xor_sync(full, wm, off));
-      const int owner = __ffs(__ballot_sync(full, lm == wm)) - 1;
-      if (lane == owner) {
-#pragma unroll
-        for (int i = 0; i < RR_PER_LANE; ++i)
-          if (i == ls) wv[i] = -FLT_MAX;
-      }
-      kth = wm;
-    }
-    // same keep rule as the screening kernel, now with the global k-th best
-    ListState st;
-    st.ha = ha[row];
-    st.e2 = 2.f * (ea[row] + bsc->err_max);
-    st.dl = (st.ha + bsc->hn_max) * SCR_ACC_EPS;
-    st.tk = kth;
-    const float tkeep = keep_threshold(st);
-#pragma unroll
-    for (int i = 0; i < RR_PER_LANE; ++i) {
-      const bool keep = ei[i] >= 0 && ev[i] >= tkeep;
-      const unsigned m = __ballot_sync(full, keep);
-      const int pos = n_surv + __popc(m & ((1u << lane) - 1u));
-      if (keep && pos < RR_SURV) s_surv[wib][pos] = ei[i];
-      n_surv += __popc(m);
-    }
-    if (n_surv > RR_SURV) undecided = true;
-    __syncwarp();
-  }
-  if (undecided) {
-    if (lane == 0) {
-      const int pos = atomicAdd(&status->n_fallback, 1);
-      if (pos < fallback_cap) fallback_rows[pos] = (int)row;
-      else status->invalid = 1;
-    }
-    return;
-  }
-
-  // ---- exact fp32 direct-difference distances of the survivors, warp-resident sorted top-k
-  float q[16];
-#pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    const int c = lane + 32 * i;
-    q[i] = (c < dim) ? Q[row * dim + c] : 0.f;
-  }
-  float lv = FLT_MAX;
-  int li = INT_MAX;
-  for (int c0 = 0; c0 < n_surv; c0 += 4) {
-    int j[4];
-    const float* bp[4];
-    float a[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      j[u] = s_surv[wib][min(c0 + u, n_surv - 1)];
-      bp[u] = B + (int64_t)j[u] * dim;
-    }
-#pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const int c = lane + 32 * i;
-      if (c < dim) {
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const float d = q[i] - __ldg(bp[u] + c);
-          a[u] = fmaf(d, d, a[u]);
-        }
-      }
-    }
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1)
-#pragma unroll
-      for (int u = 0; u < 4; ++u) a[u] += __shfl_xor_sync(full, a[u], off);
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      if (c0 + u < n_surv) {
-        const float v = a[u];
-        const float thr_v = __shfl_sync(full, lv, k - 1);
-        const int thr_i = __shfl_sync(full, li, k - 1);
-        if (pair_less(v, j[u], thr_v, thr_i)) {
-          const int pos = __popc(__ballot_sync(full, pair_less(lv, li, v, j[u])));
-          const float up_v = __shfl_up_sync(full, lv, 1);
-          const int up_i = __shfl_up_sync(full, li, 1);
-          if (lane == pos) { lv = v; li = j[u]; }
-          else if (lane > pos) { lv = up_v; li = up_i; }
-        }
-      }
-    }
-  }
-  if (lane == 0) atomicAdd(&status->pairs, (unsigned long long)n_surv);
-  if (lane < k) {
-    out_dist[row * k + lane] = sqrtf(lv);
-    out_idx[row * k + lane] = li + idx_base;
-  }
-}
+namespace exb {
 
 // ------------------------------------------------------------------------------------------
 // host side
@@ -938,6 +661,7 @@ static ScreenProfile g_prof;
 static inline int dim_pad(int dim) { return (dim + SCR_KC - 1) / SCR_KC * SCR_KC; }
 
 struct ScreenPlan {
+  bool lat; // per-update sizes: latency kernel (64-row bank tiles, everything resident, knn_lat.cuh)
   int cg;   // CTAs cooperating on one MMA (1, or 2 = cta_group::2 pair)
   int dpad, nkc, n_tiles, m_tiles, splits, tiles_per_split, stages;
   size_t smem;
@@ -949,6 +673,36 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
     return false;
   pl->dpad = dim_pad(dim);
   pl->nkc = pl->dpad / SCR_KC;
+  pl->fb_cap = (int)(nq < FALLBACK_CAP ? nq : FALLBACK_CAP);
+  int fbs = (int)((nb + 127) / 128);
+  if (fbs > FALLBACK_SPLITS) fbs = FALLBACK_SPLITS;
+  if (fbs * k > 512) fbs = 512 / k;
+  pl->fb_splits = fbs < 1 ? 1 : fbs;
+  // ---- latency mode: few query tiles, a bank that one wave of 64-row tiles (x <= 8) covers
+  static const int lat_enabled = [] {
+    const char* e = getenv("EXB_SCREEN_LAT");
+    return e ? atoi(e) : 1;
+  }();
+  pl->lat = false;
+  {
+    const int mt = (int)((nq + SCR_M - 1) / SCR_M);
+    const int64_t nt = (nb + LAT_N - 1) / LAT_N;
+    int sp = sm_count() / mt;
+    if (sp > 16) sp = 16;
+    if (sp > nt) sp = (int)nt;
+    if (lat_enabled && mt <= sm_count() && sp >= 1 && nt <= (int64_t)sp * 8) {
+      pl->lat = true;
+      pl->cg = 1;
+      pl->m_tiles = mt;
+      pl->n_tiles = (int)nt;
+      pl->tiles_per_split = (int)((nt + sp - 1) / sp);
+      pl->splits = (int)((nt + pl->tiles_per_split - 1) / pl->tiles_per_split);
+      pl->stages = 0;
+      pl->smem = (size_t)pl->nkc * (SCR_A_CHUNK_BYTES + LAT_B_CHUNK_BYTES) +
+                 2 * SCR_CAP * SCR_M * 4 + 2 * LAT_N * 4 + 64 + 13 * 8 + 16 + 1024;
+      return true;
+    }
+  }
   pl->n_tiles = (int)((nb + SCR_N - 1) / SCR_N);
   pl->m_tiles = (int)((nq + SCR_M - 1) / SCR_M);
   // CTA pairs (cta_group::2) halve each CTA's share of the bank-tile traffic and leave room for a
@@ -973,15 +727,11 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
   if (stages < 2) return false;
   pl->stages = stages;
   pl->smem = fixed + (size_t)stages * b_stage;
-  pl->fb_cap = (int)(nq < FALLBACK_CAP ? nq : FALLBACK_CAP);
-  int fbs = (int)((nb + 127) / 128);
-  if (fbs > FALLBACK_SPLITS) fbs = FALLBACK_SPLITS;
-  if (fbs * k > 512) fbs = 512 / k;
-  pl->fb_splits = fbs < 1 ? 1 : fbs;
   return true;
 }
 
 struct ScreenWs {
+  long long* trace;   // 16 phase timestamps (debug, EXB_SCREEN_TRACE)
   RerankStatus* status;
   PrepScalars* qsc;
   PrepScalars* bsc;
@@ -1000,6 +750,7 @@ static size_t carve_screen(void* ws, int64_t nq, int64_t nb, const ScreenPlan& p
   o->status = cv.take<RerankStatus>(1);
   o->qsc = cv.take<PrepScalars>(1);
   o->bsc = cv.take<PrepScalars>(1);
+  o->trace = cv.take<long long>(16);
   o->b16 = cv.take<__half>((size_t)nb * pl.dpad);
   o->q16 = same ? o->b16 : cv.take<__half>((size_t)nq * pl.dpad);
   o->hb = cv.take<float>(nb);
@@ -1016,8 +767,15 @@ static size_t carve_screen(void* ws, int64_t nq, int64_t nb, const ScreenPlan& p
 }
 
 static int launch_prep(const float* x, int64_t n, int dim, int dpad, __half* out, float* hn,
-                       float* er, PrepScalars* sc, cudaStream_t st) {
-  knn_prep_kernel<<<(unsigned)((n + 7) / 8), 256, 0, st>>>(x, n, dim, dpad, out, hn, er, sc);
+                       float* er, PrepScalars* sc, cudaStream_t st,
+                       unsigned long long* zero16 = nullptr) {
+  const bool vec = (dim % 4 == 0) && (((uintptr_t)x & 15) == 0) && dim <= 512;
+  if (vec)
+    knn_prep_kernel<true><<<(unsigned)((n + 7) / 8), 256, 0, st>>>(x, n, dim, dpad, out, hn,
+                                                                   er, sc, zero16);
+  else
+    knn_prep_kernel<false><<<(unsigned)((n + 7) / 8), 256, 0, st>>>(x, n, dim, dpad, out, hn,
+                                                                    er, sc, zero16);
   EXB_LAUNCH_CHECK();
   return EXB_OK;
 }
@@ -1067,6 +825,64 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
   EXB_CHECK_ARG(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
   carve_screen(workspace, nq, nb, pl, k, same, &w);
   cudaStream_t st = (cudaStream_t)stream;
+
+  static const int trace_on = [] {
+    const char* e = getenv("EXB_SCREEN_TRACE");
+    return e ? atoi(e) : 0;
+  }();
+  const bool vec = (dim % 4 == 0) && (((uintptr_t)src | (uintptr_t)bank) & 15) == 0;
+  RerankParams rp;
+  rp.Q = src; rp.B = bank; rp.nq = nq; rp.nb = nb; rp.dim = dim; rp.k = k; rp.idx_base = idx_base;
+  rp.splits = pl.splits; rp.cand_val = w.cand_val; rp.cand_idx = w.cand_idx;
+  rp.cand_cnt = w.cand_cnt; rp.ha = w.ha; rp.ea = w.ea; rp.qsc = same ? w.bsc : w.qsc;
+  rp.bsc = w.bsc; rp.bank_max = reinterpret_cast<const float*>(w.bsc); rp.out_dist = out_dist;
+  rp.out_idx = out_idx; rp.fallback_rows = w.fb_rows; rp.fallback_cap = pl.fb_cap;
+  rp.status = w.status; rp.trace = trace_on ? w.trace : nullptr;
+  const unsigned rr_grid = (unsigned)((nq + RR_WARPS - 1) / RR_WARPS);
+
+  if (pl.lat) {
+    // per-update chain: prep -> latency screen -> rerank (inline fallback); no memset, no atomics
+    int rc = launch_prep(bank, nb, dim, pl.dpad, w.b16, w.hb, w.eb, nullptr, st,
+                         reinterpret_cast<unsigned long long*>(w.status));
+    if (rc) return rc;
+    if (!same) {
+      rc = launch_prep(src, nq, dim, pl.dpad, w.q16, w.ha, w.ea, nullptr, st);
+      if (rc) return rc;
+    }
+    CUtensorMap tq, tb;
+    rc = make_tmap(&tq, w.q16, nq, pl.dpad, SCR_M);
+    if (rc) return rc;
+    rc = make_tmap(&tb, w.b16, nb, pl.dpad, LAT_N);
+    if (rc) return rc;
+    static bool lat_attr_set = false;
+    if (!lat_attr_set) {
+      EXB_CUDA(cudaFuncSetAttribute(knn_screen_lat_kernel<4>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
+      EXB_CUDA(cudaFuncSetAttribute(knn_screen_lat_kernel<12>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
+      EXB_CUDA(cudaFuncSetAttribute(knn_screen_lat_kernel<16>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
+      lat_attr_set = true;
+    }
+    LatParams lp;
+    lp.ha = w.ha; lp.ea = w.ea; lp.hb = w.hb; lp.eb = w.eb; lp.nq = nq; lp.nb = nb;
+    lp.nkc = pl.nkc; lp.n_tiles = pl.n_tiles; lp.tiles_per_split = pl.tiles_per_split;
+    lp.splits = pl.splits; lp.k = k; lp.cand_val = w.cand_val; lp.cand_idx = w.cand_idx;
+    lp.cand_cnt = w.cand_cnt; lp.bank_max = reinterpret_cast<float*>(w.bsc);
+    lp.trace = trace_on ? w.trace : nullptr;
+    dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
+    const bool prof = g_prof.on && g_prof.n < 64;
+    if (prof) EXB_CUDA(cudaEventRecord(g_prof.e0[g_prof.n], st));
+    if (k <= 4) knn_screen_lat_kernel<4><<<grid, LAT_THREADS, pl.smem, st>>>(tq, tb, lp);
+    else if (k <= 12) knn_screen_lat_kernel<12><<<grid, LAT_THREADS, pl.smem, st>>>(tq, tb, lp);
+    else knn_screen_lat_kernel<16><<<grid, LAT_THREADS, pl.smem, st>>>(tq, tb, lp);
+    EXB_LAUNCH_CHECK();
+    if (prof) EXB_CUDA(cudaEventRecord(g_prof.e1[g_prof.n++], st));
+    if (vec) knn_rerank_kernel<true, true><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp);
+    else knn_rerank_kernel<true, false><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp);
+    EXB_LAUNCH_CHECK();
+    return EXB_OK;
+  }
 
   // header (status + scalars) is the first 3 x 256 bytes
   EXB_CUDA(cudaMemsetAsync(workspace, 0, 768, st));
@@ -1136,9 +952,8 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
   EXB_LAUNCH_CHECK();
   if (prof) EXB_CUDA(cudaEventRecord(g_prof.e1[g_prof.n++], st));
 
-  knn_rerank_kernel<<<(unsigned)((nq + 7) / 8), 256, 0, st>>>(
-      src, nq, bank, dim, k, idx_base, w.cand_val, w.cand_idx, w.cand_cnt, pl.splits, w.ha, w.ea,
-      same ? w.bsc : w.qsc, w.bsc, out_dist, out_idx, w.fb_rows, pl.fb_cap, w.status);
+  if (vec) knn_rerank_kernel<false, true><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp);
+  else knn_rerank_kernel<false, false><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp);
   EXB_LAUNCH_CHECK();
 
   // undecided rows -> exact kernel, indirect through the device-side row list / count
@@ -1157,6 +972,16 @@ extern "C" int exb_knn_screened_status_sync(const void* workspace, int32_t host_
   host_status[1] = s.invalid;
   host_status[2] = (int32_t)(s.pairs > 0x7fffffffULL ? 0x7fffffff : s.pairs);
   host_status[3] = (int32_t)(s.pairs >> 31);
+  return EXB_OK;
+}
+
+extern "C" int exb_debug_trace_sync(const void* workspace, int64_t host_ns[16],
+                                    exb_stream_t stream) {
+  EXB_CHECK_ARG(workspace && host_ns, "null pointer");
+  // carve_screen: status, qsc, bsc, trace at 256-byte steps
+  EXB_CUDA(cudaMemcpyAsync(host_ns, static_cast<const char*>(workspace) + 768, 16 * 8,
+                           cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  EXB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
   return EXB_OK;
 }
 

@@ -91,6 +91,13 @@ int exb_knn_screened_f32(const float* src, int64_t nq, const float* bank, int64_
 int exb_knn_screened_status_sync(const void* workspace, int32_t host_status[4],
                                  exb_stream_t stream);
 
+/* Debug: with EXB_SCREEN_TRACE=1 in the environment the per-update kernels stamp %globaltimer at
+ * their phase boundaries (block 0 / row 0 only); this copies the 16 stamps (ns) to the host.
+ *   [0] screen start, [1] first operand chunk landed, [2] MMAs issued, [3] accumulator ready,
+ *   [4] k-th best known, [5] candidates collected, [6] lists written,
+ *   [8] rerank start, [9] lists gathered, [10] survivors chosen, [11] top-k written. */
+int exb_debug_trace_sync(const void* workspace, int64_t host_ns[16], exb_stream_t stream);
+
 /* Measurement hook (bench.py): when enabled, every screening-kernel launch is bracketed by CUDA
  * events on its own stream (up to 64 launches); collect returns their durations in ms. */
 int exb_profile_begin(int enable);
