@@ -24,6 +24,8 @@ constexpr int LAT_N = 64;
 constexpr int LAT_B_CHUNK_BYTES = LAT_N * SCR_KC * 2;   // 8 KB
 constexpr int LAT_THREADS = 192;
 constexpr int LAT_TMEM_COLS = 128;
+constexpr int LAT_LS = SCR_M + 1;   // list row stride in shared memory: slot-major reads and
+                                    // row-major writes are both bank-conflict free
 
 struct LatParams {
   const float* ha;   // [nq]
@@ -35,6 +37,7 @@ struct LatParams {
   float* cand_val;
   int* cand_idx;
   int* cand_cnt;
+  float* cand_tk;    // [nq, splits] lower bound of the split's k-th best score (rerank prefilter)
   float* bank_max;   // [2] out: EB, HBmax (written by block (0,0) for the rerank kernel)
   long long* trace;  // optional phase timestamps (debug)
 };
@@ -61,8 +64,8 @@ knn_screen_lat_kernel(const __grid_constant__ CUtensorMap tmap_q,
   const uint32_t a_off = 0;
   const uint32_t b_off = a_off + (uint32_t)nkc * SCR_A_CHUNK_BYTES;
   const uint32_t lv_off = b_off + (uint32_t)nkc * LAT_B_CHUNK_BYTES;
-  const uint32_t li_off = lv_off + SCR_CAP * SCR_M * 4;
-  const uint32_t hn_off = li_off + SCR_CAP * SCR_M * 4;
+  const uint32_t li_off = lv_off + (SCR_CAP + 1) * LAT_LS * 4;
+  const uint32_t hn_off = (li_off + (SCR_CAP + 1) * LAT_LS * 4 + 15u) & ~15u;
   const uint32_t red_off = hn_off + 2 * LAT_N * 4;
   const uint32_t bar_off = red_off + 16 * 4;
   float* s_lv = reinterpret_cast<float*>(sm + lv_off);
@@ -228,38 +231,54 @@ knn_screen_lat_kernel(const __grid_constant__ CUtensorMap tmap_q,
         sc[32 + 4 * q + 2] = __uint_as_float(rb[4 * q + 2]) - g.z;
         sc[32 + 4 * q + 3] = __uint_as_float(rb[4 * q + 3]) - g.w;
       }
+      // Chain fed with maxima of column pairs: its k-th entry is the k-th best of 32 real scores,
+      // a lower bound of the true k-th best (conservative threshold) at half the min/max work.
 #pragma unroll
-      for (int c = 0; c < 2 * 32; ++c) chain_push_ks<KS>(tv, sc[c]);
+      for (int c = 0; c < 32; ++c) chain_push_ks<KS>(tv, fmaxf(sc[2 * c], sc[2 * c + 1]));
       st.tk = tv[KS - 1];
       if (st.tk > -FLT_MAX) st.tkeep = fmaxf(st.tkeep, keep_threshold(st));
       if (tr && j == 0 && et == 0) p.trace[4] = clock_now();
-      if (j > 0 && st.n > SCR_CAP - 14) list_compact(st, lv, li);
+      if (j > 0 && st.n > SCR_CAP - 14) list_compact<LAT_LS>(st, lv, li);
+      // branch-free appends: slot SCR_CAP is a trash row for hits beyond the capacity
       const float tkeep = st.tkeep;
+      int n = st.n;
+      float dropped = st.dropped;
 #pragma unroll
       for (int c = 0; c < 2 * 32; ++c) {
-        if (sc[c] >= tkeep) {
-          if (st.n < SCR_CAP) {
-            lv[st.n * SCR_M] = sc[c];
-            li[st.n * SCR_M] = t * LAT_N + c;
-            ++st.n;
-          } else {
-            st.dropped = fmaxf(st.dropped, sc[c]);   // judged against the final tkeep
-          }
+        const bool hit = sc[c] >= tkeep;
+        const int slot = min(n, SCR_CAP);
+        if (hit) {
+          lv[slot * LAT_LS] = sc[c];
+          li[slot * LAT_LS] = t * LAT_N + c;
         }
+        dropped = (hit && n >= SCR_CAP) ? fmaxf(dropped, sc[c]) : dropped;   // vs the final tkeep
+        n += hit ? 1 : 0;
       }
+      st.n = min(n, SCR_CAP);
+      st.dropped = dropped;
       if (tr && j == 0 && et == 0) p.trace[5] = clock_now();
       // the next iteration rewrites s_hn[as ^ 1 ^ 1] two tiles later: order the 64 writers/readers
       asm volatile("bar.sync 1, 128;" ::: "memory");
     }
 
+    if (n_local > 1) list_compact<LAT_LS>(st, lv, li);
+    const bool overflow = st.dropped > -FLT_MAX && st.dropped >= st.tkeep;
     if (row_ok) {
       const int64_t o = row * p.splits + split;
-      if (n_local > 1) list_compact(st, lv, li);
-      const bool overflow = st.dropped > -FLT_MAX && st.dropped >= st.tkeep;
       p.cand_cnt[o] = overflow ? -1 : st.n;
-      for (int c = 0; c < st.n; ++c) {
-        p.cand_idx[o * SCR_CAP + c] = li[c * SCR_M];
-        p.cand_val[o * SCR_CAP + c] = lv[c * SCR_M];
+      p.cand_tk[o] = st.tk;
+    }
+    // coalesced list output: the warp writes one row's slots (96 contiguous bytes) per step
+    __syncwarp();
+    if (tr && et == 0) p.trace[7] = clock_now();
+    const int64_t row0 = (int64_t)m_tile * SCR_M + quad * 32;
+#pragma unroll
+    for (int r = 0; r < 32; ++r) {
+      const int n_r = __shfl_sync(0xffffffffu, st.n, r);
+      if (row0 + r < p.nq && lane < n_r) {
+        const int64_t o = (row0 + r) * p.splits + split;
+        p.cand_val[o * SCR_CAP + lane] = s_lv[lane * LAT_LS + quad * 32 + r];
+        p.cand_idx[o * SCR_CAP + lane] = s_li[lane * LAT_LS + quad * 32 + r];
       }
     }
     if (tr && et == 0) p.trace[6] = clock_now();

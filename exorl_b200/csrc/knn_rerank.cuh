@@ -8,15 +8,31 @@
 //   LAT = true   per-update path: scalars come from the two floats the latency screen kernel
 //                wrote, undecided rows (rare) are recomputed inline against the whole bank, so the
 //                chain has no fallback launches; optional fused PBE epilogue by the last block.
-//   VEC          dim % 4 == 0 and 16-byte aligned rows: float4 loads, 8 survivors per batch.
+//   NI > 0       dim % 4 == 0, dim <= 128 NI, 16-byte aligned rows: float4 loads, 8 survivors per
+//                batch, all loads of a batch in flight; NI = 0: scalar loads, any dim <= 512.
 #pragma once
+#include "pbe_common.cuh"
 
 namespace exb {
 
-struct RerankStatus {   // device, zeroed per call
+struct RerankStatus {   // device, zeroed per call (24 bytes: the prep kernel clears 3 words)
   int n_fallback;
   int invalid;
   unsigned long long pairs;
+  unsigned ticket;      // fused PBE epilogue: blocks finished
+  unsigned pad;
+};
+
+// Fused PBE epilogue of the per-update chain (LAT only): utils/utils.py:301-318 + RMS :264-276
+// the moments are accumulated by the rerank blocks and the last block to finish applies the RMS
+// update; without RMS every warp finishes its own row.  (With RMS the per-row finish needs the
+// updated mean of ALL rows, so it stays a separate, fully parallel launch.)
+struct FusedPbe {
+  int on, avg, use_rms, use_clip;
+  float clip;
+  RmsParams rms;
+  float* out_reward;     // [nq]
+  double2* partials;     // [gridDim.x]
 };
 
 constexpr int RR_PER_LANE = 12;   // 32 * 12 = 384 >= 16 splits * 24 slots
@@ -31,6 +47,7 @@ struct RerankParams {
   const float* cand_val;
   const int* cand_idx;
   const int* cand_cnt;
+  const float* cand_tk;      // LAT: per-split lower bound of the k-th best score
   const float* ha;
   const float* ea;
   const PrepScalars* qsc;    // !LAT
@@ -42,6 +59,7 @@ struct RerankParams {
   int fallback_cap;
   RerankStatus* status;
   long long* trace;
+  FusedPbe pbe;
 };
 
 // Warp-resident ascending top-k of (value, index) pairs: lane r holds the r-th smallest.
@@ -63,14 +81,71 @@ struct WarpTopK {
   }
 };
 
+// Bitonic sorts across a warp, two elements per lane (element e = lane + 32 * slot).
+// Scores: descending.  Partner distance 32 is the only in-register stage.
+__device__ __forceinline__ void bitonic64_desc(float& x0, float& x1, int lane) {
+  const unsigned full = 0xffffffffu;
+#pragma unroll
+  for (int ksz = 2; ksz <= 64; ksz <<= 1) {
+#pragma unroll
+    for (int j = ksz >> 1; j > 0; j >>= 1) {
+      if (j == 32) {
+        const float lo = fminf(x0, x1), hi = fmaxf(x0, x1);
+        x0 = hi;   // (e & 64) == 0 for every element: one descending run
+        x1 = lo;
+      } else {
+        const float y0 = __shfl_xor_sync(full, x0, j), y1 = __shfl_xor_sync(full, x1, j);
+        const bool lower = (lane & j) == 0;
+        const bool d0 = ((lane & ksz) == 0), d1 = (((lane + 32) & ksz) == 0);
+        // descending run: the lower position keeps the max
+        x0 = (lower == d0) ? fmaxf(x0, y0) : fminf(x0, y0);
+        x1 = (lower == d1) ? fmaxf(x1, y1) : fminf(x1, y1);
+      }
+    }
+  }
+}
+
+// (value, index) pairs ascending by pair_less; N = 32 (slot 0 only) or 64.
+template <int N>
+__device__ __forceinline__ void bitonic_pairs_asc(float (&v)[2], int (&ix)[2], int lane) {
+  const unsigned full = 0xffffffffu;
+#pragma unroll
+  for (int ksz = 2; ksz <= N; ksz <<= 1) {
+#pragma unroll
+    for (int j = ksz >> 1; j > 0; j >>= 1) {
+      if (j == 32) {
+        if (pair_less(v[1], ix[1], v[0], ix[0])) {
+          const float tv = v[0]; v[0] = v[1]; v[1] = tv;
+          const int ti = ix[0]; ix[0] = ix[1]; ix[1] = ti;
+        }
+      } else {
+#pragma unroll
+        for (int s = 0; s < N / 32; ++s) {
+          const float yv = __shfl_xor_sync(full, v[s], j);
+          const int yi = __shfl_xor_sync(full, ix[s], j);
+          const bool lower = (lane & j) == 0;
+          const bool asc = (((lane + 32 * s) & ksz) == 0);
+          const bool y_less = pair_less(yv, yi, v[s], ix[s]);
+          // ascending run: the lower position keeps the smaller pair
+          const bool take = (lower == asc) ? y_less : !y_less;
+          if (take) { v[s] = yv; ix[s] = yi; }
+        }
+      }
+    }
+  }
+}
+
 // Exact squared distances of `count` bank rows (ids from idx_of(c)) to the query held in
-// registers, inserted into `top`.  NB rows per batch so that NB x (dim/32) loads are in flight.
-template <bool VEC, typename IdxOf>
+// registers.  NI = float4 loads per lane and row (dim <= 128 * NI, dim % 4 == 0, aligned rows);
+// NI = 0: scalar loads for any dim <= 512.  NB rows per batch and ALL of a batch's loads are
+// issued before the first use, so a batch costs one memory round trip.
+// STORE: lane (c & 31) keeps candidate c in slot c >> 5 (count <= 64); else insert into `top`.
+template <int NI, bool STORE, typename IdxOf>
 __device__ __forceinline__ void exact_scan(const float (&q)[16], const float* __restrict__ B,
                                            int dim, int k, int lane, int count, IdxOf idx_of,
-                                           WarpTopK& top) {
+                                           WarpTopK& top, float (&sv)[2], int (&si)[2]) {
   const unsigned full = 0xffffffffu;
-  constexpr int NB = VEC ? 8 : 4;
+  constexpr int NB = NI > 0 ? 8 : 4;
   for (int c0 = 0; c0 < count; c0 += NB) {
     int j[NB];
     float a[NB];
@@ -79,27 +154,31 @@ __device__ __forceinline__ void exact_scan(const float (&q)[16], const float* __
       j[u] = idx_of(min(c0 + u, count - 1));
       a[u] = 0.f;
     }
-    if constexpr (VEC) {
+    if constexpr (NI > 0) {
       const int nv = dim >> 2;
+      float4 b[NI][NB];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
+      for (int i = 0; i < NI; ++i) {
         const int c = lane + 32 * i;
-        if (c < nv) {
-          float4 b[NB];
+        const int cc = (c < nv) ? c : 0;       // clamped, masked below: loads stay unconditional
 #pragma unroll
-          for (int u = 0; u < NB; ++u)
-            b[u] = __ldg(reinterpret_cast<const float4*>(B + (int64_t)j[u] * dim) + c);
+        for (int u = 0; u < NB; ++u)
+          b[i][u] = __ldg(reinterpret_cast<const float4*>(B + (int64_t)j[u] * dim) + cc);
+      }
 #pragma unroll
-          for (int u = 0; u < NB; ++u) {
-            float d = q[4 * i] - b[u].x;
-            a[u] = fmaf(d, d, a[u]);
-            d = q[4 * i + 1] - b[u].y;
-            a[u] = fmaf(d, d, a[u]);
-            d = q[4 * i + 2] - b[u].z;
-            a[u] = fmaf(d, d, a[u]);
-            d = q[4 * i + 3] - b[u].w;
-            a[u] = fmaf(d, d, a[u]);
-          }
+      for (int i = 0; i < NI; ++i) {
+        const bool ok = (lane + 32 * i) < nv;
+#pragma unroll
+        for (int u = 0; u < NB; ++u) {
+          float d = q[4 * i] - b[i][u].x;
+          float t = d * d;
+          d = q[4 * i + 1] - b[i][u].y;
+          t = fmaf(d, d, t);
+          d = q[4 * i + 2] - b[i][u].z;
+          t = fmaf(d, d, t);
+          d = q[4 * i + 3] - b[i][u].w;
+          t = fmaf(d, d, t);
+          a[u] += ok ? t : 0.f;
         }
       }
     } else {
@@ -120,30 +199,37 @@ __device__ __forceinline__ void exact_scan(const float (&q)[16], const float* __
 #pragma unroll
       for (int u = 0; u < NB; ++u) a[u] += __shfl_xor_sync(full, a[u], off);
 #pragma unroll
-    for (int u = 0; u < NB; ++u)
-      if (c0 + u < count) top.insert(a[u], j[u], k, lane);
+    for (int u = 0; u < NB; ++u) {
+      if constexpr (STORE) {
+        const int c = c0 + u;
+        if (c < count && (c & 31) == lane) {
+          if (c < 32) { sv[0] = a[u]; si[0] = j[u]; }
+          else { sv[1] = a[u]; si[1] = j[u]; }
+        }
+      } else {
+        if (c0 + u < count) top.insert(a[u], j[u], k, lane);
+      }
+    }
   }
 }
 
-template <bool LAT, bool VEC>
-__global__ void __launch_bounds__(RR_WARPS * 32)
-knn_rerank_kernel(const RerankParams p) {
-  __shared__ int s_surv[RR_WARPS][RR_SURV];
+// One warp, one query row.  Returns (in lanes < k) the row's k smallest distances, ascending.
+template <bool LAT, int NI>
+__device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, int lane, int wib,
+                                            int (&s_surv)[RR_WARPS][RR_SURV],
+                                            float (&s_val)[RR_WARPS][RR_SURV]) {
   const unsigned full = 0xffffffffu;
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  const int64_t row = (int64_t)blockIdx.x * RR_WARPS + wib;
-  if (row >= p.nq) return;
   const bool tr = p.trace != nullptr && row == 0;
   if (tr && lane == 0) p.trace[8] = clock_now();
   const int k = p.k, splits = p.splits, dim = p.dim;
 
   // query row into registers first: its latency hides behind the list gathering
   float q[16];
-  if constexpr (VEC) {
+  if constexpr (NI > 0) {
     const float4* q4 = reinterpret_cast<const float4*>(p.Q + row * dim);
     const int nv = dim >> 2;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < NI; ++i) {
       const int c = lane + 32 * i;
       const float4 v = (c < nv) ? __ldg(q4 + c) : make_float4(0.f, 0.f, 0.f, 0.f);
       q[4 * i] = v.x; q[4 * i + 1] = v.y; q[4 * i + 2] = v.z; q[4 * i + 3] = v.w;
@@ -168,60 +254,100 @@ knn_rerank_kernel(const RerankParams p) {
     undecided = (p.qsc->range_flag | p.bsc->range_flag) != 0;
   }
 
-  // ---- per-split counts: lane sp holds the count of split sp (splits <= 16)
+  // ---- everything this row needs from the screen is requested at once (one round trip): counts
+  // (lane sp holds split sp, splits <= 16), per-split thresholds, the row's scalars, and all list
+  // slots (entry e = lane + 32 i; slots beyond a split's count are read and masked afterwards).
   const int my_cnt = (lane < splits) ? p.cand_cnt[row * splits + lane] : 0;
-  if (__any_sync(full, my_cnt < 0)) undecided = true;
-  int total = max(my_cnt, 0);
-#pragma unroll
-  for (int off = 16; off > 0; off >>= 1) total += __shfl_xor_sync(full, total, off);
-  if (total < k) undecided = true;
-
-  // ---- gather the per-split lists of this row into registers (entry e = lane + 32 i)
+  float my_tk = -FLT_MAX;
+  if constexpr (LAT) {
+    if (lane < splits) my_tk = p.cand_tk[row * splits + lane];
+  }
+  const float ea_row = p.ea[row];
+  const float ha_row = p.ha[row];
   float ev[RR_PER_LANE];
   int ei[RR_PER_LANE];
 #pragma unroll
   for (int i = 0; i < RR_PER_LANE; ++i) {
     const int e = lane + 32 * i;
-    const int sp = e / SCR_CAP, c = e - sp * SCR_CAP;
-    const int cnt = __shfl_sync(full, my_cnt, sp & 31);
+    const int sp = e / SCR_CAP;
     ev[i] = -FLT_MAX;
     ei[i] = -1;
-    if (sp < splits && c < cnt) {
-      ev[i] = p.cand_val[(row * splits + sp) * SCR_CAP + c];
-      ei[i] = p.cand_idx[(row * splits + sp) * SCR_CAP + c];
+    if (sp < splits) {
+      ev[i] = p.cand_val[row * splits * SCR_CAP + e];
+      ei[i] = p.cand_idx[row * splits * SCR_CAP + e];
+    }
+  }
+  if (__any_sync(full, my_cnt < 0)) undecided = true;
+  int total = max(my_cnt, 0);
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) total += __shfl_xor_sync(full, total, off);
+  if (total < k) undecided = true;
+#pragma unroll
+  for (int i = 0; i < RR_PER_LANE; ++i) {
+    const int e = lane + 32 * i;
+    const int sp = e / SCR_CAP, c = e - sp * SCR_CAP;
+    const int cnt = __shfl_sync(full, my_cnt, sp & 31);
+    if (!(sp < splits && c < cnt)) {
+      ev[i] = -FLT_MAX;
+      ei[i] = -1;
     }
   }
   if (tr && lane == 0) p.trace[9] = clock_now();
 
   int n_surv = 0;
-  const float ea_row = p.ea[row];
   if (!undecided && !(ea_row < INFINITY)) undecided = true;   // query row outside the fp16 range
   if (!undecided) {
-    // ---- k-th best screened score over the union of splits (k rounds of warp arg-max)
-    float wv[RR_PER_LANE];
+    // ---- k-th best screened score over the union of splits.
+    // T0 = the best per-split lower bound of the k-th best: the global k-th best is >= T0 and is
+    // the k-th largest of the entries >= T0 (the split that attains T0 alone holds k of them).
+    float t0 = -FLT_MAX;
+    if constexpr (LAT) {
+      if (lane < splits && my_cnt >= k) t0 = my_tk;
 #pragma unroll
-    for (int i = 0; i < RR_PER_LANE; ++i) wv[i] = ev[i];
+      for (int off = 16; off > 0; off >>= 1) t0 = fmaxf(t0, __shfl_xor_sync(full, t0, off));
+    }
+    int n0 = 0;
+#pragma unroll
+    for (int i = 0; i < RR_PER_LANE; ++i) {
+      const bool keep = ei[i] >= 0 && ev[i] >= t0;
+      const unsigned m = __ballot_sync(full, keep);
+      const int pos = n0 + __popc(m & ((1u << lane) - 1u));
+      if (keep && pos < RR_SURV) s_val[wib][pos] = ev[i];
+      n0 += __popc(m);
+    }
+    __syncwarp();
     float kth = -FLT_MAX;
-    for (int round = 0; round < k; ++round) {
-      float lm = wv[0];
-      int ls = 0;
+    if (n0 <= RR_SURV) {
+      // one 64-element bitonic sort instead of k dependent arg-max rounds
+      float x0 = (lane < n0) ? s_val[wib][lane] : -FLT_MAX;
+      float x1 = (lane + 32 < n0) ? s_val[wib][lane + 32] : -FLT_MAX;
+      bitonic64_desc(x0, x1, lane);
+      kth = __shfl_sync(full, x0, k - 1);      // k <= 16: always in slot 0
+    } else {
+      float wv[RR_PER_LANE];
 #pragma unroll
-      for (int i = 1; i < RR_PER_LANE; ++i)
-        if (wv[i] > lm) { lm = wv[i]; ls = i; }
-      float wm = lm;
+      for (int i = 0; i < RR_PER_LANE; ++i) wv[i] = ev[i];
+      for (int round = 0; round < k; ++round) {
+        float lm = wv[0];
+        int ls = 0;
 #pragma unroll
-      for (int off = 16; off > 0; off >>= 1) wm = fmaxf(wm, __shfl_xor_sync(full, wm, off));
-      const int owner = __ffs(__ballot_sync(full, lm == wm)) - 1;
-      if (lane == owner) {
+        for (int i = 1; i < RR_PER_LANE; ++i)
+          if (wv[i] > lm) { lm = wv[i]; ls = i; }
+        float wm = lm;
 #pragma unroll
-        for (int i = 0; i < RR_PER_LANE; ++i)
-          if (i == ls) wv[i] = -FLT_MAX;
+        for (int off = 16; off > 0; off >>= 1) wm = fmaxf(wm, __shfl_xor_sync(full, wm, off));
+        const int owner = __ffs(__ballot_sync(full, lm == wm)) - 1;
+        if (lane == owner) {
+#pragma unroll
+          for (int i = 0; i < RR_PER_LANE; ++i)
+            if (i == ls) wv[i] = -FLT_MAX;
+        }
+        kth = wm;
       }
-      kth = wm;
     }
     // same keep rule as the screening kernel, now with the global k-th best
     ListState st;
-    st.ha = p.ha[row];
+    st.ha = ha_row;
     st.e2 = 2.f * (ea_row + eb_max);
     st.dl = (st.ha + hb_max) * SCR_ACC_EPS;
     st.tk = kth;
@@ -241,29 +367,103 @@ knn_rerank_kernel(const RerankParams p) {
 
   WarpTopK top;
   top.init();
+  float sv[2] = {FLT_MAX, FLT_MAX};
+  int si[2] = {INT_MAX, INT_MAX};
   if (undecided) {
     if constexpr (LAT) {
       // rare: recompute this row against the whole bank here (no fallback launches in the chain)
       if (lane == 0) atomicAdd(&p.status->n_fallback, 1);
-      exact_scan<VEC>(q, p.B, dim, k, lane, (int)p.nb, [](int c) { return c; }, top);
+      exact_scan<NI, false>(q, p.B, dim, k, lane, (int)p.nb, [](int c) { return c; }, top, sv,
+                             si);
     } else {
       if (lane == 0) {
         const int pos = atomicAdd(&p.status->n_fallback, 1);
         if (pos < p.fallback_cap) p.fallback_rows[pos] = (int)row;
         else p.status->invalid = 1;
       }
-      return;
+      return 0.f;
     }
   } else {
+    // survivors' exact distances stay distributed over the lanes, then one bitonic sort
     const int* surv = s_surv[wib];
-    exact_scan<VEC>(q, p.B, dim, k, lane, n_surv, [surv](int c) { return surv[c]; }, top);
+    exact_scan<NI, true>(q, p.B, dim, k, lane, n_surv, [surv](int c) { return surv[c]; }, top,
+                          sv, si);
+    if (n_surv <= 32) bitonic_pairs_asc<32>(sv, si, lane);
+    else bitonic_pairs_asc<64>(sv, si, lane);
+    top.v = sv[0];
+    top.i = si[0];
     if (lane == 0) atomicAdd(&p.status->pairs, (unsigned long long)n_surv);
   }
+  const float dist = sqrtf(top.v);
   if (lane < k) {
-    p.out_dist[row * k + lane] = sqrtf(top.v);
+    p.out_dist[row * k + lane] = dist;
     p.out_idx[row * k + lane] = top.i + p.idx_base;
   }
   if (tr && lane == 0) p.trace[11] = clock_now();
+  return dist;
+}
+
+template <bool LAT, int NI>
+__global__ void __launch_bounds__(RR_WARPS * 32)
+knn_rerank_kernel(const RerankParams p) {
+  __shared__ int s_surv[RR_WARPS][RR_SURV];
+  __shared__ float s_val[RR_WARPS][RR_SURV];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int64_t row = (int64_t)blockIdx.x * RR_WARPS + wib;
+  const bool active = row < p.nq;
+  float dist = 0.f;
+  if (active) dist = rerank_row<LAT, NI>(p, row, lane, wib, s_surv, s_val);
+  if constexpr (LAT) {
+    if (!p.pbe.on) return;
+    const FusedPbe& f = p.pbe;
+    const int k = p.k;
+    if (!f.use_rms) {
+      // no running moments: every warp finishes its own row (same order of operations as pbe_row)
+      if (active) {
+        float acc = 0.f, r = 0.f;
+        for (int j = 0; j < k; ++j) {
+          float v = __shfl_sync(0xffffffffu, dist, j);
+          if (f.use_clip) v = clip_nan(v - f.clip);
+          acc += v;
+          r = v;
+        }
+        if (lane == 0) f.out_reward[row] = logf((f.avg ? acc / (float)k : r) + 1.0f);
+      }
+      return;
+    }
+    __shared__ double2 s_part[RR_WARPS];
+    __shared__ double2 s_red[RR_WARPS];
+    __shared__ bool s_last;
+    double2 acc = make_double2(0.0, 0.0);
+    if (active && (f.avg ? lane < k : lane == k - 1)) {
+      acc.x = (double)dist;
+      acc.y = (double)dist * (double)dist;
+    }
+    acc = warp_sum2(acc);
+    if (lane == 0) s_part[wib] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double2 t = s_part[0];
+      for (int w = 1; w < RR_WARPS; ++w) { t.x += s_part[w].x; t.y += s_part[w].y; }
+      f.partials[blockIdx.x] = t;
+      __threadfence();
+      s_last = atomicAdd(&p.status->ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    double2 a = make_double2(0.0, 0.0);
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += RR_WARPS * 32) {
+      const double2 t = __ldcg(f.partials + i);
+      a.x += t.x;
+      a.y += t.y;
+    }
+    const double2 all = block_sum2<RR_WARPS * 32>(a, s_red);
+    if (threadIdx.x == 0) {
+      const double sums[3] = {(double)(f.avg ? p.nq * k : p.nq), all.x, all.y};
+      rms_apply(sums, f.rms);   // M', S' for the per-row finish kernel that follows
+    }
+  }
 }
 
 }  // namespace exb

@@ -35,6 +35,8 @@
 namespace exb {
 
 int exact_splits(int64_t nq, int64_t nb, int k);
+int launch_pbe_finish(const float* dist, int64_t nq, int k, int avg, int use_rms, int use_clip,
+                      float clip, const float* m_ptr, float* out, cudaStream_t st);
 int launch_exact(const float* src, int64_t nq, const float* bank, int64_t nb, int dim, int k,
                  int idx_base, float* out_dist, int* out_idx, float* part_d2, int* part_idx,
                  int splits, const int* row_list, const int* row_count, int64_t max_slots,
@@ -76,7 +78,7 @@ knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
                 __half* __restrict__ out, float* __restrict__ half_norm,
                 float* __restrict__ round_err, PrepScalars* __restrict__ sc,
                 unsigned long long* __restrict__ zero16) {
-  if (zero16 != nullptr && blockIdx.x == 0 && threadIdx.x < 2) zero16[threadIdx.x] = 0ull;
+  if (zero16 != nullptr && blockIdx.x == 0 && threadIdx.x < 3) zero16[threadIdx.x] = 0ull;
   const int lane = threadIdx.x & 31;
   const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= n) return;
@@ -194,15 +196,16 @@ __device__ __forceinline__ float keep_threshold(const ListState& s) {
   return t;
 }
 
-// bv/bi: this thread's column of the [CAP][128] arrays (stride SCR_M)
+// bv/bi: this thread's column of the [CAP][STRIDE] arrays
+template <int STRIDE = SCR_M>
 __device__ __forceinline__ void list_compact(ListState& s, float* bv, int* bi) {
   int w = 0;
   for (int r = 0; r < s.n; ++r) {
-    const float v = bv[r * SCR_M];
-    const int j = bi[r * SCR_M];
+    const float v = bv[r * STRIDE];
+    const int j = bi[r * STRIDE];
     if (v >= s.tkeep) {
-      bv[w * SCR_M] = v;
-      bi[w * SCR_M] = j;
+      bv[w * STRIDE] = v;
+      bi[w * STRIDE] = j;
       ++w;
     }
   }
@@ -699,7 +702,7 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
       pl->splits = (int)((nt + pl->tiles_per_split - 1) / pl->tiles_per_split);
       pl->stages = 0;
       pl->smem = (size_t)pl->nkc * (SCR_A_CHUNK_BYTES + LAT_B_CHUNK_BYTES) +
-                 2 * SCR_CAP * SCR_M * 4 + 2 * LAT_N * 4 + 64 + 13 * 8 + 16 + 1024;
+                 2 * (SCR_CAP + 1) * LAT_LS * 4 + 32 + 2 * LAT_N * 4 + 64 + 13 * 8 + 16 + 1024;
       return true;
     }
   }
@@ -730,6 +733,17 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
   return true;
 }
 
+template <bool LAT>
+static void launch_rerank(const RerankParams& rp, unsigned grid, int ni, cudaStream_t st) {
+  switch (ni) {
+    case 1: knn_rerank_kernel<LAT, 1><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
+    case 2: knn_rerank_kernel<LAT, 2><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
+    case 3: knn_rerank_kernel<LAT, 3><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
+    case 4: knn_rerank_kernel<LAT, 4><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
+    default: knn_rerank_kernel<LAT, 0><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
+  }
+}
+
 struct ScreenWs {
   long long* trace;   // 16 phase timestamps (debug, EXB_SCREEN_TRACE)
   RerankStatus* status;
@@ -740,6 +754,8 @@ struct ScreenWs {
   float *ha, *ea, *hb, *eb;
   float* cand_val;
   int *cand_idx, *cand_cnt, *fb_rows;
+  float* cand_tk;
+  double2* pbe_partials;   // fused per-update epilogue: one per rerank block
   float* fb_d2;
   int* fb_idx;
 };
@@ -760,6 +776,8 @@ static size_t carve_screen(void* ws, int64_t nq, int64_t nb, const ScreenPlan& p
   o->cand_val = cv.take<float>((size_t)nq * pl.splits * SCR_CAP);
   o->cand_idx = cv.take<int>((size_t)nq * pl.splits * SCR_CAP);
   o->cand_cnt = cv.take<int>((size_t)nq * pl.splits);
+  o->cand_tk = cv.take<float>((size_t)nq * pl.splits);
+  o->pbe_partials = cv.take<double2>(pl.lat ? (size_t)((nq + RR_WARPS - 1) / RR_WARPS) : 1);
   o->fb_rows = cv.take<int>(pl.fb_cap);
   o->fb_d2 = cv.take<float>((size_t)pl.fb_cap * pl.fb_splits * k);
   o->fb_idx = cv.take<int>((size_t)pl.fb_cap * pl.fb_splits * k);
@@ -801,10 +819,13 @@ extern "C" size_t exb_knn_screened_workspace_bytes(int64_t nq, int64_t nb, int d
   return carve_screen(nullptr, nq, nb, pl, k, false, &w);
 }
 
-extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* bank, int64_t nb,
-                                    int dim, int k, int32_t idx_base, int src_is_bank,
-                                    float* out_dist, int32_t* out_idx, void* workspace,
-                                    size_t workspace_bytes, exb_stream_t stream) {
+// pbe: optional fused epilogue request; *fused tells the caller whether it was honoured (only the
+// per-update latency chain fuses it).
+static int screened_impl(const float* src, int64_t nq, const float* bank, int64_t nb, int dim,
+                         int k, int32_t idx_base, int src_is_bank, float* out_dist,
+                         int32_t* out_idx, void* workspace, size_t workspace_bytes,
+                         exb_stream_t stream, const FusedPbe* pbe, bool* fused) {
+  if (fused) *fused = false;
   EXB_CHECK_ARG(src && bank && out_dist && out_idx, "null pointer");
   EXB_CHECK_ARG(nq > 0 && nb > 0 && nq < (1LL << 31) && nb < (1LL << 31), "bad row counts");
   if (k > nb) {
@@ -831,13 +852,15 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
     return e ? atoi(e) : 0;
   }();
   const bool vec = (dim % 4 == 0) && (((uintptr_t)src | (uintptr_t)bank) & 15) == 0;
+  const int ni = vec ? (dim + 127) / 128 : 0;   // float4 loads per lane and row (0 = scalar path)
   RerankParams rp;
   rp.Q = src; rp.B = bank; rp.nq = nq; rp.nb = nb; rp.dim = dim; rp.k = k; rp.idx_base = idx_base;
   rp.splits = pl.splits; rp.cand_val = w.cand_val; rp.cand_idx = w.cand_idx;
-  rp.cand_cnt = w.cand_cnt; rp.ha = w.ha; rp.ea = w.ea; rp.qsc = same ? w.bsc : w.qsc;
+  rp.cand_cnt = w.cand_cnt; rp.cand_tk = w.cand_tk; rp.ha = w.ha; rp.ea = w.ea; rp.qsc = same ? w.bsc : w.qsc;
   rp.bsc = w.bsc; rp.bank_max = reinterpret_cast<const float*>(w.bsc); rp.out_dist = out_dist;
   rp.out_idx = out_idx; rp.fallback_rows = w.fb_rows; rp.fallback_cap = pl.fb_cap;
   rp.status = w.status; rp.trace = trace_on ? w.trace : nullptr;
+  rp.pbe.on = 0;
   const unsigned rr_grid = (unsigned)((nq + RR_WARPS - 1) / RR_WARPS);
 
   if (pl.lat) {
@@ -868,7 +891,7 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
     lp.ha = w.ha; lp.ea = w.ea; lp.hb = w.hb; lp.eb = w.eb; lp.nq = nq; lp.nb = nb;
     lp.nkc = pl.nkc; lp.n_tiles = pl.n_tiles; lp.tiles_per_split = pl.tiles_per_split;
     lp.splits = pl.splits; lp.k = k; lp.cand_val = w.cand_val; lp.cand_idx = w.cand_idx;
-    lp.cand_cnt = w.cand_cnt; lp.bank_max = reinterpret_cast<float*>(w.bsc);
+    lp.cand_cnt = w.cand_cnt; lp.cand_tk = w.cand_tk; lp.bank_max = reinterpret_cast<float*>(w.bsc);
     lp.trace = trace_on ? w.trace : nullptr;
     dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
     const bool prof = g_prof.on && g_prof.n < 64;
@@ -878,9 +901,17 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
     else knn_screen_lat_kernel<16><<<grid, LAT_THREADS, pl.smem, st>>>(tq, tb, lp);
     EXB_LAUNCH_CHECK();
     if (prof) EXB_CUDA(cudaEventRecord(g_prof.e1[g_prof.n++], st));
-    if (vec) knn_rerank_kernel<true, true><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp);
-    else knn_rerank_kernel<true, false><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp);
+    if (pbe) {
+      rp.pbe = *pbe;
+      rp.pbe.on = 1;
+      rp.pbe.partials = w.pbe_partials;
+      if (fused) *fused = true;
+    }
+    launch_rerank<true>(rp, rr_grid, ni, st);
     EXB_LAUNCH_CHECK();
+    if (pbe && pbe->use_rms)
+      return launch_pbe_finish(out_dist, nq, k, pbe->avg, 1, pbe->use_clip, pbe->clip,
+                               pbe->rms.m_out, pbe->out_reward, st);
     return EXB_OK;
   }
 
@@ -952,13 +983,81 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
   EXB_LAUNCH_CHECK();
   if (prof) EXB_CUDA(cudaEventRecord(g_prof.e1[g_prof.n++], st));
 
-  if (vec) knn_rerank_kernel<false, true><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp);
-  else knn_rerank_kernel<false, false><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp);
+  launch_rerank<false>(rp, rr_grid, ni, st);
   EXB_LAUNCH_CHECK();
 
   // undecided rows -> exact kernel, indirect through the device-side row list / count
   return launch_exact(src, nq, bank, nb, dim, k, idx_base, out_dist, out_idx, w.fb_d2, w.fb_idx,
                       pl.fb_splits, w.fb_rows, &w.status->n_fallback, pl.fb_cap, st);
+}
+
+extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* bank, int64_t nb,
+                                    int dim, int k, int32_t idx_base, int src_is_bank,
+                                    float* out_dist, int32_t* out_idx, void* workspace,
+                                    size_t workspace_bytes, exb_stream_t stream) {
+  return screened_impl(src, nq, bank, nb, dim, k, idx_base, src_is_bank, out_dist, out_idx,
+                       workspace, workspace_bytes, stream, nullptr, nullptr);
+}
+
+// ------------------------------------------------------------------------------------------
+// PBE.__call__ in one call (utils/utils.py:289-319): kNN + RMS + epilogue
+// ------------------------------------------------------------------------------------------
+static size_t apt_knn_ws_bytes(int64_t nq, int64_t nb, int dim, int k) {
+  const size_t a = exb_knn_screened_workspace_bytes(nq, nb, dim, k);
+  const size_t b = exb_knn_exact_workspace_bytes(nq, nb, dim, k);
+  return align_up(a > b ? a : b, 256);
+}
+
+extern "C" size_t exb_apt_reward_workspace_bytes(int64_t nq, int64_t nb, int dim, int k) {
+  if (nq <= 0 || nb <= 0 || dim <= 0 || k <= 0 || k > EXB_MAX_K) return 0;
+  return apt_knn_ws_bytes(nq, nb, dim, k) + align_up(exb_pbe_workspace_bytes(nq, k), 256);
+}
+
+extern "C" int exb_apt_reward_f32(const float* src, int64_t nq, const float* bank, int64_t nb,
+                                  int dim, int k, int src_is_bank, int mode, int avg, int use_rms,
+                                  float clip, const float* rms_m_in, const float* rms_s_in,
+                                  double rms_n, float* rms_m_out, float* rms_s_out,
+                                  float* out_reward, float* out_dist, int32_t* out_idx,
+                                  void* workspace, size_t workspace_bytes, exb_stream_t stream) {
+  EXB_CHECK_ARG(src && bank && out_reward && out_dist && out_idx, "null pointer");
+  EXB_CHECK_ARG(nq > 0 && nb > 0 && dim > 0, "empty input");
+  EXB_CHECK_ARG(k >= 1 && k <= EXB_MAX_K, "k=%d outside [1,%d]", k, EXB_MAX_K);
+  EXB_CHECK_ARG(mode >= 0 && mode <= 2, "mode must be 0 (auto), 1 (exact) or 2 (screened)");
+  EXB_CHECK_ARG(!use_rms || (rms_m_in && rms_s_in && rms_m_out && rms_s_out),
+                "use_rms needs the RMS state pointers");
+  if (k > nb) {
+    set_error("selected index k out of range (k=%d > bank rows=%lld)", k, (long long)nb);
+    return EXB_EKRANGE;
+  }
+  const size_t knn_bytes = apt_knn_ws_bytes(nq, nb, dim, k);
+  const size_t pbe_bytes = exb_pbe_workspace_bytes(nq, k);
+  EXB_CHECK_ARG(workspace && workspace_bytes >= knn_bytes + pbe_bytes,
+                "workspace too small: %zu < %zu", workspace_bytes, knn_bytes + pbe_bytes);
+  void* pbe_ws = static_cast<char*>(workspace) + knn_bytes;
+  const bool can_screen = dim <= EXB_SCREEN_MAX_DIM && k <= SCR_MAX_K;
+  if (mode == 2 && !can_screen) {
+    set_error("screened kNN supports dim <= %d and k <= %d (got dim=%d k=%d)", EXB_SCREEN_MAX_DIM,
+              SCR_MAX_K, dim, k);
+    return EXB_EUNSUPPORTED;
+  }
+  const bool screen = mode == 2 || (mode == 0 && can_screen && nq >= 128 && nb >= 256);
+  int rc;
+  if (screen) {
+    FusedPbe f;
+    f.on = 1; f.avg = avg; f.use_rms = use_rms; f.use_clip = clip >= 0.0f; f.clip = clip;
+    f.rms = RmsParams{rms_m_in, rms_s_in, rms_n, rms_m_out, rms_s_out};
+    f.out_reward = out_reward; f.partials = nullptr;
+    bool fused = false;
+    rc = screened_impl(src, nq, bank, nb, dim, k, 0, src_is_bank, out_dist, out_idx, workspace,
+                       knn_bytes, stream, &f, &fused);
+    if (rc || fused) return rc;
+  } else {
+    rc = exb_knn_exact_f32(src, nq, bank, nb, dim, k, 0, out_dist, out_idx, workspace, knn_bytes,
+                           stream);
+    if (rc) return rc;
+  }
+  return exb_pbe_reward(out_dist, nq, k, avg, use_rms, clip, rms_m_in, rms_s_in, rms_n, rms_m_out,
+                        rms_s_out, out_reward, pbe_ws, pbe_bytes, stream);
 }
 
 extern "C" int exb_knn_screened_status_sync(const void* workspace, int32_t host_status[4],

@@ -8,93 +8,13 @@
 // exposes, n is the python float passed by value.  Sums are accumulated in fp64 and the updated
 // M, S are rounded to fp32, like the reference's fp32 tensors.
 #include "common.cuh"
+#include "pbe_common.cuh"
 #include <math.h>
 
 namespace exb {
 
-constexpr int PBE_THREADS = 256;
 constexpr int PBE_SMALL_THREADS = 1024;
 constexpr int64_t PBE_SMALL_LIMIT = 16384;  // values handled by the single-block kernel
-
-struct RmsParams {
-  const float* m_in;
-  const float* s_in;
-  double n;
-  float* m_out;
-  float* s_out;
-};
-
-// values entering the moments: avg -> all nq*k, else column k-1 of each row
-__device__ __forceinline__ int64_t value_index(int64_t i, int k, int avg) {
-  return avg ? i : i * k + (k - 1);
-}
-
-__device__ __forceinline__ double2 warp_sum2(double2 v) {
-#pragma unroll
-  for (int off = 16; off > 0; off >>= 1) {
-    v.x += __shfl_xor_sync(0xffffffffu, v.x, off);
-    v.y += __shfl_xor_sync(0xffffffffu, v.y, off);
-  }
-  return v;
-}
-
-// Block-wide (sum, sumsq); result valid in thread 0.
-template <int THREADS>
-__device__ double2 block_sum2(double2 v, double2* smem) {
-  v = warp_sum2(v);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (lane == 0) smem[warp] = v;
-  __syncthreads();
-  if (warp == 0) {
-    double2 t = (lane < THREADS / 32) ? smem[lane] : make_double2(0.0, 0.0);
-    t = warp_sum2(t);
-    if (lane == 0) smem[0] = t;
-  }
-  __syncthreads();
-  return smem[0];
-}
-
-// utils/utils.py:264-276 on scalars.  sums = {count, sum, sumsq}.
-__device__ void rms_apply(const double* sums, const RmsParams& p) {
-  const double bs = sums[0], sum = sums[1], sumsq = sums[2];
-  const double M = (double)*p.m_in, S = (double)*p.s_in, n = p.n;
-  const double mean = sum / bs;
-  // torch.var(unbiased): NaN for a single element, like the reference.
-  const double var = (bs > 1.0) ? fmax(sumsq - sum * mean, 0.0) / (bs - 1.0) : (double)NAN;
-  const double tot = n + bs;
-  const double delta = mean - M;
-  const double new_m = M + delta * bs / tot;
-  const double new_s = (S * n + var * bs + delta * delta * n * bs / tot) / tot;
-  *p.m_out = (float)new_m;
-  *p.s_out = (float)new_s;
-}
-
-// torch.maximum(t, 0) propagates NaN (0/0 when every distance is 0, e.g. k = 1 on source =
-// target); fmaxf would not.
-__device__ __forceinline__ float clip_nan(float t) { return (t < 0.f) ? 0.f : t; }
-
-__device__ __forceinline__ float pbe_row(const float* __restrict__ d, int k, int avg, float inv_on,
-                                         float m, int use_clip, float clip) {
-  // r / M (true division, utils.py:304/311), max(r - clip, 0) (:305-308/:312-315),
-  // mean over k (:317), log(r + 1) (:318)
-  float r;
-  if (avg) {
-    float acc = 0.f;
-    for (int j = 0; j < k; ++j) {
-      float v = d[j];
-      if (inv_on != 0.f) v = v / m;
-      if (use_clip) v = clip_nan(v - clip);
-      acc += v;
-    }
-    r = acc / (float)k;
-  } else {
-    float v = d[k - 1];
-    if (inv_on != 0.f) v = v / m;
-    if (use_clip) v = clip_nan(v - clip);
-    r = v;
-  }
-  return logf(r + 1.0f);
-}
 
 // Partial sums per block, then the last block to finish (ticket) reduces them in a fixed order,
 // optionally applies the RMS update, and re-arms the ticket.
@@ -145,7 +65,7 @@ __global__ void __launch_bounds__(PBE_THREADS)
 pbe_finish_kernel(const float* __restrict__ dist, int64_t nq, int k, int avg, int use_rms,
                   int use_clip, float clip, const float* __restrict__ m_ptr,
                   float* __restrict__ out) {
-  const int64_t i = (int64_t)blockIdx.x * PBE_THREADS + threadIdx.x;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nq) return;
   const float m = use_rms ? *m_ptr : 1.0f;
   out[i] = pbe_row(dist + i * k, k, avg, use_rms ? 1.f : 0.f, m, use_clip, clip);
@@ -184,6 +104,15 @@ __global__ void take_kth_kernel(const float* __restrict__ dist, int64_t nq, int 
                                 float* __restrict__ out) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < nq) out[i] = dist[i * k + (k - 1)];
+}
+
+// per-row finish after the fused rerank + moments kernel of the per-update chain (knn_screen.cu)
+int launch_pbe_finish(const float* dist, int64_t nq, int k, int avg, int use_rms, int use_clip,
+                      float clip, const float* m_ptr, float* out, cudaStream_t st) {
+  pbe_finish_kernel<<<(unsigned)((nq + 127) / 128), 128, 0, st>>>(dist, nq, k, avg, use_rms,
+                                                                  use_clip, clip, m_ptr, out);
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
 }
 
 static int moments_blocks(int64_t count) {

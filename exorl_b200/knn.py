@@ -79,11 +79,13 @@ def _screen_ok(nq, nb, dim, k):
     return (dim <= _lib.SCREEN_MAX_DIM and k <= _lib.SCREEN_MAX_K and nq >= 128 and nb >= 256)
 
 
-def screened_status(device=None):
-    """(undecided_rows, invalid_flag, reranked_pairs, _) of the last screened call (syncs)."""
+def screened_status(device=None, key="knn_screened"):
+    """(undecided_rows, invalid_flag, reranked_pairs, _) of the last screened call that used the
+    workspace `key` ("knn_screened": knn_topk / relabel, "apt_reward": PBE / compute_apt_reward);
+    synchronises."""
     lib = _lib.load()
     dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
-    ws, fresh = _lib.Workspace.get(dev, "knn_screened", 1024)
+    ws, fresh = _lib.Workspace.get(dev, key, 1024)
     if fresh:
         return (0, 0, 0, 0)
     out = (ctypes.c_int32 * 4)()
@@ -164,17 +166,66 @@ def _reward_from_knn(dist, k, knn_avg, knn_rms, knn_clip, rms):
     return out
 
 
-def compute_apt_reward(source, target, args, rms=None, mode="auto"):
+_MODE_ID = {"auto": 0, "exact": 1, "screened": 2}
+
+
+def compute_apt_reward(source, target, args, rms=None, mode="auto", return_knn=False):
     """APT particle-based reward of every `source` row against the `target` bank, (b1, 1).
 
     `args` exposes knn_k, knn_avg, knn_rms, knn_clip (and optionally .rms); this is the
     signature the computation had before the reference folded it into PBE.__call__
-    (utils/utils.py:289-319, where source = target = rep)."""
+    (utils/utils.py:289-319, where source = target = rep).  One C call (exb_apt_reward_f32):
+    for per-update sizes a 3-launch chain prep -> tcgen05 screen -> rerank + RMS/epilogue."""
+    if mode not in _MODES:
+        raise ValueError(f"mode must be one of {_MODES}")
     if rms is None:
         rms = getattr(args, "rms", None)
+    lib = _lib.load()
     k = int(args.knn_k)
-    dist, _ = knn_topk(source, target, k, mode=mode)
-    return _reward_from_knn(dist, k, args.knn_avg, args.knn_rms, args.knn_clip, rms)
+    knn_avg, knn_rms, knn_clip = bool(args.knn_avg), bool(args.knn_rms), float(args.knn_clip)
+    src = _as_rows(source, "source")
+    same = target is source
+    tgt = src if same else _as_rows(target, "target")
+    if src.size(1) != tgt.size(1):
+        raise RuntimeError(f"feature sizes differ: {src.size(1)} vs {tgt.size(1)}")
+    if src.device != tgt.device:
+        raise RuntimeError("source and target must be on the same device")
+    nq, nb, dim = src.size(0), tgt.size(0), src.size(1)
+    if k > nb:
+        raise RuntimeError("selected index k out of range")
+    if k < 1 or k > _lib.MAX_K:
+        raise ValueError(f"exorl_b200: knn_k={k} outside [1, {_lib.MAX_K}]")
+    if mode == "screened" and (dim > _lib.SCREEN_MAX_DIM or k > _lib.SCREEN_MAX_K):
+        raise ValueError(f"exorl_b200: screened kNN does not support dim={dim}, k={k}")
+    dev = src.device
+    if knn_rms:
+        if rms is None:
+            raise ValueError("knn_rms=True needs an RMS state object")
+        if rms.M.numel() != 1 or not rms.M.is_cuda:
+            raise ValueError("the RMS state used by PBE must have shape (1,) on the GPU")
+    with torch.cuda.device(dev):
+        out = torch.empty(nq, 1, dtype=torch.float32, device=dev)
+        dist = torch.empty(nq, k, dtype=torch.float32, device=dev)
+        idx = torch.empty(nq, k, dtype=torch.int32, device=dev)
+        if nq == 0:
+            return (out, dist, idx) if return_knn else out
+        need = lib.exb_apt_reward_workspace_bytes(nq, nb, dim, k)
+        ws, _ = _lib.Workspace.get(dev, "apt_reward", need, zero_init=True)
+        if knn_rms:
+            new_m, new_s = torch.empty_like(rms.M), torch.empty_like(rms.S)
+            st = (_lib.ptr(rms.M), _lib.ptr(rms.S), float(rms.n), _lib.ptr(new_m),
+                  _lib.ptr(new_s))
+        else:
+            st = (None, None, 0.0, None, None)
+        _lib.check(lib.exb_apt_reward_f32(
+            _lib.ptr(src), nq, _lib.ptr(tgt), nb, dim, k, int(same), _MODE_ID[mode],
+            int(knn_avg), int(knn_rms), knn_clip, *st, _lib.ptr(out), _lib.ptr(dist),
+            _lib.ptr(idx), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+    if knn_rms:
+        # utils/utils.py:272-274: rebind M, S and advance n by the number of values seen
+        rms.M, rms.S = new_m, new_s
+        rms.n += nq * k if knn_avg else nq
+    return (out, dist, idx) if return_knn else out
 
 
 class PBE(object):

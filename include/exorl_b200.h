@@ -143,6 +143,24 @@ int exb_rms_update(const float* x, int64_t n, const float* rms_m_in, const float
                    double rms_n, float* rms_m_out, float* rms_s_out, void* workspace,
                    size_t workspace_bytes, exb_stream_t stream);
 
+/* --------------------------------------------------------------------------------------------
+ * PBE.__call__ as ONE call: replaces utils/utils.py:289-319 end to end (distance + topk, RMS
+ * update, divide by the updated mean, clip, mean over k, log(1 + r)); compute_apt_reward(source,
+ * target, args) of the north star.  mode: 0 = auto, 1 = exact fp32 kernel, 2 = screened.
+ * For the per-update sizes (a few thousand rows) the screened path is a 3-launch chain
+ * prep -> tcgen05 screen -> rerank, with the RMS/epilogue executed by the last rerank block.
+ * out_dist / out_idx [nq,k] are also produced (the neighbours the reference discards, :297).
+ * The workspace must be zeroed ONCE after allocation (it carries the epilogue's ticket word);
+ * RMS state convention as for exb_pbe_reward (caller advances n).
+ * ------------------------------------------------------------------------------------------ */
+size_t exb_apt_reward_workspace_bytes(int64_t nq, int64_t nb, int dim, int k);
+int exb_apt_reward_f32(const float* src, int64_t nq, const float* bank, int64_t nb, int dim, int k,
+                       int src_is_bank, int mode, int avg, int use_rms, float clip,
+                       const float* rms_m_in, const float* rms_s_in, double rms_n,
+                       float* rms_m_out, float* rms_s_out, float* out_reward /* [nq] */,
+                       float* out_dist /* [nq,k] */, int32_t* out_idx /* [nq,k] */,
+                       void* workspace, size_t workspace_bytes, exb_stream_t stream);
+
 /* ProtoRL reward: k-th smallest distance only, no RMS/clip/log (proto.py:115-118). */
 int exb_take_kth(const float* knn_dist, int64_t nq, int k, float* out /* [nq] */,
                  exb_stream_t stream);

@@ -278,3 +278,37 @@ def test_large_moments_path():
     st2 = RmsState()
     want2 = pbe_reward(x, x, st2, 12, False, True, 0.5)
     _close(_pbe(0.5, 12, False, True)(x.to(DEV)).cpu().numpy(), want2.numpy())
+
+
+@pytest.mark.parametrize("avg,rms_on,clip", [(True, True, 0.0), (False, True, 0.5), (True, False, 0.0),
+                                            (False, False, -1.0)])
+@pytest.mark.parametrize("b,d,k", [(1024, 512, 12), (1000, 50, 12), (640, 128, 3), (2048, 64, 16)])
+def test_fused_per_update_chain_matches_oracle(avg, rms_on, clip, b, d, k):
+    """exb_apt_reward_f32 on per-update sizes: latency screen + rerank with the RMS/epilogue fused
+    into the last rerank block; three sequential calls carry the RMS state."""
+    args = types.SimpleNamespace(knn_k=k, knn_avg=avg, knn_rms=rms_on, knn_clip=clip)
+    rms, st = xb.RMS(DEV), RmsState()
+    for call in range(3):
+        x = reps(500 + call + b, b, d)
+        want = pbe_reward(x, x, st, k, avg, rms_on, clip)
+        xd = x.to(DEV)
+        got, dist, idx = xb.compute_apt_reward(xd, xd, args, rms=rms, mode="screened",
+                                               return_knn=True)
+        _close(got.cpu().numpy(), want.numpy())
+        assert_knn_matches(x, x, k, dist, idx)
+        if rms_on:
+            _close([float(rms.M), float(rms.S)], [float(st.M), float(st.S)], rtol=2e-5)
+            assert rms.n == st.n
+    und, invalid, pairs, _ = xknn.screened_status(torch.device(DEV), key="apt_reward")
+    assert invalid == 0 and und <= 8
+
+
+def test_fused_chain_source_ne_target_and_ragged():
+    s, t = reps(1, 333, 96), reps(2, 1500, 96)
+    args = types.SimpleNamespace(knn_k=12, knn_avg=True, knn_rms=True, knn_clip=0.0)
+    st = RmsState()
+    want = pbe_reward(s, t, st, 12, True, True, 0.0)
+    rms = xb.RMS(DEV)
+    got = xb.compute_apt_reward(s.to(DEV), t.to(DEV), args, rms=rms, mode="screened")
+    _close(got.cpu().numpy(), want.numpy())
+    _close([float(rms.M), float(rms.S)], [float(st.M), float(st.S)], rtol=2e-5)
