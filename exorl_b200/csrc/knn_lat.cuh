@@ -38,6 +38,8 @@ struct LatParams {
   int* cand_idx;
   int* cand_cnt;
   float* cand_tk;    // [nq, splits] lower bound of the split's k-th best score (rerank prefilter)
+  float* cand_tr;    // [nq, splits] the split's rsel-th best pair maximum (rerank prefilter)
+  int rsel;          // ceil(k / splits)
   float* bank_max;   // [2] out: EB, HBmax (written by block (0,0) for the rerank kernel)
   long long* trace;  // optional phase timestamps (debug)
 };
@@ -267,6 +269,12 @@ knn_screen_lat_kernel(const __grid_constant__ CUtensorMap tmap_q,
       const int64_t o = row * p.splits + split;
       p.cand_cnt[o] = overflow ? -1 : st.n;
       p.cand_tk[o] = st.tk;
+      // right-aligned chain: slot KS - k holds the best, KS - k + r the (r+1)-th best
+      float tr = -FLT_MAX;
+#pragma unroll
+      for (int i = 0; i < KS; ++i)
+        if (i == KS - p.k + p.rsel - 1) tr = tv[i];
+      p.cand_tr[o] = tr;
     }
     // coalesced list output: the warp writes one row's slots (96 contiguous bytes) per step
     __syncwarp();

@@ -48,6 +48,7 @@ struct RerankParams {
   const int* cand_idx;
   const int* cand_cnt;
   const float* cand_tk;      // LAT: per-split lower bound of the k-th best score
+  const float* cand_tr;      // LAT: per-split rsel-th best pair maximum, rsel = ceil(k / splits)
   const float* ha;
   const float* ea;
   const PrepScalars* qsc;    // !LAT
@@ -258,9 +259,12 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
   // (lane sp holds split sp, splits <= 16), per-split thresholds, the row's scalars, and all list
   // slots (entry e = lane + 32 i; slots beyond a split's count are read and masked afterwards).
   const int my_cnt = (lane < splits) ? p.cand_cnt[row * splits + lane] : 0;
-  float my_tk = -FLT_MAX;
+  float my_tk = -FLT_MAX, my_tr = -FLT_MAX;
   if constexpr (LAT) {
-    if (lane < splits) my_tk = p.cand_tk[row * splits + lane];
+    if (lane < splits) {
+      my_tk = p.cand_tk[row * splits + lane];
+      my_tr = p.cand_tr[row * splits + lane];
+    }
   }
   const float ea_row = p.ea[row];
   const float ha_row = p.ha[row];
@@ -300,11 +304,23 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
     // ---- k-th best screened score over the union of splits.
     // T0 = the best per-split lower bound of the k-th best: the global k-th best is >= T0 and is
     // the k-th largest of the entries >= T0 (the split that attains T0 alone holds k of them).
+    // L1: with r = ceil(k / splits), every split holds r scores >= its r-th best, so the m-th
+    // largest of those per-split values, m = ceil(k / r), has m * r >= k scores at or above it.
     float t0 = -FLT_MAX;
     if constexpr (LAT) {
       if (lane < splits && my_cnt >= k) t0 = my_tk;
 #pragma unroll
       for (int off = 16; off > 0; off >>= 1) t0 = fmaxf(t0, __shfl_xor_sync(full, t0, off));
+      const int rsel = (k + splits - 1) / splits;
+      const int msel = (k + rsel - 1) / rsel;
+      const float mine = (lane < splits) ? my_tr : -FLT_MAX;
+      int above = 0;       // how many splits' values beat this lane's (ties broken by lane id)
+      for (int s2 = 0; s2 < splits; ++s2) {
+        const float o = __shfl_sync(full, mine, s2);
+        above += (o > mine || (o == mine && s2 < lane)) ? 1 : 0;
+      }
+      const unsigned who = __ballot_sync(full, lane < splits && above == msel - 1);
+      if (who != 0u) t0 = fmaxf(t0, __shfl_sync(full, mine, __ffs(who) - 1));
     }
     int n0 = 0;
 #pragma unroll
@@ -317,7 +333,12 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
     }
     __syncwarp();
     float kth = -FLT_MAX;
-    if (n0 <= RR_SURV) {
+    if (n0 <= 32) {
+      float xv[2] = {(lane < n0) ? -s_val[wib][lane] : FLT_MAX, FLT_MAX};
+      int xi[2] = {lane, lane};
+      bitonic_pairs_asc<32>(xv, xi, lane);     // ascending on the negated scores
+      kth = -__shfl_sync(full, xv[0], k - 1);
+    } else if (n0 <= RR_SURV) {
       // one 64-element bitonic sort instead of k dependent arg-max rounds
       float x0 = (lane < n0) ? s_val[wib][lane] : -FLT_MAX;
       float x1 = (lane + 32 < n0) ? s_val[wib][lane + 32] : -FLT_MAX;

@@ -755,6 +755,7 @@ struct ScreenWs {
   float* cand_val;
   int *cand_idx, *cand_cnt, *fb_rows;
   float* cand_tk;
+  float* cand_tr;
   double2* pbe_partials;   // fused per-update epilogue: one per rerank block
   float* fb_d2;
   int* fb_idx;
@@ -777,6 +778,7 @@ static size_t carve_screen(void* ws, int64_t nq, int64_t nb, const ScreenPlan& p
   o->cand_idx = cv.take<int>((size_t)nq * pl.splits * SCR_CAP);
   o->cand_cnt = cv.take<int>((size_t)nq * pl.splits);
   o->cand_tk = cv.take<float>((size_t)nq * pl.splits);
+  o->cand_tr = cv.take<float>((size_t)nq * pl.splits);
   o->pbe_partials = cv.take<double2>(pl.lat ? (size_t)((nq + RR_WARPS - 1) / RR_WARPS) : 1);
   o->fb_rows = cv.take<int>(pl.fb_cap);
   o->fb_d2 = cv.take<float>((size_t)pl.fb_cap * pl.fb_splits * k);
@@ -856,7 +858,7 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
   RerankParams rp;
   rp.Q = src; rp.B = bank; rp.nq = nq; rp.nb = nb; rp.dim = dim; rp.k = k; rp.idx_base = idx_base;
   rp.splits = pl.splits; rp.cand_val = w.cand_val; rp.cand_idx = w.cand_idx;
-  rp.cand_cnt = w.cand_cnt; rp.cand_tk = w.cand_tk; rp.ha = w.ha; rp.ea = w.ea; rp.qsc = same ? w.bsc : w.qsc;
+  rp.cand_cnt = w.cand_cnt; rp.cand_tk = w.cand_tk; rp.cand_tr = w.cand_tr; rp.ha = w.ha; rp.ea = w.ea; rp.qsc = same ? w.bsc : w.qsc;
   rp.bsc = w.bsc; rp.bank_max = reinterpret_cast<const float*>(w.bsc); rp.out_dist = out_dist;
   rp.out_idx = out_idx; rp.fallback_rows = w.fb_rows; rp.fallback_cap = pl.fb_cap;
   rp.status = w.status; rp.trace = trace_on ? w.trace : nullptr;
@@ -891,7 +893,8 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
     lp.ha = w.ha; lp.ea = w.ea; lp.hb = w.hb; lp.eb = w.eb; lp.nq = nq; lp.nb = nb;
     lp.nkc = pl.nkc; lp.n_tiles = pl.n_tiles; lp.tiles_per_split = pl.tiles_per_split;
     lp.splits = pl.splits; lp.k = k; lp.cand_val = w.cand_val; lp.cand_idx = w.cand_idx;
-    lp.cand_cnt = w.cand_cnt; lp.cand_tk = w.cand_tk; lp.bank_max = reinterpret_cast<float*>(w.bsc);
+    lp.cand_cnt = w.cand_cnt; lp.cand_tk = w.cand_tk; lp.cand_tr = w.cand_tr;
+    lp.rsel = (k + pl.splits - 1) / pl.splits; lp.bank_max = reinterpret_cast<float*>(w.bsc);
     lp.trace = trace_on ? w.trace : nullptr;
     dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
     const bool prof = g_prof.on && g_prof.n < 64;
