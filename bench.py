@@ -41,6 +41,8 @@ def parse():
     ap.add_argument("--cpu-queries", type=int, default=128,
                     help="queries of the bounded CPU-baseline sample (vs the full bank)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--stage-times", action="store_true",
+                    help="after the timed runs, one extra step with per-stage CUDA events (stderr)")
     return ap.parse_args()
 
 
@@ -239,6 +241,15 @@ def run_ours(a, rank, world, local_rank):
     e1.record()
     barrier()
     ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+
+    if a.stage_times:
+        from exorl_b200.relabel import StageTimer
+        tmr = StageTimer()
+        xb.relabel_apt_reward(rep, args, rms=rms, exchange=a.exchange, mode="screened", timer=tmr)
+        st = tmr.summary()
+        if rank == 0:
+            print("stage times (ms): " + json.dumps({k: round(v, 3) for k, v in st.items()}),
+                  file=sys.stderr)
 
     if rank == 0:
         sustained, burst, src = peaks()

@@ -1,0 +1,73 @@
+"""Multi-GPU parity of the sharded relabel (run under torchrun, one rank per GPU, NCCL):
+the bank-sharded result (both exchanges) must equal the single-shard result computed on rank 0's
+GPU from the same reps: identical index sets outside fp32 near-ties, rewards rel 1e-5, same RMS.
+
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
+      --master-port 29511 benchmarks/relabel_nccl_check.py [--n 20000] [--dim 512]
+"""
+import argparse
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import exorl_b200 as xb  # noqa: E402
+from exorl_b200.knn import knn_topk, _reward_from_knn  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--n", type=int, default=20000)
+    ap.add_argument("--dim", type=int, default=512)
+    ap.add_argument("--k", type=int, default=12)
+    a = ap.parse_args()
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    g = torch.Generator().manual_seed(5)
+    rep = torch.tanh(torch.randn(a.n, a.dim, generator=g)).to(dev)
+    args = types.SimpleNamespace(knn_k=a.k, knn_avg=True, knn_rms=True, knn_clip=0.0)
+
+    # single-shard truth on this rank's GPU (no collectives involved)
+    d0, i0 = knn_topk(rep, rep, a.k, mode="screened")
+    rms0 = xb.RMS(dev)
+    r0 = _reward_from_knn(d0, a.k, True, True, 0.0, rms0)
+
+    ok = True
+    for exchange in ("all_to_all", "all_gather"):
+        rms = xb.RMS(dev)
+        out = xb.relabel_apt_reward(rep, args, rms=rms, exchange=exchange, mode="screened",
+                                    return_knn=True)
+        r, d, i = out
+        torch.cuda.synchronize()
+        np.testing.assert_allclose(r.cpu().numpy(), r0.cpu().numpy(), rtol=1e-5, atol=1e-7)
+        assert abs(float(rms.M) - float(rms0.M)) <= 1e-6 * abs(float(rms0.M))
+        assert rms.n == rms0.n
+        if exchange == "all_gather":            # every rank holds all rows
+            lo, hi = 0, a.n
+        else:                                    # rank r finalised query block r
+            from exorl_b200.relabel import shard_bounds
+            lo, hi = shard_bounds(a.n, world, rank)
+        np.testing.assert_allclose(d.cpu().numpy(), d0[lo:hi].cpu().numpy(), rtol=1e-6)
+        same = (i.sort(dim=1).values == i0[lo:hi].sort(dim=1).values).all(dim=1)
+        bad = int((~same).sum())
+        assert bad <= max(1, (hi - lo) // 1000), f"{bad} rows differ"   # fp32 near-ties only
+        # identical on every rank
+        chk = r.double().sum().reshape(1)
+        lst = [torch.empty_like(chk) for _ in range(world)]
+        dist.all_gather(lst, chk)
+        assert all(float(x) == float(lst[0]) for x in lst), "ranks disagree"
+        if rank == 0:
+            print(f"[nccl check] world={world} n={a.n} exchange={exchange}: OK "
+                  f"(rows with near-tie swaps: {bad})", flush=True)
+    dist.destroy_process_group()
+    return 0 if ok else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -90,8 +90,27 @@ class _CudaStages:
         return _reward_from_knn(knn_dist, k, avg, use_rms, clip, rms)
 
 
+class StageTimer:
+    """Optional CUDA-event stopwatch for the relabel stages (bench.py --stage-times)."""
+
+    def __init__(self):
+        self.marks = []
+
+    def mark(self, name):
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        self.marks.append((name, e))
+
+    def summary(self):
+        torch.cuda.synchronize()
+        out = {}
+        for (_, a), (name, b) in zip(self.marks[:-1], self.marks[1:]):
+            out[name] = out.get(name, 0.0) + a.elapsed_time(b)
+        return out
+
+
 def relabel_apt_reward(rep, args, rms=None, group=None, exchange="all_to_all", mode="auto",
-                       return_knn=False, stages=_CudaStages):
+                       return_knn=False, stages=_CudaStages, timer=None):
     """APT reward (N, 1) of every row of `rep` against all N rows, identical on every rank.
 
     `args` exposes knn_k, knn_avg, knn_rms, knn_clip like PBE; `rms` is the running-moment state
@@ -110,7 +129,10 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="all_to_all", m
     if hi - lo < k:
         raise RuntimeError("selected index k out of range")   # a shard smaller than k rows
 
+    tm = timer.mark if timer is not None else (lambda name: None)
+    tm("start")
     d_loc, i_loc = stages.local_knn(rep, lo, hi, k, mode)      # (N, k) exact, global ids
+    tm("local_knn")
     if world == 1:
         reward = stages.reward(d_loc, k, avg, use_rms, clip, rms)
         return (reward, d_loc, i_loc) if return_knn else reward
@@ -132,12 +154,16 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="all_to_all", m
     i_blk = torch.empty((world * my_n, k), dtype=i_loc.dtype, device=i_loc.device)
     dist.all_to_all_single(d_blk, d_loc.contiguous(), [my_n] * world, in_split, group=group)
     dist.all_to_all_single(i_blk, i_loc.contiguous(), [my_n] * world, in_split, group=group)
+    tm("all_to_all")
     d_mine, i_mine = stages.merge(d_blk.view(world, my_n, k), i_blk.view(world, my_n, k), k)
+    tm("merge")
     sums = None
     if use_rms:
         sums = stages.sums(d_mine, k, avg)                      # {count, sum, sumsq} of my block
         dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
+    tm("rms_allreduce")
     r_mine = stages.finish(d_mine, k, avg, use_rms, clip, sums, rms)
+    tm("finish")
     if use_rms:
         rms.n += n * k if avg else n
     # variable block sizes: gather padded to the largest block
@@ -147,6 +173,7 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="all_to_all", m
     gathered = torch.empty((world * mx, 1), dtype=r_mine.dtype, device=r_mine.device)
     dist.all_gather_into_tensor(gathered, pad, group=group)
     reward = torch.cat([gathered[r * mx:r * mx + in_split[r]] for r in range(world)], dim=0)
+    tm("reward_allgather")
     if return_knn:
         return reward, d_mine, i_mine
     return reward
