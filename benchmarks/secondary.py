@@ -31,13 +31,17 @@ except Exception:
 
 
 def time_gpu(fn, iters=50, warm=10, flush=True):
+    # L2 flush = write 256 MB, then read another 256 MB so that the lines left in L2 are clean
+    # (otherwise the timed kernel pays the write-back of the flush's own dirty lines)
     scratch = torch.empty(256 << 20, dtype=torch.uint8, device=DEV) if flush else None
+    scratch2 = torch.zeros(64 << 20, dtype=torch.int32, device=DEV) if flush else None
     for _ in range(warm):
         fn()
     ts = []
     for _ in range(iters):
         if flush:
             scratch.zero_()
+            scratch2.max()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         fn()
@@ -125,8 +129,13 @@ def c3():
 
     def draw_and_gather():
         call[0] += 1
-        return buf.gather(buf.draw_rows_philox(1024, 7, call[0]))
+        return buf.sample_philox(1024, 7, call[0])
     med, best = time_gpu(draw_and_gather)
+
+    def draw_then_gather():
+        call[0] += 1
+        return buf.gather(buf.draw_rows_philox(1024, 7, call[0]))
+    med2, best2 = time_gpu(draw_then_gather)
     rows = buf.draw_rows_philox(1024, 7, 0)
     gmed, gbest = time_gpu(lambda: buf.gather(rows))
     # CPU port: the reference's per-sample arithmetic (python loop) for one 1024-batch
@@ -135,7 +144,8 @@ def c3():
             nstep_transition(eps[s % 8], 1 + (s * 37) % (L - 3), 3, 0.99)
     cpu_us = time_cpu(cpu_batch, iters=3, warm=1)
     emit(case="C3 walker-state gather B=1024 nstep=3 (1M-transition buffer)",
-         draw_plus_gather_us_median=med, draw_plus_gather_us_min=best, gather_only_us_median=gmed,
+         sample_us_median=med, sample_us_min=best, two_launch_draw_gather_us_median=med2,
+         two_launch_draw_gather_us_min=best2, gather_only_us_median=gmed,
          gather_only_us_min=gbest, algorithmic_bytes=464 * 1024, cpu_us_median=cpu_us, cpu_cores=1,
          note="latency-bound (475 KB per batch); CPU = reference per-sample python arithmetic")
 
@@ -166,7 +176,7 @@ def c4(n_trans):
 
         def draw_and_gather():
             call[0] += 1
-            return buf.gather(buf.draw_rows_philox(batch, 11, call[0]))
+            return buf.sample_philox(batch, 11, call[0])
         med, best = time_gpu(draw_and_gather, iters=30, warm=5, flush=True)
         alg = (2 * obs_bytes + 24 + 3 * 8 + 2 * obs_bytes + 24 + 8) * batch
         emit(case=f"C4 pixel gather B={batch} nstep=3 from {n_trans} uint8(9,84,84) transitions",
@@ -174,7 +184,7 @@ def c4(n_trans):
              achieved_gbs=alg / (med * 1e-6) / 1e9, hbm_peak_gbs=HBM_GBS,
              frac_of_hbm_peak=alg / (med * 1e-6) / 1e9 / HBM_GBS,
              buffer_gb=n_eps * (L + 1) * obs_bytes / 1e9,
-             note="fresh random rows every iteration from a 63.6 GB buffer; a 256 MB L2 flush runs "
+             note="one launch (fused draw + gather); fresh random rows every iteration; a 256 MB L2 flush runs "
                   "before every timed iteration (it also lets the host run ahead, so the figure "
                   "is device time, not python launch overhead)")
     # correctness spot check against the oracle on the last batch

@@ -11,7 +11,7 @@ LIB = LIB_DIR / "libexorl_b200.so"
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-Wall,-Wno-unknown-pragmas",
-         "--expt-relaxed-constexpr"]
+         "--expt-relaxed-constexpr", *os.environ.get("EXB_EXTRA_NVCC_FLAGS", "").split()]
 
 
 def _sources():

@@ -51,6 +51,9 @@ SIGNATURES = {
     "exb_replay_gather": (_c.c_int, [_vp, _i64, _c.POINTER(GatherCol), _c.c_int, _vp, _vp,
                                      _c.c_int, _c.c_int, _f32, _vp, _vp, _vp]),
     "exb_replay_draw": (_c.c_int, [_u64, _u64, _vp, _vp, _i64, _c.c_int, _i64, _vp, _vp, _vp]),
+    "exb_replay_sample": (_c.c_int, [_u64, _u64, _vp, _vp, _i64, _i64, _c.POINTER(GatherCol),
+                                     _c.c_int, _vp, _vp, _c.c_int, _c.c_int, _f32, _vp, _vp, _vp,
+                                     _vp]),
 }
 
 EXB_OK, EXB_EINVAL, EXB_EKRANGE, EXB_EUNSUPPORTED, EXB_ECUDA, EXB_EFALLBACK = range(6)

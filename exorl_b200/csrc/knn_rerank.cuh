@@ -281,11 +281,12 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
       ei[i] = p.cand_idx[row * splits * SCR_CAP + e];
     }
   }
-  if (__any_sync(full, my_cnt < 0)) undecided = true;
+  int why = undecided ? 4 : 0;           // debug only (trace[12..15] of an undecided row)
+  if (__any_sync(full, my_cnt < 0)) { undecided = true; why |= 1; }
   int total = max(my_cnt, 0);
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) total += __shfl_xor_sync(full, total, off);
-  if (total < k) undecided = true;
+  if (total < k) { undecided = true; why |= 2; }
 #pragma unroll
   for (int i = 0; i < RR_PER_LANE; ++i) {
     const int e = lane + 32 * i;
@@ -381,8 +382,14 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
       if (keep && pos < RR_SURV) s_surv[wib][pos] = ei[i];
       n_surv += __popc(m);
     }
-    if (n_surv > RR_SURV) undecided = true;
+    if (n_surv > RR_SURV) { undecided = true; why |= 8; }
     __syncwarp();
+  }
+  if (!LAT && undecided && p.trace != nullptr && lane == 0) {
+    p.trace[12] = row;
+    p.trace[13] = why;
+    p.trace[14] = total;
+    p.trace[15] = n_surv;
   }
   if (tr && lane == 0) p.trace[10] = clock_now();
 

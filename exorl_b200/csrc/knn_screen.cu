@@ -16,13 +16,22 @@
 // exact kernel.  The survivors' distances are then recomputed in fp32 direct-difference form,
 // so the returned distances/indices are those of the exact path.
 //
-// Kernel structure (one CTA per 128 query rows x a range of 256-row bank tiles):
+// Kernel structure (one CTA per 128 query rows x a range of 256-row bank tiles; CTA pairs with
+// cta_group::2 share each bank tile):
 //   warp 0      TMA producer: query tile once (resident in smem), bank tiles through a ring
-//   warp 1      TMEM allocator + single-thread tcgen05.mma issuer (M=128, N=256, K=16)
-//   warps 2-5   epilogue: tcgen05.ld 32 columns at a time (thread = TMEM lane = query row),
-//               subtract hb, compare with tkeep; inserts are rare and go to a per-thread
-//               sorted list in shared memory
+//   warp 1      TMEM allocator + single-thread tcgen05.mma issuer (M=128|256, N=256, K=16)
+//   warps 2-5   epilogue (FILT 1, 2): tcgen05.ld 32 columns at a time (thread = TMEM lane =
+//   (2-9)       query row), subtract hb, compare with tkeep; hits are rare and handled by a
+//               per-thread loop (k-th-best chain in registers, candidate list in shared memory).
+//               FILT 3 runs eight epilogue warps — two trackers per row, one per 128-column half
+//               of the tile, lists in global memory — for scans short enough that hit handling,
+//               not the tensor pipe, would otherwise set the pace.
 //   two 256-column TMEM accumulators so the MMA of tile t+1 overlaps the filter of tile t.
+// Scan order: every CTA walks its tile range cyclically, starting where the CTAs already running
+// are (a shared stream head in global memory), so the co-resident CTAs pull the same window of
+// the bank through L2: DRAM reads fell from 146 GB to 37 GB per 1M x 500k launch (L2 hit 90 ->
+// 98 %), which under the 1 kW power cap is clock, not just bandwidth.  The first few tiles are
+// scored twice (FILT 2, 3): once only to seed the k-th-best chain from their group maxima.
 #include "common.cuh"
 #include "tc_ptx.cuh"
 #include <cuda.h>
@@ -47,7 +56,15 @@ constexpr int SCR_N = 256;          // bank rows per tile (UMMA N)
 constexpr int SCR_KC = 64;          // fp16 elements per K chunk = one 128-byte swizzle row
 constexpr int SCR_CAP = 24;         // list slots per (row, split)
 constexpr int SCR_MAX_K = 16;       // k supported by the screened path
+// Cycle-counter instrumentation of the streaming kernel (exb_debug_trace_sync) costs registers in
+// the hot loop, so it is compiled in only for diagnostic builds:
+//   EXB_EXTRA_NVCC_FLAGS=-DEXB_SCREEN_STATS=1 python -m exorl_b200._build --force
+#ifndef EXB_SCREEN_STATS
+#define EXB_SCREEN_STATS 0
+#endif
 constexpr int SCR_THREADS = 192;
+constexpr int SCR_THREADS_V3 = 320;
+constexpr int SCR_SCAN_CAP = 64;      // FILT 3: in-scan scratch list slots per tracker (global memory)   // FILT 3: TMA warp, MMA warp, eight epilogue warps
 constexpr int SCR_A_CHUNK_BYTES = SCR_M * SCR_KC * 2;   // 16 KB
 constexpr int SCR_B_STAGE_BYTES = SCR_N * SCR_KC * 2;   // 32 KB
 constexpr int SCR_MAX_STAGES = 8;
@@ -169,6 +186,14 @@ struct ScreenParams {
   float* cand_val;        // [nq, splits, CAP] screened scores s = a^.b^ - hb
   int* cand_idx;          // [nq, splits, CAP]
   int* cand_cnt;          // [nq, splits]; -1 = undecided
+  long long* stats;       // debug (EXB_SCREEN_TRACE): 8 accumulated cycle counters, else null
+  int lists;              // candidate lists per query row = splits x trackers per (row, split)
+  int seed_tiles;         // FILT 3: tiles scored twice — first only to seed the k-th-best chain
+  int scan_cap;           // FILT 3: slots of the in-scan scratch list per tracker
+  float* scan_val;        // FILT 3: [nq, lists, scan_cap] scratch lists (global)
+  int* scan_idx;
+  int* head;              // [splits] shared stream head (virtual tile position), zeroed per call;
+                          // null = every CTA scans its tile range from the first tile
 };
 
 // Per-row candidate state of one epilogue thread.  The k best scores seen so far are kept sorted
@@ -188,8 +213,10 @@ struct ListState {
 };
 
 __device__ __forceinline__ float keep_threshold(const ListState& s) {
-  // DESIGN.md §4; evaluated conservatively (round the kept region outwards)
-  const float dk = sqrtf(fmaxf(2.f * (s.ha - s.tk), 0.f) + 2.f * s.dl);
+  // DESIGN.md §4; evaluated conservatively (round the kept region outwards).  sqrt(x) as
+  // x * rsqrt(x) (2 ulp) inflated by 1e-6: a hit pays for this on its critical path.
+  const float x = fmaxf(2.f * (s.ha - s.tk), 0.f) + 2.f * s.dl + 1e-30f;
+  const float dk = x * rsqrtf(x) * 1.000001f;
   const float bound = dk + s.e2;
   float t = s.ha - 0.5f * bound * bound - s.dl;
   t -= 4e-6f * (fabsf(s.ha) + fabsf(s.tk));
@@ -212,14 +239,15 @@ __device__ __forceinline__ void list_compact(ListState& s, float* bv, int* bi) {
   s.n = w;
 }
 
-// Push one score through the sorted register chain (branch-free).
+// Insert one score into the sorted (descending) register chain, branch-free and with every slot
+// independent of the others: tv'[i] = max(tv[i], min(tv[i-1], x)) — x lands where it belongs,
+// smaller entries shift down one slot, the old last entry falls off.  (Depth 2 instead of a
+// 2*16-deep dependent min/max chain: an epilogue warp runs alone on its scheduler, so dependent
+// latency, not issue slots, is what a hit costs.)
 __device__ __forceinline__ void chain_push(ListState& s, float x) {
 #pragma unroll
-  for (int i = 0; i < SCR_MAX_K; ++i) {
-    const float hi = fmaxf(s.tv[i], x);
-    x = fminf(s.tv[i], x);
-    s.tv[i] = hi;
-  }
+  for (int i = SCR_MAX_K - 1; i > 0; --i) s.tv[i] = fmaxf(s.tv[i], fminf(s.tv[i - 1], x));
+  s.tv[0] = fmaxf(s.tv[0], x);
 }
 
 __device__ __forceinline__ void refresh_threshold(ListState& s) {
@@ -293,7 +321,7 @@ __device__ __forceinline__ void filter_chunk(ListState& st, const uint32_t (&r)[
 // the warp are revisited one by one with uniform control flow and inserted individually; every
 // inserted score also goes through the chain, so tk is the exact k-th best of what was kept.
 __device__ __forceinline__ void list_insert(ListState& s, float* bv, int* bi, float v, int j,
-                                            int k) {
+                                            int k, bool push = true) {
   // precondition: v >= s.tkeep
   if (s.n == SCR_CAP) list_compact(s, bv, bi);
   if (s.n < SCR_CAP) {
@@ -317,47 +345,189 @@ __device__ __forceinline__ void list_insert(ListState& s, float* bv, int* bi, fl
       s.dropped = fmaxf(s.dropped, v);
     }
   }
-  if (v > s.tk) {            // enters the k best: push through the sorted register chain
+  if (push && v > s.tk) {    // enters the k best: push through the sorted register chain
     chain_push(s, v);
     refresh_threshold(s);
   }
 }
 
-// Filter one 32-column chunk of the accumulator held in registers (thread = query row).
-__device__ __forceinline__ void filter_chunk_visit(ListState& st, const uint32_t (&r)[32], int ch,
-                                             const float* hn, float* lv, int* li, uint32_t t_row,
-                                             int t, int k) {
+// Select the 4 accumulators of column group q (runtime) without dynamic register indexing.
+__device__ __forceinline__ void select_group(const uint32_t (&r)[32], int q, uint32_t (&o)[4]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint32_t a0 = (q & 1) ? r[4 + i] : r[i], a1 = (q & 1) ? r[12 + i] : r[8 + i];
+    const uint32_t a2 = (q & 1) ? r[20 + i] : r[16 + i], a3 = (q & 1) ? r[28 + i] : r[24 + i];
+    const uint32_t b0 = (q & 2) ? a1 : a0, b1 = (q & 2) ? a3 : a2;
+    o[i] = (q & 4) ? b1 : b0;
+  }
+}
+
+// Per-thread hit loop: every thread walks ITS OWN hit groups (4 columns each, found from the
+// group maxima the fast path already has) and inserts from its registers, so a warp pays
+// max-over-rows (not sum-over-rows) insertions per chunk and no TMEM re-read.  `push` = false on
+// the first tile after a seed pass (its group maxima are already in the chain; pushing them again
+// would count a bank row twice).
+__device__ __forceinline__ void filter_chunk_bits(ListState& st, const uint32_t (&r)[32], int ch,
+                                                  const float* hn, float* lv, int* li, int t,
+                                                  int k, bool push, long long* slow = nullptr) {
   const float4* hn4 = reinterpret_cast<const float4*>(hn + ch * 32);
-  float m = -INFINITY;
+  float g[8];
 #pragma unroll
   for (int q = 0; q < 8; ++q) {
     const float4 h = hn4[q];
-    m = fmaxf(m, fmaxf(fmaxf(__uint_as_float(r[4 * q]) - h.x, __uint_as_float(r[4 * q + 1]) - h.y),
-                       fmaxf(__uint_as_float(r[4 * q + 2]) - h.z,
-                             __uint_as_float(r[4 * q + 3]) - h.w)));
+    g[q] = fmaxf(fmaxf(__uint_as_float(r[4 * q]) - h.x, __uint_as_float(r[4 * q + 1]) - h.y),
+                 fmaxf(__uint_as_float(r[4 * q + 2]) - h.z, __uint_as_float(r[4 * q + 3]) - h.w));
   }
+  const float m = fmaxf(fmaxf(fmaxf(g[0], g[1]), fmaxf(g[2], g[3])),
+                        fmaxf(fmaxf(g[4], g[5]), fmaxf(g[6], g[7])));
   if (__any_sync(0xffffffffu, m >= st.tkeep)) {
-    // slow path: union of hit columns over the warp, revisited with uniform control flow
-    uint32_t mask = 0;
+    const long long c0 = slow ? clock64() : 0;
+    uint32_t gm = 0;
 #pragma unroll
-    for (int c = 0; c < 32; ++c)
-      mask |= ((__uint_as_float(r[c]) - hn[ch * 32 + c]) >= st.tkeep ? 1u : 0u) << c;
-    uint32_t wm = __reduce_or_sync(0xffffffffu, mask);
-    while (wm) {
-      const int c = __ffs(wm) - 1;
-      wm &= wm - 1;
-      const float acc = __uint_as_float(tmem_ld1(t_row + ch * 32 + c));
-      tmem_ld_wait();
-      const float s = acc - hn[ch * 32 + c];
-      if (s >= st.tkeep) list_insert(st, lv, li, s, t * SCR_N + ch * 32 + c, k);
+    for (int q = 0; q < 8; ++q) gm |= (g[q] >= st.tkeep ? 1u : 0u) << q;
+    while (gm) {
+      const int q = __ffs(gm) - 1;
+      gm &= gm - 1;
+      uint32_t u[4];
+      select_group(r, q, u);
+      const float4 h = hn4[q];
+      const float sv[4] = {__uint_as_float(u[0]) - h.x, __uint_as_float(u[1]) - h.y,
+                           __uint_as_float(u[2]) - h.z, __uint_as_float(u[3]) - h.w};
+      const int col = t * SCR_N + ch * 32 + 4 * q;
+      uint32_t hm = 0;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) hm |= (sv[i] >= st.tkeep ? 1u : 0u) << i;
+      // one (non-unrolled) insertion site: the slow path must stay small in the instruction cache
+#pragma unroll 1
+      while (hm) {
+        const int i = __ffs(hm) - 1;
+        hm &= hm - 1;
+        const float lo = (i & 1) ? sv[1] : sv[0], hi = (i & 1) ? sv[3] : sv[2];
+        const float v = (i & 2) ? hi : lo;
+        if (v >= st.tkeep) list_insert(st, lv, li, v, col + i, k, push);
+      }
+    }
+    __syncwarp();
+    if (slow) {
+      slow[0] += 1;
+      slow[1] += clock64() - c0;
     }
   }
 }
 
-// SEED = true: latency mode (each CTA sees only a few bank tiles, the list fill phase dominates):
-// seed pass on the first tile + inline appends.  SEED = false: long scans, visit-based inserts.
-template <int CG, bool SEED>
-__global__ void __launch_bounds__(SCR_THREADS, 1)
+// ---- FILT 3: candidate lists live in GLOBAL memory (the row's final [CAP] slots of cand_val /
+// cand_idx), which frees the shared memory for eight epilogue warps.  Appends are two stores;
+// when the CAP slots are full the whole list makes one register round trip: entries below the
+// risen tkeep are dropped, and if it is still full the smallest entry is evicted (remembered in
+// `dropped`, judged against the final tkeep like everywhere else).
+// Compact `n` (score, index) entries of a global list: entries below tkeep are dropped, the rest
+// written to dst (in place when dst == src: writes trail the reads), at most cap_dst of them.
+// 16 loads in flight per round trip.  Returns the number of live entries found.
+__device__ __forceinline__ int list_compact_g(const float* sv, const int* si, int n, float tkeep,
+                                              float* dv, int* di, int cap_dst) {
+  int w = 0;
+  for (int base = 0; base < n; base += 16) {
+    float v[16];
+    int j[16];
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+      const bool ok = base + r < n;
+      v[r] = ok ? sv[base + r] : -FLT_MAX;
+      j[r] = ok ? si[base + r] : 0;
+    }
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+      if (base + r < n && v[r] >= tkeep) {
+        if (w < cap_dst) {
+          dv[w] = v[r];
+          di[w] = j[r];
+        }
+        ++w;
+      }
+    }
+  }
+  return w;
+}
+
+__device__ __forceinline__ void list_insert_g(ListState& s, float* gv, int* gi, int cap, float v,
+                                              int j, bool push, long long* slow = nullptr) {
+  // precondition: v >= s.tkeep
+  const long long c0 = slow ? clock64() : 0;
+  if (s.n == cap) {
+    if (slow) slow[4] += 1;
+    s.n = min(list_compact_g(gv, gi, cap, s.tkeep, gv, gi, cap), cap);
+  }
+  if (s.n < cap) {
+    gv[s.n] = v;
+    gi[s.n] = j;
+    ++s.n;
+  } else {
+    s.dropped = fmaxf(s.dropped, v);   // every slot still live: judged against the final tkeep
+  }
+  const long long c1 = slow ? clock64() : 0;
+  if (push && v > s.tk) {
+    chain_push(s, v);
+    refresh_threshold(s);
+  }
+  if (slow) {
+    slow[2] += 1;
+    slow[3] += c1 - c0;
+    slow[5] += clock64() - c1;
+  }
+}
+
+// One 32-column chunk of a tracker (thread = query row, columns of this warp's half tile).
+__device__ __forceinline__ void filter_chunk_g(ListState& st, const uint32_t (&r)[32],
+                                               const float* hn_chunk, float* gv, int* gi, int cap,
+                                               int col0, bool push, long long* slow) {
+  const float4* hn4 = reinterpret_cast<const float4*>(hn_chunk);
+  float g[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    const float4 h = hn4[q];
+    g[q] = fmaxf(fmaxf(__uint_as_float(r[4 * q]) - h.x, __uint_as_float(r[4 * q + 1]) - h.y),
+                 fmaxf(__uint_as_float(r[4 * q + 2]) - h.z, __uint_as_float(r[4 * q + 3]) - h.w));
+  }
+  const float m = fmaxf(fmaxf(fmaxf(g[0], g[1]), fmaxf(g[2], g[3])),
+                        fmaxf(fmaxf(g[4], g[5]), fmaxf(g[6], g[7])));
+  if (__any_sync(0xffffffffu, m >= st.tkeep)) {
+    const long long c0 = slow ? clock64() : 0;
+    uint32_t gm = 0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) gm |= (g[q] >= st.tkeep ? 1u : 0u) << q;
+    while (gm) {
+      const int q = __ffs(gm) - 1;
+      gm &= gm - 1;
+      uint32_t u[4];
+      select_group(r, q, u);
+      const float4 h = hn4[q];
+      const float sv[4] = {__uint_as_float(u[0]) - h.x, __uint_as_float(u[1]) - h.y,
+                           __uint_as_float(u[2]) - h.z, __uint_as_float(u[3]) - h.w};
+      uint32_t hm = 0;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) hm |= (sv[i] >= st.tkeep ? 1u : 0u) << i;
+#pragma unroll 1
+      while (hm) {
+        const int i = __ffs(hm) - 1;
+        hm &= hm - 1;
+        const float lo = (i & 1) ? sv[1] : sv[0], hi = (i & 1) ? sv[3] : sv[2];
+        const float v = (i & 2) ? hi : lo;
+        if (v >= st.tkeep) list_insert_g(st, gv, gi, cap, v, col0 + 4 * q + i, push, slow);
+      }
+    }
+    __syncwarp();
+    if (slow) {
+      slow[0] += 1;
+      slow[1] += clock64() - c0;
+    }
+  }
+}
+
+// FILT 1: seed + inline appends (short scans); 2: sample-tile seed + per-thread hit loop;
+// 3: as 2 with EIGHT epilogue warps — two trackers per query row, one per 128-column half of
+// the bank tile, lists in global memory, no barrier between the epilogue warps.
+template <int CG, int FILT>
+__global__ void __launch_bounds__(FILT == 3 ? SCR_THREADS_V3 : SCR_THREADS, 1)
 knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
                   const __grid_constant__ CUtensorMap tmap_b, const ScreenParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -372,10 +542,11 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
   const int nkc = p.nkc, stages = p.stages;
   const uint32_t a_off = 0;
   const uint32_t b_off = a_off + (uint32_t)nkc * SCR_A_CHUNK_BYTES;
+  constexpr bool V3 = FILT == 3;
   const uint32_t lv_off = b_off + (uint32_t)stages * B_STAGE;
-  const uint32_t li_off = lv_off + SCR_CAP * SCR_M * 4;
-  const uint32_t hn_off = li_off + SCR_CAP * SCR_M * 4;
-  const uint32_t bar_off = hn_off + 2 * SCR_N * 4;
+  const uint32_t li_off = lv_off + (V3 ? 0 : SCR_CAP * SCR_M * 4);
+  const uint32_t hn_off = li_off + (V3 ? 0 : SCR_CAP * SCR_M * 4);
+  const uint32_t bar_off = hn_off + (V3 ? 8 * (SCR_N / 2) * 4 : 2 * SCR_N * 4);
   float* s_lv = reinterpret_cast<float*>(sm + lv_off);
   int* s_li = reinterpret_cast<int*>(sm + li_off);
   float* s_hn = reinterpret_cast<float*>(sm + hn_off);
@@ -388,6 +559,7 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
   auto bar_tfull = [&](int s) { return bar_base + 8u * (2 * SCR_MAX_STAGES + 1 + s); };
   auto bar_tempty = [&](int s) { return bar_base + 8u * (2 * SCR_MAX_STAGES + 3 + s); };
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 2 * SCR_MAX_STAGES + 5);
+  uint32_t* s_start = s_tmem + 1;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m_tile = blockIdx.x, split = blockIdx.y;
@@ -405,9 +577,14 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
     mbar_init(bar_a, 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_tfull(s), 1);
-      mbar_init(bar_tempty(s), 4 * CG);
+      mbar_init(bar_tempty(s), (V3 ? 8 : 4) * CG);
     }
     fence_barrier_init();
+    // Shared stream head: CTAs that start later join the bank scan where the running CTAs are
+    // (cyclic tile order), so that all co-resident CTAs stream the same window of the bank
+    // through L2 instead of each pulling its own copy from HBM.
+    *s_start = (p.head != nullptr && leader)
+                   ? (uint32_t)*reinterpret_cast<volatile int*>(p.head + split) : 0u;
   }
   if (warp == 1) {
     if constexpr (CG == 2) tmem_alloc_512_pair(smem_u32(s_tmem));
@@ -418,6 +595,20 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
   if constexpr (CG == 2) cluster_sync_all();   // peer barriers initialised before any remote signal
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
+  uint32_t start_v = *s_start;
+  if constexpr (CG == 2) {
+    if (!leader) start_v = ld_cluster_u32(smem_u32(s_start), 0);   // the pair scans in step
+  }
+  const int start = n_local > 0 ? (int)(start_v % (uint32_t)n_local) : 0;
+  auto tile_of = [&](int j) {   // j-th tile of this CTA's scan
+    int tt = start + j;
+    if (tt >= n_local) tt -= n_local;
+    return t_begin + tt;
+  };
+  // FILT 3: the first n_seed tiles are scored twice (seed phase, then again in the main phase)
+  const int n_seed = (FILT >= 2) ? min(p.seed_tiles, n_local) : 0;
+  const int n_total = n_local + n_seed;
+  auto tile_seq = [&](int jj) { return tile_of(jj < n_seed ? jj : jj - n_seed); };
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -435,7 +626,10 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
       }
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = t_begin; t < t_end; ++t) {
+      for (int j = 0; j < n_total; ++j) {
+        const int t = tile_seq(j);
+        if (p.head != nullptr && leader && (j & 7) == 7 && j >= n_seed)
+          atomicMax(p.head + split, (int)(start_v + (uint32_t)(j - n_seed)));
         const int brow = t * SCR_N + (int)cta_rank * B_ROWS;
         for (int kc = 0; kc < nkc; ++kc) {
           // pull this CTA's share of a later tile into L2 so the ring only sees L2 latency
@@ -460,13 +654,19 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
       tc_fence_after();
       int stage = 0;
       uint32_t phase = 0;
-      for (int j = 0; j < n_local; ++j) {
+      long long w_empty = 0, w_full = 0;
+      const long long m0 = (EXB_SCREEN_STATS && p.stats) ? clock64() : 0;
+      for (int j = 0; j < n_total; ++j) {
         const int as = j & 1;
+        const long long c0 = (EXB_SCREEN_STATS && p.stats) ? clock64() : 0;
         mbar_wait(bar_tempty(as), (((uint32_t)j >> 1) & 1u) ^ 1u);
+        if (EXB_SCREEN_STATS && p.stats) w_empty += clock64() - c0;
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)as * SCR_N;
         for (int kc = 0; kc < nkc; ++kc) {
+          const long long c1 = (EXB_SCREEN_STATS && p.stats) ? clock64() : 0;
           mbar_wait(bar_full(stage), phase);
+          if (EXB_SCREEN_STATS && p.stats) w_full += clock64() - c1;
           tc_fence_after();
           const uint64_t adesc = make_sw128_desc(base + a_off + kc * SCR_A_CHUNK_BYTES);
           const uint64_t bdesc = make_sw128_desc(base + b_off + stage * B_STAGE);
@@ -487,6 +687,128 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
         if constexpr (CG == 2) umma_commit_pair(bar_tfull(as));
         else umma_commit(bar_tfull(as));
       }
+      if (EXB_SCREEN_STATS && p.stats) {
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + 4), (unsigned long long)w_empty);
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + 5), (unsigned long long)w_full);
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + 6),
+                  (unsigned long long)(clock64() - m0));
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + 7), 1ull);
+      }
+    }
+  } else if constexpr (V3) {
+    // ===================== epilogue, eight warps: (lane quadrant, column half) ================
+    const int quad = warp & 3;                    // TMEM lane quadrant this warp may access
+    const int half = (warp - 2) >> 2;             // columns [128 half, 128 half + 128) of a tile
+    const int e = quad * 32 + lane;               // row inside the tile
+    const int64_t row = (int64_t)m_tile * SCR_M + e;
+    const bool row_ok = row < p.nq;
+    const int64_t o = (row_ok ? row : 0) * p.lists + split * 2 + half;
+    const int cap = p.scan_cap;
+    float* gv = p.scan_val + o * SCR_SCAN_CAP;    // in-scan scratch list of this tracker
+    int* gi = p.scan_idx + o * SCR_SCAN_CAP;
+    float* hn = s_hn + (warp - 2) * (SCR_N / 2);  // this warp's private copy of its 128 half norms
+    ListState st;
+    st.n = 0;
+    st.dropped = -FLT_MAX;
+    st.tk = -FLT_MAX;
+    // padding rows past nq own no list: an unreachable threshold keeps them out of the slow path
+    st.tkeep = row_ok ? -FLT_MAX : FLT_MAX;
+#pragma unroll
+    for (int i = 0; i < SCR_MAX_K; ++i) st.tv[i] = (i < SCR_MAX_K - p.k) ? FLT_MAX : -FLT_MAX;
+    st.ha = row_ok ? p.ha[row] : 0.f;
+    const float eb_max = p.bsc->err_max, hb_max = p.bsc->hn_max;
+    st.e2 = 2.f * ((row_ok ? p.ea[row] : 0.f) + eb_max);
+    st.dl = (st.ha + hb_max) * SCR_ACC_EPS;
+
+    auto load_hn4 = [&](int t) -> float4 {
+      const int64_t c0 = (int64_t)t * SCR_N + half * (SCR_N / 2) + 4 * lane;
+      float4 h;
+      if (c0 + 3 < p.nb) {
+        h = __ldg(reinterpret_cast<const float4*>(p.hb + c0));
+      } else {
+        h.x = (c0 < p.nb) ? p.hb[c0] : INFINITY;
+        h.y = (c0 + 1 < p.nb) ? p.hb[c0 + 1] : INFINITY;
+        h.z = (c0 + 2 < p.nb) ? p.hb[c0 + 2] : INFINITY;
+        h.w = (c0 + 3 < p.nb) ? p.hb[c0 + 3] : INFINITY;
+      }
+      return h;
+    };
+    float4 hnext = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (n_total > 0) hnext = load_hn4(tile_seq(0));
+    long long e_wait = 0, e_work = 0, e_slow[6] = {0, 0, 0, 0, 0, 0};
+    long long* slow = (EXB_SCREEN_STATS && p.stats) ? e_slow : nullptr;
+    constexpr int NCH = SCR_N / 2 / 32;            // 4 chunks of 32 columns per tile and tracker
+
+    for (int jj = 0; jj < n_total; ++jj) {
+      const int t = tile_seq(jj);
+      const int as = jj & 1;
+      __syncwarp();                                // every lane is done with the previous tile's hn
+      reinterpret_cast<float4*>(hn)[lane] = hnext;
+      __syncwarp();
+      if (jj + 1 < n_total) hnext = load_hn4(tile_seq(jj + 1));
+      const long long c0 = (EXB_SCREEN_STATS && p.stats) ? clock64() : 0;
+      mbar_wait(bar_tfull(as), ((uint32_t)jj >> 1) & 1u);
+      const long long c1 = (EXB_SCREEN_STATS && p.stats) ? clock64() : 0;
+      e_wait += c1 - c0;
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)as * SCR_N +
+                             (uint32_t)half * (SCR_N / 2);
+      const int col_base = t * SCR_N + half * (SCR_N / 2);
+      uint32_t ra[32], rb[32];
+      tmem_ld32(t_row, ra);
+      if (jj < n_seed) {
+        // seed phase: group maxima of the sample tiles feed the chain only (nothing is recorded;
+        // the same tiles come round again in the main phase)
+#pragma unroll 1
+        for (int ch = 0; ch < NCH; ch += 2) {
+          tmem_ld_wait();
+          tmem_ld32(t_row + (ch + 1) * 32, rb);
+          seed_chunk(st, ra, hn + ch * 32);
+          tmem_ld_wait();
+          if (ch + 2 < NCH) tmem_ld32(t_row + (ch + 2) * 32, ra);
+          seed_chunk(st, rb, hn + (ch + 1) * 32);
+        }
+        if (jj == n_seed - 1) refresh_threshold(st);
+      } else {
+        // main phase; the sample tiles' scores are already in the chain (push them once only)
+        const bool push = jj >= 2 * n_seed;
+#pragma unroll 1
+        for (int ch = 0; ch < NCH; ch += 2) {
+          tmem_ld_wait();
+          tmem_ld32(t_row + (ch + 1) * 32, rb);
+          filter_chunk_g(st, ra, hn + ch * 32, gv, gi, cap, col_base + ch * 32, push, slow);
+          tmem_ld_wait();
+          if (ch + 2 < NCH) tmem_ld32(t_row + (ch + 2) * 32, ra);
+          filter_chunk_g(st, rb, hn + (ch + 1) * 32, gv, gi, cap, col_base + (ch + 1) * 32, push,
+                         slow);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if constexpr (CG == 2) mbar_arrive_leader(bar_tempty(as));
+        else mbar_arrive(bar_tempty(as));
+      }
+      if (EXB_SCREEN_STATS && p.stats) e_work += clock64() - c1;
+    }
+    if (EXB_SCREEN_STATS && p.stats) {
+      if (lane == 0) {
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + 0), (unsigned long long)e_wait);
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + 1), (unsigned long long)e_work);
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + 2), (unsigned long long)e_slow[0]);
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + 3), (unsigned long long)e_slow[1]);
+      }
+      // per-lane: inserts, cycles storing, repacks, cycles in chain + threshold refresh
+      for (int q = 2; q < 6; ++q)
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + 10 + q),
+                  (unsigned long long)e_slow[q]);
+    }
+    if (row_ok) {
+      // final prune: scratch list -> the row's SCR_CAP result slots, entries below the final tkeep go
+      const int w = list_compact_g(gv, gi, st.n, st.tkeep, p.cand_val + o * SCR_CAP,
+                                   p.cand_idx + o * SCR_CAP, SCR_CAP);
+      const bool overflow = w > SCR_CAP || (st.dropped > -FLT_MAX && st.dropped >= st.tkeep);
+      p.cand_cnt[o] = overflow ? -1 : w;
     }
   } else {
     // ===================== epilogue: filter accumulators =====================
@@ -515,27 +837,33 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
       h1 = (c0 + 1 < p.nb) ? p.hb[c0 + 1] : INFINITY;
     };
     float h0 = 0.f, h1 = 0.f;
-    if (n_local > 0) load_hn(t_begin, h0, h1);
+    if (n_total > 0) load_hn(tile_seq(0), h0, h1);
+    long long e_wait = 0, e_work = 0, e_slow[2] = {0, 0};
+    long long* slow = (EXB_SCREEN_STATS && p.stats) ? e_slow : nullptr;
 
-    for (int j = 0; j < n_local; ++j) {
-      const int t = t_begin + j;
-      const int as = j & 1;
+    for (int jj = 0; jj < n_total; ++jj) {
+      const int j = jj < n_seed ? jj : jj - n_seed;   // tile of the scan (sample tiles come twice)
+      const int t = tile_of(j);
+      const int as = jj & 1;
       float* hn = s_hn + as * SCR_N;
       hn[2 * et] = h0;
       hn[2 * et + 1] = h1;
       asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (j + 1 < n_local) load_hn(t + 1, h0, h1);
-      mbar_wait(bar_tfull(as), ((uint32_t)j >> 1) & 1u);
+      if (jj + 1 < n_total) load_hn(tile_seq(jj + 1), h0, h1);
+      const long long c0 = (EXB_SCREEN_STATS && p.stats) ? clock64() : 0;
+      mbar_wait(bar_tfull(as), ((uint32_t)jj >> 1) & 1u);
+      const long long c1 = (EXB_SCREEN_STATS && p.stats) ? clock64() : 0;
+      e_wait += c1 - c0;
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)as * SCR_N;
-      // Software-pipelined drain: the TMEM load of chunk c+1 is in flight while chunk c is
-      // filtered (tcgen05.wait::ld waits for every outstanding load of the thread, so the order
-      // is wait -> issue next -> process current, alternating two register buffers).
       if (p.debug != 1) {
         uint32_t ra[32], rb[32];
-        const bool first = (j == 0);
-        if (SEED && first && p.debug == 0) {
-          // seed pass over the whole first tile (the accumulator stays in TMEM for the real pass)
+        // `first`: scores of these tiles are already in the chain (seeded), do not push them again
+        const bool first = n_seed > 0 ? (jj < 2 * n_seed) : (j == 0);
+        const bool seed_now = n_seed > 0 ? (jj < n_seed) : (j == 0);
+        if (seed_now && p.debug == 0) {
+          // seed pass: group maxima -> chain only.  Without sample tiles (n_seed == 0) this is a
+          // first pass over tile 0, whose accumulator stays in TMEM for the real pass below.
           tmem_ld32(t_row, ra);
 #pragma unroll 1
           for (int ch = 0; ch < SCR_N / 32; ch += 2) {
@@ -546,8 +874,9 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
             if (ch + 2 < SCR_N / 32) tmem_ld32(t_row + (ch + 2) * 32, ra);
             seed_chunk(st, rb, hn + (ch + 1) * 32);
           }
-          refresh_threshold(st);
+          if (n_seed == 0 || jj == n_seed - 1) refresh_threshold(st);
         }
+        if (jj >= n_seed) {
         // Software-pipelined drain: the TMEM load of chunk c+1 is in flight while chunk c is
         // filtered (tcgen05.wait::ld waits for every outstanding load of the thread, so the order
         // is wait -> issue next -> process current, alternating two register buffers).
@@ -557,19 +886,20 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
           tmem_ld_wait();
           tmem_ld32(t_row + (ch + 1) * 32, rb);
           if (p.debug == 0) {
-            if constexpr (SEED)
+            if constexpr (FILT == 1)
               filter_chunk(st, ra, t * SCR_N + ch * 32, hn + ch * 32, lv, li, !first);
             else
-              filter_chunk_visit(st, ra, ch, hn, lv, li, t_row, t, p.k);
+              filter_chunk_bits(st, ra, ch, hn, lv, li, t, p.k, !first, slow);
           }
           tmem_ld_wait();
           if (ch + 2 < SCR_N / 32) tmem_ld32(t_row + (ch + 2) * 32, ra);
           if (p.debug == 0) {
-            if constexpr (SEED)
+            if constexpr (FILT == 1)
               filter_chunk(st, rb, t * SCR_N + (ch + 1) * 32, hn + (ch + 1) * 32, lv, li, !first);
             else
-              filter_chunk_visit(st, rb, ch + 1, hn, lv, li, t_row, t, p.k);
+              filter_chunk_bits(st, rb, ch + 1, hn, lv, li, t, p.k, !first, slow);
           }
+        }
         }
       }
       tc_fence_before();
@@ -578,6 +908,13 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
         if constexpr (CG == 2) mbar_arrive_leader(bar_tempty(as));
         else mbar_arrive(bar_tempty(as));
       }
+      if (EXB_SCREEN_STATS && p.stats) e_work += clock64() - c1;
+    }
+    if (EXB_SCREEN_STATS && p.stats && lane == 0) {
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + 0), (unsigned long long)e_wait);
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + 1), (unsigned long long)e_work);
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + 2), (unsigned long long)e_slow[0]);
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + 3), (unsigned long long)e_slow[1]);
     }
 
     if (row_ok) {
@@ -667,6 +1004,8 @@ struct ScreenPlan {
   bool lat; // per-update sizes: latency kernel (64-row bank tiles, everything resident, knn_lat.cuh)
   int cg;   // CTAs cooperating on one MMA (1, or 2 = cta_group::2 pair)
   int dpad, nkc, n_tiles, m_tiles, splits, tiles_per_split, stages;
+  int filt;      // streaming kernel variant (knn_screen_kernel<CG, FILT>)
+  int trackers;  // candidate lists per (row, split): 2 for FILT 3, else 1
   size_t smem;
   int fb_cap, fb_splits;
 };
@@ -701,6 +1040,8 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
       pl->tiles_per_split = (int)((nt + sp - 1) / sp);
       pl->splits = (int)((nt + pl->tiles_per_split - 1) / pl->tiles_per_split);
       pl->stages = 0;
+      pl->filt = 1;
+      pl->trackers = 1;
       pl->smem = (size_t)pl->nkc * (SCR_A_CHUNK_BYTES + LAT_B_CHUNK_BYTES) +
                  2 * (SCR_CAP + 1) * LAT_LS * 4 + 32 + 2 * LAT_N * 4 + 64 + 13 * 8 + 16 + 1024;
       return true;
@@ -722,8 +1063,26 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
   if (splits < 1) splits = 1;
   pl->tiles_per_split = (pl->n_tiles + splits - 1) / splits;
   pl->splits = (pl->n_tiles + pl->tiles_per_split - 1) / pl->tiles_per_split;
-  const size_t fixed = (size_t)pl->nkc * SCR_A_CHUNK_BYTES + 2 * SCR_CAP * SCR_M * 4 +
-                       2 * SCR_N * 4 + (2 * SCR_MAX_STAGES + 5) * 8 + 16 + 1024;
+  // variant: short scans -> 1 (the list fill phase dominates); mid-length scans (a bank shard of
+  // <= 262k rows per CTA) -> 3 (eight epilogue warps: the hit handling, which stalls the MMA on
+  // short scans, runs on twice the warps; measured 103 vs 114 ms on a 125k-row shard); long scans
+  // -> 2 (four epilogue warps: fewest instructions, the kernel is power-bound there; measured 762
+  // vs 769 ms on 1M rows).  EXB_SCREEN_FILTER=2|3 forces one of them (A/B).
+  static const int long_filt = [] {
+    const char* e = getenv("EXB_SCREEN_FILTER");
+    const int v = e ? atoi(e) : 0;
+    return (v == 2 || v == 3) ? v : 0;
+  }();
+  pl->filt = pl->tiles_per_split <= 16 ? 1
+             : long_filt ? long_filt : (pl->tiles_per_split <= 1024 ? 3 : 2);
+  if (pl->filt == 3 && pl->splits > 8) {   // the rerank gathers at most 16 lists per row
+    pl->tiles_per_split = (pl->n_tiles + 7) / 8;
+    pl->splits = (pl->n_tiles + pl->tiles_per_split - 1) / pl->tiles_per_split;
+  }
+  pl->trackers = pl->filt == 3 ? 2 : 1;
+  const size_t fixed = (size_t)pl->nkc * SCR_A_CHUNK_BYTES +
+                       (pl->filt == 3 ? 8 * (SCR_N / 2) * 4 : 2 * SCR_CAP * SCR_M * 4 + 2 * SCR_N * 4) +
+                       (2 * SCR_MAX_STAGES + 5) * 8 + 16 + 1024;
   const int b_stage = SCR_B_STAGE_BYTES / pl->cg;
   int stages = (int)((SCR_SMEM_LIMIT - fixed) / b_stage);
   if (stages > SCR_MAX_STAGES) stages = SCR_MAX_STAGES;
@@ -746,6 +1105,7 @@ static void launch_rerank(const RerankParams& rp, unsigned grid, int ni, cudaStr
 
 struct ScreenWs {
   long long* trace;   // 16 phase timestamps (debug, EXB_SCREEN_TRACE)
+  int* head;          // 16 shared stream heads (one per bank split), zeroed per call
   RerankStatus* status;
   PrepScalars* qsc;
   PrepScalars* bsc;
@@ -756,6 +1116,8 @@ struct ScreenWs {
   int *cand_idx, *cand_cnt, *fb_rows;
   float* cand_tk;
   float* cand_tr;
+  float* scan_val;    // FILT 3 scratch lists [nq, lists, SCR_SCAN_CAP]
+  int* scan_idx;
   double2* pbe_partials;   // fused per-update epilogue: one per rerank block
   float* fb_d2;
   int* fb_idx;
@@ -768,17 +1130,21 @@ static size_t carve_screen(void* ws, int64_t nq, int64_t nb, const ScreenPlan& p
   o->qsc = cv.take<PrepScalars>(1);
   o->bsc = cv.take<PrepScalars>(1);
   o->trace = cv.take<long long>(16);
+  o->head = cv.take<int>(16);
   o->b16 = cv.take<__half>((size_t)nb * pl.dpad);
   o->q16 = same ? o->b16 : cv.take<__half>((size_t)nq * pl.dpad);
   o->hb = cv.take<float>(nb);
   o->eb = cv.take<float>(nb);
   o->ha = same ? o->hb : cv.take<float>(nq);
   o->ea = same ? o->eb : cv.take<float>(nq);
-  o->cand_val = cv.take<float>((size_t)nq * pl.splits * SCR_CAP);
-  o->cand_idx = cv.take<int>((size_t)nq * pl.splits * SCR_CAP);
-  o->cand_cnt = cv.take<int>((size_t)nq * pl.splits);
-  o->cand_tk = cv.take<float>((size_t)nq * pl.splits);
-  o->cand_tr = cv.take<float>((size_t)nq * pl.splits);
+  const size_t lists = (size_t)pl.splits * pl.trackers;
+  o->cand_val = cv.take<float>((size_t)nq * lists * SCR_CAP);
+  o->cand_idx = cv.take<int>((size_t)nq * lists * SCR_CAP);
+  o->cand_cnt = cv.take<int>((size_t)nq * lists);
+  o->cand_tk = cv.take<float>((size_t)nq * lists);
+  o->cand_tr = cv.take<float>((size_t)nq * lists);
+  o->scan_val = cv.take<float>(pl.filt == 3 ? (size_t)nq * lists * SCR_SCAN_CAP : 0);
+  o->scan_idx = cv.take<int>(pl.filt == 3 ? (size_t)nq * lists * SCR_SCAN_CAP : 0);
   o->pbe_partials = cv.take<double2>(pl.lat ? (size_t)((nq + RR_WARPS - 1) / RR_WARPS) : 1);
   o->fb_rows = cv.take<int>(pl.fb_cap);
   o->fb_d2 = cv.take<float>((size_t)pl.fb_cap * pl.fb_splits * k);
@@ -857,7 +1223,7 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
   const int ni = vec ? (dim + 127) / 128 : 0;   // float4 loads per lane and row (0 = scalar path)
   RerankParams rp;
   rp.Q = src; rp.B = bank; rp.nq = nq; rp.nb = nb; rp.dim = dim; rp.k = k; rp.idx_base = idx_base;
-  rp.splits = pl.splits; rp.cand_val = w.cand_val; rp.cand_idx = w.cand_idx;
+  rp.splits = pl.splits * pl.trackers; rp.cand_val = w.cand_val; rp.cand_idx = w.cand_idx;
   rp.cand_cnt = w.cand_cnt; rp.cand_tk = w.cand_tk; rp.cand_tr = w.cand_tr; rp.ha = w.ha; rp.ea = w.ea; rp.qsc = same ? w.bsc : w.qsc;
   rp.bsc = w.bsc; rp.bank_max = reinterpret_cast<const float*>(w.bsc); rp.out_dist = out_dist;
   rp.out_idx = out_idx; rp.fallback_rows = w.fb_rows; rp.fallback_cap = pl.fb_cap;
@@ -918,8 +1284,8 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
     return EXB_OK;
   }
 
-  // header (status + scalars) is the first 3 x 256 bytes
-  EXB_CUDA(cudaMemsetAsync(workspace, 0, 768, st));
+  // header (status + scalars) is the first 3 x 256 bytes (+ the 16 debug counters when tracing)
+  EXB_CUDA(cudaMemsetAsync(workspace, 0, 1024 + 64, st));
   int rc = launch_prep(bank, nb, dim, pl.dpad, w.b16, w.hb, w.eb, w.bsc, st);
   if (rc) return rc;
   if (!same) {
@@ -935,13 +1301,17 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
 
   static bool attr_set = false;
   if (!attr_set) {
-    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<1, false>,
+    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<1, 1>,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
-    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<2, false>,
+    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<2, 1>,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
-    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<1, true>,
+    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<1, 2>,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
-    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<2, true>,
+    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<2, 2>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
+    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<1, 3>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
+    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<2, 3>,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
     attr_set = true;
   }
@@ -959,15 +1329,41 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
     return e ? atoi(e) : 0;
   }();
   sp.prefetch = pf;
+  sp.stats = trace_on ? w.trace : nullptr;
   sp.stages = pl.stages; sp.cand_val = w.cand_val; sp.cand_idx = w.cand_idx; sp.cand_cnt = w.cand_cnt;
   dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
-  const bool seed = pl.tiles_per_split <= 16;   // fill phase dominates short scans
+  sp.lists = pl.splits * pl.trackers;
+  // sample tiles that seed the k-th-best chain before the real scan (FILT 3): ~1.5 % extra MMA
+  // work buys roughly half the list insertions
+  static const int seed_env = [] {
+    const char* e = getenv("EXB_SCREEN_SEED");
+    return e ? atoi(e) : 0;
+  }();
+  int seed_tiles = seed_env != 0 ? seed_env : pl.tiles_per_split / 16;
+  if (seed_env == 0) seed_tiles = seed_tiles < 2 ? 2 : (seed_tiles > 32 ? 32 : seed_tiles);
+  if (seed_tiles < 0) seed_tiles = 0;      // EXB_SCREEN_SEED=-1: no sample tiles
+  sp.seed_tiles = pl.filt >= 2 ? seed_tiles : 0;
+  static const int scan_cap_env = [] {
+    const char* e = getenv("EXB_SCREEN_SCANCAP");   // A/B: repack period of the scratch lists
+    const int v = e ? atoi(e) : SCR_SCAN_CAP;
+    return v < 16 ? 16 : (v > SCR_SCAN_CAP ? SCR_SCAN_CAP : v);
+  }();
+  sp.scan_cap = scan_cap_env;
+  sp.scan_val = w.scan_val;
+  sp.scan_idx = w.scan_idx;
+  static const int share_head = [] {
+    const char* e = getenv("EXB_SCREEN_HEAD");   // A/B: 0 = every CTA scans from its first tile
+    return e ? atoi(e) : 1;
+  }();
+  sp.head = share_head ? w.head : nullptr;
+  const int filt = pl.filt;
+  const unsigned threads = filt == 3 ? SCR_THREADS_V3 : SCR_THREADS;
   const bool prof = g_prof.on && g_prof.n < 64;
   if (prof) EXB_CUDA(cudaEventRecord(g_prof.e0[g_prof.n], st));
   if (pl.cg == 2) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
-    cfg.blockDim = dim3(SCR_THREADS);
+    cfg.blockDim = dim3(threads);
     cfg.dynamicSmemBytes = pl.smem;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -977,11 +1373,13 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    if (seed) EXB_CUDA(cudaLaunchKernelEx(&cfg, knn_screen_kernel<2, true>, tq, tb, sp));
-    else EXB_CUDA(cudaLaunchKernelEx(&cfg, knn_screen_kernel<2, false>, tq, tb, sp));
+    if (filt == 1) EXB_CUDA(cudaLaunchKernelEx(&cfg, knn_screen_kernel<2, 1>, tq, tb, sp));
+    else if (filt == 3) EXB_CUDA(cudaLaunchKernelEx(&cfg, knn_screen_kernel<2, 3>, tq, tb, sp));
+    else EXB_CUDA(cudaLaunchKernelEx(&cfg, knn_screen_kernel<2, 2>, tq, tb, sp));
   } else {
-    if (seed) knn_screen_kernel<1, true><<<grid, SCR_THREADS, pl.smem, st>>>(tq, tb, sp);
-    else knn_screen_kernel<1, false><<<grid, SCR_THREADS, pl.smem, st>>>(tq, tb, sp);
+    if (filt == 1) knn_screen_kernel<1, 1><<<grid, SCR_THREADS, pl.smem, st>>>(tq, tb, sp);
+    else if (filt == 3) knn_screen_kernel<1, 3><<<grid, SCR_THREADS_V3, pl.smem, st>>>(tq, tb, sp);
+    else knn_screen_kernel<1, 2><<<grid, SCR_THREADS, pl.smem, st>>>(tq, tb, sp);
   }
   EXB_LAUNCH_CHECK();
   if (prof) EXB_CUDA(cudaEventRecord(g_prof.e1[g_prof.n++], st));

@@ -12,45 +12,121 @@ namespace exb {
 
 constexpr int GATHER_MAX_COLS = 8;
 constexpr int GATHER_THREADS = 256;
+constexpr int GATHER_UNROLL = 4;                                  // vectors in flight per thread
+constexpr int GATHER_PIECE_VECS = GATHER_THREADS * GATHER_UNROLL;  // vectors per long-row piece
 
-struct GatherCols {
+// Work list of one launch.  Columns are ordered long rows first; block ids are a flat prefix sum
+// over the columns (+ the reward/discount pseudo-column last), so no block is launched idle.
+//   long row  (more than 128 vectors): one block per PIECE of 1024 vectors (16 KB at 16 B/vector);
+//                                      a 63 504-B frame is 4 pieces, a 1024-batch 8192 blocks.
+//   short row: one warp per row, 8 rows per block.
+struct GatherPlan {
   exb_gather_col c[GATHER_MAX_COLS];
-  int vec[GATHER_MAX_COLS];    // bytes per vector access: 16, 8, 4 or 1
-  int group[GATHER_MAX_COLS];  // threads cooperating on one row: 32 or 256
+  int vec[GATHER_MAX_COLS];      // bytes per vector access: 16, 8, 4 or 1
+  int pieces[GATHER_MAX_COLS];   // 0 = short row (warp per row), else pieces per row
+  unsigned block_base[GATHER_MAX_COLS + 2];
   int n;
 };
 
-template <typename V>
-__device__ __forceinline__ void copy_row(const char* __restrict__ s, char* __restrict__ d,
-                                         int64_t bytes, int t, int group) {
-  const int64_t nv = bytes / (int64_t)sizeof(V);
-  const V* sv = reinterpret_cast<const V*>(s);
-  V* dv = reinterpret_cast<V*>(d);
-  int64_t i = t;
-  // 4 independent loads in flight per thread before the stores (latency hiding on long rows)
-  for (; i + 3 * (int64_t)group < nv; i += 4 * (int64_t)group) {
-    const V a = __ldg(sv + i), b = __ldg(sv + i + group), c = __ldg(sv + i + 2 * group),
-            e = __ldg(sv + i + 3 * group);
-    dv[i] = a;
-    dv[i + group] = b;
-    dv[i + 2 * group] = c;
-    dv[i + 3 * group] = e;
-  }
-  for (; i < nv; i += group) dv[i] = __ldg(sv + i);
+// Optional fused index draw (replay_draw_kernel's arithmetic, below): rows == nullptr.
+struct GatherDraw {
+  uint64_t seed, call;
+  const int64_t* eps_start;
+  const int32_t* eps_len;
+  int64_t n_episodes;
+  int nstep;
+  int64_t* out_rows;   // may be null
+};
+
+__device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+  const uint32_t hi0 = __umulhi(0xD2511F53u, c[0]), lo0 = 0xD2511F53u * c[0];
+  const uint32_t hi1 = __umulhi(0xCD9E8D57u, c[2]), lo1 = 0xCD9E8D57u * c[2];
+  const uint32_t n0 = hi1 ^ c[1] ^ k0, n2 = hi0 ^ c[3] ^ k1;
+  c[0] = n0; c[1] = lo1; c[2] = n2; c[3] = lo0;
 }
 
-// grid.y = column id (n == reward/discount pseudo-column), grid.x covers the batch.
+// Philox4x32-10, counter (sample, call_lo, call_hi, 0), key = seed.  episode ~ U{0..n_episodes-1}
+// (random.choice, utils/replay_buffer.py:168-170), idx ~ U{1..eps_len-nstep+1} (:222; nstep = 1
+// is the offline range of :90); returns the global row = episode start + idx.
+__device__ __forceinline__ int64_t draw_row(int64_t s, uint64_t seed, uint64_t call,
+                                            const int64_t* __restrict__ eps_start,
+                                            const int32_t* __restrict__ eps_len,
+                                            int64_t n_episodes, int nstep, int32_t* episode) {
+  uint32_t c[4] = {(uint32_t)s, (uint32_t)call, (uint32_t)(call >> 32), 0u};
+  uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    philox_round(c, k0, k1);
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  const int64_t ep = (int64_t)(((uint64_t)c[0] * (uint64_t)n_episodes) >> 32);
+  const uint64_t span = (uint64_t)(__ldg(eps_len + ep) - nstep + 1);
+  const int64_t idx = (int64_t)(((uint64_t)c[1] * span) >> 32) + 1;
+  if (episode) *episode = (int32_t)ep;
+  return __ldg(eps_start + ep) + idx;
+}
+
+template <typename V>
+__device__ __forceinline__ V ld_stream(const V* p) { return __ldcs(p); }
+template <>
+__device__ __forceinline__ uint8_t ld_stream<uint8_t>(const uint8_t* p) { return __ldg(p); }
+
+// One piece of a long row: GATHER_UNROLL independent vector loads per thread in flight (source
+// rows are read once: streaming / evict-first), then the stores.
+template <typename V>
+__device__ __forceinline__ void copy_piece(const char* __restrict__ s, char* __restrict__ d,
+                                           int64_t nv, int64_t v0, int t) {
+  const V* sv = reinterpret_cast<const V*>(s);
+  V* dv = reinterpret_cast<V*>(d);
+  V r[GATHER_UNROLL];
+#pragma unroll
+  for (int u = 0; u < GATHER_UNROLL; ++u) {
+    const int64_t i = v0 + t + u * GATHER_THREADS;
+    if (i < nv) r[u] = ld_stream(sv + i);
+  }
+#pragma unroll
+  for (int u = 0; u < GATHER_UNROLL; ++u) {
+    const int64_t i = v0 + t + u * GATHER_THREADS;
+    if (i < nv) dv[i] = r[u];
+  }
+}
+
+// Short row: one warp, at most 128 vectors -> at most 4 per lane, all in flight.
+template <typename V>
+__device__ __forceinline__ void copy_short(const char* __restrict__ s, char* __restrict__ d,
+                                           int nv, int lane) {
+  const V* sv = reinterpret_cast<const V*>(s);
+  V* dv = reinterpret_cast<V*>(d);
+  V r[4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u)
+    if (lane + 32 * u < nv) r[u] = __ldg(sv + lane + 32 * u);
+#pragma unroll
+  for (int u = 0; u < 4; ++u)
+    if (lane + 32 * u < nv) dv[lane + 32 * u] = r[u];
+}
+
 __global__ void __launch_bounds__(GATHER_THREADS)
-replay_gather_kernel(const int64_t* __restrict__ rows, int64_t batch, GatherCols cols,
-                     const float* __restrict__ reward_src, const float* __restrict__ discount_src,
-                     int nstep, int nstep_mode, float gamma, float* __restrict__ out_reward,
+replay_gather_kernel(const int64_t* __restrict__ rows, int64_t batch, GatherPlan plan,
+                     GatherDraw draw, const float* __restrict__ reward_src,
+                     const float* __restrict__ discount_src, int nstep, int nstep_mode,
+                     float gamma, float* __restrict__ out_reward,
                      float* __restrict__ out_discount) {
-  const int col = blockIdx.y;
-  if (col == cols.n) {
+  int col = 0;
+  while (blockIdx.x >= plan.block_base[col + 1]) ++col;
+  const unsigned local = blockIdx.x - plan.block_base[col];
+  auto row_of = [&](int64_t b) -> int64_t {
+    return rows ? rows[b]
+                : draw_row(b, draw.seed, draw.call, draw.eps_start, draw.eps_len,
+                           draw.n_episodes, draw.nstep, nullptr);
+  };
+  if (col == plan.n) {
     // utils/replay_buffer.py:229-234 — fp32, multiply then add (no fused multiply-add), in order.
-    const int64_t b = (int64_t)blockIdx.x * GATHER_THREADS + threadIdx.x;
+    const int64_t b = (int64_t)local * GATHER_THREADS + threadIdx.x;
     if (b >= batch) return;
-    const int64_t row = rows[b];
+    const int64_t row = row_of(b);
+    if (!rows && draw.out_rows) draw.out_rows[b] = row;
     float r, g;
     if (nstep_mode) {
       r = 0.f;
@@ -67,20 +143,34 @@ replay_gather_kernel(const int64_t* __restrict__ rows, int64_t batch, GatherCols
     out_discount[b] = g;
     return;
   }
-  const int group = cols.group[col];
-  const int per_block = GATHER_THREADS / group;
-  const int64_t b = (int64_t)blockIdx.x * per_block + threadIdx.x / group;
-  if (b >= batch) return;
-  const int t = threadIdx.x % group;
-  const exb_gather_col c = cols.c[col];
-  const int64_t srow = rows[b] + c.row_offset;
-  const char* s = static_cast<const char*>(c.src) + srow * c.row_bytes;
+  const exb_gather_col c = plan.c[col];
+  const int vec = plan.vec[col];
+  const int pieces = plan.pieces[col];
+  if (pieces == 0) {
+    const int64_t b = (int64_t)local * (GATHER_THREADS / 32) + (threadIdx.x >> 5);
+    if (b >= batch) return;
+    const int lane = threadIdx.x & 31;
+    const char* s = static_cast<const char*>(c.src) + (row_of(b) + c.row_offset) * c.row_bytes;
+    char* d = static_cast<char*>(c.dst) + b * c.row_bytes;
+    const int nv = (int)(c.row_bytes / vec);
+    switch (vec) {
+      case 16: copy_short<uint4>(s, d, nv, lane); break;
+      case 8: copy_short<uint2>(s, d, nv, lane); break;
+      case 4: copy_short<uint32_t>(s, d, nv, lane); break;
+      default: copy_short<uint8_t>(s, d, nv, lane); break;
+    }
+    return;
+  }
+  const int64_t b = local / (unsigned)pieces;
+  const int64_t v0 = (int64_t)(local % (unsigned)pieces) * GATHER_PIECE_VECS;
+  const char* s = static_cast<const char*>(c.src) + (row_of(b) + c.row_offset) * c.row_bytes;
   char* d = static_cast<char*>(c.dst) + b * c.row_bytes;
-  switch (cols.vec[col]) {
-    case 16: copy_row<uint4>(s, d, c.row_bytes, t, group); break;
-    case 8: copy_row<uint2>(s, d, c.row_bytes, t, group); break;
-    case 4: copy_row<uint32_t>(s, d, c.row_bytes, t, group); break;
-    default: copy_row<uint8_t>(s, d, c.row_bytes, t, group); break;
+  const int64_t nv = c.row_bytes / vec;
+  switch (vec) {
+    case 16: copy_piece<uint4>(s, d, nv, v0, threadIdx.x); break;
+    case 8: copy_piece<uint2>(s, d, nv, v0, threadIdx.x); break;
+    case 4: copy_piece<uint32_t>(s, d, nv, v0, threadIdx.x); break;
+    default: copy_piece<uint8_t>(s, d, nv, v0, threadIdx.x); break;
   }
 }
 
@@ -179,13 +269,6 @@ replay_gather_bulk_kernel(const int64_t* __restrict__ rows, int64_t batch, BulkC
   asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
-__device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
-  const uint32_t hi0 = __umulhi(0xD2511F53u, c[0]), lo0 = 0xD2511F53u * c[0];
-  const uint32_t hi1 = __umulhi(0xCD9E8D57u, c[2]), lo1 = 0xCD9E8D57u * c[2];
-  const uint32_t n0 = hi1 ^ c[1] ^ k0, n2 = hi0 ^ c[3] ^ k1;
-  c[0] = n0; c[1] = lo1; c[2] = n2; c[3] = lo0;
-}
-
 __global__ void replay_draw_kernel(uint64_t seed, uint64_t call,
                                    const int64_t* __restrict__ eps_start,
                                    const int32_t* __restrict__ eps_len, int64_t n_episodes,
@@ -193,31 +276,20 @@ __global__ void replay_draw_kernel(uint64_t seed, uint64_t call,
                                    int32_t* __restrict__ out_episode) {
   const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= batch) return;
-  uint32_t c[4] = {(uint32_t)s, (uint32_t)call, (uint32_t)(call >> 32), 0u};
-  uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
-#pragma unroll
-  for (int r = 0; r < 10; ++r) {
-    philox_round(c, k0, k1);
-    k0 += 0x9E3779B9u;
-    k1 += 0xBB67AE85u;
-  }
-  const int64_t ep = (int64_t)(((uint64_t)c[0] * (uint64_t)n_episodes) >> 32);
-  const uint64_t span = (uint64_t)(eps_len[ep] - nstep + 1);
-  const int64_t idx = (int64_t)(((uint64_t)c[1] * span) >> 32) + 1;
-  out_rows[s] = eps_start[ep] + idx;
-  if (out_episode) out_episode[s] = (int32_t)ep;
+  int32_t ep;
+  out_rows[s] = draw_row(s, seed, call, eps_start, eps_len, n_episodes, nstep, &ep);
+  if (out_episode) out_episode[s] = ep;
 }
 
 }  // namespace exb
 
 using namespace exb;
 
-extern "C" int exb_replay_gather(const int64_t* rows, int64_t batch,
-                                 const exb_gather_col* host_cols, int n_cols,
-                                 const float* reward_src, const float* discount_src, int nstep,
-                                 int nstep_mode, float gamma, float* out_reward,
-                                 float* out_discount, exb_stream_t stream) {
-  EXB_CHECK_ARG(rows && batch > 0, "bad rows/batch");
+static int launch_gather(const int64_t* rows, const GatherDraw& draw, int64_t batch,
+                         const exb_gather_col* host_cols, int n_cols, const float* reward_src,
+                         const float* discount_src, int nstep, int nstep_mode, float gamma,
+                         float* out_reward, float* out_discount, exb_stream_t stream) {
+  EXB_CHECK_ARG(batch > 0, "bad batch");
   EXB_CHECK_ARG(n_cols >= 0 && n_cols <= GATHER_MAX_COLS && (n_cols == 0 || host_cols),
                 "n_cols=%d outside [0,%d]", n_cols, GATHER_MAX_COLS);
   EXB_CHECK_ARG(reward_src && discount_src && out_reward && out_discount, "null reward pointers");
@@ -229,26 +301,33 @@ extern "C" int exb_replay_gather(const int64_t* rows, int64_t batch,
     const char* e = getenv("EXB_GATHER_BULK");
     return e ? atoi(e) : 0;
   }();
-  GatherCols g;
+  GatherPlan g;
   BulkCols bk;
   g.n = 0;
   bk.n = 0;
   bk.chunk_base[0] = 0;
-  for (int i = 0; i < n_cols; ++i) {
-    const exb_gather_col& c = host_cols[i];
-    EXB_CHECK_ARG(c.src && c.dst && c.row_bytes > 0, "column %d: bad pointer or row_bytes", i);
-    const uintptr_t a = (uintptr_t)c.src | (uintptr_t)c.dst | (uintptr_t)c.row_bytes;
-    if (bulk_enabled && a % 16 == 0 && c.row_bytes >= 4096 && bk.n < BULK_MAX_COLS) {
-      bk.c[bk.n] = c;
-      bk.chunks_per_row[bk.n] = (int)((c.row_bytes + BULK_CHUNK - 1) / BULK_CHUNK);
-      bk.chunk_base[bk.n + 1] = bk.chunk_base[bk.n] + bk.chunks_per_row[bk.n];
-      ++bk.n;
-      continue;
+  // long rows first, so the short columns and the reward pseudo-column fill the tail
+  for (int pass = 0; pass < 2; ++pass) {
+    for (int i = 0; i < n_cols; ++i) {
+      const exb_gather_col& c = host_cols[i];
+      EXB_CHECK_ARG(c.src && c.dst && c.row_bytes > 0, "column %d: bad pointer or row_bytes", i);
+      const uintptr_t a = (uintptr_t)c.src | (uintptr_t)c.dst | (uintptr_t)c.row_bytes;
+      const int vec = (a % 16 == 0) ? 16 : (a % 8 == 0) ? 8 : (a % 4 == 0) ? 4 : 1;
+      const int64_t nv = c.row_bytes / vec;
+      const bool is_long = nv > 128;
+      if (is_long != (pass == 0)) continue;
+      if (bulk_enabled && rows && a % 16 == 0 && c.row_bytes >= 4096 && bk.n < BULK_MAX_COLS) {
+        bk.c[bk.n] = c;
+        bk.chunks_per_row[bk.n] = (int)((c.row_bytes + BULK_CHUNK - 1) / BULK_CHUNK);
+        bk.chunk_base[bk.n + 1] = bk.chunk_base[bk.n] + bk.chunks_per_row[bk.n];
+        ++bk.n;
+        continue;
+      }
+      const int j = g.n++;
+      g.c[j] = c;
+      g.vec[j] = vec;
+      g.pieces[j] = is_long ? (int)((nv + GATHER_PIECE_VECS - 1) / GATHER_PIECE_VECS) : 0;
     }
-    const int j = g.n++;
-    g.c[j] = c;
-    g.vec[j] = (a % 16 == 0) ? 16 : (a % 8 == 0) ? 8 : (a % 4 == 0) ? 4 : 1;
-    g.group[j] = (c.row_bytes / g.vec[j] > 128) ? GATHER_THREADS : 32;
   }
   if (bk.n > 0) {
     static bool attr_set = false;
@@ -264,24 +343,51 @@ extern "C" int exb_replay_gather(const int64_t* rows, int64_t batch,
     replay_gather_bulk_kernel<<<(unsigned)ctas, 32, smem, (cudaStream_t)stream>>>(rows, batch, bk);
     EXB_LAUNCH_CHECK();
   }
-  n_cols = g.n;
-  // grid.x must cover the column with the fewest rows per block and the reward pseudo-column
-  const int64_t per_block_min = 1;  // group == GATHER_THREADS -> one row per block
-  (void)per_block_min;
-  int64_t gx = 0;
-  for (int i = 0; i < n_cols; ++i) {
-    const int64_t per_block = GATHER_THREADS / g.group[i];
-    const int64_t need = (batch + per_block - 1) / per_block;
-    if (need > gx) gx = need;
+  int64_t blocks = 0;
+  for (int i = 0; i < g.n; ++i) {
+    g.block_base[i] = (unsigned)blocks;
+    blocks += g.pieces[i] ? batch * g.pieces[i]
+                          : (batch + GATHER_THREADS / 32 - 1) / (GATHER_THREADS / 32);
   }
-  const int64_t need_r = (batch + GATHER_THREADS - 1) / GATHER_THREADS;
-  if (need_r > gx) gx = need_r;
-  dim3 grid((unsigned)gx, (unsigned)(n_cols + 1));
-  replay_gather_kernel<<<grid, GATHER_THREADS, 0, (cudaStream_t)stream>>>(
-      rows, batch, g, reward_src, discount_src, nstep, nstep_mode, gamma, out_reward,
+  g.block_base[g.n] = (unsigned)blocks;
+  blocks += (batch + GATHER_THREADS - 1) / GATHER_THREADS;
+  g.block_base[g.n + 1] = (unsigned)blocks;
+  EXB_CHECK_ARG(blocks < (int64_t)0x7fffffff, "batch too large for one launch");
+  replay_gather_kernel<<<(unsigned)blocks, GATHER_THREADS, 0, (cudaStream_t)stream>>>(
+      rows, batch, g, draw, reward_src, discount_src, nstep, nstep_mode, gamma, out_reward,
       out_discount);
   EXB_LAUNCH_CHECK();
   return EXB_OK;
+}
+
+extern "C" int exb_replay_gather(const int64_t* rows, int64_t batch,
+                                 const exb_gather_col* host_cols, int n_cols,
+                                 const float* reward_src, const float* discount_src, int nstep,
+                                 int nstep_mode, float gamma, float* out_reward,
+                                 float* out_discount, exb_stream_t stream) {
+  EXB_CHECK_ARG(rows, "null rows");
+  GatherDraw none = {};
+  return launch_gather(rows, none, batch, host_cols, n_cols, reward_src, discount_src, nstep,
+                       nstep_mode, gamma, out_reward, out_discount, stream);
+}
+
+extern "C" int exb_replay_sample(uint64_t seed, uint64_t call, const int64_t* eps_start,
+                                 const int32_t* eps_len, int64_t n_episodes, int64_t batch,
+                                 const exb_gather_col* host_cols, int n_cols,
+                                 const float* reward_src, const float* discount_src, int nstep,
+                                 int nstep_mode, float gamma, float* out_reward,
+                                 float* out_discount, int64_t* out_rows, exb_stream_t stream) {
+  EXB_CHECK_ARG(eps_start && eps_len && n_episodes > 0, "bad episode tables");
+  GatherDraw d;
+  d.seed = seed;
+  d.call = call;
+  d.eps_start = eps_start;
+  d.eps_len = eps_len;
+  d.n_episodes = n_episodes;
+  d.nstep = nstep_mode ? nstep : 1;
+  d.out_rows = out_rows;
+  return launch_gather(nullptr, d, batch, host_cols, n_cols, reward_src, discount_src, nstep,
+                       nstep_mode, gamma, out_reward, out_discount, stream);
 }
 
 extern "C" int exb_replay_draw(uint64_t seed, uint64_t call, const int64_t* eps_start,

@@ -164,21 +164,18 @@ class DeviceReplayBuffer:
         rows = np.array([eps[int(e)]["start"] + int(i) for e, i in draws], np.int64)
         return torch.from_numpy(rows).to(self.device)
 
-    def gather(self, rows, offline=False):
-        """(obs, action, reward, discount, next_obs, *meta) for global `rows`, as CUDA tensors —
-        the tuple of utils/replay_buffer.py:235 (:96 offline)."""
-        lib = _lib.load()
-        batch = rows.numel()
+    def _outputs(self, batch, offline):
+        """Output tensors + column specs of one batch (the tuple of utils/replay_buffer.py:235)."""
         nstep = 1 if offline else self.nstep
         obs_src, act_src = self.cols["observation"], self.cols["action"]
         dev = self.device
+        if self.cols["reward"][0].numel() != 1 or self.cols["reward"].dtype != torch.float32:
+            raise ValueError("reward/discount columns must be float32 of shape (1,) per step")
         obs = torch.empty((batch, *obs_src.shape[1:]), dtype=obs_src.dtype, device=dev)
         nobs = torch.empty_like(obs)
         act = torch.empty((batch, *act_src.shape[1:]), dtype=act_src.dtype, device=dev)
         rew = torch.empty((batch, *self.cols["reward"].shape[1:]), dtype=torch.float32, device=dev)
         disc = torch.empty_like(rew)
-        if self.cols["reward"][0].numel() != 1 or self.cols["reward"].dtype != torch.float32:
-            raise ValueError("reward/discount columns must be float32 of shape (1,) per step")
         specs = [(obs_src, obs, -1), (act_src, act, 0), (obs_src, nobs, nstep - 1)]
         metas = []
         if not offline:
@@ -192,12 +189,37 @@ class DeviceReplayBuffer:
             c.src, c.dst = src.data_ptr(), dst.data_ptr()
             c.row_bytes = src[0].numel() * src.element_size()
             c.row_offset = off
-        with torch.cuda.device(dev):
+        return (obs, act, rew, disc, nobs, *metas), cols, len(specs), nstep
+
+    def gather(self, rows, offline=False):
+        """(obs, action, reward, discount, next_obs, *meta) for global `rows`, as CUDA tensors —
+        the tuple of utils/replay_buffer.py:235 (:96 offline)."""
+        lib = _lib.load()
+        batch = rows.numel()
+        out, cols, n_cols, nstep = self._outputs(batch, offline)
+        with torch.cuda.device(self.device):
             _lib.check(lib.exb_replay_gather(
-                _lib.ptr(rows), batch, cols, len(specs), _lib.ptr(self.cols["reward"]),
+                _lib.ptr(rows), batch, cols, n_cols, _lib.ptr(self.cols["reward"]),
                 _lib.ptr(self.cols["discount"]), nstep, 0 if offline else 1, self.discount,
-                _lib.ptr(rew), _lib.ptr(disc), _lib.stream_ptr(dev)))
-        return (obs, act, rew, disc, nobs, *metas)
+                _lib.ptr(out[2]), _lib.ptr(out[3]), _lib.stream_ptr(self.device)))
+        return out
+
+    def sample_philox(self, batch, seed, call, offline=False, return_rows=False):
+        """Index draw + gather as ONE kernel launch (exb_replay_sample): same result as
+        `gather(draw_rows_philox(batch, seed, call))`."""
+        lib = _lib.load()
+        eps, starts, lens = self._tables()
+        if not eps:
+            raise RuntimeError("replay buffer is empty")
+        out, cols, n_cols, nstep = self._outputs(batch, offline)
+        rows = torch.empty(batch, dtype=torch.int64, device=self.device) if return_rows else None
+        with torch.cuda.device(self.device):
+            _lib.check(lib.exb_replay_sample(
+                ctypes.c_uint64(seed), ctypes.c_uint64(call), _lib.ptr(starts), _lib.ptr(lens),
+                len(eps), batch, cols, n_cols, _lib.ptr(self.cols["reward"]),
+                _lib.ptr(self.cols["discount"]), nstep, 0 if offline else 1, self.discount,
+                _lib.ptr(out[2]), _lib.ptr(out[3]), _lib.ptr(rows), _lib.stream_ptr(self.device)))
+        return (out, rows) if return_rows else out
 
 
 class DeviceReplayLoader:
@@ -265,12 +287,11 @@ class DeviceReplayLoader:
         else:
             self._try_fetch()
             self._since_fetch += self.batch_size
-        if self.sampler == "philox":
-            rows = self.buffer.draw_rows_philox(self.batch_size, self.seed, self._calls,
-                                                offline=self.offline)
-        else:
-            rows = self.buffer.draw_rows_reference_rng(self.batch_size, offline=self.offline)
         self._calls += 1
+        if self.sampler == "philox":
+            return self.buffer.sample_philox(self.batch_size, self.seed, self._calls - 1,
+                                             offline=self.offline)
+        rows = self.buffer.draw_rows_reference_rng(self.batch_size, offline=self.offline)
         return self.buffer.gather(rows, offline=self.offline)
 
     def __iter__(self):

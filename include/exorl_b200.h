@@ -95,7 +95,12 @@ int exb_knn_screened_status_sync(const void* workspace, int32_t host_status[4],
  * their phase boundaries (block 0 / row 0 only); this copies the 16 stamps (ns) to the host.
  *   [0] screen start, [1] first operand chunk landed, [2] MMAs issued, [3] accumulator ready,
  *   [4] k-th best known, [5] candidates collected, [6] lists written,
- *   [8] rerank start, [9] lists gathered, [10] survivors chosen, [11] top-k written. */
+ *   [8] rerank start, [9] lists gathered, [10] survivors chosen, [11] top-k written.
+ * For the streaming (dataset-scale) screen kernel the same 16 words are cycle counters summed
+ * over the launch instead: [0] epilogue warps waiting for an accumulator, [1] epilogue warps
+ * filtering, [2] slow-path (hit) chunk events, [3] cycles inside the slow path, [4] MMA issuer
+ * waiting for a free accumulator (= stalled by the epilogue), [5] MMA issuer waiting for TMA
+ * data, [6] MMA issuer total, [7] CTAs that issued MMAs. */
 int exb_debug_trace_sync(const void* workspace, int64_t host_ns[16], exb_stream_t stream);
 
 /* Measurement hook (bench.py): when enabled, every screening-kernel launch is bracketed by CUDA
@@ -197,6 +202,18 @@ int exb_replay_draw(uint64_t seed, uint64_t call, const int64_t* eps_start,
                     const int32_t* eps_len, int64_t n_episodes, int nstep, int64_t batch,
                     int64_t* out_rows, int32_t* out_episode /* may be NULL */,
                     exb_stream_t stream);
+
+/* Draw + gather in ONE launch: every block recomputes the Philox draw of the samples it copies
+ * (same arithmetic as exb_replay_draw with nstep_draw = nstep_mode ? nstep : 1), so a batch is a
+ * single kernel.  Identical outputs to exb_replay_draw followed by exb_replay_gather; the drawn
+ * rows are also written to out_rows [batch] when it is not NULL.  Replaces one whole
+ * `next(replay_iter)` of utils/replay_buffer.py:214-244 (:77-99 offline). */
+int exb_replay_sample(uint64_t seed, uint64_t call, const int64_t* eps_start,
+                      const int32_t* eps_len, int64_t n_episodes, int64_t batch,
+                      const exb_gather_col* host_cols, int n_cols, const float* reward_src,
+                      const float* discount_src, int nstep, int nstep_mode, float gamma,
+                      float* out_reward, float* out_discount, int64_t* out_rows /* may be NULL */,
+                      exb_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -191,3 +191,71 @@ def test_offline_loader_and_fifo_eviction(tmp_path):
     out = buf.gather(buf.rows_from_draws([(0, 1), (2, 8)]))
     assert np.array_equal(out[0][0].cpu().numpy(), eps[3]["observation"][0])
     assert np.array_equal(out[4][1].cpu().numpy(), eps[5]["observation"][10])
+
+
+@pytest.mark.parametrize("offline", [False, True])
+def test_fused_sample_equals_draw_then_gather(offline):
+    """exb_replay_sample (draw + gather in one launch) == exb_replay_draw + exb_replay_gather."""
+    rng = np.random.default_rng(21)
+    eps = []
+    for L in (5, 40, 13, 300, 8):
+        ep = _synth(rng, L, terminal=True)
+        ep["skill"] = rng.standard_normal((L + 1, 4)).astype(np.float32)
+        eps.append(ep)
+    buf = _buffer(eps, 3, meta=("skill",))
+    for batch, call in ((1, 0), (257, 3), (2048, 2 ** 33 + 5)):
+        rows = buf.draw_rows_philox(batch, 987654321, call, offline=offline)
+        want = buf.gather(rows, offline=offline)
+        got, got_rows = buf.sample_philox(batch, 987654321, call, offline=offline,
+                                          return_rows=True)
+        assert torch.equal(got_rows, rows)
+        assert len(got) == len(want)
+        for a, b in zip(got, want):
+            assert a.dtype == b.dtype and torch.equal(a, b)
+
+
+@pytest.mark.parametrize("obs_shape,dtype", [((129 * 4,), np.float32), ((1024 * 4 + 4,), np.float32),
+                                             ((3, 84, 84), np.uint8), ((4099,), np.uint8),
+                                             ((2, 1031), np.float32)])
+def test_long_rows_are_copied_in_pieces(obs_shape, dtype):
+    """Rows longer than 128 vectors are split into 1024-vector pieces (one block each); sizes
+    just above the short-row limit, just above one piece, ragged last pieces and odd byte counts
+    (1-byte vector path) must all arrive intact."""
+    rng = np.random.default_rng(22)
+    eps = [_synth(rng, 9, obs_shape, dtype) for _ in range(3)]
+    if dtype != np.uint8:
+        for ep in eps:
+            ep["observation"] = rng.standard_normal((10, *obs_shape)).astype(np.float32)
+    buf = _buffer(eps, 2)
+    draws = [(e, i) for e in range(3) for i in (1, 4, 8)]
+    rows = buf.rows_from_draws(draws)
+    out = buf.gather(rows)
+    for s, (e, idx) in enumerate(draws):
+        want = nstep_transition(eps[e], idx, 2, 0.99)
+        for j in range(5):
+            assert np.array_equal(out[j][s].cpu().numpy(), np.asarray(want[j])), (s, j)
+
+
+def test_full_size_gather_properties():
+    """BASELINE C4 shape at reduced depth: 1024-batch of (9,84,84) uint8 frames; every gathered
+    frame equals a direct index of the device column (size-independent identity)."""
+    n_rows = 4004
+    g = torch.Generator(device=DEV).manual_seed(4)
+    buf = xb.DeviceReplayBuffer(DEV, 4000, 3, 0.99, capacity_rows=n_rows)
+    buf.cols["observation"] = torch.randint(0, 256, (n_rows, 9, 84, 84), generator=g,
+                                            dtype=torch.uint8, device=DEV)
+    buf.cols["action"] = torch.rand((n_rows, 6), generator=g, device=DEV)
+    buf.cols["reward"] = torch.rand((n_rows, 1), generator=g, device=DEV)
+    buf.cols["discount"] = torch.ones((n_rows, 1), device=DEV)
+    buf.episodes = [{"key": f"episode_{e:06d}_1000.npz", "start": e * 1001, "len": 1000}
+                    for e in range(4)]
+    buf.size = 4000
+    (obs, act, rew, disc, nobs), rows = buf.sample_philox(1024, 3, 9, return_rows=True)
+    assert torch.equal(obs, buf.cols["observation"][rows - 1])
+    assert torch.equal(nobs, buf.cols["observation"][rows + 2])
+    assert torch.equal(act, buf.cols["action"][rows])
+    r = buf.cols["reward"]
+    g1 = torch.tensor(0.99, device=DEV)
+    want = (r[rows] + g1 * r[rows + 1]) + (g1 * g1) * r[rows + 2]
+    assert torch.equal(rew, want)
+    assert torch.all(disc == np.float32(0.99) * np.float32(0.99) * np.float32(0.99))
