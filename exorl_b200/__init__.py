@@ -5,12 +5,14 @@ Drop-in surface of the reference's hot path:
   compute_apt_reward            <- the pre-refactor name of the same computation (source != target)
   proto_knn_reward, proto_enqueue <- agents/unsupervised_learning/proto.py:110-118
   make_replay_loader, make_offline_replay_loader <- utils/replay_buffer.py:246-277
+  read_episode(s)               <- load_episode, utils/replay_buffer.py:26-29 (native .npz reader)
 """
 from .knn import RMS, PBE, compute_apt_reward, knn_topk, proto_knn_reward, proto_enqueue
 from .replay import (DeviceReplayBuffer, DeviceReplayLoader, make_replay_loader,
                      make_offline_replay_loader)
 from .relabel import relabel_apt_reward
+from .ingest import read_episode, read_episodes
 
 __all__ = ["RMS", "PBE", "compute_apt_reward", "knn_topk", "proto_knn_reward", "proto_enqueue",
            "DeviceReplayBuffer", "DeviceReplayLoader", "make_replay_loader",
-           "make_offline_replay_loader", "relabel_apt_reward"]
+           "make_offline_replay_loader", "relabel_apt_reward", "read_episode", "read_episodes"]

@@ -54,7 +54,8 @@ def build_library(force=False, verbose=False):
             print(log)
     objs = [obj_dir / (s.stem + ".o") for s in _sources()]
     if force or jobs or _stale(LIB, objs):
-        cmd = [NVCC, *ARCH, "-shared", "-o", str(LIB), *map(str, objs), "-cudart", "static"]
+        cmd = [NVCC, *ARCH, "-shared", "-o", str(LIB), *map(str, objs), "-cudart", "static",
+               "-lz"]   # zlib: raw inflate of .npz members (csrc/npz_ingest.cu)
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

@@ -18,6 +18,11 @@ class GatherCol(_c.Structure):
     _fields_ = [("src", _vp), ("dst", _vp), ("row_bytes", _i64), ("row_offset", _i32)]
 
 
+class NpzArray(_c.Structure):
+    _fields_ = [("name", _c.c_char * 64), ("dtype", _c.c_char * 8), ("ndim", _i32),
+                ("fortran_order", _i32), ("shape", _i64 * 8), ("nbytes", _i64)]
+
+
 # name -> (restype, argtypes); mirrors include/exorl_b200.h one to one
 SIGNATURES = {
     "exb_abi_version": (_c.c_int, []),
@@ -54,6 +59,10 @@ SIGNATURES = {
     "exb_replay_sample": (_c.c_int, [_u64, _u64, _vp, _vp, _i64, _i64, _c.POINTER(GatherCol),
                                      _c.c_int, _vp, _vp, _c.c_int, _c.c_int, _f32, _vp, _vp, _vp,
                                      _vp]),
+    "exb_npz_open": (_c.c_int, [_c.c_char_p, _c.POINTER(_vp), _c.POINTER(_c.c_int)]),
+    "exb_npz_info": (_c.c_int, [_vp, _c.c_int, _c.POINTER(NpzArray)]),
+    "exb_npz_read": (_c.c_int, [_vp, _c.c_int, _vp, _i64]),
+    "exb_npz_close": (None, [_vp]),
 }
 
 EXB_OK, EXB_EINVAL, EXB_EKRANGE, EXB_EUNSUPPORTED, EXB_ECUDA, EXB_EFALLBACK = range(6)

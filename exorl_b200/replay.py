@@ -15,6 +15,7 @@ import numpy as np
 import torch
 
 from . import _lib
+from . import ingest
 
 _CORE = ("observation", "action", "reward", "discount")
 
@@ -25,9 +26,12 @@ def _episode_len(episode):
 
 
 def _load_npz(path):
-    with open(path, "rb") as f:
-        z = np.load(f)
-        return {k: z[k] for k in z.keys()}
+    """One episode file -> dict of (pinned) CPU tensors, via the native reader."""
+    return ingest.read_episode(path)
+
+
+def _as_tensor(a):
+    return a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a))
 
 
 class DeviceReplayBuffer:
@@ -64,9 +68,9 @@ class DeviceReplayBuffer:
             n_eps = self.max_size // max(eps_len, 1) + 2
             self.capacity_rows = n_eps * per + per
         for name in (*_CORE, *self.meta_names):
-            a = episode[name]
-            self.cols[name] = torch.empty((self.capacity_rows, *a.shape[1:]),
-                                          dtype=torch.from_numpy(a[:1]).dtype, device=self.device)
+            a = _as_tensor(episode[name])
+            self.cols[name] = torch.empty((self.capacity_rows, *a.shape[1:]), dtype=a.dtype,
+                                          device=self.device)
 
     def _evict_oldest(self):
         old = self.episodes.pop(0)
@@ -106,10 +110,13 @@ class DeviceReplayBuffer:
             self._evict_oldest()
         start = self._reserve(eps_len + 1)
         for name, col in self.cols.items():
-            a = np.ascontiguousarray(episode[name])
+            a = _as_tensor(episode[name])
             if a.shape[0] != eps_len + 1:
                 raise ValueError(f"column {name}: {a.shape[0]} rows, expected {eps_len + 1}")
-            col[start:start + eps_len + 1].copy_(torch.from_numpy(a), non_blocking=False)
+            # pinned staging (ingest.read_episode) -> asynchronous DMA on the current stream; the
+            # staging tensor stays referenced by `episode` until the caller drops it, and the
+            # caching host allocator does not reuse a pinned block with a copy in flight
+            col[start:start + eps_len + 1].copy_(a, non_blocking=a.is_pinned())
         self._head = start + eps_len + 1
         self.episodes.append({"key": key if key is not None else len(self.episodes),
                               "start": start, "len": eps_len})
@@ -261,22 +268,21 @@ class DeviceReplayLoader:
                 break
             fetched += eps_len
             new.append(fn)
-        for fn in new:    # the reference stores them in this (newest-first) order too
-            try:
-                episode = _load_npz(fn)
-            except Exception:
-                break
-            self.buffer.add_episode(episode, key=str(fn))
-            self._seen.add(fn)
-            if not self.save_snapshot:
-                fn.unlink(missing_ok=True)
+        try:              # the reference stores them in this (newest-first) order too
+            for fn, episode in ingest.read_episodes(new):
+                self.buffer.add_episode(episode, key=str(fn))
+                self._seen.add(fn)
+                if not self.save_snapshot:
+                    fn.unlink(missing_ok=True)
+        except (ValueError, RuntimeError, OSError):
+            pass          # a half-written file: stop here, like the `break` of :206-209
 
     def _load_offline(self):
         """Offline: sorted scan until the size cap (utils/replay_buffer.py:57-75)."""
-        for fn in sorted(self.replay_dir.glob("*.npz")):
+        for fn, episode in ingest.read_episodes(sorted(self.replay_dir.glob("*.npz"))):
             if self.buffer.size > self.buffer.max_size:
                 break
-            self.buffer.add_episode(_load_npz(fn), key=str(fn))
+            self.buffer.add_episode(episode, key=str(fn))
         self._loaded = True
 
     # -- iteration ---------------------------------------------------------------------------

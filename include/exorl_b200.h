@@ -215,6 +215,30 @@ int exb_replay_sample(uint64_t seed, uint64_t call, const int64_t* eps_start,
                       float* out_reward, float* out_discount, int64_t* out_rows /* may be NULL */,
                       exb_stream_t stream);
 
+/* --------------------------------------------------------------------------------------------
+ * Episode ingestion (host side, no GPU involved): reads the reference's episode files — ZIP
+ * archives of .npy members written by np.savez_compressed, utils/replay_buffer.py:18-23 — so
+ * that a pool of host threads can inflate episodes in parallel into pinned staging buffers.
+ * Replaces np.load in load_episode (:26-29) as used by _try_fetch / _store_episode (:172-212)
+ * and OfflineReplayBuffer._load (:57-75).  Stored and deflated members, little-endian scalar
+ * dtypes, C order.  A handle may be used by one thread at a time; different handles are
+ * independent.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  char name[64];       /* member name without ".npy" (the spec name: observation, action, ...) */
+  char dtype[8];       /* numpy descr, e.g. "<f4", "|u1", "|b1"                                 */
+  int32_t ndim;
+  int32_t fortran_order;
+  int64_t shape[8];
+  int64_t nbytes;      /* payload bytes = prod(shape) * itemsize                                */
+} exb_npz_array;
+
+int exb_npz_open(const char* path, void** handle, int* n_arrays);
+int exb_npz_info(void* handle, int i, exb_npz_array* out);
+/* Inflate array i into host_dst (dst_bytes must equal nbytes). */
+int exb_npz_read(void* handle, int i, void* host_dst, int64_t dst_bytes);
+void exb_npz_close(void* handle);
+
 #ifdef __cplusplus
 }
 #endif
