@@ -138,6 +138,43 @@ class DeviceReplayBuffer:
     def __len__(self):
         return self.size
 
+    # -- relabelling (the step after the kNN reward path) ------------------------
+    def live_rows(self):
+        """Global row ids of every stored step (all L+1 rows of every episode, in the sorted
+        episode order of `_tables`), as a device int64 vector."""
+        eps, _, _ = self._tables()
+        parts = [torch.arange(e["start"], e["start"] + e["len"] + 1, device=self.device)
+                 for e in eps]
+        return torch.cat(parts) if parts else torch.empty(0, dtype=torch.int64, device=self.device)
+
+    def relabel_rewards(self, rewards, rows=None):
+        """Overwrite the stored reward of `rows` (default: every live row, `live_rows()` order)
+        with `rewards` (n, 1) — the in-memory effect of relabel_episode
+        (utils/replay_buffer.py:31-42: episode['reward'] = one reward per stored state), with the
+        rewards coming from the kNN reward path instead of the simulator."""
+        rows = self.live_rows() if rows is None else rows
+        r = rewards.reshape(-1, 1).to(device=self.device, dtype=torch.float32)
+        if r.size(0) != rows.numel():
+            raise ValueError(f"{r.size(0)} rewards for {rows.numel()} rows")
+        self.cols["reward"].index_copy_(0, rows, r)
+
+    def export_episodes(self, out_dir):
+        """Write every stored episode back in the reference's format (save_episode,
+        utils/replay_buffer.py:18-23), one `.npz` per episode under its original file name."""
+        out_dir = pathlib.Path(out_dir)
+        out_dir.mkdir(parents=True, exist_ok=True)
+        written = []
+        for e in self.episodes:
+            lo, hi = e["start"], e["start"] + e["len"] + 1
+            ep = {name: col[lo:hi].cpu().numpy() for name, col in self.cols.items()}
+            name = pathlib.Path(str(e["key"])).name
+            if not name.endswith(".npz"):
+                name = f"episode_{name}_{e['len']}.npz"
+            with open(out_dir / name, "wb") as f:
+                np.savez_compressed(f, **ep)
+            written.append(out_dir / name)
+        return written
+
     # -- sampling ---------------------------------------------------------------------------
     def draw_rows_philox(self, batch, seed, call, offline=False):
         """Device index draw: uniform episode, then uniform start (range of :222 / :90)."""

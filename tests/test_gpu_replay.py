@@ -259,3 +259,42 @@ def test_full_size_gather_properties():
     want = (r[rows] + g1 * r[rows + 1]) + (g1 * g1) * r[rows + 2]
     assert torch.equal(rew, want)
     assert torch.all(disc == np.float32(0.99) * np.float32(0.99) * np.float32(0.99))
+
+
+def test_relabel_rewards_and_export_roundtrip(tmp_path):
+    """§8f.4: rewards computed for every stored state are written back into the reward column
+    (relabel_episode's in-memory effect, utils/replay_buffer.py:31-42), sampled n-step returns use
+    them, and the exported files are episodes in the reference's format."""
+    rng = np.random.default_rng(31)
+    eps = [_synth(rng, L) for L in (6, 11, 9)]
+    buf = _buffer(eps, 3)
+    rows = buf.live_rows()
+    assert rows.numel() == sum(L + 1 for L in (6, 11, 9))
+    new_r = torch.arange(rows.numel(), dtype=torch.float32, device=DEV).reshape(-1, 1) * 0.5
+    buf.relabel_rewards(new_r)
+    # the same rewards laid over the episodes on the host
+    off = 0
+    relabelled = []
+    for e in buf._tables()[0]:
+        k = int(str(e["key"]).split("_")[1])
+        ep = dict(eps[k])
+        ep["reward"] = new_r[off:off + e["len"] + 1].cpu().numpy()
+        off += e["len"] + 1
+        relabelled.append((k, ep))
+    draws = [(pos, 1) for pos in range(3)] + [(1, 5)]
+    out = buf.gather(buf.rows_from_draws(draws))
+    for s, (pos, idx) in enumerate(draws):
+        want = nstep_transition(relabelled[pos][1], idx, 3, 0.99)
+        for j in range(5):
+            assert np.array_equal(out[j][s].cpu().numpy(), np.asarray(want[j])), (s, j)
+    files = buf.export_episodes(tmp_path / "relabelled")
+    assert sorted(f.name for f in files) == ["episode_0_6.npz", "episode_1_11.npz",
+                                             "episode_2_9.npz"]
+    from oracle import read_episode_npz
+    for k, ep in relabelled:
+        got = read_episode_npz(tmp_path / "relabelled" / f"episode_{k}_{len(ep['reward']) - 1}.npz")
+        assert set(got) == set(ep)
+        for name in ep:
+            assert np.array_equal(got[name], ep[name]), (k, name)
+    with pytest.raises(ValueError):
+        buf.relabel_rewards(new_r[:-1])
