@@ -37,7 +37,8 @@ def parse():
     ap.add_argument("--n", type=int, default=1_000_000)
     ap.add_argument("--dim", type=int, default=512)
     ap.add_argument("--k", type=int, default=12)
-    ap.add_argument("--exchange", default="all_to_all", choices=["all_to_all", "all_gather"])
+    ap.add_argument("--exchange", default="auto",
+                    choices=["auto", "lists", "all_to_all", "all_gather"])
     ap.add_argument("--cpu-queries", type=int, default=128,
                     help="queries of the bounded CPU-baseline sample (vs the full bank)")
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -39,7 +39,7 @@ def main():
     r0 = _reward_from_knn(d0, a.k, True, True, 0.0, rms0)
 
     ok = True
-    for exchange in ("all_to_all", "all_gather"):
+    for exchange in ("lists", "auto", "all_to_all", "all_gather"):
         rms = xb.RMS(dev)
         out = xb.relabel_apt_reward(rep, args, rms=rms, exchange=exchange, mode="screened",
                                     return_knn=True)

@@ -35,6 +35,13 @@ SIGNATURES = {
     "exb_knn_screened_workspace_bytes": (_sz, [_i64, _i64, _c.c_int, _c.c_int]),
     "exb_knn_screened_f32": (_c.c_int, [_vp, _i64, _vp, _i64, _c.c_int, _c.c_int, _i32,
                                         _c.c_int, _vp, _vp, _vp, _sz, _vp]),
+    "exb_knn_screen_lists_count": (_c.c_int, [_i64, _i64, _c.c_int, _c.c_int]),
+    "exb_knn_screen_lists_f32": (_c.c_int, [_vp, _i64, _vp, _i64, _c.c_int, _c.c_int, _c.c_int,
+                                            _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "exb_knn_rerank_lists_workspace_bytes": (_sz, [_i64, _i64, _c.c_int]),
+    "exb_knn_rerank_lists_f32": (_c.c_int, [_vp, _i64, _vp, _i64, _c.c_int, _c.c_int, _c.c_int,
+                                            _c.c_int, _vp, _vp, _vp, _c.POINTER(_i32), _vp, _vp,
+                                            _vp, _vp, _vp, _vp, _sz, _vp]),
     "exb_knn_screened_status_sync": (_c.c_int, [_vp, _c.POINTER(_i32), _vp]),
     "exb_debug_trace_sync": (_c.c_int, [_vp, _c.POINTER(_i64), _vp]),
     "exb_profile_begin": (_c.c_int, [_c.c_int]),

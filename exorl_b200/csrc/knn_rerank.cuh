@@ -44,6 +44,13 @@ struct RerankParams {
   const float* B;
   int64_t nq, nb;
   int dim, k, idx_base, splits;
+  // Lists gathered from several bank shards (exb_knn_rerank_lists_f32): list s of a row belongs
+  // to shard s / lists_per_shard, whose arrays start shard_stride rows further on and whose
+  // indices are local to the shard (global = local + shard_lo).  One shard: lists_per_shard =
+  // splits, shard_rows = 0.
+  int lists_per_shard;
+  int64_t shard_rows;        // rows per shard block in cand_* ([n_shards, shard_rows, lps, CAP])
+  int shard_lo[16];
   const float* cand_val;
   const int* cand_idx;
   const int* cand_cnt;
@@ -258,12 +265,17 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
   // ---- everything this row needs from the screen is requested at once (one round trip): counts
   // (lane sp holds split sp, splits <= 16), per-split thresholds, the row's scalars, and all list
   // slots (entry e = lane + 32 i; slots beyond a split's count are read and masked afterwards).
-  const int my_cnt = (lane < splits) ? p.cand_cnt[row * splits + lane] : 0;
+  const int lps = p.lists_per_shard;
+  auto list_base = [&](int sp) -> int64_t {   // index of list sp of this row in cand_cnt
+    const int sh = sp / lps;
+    return ((int64_t)sh * p.shard_rows + row) * lps + (sp - sh * lps);
+  };
+  const int my_cnt = (lane < splits) ? p.cand_cnt[list_base(lane)] : 0;
   float my_tk = -FLT_MAX, my_tr = -FLT_MAX;
   if constexpr (LAT) {
     if (lane < splits) {
-      my_tk = p.cand_tk[row * splits + lane];
-      my_tr = p.cand_tr[row * splits + lane];
+      my_tk = p.cand_tk[list_base(lane)];
+      my_tr = p.cand_tr[list_base(lane)];
     }
   }
   const float ea_row = p.ea[row];
@@ -277,8 +289,9 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
     ev[i] = -FLT_MAX;
     ei[i] = -1;
     if (sp < splits) {
-      ev[i] = p.cand_val[row * splits * SCR_CAP + e];
-      ei[i] = p.cand_idx[row * splits * SCR_CAP + e];
+      const int64_t a = list_base(sp) * SCR_CAP + (e - sp * SCR_CAP);
+      ev[i] = p.cand_val[a];
+      ei[i] = p.cand_idx[a] + p.shard_lo[sp / lps];
     }
   }
   int why = undecided ? 4 : 0;           // debug only (trace[12..15] of an undecided row)

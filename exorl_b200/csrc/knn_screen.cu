@@ -1189,12 +1189,32 @@ extern "C" size_t exb_knn_screened_workspace_bytes(int64_t nq, int64_t nb, int d
 
 // pbe: optional fused epilogue request; *fused tells the caller whether it was honoured (only the
 // per-update latency chain fuses it).
+__global__ void fold_scalars_kernel(const PrepScalars* bsc, const PrepScalars* qsc,
+                                    PrepScalars* out) {
+  PrepScalars o = *bsc;
+  if (qsc) o.range_flag |= qsc->range_flag;   // a query row outside the fp16 range
+  o.pad = 0;
+  *out = o;
+}
+
+// Screen-only mode (exb_knn_screen_lists_f32): the candidate lists, the query rows' half norms /
+// rounding errors and the bank scalars go to caller buffers; no rerank, no fallback.
+struct ListsOut {
+  float* val;      // [nq, lists, SCR_CAP]
+  int* idx;        // [nq, lists, SCR_CAP], indices local to `bank`
+  int* cnt;        // [nq, lists]
+  float* ha;       // [nq]
+  float* ea;       // [nq]
+  void* scalars;   // 16 bytes: PrepScalars of the bank (query-side range flag folded in)
+};
+
 static int screened_impl(const float* src, int64_t nq, const float* bank, int64_t nb, int dim,
                          int k, int32_t idx_base, int src_is_bank, float* out_dist,
                          int32_t* out_idx, void* workspace, size_t workspace_bytes,
-                         exb_stream_t stream, const FusedPbe* pbe, bool* fused) {
+                         exb_stream_t stream, const FusedPbe* pbe, bool* fused,
+                         const ListsOut* lo = nullptr) {
   if (fused) *fused = false;
-  EXB_CHECK_ARG(src && bank && out_dist && out_idx, "null pointer");
+  EXB_CHECK_ARG(src && bank && (lo || (out_dist && out_idx)), "null pointer");
   EXB_CHECK_ARG(nq > 0 && nb > 0 && nq < (1LL << 31) && nb < (1LL << 31), "bad row counts");
   if (k > nb) {
     set_error("selected index k out of range (k=%d > bank rows=%lld)", k, (long long)nb);
@@ -1229,9 +1249,17 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
   rp.out_idx = out_idx; rp.fallback_rows = w.fb_rows; rp.fallback_cap = pl.fb_cap;
   rp.status = w.status; rp.trace = trace_on ? w.trace : nullptr;
   rp.pbe.on = 0;
+  rp.lists_per_shard = rp.splits;
+  rp.shard_rows = 0;
+  for (int i = 0; i < 16; ++i) rp.shard_lo[i] = 0;
   const unsigned rr_grid = (unsigned)((nq + RR_WARPS - 1) / RR_WARPS);
 
   if (pl.lat) {
+    if (lo) {
+      set_error("screen-only lists need the streaming kernel (input too small: %lld x %lld)",
+                (long long)nq, (long long)nb);
+      return EXB_EUNSUPPORTED;
+    }
     // per-update chain: prep -> latency screen -> rerank (inline fallback); no memset, no atomics
     int rc = launch_prep(bank, nb, dim, pl.dpad, w.b16, w.hb, w.eb, nullptr, st,
                          reinterpret_cast<unsigned long long*>(w.status));
@@ -1331,6 +1359,11 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
   sp.prefetch = pf;
   sp.stats = trace_on ? w.trace : nullptr;
   sp.stages = pl.stages; sp.cand_val = w.cand_val; sp.cand_idx = w.cand_idx; sp.cand_cnt = w.cand_cnt;
+  if (lo) {
+    sp.cand_val = lo->val;
+    sp.cand_idx = lo->idx;
+    sp.cand_cnt = lo->cnt;
+  }
   dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
   sp.lists = pl.splits * pl.trackers;
   // sample tiles that seed the k-th-best chain before the real scan (FILT 3): ~1.5 % extra MMA
@@ -1384,6 +1417,15 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
   EXB_LAUNCH_CHECK();
   if (prof) EXB_CUDA(cudaEventRecord(g_prof.e1[g_prof.n++], st));
 
+  if (lo) {
+    EXB_CUDA(cudaMemcpyAsync(lo->ha, w.ha, (size_t)nq * 4, cudaMemcpyDeviceToDevice, st));
+    EXB_CUDA(cudaMemcpyAsync(lo->ea, w.ea, (size_t)nq * 4, cudaMemcpyDeviceToDevice, st));
+    fold_scalars_kernel<<<1, 1, 0, st>>>(w.bsc, same ? nullptr : w.qsc,
+                                         static_cast<PrepScalars*>(lo->scalars));
+    EXB_LAUNCH_CHECK();
+    return EXB_OK;
+  }
+
   launch_rerank<false>(rp, rr_grid, ni, st);
   EXB_LAUNCH_CHECK();
 
@@ -1398,6 +1440,106 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
                                     size_t workspace_bytes, exb_stream_t stream) {
   return screened_impl(src, nq, bank, nb, dim, k, idx_base, src_is_bank, out_dist, out_idx,
                        workspace, workspace_bytes, stream, nullptr, nullptr);
+}
+
+// ------------------------------------------------------------------------------------------
+// Sharded relabel, "exchange the candidate lists" form: screen only, then (after the exchange)
+// rerank the lists of all shards for this rank's query block.
+// ------------------------------------------------------------------------------------------
+extern "C" int exb_knn_screen_lists_count(int64_t nq, int64_t nb, int dim, int k) {
+  ScreenPlan pl;
+  if (!make_plan(nq, nb, dim, k, &pl) || pl.lat) return 0;
+  return pl.splits * pl.trackers;
+}
+
+extern "C" int exb_knn_screen_lists_f32(const float* src, int64_t nq, const float* bank,
+                                        int64_t nb, int dim, int k, int src_is_bank,
+                                        float* out_val, int32_t* out_idx, int32_t* out_cnt,
+                                        float* out_ha, float* out_ea, void* out_scalars,
+                                        void* workspace, size_t workspace_bytes,
+                                        exb_stream_t stream) {
+  EXB_CHECK_ARG(out_val && out_idx && out_cnt && out_ha && out_ea && out_scalars, "null output");
+  ListsOut lo = {out_val, out_idx, out_cnt, out_ha, out_ea, out_scalars};
+  return screened_impl(src, nq, bank, nb, dim, k, 0, src_is_bank, nullptr, nullptr, workspace,
+                       workspace_bytes, stream, nullptr, nullptr, &lo);
+}
+
+struct RerankListsWs {
+  RerankStatus* status;
+  int* fb_rows;
+  float* fb_d2;
+  int* fb_idx;
+  int fb_cap, fb_splits;
+};
+
+static size_t carve_rerank_lists(void* ws, int64_t nq, int64_t nb, int k, RerankListsWs* o) {
+  Carver cv(ws ? ws : reinterpret_cast<void*>(256));
+  o->fb_cap = (int)(nq < FALLBACK_CAP ? nq : FALLBACK_CAP);
+  int fbs = (int)((nb + 127) / 128);
+  if (fbs > FALLBACK_SPLITS) fbs = FALLBACK_SPLITS;
+  if (fbs * k > 512) fbs = 512 / k;
+  o->fb_splits = fbs < 1 ? 1 : fbs;
+  o->status = cv.take<RerankStatus>(1);
+  o->fb_rows = cv.take<int>(o->fb_cap);
+  o->fb_d2 = cv.take<float>((size_t)o->fb_cap * o->fb_splits * k);
+  o->fb_idx = cv.take<int>((size_t)o->fb_cap * o->fb_splits * k);
+  return cv.off + 256;
+}
+
+extern "C" size_t exb_knn_rerank_lists_workspace_bytes(int64_t nq, int64_t nb, int k) {
+  if (nq <= 0 || nb <= 0 || k < 1 || k > SCR_MAX_K) return 0;
+  RerankListsWs w;
+  return carve_rerank_lists(nullptr, nq, nb, k, &w);
+}
+
+extern "C" int exb_knn_rerank_lists_f32(const float* src, int64_t nq, const float* bank,
+                                        int64_t nb, int dim, int k, int n_shards,
+                                        int lists_per_shard, const float* cand_val,
+                                        const int32_t* cand_idx, const int32_t* cand_cnt,
+                                        const int32_t* host_shard_lo, const float* ha,
+                                        const float* ea, const void* scalars, float* out_dist,
+                                        int32_t* out_idx, void* workspace, size_t workspace_bytes,
+                                        exb_stream_t stream) {
+  EXB_CHECK_ARG(src && bank && cand_val && cand_idx && cand_cnt && host_shard_lo && ha && ea &&
+                    scalars && out_dist && out_idx, "null pointer");
+  EXB_CHECK_ARG(nq > 0 && nb > 0 && nq < (1LL << 31) && nb < (1LL << 31), "bad row counts");
+  EXB_CHECK_ARG(dim >= 1 && dim <= EXB_SCREEN_MAX_DIM && k >= 1 && k <= SCR_MAX_K,
+                "unsupported dim=%d or k=%d", dim, k);
+  EXB_CHECK_ARG(n_shards >= 1 && lists_per_shard >= 1 && n_shards * lists_per_shard <= 16,
+                "n_shards x lists_per_shard = %d x %d exceeds the 16 lists a row can gather",
+                n_shards, lists_per_shard);
+  if (k > nb) {
+    set_error("selected index k out of range (k=%d > bank rows=%lld)", k, (long long)nb);
+    return EXB_EKRANGE;
+  }
+  RerankListsWs w;
+  const size_t need = carve_rerank_lists(nullptr, nq, nb, k, &w);
+  EXB_CHECK_ARG(workspace && workspace_bytes >= need, "workspace too small: %zu < %zu",
+                workspace_bytes, need);
+  EXB_CHECK_ARG(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  carve_rerank_lists(workspace, nq, nb, k, &w);
+  cudaStream_t st = (cudaStream_t)stream;
+  EXB_CUDA(cudaMemsetAsync(w.status, 0, 256, st));
+  const bool vec = (dim % 4 == 0) && (((uintptr_t)src | (uintptr_t)bank) & 15) == 0;
+  const int ni = vec ? (dim + 127) / 128 : 0;
+  RerankParams rp;
+  memset(&rp, 0, sizeof(rp));
+  rp.Q = src; rp.B = bank; rp.nq = nq; rp.nb = nb; rp.dim = dim; rp.k = k; rp.idx_base = 0;
+  rp.splits = n_shards * lists_per_shard;
+  rp.lists_per_shard = lists_per_shard;
+  rp.shard_rows = nq;
+  for (int i = 0; i < 16; ++i) rp.shard_lo[i] = i < n_shards ? host_shard_lo[i] : 0;
+  rp.cand_val = cand_val; rp.cand_idx = cand_idx; rp.cand_cnt = cand_cnt;
+  rp.ha = ha; rp.ea = ea;
+  rp.qsc = static_cast<const PrepScalars*>(scalars);
+  rp.bsc = rp.qsc;
+  rp.out_dist = out_dist; rp.out_idx = out_idx;
+  rp.fallback_rows = w.fb_rows; rp.fallback_cap = w.fb_cap; rp.status = w.status;
+  launch_rerank<false>(rp, (unsigned)((nq + RR_WARPS - 1) / RR_WARPS), ni, st);
+  EXB_LAUNCH_CHECK();
+  // undecided rows: exact kernel against the WHOLE bank (every rank holds it)
+  return launch_exact(src, nq, bank, nb, dim, k, 0, out_dist, out_idx, w.fb_d2, w.fb_idx,
+                      w.fb_splits, w.fb_rows, &w.status->n_fallback, w.fb_cap, st);
 }
 
 // ------------------------------------------------------------------------------------------

@@ -75,6 +75,75 @@ def knn_topk(source, target, k, idx_base=0, mode="auto"):
     return dist, idx
 
 
+SCREEN_CAP = 24   # EXB_SCREEN_CAP: candidate slots per list
+
+
+def screen_lists_count(nq, nb, dim, k):
+    """Candidate lists per (query, shard) the screen-only form produces; 0 = not available for
+    these sizes (per-update inputs use the fused chain instead)."""
+    if dim > _lib.SCREEN_MAX_DIM or k > _lib.SCREEN_MAX_K:
+        return 0
+    return int(_lib.load().exb_knn_screen_lists_count(nq, nb, dim, k))
+
+
+def knn_screen_lists(source, bank, k):
+    """Screen every `source` row against `bank` (one shard) and stop: returns
+    (val (nq, L, 24) f32, idx (nq, L, 24) i32 local to bank, cnt (nq, L) i32, ha (nq,), ea (nq,),
+    scalars (4,) i32 view of {err_max, hn_max, range_flag, 0}).  exb_knn_screen_lists_f32."""
+    lib = _lib.load()
+    src = _as_rows(source, "source")
+    same = bank is source
+    tgt = src if same else _as_rows(bank, "bank")
+    nq, nb, dim = src.size(0), tgt.size(0), src.size(1)
+    k = int(k)
+    if k > nb:
+        raise RuntimeError("selected index k out of range")
+    lists = screen_lists_count(nq, nb, dim, k)
+    if lists == 0:
+        raise ValueError(f"exorl_b200: no screen-only form for nq={nq}, nb={nb}, dim={dim}, k={k}")
+    dev = src.device
+    with torch.cuda.device(dev):
+        val = torch.empty(nq, lists, SCREEN_CAP, dtype=torch.float32, device=dev)
+        idx = torch.empty(nq, lists, SCREEN_CAP, dtype=torch.int32, device=dev)
+        cnt = torch.empty(nq, lists, dtype=torch.int32, device=dev)
+        ha = torch.empty(nq, dtype=torch.float32, device=dev)
+        ea = torch.empty(nq, dtype=torch.float32, device=dev)
+        sc = torch.empty(4, dtype=torch.int32, device=dev)
+        need = lib.exb_knn_screened_workspace_bytes(nq, nb, dim, k)
+        ws, _ = _lib.Workspace.get(dev, "knn_screened", need)
+        _lib.check(lib.exb_knn_screen_lists_f32(
+            _lib.ptr(src), nq, _lib.ptr(tgt), nb, dim, k, int(same), _lib.ptr(val), _lib.ptr(idx),
+            _lib.ptr(cnt), _lib.ptr(ha), _lib.ptr(ea), _lib.ptr(sc), _lib.ptr(ws), ws.numel(),
+            _lib.stream_ptr(dev)))
+    return val, idx, cnt, ha, ea, sc
+
+
+def knn_rerank_lists(source, bank, k, val, idx, cnt, shard_lo, ha, ea, scalars):
+    """Exact top-k of `source` rows (a query block) from the candidate lists of all shards:
+    val/idx (G, nq, L, 24), cnt (G, nq, L), shard_lo = first bank row of every shard, `bank` the
+    whole fp32 bank, scalars the MAX-combined (4,) i32 word.  exb_knn_rerank_lists_f32."""
+    lib = _lib.load()
+    src = _as_rows(source, "source")
+    tgt = src if bank is source else _as_rows(bank, "bank")
+    nq, nb, dim = src.size(0), tgt.size(0), src.size(1)
+    g, lists = val.size(0), val.size(2)
+    if val.size(1) != nq or cnt.shape != (g, nq, lists) or len(shard_lo) != g:
+        raise ValueError("candidate lists do not match the query block / shard count")
+    dev = src.device
+    lo = (ctypes.c_int32 * g)(*[int(x) for x in shard_lo])
+    with torch.cuda.device(dev):
+        dist = torch.empty(nq, k, dtype=torch.float32, device=dev)
+        out_i = torch.empty(nq, k, dtype=torch.int32, device=dev)
+        need = lib.exb_knn_rerank_lists_workspace_bytes(nq, nb, int(k))
+        ws, _ = _lib.Workspace.get(dev, "knn_rerank_lists", need)
+        _lib.check(lib.exb_knn_rerank_lists_f32(
+            _lib.ptr(src), nq, _lib.ptr(tgt), nb, dim, int(k), g, lists,
+            _lib.ptr(val.contiguous()), _lib.ptr(idx.contiguous()), _lib.ptr(cnt.contiguous()),
+            lo, _lib.ptr(ha.contiguous()), _lib.ptr(ea.contiguous()), _lib.ptr(scalars),
+            _lib.ptr(dist), _lib.ptr(out_i), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+    return dist, out_i
+
+
 def _screen_ok(nq, nb, dim, k):
     return (dim <= _lib.SCREEN_MAX_DIM and k <= _lib.SCREEN_MAX_K and nq >= 128 and nb >= 256)
 

@@ -9,6 +9,13 @@ reference formula cannot be evaluated (it materialises an (N, N, c) tensor); SUR
                                N rows (north_star's formulation), or
                "all_to_all"  — rank r receives the G lists of query block r only, merges N/G
                                rows, and the RMS sums are all-reduced (8x less traffic/merge work)
+               "lists"       — step 1 stops after the tensor-core screen; the CANDIDATE lists of
+                               query block r go to rank r (all-to-all), which recomputes them
+                               exactly against the whole fp32 bank it holds anyway: the exact
+                               recompute runs once per query instead of once per (query, shard)
+                               and there is no merge
+               "auto"        — "lists" when the screen-only form exists for the sizes, else
+                               "all_to_all"
   3. one global RMS update with bs = N*k (or N), then the epilogue
   4. all_to_all only: rewards all-gathered so every rank returns the full (N, 1).
 
@@ -19,7 +26,8 @@ import torch
 import torch.distributed as dist
 
 from . import _lib
-from .knn import knn_topk, _reward_from_knn, _pbe_ws
+from .knn import (knn_topk, _reward_from_knn, _pbe_ws, knn_screen_lists, knn_rerank_lists,
+                  screen_lists_count)
 
 
 def shard_bounds(n, world, rank):
@@ -79,8 +87,26 @@ def _cuda_finish(knn_dist, k, avg, use_rms, clip, sums, rms):
     return out
 
 
+def _cuda_screen_lists(rep, lo, hi, k):
+    bank = rep if (lo == 0 and hi == rep.size(0)) else rep[lo:hi]
+    return knn_screen_lists(rep, bank, k)
+
+
+def _cuda_rerank_lists(rep, lo, hi, k, val, idx, cnt, shard_lo, ha, ea, sc):
+    return knn_rerank_lists(rep[lo:hi], rep, k, val, idx, cnt, shard_lo, ha, ea, sc)
+
+
+def _cuda_lists_available(n, nb, dim, k, world):
+    """Candidate lists per (row, shard) of the screen-only form, 0 if it cannot be used."""
+    lists = screen_lists_count(n, nb, dim, k)
+    return lists if 0 < lists * world <= 16 else 0
+
+
 class _CudaStages:
     local_knn = staticmethod(_cuda_local_knn)
+    screen_lists = staticmethod(_cuda_screen_lists)
+    rerank_lists = staticmethod(_cuda_rerank_lists)
+    lists_available = staticmethod(_cuda_lists_available)
     merge = staticmethod(_cuda_merge)
     sums = staticmethod(_cuda_sums)
     finish = staticmethod(_cuda_finish)
@@ -109,15 +135,42 @@ class StageTimer:
         return out
 
 
-def relabel_apt_reward(rep, args, rms=None, group=None, exchange="all_to_all", mode="auto",
+def _finish_block(d_mine, i_mine, n, lo, hi, in_split, world, k, avg, use_rms, clip, rms, group,
+                  stages, tm, return_knn):
+    """Global RMS update from all-reduced sums, epilogue of this rank's query block, rewards
+    all-gathered so that every rank returns the full (N, 1)."""
+    my_n = hi - lo
+    sums = None
+    if use_rms:
+        sums = stages.sums(d_mine, k, avg)                      # {count, sum, sumsq} of my block
+        dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
+    tm("rms_allreduce")
+    r_mine = stages.finish(d_mine, k, avg, use_rms, clip, sums, rms)
+    tm("finish")
+    if use_rms:
+        rms.n += n * k if avg else n
+    # variable block sizes: gather padded to the largest block
+    mx = max(in_split)
+    pad = torch.zeros((mx, 1), dtype=r_mine.dtype, device=r_mine.device)
+    pad[:my_n] = r_mine
+    gathered = torch.empty((world * mx, 1), dtype=r_mine.dtype, device=r_mine.device)
+    dist.all_gather_into_tensor(gathered, pad, group=group)
+    reward = torch.cat([gathered[r * mx:r * mx + in_split[r]] for r in range(world)], dim=0)
+    tm("reward_allgather")
+    if return_knn:
+        return reward, d_mine, i_mine
+    return reward
+
+
+def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="auto",
                        return_knn=False, stages=_CudaStages, timer=None):
     """APT reward (N, 1) of every row of `rep` against all N rows, identical on every rank.
 
     `args` exposes knn_k, knn_avg, knn_rms, knn_clip like PBE; `rms` is the running-moment state
     (updated once with bs = N*k in avg mode, N otherwise).  Works without an initialised process
     group (single shard)."""
-    if exchange not in ("all_gather", "all_to_all"):
-        raise ValueError("exchange must be 'all_gather' or 'all_to_all'")
+    if exchange not in ("auto", "lists", "all_gather", "all_to_all"):
+        raise ValueError("exchange must be 'auto', 'lists', 'all_gather' or 'all_to_all'")
     if rms is None:
         rms = getattr(args, "rms", None)
     k, avg, use_rms, clip = int(args.knn_k), bool(args.knn_avg), bool(args.knn_rms), args.knn_clip
@@ -131,6 +184,45 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="all_to_all", m
 
     tm = timer.mark if timer is not None else (lambda name: None)
     tm("start")
+    if world > 1 and exchange in ("auto", "lists"):
+        cnt = 0
+        if mode != "exact" and hasattr(stages, "lists_available"):
+            cnt = int(stages.lists_available(n, hi - lo, rep[0].numel(), k, world))
+        # every rank must take the same branch with the same list count (shard sizes differ by
+        # up to one row, which can change the kernel variant): agree on min and max
+        flag = torch.tensor([cnt, -cnt], device=rep.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        lo_cnt, hi_cnt = (int(v) for v in flag.tolist())
+        ok = lo_cnt > 0 and lo_cnt == -hi_cnt
+        if exchange == "lists" and not ok:
+            raise ValueError("exchange='lists' is not available for these sizes / this mode")
+        exchange = "lists" if ok else "all_to_all"
+    elif exchange == "auto":
+        exchange = "all_to_all"
+
+    if world > 1 and exchange == "lists":
+        bounds = [shard_bounds(n, world, r) for r in range(world)]
+        in_split = [(b - a) for a, b in bounds]
+        my_n = hi - lo
+        val, idx, cnt, ha, ea, sc = stages.screen_lists(rep, lo, hi, k)   # (N, L, 24) / (N, L)
+        tm("screen")
+        lists = val.size(1)
+        r_val = torch.empty((world * my_n, *val.shape[1:]), dtype=val.dtype, device=val.device)
+        r_idx = torch.empty((world * my_n, *idx.shape[1:]), dtype=idx.dtype, device=idx.device)
+        r_cnt = torch.empty((world * my_n, lists), dtype=cnt.dtype, device=cnt.device)
+        dist.all_to_all_single(r_val, val, [my_n] * world, in_split, group=group)
+        dist.all_to_all_single(r_idx, idx, [my_n] * world, in_split, group=group)
+        dist.all_to_all_single(r_cnt, cnt, [my_n] * world, in_split, group=group)
+        dist.all_reduce(sc, op=dist.ReduceOp.MAX, group=group)   # int32 view of >= 0 floats
+        tm("all_to_all")
+        d_mine, i_mine = stages.rerank_lists(
+            rep, lo, hi, k, r_val.view(world, my_n, *val.shape[1:]),
+            r_idx.view(world, my_n, *idx.shape[1:]), r_cnt.view(world, my_n, lists),
+            [a for a, _ in bounds], ha[lo:hi], ea[lo:hi], sc)
+        tm("rerank")
+        return _finish_block(d_mine, i_mine, n, lo, hi, in_split, world, k, avg, use_rms, clip, rms,
+                             group, stages, tm, return_knn)
+
     d_loc, i_loc = stages.local_knn(rep, lo, hi, k, mode)      # (N, k) exact, global ids
     tm("local_knn")
     if world == 1:
@@ -157,23 +249,5 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="all_to_all", m
     tm("all_to_all")
     d_mine, i_mine = stages.merge(d_blk.view(world, my_n, k), i_blk.view(world, my_n, k), k)
     tm("merge")
-    sums = None
-    if use_rms:
-        sums = stages.sums(d_mine, k, avg)                      # {count, sum, sumsq} of my block
-        dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
-    tm("rms_allreduce")
-    r_mine = stages.finish(d_mine, k, avg, use_rms, clip, sums, rms)
-    tm("finish")
-    if use_rms:
-        rms.n += n * k if avg else n
-    # variable block sizes: gather padded to the largest block
-    mx = max(in_split)
-    pad = torch.zeros((mx, 1), dtype=r_mine.dtype, device=r_mine.device)
-    pad[:my_n] = r_mine
-    gathered = torch.empty((world * mx, 1), dtype=r_mine.dtype, device=r_mine.device)
-    dist.all_gather_into_tensor(gathered, pad, group=group)
-    reward = torch.cat([gathered[r * mx:r * mx + in_split[r]] for r in range(world)], dim=0)
-    tm("reward_allgather")
-    if return_knn:
-        return reward, d_mine, i_mine
-    return reward
+    return _finish_block(d_mine, i_mine, n, lo, hi, in_split, world, k, avg, use_rms, clip, rms,
+                         group, stages, tm, return_knn)

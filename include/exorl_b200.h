@@ -118,6 +118,35 @@ int exb_topk_merge(const float* dist_lists, const int32_t* idx_lists, int n_list
                    int k, float* out_dist, int32_t* out_idx, exb_stream_t stream);
 
 /* --------------------------------------------------------------------------------------------
+ * Sharded kNN, "exchange the candidate lists" form (SURVEY.md §8e refinement): a rank screens all
+ * queries against ITS bank shard and stops there (exb_knn_screen_lists_f32); ranks all-to-all the
+ * lists by query block; each rank then reranks the lists of ALL shards for its own query block
+ * against the whole fp32 bank (exb_knn_rerank_lists_f32) — the exact recompute and the top-k
+ * selection are done once per query instead of once per (query, shard), and no merge is needed.
+ *   lists per row and shard: exb_knn_screen_lists_count (0 = inputs too small for this form);
+ *   out_val/out_idx [nq, lists, EXB_SCREEN_CAP] (indices local to `bank`), out_cnt [nq, lists]
+ *   (-1 = the row is undecided), out_ha/out_ea [nq] query half norms / rounding errors,
+ *   out_scalars 16 device bytes {float err_max, float hn_max, int range_flag, int 0}: combine
+ *   across ranks with an element-wise MAX over the int32 view before the rerank.
+ *   Rerank inputs are laid out [n_shards, nq, lists_per_shard, ...] (the all-to-all receive
+ *   buffer), host_shard_lo[s] = first bank row of shard s; rows that stay undecided are
+ *   recomputed by the exact kernel against the whole bank.  Same results as exb_knn_exact_f32.
+ * ------------------------------------------------------------------------------------------ */
+int exb_knn_screen_lists_count(int64_t nq, int64_t nb, int dim, int k);
+int exb_knn_screen_lists_f32(const float* src, int64_t nq, const float* bank, int64_t nb, int dim,
+                             int k, int src_is_bank, float* out_val, int32_t* out_idx,
+                             int32_t* out_cnt, float* out_ha, float* out_ea, void* out_scalars,
+                             void* workspace /* exb_knn_screened_workspace_bytes */,
+                             size_t workspace_bytes, exb_stream_t stream);
+size_t exb_knn_rerank_lists_workspace_bytes(int64_t nq, int64_t nb, int k);
+int exb_knn_rerank_lists_f32(const float* src, int64_t nq, const float* bank, int64_t nb, int dim,
+                             int k, int n_shards, int lists_per_shard, const float* cand_val,
+                             const int32_t* cand_idx, const int32_t* cand_cnt,
+                             const int32_t* host_shard_lo, const float* ha, const float* ea,
+                             const void* scalars, float* out_dist, int32_t* out_idx,
+                             void* workspace, size_t workspace_bytes, exb_stream_t stream);
+
+/* --------------------------------------------------------------------------------------------
  * RMS state + PBE epilogue.  Replaces utils/utils.py:264-276 (RMS.__call__) and :301-318.
  *   knn_dist [nq,k] ascending.  avg != 0: all nq*k values enter the running moments and the
  *   reward is the mean over k; avg == 0: column k-1 only.  use_rms: update state (M,S,n) then

@@ -68,3 +68,46 @@ def test_medium_bank_screened_equals_exact_kernel():
     sub = torch.arange(0, n, n // 256)[:256]
     od, oi = knn_smallest(x[sub], x, 12)
     assert_knn_matches(x[sub], x, 12, d_s[sub.to(DEV)], i_s[sub.to(DEV)], oracle=(od, oi))
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_lists_exchange_form_equals_exact_kernel(world):
+    """'lists' exchange on one device with virtual shards: screen-only per shard
+    (exb_knn_screen_lists_f32), lists regrouped by query block as the all-to-all would, exact
+    rerank per block against the whole bank (exb_knn_rerank_lists_f32) == the fp32 exact kernel;
+    a 200-query subset is checked against the oracle."""
+    from exorl_b200 import knn as xknn
+    n, dim, k = 40000, 64, 12
+    x = reps(7, n, dim)
+    xd = x.to(DEV)
+    bounds = [shard_bounds(n, world, r) for r in range(world)]
+    per_shard = []
+    sc = None
+    for lo, hi in bounds:
+        assert xknn.screen_lists_count(n, hi - lo, dim, k) * world <= 16
+        val, idx, cnt, ha, ea, s = xknn.knn_screen_lists(xd, xd[lo:hi], k)
+        per_shard.append((val.clone(), idx.clone(), cnt.clone()))
+        sc = s.clone() if sc is None else torch.maximum(sc, s)
+    d_e, i_e = xb.knn_topk(xd, xd, k, mode="exact")
+    d_all = torch.empty(n, k, device=DEV)
+    i_all = torch.empty(n, k, dtype=torch.int32, device=DEV)
+    for lo, hi in bounds:
+        val = torch.stack([p[0][lo:hi] for p in per_shard])
+        idx = torch.stack([p[1][lo:hi] for p in per_shard])
+        cnt = torch.stack([p[2][lo:hi] for p in per_shard])
+        d, i = xknn.knn_rerank_lists(xd[lo:hi], xd, k, val, idx, cnt, [a for a, _ in bounds],
+                                     ha[lo:hi], ea[lo:hi], sc)
+        d_all[lo:hi], i_all[lo:hi] = d, i
+    np.testing.assert_allclose(d_all.cpu().numpy(), d_e.cpu().numpy(), rtol=1e-6)
+    diff = (i_all.sort(dim=1).values != i_e.sort(dim=1).values).any(dim=1).sum().item()
+    assert diff <= n // 1000
+    sub = torch.arange(0, n, n // 200)[:200]
+    assert_knn_matches(x[sub], x, k, d_all[sub.to(DEV)], i_all[sub.to(DEV)])
+
+
+def test_lists_form_rejects_per_update_sizes():
+    from exorl_b200 import knn as xknn
+    assert xknn.screen_lists_count(1024, 1024, 512, 12) == 0
+    x = reps(1, 1024, 64).to(DEV)
+    with pytest.raises(ValueError):
+        xknn.knn_screen_lists(x, x, 12)

@@ -28,6 +28,52 @@ class _OracleStages:
         d, i = knn_smallest(rep, rep[lo:hi], k)
         return d, (i + lo).to(torch.int32)
 
+    # "lists" exchange: stand-ins with the CUDA contracts — per shard, every query keeps its k + 2
+    # best bank rows as (score = -dist^2, LOCAL index) in two lists of 24 slots (as the 8-warp
+    # screen does: even / odd positions), counts in cnt; the rerank merges all shards' lists.
+    @staticmethod
+    def lists_available(n, nb, dim, k, world):
+        return 2 if 2 * world <= 16 else 0
+
+    @staticmethod
+    def screen_lists(rep, lo, hi, k):
+        from oracle import knn_smallest
+        n = rep.size(0)
+        kk = min(k + 2, hi - lo)
+        d, i = knn_smallest(rep, rep[lo:hi], kk)
+        val = torch.full((n, 2, 24), -3.0e38)
+        idx = torch.zeros((n, 2, 24), dtype=torch.int32)
+        cnt = torch.zeros((n, 2), dtype=torch.int32)
+        for h in range(2):
+            sel = torch.arange(h, kk, 2)
+            val[:, h, :len(sel)] = -(d[:, sel] ** 2)
+            idx[:, h, :len(sel)] = i[:, sel].to(torch.int32)
+            cnt[:, h] = len(sel)
+        sc = torch.tensor([1, 2 + lo, 0, 0], dtype=torch.int32)     # rank-dependent: MAX-reduced
+        return val, idx, cnt, torch.zeros(n), torch.zeros(n), sc
+
+    @staticmethod
+    def rerank_lists(rep, lo, hi, k, val, idx, cnt, shard_lo, ha, ea, sc):
+        g, my_n, lists, cap = val.shape
+        assert my_n == hi - lo and len(shard_lo) == g and ha.numel() == my_n
+        assert sc.tolist()[0] == 1 and sc.tolist()[1] == 2 + max(shard_lo)   # MAX over ranks
+        q = rep[lo:hi]
+        out_d = torch.empty(my_n, k)
+        out_i = torch.empty(my_n, k, dtype=torch.int32)
+        for r in range(my_n):
+            cand = []
+            for s in range(g):
+                for h in range(lists):
+                    c = int(cnt[s, r, h])
+                    cand += [int(x) + shard_lo[s] for x in idx[s, r, h, :c]]
+            cand = torch.tensor(sorted(set(cand)))
+            dd = torch.norm(q[r][None, :] - rep[cand], dim=1, p=2)
+            key = dd.double() * 1e7 + cand.double() * 1e-3
+            pos = key.argsort()[:k]
+            out_d[r] = dd[pos]
+            out_i[r] = cand[pos].to(torch.int32)
+        return out_d, out_i
+
     @staticmethod
     def merge(d_lists, i_lists, k):
         g, n, _ = d_lists.shape
@@ -85,7 +131,7 @@ def _worker(rank, world, port, exchange, n, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("exchange", ["all_gather", "all_to_all"])
+@pytest.mark.parametrize("exchange", ["all_gather", "all_to_all", "lists", "auto"])
 @pytest.mark.parametrize("n", [64, 51])
 def test_two_rank_relabel_equals_unsharded(exchange, n):
     from oracle import RmsState, pbe_reward
