@@ -166,6 +166,10 @@ def run_ours(a, rank, world, local_rank):
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
     if world > 1:
+        # NCCL prints its version banner to STDOUT at NCCL_DEBUG=VERSION; keep stdout to the one
+        # JSON line of the contract
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.load()
     args = types.SimpleNamespace(knn_k=a.k, knn_avg=True, knn_rms=True, knn_clip=0.0)

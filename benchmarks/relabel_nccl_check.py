@@ -3,7 +3,7 @@ the bank-sharded result (both exchanges) must equal the single-shard result comp
 GPU from the same reps: identical index sets outside fp32 near-ties, rewards rel 1e-5, same RMS.
 
   python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
-      --master-port 29511 benchmarks/relabel_nccl_check.py [--n 20000] [--dim 512]
+      --master-port 29511 benchmarks/relabel_nccl_check.py [--rows 20000] [--dim 512]
 """
 import argparse
 import os
@@ -21,7 +21,7 @@ from exorl_b200.knn import knn_topk, _reward_from_knn  # noqa: E402
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=20000)
+    ap.add_argument("--rows", dest="n", type=int, default=20000)
     ap.add_argument("--dim", type=int, default=512)
     ap.add_argument("--k", type=int, default=12)
     a = ap.parse_args()
