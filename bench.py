@@ -212,7 +212,8 @@ def run_ours(a, rank, world, local_rank):
         return xb.relabel_apt_reward(rep, args, rms=rms, exchange=a.exchange, mode="screened")
 
     def step_e2e():
-        rep.copy_(rep_host, non_blocking=True)
+        # every rank copies its own rows from pinned host memory, NVLink all-gathers the rest
+        xb.reps_from_host(rep_host, out=rep)
         r = step()
         reward_host.copy_(r, non_blocking=True)
 
@@ -278,7 +279,7 @@ def run_ours(a, rank, world, local_rank):
                        "undecided_rows_last_step": und, "invalid": invalid},
             "clocks": clocks,
             "e2e": {"value": a.n * a.steps / (ms_e2e * 1e-3), "unit": UNIT,
-                    "h2d_bytes_per_step": rep_host.numel() * 4,
+                    "h2d_bytes_per_step": rep_host.numel() * 4,   # whole job: each rank its shard
                     "d2h_bytes_per_step": reward_host.numel() * 4,
                     "ms_per_step": ms_e2e / a.steps},
             "gpu_launches": launches_per_step * a.steps,

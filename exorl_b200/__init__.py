@@ -10,9 +10,9 @@ Drop-in surface of the reference's hot path:
 from .knn import RMS, PBE, compute_apt_reward, knn_topk, proto_knn_reward, proto_enqueue
 from .replay import (DeviceReplayBuffer, DeviceReplayLoader, make_replay_loader,
                      make_offline_replay_loader)
-from .relabel import relabel_apt_reward
+from .relabel import relabel_apt_reward, reps_from_host
 from .ingest import read_episode, read_episodes
 
 __all__ = ["RMS", "PBE", "compute_apt_reward", "knn_topk", "proto_knn_reward", "proto_enqueue",
            "DeviceReplayBuffer", "DeviceReplayLoader", "make_replay_loader",
-           "make_offline_replay_loader", "relabel_apt_reward", "read_episode", "read_episodes"]
+           "make_offline_replay_loader", "relabel_apt_reward", "reps_from_host", "read_episode", "read_episodes"]

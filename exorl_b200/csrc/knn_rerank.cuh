@@ -222,7 +222,7 @@ __device__ __forceinline__ void exact_scan(const float (&q)[16], const float* __
 }
 
 // One warp, one query row.  Returns (in lanes < k) the row's k smallest distances, ascending.
-template <bool LAT, int NI>
+template <bool LAT, int NI, bool SH = false>
 __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, int lane, int wib,
                                             int (&s_surv)[RR_WARPS][RR_SURV],
                                             float (&s_val)[RR_WARPS][RR_SURV]) {
@@ -265,17 +265,24 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
   // ---- everything this row needs from the screen is requested at once (one round trip): counts
   // (lane sp holds split sp, splits <= 16), per-split thresholds, the row's scalars, and all list
   // slots (entry e = lane + 32 i; slots beyond a split's count are read and masked afterwards).
-  const int lps = p.lists_per_shard;
-  auto list_base = [&](int sp) -> int64_t {   // index of list sp of this row in cand_cnt
-    const int sh = sp / lps;
-    return ((int64_t)sh * p.shard_rows + row) * lps + (sp - sh * lps);
-  };
-  const int my_cnt = (lane < splits) ? p.cand_cnt[list_base(lane)] : 0;
+  // SH (lists gathered from several shards): lane L < splits owns list L of the row and works out
+  // once where it lives (its shard's block, its slot) and the shard's index offset; the gather
+  // below fetches them by shuffle.  !SH: list sp of the row is simply row * splits + sp.
+  int64_t my_base = row * splits + lane;
+  int my_lo = 0;
+  if constexpr (SH) {
+    const int lps = p.lists_per_shard;
+    const int sh = lane / lps;
+    my_base = ((int64_t)sh * p.shard_rows + row) * lps + (lane - sh * lps);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) my_lo = (sh == i) ? p.shard_lo[i] : my_lo;
+  }
+  const int my_cnt = (lane < splits) ? p.cand_cnt[my_base] : 0;
   float my_tk = -FLT_MAX, my_tr = -FLT_MAX;
   if constexpr (LAT) {
     if (lane < splits) {
-      my_tk = p.cand_tk[list_base(lane)];
-      my_tr = p.cand_tr[list_base(lane)];
+      my_tk = p.cand_tk[my_base];
+      my_tr = p.cand_tr[my_base];
     }
   }
   const float ea_row = p.ea[row];
@@ -288,10 +295,17 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
     const int sp = e / SCR_CAP;
     ev[i] = -FLT_MAX;
     ei[i] = -1;
-    if (sp < splits) {
-      const int64_t a = list_base(sp) * SCR_CAP + (e - sp * SCR_CAP);
-      ev[i] = p.cand_val[a];
-      ei[i] = p.cand_idx[a] + p.shard_lo[sp / lps];
+    if constexpr (SH) {
+      const int64_t b = __shfl_sync(full, my_base, sp & 31);
+      const int lo = __shfl_sync(full, my_lo, sp & 31);
+      if (sp < splits) {
+        const int64_t a = b * SCR_CAP + (e - sp * SCR_CAP);
+        ev[i] = p.cand_val[a];
+        ei[i] = p.cand_idx[a] + lo;
+      }
+    } else if (sp < splits) {
+      ev[i] = p.cand_val[row * splits * SCR_CAP + e];
+      ei[i] = p.cand_idx[row * splits * SCR_CAP + e];
     }
   }
   int why = undecided ? 4 : 0;           // debug only (trace[12..15] of an undecided row)
@@ -444,7 +458,7 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
   return dist;
 }
 
-template <bool LAT, int NI>
+template <bool LAT, int NI, bool SH = false>
 __global__ void __launch_bounds__(RR_WARPS * 32)
 knn_rerank_kernel(const RerankParams p) {
   __shared__ int s_surv[RR_WARPS][RR_SURV];
@@ -453,7 +467,7 @@ knn_rerank_kernel(const RerankParams p) {
   const int64_t row = (int64_t)blockIdx.x * RR_WARPS + wib;
   const bool active = row < p.nq;
   float dist = 0.f;
-  if (active) dist = rerank_row<LAT, NI>(p, row, lane, wib, s_surv, s_val);
+  if (active) dist = rerank_row<LAT, NI, SH>(p, row, lane, wib, s_surv, s_val);
   if constexpr (LAT) {
     if (!p.pbe.on) return;
     const FusedPbe& f = p.pbe;

@@ -72,8 +72,9 @@ constexpr int SCR_SMEM_LIMIT = 232448;                  // 227 KB
 constexpr int FALLBACK_CAP = 4096;
 constexpr int FALLBACK_SPLITS = 42;   // x k <= 512 entries, the merge kernel's capacity
 // fp32 accumulation error of a <= 512-term fp16 dot product, relative to ||a^|| ||b^|| <= ha + hb:
-// 512 additions x 2^-23 per (truncating) add.
-constexpr float SCR_ACC_EPS = 1.0f / 16384.0f;
+// 512 additions x 2^-23 per (truncating) add = 2^-14, plus 2^-18 for the fp32
+// rounding of the two half norms themselves (21 roundings x 2^-24 each, for ha and for hb).
+constexpr float SCR_ACC_EPS = 1.0f / 16384.0f + 1.0f / 262144.0f;
 
 // ------------------------------------------------------------------------------------------
 // prep: fp32 rows -> padded fp16 operand, half squared norm of the rounded row, rounding error
@@ -101,7 +102,11 @@ knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
   if (row >= n) return;
   const float* xr = x + row * dim;
   __half* orow = out + row * dpad;
-  double nn = 0.0, ee = 0.0;
+  // fp32 throughout: hf * hf is exact (11-bit significands), the norm sum is rounded to nearest
+  // (its <= 21 roundings, 16 per lane + 5 tree levels, are budgeted in SCR_ACC_EPS), and the
+  // error sum is rounded UP at every step so that round_err stays a rigorous upper bound
+  // (f - hf is exact: hf is f rounded to 11 bits).
+  float nn = 0.f, ee = 0.f;
   bool bad = false;
   if constexpr (VEC) {
     const float4* x4 = reinterpret_cast<const float4*>(xr);
@@ -124,9 +129,9 @@ knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
           bad |= !(fabsf(f[j]) <= 65504.f);
           h[j] = __float2half_rn(f[j]);
           const float hf = __half2float(h[j]);
-          nn += (double)hf * (double)hf;
-          const double e = (double)f[j] - (double)hf;
-          ee += e * e;
+          nn = fmaf(hf, hf, nn);
+          const float e = f[j] - hf;
+          ee = __fmaf_ru(e, e, ee);
         }
         uint2 pk;
         pk.x = (uint32_t)__half_as_ushort(h[0]) | ((uint32_t)__half_as_ushort(h[1]) << 16);
@@ -141,21 +146,20 @@ knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
       const __half h = __float2half_rn(v);
       const float hf = __half2float(h);
       orow[c] = h;
-      nn += (double)hf * (double)hf;
-      const double e = (double)v - (double)hf;
-      ee += e * e;
+      nn = fmaf(hf, hf, nn);
+      const float e = v - hf;
+      ee = __fmaf_ru(e, e, ee);
     }
   }
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) {
     nn += __shfl_xor_sync(0xffffffffu, nn, off);
-    ee += __shfl_xor_sync(0xffffffffu, ee, off);
+    ee = __fadd_ru(ee, __shfl_xor_sync(0xffffffffu, ee, off));
   }
   bad = __any_sync(0xffffffffu, bad);
   if (lane == 0) {
-    const float hn = bad ? 0.f : (float)(0.5 * nn);
-    // round the error norm up so the bound stays rigorous after the fp32 conversion
-    const float er = bad ? INFINITY : __double2float_ru(sqrt(ee));
+    const float hn = bad ? 0.f : 0.5f * nn;
+    const float er = bad ? INFINITY : __fsqrt_ru(ee);   // rounded up: the bound stays rigorous
     half_norm[row] = hn;
     round_err[row] = er;
     if (sc) {
@@ -1092,14 +1096,14 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
   return true;
 }
 
-template <bool LAT>
+template <bool LAT, bool SH = false>
 static void launch_rerank(const RerankParams& rp, unsigned grid, int ni, cudaStream_t st) {
   switch (ni) {
-    case 1: knn_rerank_kernel<LAT, 1><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
-    case 2: knn_rerank_kernel<LAT, 2><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
-    case 3: knn_rerank_kernel<LAT, 3><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
-    case 4: knn_rerank_kernel<LAT, 4><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
-    default: knn_rerank_kernel<LAT, 0><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
+    case 1: knn_rerank_kernel<LAT, 1, SH><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
+    case 2: knn_rerank_kernel<LAT, 2, SH><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
+    case 3: knn_rerank_kernel<LAT, 3, SH><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
+    case 4: knn_rerank_kernel<LAT, 4, SH><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
+    default: knn_rerank_kernel<LAT, 0, SH><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
   }
 }
 
@@ -1535,7 +1539,7 @@ extern "C" int exb_knn_rerank_lists_f32(const float* src, int64_t nq, const floa
   rp.bsc = rp.qsc;
   rp.out_dist = out_dist; rp.out_idx = out_idx;
   rp.fallback_rows = w.fb_rows; rp.fallback_cap = w.fb_cap; rp.status = w.status;
-  launch_rerank<false>(rp, (unsigned)((nq + RR_WARPS - 1) / RR_WARPS), ni, st);
+  launch_rerank<false, true>(rp, (unsigned)((nq + RR_WARPS - 1) / RR_WARPS), ni, st);
   EXB_LAUNCH_CHECK();
   // undecided rows: exact kernel against the WHOLE bank (every rank holds it)
   return launch_exact(src, nq, bank, nb, dim, k, 0, out_dist, out_idx, w.fb_d2, w.fb_idx,

@@ -116,6 +116,30 @@ class _CudaStages:
         return _reward_from_knn(knn_dist, k, avg, use_rms, clip, rms)
 
 
+def reps_from_host(rep_host, out=None, group=None):
+    """Full (N, c) device copy of host-resident reps for a sharded relabel: every rank copies only
+    ITS rows over PCIe (pinned host memory -> asynchronous DMA) and the shards are all-gathered over
+    NVLink, instead of G ranks each pulling all N rows through the host links."""
+    distributed = dist.is_available() and dist.is_initialized()
+    world = dist.get_world_size(group) if distributed else 1
+    rank = dist.get_rank(group) if distributed else 0
+    n = rep_host.size(0)
+    if out is None:
+        out = torch.empty(rep_host.shape, dtype=rep_host.dtype,
+                          device=torch.device("cuda", torch.cuda.current_device()))
+    lo, hi = shard_bounds(n, world, rank)
+    out[lo:hi].copy_(rep_host[lo:hi], non_blocking=True)
+    if world > 1:
+        if n % world == 0:
+            dist.all_gather_into_tensor(out, out[lo:hi], group=group)     # in place
+        else:
+            for r in range(world):            # ragged shards: one broadcast per owner
+                a, b = shard_bounds(n, world, r)
+                dist.broadcast(out[a:b], src=dist.get_global_rank(group, r) if group else r,
+                               group=group)
+    return out
+
+
 class StageTimer:
     """Optional CUDA-event stopwatch for the relabel stages (bench.py --stage-times)."""
 

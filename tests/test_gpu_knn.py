@@ -312,3 +312,34 @@ def test_fused_chain_source_ne_target_and_ragged():
     got = xb.compute_apt_reward(s.to(DEV), t.to(DEV), args, rms=rms, mode="screened")
     _close(got.cpu().numpy(), want.numpy())
     _close([float(rms.M), float(rms.S)], [float(st.M), float(st.S)], rtol=2e-5)
+
+
+@pytest.mark.parametrize("n,dim", [(1000, 512), (777, 50), (64, 130)])
+def test_prep_operand_norms_and_rigorous_error_bound(n, dim):
+    """exb_knn_prep_f16: the fp16 operand is the round-to-nearest of the input, half_norm matches
+    the fp64 value to the budgeted 2^-19, and round_err is an UPPER bound of ||x - fp16(x)||
+    (the screening certificate needs the bound, not an estimate) that is tight to 1e-5."""
+    import ctypes
+    from exorl_b200 import _lib
+    lib = _lib.load()
+    x = reps(11, n, dim) * 3.0
+    xd = x.to(DEV).contiguous()
+    dpad = (dim + 63) // 64 * 64
+    out = torch.full((n, dpad), 7.0, dtype=torch.float16, device=DEV)
+    hn = torch.empty(n, device=DEV)
+    er = torch.empty(n, device=DEV)
+    sc = torch.zeros(4, dtype=torch.int32, device=DEV)
+    _lib.check(lib.exb_knn_prep_f16(_lib.ptr(xd), n, dim, _lib.ptr(out), _lib.ptr(hn),
+                                    _lib.ptr(er), _lib.ptr(sc), _lib.stream_ptr(torch.device(DEV))))
+    torch.cuda.synchronize()
+    xh = x.half()
+    assert torch.equal(out[:, :dim].cpu(), xh) and torch.all(out[:, dim:] == 0)
+    xh64 = xh.double()
+    want_hn = 0.5 * (xh64 ** 2).sum(dim=1)
+    want_er = ((x.double() - xh64) ** 2).sum(dim=1).sqrt()
+    got_hn, got_er = hn.cpu().double(), er.cpu().double()
+    assert torch.all((got_hn - want_hn).abs() <= want_hn * 2.0 ** -19)
+    assert torch.all(got_er >= want_er) and torch.all(got_er <= want_er * (1 + 1e-5) + 1e-12)
+    s = sc.cpu()
+    assert float(s[:1].view(torch.float32)) == float(er.max()) and int(s[2]) == 0
+    assert float(s[1:2].view(torch.float32)) == float(hn.max())

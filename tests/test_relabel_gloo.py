@@ -154,3 +154,32 @@ def test_two_rank_relabel_equals_unsharded(exchange, n):
         np.testing.assert_allclose(r, want, rtol=1e-5, atol=1e-7)
         assert m == pytest.approx(float(st.M), rel=1e-5) and s == pytest.approx(float(st.S), rel=1e-4)
         assert cnt == pytest.approx(st.n)
+
+
+def _host_worker(rank, world, port, n, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from exorl_b200.relabel import reps_from_host
+        g = torch.Generator().manual_seed(9)
+        host = torch.randn(n, 8, generator=g)
+        out = reps_from_host(host, out=torch.full((n, 8), float("nan")))
+        q.put((rank, bool(torch.equal(out, host))))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n", [64, 51])
+def test_reps_from_host_shards_then_gathers(n):
+    """Each rank copies only its rows and the collective fills in the rest (even and ragged)."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_host_worker, args=(r, 2, port, n, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(2)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(ok for _, ok in res)
