@@ -5,6 +5,8 @@ Drop-in surface of the reference's hot path:
   compute_apt_reward            <- the pre-refactor name of the same computation (source != target)
   proto_knn_reward, proto_enqueue <- agents/unsupervised_learning/proto.py:110-118
   make_replay_loader, make_offline_replay_loader <- utils/replay_buffer.py:246-277
+  icm_get_rep, normalize_rep    <- ICM.trunk (icm_apt.py:17-18,50-52), F.normalize (proto.py:104):
+                                   rep producers that also emit the prepared kNN operand
   read_episode(s)               <- load_episode, utils/replay_buffer.py:26-29 (native .npz reader)
 """
 from .knn import RMS, PBE, compute_apt_reward, knn_topk, proto_knn_reward, proto_enqueue
@@ -12,7 +14,9 @@ from .replay import (DeviceReplayBuffer, DeviceReplayLoader, make_replay_loader,
                      make_offline_replay_loader)
 from .relabel import relabel_apt_reward, reps_from_host
 from .ingest import read_episode, read_episodes
+from .rep import PreparedRep, icm_get_rep, ln_tanh_rep, normalize_rep, prepare_rep
 
 __all__ = ["RMS", "PBE", "compute_apt_reward", "knn_topk", "proto_knn_reward", "proto_enqueue",
            "DeviceReplayBuffer", "DeviceReplayLoader", "make_replay_loader",
-           "make_offline_replay_loader", "relabel_apt_reward", "reps_from_host", "read_episode", "read_episodes"]
+           "make_offline_replay_loader", "relabel_apt_reward", "reps_from_host", "read_episode", "read_episodes",
+           "PreparedRep", "icm_get_rep", "ln_tanh_rep", "normalize_rep", "prepare_rep"]

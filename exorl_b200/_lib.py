@@ -23,6 +23,13 @@ class NpzArray(_c.Structure):
                 ("fortran_order", _i32), ("shape", _i64 * 8), ("nbytes", _i64)]
 
 
+class Operand(_c.Structure):
+    """exb_operand: a prepared fp16 kNN operand (device pointers)."""
+    _fields_ = [("f16", _vp), ("half_norm", _vp), ("round_err", _vp), ("scalars", _vp)]
+
+
+_op_p = _c.POINTER(Operand)
+
 # name -> (restype, argtypes); mirrors include/exorl_b200.h one to one
 SIGNATURES = {
     "exb_abi_version": (_c.c_int, []),
@@ -38,6 +45,9 @@ SIGNATURES = {
     "exb_knn_screen_lists_count": (_c.c_int, [_i64, _i64, _c.c_int, _c.c_int]),
     "exb_knn_screen_lists_f32": (_c.c_int, [_vp, _i64, _vp, _i64, _c.c_int, _c.c_int, _c.c_int,
                                             _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "exb_knn_screen_lists_pre_f32": (_c.c_int, [_vp, _i64, _op_p, _vp, _i64, _op_p, _c.c_int,
+                                                _c.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz,
+                                                _vp]),
     "exb_knn_rerank_lists_workspace_bytes": (_sz, [_i64, _i64, _c.c_int]),
     "exb_knn_rerank_lists_f32": (_c.c_int, [_vp, _i64, _vp, _i64, _c.c_int, _c.c_int, _c.c_int,
                                             _c.c_int, _vp, _vp, _vp, _c.POINTER(_i32), _vp, _vp,
@@ -58,6 +68,16 @@ SIGNATURES = {
     "exb_apt_reward_f32": (_c.c_int, [_vp, _i64, _vp, _i64, _c.c_int, _c.c_int, _c.c_int, _c.c_int,
                                       _c.c_int, _c.c_int, _f32, _vp, _vp, _f64, _vp, _vp, _vp, _vp,
                                       _vp, _vp, _sz, _vp]),
+    "exb_rep_trunk_smem_bytes": (_sz, [_c.c_int, _c.c_int]),
+    "exb_rep_trunk_f32": (_c.c_int, [_vp, _i64, _c.c_int, _vp, _vp, _vp, _vp, _f32, _c.c_int,
+                                     _vp, _op_p, _vp]),
+    "exb_rep_ln_tanh_f32": (_c.c_int, [_vp, _i64, _c.c_int, _vp, _vp, _f32, _vp, _op_p, _vp]),
+    "exb_rep_normalize_f32": (_c.c_int, [_vp, _i64, _c.c_int, _f32, _vp, _op_p, _vp]),
+    "exb_knn_screened_pre_f32": (_c.c_int, [_vp, _i64, _op_p, _vp, _i64, _op_p, _c.c_int,
+                                            _c.c_int, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "exb_apt_reward_pre_f32": (_c.c_int, [_vp, _i64, _op_p, _vp, _i64, _op_p, _c.c_int, _c.c_int,
+                                          _c.c_int, _c.c_int, _f32, _vp, _vp, _f64, _vp, _vp,
+                                          _vp, _vp, _vp, _vp, _sz, _vp]),
     "exb_rms_update": (_c.c_int, [_vp, _i64, _vp, _vp, _f64, _vp, _vp, _vp, _sz, _vp]),
     "exb_take_kth": (_c.c_int, [_vp, _i64, _c.c_int, _vp, _vp]),
     "exb_replay_gather": (_c.c_int, [_vp, _i64, _c.POINTER(GatherCol), _c.c_int, _vp, _vp,

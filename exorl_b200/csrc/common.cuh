@@ -48,6 +48,15 @@ struct Carver {
 
 int sm_count();
 
+// Scalars of a prepared fp16 kNN operand (exb_knn_prep_f16 and the rep producers), max-accumulated
+// over the rows of a call; device struct, zeroed by the caller.
+struct PrepScalars {
+  float err_max;       // max_j ||x_j - fp16(x_j)||
+  float hn_max;        // max_j ||fp16(x_j)||^2 / 2
+  int range_flag;      // a value does not fit fp16 / is not finite
+  int pad;
+};
+
 // (value, index) ordering used everywhere: smaller value first, then smaller index.
 __device__ __forceinline__ bool pair_less(float va, int ia, float vb, int ib) {
   return va < vb || (va == vb && ia < ib);

@@ -33,6 +33,7 @@
 // 98 %), which under the 1 kW power cap is clock, not just bandwidth.  The first few tiles are
 // scored twice (FILT 2, 3): once only to seed the k-th-best chain from their group maxima.
 #include "common.cuh"
+#include "prep_row.cuh"
 #include "tc_ptx.cuh"
 #include <cuda.h>
 #include <cuda_fp16.h>
@@ -79,12 +80,7 @@ constexpr float SCR_ACC_EPS = 1.0f / 16384.0f + 1.0f / 262144.0f;
 // ------------------------------------------------------------------------------------------
 // prep: fp32 rows -> padded fp16 operand, half squared norm of the rounded row, rounding error
 // ------------------------------------------------------------------------------------------
-struct PrepScalars {   // device struct, zeroed per call
-  float err_max;       // max_j ||x_j - fp16(x_j)||
-  float hn_max;        // max_j ||fp16(x_j)||^2 / 2
-  int range_flag;      // a value does not fit fp16 / is not finite
-  int pad;
-};
+// PrepScalars {err_max, hn_max, range_flag, pad}: common.cuh (shared with rep_producer.cu)
 
 // One warp per row.  VEC: dim % 4 == 0 and 16-byte aligned rows -> every lane issues all of its
 // float4 loads up front (<= 4 for dim <= 512) instead of a dependent scalar loop.  A row with a
@@ -101,45 +97,24 @@ knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
   const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= n) return;
   const float* xr = x + row * dim;
-  __half* orow = out + row * dpad;
-  // fp32 throughout: hf * hf is exact (11-bit significands), the norm sum is rounded to nearest
-  // (its <= 21 roundings, 16 per lane + 5 tree levels, are budgeted in SCR_ACC_EPS), and the
-  // error sum is rounded UP at every step so that round_err stays a rigorous upper bound
-  // (f - hf is exact: hf is f rounded to 11 bits).
-  float nn = 0.f, ee = 0.f;
-  bool bad = false;
   if constexpr (VEC) {
+    // shared with the rep producers (prep_row.cuh): bit-identical operands
     const float4* x4 = reinterpret_cast<const float4*>(xr);
-    uint2* o2 = reinterpret_cast<uint2*>(orow);
-    const int nv = dim >> 2, nvp = dpad >> 2;
-    float4 v[4];
+    const int nv = dim >> 2;
+    float4 v[1][4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int c = lane + 32 * i;
-      v[i] = (c < nv) ? __ldg(x4 + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+      v[0][i] = (c < nv) ? __ldg(x4 + c) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int c = lane + 32 * i;
-      if (c < nvp) {
-        const float f[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
-        __half h[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          bad |= !(fabsf(f[j]) <= 65504.f);
-          h[j] = __float2half_rn(f[j]);
-          const float hf = __half2float(h[j]);
-          nn = fmaf(hf, hf, nn);
-          const float e = f[j] - hf;
-          ee = __fmaf_ru(e, e, ee);
-        }
-        uint2 pk;
-        pk.x = (uint32_t)__half_as_ushort(h[0]) | ((uint32_t)__half_as_ushort(h[1]) << 16);
-        pk.y = (uint32_t)__half_as_ushort(h[2]) | ((uint32_t)__half_as_ushort(h[3]) << 16);
-        o2[c] = pk;
-      }
-    }
+    const OpOut op{out, half_norm, round_err, sc, dpad};
+    emit_rows<1, 4, false>(v, lane, dim, row, 1, nullptr, op);
   } else {
+    // scalar path (dim % 4 != 0): fp32 throughout, norm sum rounded to nearest, error sum rounded
+    // UP at every step so that round_err stays a rigorous upper bound (f - hf is exact)
+    __half* orow = out + row * dpad;
+    float nn = 0.f, ee = 0.f;
+    bool bad = false;
     for (int c = lane; c < dpad; c += 32) {
       float v = (c < dim) ? xr[c] : 0.f;
       bad |= !(fabsf(v) <= 65504.f);
@@ -150,22 +125,26 @@ knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
       const float e = v - hf;
       ee = __fmaf_ru(e, e, ee);
     }
-  }
 #pragma unroll
-  for (int off = 16; off > 0; off >>= 1) {
-    nn += __shfl_xor_sync(0xffffffffu, nn, off);
-    ee = __fadd_ru(ee, __shfl_xor_sync(0xffffffffu, ee, off));
-  }
-  bad = __any_sync(0xffffffffu, bad);
-  if (lane == 0) {
-    const float hn = bad ? 0.f : 0.5f * nn;
-    const float er = bad ? INFINITY : __fsqrt_ru(ee);   // rounded up: the bound stays rigorous
-    half_norm[row] = hn;
-    round_err[row] = er;
-    if (sc) {
-      atomicMax(reinterpret_cast<int*>(&sc->err_max), __float_as_int(er));
-      atomicMax(reinterpret_cast<int*>(&sc->hn_max), __float_as_int(hn));
-      if (bad) atomicExch(&sc->range_flag, 1);
+    for (int off = 16; off > 0; off >>= 1) {
+      nn += __shfl_xor_sync(0xffffffffu, nn, off);
+      ee = __fadd_ru(ee, __shfl_xor_sync(0xffffffffu, ee, off));
+    }
+    bad = __any_sync(0xffffffffu, bad);
+    if (lane == 0) {
+      const float hn = bad ? 0.f : 0.5f * nn;
+      const float er = bad ? INFINITY : __fsqrt_ru(ee);   // rounded up: the bound stays rigorous
+      half_norm[row] = hn;
+      round_err[row] = er;
+      if (sc) {
+        int* pe = reinterpret_cast<int*>(&sc->err_max);
+        int* ph = reinterpret_cast<int*>(&sc->hn_max);
+        if (__float_as_int(er) > *reinterpret_cast<volatile int*>(pe))
+          atomicMax(pe, __float_as_int(er));
+        if (__float_as_int(hn) > *reinterpret_cast<volatile int*>(ph))
+          atomicMax(ph, __float_as_int(hn));
+        if (bad) atomicExch(&sc->range_flag, 1);
+      }
     }
   }
 }
@@ -1216,7 +1195,8 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
                          int k, int32_t idx_base, int src_is_bank, float* out_dist,
                          int32_t* out_idx, void* workspace, size_t workspace_bytes,
                          exb_stream_t stream, const FusedPbe* pbe, bool* fused,
-                         const ListsOut* lo = nullptr) {
+                         const ListsOut* lo = nullptr, const exb_operand* pre_q = nullptr,
+                         const exb_operand* pre_b = nullptr) {
   if (fused) *fused = false;
   EXB_CHECK_ARG(src && bank && (lo || (out_dist && out_idx)), "null pointer");
   EXB_CHECK_ARG(nq > 0 && nb > 0 && nq < (1LL << 31) && nb < (1LL << 31), "bad row counts");
@@ -1238,6 +1218,19 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
   EXB_CHECK_ARG(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
   carve_screen(workspace, nq, nb, pl, k, same, &w);
   cudaStream_t st = (cudaStream_t)stream;
+  // caller-prepared operands (rep producers): use them in place of the workspace copies and skip
+  // the prep launches.  The per-update chain derives the bank maxima itself (lat kernel), so its
+  // scalars stay in the workspace; the streaming path reads the producer's scalars.
+  const bool pre = pre_b != nullptr;
+  if (pre) {
+    w.b16 = static_cast<__half*>(pre_b->f16); w.hb = pre_b->half_norm; w.eb = pre_b->round_err;
+    const exb_operand* q = same ? pre_b : pre_q;
+    w.q16 = static_cast<__half*>(q->f16); w.ha = q->half_norm; w.ea = q->round_err;
+    if (!pl.lat) {
+      w.bsc = static_cast<PrepScalars*>(pre_b->scalars);
+      w.qsc = static_cast<PrepScalars*>(q->scalars);
+    }
+  }
 
   static const int trace_on = [] {
     const char* e = getenv("EXB_SCREEN_TRACE");
@@ -1265,12 +1258,17 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
       return EXB_EUNSUPPORTED;
     }
     // per-update chain: prep -> latency screen -> rerank (inline fallback); no memset, no atomics
-    int rc = launch_prep(bank, nb, dim, pl.dpad, w.b16, w.hb, w.eb, nullptr, st,
-                         reinterpret_cast<unsigned long long*>(w.status));
-    if (rc) return rc;
-    if (!same) {
-      rc = launch_prep(src, nq, dim, pl.dpad, w.q16, w.ha, w.ea, nullptr, st);
+    int rc = EXB_OK;
+    if (pre) {
+      EXB_CUDA(cudaMemsetAsync(w.status, 0, 24, st));   // what prep's zero16 does
+    } else {
+      rc = launch_prep(bank, nb, dim, pl.dpad, w.b16, w.hb, w.eb, nullptr, st,
+                       reinterpret_cast<unsigned long long*>(w.status));
       if (rc) return rc;
+      if (!same) {
+        rc = launch_prep(src, nq, dim, pl.dpad, w.q16, w.ha, w.ea, nullptr, st);
+        if (rc) return rc;
+      }
     }
     CUtensorMap tq, tb;
     rc = make_tmap(&tq, w.q16, nq, pl.dpad, SCR_M);
@@ -1318,11 +1316,14 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
 
   // header (status + scalars) is the first 3 x 256 bytes (+ the 16 debug counters when tracing)
   EXB_CUDA(cudaMemsetAsync(workspace, 0, 1024 + 64, st));
-  int rc = launch_prep(bank, nb, dim, pl.dpad, w.b16, w.hb, w.eb, w.bsc, st);
-  if (rc) return rc;
-  if (!same) {
-    rc = launch_prep(src, nq, dim, pl.dpad, w.q16, w.ha, w.ea, w.qsc, st);
+  int rc = EXB_OK;
+  if (!pre) {
+    rc = launch_prep(bank, nb, dim, pl.dpad, w.b16, w.hb, w.eb, w.bsc, st);
     if (rc) return rc;
+    if (!same) {
+      rc = launch_prep(src, nq, dim, pl.dpad, w.q16, w.ha, w.ea, w.qsc, st);
+      if (rc) return rc;
+    }
   }
 
   CUtensorMap tq, tb;
@@ -1446,6 +1447,25 @@ extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* b
                        workspace, workspace_bytes, stream, nullptr, nullptr);
 }
 
+extern "C" int exb_knn_screened_pre_f32(const float* src, int64_t nq, const exb_operand* src_op,
+                                        const float* bank, int64_t nb, const exb_operand* bank_op,
+                                        int dim, int k, int32_t idx_base, float* out_dist,
+                                        int32_t* out_idx, void* workspace, size_t workspace_bytes,
+                                        exb_stream_t stream) {
+  EXB_CHECK_ARG(bank_op && bank_op->f16 && bank_op->half_norm && bank_op->round_err &&
+                bank_op->scalars, "bank_op missing");
+  const bool same = src == bank && nq == nb && (src_op == nullptr || src_op == bank_op ||
+                                                src_op->f16 == bank_op->f16);
+  if (!same)
+    EXB_CHECK_ARG(src_op && src_op->f16 && src_op->half_norm && src_op->round_err &&
+                  src_op->scalars, "src_op missing (src is not the bank)");
+  EXB_CHECK_ARG((((uintptr_t)bank_op->f16 | (uintptr_t)(same ? bank_op : src_op)->f16) & 127) == 0,
+                "prepared fp16 operands must be 128-byte aligned (TMA)");
+  return screened_impl(src, nq, bank, nb, dim, k, idx_base, same ? 1 : 0, out_dist, out_idx,
+                       workspace, workspace_bytes, stream, nullptr, nullptr, nullptr,
+                       same ? bank_op : src_op, bank_op);
+}
+
 // ------------------------------------------------------------------------------------------
 // Sharded relabel, "exchange the candidate lists" form: screen only, then (after the exchange)
 // rerank the lists of all shards for this rank's query block.
@@ -1466,6 +1486,37 @@ extern "C" int exb_knn_screen_lists_f32(const float* src, int64_t nq, const floa
   ListsOut lo = {out_val, out_idx, out_cnt, out_ha, out_ea, out_scalars};
   return screened_impl(src, nq, bank, nb, dim, k, 0, src_is_bank, nullptr, nullptr, workspace,
                        workspace_bytes, stream, nullptr, nullptr, &lo);
+}
+
+static int check_pre_ops(const float* src, int64_t nq, const exb_operand* src_op,
+                         const float* bank, int64_t nb, const exb_operand* bank_op, bool* same) {
+  EXB_CHECK_ARG(bank_op && bank_op->f16 && bank_op->half_norm && bank_op->round_err &&
+                bank_op->scalars, "bank_op missing");
+  *same = src == bank && nq == nb && (src_op == nullptr || src_op == bank_op ||
+                                      src_op->f16 == bank_op->f16);
+  if (!*same)
+    EXB_CHECK_ARG(src_op && src_op->f16 && src_op->half_norm && src_op->round_err &&
+                  src_op->scalars, "src_op missing (src is not the bank)");
+  EXB_CHECK_ARG((((uintptr_t)bank_op->f16 | (uintptr_t)(*same ? bank_op : src_op)->f16) & 127) == 0,
+                "prepared fp16 operands must be 128-byte aligned (TMA)");
+  return EXB_OK;
+}
+
+extern "C" int exb_knn_screen_lists_pre_f32(const float* src, int64_t nq,
+                                            const exb_operand* src_op, const float* bank,
+                                            int64_t nb, const exb_operand* bank_op, int dim,
+                                            int k, float* out_val, int32_t* out_idx,
+                                            int32_t* out_cnt, float* out_ha, float* out_ea,
+                                            void* out_scalars, void* workspace,
+                                            size_t workspace_bytes, exb_stream_t stream) {
+  EXB_CHECK_ARG(out_val && out_idx && out_cnt && out_ha && out_ea && out_scalars, "null output");
+  bool same = false;
+  const int rc = check_pre_ops(src, nq, src_op, bank, nb, bank_op, &same);
+  if (rc) return rc;
+  ListsOut lo = {out_val, out_idx, out_cnt, out_ha, out_ea, out_scalars};
+  return screened_impl(src, nq, bank, nb, dim, k, 0, same ? 1 : 0, nullptr, nullptr, workspace,
+                       workspace_bytes, stream, nullptr, nullptr, &lo, same ? bank_op : src_op,
+                       bank_op);
 }
 
 struct RerankListsWs {
@@ -1560,12 +1611,13 @@ extern "C" size_t exb_apt_reward_workspace_bytes(int64_t nq, int64_t nb, int dim
   return apt_knn_ws_bytes(nq, nb, dim, k) + align_up(exb_pbe_workspace_bytes(nq, k), 256);
 }
 
-extern "C" int exb_apt_reward_f32(const float* src, int64_t nq, const float* bank, int64_t nb,
-                                  int dim, int k, int src_is_bank, int mode, int avg, int use_rms,
-                                  float clip, const float* rms_m_in, const float* rms_s_in,
-                                  double rms_n, float* rms_m_out, float* rms_s_out,
-                                  float* out_reward, float* out_dist, int32_t* out_idx,
-                                  void* workspace, size_t workspace_bytes, exb_stream_t stream) {
+static int apt_reward_impl(const float* src, int64_t nq, const float* bank, int64_t nb,
+                           int dim, int k, int src_is_bank, int mode, int avg, int use_rms,
+                           float clip, const float* rms_m_in, const float* rms_s_in,
+                           double rms_n, float* rms_m_out, float* rms_s_out,
+                           float* out_reward, float* out_dist, int32_t* out_idx,
+                           void* workspace, size_t workspace_bytes, exb_stream_t stream,
+                           const exb_operand* pre_q, const exb_operand* pre_b) {
   EXB_CHECK_ARG(src && bank && out_reward && out_dist && out_idx, "null pointer");
   EXB_CHECK_ARG(nq > 0 && nb > 0 && dim > 0, "empty input");
   EXB_CHECK_ARG(k >= 1 && k <= EXB_MAX_K, "k=%d outside [1,%d]", k, EXB_MAX_K);
@@ -1596,7 +1648,7 @@ extern "C" int exb_apt_reward_f32(const float* src, int64_t nq, const float* ban
     f.out_reward = out_reward; f.partials = nullptr;
     bool fused = false;
     rc = screened_impl(src, nq, bank, nb, dim, k, 0, src_is_bank, out_dist, out_idx, workspace,
-                       knn_bytes, stream, &f, &fused);
+                       knn_bytes, stream, &f, &fused, nullptr, pre_q, pre_b);
     if (rc || fused) return rc;
   } else {
     rc = exb_knn_exact_f32(src, nq, bank, nb, dim, k, 0, out_dist, out_idx, workspace, knn_bytes,
@@ -1605,6 +1657,38 @@ extern "C" int exb_apt_reward_f32(const float* src, int64_t nq, const float* ban
   }
   return exb_pbe_reward(out_dist, nq, k, avg, use_rms, clip, rms_m_in, rms_s_in, rms_n, rms_m_out,
                         rms_s_out, out_reward, pbe_ws, pbe_bytes, stream);
+}
+
+extern "C" int exb_apt_reward_f32(const float* src, int64_t nq, const float* bank, int64_t nb,
+                                  int dim, int k, int src_is_bank, int mode, int avg, int use_rms,
+                                  float clip, const float* rms_m_in, const float* rms_s_in,
+                                  double rms_n, float* rms_m_out, float* rms_s_out,
+                                  float* out_reward, float* out_dist, int32_t* out_idx,
+                                  void* workspace, size_t workspace_bytes, exb_stream_t stream) {
+  return apt_reward_impl(src, nq, bank, nb, dim, k, src_is_bank, mode, avg, use_rms, clip,
+                         rms_m_in, rms_s_in, rms_n, rms_m_out, rms_s_out, out_reward, out_dist,
+                         out_idx, workspace, workspace_bytes, stream, nullptr, nullptr);
+}
+
+extern "C" int exb_apt_reward_pre_f32(const float* src, int64_t nq, const exb_operand* src_op,
+                                      const float* bank, int64_t nb, const exb_operand* bank_op,
+                                      int dim, int k, int avg, int use_rms, float clip,
+                                      const float* rms_m_in, const float* rms_s_in, double rms_n,
+                                      float* rms_m_out, float* rms_s_out, float* out_reward,
+                                      float* out_dist, int32_t* out_idx, void* workspace,
+                                      size_t workspace_bytes, exb_stream_t stream) {
+  EXB_CHECK_ARG(bank_op && bank_op->f16 && bank_op->half_norm && bank_op->round_err &&
+                bank_op->scalars, "bank_op missing");
+  const bool same = src == bank && nq == nb && (src_op == nullptr || src_op == bank_op ||
+                                                src_op->f16 == bank_op->f16);
+  if (!same)
+    EXB_CHECK_ARG(src_op && src_op->f16 && src_op->half_norm && src_op->round_err &&
+                  src_op->scalars, "src_op missing (src is not the bank)");
+  EXB_CHECK_ARG((((uintptr_t)bank_op->f16 | (uintptr_t)(same ? bank_op : src_op)->f16) & 127) == 0,
+                "prepared fp16 operands must be 128-byte aligned (TMA)");
+  return apt_reward_impl(src, nq, bank, nb, dim, k, same ? 1 : 0, 2, avg, use_rms, clip, rms_m_in,
+                         rms_s_in, rms_n, rms_m_out, rms_s_out, out_reward, out_dist, out_idx,
+                         workspace, workspace_bytes, stream, same ? bank_op : src_op, bank_op);
 }
 
 extern "C" int exb_knn_screened_status_sync(const void* workspace, int32_t host_status[4],

@@ -1,0 +1,368 @@
+// Rep producers: the step immediately in front of the kNN screen.  They
+// compute the representation the reference feeds to PBE / the Proto kNN and emit, in the same
+// pass, the fp32 rep (needed by the exact rerank) AND the prepared fp16 operand + row norms that
+// exb_knn_prep_f16 would otherwise produce by re-reading the rep from HBM.
+//
+//   rep_trunk_kernel     ICM trunk  Linear(in_dim -> D) -> LayerNorm(D) -> Tanh
+//                        (agents/unsupervised_learning/icm_apt.py:17-18, get_rep :50-52)
+//   rep_ln_tanh_kernel   LayerNorm -> Tanh on given pre-activations (wide inputs: the Linear is a
+//                        library GEMM, e.g. the 39200-wide pixel encoder output)
+//   rep_normalize_kernel F.normalize(z, dim=1, p=2) (agents/unsupervised_learning/proto.py:104)
+//
+// All are HBM-write bound: per row 4*D (rep) + 2*Dpad + 8 (operand) bytes out, 4*in_dim in.
+// The operand arithmetic (fp16 rounding, half norm, rounded-up error norm) is the SAME sequence of
+// operations as knn_prep_kernel<true> in knn_screen.cu, so producer output == prep(rep) bitwise
+// (tests/test_gpu_rep.py asserts it) and the screening certificate of DESIGN.md §4 carries over.
+#include "common.cuh"
+#include "prep_row.cuh"
+#include <cuda_fp16.h>
+#include <math.h>
+#include <stdlib.h>
+
+namespace exb {
+
+constexpr int RP_WARPS = 8;
+constexpr int RP_SMEM_LIMIT = 232448;   // 227 KB
+
+// LayerNorm (biased variance, two-pass in registers) + affine + tanh on R warp-resident rows;
+// the R reductions are interleaved so that their shuffle latencies overlap.
+// torch.nn.LayerNorm semantics: y = (x - mean) / sqrt(var + eps) * weight + bias.
+template <int R, int NCH, bool FULL>
+__device__ __forceinline__ void ln_tanh_rows(float4 (&v)[R][NCH], int lane, int dim,
+                                             const float4* __restrict__ g4,
+                                             const float4* __restrict__ b4, float eps) {
+  const int nv = dim >> 2;
+  const float inv_dim = 1.0f / (float)dim;
+  float s[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    s[r] = 0.f;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i)
+      if (FULL || lane + 32 * i < nv) s[r] += (v[r][i].x + v[r][i].y) + (v[r][i].z + v[r][i].w);
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1)
+#pragma unroll
+    for (int r = 0; r < R; ++r) s[r] += __shfl_xor_sync(0xffffffffu, s[r], off);
+  float q[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const float mean = s[r] * inv_dim;
+    float2 q2 = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int i = 0; i < NCH; ++i)
+      if (FULL || lane + 32 * i < nv) {
+        v[r][i].x -= mean; v[r][i].y -= mean; v[r][i].z -= mean; v[r][i].w -= mean;
+        const float2 a = make_float2(v[r][i].x, v[r][i].y), b = make_float2(v[r][i].z, v[r][i].w);
+        q2 = __ffma2_rn(a, a, q2);
+        q2 = __ffma2_rn(b, b, q2);
+      }
+    q[r] = q2.x + q2.y;
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1)
+#pragma unroll
+    for (int r = 0; r < R; ++r) q[r] += __shfl_xor_sync(0xffffffffu, q[r], off);
+  float rstd[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) rstd[r] = rsqrtf(fmaf(q[r], inv_dim, eps));
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    const int c = lane + 32 * i;
+    if (FULL || c < nv) {
+      const float4 g = __ldg(g4 + c), b = __ldg(b4 + c);
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        v[r][i].x = tanhf(fmaf(v[r][i].x * rstd[r], g.x, b.x));
+        v[r][i].y = tanhf(fmaf(v[r][i].y * rstd[r], g.y, b.y));
+        v[r][i].z = tanhf(fmaf(v[r][i].z * rstd[r], g.z, b.z));
+        v[r][i].w = tanhf(fmaf(v[r][i].w * rstd[r], g.w, b.w));
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// ICM trunk, narrow input (in_dim * (D + 8 R) * 4 bytes of shared memory): persistent blocks,
+// W^T resident in shared memory as [in_dim][D/4] float4, each warp computes R rows at a time so
+// that one shared-memory read of W feeds R FMAs; the FMAs are packed (FFMA2: two fp32 FMAs per
+// issue slot — the fp32 pipe takes one plain FFMA per two cycles and SMSP).  Linear = bias +
+// sequential fma over the input columns (fp32, like the reference's addmm up to summation order).
+// ------------------------------------------------------------------------------------------
+template <int R, int NCH, bool FULL>
+__global__ void __launch_bounds__(RP_WARPS * 32, R <= 4 ? 2 : 1)
+rep_trunk_kernel(const float* __restrict__ obs, int64_t n, int in_dim,
+                 const float* __restrict__ W, const float* __restrict__ bias,
+                 const float* __restrict__ ln_w, const float* __restrict__ ln_b, float eps,
+                 int dim, float* __restrict__ out_rep, OpOut op) {
+  extern __shared__ float4 rp_smem[];
+  const int nv = dim >> 2;
+  float4* Wt = rp_smem;                                        // [in_dim][nv]
+  float* obs_all = reinterpret_cast<float*>(Wt + (size_t)in_dim * nv);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* obs_s = obs_all + (size_t)warp * in_dim * R;          // [in_dim][R]
+  {
+    float* wt = reinterpret_cast<float*>(Wt);
+    const int total = in_dim * dim;
+    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+      const int kk = i / dim, d = i - kk * dim;                // shared-memory-coalesced order
+      wt[i] = __ldg(W + (size_t)d * in_dim + kk);
+    }
+  }
+  __syncthreads();
+  const float4* b4 = reinterpret_cast<const float4*>(bias);
+  const float4* g4 = reinterpret_cast<const float4*>(ln_w);
+  const float4* be4 = reinterpret_cast<const float4*>(ln_b);
+  const int64_t groups = (n + R - 1) / R;
+  for (int64_t grp = (int64_t)blockIdx.x * RP_WARPS + warp; grp < groups;
+       grp += (int64_t)gridDim.x * RP_WARPS) {
+    const int64_t row0 = grp * R;
+    const int rows = (int)((n - row0) < R ? (n - row0) : R);
+    const float* src = obs + row0 * in_dim;
+    for (int i = lane; i < R * in_dim; i += 32) {
+      const int r = i / in_dim, kk = i - r * in_dim;
+      obs_s[kk * R + r] = (r < rows) ? __ldg(src + i) : 0.f;
+    }
+    __syncwarp();
+    float4 acc[R][NCH];
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      const int c = lane + 32 * i;
+      const float4 bv = (FULL || c < nv) ? __ldg(b4 + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int r = 0; r < R; ++r) acc[r][i] = bv;
+    }
+#pragma unroll 2
+    for (int kk = 0; kk < in_dim; ++kk) {
+      float4 w[NCH];
+#pragma unroll
+      for (int i = 0; i < NCH; ++i) {
+        const int c = lane + 32 * i;
+        w[i] = (FULL || c < nv) ? Wt[kk * nv + c] : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      float o[R];
+#pragma unroll
+      for (int r4 = 0; r4 < R / 4; ++r4) {
+        const float4 t = reinterpret_cast<const float4*>(obs_s + kk * R)[r4];
+        o[4 * r4] = t.x; o[4 * r4 + 1] = t.y; o[4 * r4 + 2] = t.z; o[4 * r4 + 3] = t.w;
+      }
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const float2 oo = make_float2(o[r], o[r]);
+#pragma unroll
+        for (int i = 0; i < NCH; ++i) {
+          const float2 lo = __ffma2_rn(oo, make_float2(w[i].x, w[i].y),
+                                       make_float2(acc[r][i].x, acc[r][i].y));
+          const float2 hi = __ffma2_rn(oo, make_float2(w[i].z, w[i].w),
+                                       make_float2(acc[r][i].z, acc[r][i].w));
+          acc[r][i] = make_float4(lo.x, lo.y, hi.x, hi.y);
+        }
+      }
+    }
+    __syncwarp();   // obs_s is restaged by the next group
+    ln_tanh_rows<R, NCH, FULL>(acc, lane, dim, g4, be4, eps);
+    emit_rows<R, NCH, FULL>(acc, lane, dim, row0, rows, out_rep, op);
+  }
+}
+
+// LayerNorm -> Tanh on given pre-activations, one warp per row (in place allowed).
+template <int NCH>
+__global__ void __launch_bounds__(RP_WARPS * 32)
+rep_ln_tanh_kernel(const float* __restrict__ pre, int64_t n, int dim,
+                   const float* __restrict__ ln_w, const float* __restrict__ ln_b, float eps,
+                   float* out_rep, OpOut op) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * RP_WARPS + (threadIdx.x >> 5);
+  if (row >= n) return;
+  const int nv = dim >> 2;
+  const float4* x4 = reinterpret_cast<const float4*>(pre + row * dim);
+  float4 v[1][NCH];
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    const int c = lane + 32 * i;
+    v[0][i] = (c < nv) ? x4[c] : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  ln_tanh_rows<1, NCH, false>(v, lane, dim, reinterpret_cast<const float4*>(ln_w),
+                              reinterpret_cast<const float4*>(ln_b), eps);
+  emit_rows<1, NCH, false>(v, lane, dim, row, 1, out_rep, op);
+}
+
+// F.normalize(x, dim=1, p=2, eps): x / max(||x||_2, eps), one warp per row (in place allowed).
+template <int NCH>
+__global__ void __launch_bounds__(RP_WARPS * 32)
+rep_normalize_kernel(const float* __restrict__ x, int64_t n, int dim, float eps, float* out_rep,
+                     OpOut op) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * RP_WARPS + (threadIdx.x >> 5);
+  if (row >= n) return;
+  const int nv = dim >> 2;
+  const float4* x4 = reinterpret_cast<const float4*>(x + row * dim);
+  float4 v[1][NCH];
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    const int c = lane + 32 * i;
+    v[0][i] = (c < nv) ? x4[c] : make_float4(0.f, 0.f, 0.f, 0.f);
+    ss = fmaf(v[0][i].x, v[0][i].x, ss); ss = fmaf(v[0][i].y, v[0][i].y, ss);
+    ss = fmaf(v[0][i].z, v[0][i].z, ss); ss = fmaf(v[0][i].w, v[0][i].w, ss);
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
+  const float den = fmaxf(sqrtf(ss), eps);
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    v[0][i].x = v[0][i].x / den; v[0][i].y = v[0][i].y / den;
+    v[0][i].z = v[0][i].z / den; v[0][i].w = v[0][i].w / den;
+  }
+  emit_rows<1, NCH, false>(v, lane, dim, row, 1, out_rep, op);
+}
+
+static int make_op(const exb_operand* o, int dim, OpOut* out) {
+  out->f16 = nullptr; out->hn = nullptr; out->er = nullptr; out->sc = nullptr;
+  out->dpad = (dim + 63) / 64 * 64;
+  if (o == nullptr) return EXB_OK;
+  EXB_CHECK_ARG(o->f16 && o->half_norm && o->round_err && o->scalars,
+                "exb_operand with a null member");
+  EXB_CHECK_ARG(((uintptr_t)o->f16 & 15) == 0, "operand rows must be 16-byte aligned");
+  out->f16 = static_cast<__half*>(o->f16);
+  out->hn = o->half_norm;
+  out->er = o->round_err;
+  out->sc = static_cast<PrepScalars*>(o->scalars);
+  return EXB_OK;
+}
+
+static int check_rep_args(const void* in, int64_t n, int dim, float* out_rep,
+                          const exb_operand* op) {
+  EXB_CHECK_ARG(in && n > 0, "bad arguments");
+  EXB_CHECK_ARG(out_rep || op, "nothing to produce: out_rep and out_op are both null");
+  if (dim < 4 || dim > EXB_SCREEN_MAX_DIM || (dim & 3)) {
+    set_error("rep producers support rep_dim %% 4 == 0, 4 <= rep_dim <= %d (got %d)",
+              EXB_SCREEN_MAX_DIM, dim);
+    return EXB_EUNSUPPORTED;
+  }
+  EXB_CHECK_ARG((((uintptr_t)in | (uintptr_t)out_rep) & 15) == 0, "rows must be 16-byte aligned");
+  return EXB_OK;
+}
+
+}  // namespace exb
+
+using namespace exb;
+
+extern "C" size_t exb_rep_trunk_smem_bytes(int in_dim, int rep_dim) {
+  return (size_t)in_dim * ((size_t)rep_dim + RP_WARPS * 8) * sizeof(float);
+}
+
+template <int R>
+static int launch_trunk(const float* obs, int64_t n, int in_dim, const float* W, const float* b,
+                        const float* g, const float* be, float eps, int dim, float* out_rep,
+                        const OpOut& op, cudaStream_t st) {
+  const size_t smem = (size_t)in_dim * ((size_t)dim + RP_WARPS * R) * sizeof(float);
+  const int nch = (dim / 4 + 31) / 32;
+  const int64_t groups = (n + R - 1) / R;
+  int64_t blocks = (groups + RP_WARPS - 1) / RP_WARPS;
+  const int sms = sm_count();
+  // persistent: as many blocks per SM as registers / shared memory allow (R = 4: two)
+  const int per_sm = (R <= 4 && 2 * (smem + 1024) <= (size_t)RP_SMEM_LIMIT) ? 2 : 1;
+  if (blocks > (int64_t)sms * per_sm) blocks = (int64_t)sms * per_sm;
+#define EXB_TRUNK_CASE(KEY, NCH, FULL)                                                          \
+  case KEY: {                                                                                   \
+    static bool attr = false;                                                                   \
+    if (!attr) {                                                                                \
+      EXB_CUDA(cudaFuncSetAttribute(rep_trunk_kernel<R, NCH, FULL>,                             \
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, RP_SMEM_LIMIT)); \
+      attr = true;                                                                              \
+    }                                                                                           \
+    rep_trunk_kernel<R, NCH, FULL><<<(unsigned)blocks, RP_WARPS * 32, smem, st>>>(              \
+        obs, n, in_dim, W, b, g, be, eps, dim, out_rep, op);                                    \
+  } break;
+  const int key = nch * 2 + (dim == nch * 128 ? 1 : 0);
+  switch (key) {
+    EXB_TRUNK_CASE(2, 1, false)
+    EXB_TRUNK_CASE(3, 1, true)
+    EXB_TRUNK_CASE(4, 2, false)
+    EXB_TRUNK_CASE(5, 2, true)
+    EXB_TRUNK_CASE(6, 3, false)
+    EXB_TRUNK_CASE(7, 3, true)
+    EXB_TRUNK_CASE(8, 4, false)
+    EXB_TRUNK_CASE(9, 4, true)
+    default: set_error("rep_dim %d too wide", dim); return EXB_EUNSUPPORTED;
+  }
+#undef EXB_TRUNK_CASE
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}
+
+extern "C" int exb_rep_trunk_f32(const float* obs, int64_t n, int in_dim, const float* weight,
+                                 const float* bias, const float* ln_weight, const float* ln_bias,
+                                 float ln_eps, int rep_dim, float* out_rep,
+                                 const exb_operand* out_op, exb_stream_t stream) {
+  int rc = check_rep_args(obs, n, rep_dim, out_rep, out_op);
+  if (rc) return rc;
+  EXB_CHECK_ARG(weight && bias && ln_weight && ln_bias && in_dim > 0, "bad arguments");
+  EXB_CHECK_ARG((((uintptr_t)bias | (uintptr_t)ln_weight | (uintptr_t)ln_bias) & 15) == 0,
+                "bias / LayerNorm vectors must be 16-byte aligned");
+  if (exb_rep_trunk_smem_bytes(in_dim, rep_dim) > (size_t)RP_SMEM_LIMIT) {
+    set_error("fused trunk keeps W in shared memory: in_dim %d x rep_dim %d does not fit "
+              "(run the Linear as a GEMM and call exb_rep_ln_tanh_f32)", in_dim, rep_dim);
+    return EXB_EUNSUPPORTED;
+  }
+  OpOut op;
+  rc = make_op(out_op, rep_dim, &op);
+  if (rc) return rc;
+  // rows per warp step: 4 (128 registers, two blocks per SM) measured 1.24 ms per 10^6 walker
+  // rows against 1.49 ms for 8 (255 registers, one block per SM); EXB_TRUNK_R=8 for A/B
+  static const int r4 = [] {
+    const char* e = getenv("EXB_TRUNK_R");
+    return e ? atoi(e) != 8 : 1;
+  }();
+  if (r4)
+    return launch_trunk<4>(obs, n, in_dim, weight, bias, ln_weight, ln_bias, ln_eps, rep_dim,
+                           out_rep, op, (cudaStream_t)stream);
+  return launch_trunk<8>(obs, n, in_dim, weight, bias, ln_weight, ln_bias, ln_eps, rep_dim,
+                         out_rep, op, (cudaStream_t)stream);
+}
+
+extern "C" int exb_rep_ln_tanh_f32(const float* pre, int64_t n, int rep_dim,
+                                   const float* ln_weight, const float* ln_bias, float ln_eps,
+                                   float* out_rep, const exb_operand* out_op,
+                                   exb_stream_t stream) {
+  int rc = check_rep_args(pre, n, rep_dim, out_rep, out_op);
+  if (rc) return rc;
+  EXB_CHECK_ARG(ln_weight && ln_bias, "bad arguments");
+  EXB_CHECK_ARG((((uintptr_t)ln_weight | (uintptr_t)ln_bias) & 15) == 0,
+                "LayerNorm vectors must be 16-byte aligned");
+  OpOut op;
+  rc = make_op(out_op, rep_dim, &op);
+  if (rc) return rc;
+  const unsigned grid = (unsigned)((n + RP_WARPS - 1) / RP_WARPS);
+  cudaStream_t st = (cudaStream_t)stream;
+  switch ((rep_dim / 4 + 31) / 32) {
+    case 1: rep_ln_tanh_kernel<1><<<grid, RP_WARPS * 32, 0, st>>>(pre, n, rep_dim, ln_weight, ln_bias, ln_eps, out_rep, op); break;
+    case 2: rep_ln_tanh_kernel<2><<<grid, RP_WARPS * 32, 0, st>>>(pre, n, rep_dim, ln_weight, ln_bias, ln_eps, out_rep, op); break;
+    case 3: rep_ln_tanh_kernel<3><<<grid, RP_WARPS * 32, 0, st>>>(pre, n, rep_dim, ln_weight, ln_bias, ln_eps, out_rep, op); break;
+    default: rep_ln_tanh_kernel<4><<<grid, RP_WARPS * 32, 0, st>>>(pre, n, rep_dim, ln_weight, ln_bias, ln_eps, out_rep, op); break;
+  }
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}
+
+extern "C" int exb_rep_normalize_f32(const float* x, int64_t n, int dim, float eps,
+                                     float* out_rep, const exb_operand* out_op,
+                                     exb_stream_t stream) {
+  int rc = check_rep_args(x, n, dim, out_rep, out_op);
+  if (rc) return rc;
+  OpOut op;
+  rc = make_op(out_op, dim, &op);
+  if (rc) return rc;
+  const unsigned grid = (unsigned)((n + RP_WARPS - 1) / RP_WARPS);
+  cudaStream_t st = (cudaStream_t)stream;
+  switch ((dim / 4 + 31) / 32) {
+    case 1: rep_normalize_kernel<1><<<grid, RP_WARPS * 32, 0, st>>>(x, n, dim, eps, out_rep, op); break;
+    case 2: rep_normalize_kernel<2><<<grid, RP_WARPS * 32, 0, st>>>(x, n, dim, eps, out_rep, op); break;
+    case 3: rep_normalize_kernel<3><<<grid, RP_WARPS * 32, 0, st>>>(x, n, dim, eps, out_rep, op); break;
+    default: rep_normalize_kernel<4><<<grid, RP_WARPS * 32, 0, st>>>(x, n, dim, eps, out_rep, op); break;
+  }
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}

@@ -26,6 +26,18 @@ def _as_rows(x, name):
     return x.reshape(x.size(0), -1).contiguous()
 
 
+def _prepared_pair(source, target):
+    """(PreparedRep, PreparedRep) if either side is one (the other side is prepared here with
+    exb_knn_prep_f16), else (None, None)."""
+    from .rep import PreparedRep, prepare_rep
+    ps, pt = isinstance(source, PreparedRep), isinstance(target, PreparedRep)
+    if not (ps or pt):
+        return None, None
+    if target is source:
+        return source, source
+    return (source if ps else prepare_rep(source)), (target if pt else prepare_rep(target))
+
+
 def knn_topk(source, target, k, idx_base=0, mode="auto"):
     """k smallest L2 distances (ascending) of every source row to the target rows.
 
@@ -38,8 +50,11 @@ def knn_topk(source, target, k, idx_base=0, mode="auto"):
     if mode not in _MODES:
         raise ValueError(f"mode must be one of {_MODES}")
     lib = _lib.load()
-    src = _as_rows(source, "source")
     same = target is source
+    pre_s, pre_t = _prepared_pair(source, target)
+    if pre_s is not None:
+        source, target = pre_s.rep, pre_t.rep
+    src = _as_rows(source, "source")
     tgt = src if same else _as_rows(target, "target")
     if src.size(1) != tgt.size(1):
         raise RuntimeError(f"feature sizes differ: {src.size(1)} vs {tgt.size(1)}")
@@ -56,6 +71,18 @@ def knn_topk(source, target, k, idx_base=0, mode="auto"):
         dist = torch.empty(nq, k, dtype=torch.float32, device=dev)
         idx = torch.empty(nq, k, dtype=torch.int32, device=dev)
         if nq == 0:
+            return dist, idx
+        if pre_s is not None:
+            if mode == "exact":
+                raise ValueError("exorl_b200: a PreparedRep is consumed by the screened path")
+            need = lib.exb_knn_screened_workspace_bytes(nq, nb, dim, k)
+            if need == 0:
+                raise ValueError(f"exorl_b200: screened kNN does not support dim={dim}, k={k}")
+            ws, _ = _lib.Workspace.get(dev, "knn_screened", need)
+            _lib.check(lib.exb_knn_screened_pre_f32(
+                _lib.ptr(src), nq, pre_s.operand, _lib.ptr(tgt), nb, pre_t.operand, dim, k,
+                int(idx_base), _lib.ptr(dist), _lib.ptr(idx), _lib.ptr(ws), ws.numel(),
+                _lib.stream_ptr(dev)))
             return dist, idx
         use_screen = mode == "screened" or (mode == "auto" and _screen_ok(nq, nb, dim, k))
         if use_screen:
@@ -91,8 +118,11 @@ def knn_screen_lists(source, bank, k):
     (val (nq, L, 24) f32, idx (nq, L, 24) i32 local to bank, cnt (nq, L) i32, ha (nq,), ea (nq,),
     scalars (4,) i32 view of {err_max, hn_max, range_flag, 0}).  exb_knn_screen_lists_f32."""
     lib = _lib.load()
-    src = _as_rows(source, "source")
     same = bank is source
+    pre_s, pre_t = _prepared_pair(source, bank)
+    if pre_s is not None:
+        source, bank = pre_s.rep, pre_t.rep
+    src = _as_rows(source, "source")
     tgt = src if same else _as_rows(bank, "bank")
     nq, nb, dim = src.size(0), tgt.size(0), src.size(1)
     k = int(k)
@@ -111,10 +141,16 @@ def knn_screen_lists(source, bank, k):
         sc = torch.empty(4, dtype=torch.int32, device=dev)
         need = lib.exb_knn_screened_workspace_bytes(nq, nb, dim, k)
         ws, _ = _lib.Workspace.get(dev, "knn_screened", need)
-        _lib.check(lib.exb_knn_screen_lists_f32(
-            _lib.ptr(src), nq, _lib.ptr(tgt), nb, dim, k, int(same), _lib.ptr(val), _lib.ptr(idx),
-            _lib.ptr(cnt), _lib.ptr(ha), _lib.ptr(ea), _lib.ptr(sc), _lib.ptr(ws), ws.numel(),
-            _lib.stream_ptr(dev)))
+        if pre_s is not None:
+            _lib.check(lib.exb_knn_screen_lists_pre_f32(
+                _lib.ptr(src), nq, pre_s.operand, _lib.ptr(tgt), nb, pre_t.operand, dim, k,
+                _lib.ptr(val), _lib.ptr(idx), _lib.ptr(cnt), _lib.ptr(ha), _lib.ptr(ea),
+                _lib.ptr(sc), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+        else:
+            _lib.check(lib.exb_knn_screen_lists_f32(
+                _lib.ptr(src), nq, _lib.ptr(tgt), nb, dim, k, int(same), _lib.ptr(val),
+                _lib.ptr(idx), _lib.ptr(cnt), _lib.ptr(ha), _lib.ptr(ea), _lib.ptr(sc),
+                _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
     return val, idx, cnt, ha, ea, sc
 
 
@@ -252,8 +288,13 @@ def compute_apt_reward(source, target, args, rms=None, mode="auto", return_knn=F
     lib = _lib.load()
     k = int(args.knn_k)
     knn_avg, knn_rms, knn_clip = bool(args.knn_avg), bool(args.knn_rms), float(args.knn_clip)
-    src = _as_rows(source, "source")
     same = target is source
+    pre_s, pre_t = _prepared_pair(source, target)
+    if pre_s is not None:
+        if mode == "exact":
+            raise ValueError("exorl_b200: a PreparedRep is consumed by the screened path")
+        source, target = pre_s.rep, pre_t.rep
+    src = _as_rows(source, "source")
     tgt = src if same else _as_rows(target, "target")
     if src.size(1) != tgt.size(1):
         raise RuntimeError(f"feature sizes differ: {src.size(1)} vs {tgt.size(1)}")
@@ -286,10 +327,18 @@ def compute_apt_reward(source, target, args, rms=None, mode="auto", return_knn=F
                   _lib.ptr(new_s))
         else:
             st = (None, None, 0.0, None, None)
-        _lib.check(lib.exb_apt_reward_f32(
-            _lib.ptr(src), nq, _lib.ptr(tgt), nb, dim, k, int(same), _MODE_ID[mode],
-            int(knn_avg), int(knn_rms), knn_clip, *st, _lib.ptr(out), _lib.ptr(dist),
-            _lib.ptr(idx), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+        if pre_s is not None:
+            if dim > _lib.SCREEN_MAX_DIM or k > _lib.SCREEN_MAX_K:
+                raise ValueError(f"exorl_b200: screened kNN does not support dim={dim}, k={k}")
+            _lib.check(lib.exb_apt_reward_pre_f32(
+                _lib.ptr(src), nq, pre_s.operand, _lib.ptr(tgt), nb, pre_t.operand, dim, k,
+                int(knn_avg), int(knn_rms), knn_clip, *st, _lib.ptr(out), _lib.ptr(dist),
+                _lib.ptr(idx), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+        else:
+            _lib.check(lib.exb_apt_reward_f32(
+                _lib.ptr(src), nq, _lib.ptr(tgt), nb, dim, k, int(same), _MODE_ID[mode],
+                int(knn_avg), int(knn_rms), knn_clip, *st, _lib.ptr(out), _lib.ptr(dist),
+                _lib.ptr(idx), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
     if knn_rms:
         # utils/utils.py:272-274: rebind M, S and advance n by the number of values seen
         rms.M, rms.S = new_m, new_s

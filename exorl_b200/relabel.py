@@ -26,6 +26,7 @@ import torch
 import torch.distributed as dist
 
 from . import _lib
+from .rep import PreparedRep
 from .knn import (knn_topk, _reward_from_knn, _pbe_ws, knn_screen_lists, knn_rerank_lists,
                   screen_lists_count)
 
@@ -37,9 +38,22 @@ def shard_bounds(n, world, rank):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
+def _shard(rep, lo, hi):
+    """Bank shard [lo, hi) of a rep tensor or PreparedRep; the object itself when the shard is the
+    whole set (`is` marks source = target)."""
+    if lo == 0 and hi == rep.size(0):
+        return rep
+    return rep.rows(lo, hi) if isinstance(rep, PreparedRep) else rep[lo:hi]
+
+
+def _fp32(rep):
+    return rep.rep if isinstance(rep, PreparedRep) else rep
+
+
 def _cuda_local_knn(rep, lo, hi, k, mode):
-    bank = rep if (lo == 0 and hi == rep.size(0)) else rep[lo:hi]   # `is` marks source = target
-    return knn_topk(rep, bank, k, idx_base=lo, mode=mode)
+    if isinstance(rep, PreparedRep) and mode == "auto":
+        mode = "screened"
+    return knn_topk(rep, _shard(rep, lo, hi), k, idx_base=lo, mode=mode)
 
 
 def _cuda_merge(dist_lists, idx_lists, k):
@@ -88,11 +102,11 @@ def _cuda_finish(knn_dist, k, avg, use_rms, clip, sums, rms):
 
 
 def _cuda_screen_lists(rep, lo, hi, k):
-    bank = rep if (lo == 0 and hi == rep.size(0)) else rep[lo:hi]
-    return knn_screen_lists(rep, bank, k)
+    return knn_screen_lists(rep, _shard(rep, lo, hi), k)
 
 
 def _cuda_rerank_lists(rep, lo, hi, k, val, idx, cnt, shard_lo, ha, ea, sc):
+    rep = _fp32(rep)     # the exact recompute reads the fp32 rows only
     return knn_rerank_lists(rep[lo:hi], rep, k, val, idx, cnt, shard_lo, ha, ea, sc)
 
 
@@ -190,6 +204,10 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="a
                        return_knn=False, stages=_CudaStages, timer=None):
     """APT reward (N, 1) of every row of `rep` against all N rows, identical on every rank.
 
+    `rep` is the (N, c) fp32 rep tensor or a PreparedRep (exorl_b200.rep: e.g. icm_get_rep of the
+    dataset's observations — the trunk then emits the kNN operand itself and the relabel never
+    re-reads the rep to prepare it).
+
     `args` exposes knn_k, knn_avg, knn_rms, knn_clip like PBE; `rms` is the running-moment state
     (updated once with bs = N*k in avg mode, N otherwise).  Works without an initialised process
     group (single shard)."""
@@ -211,10 +229,10 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="a
     if world > 1 and exchange in ("auto", "lists"):
         cnt = 0
         if mode != "exact" and hasattr(stages, "lists_available"):
-            cnt = int(stages.lists_available(n, hi - lo, rep[0].numel(), k, world))
+            cnt = int(stages.lists_available(n, hi - lo, _fp32(rep)[0].numel(), k, world))
         # every rank must take the same branch with the same list count (shard sizes differ by
         # up to one row, which can change the kernel variant): agree on min and max
-        flag = torch.tensor([cnt, -cnt], device=rep.device)
+        flag = torch.tensor([cnt, -cnt], device=_fp32(rep).device)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
         lo_cnt, hi_cnt = (int(v) for v in flag.tolist())
         ok = lo_cnt > 0 and lo_cnt == -hi_cnt

@@ -1,0 +1,161 @@
+"""Rep producers: the step in front of the kNN reward.
+
+  icm_get_rep(icm, obs)     <- ICM.get_rep / ICM.trunk = Linear -> LayerNorm -> Tanh,
+                               agents/unsupervised_learning/icm_apt.py:17-18,50-52
+  normalize_rep(z)          <- F.normalize(z, dim=1, p=2), agents/unsupervised_learning/proto.py:104
+
+Each returns a PreparedRep: the fp32 rep the reference would hand to PBE.__call__ / the Proto kNN
+lines, plus the prepared fp16 operand + row norms the screening kernel consumes, written by ONE
+kernel (csrc/rep_producer.cu) — the kNN then skips its own prep pass over the rep.
+PBE.__call__, compute_apt_reward, knn_topk and proto_knn_reward accept a PreparedRep wherever they
+accept a rep tensor.  No CPU path.
+"""
+import torch
+
+from . import _lib
+
+
+def _dim_pad(dim):
+    return (dim + 63) // 64 * 64
+
+
+class PreparedRep:
+    """`.rep` (n, dim) fp32 + the prepared operand (`f16` (n, dim_pad), `half_norm`, `round_err`
+    (n,), `scalars` 16 bytes).  Behaves like the rep for shape queries."""
+
+    def __init__(self, n, dim, device, rep=None):
+        dev = torch.device(device)
+        self.rep = rep if rep is not None else torch.empty(n, dim, dtype=torch.float32,
+                                                           device=dev)
+        # one allocation, 256-byte aligned pieces (TMA needs the fp16 rows 128-byte aligned)
+        self.f16 = torch.empty(n, _dim_pad(dim), dtype=torch.float16, device=dev)
+        self.half_norm = torch.empty(n, dtype=torch.float32, device=dev)
+        self.round_err = torch.empty(n, dtype=torch.float32, device=dev)
+        self.scalars = torch.zeros(4, dtype=torch.int32, device=dev)
+        self._c = _lib.Operand(self.f16.data_ptr(), self.half_norm.data_ptr(),
+                               self.round_err.data_ptr(), self.scalars.data_ptr())
+
+    def rows(self, lo, hi):
+        """Row-slice view [lo, hi) (a bank shard): shares storage and the scalars word of the
+        whole set — maxima over a superset keep the screening certificate rigorous."""
+        v = object.__new__(PreparedRep)
+        v.rep, v.f16 = self.rep[lo:hi], self.f16[lo:hi]
+        v.half_norm, v.round_err = self.half_norm[lo:hi], self.round_err[lo:hi]
+        v.scalars = self.scalars
+        v._c = _lib.Operand(v.f16.data_ptr(), v.half_norm.data_ptr(), v.round_err.data_ptr(),
+                            v.scalars.data_ptr())
+        return v
+
+    @property
+    def operand(self):
+        return self._c
+
+    @property
+    def device(self):
+        return self.rep.device
+
+    @property
+    def shape(self):
+        return self.rep.shape
+
+    def size(self, *a):
+        return self.rep.size(*a)
+
+
+def _f32c(t, name):
+    _lib.require_cuda(t, name)
+    t = t.detach()
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _trunk_params(trunk):
+    """(weight, bias, ln_weight, ln_bias, eps) of nn.Sequential(Linear, LayerNorm, Tanh)
+    (icm_apt.py:17-18) or of a module exposing it as `.trunk`."""
+    if hasattr(trunk, "trunk"):
+        trunk = trunk.trunk
+    if isinstance(trunk, (tuple, list)):
+        w, b, g, be, *rest = trunk
+        return w, b, g, be, (float(rest[0]) if rest else 1e-5)
+    lin, ln, act = trunk[0], trunk[1], trunk[2]
+    if not (isinstance(lin, torch.nn.Linear) and isinstance(ln, torch.nn.LayerNorm)
+            and isinstance(act, torch.nn.Tanh)) or lin.bias is None or ln.weight is None:
+        raise ValueError("exorl_b200: expected nn.Sequential(Linear, LayerNorm, Tanh)")
+    return lin.weight, lin.bias, ln.weight, ln.bias, float(ln.eps)
+
+
+def ln_tanh_rep(pre, ln_weight, ln_bias, eps=1e-5):
+    """tanh(LayerNorm(pre)) for given pre-activations (n, dim) -> PreparedRep."""
+    lib = _lib.load()
+    pre = _f32c(pre, "pre")
+    n, dim = pre.shape
+    dev = pre.device
+    g, be = _f32c(ln_weight, "ln_weight"), _f32c(ln_bias, "ln_bias")
+    with torch.cuda.device(dev):
+        out = PreparedRep(n, dim, dev)
+        if n:
+            _lib.check(lib.exb_rep_ln_tanh_f32(_lib.ptr(pre), n, dim, _lib.ptr(g), _lib.ptr(be),
+                                               float(eps), _lib.ptr(out.rep), out.operand,
+                                               _lib.stream_ptr(dev)))
+    return out
+
+
+def icm_get_rep(icm, obs):
+    """ICM.get_rep(obs, action) = trunk(obs) (icm_apt.py:50-52) -> PreparedRep.
+
+    `icm`: the ICM module, its trunk, or (weight, bias, ln_weight, ln_bias[, eps]).  Narrow inputs
+    (state observations) run the Linear inside the kernel with W^T in shared memory; wide inputs
+    (the 39200-wide pixel encoder output) run the Linear as a library GEMM and fuse the rest."""
+    lib = _lib.load()
+    w, b, g, be, eps = _trunk_params(icm)
+    obs = _f32c(obs, "obs")
+    obs = obs.reshape(obs.size(0), -1)
+    w, b, g, be = _f32c(w, "weight"), _f32c(b, "bias"), _f32c(g, "ln_weight"), _f32c(be, "ln_bias")
+    n, in_dim = obs.shape
+    dim = w.size(0)
+    if w.size(1) != in_dim:
+        raise RuntimeError(f"mat1 and mat2 shapes cannot be multiplied ({n}x{in_dim} and "
+                           f"{w.size(1)}x{dim})")
+    if lib.exb_rep_trunk_smem_bytes(in_dim, dim) > 232448:
+        return ln_tanh_rep(torch.addmm(b, obs, w.t()), g, be, eps)
+    dev = obs.device
+    with torch.cuda.device(dev):
+        out = PreparedRep(n, dim, dev)
+        if n:
+            _lib.check(lib.exb_rep_trunk_f32(_lib.ptr(obs), n, in_dim, _lib.ptr(w), _lib.ptr(b),
+                                             _lib.ptr(g), _lib.ptr(be), eps, dim,
+                                             _lib.ptr(out.rep), out.operand,
+                                             _lib.stream_ptr(dev)))
+    return out
+
+
+def normalize_rep(x, eps=1e-12):
+    """F.normalize(x, dim=1, p=2, eps) (proto.py:104) -> PreparedRep."""
+    lib = _lib.load()
+    x = _f32c(x, "x")
+    n, dim = x.shape
+    dev = x.device
+    with torch.cuda.device(dev):
+        out = PreparedRep(n, dim, dev)
+        if n:
+            _lib.check(lib.exb_rep_normalize_f32(_lib.ptr(x), n, dim, float(eps),
+                                                 _lib.ptr(out.rep), out.operand,
+                                                 _lib.stream_ptr(dev)))
+    return out
+
+
+def prepare_rep(rep):
+    """Prepared operand of an existing fp32 rep (exb_knn_prep_f16), e.g. the Proto queue."""
+    lib = _lib.load()
+    rep = _f32c(rep, "rep")
+    rep = rep.reshape(rep.size(0), -1)
+    n, dim = rep.shape
+    dev = rep.device
+    with torch.cuda.device(dev):
+        out = PreparedRep(n, dim, dev, rep=rep)
+        if n:
+            _lib.check(lib.exb_knn_prep_f16(_lib.ptr(rep), n, dim, _lib.ptr(out.f16),
+                                            _lib.ptr(out.half_norm), _lib.ptr(out.round_err),
+                                            _lib.ptr(out.scalars), _lib.stream_ptr(dev)))
+    return out

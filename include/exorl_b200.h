@@ -109,6 +109,45 @@ int exb_profile_begin(int enable);
 int exb_profile_collect_sync(float* host_ms, int cap, int* host_n);
 
 /* --------------------------------------------------------------------------------------------
+ * Rep producers: the step in front of the kNN.  One pass computes the rep
+ * the reference hands to PBE / the Proto kNN and writes BOTH the fp32 rep (out_rep, [n, rep_dim])
+ * and the prepared fp16 operand (out_op; same bytes exb_knn_prep_f16 would produce from out_rep),
+ * so the screen does not re-read the rep from HBM.  Either output may be NULL, not both.
+ *   exb_rep_trunk_f32     tanh(LayerNorm(obs @ weight^T + bias)); replaces ICM.get_rep /
+ *                         ICM.trunk, agents/unsupervised_learning/icm_apt.py:17-18,50-52.
+ *                         weight [rep_dim, in_dim] row-major (nn.Linear layout); W^T is kept in
+ *                         shared memory: exb_rep_trunk_smem_bytes(in_dim, rep_dim) <= 227 KB,
+ *                         else EXB_EUNSUPPORTED (run the Linear as a GEMM, then the next call).
+ *   exb_rep_ln_tanh_f32   tanh(LayerNorm(pre)) on given pre-activations (in place allowed).
+ *   exb_rep_normalize_f32 F.normalize(x, dim=1, p=2, eps) = x / max(||x||, eps); replaces
+ *                         agents/unsupervised_learning/proto.py:104 (in place allowed).
+ * rep_dim % 4 == 0, 4 <= rep_dim <= EXB_SCREEN_MAX_DIM; rows 16-byte aligned.
+ * exb_operand.scalars (16 device bytes) is max-accumulated: zero it before the first producer call.
+ * exb_knn_screened_pre_f32 = exb_knn_screened_f32 with caller-prepared operands (bank_op == src_op
+ * or NULL src_op with src == bank means source = target, utils/utils.py:290); skips step 1.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct exb_operand {
+  void* f16;        /* [n, dim_pad] fp16, dim_pad = dim rounded up to a multiple of 64 */
+  float* half_norm; /* [n] */
+  float* round_err; /* [n] */
+  void* scalars;    /* 16 bytes {float err_max, float hn_max, int range_flag, int 0} */
+} exb_operand;
+size_t exb_rep_trunk_smem_bytes(int in_dim, int rep_dim);
+int exb_rep_trunk_f32(const float* obs, int64_t n, int in_dim, const float* weight,
+                      const float* bias, const float* ln_weight, const float* ln_bias,
+                      float ln_eps, int rep_dim, float* out_rep, const exb_operand* out_op,
+                      exb_stream_t stream);
+int exb_rep_ln_tanh_f32(const float* pre, int64_t n, int rep_dim, const float* ln_weight,
+                        const float* ln_bias, float ln_eps, float* out_rep,
+                        const exb_operand* out_op, exb_stream_t stream);
+int exb_rep_normalize_f32(const float* x, int64_t n, int dim, float eps, float* out_rep,
+                          const exb_operand* out_op, exb_stream_t stream);
+int exb_knn_screened_pre_f32(const float* src, int64_t nq, const exb_operand* src_op,
+                             const float* bank, int64_t nb, const exb_operand* bank_op, int dim,
+                             int k, int32_t idx_base, float* out_dist, int32_t* out_idx,
+                             void* workspace, size_t workspace_bytes, exb_stream_t stream);
+
+/* --------------------------------------------------------------------------------------------
  * Sharded kNN: merge G per-shard (dist, idx) lists (each [nq,k], ascending) into the global
  * k smallest per row; ties -> smaller index.  lists are laid out [G, nq, k] (the result of an
  * all-gather of per-rank results).  New composition; semantics of
@@ -138,6 +177,15 @@ int exb_knn_screen_lists_f32(const float* src, int64_t nq, const float* bank, in
                              int32_t* out_cnt, float* out_ha, float* out_ea, void* out_scalars,
                              void* workspace /* exb_knn_screened_workspace_bytes */,
                              size_t workspace_bytes, exb_stream_t stream);
+/* exb_knn_screen_lists_f32 on caller-prepared operands (rep producers).  A bank shard's operand
+ * is the row slice of the full operand; its scalars may be those of the whole set (maxima over a
+ * superset keep the certificate rigorous). */
+int exb_knn_screen_lists_pre_f32(const float* src, int64_t nq, const exb_operand* src_op,
+                                 const float* bank, int64_t nb, const exb_operand* bank_op,
+                                 int dim, int k, float* out_val, int32_t* out_idx,
+                                 int32_t* out_cnt, float* out_ha, float* out_ea,
+                                 void* out_scalars, void* workspace, size_t workspace_bytes,
+                                 exb_stream_t stream);
 size_t exb_knn_rerank_lists_workspace_bytes(int64_t nq, int64_t nb, int k);
 int exb_knn_rerank_lists_f32(const float* src, int64_t nq, const float* bank, int64_t nb, int dim,
                              int k, int n_shards, int lists_per_shard, const float* cand_val,
@@ -194,6 +242,15 @@ int exb_apt_reward_f32(const float* src, int64_t nq, const float* bank, int64_t 
                        float* rms_m_out, float* rms_s_out, float* out_reward /* [nq] */,
                        float* out_dist /* [nq,k] */, int32_t* out_idx /* [nq,k] */,
                        void* workspace, size_t workspace_bytes, exb_stream_t stream);
+
+/* exb_apt_reward_f32 on caller-prepared operands (rep producers above); screened mode only. */
+int exb_apt_reward_pre_f32(const float* src, int64_t nq, const exb_operand* src_op,
+                           const float* bank, int64_t nb, const exb_operand* bank_op, int dim,
+                           int k, int avg, int use_rms, float clip, const float* rms_m_in,
+                           const float* rms_s_in, double rms_n, float* rms_m_out,
+                           float* rms_s_out, float* out_reward, float* out_dist,
+                           int32_t* out_idx, void* workspace, size_t workspace_bytes,
+                           exb_stream_t stream);
 
 /* ProtoRL reward: k-th smallest distance only, no RMS/clip/log (proto.py:115-118). */
 int exb_take_kth(const float* knn_dist, int64_t nq, int k, float* out /* [nq] */,

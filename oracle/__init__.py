@@ -12,6 +12,7 @@ own for this path, so there are no upstream golden vectors to pi
 """
 from .pbe_oracle import (rms_step, pbe_reward, knn_smallest, proto_reward, proto_enqueue,
                          RmsState)
+from .rep_oracle import icm_trunk_rep, l2_normalize
 from .replay_oracle import (nstep_transition, onestep_transition, episode_length,
                             flatten_episodes, write_episode_npz, read_episode_npz,
                             philox4x32_10, draw_indices_philox)

@@ -217,10 +217,63 @@ def gen_replay(ref_replay):
     np.savez_compressed(OUT / "replay_reference.npz", **out)
 
 
+def load_reference_icm(ref_utils):
+    """class ICM of agents/unsupervised_learning/icm_apt.py:10-52, executed from the reference's
+    own source text (the module imports hydra / the `utils` package / .ddpg, absent here, so only
+    the class statement is compiled, with `utils` bound to the reference's utils/utils.py)."""
+    import ast
+    path = REF / "agents/unsupervised_learning/icm_apt.py"
+    tree = ast.parse(path.read_text())
+    cls = [n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "ICM"]
+    ns = {"torch": torch, "nn": torch.nn, "F": torch.nn.functional, "utils": ref_utils}
+    exec(compile(ast.Module(body=cls, type_ignores=[]), str(path), "exec"), ns)
+    return ns["ICM"]
+
+
+def gen_rep(ref_utils):
+    """Rep producers: ICM.get_rep (trunk Linear -> LayerNorm -> Tanh) on seeded
+    observations, then the reference PBE on that rep; F.normalize as used by proto.py:104."""
+    ICM = load_reference_icm(ref_utils)
+    out = {}
+    for tag, (n, obs_dim, rep_dim, scale) in {"walker": (160, 24, 512, 1.0),
+                                              "small": (96, 17, 128, 3.0),
+                                              "wide": (64, 300, 512, 0.5),
+                                              "odd": (40, 5, 36, 1.0)}.items():
+        torch.manual_seed(100 + obs_dim)
+        icm = ICM(obs_dim, 6, 64, rep_dim)
+        g = torch.Generator().manual_seed(200 + obs_dim)
+        with torch.no_grad():   # trained-looking parameters (weight_init leaves bias 0, LN 1/0)
+            icm.trunk[0].bias.copy_(0.1 * torch.randn(rep_dim, generator=g))
+            icm.trunk[1].weight.copy_(1.0 + 0.2 * torch.randn(rep_dim, generator=g))
+            icm.trunk[1].bias.copy_(0.1 * torch.randn(rep_dim, generator=g))
+            obs = scale * torch.randn(n, obs_dim, generator=g)
+            rep = icm.get_rep(obs, None)
+            rms = ref_utils.RMS("cpu")
+            reward = ref_utils.PBE(rms, 0.0, 12, True, True, "cpu")(rep.clone())
+        out[f"{tag}_obs"] = obs.numpy()
+        out[f"{tag}_w"] = icm.trunk[0].weight.detach().numpy()
+        out[f"{tag}_b"] = icm.trunk[0].bias.detach().numpy()
+        out[f"{tag}_lnw"] = icm.trunk[1].weight.detach().numpy()
+        out[f"{tag}_lnb"] = icm.trunk[1].bias.detach().numpy()
+        out[f"{tag}_eps"] = np.array(icm.trunk[1].eps, np.float64)
+        out[f"{tag}_rep"] = rep.numpy()
+        out[f"{tag}_reward"] = reward.numpy()
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn(200, 128, generator=g) * torch.logspace(-3, 3, 200)[:, None]
+    x[5] = 0.0        # all-zero row: F.normalize's eps clamp (the warm-up queue rows)
+    out["norm_x"] = x.numpy()
+    out["norm_out"] = torch.nn.functional.normalize(x, dim=1, p=2).numpy()
+    np.savez_compressed(OUT / "rep_reference.npz", **out)
+
+
 if __name__ == "__main__":
     torch.set_num_threads(8)
     OUT.mkdir(parents=True, exist_ok=True)
     ref_utils, ref_replay = load_reference()
+    if "--rep-only" in sys.argv:
+        gen_rep(ref_utils)
+        sys.exit(0)
+    gen_rep(ref_utils)
     gen_kat(ref_utils)
     gen_pbe(ref_utils)
     gen_knn_dists(ref_utils)

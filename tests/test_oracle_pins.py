@@ -162,3 +162,24 @@ def test_nstep_discount_kat():
           "reward": np.ones((5, 1), np.float32), "discount": np.ones((5, 1), np.float32)}
     out = nstep_transition(ep, 1, 3, 0.99)
     assert out[3].dtype == np.float32 and float(out[3][0]) == pytest.approx(0.97029907, abs=1e-8)
+
+
+@pytest.mark.parametrize("tag", ["walker", "small", "wide", "odd"])
+def test_golden_icm_trunk_rep_bitwise(golden, tag):
+    """oracle.icm_trunk_rep == the reference's own ICM.get_rep (icm_apt.py:17-18,50-52) and the
+    reference PBE on that rep == oracle.pbe_reward (fixtures: gen_golden.py:gen_rep)."""
+    from oracle import icm_trunk_rep
+    g = golden("rep_reference.npz")
+    t = {n: torch.from_numpy(g[f"{tag}_{n}"]) for n in ("obs", "w", "b", "lnw", "lnb")}
+    rep = icm_trunk_rep(t["obs"], t["w"], t["b"], t["lnw"], t["lnb"], float(g[f"{tag}_eps"]))
+    assert np.array_equal(rep.numpy(), g[f"{tag}_rep"])
+    r = pbe_reward(rep, rep, RmsState(), 12, True, True, 0.0)
+    assert np.array_equal(r.numpy(), g[f"{tag}_reward"])
+
+
+def test_golden_l2_normalize_bitwise(golden):
+    from oracle import l2_normalize
+    g = golden("rep_reference.npz")
+    out = l2_normalize(torch.from_numpy(g["norm_x"]))
+    assert np.array_equal(out.numpy(), g["norm_out"])
+    assert not np.any(out[5].numpy())   # zero row stays zero (eps clamp, no NaN)
