@@ -38,7 +38,7 @@ def parse():
     ap.add_argument("--dim", type=int, default=512)
     ap.add_argument("--k", type=int, default=12)
     ap.add_argument("--exchange", default="auto",
-                    choices=["auto", "lists", "all_to_all", "all_gather"])
+                    choices=["auto", "lists", "all_to_all", "all_gather", "queries"])
     ap.add_argument("--cpu-queries", type=int, default=128,
                     help="queries of the bounded CPU-baseline sample (vs the full bank)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -50,6 +50,20 @@ def parse():
 def workload(a):
     return (f"C5 APT relabel: {a.n} x {a.n} kNN reward, rep {a.dim}, k={a.k}, knn_avg+knn_rms, "
             f"clip 0, reps = tanh(randn) seed 5")
+
+
+def screen_traffic(nq, nb, dim):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one screening launch from the committed
+    `ncu --set full` capture (profiles/screen_traffic.json) when it is of this launch shape."""
+    try:
+        t = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles",
+                                        "screen_traffic.json")))
+        if (t["n_queries"], t["n_bank"], t["dim"]) == (nq, nb, dim):
+            return {"traffic": t["traffic_bytes_per_launch"], "traffic_unit": "bytes",
+                    "traffic_source": t["source"]}
+    except Exception:
+        pass
+    return {"traffic": None}
 
 
 def peaks():
@@ -273,7 +287,10 @@ def run_ours(a, rank, world, local_rank):
             "dtype": "f16 tensor-core screen (f32 accumulate) + f32 exact recompute",
             "data": "synthetic",
             "config": {"workload": workload(a), "n": a.n, "dim": a.dim, "k": a.k,
-                       "parallelism": f"bank sharded over {world} GPU(s), exchange={a.exchange}",
+                       "parallelism": (f"{world} GPU(s), exchange={a.exchange}" + (
+                           "" if world == 1 else
+                           " (query blocks over the ranks, whole bank on every rank)"
+                           if a.exchange in ("auto", "queries") else " (bank sharded)")),
                        "l2": "inputs (2 GB fp32 + 1 GB fp16 bank) larger than the 126 MB L2; "
                              "no flush needed",
                        "undecided_rows_last_step": und, "invalid": invalid},
@@ -289,7 +306,8 @@ def run_ours(a, rank, world, local_rank):
                          "frac_of_burst_peak": achieved / burst if burst else None,
                          "peak_source": src + ", sustained bf16 (kernel timed inside a long step)",
                          "kernel_ms": kernel_ms, "launches_timed": kn.value,
-                         "algorithmic_flops_per_launch": flops, "traffic": None},
+                         "algorithmic_flops_per_launch": flops,
+                         **screen_traffic(a.n, nb_local, a.dim)},
             "cpu_baseline": cpu_baseline,
         }
         print(json.dumps(out))

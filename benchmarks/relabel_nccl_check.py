@@ -39,10 +39,16 @@ def main():
     r0 = _reward_from_knn(d0, a.k, True, True, 0.0, rms0)
 
     ok = True
-    for exchange in ("lists", "auto", "all_to_all", "all_gather"):
+    # "prepared": the same set handed over as a PreparedRep (exb_knn_prep_f16 here; the rep
+    # producers emit the same operand), query-block partition
+    for exchange in ("queries", "prepared", "lists", "auto", "all_to_all", "all_gather"):
         rms = xb.RMS(dev)
-        out = xb.relabel_apt_reward(rep, args, rms=rms, exchange=exchange, mode="screened",
-                                    return_knn=True)
+        if exchange == "prepared":
+            out = xb.relabel_apt_reward(xb.prepare_rep(rep), args, rms=rms, exchange="queries",
+                                        return_knn=True)
+        else:
+            out = xb.relabel_apt_reward(rep, args, rms=rms, exchange=exchange, mode="screened",
+                                        return_knn=True)
         r, d, i = out
         torch.cuda.synchronize()
         np.testing.assert_allclose(r.cpu().numpy(), r0.cpu().numpy(), rtol=1e-5, atol=1e-7)

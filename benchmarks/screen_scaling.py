@@ -23,6 +23,8 @@ def main():
     ap.add_argument("--k", type=int, default=12)
     ap.add_argument("--shards", default="1,2,4,8")
     ap.add_argument("--reps", type=int, default=4)
+    ap.add_argument("--query-blocks", action="store_true",
+                    help="shard the QUERIES instead (block of n/G queries against the whole bank)")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     lib = _lib.load()
@@ -32,7 +34,10 @@ def main():
         nb = a.n // G
         lo = (G // 2) * nb if G > 1 else 0           # a middle shard
         bank = rep if G == 1 else rep[lo:lo + nb]
-        xb.knn_topk(rep, bank, a.k, idx_base=lo, mode="screened")     # warm-up
+        src = rep
+        if a.query_blocks:
+            src, bank, lo = bank, rep, 0
+        xb.knn_topk(src, bank, a.k, idx_base=lo, mode="screened")     # warm-up
         torch.cuda.synchronize()
         from bench import ClockSampler
         sampler = ClockSampler(0)
@@ -40,7 +45,7 @@ def main():
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(a.reps):
-            xb.knn_topk(rep, bank, a.k, idx_base=lo, mode="screened")
+            xb.knn_topk(src, bank, a.k, idx_base=lo, mode="screened")
         e1.record()
         torch.cuda.synchronize()
         kms = (ctypes.c_float * 64)()
@@ -70,9 +75,12 @@ def main():
                                     "store_cycles": t[13] / max(t[12], 1),
                                     "repacks_per_row": t[14] / (32 * n_warp),
                                     "chain_refresh_cycles": t[15] / max(t[12], 1)}}
-        print(json.dumps({"shards": G, "nb": nb, "screen_ms": k_ms,
+        print(json.dumps({"shards": G, "nb": bank.size(0), "nq": src.size(0),
+                          "sharded": "queries" if a.query_blocks else "bank",
+                          "wave_splits": os.environ.get("EXB_SCREEN_WAVESPLITS", "auto"),
+                          "screen_ms": k_ms,
                           "local_knn_ms": e0.elapsed_time(e1) / a.reps,
-                          "tflops": 2.0 * a.n * nb * a.dim / (k_ms * 1e-3) / 1e12,
+                          "tflops": 2.0 * src.size(0) * bank.size(0) * a.dim / (k_ms * 1e-3) / 1e12,
                           "undecided": und, "invalid": invalid, "rerank_pairs": pairs, "sm_mhz": clocks.get("sm_mhz"),
                           "power_w": clocks.get("power_w_max"),
                           "debug": os.environ.get("EXB_SCREEN_DEBUG", "0"), **extra}), flush=True)

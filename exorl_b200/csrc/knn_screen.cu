@@ -1043,7 +1043,20 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
   int splits = sm_count() / pl->m_tiles;
   if (splits > pl->n_tiles) splits = pl->n_tiles;
   if (splits > 16) splits = 16;
-  if (splits < 1) splits = 1;
+  if (splits < 1) {
+    // More query tiles than SMs: one bank range per CTA.  Cutting the bank into s <= 4 ranges
+    // (shorter work units, a cheaper partial last wave) was measured on 125k queries x 1M rows
+    // (978 CTAs = 6.6 waves): 93.4 ms (s = 1) vs 95.6 / 96.2 / 97.8 ms (s = 2 / 3 / 4) — the CTAs
+    // do not finish in lock-step, so the wave model does not hold, and every extra range restarts
+    // the k-th-best chain.  Kept as an A/B knob only (EXB_SCREEN_WAVESPLITS=1..4).
+    splits = 1;
+    static const int wave_splits = [] {
+      const char* e = getenv("EXB_SCREEN_WAVESPLITS");
+      return e ? atoi(e) : 0;
+    }();
+    if (wave_splits > 0) splits = wave_splits > 4 ? 4 : wave_splits;
+    if (splits > pl->n_tiles) splits = pl->n_tiles;
+  }
   pl->tiles_per_split = (pl->n_tiles + splits - 1) / splits;
   pl->splits = (pl->n_tiles + pl->tiles_per_split - 1) / pl->tiles_per_split;
   // variant: short scans -> 1 (the list fill phase dominates); mid-length scans (a bank shard of

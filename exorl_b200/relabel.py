@@ -14,8 +14,11 @@ reference formula cannot be evaluated (it materialises an (N, N, c) tensor); SUR
                                exactly against the whole fp32 bank it holds anyway: the exact
                                recompute runs once per query instead of once per (query, shard)
                                and there is no merge
-               "auto"        — "lists" when the screen-only form exists for the sizes, else
-                               "all_to_all"
+               "queries"     — no bank sharding at all: every rank already holds the whole
+                               set, so rank r computes the kNN of QUERY block r against the whole
+                               bank; nothing but the RMS sums and the rewards is exchanged, and
+                               every row's k-th-best chain sees the whole bank (fewest hits)
+               "auto"        — "queries"
   3. one global RMS update with bs = N*k (or N), then the epilogue
   4. all_to_all only: rewards all-gathered so every rank returns the full (N, 1).
 
@@ -116,8 +119,16 @@ def _cuda_lists_available(n, nb, dim, k, world):
     return lists if 0 < lists * world <= 16 else 0
 
 
+def _cuda_block_knn(rep, lo, hi, k, mode):
+    """Exact k nearest rows of the WHOLE set for the query block [lo, hi) (global ids)."""
+    if isinstance(rep, PreparedRep) and mode == "auto":
+        mode = "screened"
+    return knn_topk(_shard(rep, lo, hi), rep, k, mode=mode)
+
+
 class _CudaStages:
     local_knn = staticmethod(_cuda_local_knn)
+    block_knn = staticmethod(_cuda_block_knn)
     screen_lists = staticmethod(_cuda_screen_lists)
     rerank_lists = staticmethod(_cuda_rerank_lists)
     lists_available = staticmethod(_cuda_lists_available)
@@ -211,8 +222,9 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="a
     `args` exposes knn_k, knn_avg, knn_rms, knn_clip like PBE; `rms` is the running-moment state
     (updated once with bs = N*k in avg mode, N otherwise).  Works without an initialised process
     group (single shard)."""
-    if exchange not in ("auto", "lists", "all_gather", "all_to_all"):
-        raise ValueError("exchange must be 'auto', 'lists', 'all_gather' or 'all_to_all'")
+    if exchange not in ("auto", "lists", "all_gather", "all_to_all", "queries"):
+        raise ValueError("exchange must be 'auto', 'lists', 'all_gather', 'all_to_all' or "
+                         "'queries'")
     if rms is None:
         rms = getattr(args, "rms", None)
     k, avg, use_rms, clip = int(args.knn_k), bool(args.knn_avg), bool(args.knn_rms), args.knn_clip
@@ -226,7 +238,13 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="a
 
     tm = timer.mark if timer is not None else (lambda name: None)
     tm("start")
-    if world > 1 and exchange in ("auto", "lists"):
+    if world > 1 and exchange == "auto":
+        # every rank holds the whole set (it is the query set), so the cheapest partition is by
+        # query block: no candidate exchange, no merge, and each row's k-th-best chain sees the
+        # whole bank.  Measured on B200: 95.5 ms per rank at G = 8 against 106.6 ms for its bank
+        # shard (+ exchange); the bank-sharded forms stay for banks that do not fit one GPU.
+        exchange = "queries"
+    if world > 1 and exchange == "lists":
         cnt = 0
         if mode != "exact" and hasattr(stages, "lists_available"):
             cnt = int(stages.lists_available(n, hi - lo, _fp32(rep)[0].numel(), k, world))
@@ -241,6 +259,13 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="a
         exchange = "lists" if ok else "all_to_all"
     elif exchange == "auto":
         exchange = "all_to_all"
+
+    if world > 1 and exchange == "queries":
+        in_split = [b - a for a, b in (shard_bounds(n, world, r) for r in range(world))]
+        d_mine, i_mine = stages.block_knn(rep, lo, hi, k, mode)
+        tm("block_knn")
+        return _finish_block(d_mine, i_mine, n, lo, hi, in_split, world, k, avg, use_rms, clip, rms,
+                             group, stages, tm, return_knn)
 
     if world > 1 and exchange == "lists":
         bounds = [shard_bounds(n, world, r) for r in range(world)]

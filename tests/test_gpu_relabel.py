@@ -111,3 +111,23 @@ def test_lists_form_rejects_per_update_sizes():
     x = reps(1, 1024, 64).to(DEV)
     with pytest.raises(ValueError):
         xknn.knn_screen_lists(x, x, 12)
+
+
+def test_query_block_against_long_bank_wave_splits():
+    """A query block with more tiles than SMs against a long bank (the 'queries' exchange of the
+    sharded relabel): the plan cuts the bank into <= 4 ranges to fill the last wave; results must
+    equal the exact fp32 kernel and, on a subset, the oracle."""
+    nq, nb, dim, k = 25000, 600000, 64, 12
+    bank = reps(13, nb, dim).to(DEV)
+    q = bank[300000:300000 + nq]
+    d_s, i_s = xb.knn_topk(q, bank, k, mode="screened")
+    und, invalid, _, _ = xb.knn.screened_status(DEV)
+    assert invalid == 0
+    d_e, i_e = xb.knn_topk(q, bank, k, mode="exact")
+    np.testing.assert_allclose(d_s.cpu().numpy(), d_e.cpu().numpy(), rtol=1e-6)
+    diff = (i_s.sort(dim=1).values != i_e.sort(dim=1).values).any(dim=1).sum().item()
+    assert diff <= nq // 1000
+    assert torch.equal(i_s[:, 0].cpu(), torch.arange(300000, 300000 + nq, dtype=torch.int32))
+    sub = torch.arange(0, nq, 250)
+    qc, bc = q.cpu(), bank.cpu()
+    assert_knn_matches(qc[sub], bc, k, d_s[sub.to(DEV)], i_s[sub.to(DEV)])

@@ -28,6 +28,12 @@ class _OracleStages:
         d, i = knn_smallest(rep, rep[lo:hi], k)
         return d, (i + lo).to(torch.int32)
 
+    @staticmethod
+    def block_knn(rep, lo, hi, k, mode):
+        from oracle import knn_smallest
+        d, i = knn_smallest(rep[lo:hi], rep, k)
+        return d, i.to(torch.int32)
+
     # "lists" exchange: stand-ins with the CUDA contracts — per shard, every query keeps its k + 2
     # best bank rows as (score = -dist^2, LOCAL index) in two lists of 24 slots (as the 8-warp
     # screen does: even / odd positions), counts in cnt; the rerank merges all shards' lists.
@@ -131,7 +137,7 @@ def _worker(rank, world, port, exchange, n, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("exchange", ["all_gather", "all_to_all", "lists", "auto"])
+@pytest.mark.parametrize("exchange", ["all_gather", "all_to_all", "lists", "queries", "auto"])
 @pytest.mark.parametrize("n", [64, 51])
 def test_two_rank_relabel_equals_unsharded(exchange, n):
     from oracle import RmsState, pbe_reward
