@@ -99,6 +99,45 @@ def c1():
              cpu_cores=torch.get_num_threads(), flops=2 * 1024 * 1024 * 512, target_us=50)
 
 
+def c1b():
+    """compute_intr_reward of icm_apt.py:96-100 from observations: trunk (Linear -> LayerNorm ->
+    Tanh, 24 -> 512) then PBE.  'torch trunk' = the reference's nn.Sequential on the GPU feeding
+    xb.PBE; 'fused producer' = xb.icm_get_rep (one kernel: rep + prepared operand) feeding xb.PBE."""
+    g = torch.Generator().manual_seed(0)
+    obs = torch.randn(1024, 24, generator=g).to(DEV)
+    trunk = torch.nn.Sequential(torch.nn.Linear(24, 512), torch.nn.LayerNorm(512),
+                                torch.nn.Tanh()).to(DEV)
+    pa = xb.PBE(xb.RMS(DEV), 0.0, 12, True, True, DEV)
+    pa.mode = "screened"
+    pb = xb.PBE(xb.RMS(DEV), 0.0, 12, True, True, DEV)
+
+    def torch_trunk():
+        with torch.no_grad():
+            return pa(trunk(obs))
+
+    def fused():
+        return pb(xb.icm_get_rep(trunk, obs))
+
+    def producer_only():
+        return xb.icm_get_rep(trunk, obs)
+
+    def torch_trunk_only():
+        with torch.no_grad():
+            return trunk(obs)
+
+    for name, fn in (("torch trunk + PBE", torch_trunk), ("fused producer + PBE", fused),
+                     ("fused producer alone", producer_only),
+                     ("torch trunk alone", torch_trunk_only)):
+        med, best = time_gpu(fn)
+        try:
+            gmed, gbest = time_graph(fn)
+        except Exception as e:
+            gmed = gbest = None
+            print("graph capture failed:", e, file=sys.stderr)
+        emit(case="C1b obs (1024x24) -> ICM trunk -> PBE k=12 avg+rms", path=name,
+             gpu_us_median=med, gpu_us_min=best, graph_us_median=gmed, graph_us_min=gbest)
+
+
 def c2():
     g = torch.Generator().manual_seed(1)
     z = torch.nn.functional.normalize(torch.randn(1024, 128, generator=g), dim=1)
@@ -148,6 +187,27 @@ def c3():
          two_launch_draw_gather_us_min=best2, gather_only_us_median=gmed,
          gather_only_us_min=gbest, algorithmic_bytes=464 * 1024, cpu_us_median=cpu_us, cpu_cores=1,
          note="latency-bound (475 KB per batch); CPU = reference per-sample python arithmetic")
+
+
+    # BASELINE config 3 end to end: one APT update's data path — sample a 1024-batch from the
+    # device buffer, ICM trunk on obs (24 -> 512, fused producer), PBE reward
+    trunk = torch.nn.Sequential(torch.nn.Linear(24, 512), torch.nn.LayerNorm(512),
+                                torch.nn.Tanh()).to(DEV)
+    pbe = xb.PBE(xb.RMS(DEV), 0.0, 12, True, True, DEV)
+
+    def update_path():
+        call[0] += 1
+        batch = buf.sample_philox(1024, 7, call[0])
+        return pbe(xb.icm_get_rep(trunk, batch[0]))
+    umed, ubest = time_gpu(update_path)
+    try:
+        ugmed, ugbest = time_graph(update_path)
+    except Exception as e:
+        ugmed = ugbest = None
+        print("graph capture failed:", e, file=sys.stderr)
+    emit(case="C3 end to end: sample B=1024 nstep=3 -> ICM trunk 24->512 -> PBE k=12",
+         gpu_us_median=umed, gpu_us_min=ubest, graph_us_median=ugmed, graph_us_min=ugbest,
+         launches="replay sample, trunk producer, latency screen, rerank+moments, finish")
 
 
 def c4(n_trans):
@@ -203,4 +263,4 @@ if __name__ == "__main__":
     a = ap.parse_args()
     torch.set_num_threads(os.cpu_count() or 1)
     for c in a.cases.split(","):
-        {"c1": c1, "c2": c2, "c3": c3, "c4": lambda: c4(a.c4_transitions)}[c]()
+        {"c1": c1, "c1b": c1b, "c2": c2, "c3": c3, "c4": lambda: c4(a.c4_transitions)}[c]()

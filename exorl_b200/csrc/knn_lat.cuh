@@ -42,6 +42,8 @@ struct LatParams {
   int rsel;          // ceil(k / splits)
   float* bank_max;   // [2] out: EB, HBmax (written by block (0,0) for the rerank kernel)
   long long* trace;  // optional phase timestamps (debug)
+  unsigned long long* zero_status;   // caller-prepared operands: nobody ran prep (which zeroes the
+                                     // 24-byte rerank status), so block (0,0) does it here
 };
 
 template <int KS>
@@ -185,6 +187,9 @@ knn_screen_lat_kernel(const __grid_constant__ CUtensorMap tmap_q,
     if (et == 0 && blockIdx.x == 0 && blockIdx.y == 0) {
       p.bank_max[0] = eb_max;
       p.bank_max[1] = hb_max;
+      if (p.zero_status != nullptr) {
+        p.zero_status[0] = 0ull; p.zero_status[1] = 0ull; p.zero_status[2] = 0ull;
+      }
     }
 
     ListState st;   // tv[] of ListState unused here: the chain is the KS-stage array below

@@ -1272,9 +1272,7 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
     }
     // per-update chain: prep -> latency screen -> rerank (inline fallback); no memset, no atomics
     int rc = EXB_OK;
-    if (pre) {
-      EXB_CUDA(cudaMemsetAsync(w.status, 0, 24, st));   // what prep's zero16 does
-    } else {
+    if (!pre) {
       rc = launch_prep(bank, nb, dim, pl.dpad, w.b16, w.hb, w.eb, nullptr, st,
                        reinterpret_cast<unsigned long long*>(w.status));
       if (rc) return rc;
@@ -1305,6 +1303,7 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
     lp.cand_cnt = w.cand_cnt; lp.cand_tk = w.cand_tk; lp.cand_tr = w.cand_tr;
     lp.rsel = (k + pl.splits - 1) / pl.splits; lp.bank_max = reinterpret_cast<float*>(w.bsc);
     lp.trace = trace_on ? w.trace : nullptr;
+    lp.zero_status = pre ? reinterpret_cast<unsigned long long*>(w.status) : nullptr;
     dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
     const bool prof = g_prof.on && g_prof.n < 64;
     if (prof) EXB_CUDA(cudaEventRecord(g_prof.e0[g_prof.n], st));

@@ -24,6 +24,42 @@ namespace exb {
 constexpr int RP_WARPS = 8;
 constexpr int RP_SMEM_LIMIT = 232448;   // 227 KB
 
+// tanh of two values with packed fp32 arithmetic (FMUL2 / FFMA2 / FADD2 issue once per pair).
+//   |y| <  0.55 : y + y t Q(t), t = y^2, Q = degree-4 least-squares fit on Chebyshev nodes of
+//                 (tanh(sqrt t)/sqrt t - 1)/t over [0, 0.3025]; max error 0.83 ulp in fp32
+//   |y| >= 0.55 : sign(y) (1 - 2 / (exp(2|y|) + 1)) with ex2.approx / rcp.approx: <= 2 ulp
+//                 (exp overflow -> rcp(inf) = 0 -> 1; NaN propagates through both branches)
+// ~11 issue slots per value against ~19 for tanhf, same accuracy class (tanhf: 2 ulp).
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float2 tanh2(float2 y) {
+  const float2 t = __fmul2_rn(y, y);
+  float2 q = make_float2(-0.006615746766328812f, -0.006615746766328812f);
+  q = __ffma2_rn(q, t, make_float2(0.021312739700078964f, 0.021312739700078964f));
+  q = __ffma2_rn(q, t, make_float2(-0.053910065442323685f, -0.053910065442323685f));
+  q = __ffma2_rn(q, t, make_float2(0.13333117961883545f, 0.13333117961883545f));
+  q = __ffma2_rn(q, t, make_float2(-0.3333333134651184f, -0.3333333134651184f));
+  const float2 small = __ffma2_rn(y, __fmul2_rn(t, q), y);
+  const float2 ay = make_float2(fabsf(y.x), fabsf(y.y));
+  const float2 sc = __fmul2_rn(ay, make_float2(2.8853900817779268f, 2.8853900817779268f));
+  const float2 e1 = __fadd2_rn(make_float2(ex2_approx(sc.x), ex2_approx(sc.y)),
+                               make_float2(1.f, 1.f));
+  const float2 big = __ffma2_rn(make_float2(rcp_approx(e1.x), rcp_approx(e1.y)),
+                                make_float2(-2.f, -2.f), make_float2(1.f, 1.f));
+  float2 r;
+  r.x = ay.x < 0.55f ? small.x : copysignf(big.x, y.x);
+  r.y = ay.y < 0.55f ? small.y : copysignf(big.y, y.y);
+  return r;
+}
+
 // LayerNorm (biased variance, two-pass in registers) + affine + tanh on R warp-resident rows;
 // the R reductions are interleaved so that their shuffle latencies overlap.
 // torch.nn.LayerNorm semantics: y = (x - mean) / sqrt(var + eps) * weight + bias.
@@ -36,10 +72,13 @@ __device__ __forceinline__ void ln_tanh_rows(float4 (&v)[R][NCH], int lane, int 
   float s[R];
 #pragma unroll
   for (int r = 0; r < R; ++r) {
-    s[r] = 0.f;
+    float2 s2 = make_float2(0.f, 0.f);
 #pragma unroll
     for (int i = 0; i < NCH; ++i)
-      if (FULL || lane + 32 * i < nv) s[r] += (v[r][i].x + v[r][i].y) + (v[r][i].z + v[r][i].w);
+      if (FULL || lane + 32 * i < nv)
+        s2 = __fadd2_rn(s2, __fadd2_rn(make_float2(v[r][i].x, v[r][i].y),
+                                       make_float2(v[r][i].z, v[r][i].w)));
+    s[r] = s2.x + s2.y;
   }
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1)
@@ -49,12 +88,14 @@ __device__ __forceinline__ void ln_tanh_rows(float4 (&v)[R][NCH], int lane, int 
 #pragma unroll
   for (int r = 0; r < R; ++r) {
     const float mean = s[r] * inv_dim;
+    const float2 nm = make_float2(-mean, -mean);
     float2 q2 = make_float2(0.f, 0.f);
 #pragma unroll
     for (int i = 0; i < NCH; ++i)
       if (FULL || lane + 32 * i < nv) {
-        v[r][i].x -= mean; v[r][i].y -= mean; v[r][i].z -= mean; v[r][i].w -= mean;
-        const float2 a = make_float2(v[r][i].x, v[r][i].y), b = make_float2(v[r][i].z, v[r][i].w);
+        const float2 a = __fadd2_rn(make_float2(v[r][i].x, v[r][i].y), nm);
+        const float2 b = __fadd2_rn(make_float2(v[r][i].z, v[r][i].w), nm);
+        v[r][i] = make_float4(a.x, a.y, b.x, b.y);
         q2 = __ffma2_rn(a, a, q2);
         q2 = __ffma2_rn(b, b, q2);
       }
@@ -74,10 +115,12 @@ __device__ __forceinline__ void ln_tanh_rows(float4 (&v)[R][NCH], int lane, int 
       const float4 g = __ldg(g4 + c), b = __ldg(b4 + c);
 #pragma unroll
       for (int r = 0; r < R; ++r) {
-        v[r][i].x = tanhf(fmaf(v[r][i].x * rstd[r], g.x, b.x));
-        v[r][i].y = tanhf(fmaf(v[r][i].y * rstd[r], g.y, b.y));
-        v[r][i].z = tanhf(fmaf(v[r][i].z * rstd[r], g.z, b.z));
-        v[r][i].w = tanhf(fmaf(v[r][i].w * rstd[r], g.w, b.w));
+        const float2 rs = make_float2(rstd[r], rstd[r]);
+        const float2 lo = tanh2(__ffma2_rn(__fmul2_rn(make_float2(v[r][i].x, v[r][i].y), rs),
+                                           make_float2(g.x, g.y), make_float2(b.x, b.y)));
+        const float2 hi = tanh2(__ffma2_rn(__fmul2_rn(make_float2(v[r][i].z, v[r][i].w), rs),
+                                           make_float2(g.z, g.w), make_float2(b.z, b.w)));
+        v[r][i] = make_float4(lo.x, lo.y, hi.x, hi.y);
       }
     }
   }
@@ -104,10 +147,37 @@ rep_trunk_kernel(const float* __restrict__ obs, int64_t n, int in_dim,
   float* obs_s = obs_all + (size_t)warp * in_dim * R;          // [in_dim][R]
   {
     float* wt = reinterpret_cast<float*>(Wt);
-    const int total = in_dim * dim;
-    for (int i = threadIdx.x; i < total; i += blockDim.x) {
-      const int kk = i / dim, d = i - kk * dim;                // shared-memory-coalesced order
-      wt[i] = __ldg(W + (size_t)d * in_dim + kk);
+    if ((in_dim & 3) == 0 && (reinterpret_cast<uintptr_t>(W) & 15) == 0) {
+      // coalesced 16-byte reads of the row-major weight, all of a thread's loads in flight,
+      // transposed scalar stores (the per-update call is latency-bound on this staging)
+      const float4* W4 = reinterpret_cast<const float4*>(W);
+      const int q = in_dim >> 2, total4 = q * dim;
+      constexpr int SB = 12;   // loads in flight per thread: 24 x 512 weights = ONE round trip
+      for (int i0 = threadIdx.x; i0 < total4; i0 += SB * blockDim.x) {
+        float4 t[SB];
+#pragma unroll
+        for (int u = 0; u < SB; ++u) {
+          const int i = i0 + u * blockDim.x;
+          t[u] = (i < total4) ? __ldg(W4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < SB; ++u) {
+          const int i = i0 + u * blockDim.x;
+          if (i < total4) {
+            const int d = i / q, kk = (i - d * q) * 4;
+            wt[(kk + 0) * dim + d] = t[u].x;
+            wt[(kk + 1) * dim + d] = t[u].y;
+            wt[(kk + 2) * dim + d] = t[u].z;
+            wt[(kk + 3) * dim + d] = t[u].w;
+          }
+        }
+      }
+    } else {
+      const int total = in_dim * dim;
+      for (int i = threadIdx.x; i < total; i += blockDim.x) {
+        const int kk = i / dim, d = i - kk * dim;                // shared-memory-coalesced order
+        wt[i] = __ldg(W + (size_t)d * in_dim + kk);
+      }
     }
   }
   __syncthreads();
@@ -115,7 +185,8 @@ rep_trunk_kernel(const float* __restrict__ obs, int64_t n, int in_dim,
   const float4* g4 = reinterpret_cast<const float4*>(ln_w);
   const float4* be4 = reinterpret_cast<const float4*>(ln_b);
   const int64_t groups = (n + R - 1) / R;
-  for (int64_t grp = (int64_t)blockIdx.x * RP_WARPS + warp; grp < groups;
+  // group g -> block g % grid, warp (g / grid) % 8: a small batch spreads over all the SMs
+  for (int64_t grp = (int64_t)blockIdx.x + (int64_t)gridDim.x * warp; grp < groups;
        grp += (int64_t)gridDim.x * RP_WARPS) {
     const int64_t row0 = grp * R;
     const int rows = (int)((n - row0) < R ? (n - row0) : R);
@@ -142,10 +213,15 @@ rep_trunk_kernel(const float* __restrict__ obs, int64_t n, int in_dim,
         w[i] = (FULL || c < nv) ? Wt[kk * nv + c] : make_float4(0.f, 0.f, 0.f, 0.f);
       }
       float o[R];
+      if constexpr (R % 4 == 0) {
 #pragma unroll
-      for (int r4 = 0; r4 < R / 4; ++r4) {
-        const float4 t = reinterpret_cast<const float4*>(obs_s + kk * R)[r4];
-        o[4 * r4] = t.x; o[4 * r4 + 1] = t.y; o[4 * r4 + 2] = t.z; o[4 * r4 + 3] = t.w;
+        for (int r4 = 0; r4 < R / 4; ++r4) {
+          const float4 t = reinterpret_cast<const float4*>(obs_s + kk * R)[r4];
+          o[4 * r4] = t.x; o[4 * r4 + 1] = t.y; o[4 * r4 + 2] = t.z; o[4 * r4 + 3] = t.w;
+        }
+      } else {
+#pragma unroll
+        for (int r = 0; r < R; ++r) o[r] = obs_s[kk * R + r];
       }
 #pragma unroll
       for (int r = 0; r < R; ++r) {
@@ -164,6 +240,61 @@ rep_trunk_kernel(const float* __restrict__ obs, int64_t n, int in_dim,
     ln_tanh_rows<R, NCH, FULL>(acc, lane, dim, g4, be4, eps);
     emit_rows<R, NCH, FULL>(acc, lane, dim, row0, rows, out_rep, op);
   }
+}
+
+// Per-update batches (latency-bound): one warp per row, NO shared-memory staging and no block
+// barrier — every lane reads the rows of the row-major weight that belong to its 16 output
+// columns straight from global memory (16-byte pieces, L1/L2-resident after the first warps) and
+// accumulates even and odd input columns in the two halves of an FFMA2.  in_dim % 4 == 0.
+template <int NCH, bool FULL>
+__global__ void __launch_bounds__(128)
+rep_trunk_small_kernel(const float* __restrict__ obs, int64_t n, int in_dim,
+                       const float* __restrict__ W, const float* __restrict__ bias,
+                       const float* __restrict__ ln_w, const float* __restrict__ ln_b, float eps,
+                       int dim, float* __restrict__ out_rep, OpOut op) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (row >= n) return;
+  const int nv = dim >> 2, q = in_dim >> 2;
+  const float4* o4 = reinterpret_cast<const float4*>(obs + row * in_dim);
+  float2 acc[NCH][4];
+#pragma unroll
+  for (int i = 0; i < NCH; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = make_float2(0.f, 0.f);
+#pragma unroll 2
+  for (int kc = 0; kc < q; ++kc) {
+    const float4 o = __ldg(o4 + kc);
+    float4 w[NCH][4];
+#pragma unroll
+    for (int i = 0; i < NCH; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int d = 4 * (lane + 32 * i) + j;
+        w[i][j] = (FULL || d < dim)
+                      ? __ldg(reinterpret_cast<const float4*>(W + (size_t)d * in_dim) + kc)
+                      : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+    for (int i = 0; i < NCH; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        acc[i][j] = __ffma2_rn(make_float2(o.x, o.y), make_float2(w[i][j].x, w[i][j].y), acc[i][j]);
+        acc[i][j] = __ffma2_rn(make_float2(o.z, o.w), make_float2(w[i][j].z, w[i][j].w), acc[i][j]);
+      }
+  }
+  float4 v[1][NCH];
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    const int c = lane + 32 * i;
+    const float4 bv = (FULL || c < nv) ? __ldg(reinterpret_cast<const float4*>(bias) + c)
+                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+    v[0][i] = make_float4(bv.x + (acc[i][0].x + acc[i][0].y), bv.y + (acc[i][1].x + acc[i][1].y),
+                          bv.z + (acc[i][2].x + acc[i][2].y), bv.w + (acc[i][3].x + acc[i][3].y));
+  }
+  ln_tanh_rows<1, NCH, FULL>(v, lane, dim, reinterpret_cast<const float4*>(ln_w),
+                             reinterpret_cast<const float4*>(ln_b), eps);
+  emit_rows<1, NCH, FULL>(v, lane, dim, row, 1, out_rep, op);
 }
 
 // LayerNorm -> Tanh on given pre-activations, one warp per row (in place allowed).
@@ -253,6 +384,32 @@ extern "C" size_t exb_rep_trunk_smem_bytes(int in_dim, int rep_dim) {
   return (size_t)in_dim * ((size_t)rep_dim + RP_WARPS * 8) * sizeof(float);
 }
 
+static int launch_trunk_small(const float* obs, int64_t n, int in_dim, const float* W,
+                              const float* b, const float* g, const float* be, float eps, int dim,
+                              float* out_rep, const OpOut& op, cudaStream_t st) {
+  const int nch = (dim / 4 + 31) / 32;
+  const unsigned grid = (unsigned)((n + 3) / 4);
+#define EXB_SMALL_CASE(KEY, NCH, FULL)                                                         \
+  case KEY:                                                                                    \
+    rep_trunk_small_kernel<NCH, FULL><<<grid, 128, 0, st>>>(obs, n, in_dim, W, b, g, be, eps,  \
+                                                            dim, out_rep, op);                 \
+    break;
+  switch (nch * 2 + (dim == nch * 128 ? 1 : 0)) {
+    EXB_SMALL_CASE(2, 1, false)
+    EXB_SMALL_CASE(3, 1, true)
+    EXB_SMALL_CASE(4, 2, false)
+    EXB_SMALL_CASE(5, 2, true)
+    EXB_SMALL_CASE(6, 3, false)
+    EXB_SMALL_CASE(7, 3, true)
+    EXB_SMALL_CASE(8, 4, false)
+    EXB_SMALL_CASE(9, 4, true)
+    default: set_error("rep_dim %d too wide", dim); return EXB_EUNSUPPORTED;
+  }
+#undef EXB_SMALL_CASE
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}
+
 template <int R>
 static int launch_trunk(const float* obs, int64_t n, int in_dim, const float* W, const float* b,
                         const float* g, const float* be, float eps, int dim, float* out_rep,
@@ -260,10 +417,10 @@ static int launch_trunk(const float* obs, int64_t n, int in_dim, const float* W,
   const size_t smem = (size_t)in_dim * ((size_t)dim + RP_WARPS * R) * sizeof(float);
   const int nch = (dim / 4 + 31) / 32;
   const int64_t groups = (n + R - 1) / R;
-  int64_t blocks = (groups + RP_WARPS - 1) / RP_WARPS;
+  int64_t blocks = groups;
   const int sms = sm_count();
   // persistent: as many blocks per SM as registers / shared memory allow (R = 4: two)
-  const int per_sm = (R <= 4 && 2 * (smem + 1024) <= (size_t)RP_SMEM_LIMIT) ? 2 : 1;
+  const int per_sm = (R == 4 && 2 * (smem + 1024) <= (size_t)RP_SMEM_LIMIT) ? 2 : 1;
   if (blocks > (int64_t)sms * per_sm) blocks = (int64_t)sms * per_sm;
 #define EXB_TRUNK_CASE(KEY, NCH, FULL)                                                          \
   case KEY: {                                                                                   \
@@ -316,6 +473,22 @@ extern "C" int exb_rep_trunk_f32(const float* obs, int64_t n, int in_dim, const 
     const char* e = getenv("EXB_TRUNK_R");
     return e ? atoi(e) != 8 : 1;
   }();
+  // per-update batches: one row per warp so that a 1024-row batch runs as 1024 short warps over
+  // all SMs instead of 256 long ones (16.4 us per 1024 x 24 -> 512 call with R = 4)
+  // measured on B200, 1024 x 24 -> 512: the no-staging kernel takes 22.5 us against 14.3 us for
+  // the shared-memory kernel with one row per warp (its per-lane weight reads cost 32 sectors per
+  // load instruction), so it is an A/B knob only (EXB_TRUNK_SMALL=1)
+  static const int small_on = [] {
+    const char* e = getenv("EXB_TRUNK_SMALL");
+    return e ? atoi(e) : 0;
+  }();
+  if (small_on && n <= 8192 && (in_dim & 3) == 0 &&
+      (((uintptr_t)weight | (uintptr_t)obs) & 15) == 0)
+    return launch_trunk_small(obs, n, in_dim, weight, bias, ln_weight, ln_bias, ln_eps, rep_dim,
+                              out_rep, op, (cudaStream_t)stream);
+  if (n <= 8192)
+    return launch_trunk<1>(obs, n, in_dim, weight, bias, ln_weight, ln_bias, ln_eps, rep_dim,
+                           out_rep, op, (cudaStream_t)stream);
   if (r4)
     return launch_trunk<4>(obs, n, in_dim, weight, bias, ln_weight, ln_bias, ln_eps, rep_dim,
                            out_rep, op, (cudaStream_t)stream);

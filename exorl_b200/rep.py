@@ -23,15 +23,31 @@ class PreparedRep:
     """`.rep` (n, dim) fp32 + the prepared operand (`f16` (n, dim_pad), `half_norm`, `round_err`
     (n,), `scalars` 16 bytes).  Behaves like the rep for shape queries."""
 
+    _zero_pool = {}   # device -> [int32 tensor of pre-zeroed 16-byte slots, next slot]
+
+    @classmethod
+    def _zeroed_scalars(cls, dev):
+        """A fresh all-zero 16-byte scalars word without a fill launch per call (the per-update
+        chain is launch-bound): slots of a zeroed pool, each handed out once."""
+        key = dev.index if dev.index is not None else torch.cuda.current_device()
+        ent = cls._zero_pool.get(key)
+        if ent is None or ent[1] >= ent[0].size(0):
+            ent = [torch.zeros(4096, 4, dtype=torch.int32, device=dev), 0]
+            cls._zero_pool[key] = ent
+        ent[1] += 1
+        return ent[0][ent[1] - 1]
+
     def __init__(self, n, dim, device, rep=None):
         dev = torch.device(device)
         self.rep = rep if rep is not None else torch.empty(n, dim, dtype=torch.float32,
                                                            device=dev)
-        # one allocation, 256-byte aligned pieces (TMA needs the fp16 rows 128-byte aligned)
-        self.f16 = torch.empty(n, _dim_pad(dim), dtype=torch.float16, device=dev)
-        self.half_norm = torch.empty(n, dtype=torch.float32, device=dev)
-        self.round_err = torch.empty(n, dtype=torch.float32, device=dev)
-        self.scalars = torch.zeros(4, dtype=torch.int32, device=dev)
+        # one allocation; the fp16 block comes first (TMA needs its rows 128-byte aligned)
+        dpad = _dim_pad(dim)
+        buf = torch.empty(n * (2 * dpad + 8), dtype=torch.uint8, device=dev)
+        self.f16 = buf[:n * 2 * dpad].view(torch.float16).view(n, dpad)
+        self.half_norm = buf[n * 2 * dpad:n * (2 * dpad + 4)].view(torch.float32)
+        self.round_err = buf[n * (2 * dpad + 4):].view(torch.float32)
+        self.scalars = self._zeroed_scalars(dev)
         self._c = _lib.Operand(self.f16.data_ptr(), self.half_norm.data_ptr(),
                                self.round_err.data_ptr(), self.scalars.data_ptr())
 

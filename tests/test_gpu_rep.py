@@ -88,7 +88,8 @@ def test_apt_reward_from_obs_matches_reference(golden, tag):
 
 @pytest.mark.parametrize("n,in_dim,dim", [(1, 24, 512), (7, 24, 512), (8, 24, 512), (1027, 24, 512),
                                           (300, 3, 4), (513, 96, 256), (4099, 24, 384),
-                                          (100, 110, 512), (64, 39200, 512)])
+                                          (100, 110, 512), (64, 39200, 512),
+                                          (9001, 24, 512), (8195, 17, 128), (8194, 6, 36)])
 def test_icm_trunk_shapes_vs_oracle(n, in_dim, dim):
     g = torch.Generator().manual_seed(n + in_dim)
     obs = torch.randn(n, in_dim, generator=g)
