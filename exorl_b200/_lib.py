@@ -79,6 +79,8 @@ SIGNATURES = {
                                           _c.c_int, _c.c_int, _f32, _vp, _vp, _f64, _vp, _vp,
                                           _vp, _vp, _vp, _vp, _sz, _vp]),
     "exb_rms_update": (_c.c_int, [_vp, _i64, _vp, _vp, _f64, _vp, _vp, _vp, _sz, _vp]),
+    "exb_rnd_reward_f32": (_c.c_int, [_vp, _vp, _i64, _c.c_int, _f32, _vp, _vp, _f64, _vp, _vp,
+                                      _vp, _vp, _vp, _sz, _vp]),
     "exb_take_kth": (_c.c_int, [_vp, _i64, _c.c_int, _vp, _vp]),
     "exb_replay_gather": (_c.c_int, [_vp, _i64, _c.POINTER(GatherCol), _c.c_int, _vp, _vp,
                                      _c.c_int, _c.c_int, _f32, _vp, _vp, _vp]),

@@ -249,3 +249,115 @@ extern "C" int exb_take_kth(const float* knn_dist, int64_t nq, int k, float* out
   EXB_LAUNCH_CHECK();
   return EXB_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// RND intrinsic reward (the other consumer of the running moments):
+//   prediction_error = mean_c (target - prediction)^2            rnd.py:52-54
+//   _, var = RMS(prediction_error)                               rnd.py:96, utils/utils.py:264-276
+//   reward = rnd_scale * prediction_error / (sqrt(var) + 1e-8)   rnd.py:97-98
+// Launch 1: one warp per row computes the error, every block adds its rows' (sum, sumsq) in fp64,
+// the last block (ticket) reduces the partials and applies the Chan update.  Launch 2: scaling by
+// the UPDATED variance.
+// ------------------------------------------------------------------------------------------
+namespace exb {
+
+__global__ void __launch_bounds__(PBE_THREADS)
+rnd_error_moments_kernel(const float* __restrict__ pred, const float* __restrict__ target,
+                         int64_t n, int dim, float* __restrict__ err_out,
+                         double2* __restrict__ partials, unsigned* __restrict__ ticket,
+                         double* __restrict__ out_sums, RmsParams p) {
+  __shared__ double2 red[PBE_THREADS / 32];
+  __shared__ bool is_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const bool vec = (dim & 3) == 0 &&
+                   ((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(target)) & 15) == 0;
+  const float inv_dim = 1.0f / (float)dim;
+  double2 acc = make_double2(0.0, 0.0);
+  for (int64_t row = (int64_t)blockIdx.x * (PBE_THREADS / 32) + warp; row < n;
+       row += (int64_t)gridDim.x * (PBE_THREADS / 32)) {
+    const float* a = pred + row * dim;
+    const float* b = target + row * dim;
+    float s = 0.f;
+    if (vec) {
+      const float4* a4 = reinterpret_cast<const float4*>(a);
+      const float4* b4 = reinterpret_cast<const float4*>(b);
+      for (int c = lane; c < (dim >> 2); c += 32) {
+        const float4 x = __ldg(a4 + c), y = __ldg(b4 + c);
+        const float d0 = y.x - x.x, d1 = y.y - x.y, d2 = y.z - x.z, d3 = y.w - x.w;
+        s = fmaf(d0, d0, s); s = fmaf(d1, d1, s); s = fmaf(d2, d2, s); s = fmaf(d3, d3, s);
+      }
+    } else {
+      for (int c = lane; c < dim; c += 32) {
+        const float d = b[c] - a[c];
+        s = fmaf(d, d, s);
+      }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+    const float e = s * inv_dim;
+    if (lane == 0) {
+      err_out[row] = e;
+      acc.x += (double)e;
+      acc.y += (double)e * (double)e;
+    }
+  }
+  const double2 tot = block_sum2<PBE_THREADS>(acc, red);
+  if (threadIdx.x == 0) {
+    partials[blockIdx.x] = tot;
+    __threadfence();
+    const unsigned t = atomicAdd(ticket, 1u);
+    is_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  double2 a = make_double2(0.0, 0.0);
+  for (int i = threadIdx.x; i < (int)gridDim.x; i += PBE_THREADS) {
+    const double2 t = partials[i];
+    a.x += t.x;
+    a.y += t.y;
+  }
+  const double2 all = block_sum2<PBE_THREADS>(a, red);
+  if (threadIdx.x == 0) {
+    out_sums[0] = (double)n;
+    out_sums[1] = all.x;
+    out_sums[2] = all.y;
+    rms_apply(out_sums, p);
+    *ticket = 0u;
+  }
+}
+
+__global__ void rnd_scale_kernel(const float* __restrict__ err, int64_t n, float scale,
+                                 const float* __restrict__ s_ptr, float* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float den = sqrtf(*s_ptr) + 1e-8f;
+  out[i] = (scale * err[i]) / den;
+}
+
+}  // namespace exb
+
+extern "C" int exb_rnd_reward_f32(const float* prediction, const float* target, int64_t n,
+                                  int dim, float scale, const float* rms_m_in,
+                                  const float* rms_s_in, double rms_n, float* rms_m_out,
+                                  float* rms_s_out, float* out_error, float* out_reward,
+                                  void* workspace, size_t workspace_bytes, exb_stream_t stream) {
+  EXB_CHECK_ARG(prediction && target && out_error && out_reward && n > 0 && dim > 0,
+                "bad arguments");
+  EXB_CHECK_ARG(rms_m_in && rms_s_in && rms_m_out && rms_s_out, "RMS state pointers missing");
+  PbeWs w;
+  int rc = carve_pbe(workspace, workspace_bytes, &w);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  RmsParams p{rms_m_in, rms_s_in, rms_n, rms_m_out, rms_s_out};
+  int64_t blocks = (n + PBE_THREADS / 32 - 1) / (PBE_THREADS / 32);
+  const int64_t cap = 4LL * sm_count();
+  if (blocks > cap) blocks = cap;
+  rnd_error_moments_kernel<<<(unsigned)blocks, PBE_THREADS, 0, st>>>(
+      prediction, target, n, dim, out_error, w.partials, w.ticket, w.sums, p);
+  EXB_LAUNCH_CHECK();
+  rnd_scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out_error, n, scale, rms_s_out,
+                                                               out_reward);
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}

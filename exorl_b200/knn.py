@@ -364,6 +364,39 @@ class PBE(object):
                                   mode=getattr(self, "mode", "auto"))
 
 
+def rnd_intr_reward(prediction, target, rms, rnd_scale=1.0):
+    """RND reward from the predictor / target network outputs — replaces the arithmetic of
+    RND.forward's last line (agents/unsupervised_learning/rnd.py:52-54) and of
+    RNDAgent.compute_intr_reward (:94-99): prediction_error = mean((target - prediction)^2, -1),
+    `rms(prediction_error)` (state rebound and n advanced like utils/utils.py:272-274),
+    reward = rnd_scale * prediction_error / (sqrt(var) + 1e-8).
+    Returns (reward (n, 1), prediction_error (n, 1))."""
+    lib = _lib.load()
+    pred = _as_rows(prediction, "prediction")
+    tgt = _as_rows(target, "target")
+    if pred.shape != tgt.shape:
+        raise RuntimeError(f"The size of tensor a {tuple(tgt.shape)} must match the size of "
+                           f"tensor b {tuple(pred.shape)}")
+    if rms.M.numel() != 1 or not rms.M.is_cuda:
+        raise ValueError("the RMS state used by RND must have shape (1,) on the GPU")
+    n, dim = pred.shape
+    dev = pred.device
+    with torch.cuda.device(dev):
+        err = torch.empty(n, 1, dtype=torch.float32, device=dev)
+        reward = torch.empty(n, 1, dtype=torch.float32, device=dev)
+        if n == 0:
+            return reward, err
+        new_m, new_s = torch.empty_like(rms.M), torch.empty_like(rms.S)
+        ws = _pbe_ws(dev)
+        _lib.check(lib.exb_rnd_reward_f32(
+            _lib.ptr(pred), _lib.ptr(tgt), n, dim, float(rnd_scale), _lib.ptr(rms.M),
+            _lib.ptr(rms.S), float(rms.n), _lib.ptr(new_m), _lib.ptr(new_s), _lib.ptr(err),
+            _lib.ptr(reward), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+    rms.M, rms.S = new_m, new_s
+    rms.n += n
+    return reward, err
+
+
 def proto_enqueue(queue, queue_ptr, z, candidates):
     """FIFO write of z[candidates] into the queue; returns the new pointer (proto.py:110-112)."""
     n = candidates.numel()

@@ -126,8 +126,8 @@ def icm_get_rep(icm, obs):
     lib = _lib.load()
     w, b, g, be, eps = _trunk_params(icm)
     obs = _f32c(obs, "obs")
-    obs = obs.reshape(obs.size(0), -1)
     w, b, g, be = _f32c(w, "weight"), _f32c(b, "bias"), _f32c(g, "ln_weight"), _f32c(be, "ln_bias")
+    obs = obs.reshape(obs.size(0), w.size(1) if obs.numel() == 0 else -1)
     n, in_dim = obs.shape
     dim = w.size(0)
     if w.size(1) != in_dim:

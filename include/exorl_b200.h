@@ -252,6 +252,17 @@ int exb_apt_reward_pre_f32(const float* src, int64_t nq, const exb_operand* src_
                            int32_t* out_idx, void* workspace, size_t workspace_bytes,
                            exb_stream_t stream);
 
+/* RND intrinsic reward (the other consumer of the running moments):
+ *   out_error[i]  = mean_c (target[i,c] - prediction[i,c])^2      (rnd.py:52-54)
+ *   (M, S) <- RMS update with x = out_error, bs = n                (rnd.py:96, utils.py:264-276)
+ *   out_reward[i] = scale * out_error[i] / (sqrt(S_updated) + 1e-8) (rnd.py:97-98)
+ * workspace: exb_pbe_workspace_bytes, zeroed once; the caller advances n += rows itself. */
+int exb_rnd_reward_f32(const float* prediction, const float* target, int64_t n, int dim,
+                       float scale, const float* rms_m_in, const float* rms_s_in, double rms_n,
+                       float* rms_m_out, float* rms_s_out, float* out_error /* [n] */,
+                       float* out_reward /* [n] */, void* workspace, size_t workspace_bytes,
+                       exb_stream_t stream);
+
 /* ProtoRL reward: k-th smallest distance only, no RMS/clip/log (proto.py:115-118). */
 int exb_take_kth(const float* knn_dist, int64_t nq, int k, float* out /* [nq] */,
                  exb_stream_t stream);

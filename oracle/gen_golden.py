@@ -266,6 +266,42 @@ def gen_rep(ref_utils):
     np.savez_compressed(OUT / "rep_reference.npz", **out)
 
 
+def gen_rnd(ref_utils):
+    """RND (rnd.py:13-55) run unmodified (class statement compiled from the reference source, like
+    ICM above; predictor / target outputs captured with forward hooks), then the three lines of
+    RNDAgent.compute_intr_reward (:95-98) with the reference RMS, over three sequential calls."""
+    import ast
+    import copy
+    path = REF / "agents/unsupervised_learning/rnd.py"
+    tree = ast.parse(path.read_text())
+    cls = [n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "RND"]
+    ns = {"torch": torch, "nn": torch.nn, "F": torch.nn.functional, "utils": ref_utils,
+          "copy": copy}
+    exec(compile(ast.Module(body=cls, type_ignores=[]), str(path), "exec"), ns)
+    out = {}
+    for tag, (n, rep_dim, scale) in {"walker": (96, 512, 1.0), "odd": (77, 50, 0.5)}.items():
+        torch.manual_seed(300 + rep_dim)
+        rnd = ns["RND"](24, 64, rep_dim, torch.nn.Identity(), torch.nn.Identity(), (24,), "states")
+        cap = {}
+        rnd.predictor.register_forward_hook(lambda m, i, o: cap.__setitem__("pred", o.detach()))
+        rnd.target.register_forward_hook(lambda m, i, o: cap.__setitem__("target", o.detach()))
+        rms = ref_utils.RMS("cpu")
+        g = torch.Generator().manual_seed(400 + rep_dim)
+        for call in range(3):
+            obs = torch.randn(n, 24, generator=g) * (1.0 + call)
+            with torch.no_grad():
+                prediction_error = rnd(obs)
+                _, intr_reward_var = rms(prediction_error)
+                reward = scale * prediction_error / (torch.sqrt(intr_reward_var) + 1e-8)
+            out[f"{tag}_pred{call}"] = cap["pred"].numpy()
+            out[f"{tag}_target{call}"] = cap["target"].numpy()
+            out[f"{tag}_error{call}"] = prediction_error.numpy()
+            out[f"{tag}_reward{call}"] = reward.numpy()
+            out[f"{tag}_state{call}"] = np.array([float(rms.M), float(rms.S), rms.n], np.float64)
+        out[f"{tag}_scale"] = np.array(scale, np.float64)
+    np.savez_compressed(OUT / "rnd_reference.npz", **out)
+
+
 if __name__ == "__main__":
     torch.set_num_threads(8)
     OUT.mkdir(parents=True, exist_ok=True)
@@ -273,7 +309,11 @@ if __name__ == "__main__":
     if "--rep-only" in sys.argv:
         gen_rep(ref_utils)
         sys.exit(0)
+    if "--rnd-only" in sys.argv:
+        gen_rnd(ref_utils)
+        sys.exit(0)
     gen_rep(ref_utils)
+    gen_rnd(ref_utils)
     gen_kat(ref_utils)
     gen_pbe(ref_utils)
     gen_knn_dists(ref_utils)

@@ -122,3 +122,12 @@ def proto_reward(z: torch.Tensor, queue: torch.Tensor, topk: int):
     d = torch.norm(z[:, None, :] - queue[None, :, :], dim=2, p=2)
     near, _ = torch.topk(d, topk, dim=1, largest=False)
     return near[:, -1:]
+
+
+def rnd_reward(prediction: torch.Tensor, target: torch.Tensor, state: RmsState, rnd_scale=1.0):
+    """RND prediction error and normalised reward.
+    /root/reference/agents/unsupervised_learning/rnd.py:52-54 (error) and :94-99 (reward)."""
+    prediction_error = torch.square(target.detach() - prediction).mean(dim=-1, keepdim=True)  # :52
+    var = rms_step(state, prediction_error).S                                                 # :96
+    reward = rnd_scale * prediction_error / (torch.sqrt(var) + 1e-8)                          # :97
+    return reward, prediction_error

@@ -343,3 +343,40 @@ def test_prep_operand_norms_and_rigorous_error_bound(n, dim):
     s = sc.cpu()
     assert float(s[:1].view(torch.float32)) == float(er.max()) and int(s[2]) == 0
     assert float(s[1:2].view(torch.float32)) == float(hn.max())
+
+
+@pytest.mark.parametrize("tag", ["walker", "odd"])
+def test_rnd_reward_matches_reference_fixture(golden, tag):
+    """exb_rnd_reward_f32 against the reference's RND.forward error + RMS-normalised reward
+    (rnd.py:52-54,95-98; fixtures from oracle/gen_golden.py:gen_rnd), three sequential calls
+    carrying the RMS state.  fp32 bar: errors / rewards rel 1e-5, state rel 1e-6."""
+    g = golden("rnd_reference.npz")
+    rms = xb.RMS(DEV)
+    for call in range(3):
+        pred = torch.from_numpy(g[f"{tag}_pred{call}"]).to(DEV)
+        tgt = torch.from_numpy(g[f"{tag}_target{call}"]).to(DEV)
+        r, e = xb.rnd_intr_reward(pred, tgt, rms, float(g[f"{tag}_scale"]))
+        assert r.shape == (pred.size(0), 1) and e.shape == (pred.size(0), 1)
+        np.testing.assert_allclose(e.cpu().numpy(), g[f"{tag}_error{call}"], rtol=1e-5)
+        np.testing.assert_allclose(r.cpu().numpy(), g[f"{tag}_reward{call}"], rtol=1e-5)
+        m, s, n = g[f"{tag}_state{call}"]
+        assert abs(float(rms.M) - m) <= 1e-6 * abs(m) and abs(float(rms.S) - s) <= 2e-6 * abs(s)
+        assert rms.n == n
+
+
+def test_rnd_reward_large_and_unaligned():
+    from oracle import rnd_reward
+    gen = torch.Generator().manual_seed(8)
+    for n, dim in ((100000, 512), (3001, 50), (1, 7)):
+        p = torch.randn(n, dim, generator=gen)
+        t = torch.randn(n, dim, generator=gen)
+        st = RmsState()
+        want_r, want_e = rnd_reward(p, t, st, 2.0)
+        rms = xb.RMS(DEV)
+        r, e = xb.rnd_intr_reward(p.to(DEV), t.to(DEV), rms, 2.0)
+        np.testing.assert_allclose(e.cpu().numpy(), want_e.numpy(), rtol=1e-5)
+        if n > 1:     # a single value has NaN variance in the reference too
+            np.testing.assert_allclose(r.cpu().numpy(), want_r.numpy(), rtol=2e-5)
+            assert abs(float(rms.S) - float(st.S)) <= 1e-5 * abs(float(st.S))
+        else:
+            assert torch.isnan(r).all() and torch.isnan(want_r).all()

@@ -225,3 +225,29 @@ def test_relabel_from_observations_single_process():
     from oracle import knn_smallest
     od, oi = knn_smallest(rep[sub], rep, 12)
     assert_knn_matches(rep[sub], rep, 12, da[sub.to(DEV)], ia[sub.to(DEV)], oracle=(od, oi))
+
+
+def test_prepared_rep_edge_cases():
+    """Empty batch, k larger than the bank (reference: RuntimeError from topk, utils/utils.py:297),
+    a prepared source against a plain-tensor target (compute_apt_reward with source != target)."""
+    tr = _walker_trunk(41, 128)
+    empty = xb.icm_get_rep(tr, torch.empty(0, 24, device=DEV))
+    assert empty.rep.shape == (0, 128)
+    small = xb.icm_get_rep(tr, torch.randn(8, 24, device=DEV))
+    with pytest.raises(RuntimeError, match="selected index k out of range"):
+        xb.knn_topk(small, small, 12)
+    with pytest.raises(RuntimeError, match="selected index k out of range"):
+        xb.PBE(xb.RMS(DEV), 0.0, 12, True, True, DEV)(small)
+    g = torch.Generator().manual_seed(42)
+    src = xb.icm_get_rep(tr, torch.randn(300, 24, generator=g).to(DEV))
+    bank = torch.tanh(torch.randn(700, 128, generator=g)).to(DEV)
+    args = types.SimpleNamespace(knn_k=5, knn_avg=False, knn_rms=True, knn_clip=0.1)
+    got = xb.compute_apt_reward(src, bank, args, rms=xb.RMS(DEV))
+    want = pbe_reward(src.rep.cpu(), bank.cpu(), RmsState(), 5, False, True, 0.1)
+    np.testing.assert_allclose(got.cpu().numpy(), want.numpy(), rtol=1e-5, atol=1e-7)
+    # non-finite observation: the row is flagged (round_err = inf), nothing crashes, the other
+    # rows keep their exact neighbours
+    obs = torch.randn(400, 24, generator=g)
+    obs[7, 3] = float("nan")
+    p = xb.icm_get_rep(tr, obs.to(DEV))
+    assert torch.isinf(p.round_err[7]) and int(p.scalars[2]) == 1

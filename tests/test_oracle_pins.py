@@ -183,3 +183,20 @@ def test_golden_l2_normalize_bitwise(golden):
     out = l2_normalize(torch.from_numpy(g["norm_x"]))
     assert np.array_equal(out.numpy(), g["norm_out"])
     assert not np.any(out[5].numpy())   # zero row stays zero (eps clamp, no NaN)
+
+
+@pytest.mark.parametrize("tag", ["walker", "odd"])
+def test_golden_rnd_reward_bitwise(golden, tag):
+    """oracle.rnd_reward == the reference's RND.forward error (rnd.py:52-54) + the
+    compute_intr_reward lines (:95-98) with utils.RMS, three sequential calls."""
+    from oracle import rnd_reward
+    g = golden("rnd_reference.npz")
+    st = RmsState()
+    for call in range(3):
+        r, e = rnd_reward(torch.from_numpy(g[f"{tag}_pred{call}"]),
+                          torch.from_numpy(g[f"{tag}_target{call}"]), st,
+                          float(g[f"{tag}_scale"]))
+        assert np.array_equal(e.numpy(), g[f"{tag}_error{call}"])
+        assert np.array_equal(r.numpy(), g[f"{tag}_reward{call}"])
+        m, s, n = g[f"{tag}_state{call}"]
+        assert float(st.M) == m and float(st.S) == s and st.n == n

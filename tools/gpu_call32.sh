@@ -1,0 +1,2 @@
+O=gpurun_out/c32; mkdir -p $O
+python -m pytest tests -m gpu -q > $O/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -6 $O/pytest_gpu.log
