@@ -57,6 +57,18 @@ struct PrepScalars {
   int pad;
 };
 
+// Programmatic dependent launch (the per-update chain is launch-latency bound): a kernel launched
+// with cudaLaunchAttributeProgrammaticStreamSerialization may be scheduled while its predecessor
+// still runs; it must execute pdl_wait() — in EVERY thread block, before any early return, before
+// touching memory the predecessor reads or writes — which blocks until the predecessor grid has
+// completed and its writes are visible.  pdl_launch_dependents() in the predecessor lets the
+// dependent's blocks be scheduled early (they then sit in pdl_wait with their prologue done).
+// Both are no-ops for ordinary launches.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
 // (value, index) ordering used everywhere: smaller value first, then smaller index.
 __device__ __forceinline__ bool pair_less(float va, int ia, float vb, int ib) {
   return va < vb || (va == vb && ia < ib);

@@ -108,6 +108,10 @@ knn_screen_lat_kernel(const __grid_constant__ CUtensorMap tmap_q,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
+  // barriers, TMEM and descriptors are ready: let the rerank's blocks be scheduled, then wait for
+  // the producer of the operands (prep / rep producer) to finish before the first global read
+  pdl_launch_dependents();
+  pdl_wait();
 
   if (warp == 0) {
     // ===================== TMA producer =====================

@@ -466,6 +466,10 @@ knn_rerank_kernel(const RerankParams p) {
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int64_t row = (int64_t)blockIdx.x * RR_WARPS + wib;
   const bool active = row < p.nq;
+  if constexpr (LAT) {   // per-update chain (dependent launch): lists come from the screen
+    pdl_wait();
+    pdl_launch_dependents();
+  }
   float dist = 0.f;
   if (active) dist = rerank_row<LAT, NI, SH>(p, row, lane, wib, s_surv, s_val);
   if constexpr (LAT) {

@@ -92,6 +92,7 @@ knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
                 __half* __restrict__ out, float* __restrict__ half_norm,
                 float* __restrict__ round_err, PrepScalars* __restrict__ sc,
                 unsigned long long* __restrict__ zero16) {
+  pdl_launch_dependents();   // per-update chain: the screen's blocks may set up while this runs
   if (zero16 != nullptr && blockIdx.x == 0 && threadIdx.x < 3) zero16[threadIdx.x] = 0ull;
   const int lane = threadIdx.x & 31;
   const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -1090,6 +1091,16 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
 
 template <bool LAT, bool SH = false>
 static void launch_rerank(const RerankParams& rp, unsigned grid, int ni, cudaStream_t st) {
+  if constexpr (LAT) {   // per-update chain: dependent launch behind the latency screen
+    switch (ni) {
+      case 1: launch_pdl(knn_rerank_kernel<LAT, 1, SH>, dim3(grid), dim3(RR_WARPS * 32), 0, st, rp); break;
+      case 2: launch_pdl(knn_rerank_kernel<LAT, 2, SH>, dim3(grid), dim3(RR_WARPS * 32), 0, st, rp); break;
+      case 3: launch_pdl(knn_rerank_kernel<LAT, 3, SH>, dim3(grid), dim3(RR_WARPS * 32), 0, st, rp); break;
+      case 4: launch_pdl(knn_rerank_kernel<LAT, 4, SH>, dim3(grid), dim3(RR_WARPS * 32), 0, st, rp); break;
+      default: launch_pdl(knn_rerank_kernel<LAT, 0, SH>, dim3(grid), dim3(RR_WARPS * 32), 0, st, rp); break;
+    }
+    return;
+  }
   switch (ni) {
     case 1: knn_rerank_kernel<LAT, 1, SH><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
     case 2: knn_rerank_kernel<LAT, 2, SH><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
@@ -1097,6 +1108,30 @@ static void launch_rerank(const RerankParams& rp, unsigned grid, int ni, cudaStr
     case 4: knn_rerank_kernel<LAT, 4, SH><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
     default: knn_rerank_kernel<LAT, 0, SH><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
   }
+}
+
+// Launch with programmatic stream serialization (see common.cuh) when EXB_PDL=1.  Measured on
+// B200 (profiles/r01g_secondary_pdl.jsonl vs _nopdl): C1 39.9 us either way (stream), 36.9 vs
+// 34.8 us as a CUDA graph, C2 33.8 vs 35.8 us — inside the 2 us resolution of the event timer, so
+// the ordinary launch stays the default and the dependent-launch chain an A/B knob.
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                              cudaStream_t st, Args... args) {
+  static const int pdl_on = [] {
+    const char* e = getenv("EXB_PDL");
+    return e ? atoi(e) : 0;
+  }();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_on ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 
 struct ScreenWs {
@@ -1307,9 +1342,9 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
     dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
     const bool prof = g_prof.on && g_prof.n < 64;
     if (prof) EXB_CUDA(cudaEventRecord(g_prof.e0[g_prof.n], st));
-    if (k <= 4) knn_screen_lat_kernel<4><<<grid, LAT_THREADS, pl.smem, st>>>(tq, tb, lp);
-    else if (k <= 12) knn_screen_lat_kernel<12><<<grid, LAT_THREADS, pl.smem, st>>>(tq, tb, lp);
-    else knn_screen_lat_kernel<16><<<grid, LAT_THREADS, pl.smem, st>>>(tq, tb, lp);
+    if (k <= 4) EXB_CUDA(launch_pdl(knn_screen_lat_kernel<4>, grid, dim3(LAT_THREADS), pl.smem, st, tq, tb, lp));
+    else if (k <= 12) EXB_CUDA(launch_pdl(knn_screen_lat_kernel<12>, grid, dim3(LAT_THREADS), pl.smem, st, tq, tb, lp));
+    else EXB_CUDA(launch_pdl(knn_screen_lat_kernel<16>, grid, dim3(LAT_THREADS), pl.smem, st, tq, tb, lp));
     EXB_LAUNCH_CHECK();
     if (prof) EXB_CUDA(cudaEventRecord(g_prof.e1[g_prof.n++], st));
     if (pbe) {

@@ -65,6 +65,7 @@ __global__ void __launch_bounds__(PBE_THREADS)
 pbe_finish_kernel(const float* __restrict__ dist, int64_t nq, int k, int avg, int use_rms,
                   int use_clip, float clip, const float* __restrict__ m_ptr,
                   float* __restrict__ out) {
+  pdl_wait();   // dependent launch behind the fused rerank + moments kernel (no-op otherwise)
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nq) return;
   const float m = use_rms ? *m_ptr : 1.0f;
@@ -109,8 +110,21 @@ __global__ void take_kth_kernel(const float* __restrict__ dist, int64_t nq, int 
 // per-row finish after the fused rerank + moments kernel of the per-update chain (knn_screen.cu)
 int launch_pbe_finish(const float* dist, int64_t nq, int k, int avg, int use_rms, int use_clip,
                       float clip, const float* m_ptr, float* out, cudaStream_t st) {
-  pbe_finish_kernel<<<(unsigned)((nq + 127) / 128), 128, 0, st>>>(dist, nq, k, avg, use_rms,
-                                                                  use_clip, clip, m_ptr, out);
+  static const int pdl_on = [] {
+    const char* e = getenv("EXB_PDL");
+    return e ? atoi(e) : 0;
+  }();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)((nq + 127) / 128));
+  cfg.blockDim = dim3(128);
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_on ? 1 : 0;
+  EXB_CUDA(cudaLaunchKernelEx(&cfg, pbe_finish_kernel, dist, nq, k, avg, use_rms, use_clip, clip,
+                              m_ptr, out));
   EXB_LAUNCH_CHECK();
   return EXB_OK;
 }
