@@ -178,6 +178,10 @@ struct ScreenParams {
   int* scan_idx;
   int* head;              // [splits] shared stream head (virtual tile position), zeroed per call;
                           // null = every CTA scans its tile range from the first tile
+  // Hybrid tail (1-D grid): the first full_units CTA groups scan the whole bank for one query
+  // tile each; the query tiles of the partly filled last wave are cut into tail_splits bank
+  // ranges of tail_tps tiles so that the idle SMs of that wave share their scans.  0 = off.
+  int tail_splits, full_units, tail_tps;
 };
 
 // Per-row candidate state of one epilogue thread.  The k best scores seen so far are kept sorted
@@ -546,9 +550,23 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
   uint32_t* s_start = s_tmem + 1;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m_tile = blockIdx.x, split = blockIdx.y;
-  const int t_begin = split * p.tiles_per_split;
-  const int t_end = min(p.n_tiles, t_begin + p.tiles_per_split);
+  int m_tile = blockIdx.x, split = blockIdx.y;
+  int t_begin = split * p.tiles_per_split;
+  int t_end = min(p.n_tiles, t_begin + p.tiles_per_split);
+  int head_slot = split;
+  if (p.tail_splits > 0) {   // hybrid tail: 1-D grid of CTA groups (see ScreenParams)
+    const int unit = (int)blockIdx.x / CG, r = (int)blockIdx.x % CG;
+    if (unit < p.full_units) {
+      m_tile = unit * CG + r; split = 0; t_begin = 0; t_end = p.n_tiles; head_slot = 0;
+    } else {
+      const int t = unit - p.full_units;
+      m_tile = (p.full_units + t / p.tail_splits) * CG + r;
+      split = t % p.tail_splits;
+      t_begin = split * p.tail_tps;
+      t_end = min(p.n_tiles, t_begin + p.tail_tps);
+      head_slot = 1 + split;
+    }
+  }
   const int n_local = max(t_end - t_begin, 0);
 
   if (threadIdx.x == 0) {
@@ -568,7 +586,7 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
     // (cyclic tile order), so that all co-resident CTAs stream the same window of the bank
     // through L2 instead of each pulling its own copy from HBM.
     *s_start = (p.head != nullptr && leader)
-                   ? (uint32_t)*reinterpret_cast<volatile int*>(p.head + split) : 0u;
+                   ? (uint32_t)*reinterpret_cast<volatile int*>(p.head + head_slot) : 0u;
   }
   if (warp == 1) {
     if constexpr (CG == 2) tmem_alloc_512_pair(smem_u32(s_tmem));
@@ -613,7 +631,7 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
       for (int j = 0; j < n_total; ++j) {
         const int t = tile_seq(j);
         if (p.head != nullptr && leader && (j & 7) == 7 && j >= n_seed)
-          atomicMax(p.head + split, (int)(start_v + (uint32_t)(j - n_seed)));
+          atomicMax(p.head + head_slot, (int)(start_v + (uint32_t)(j - n_seed)));
         const int brow = t * SCR_N + (int)cta_rank * B_ROWS;
         for (int kc = 0; kc < nkc; ++kc) {
           // pull this CTA's share of a later tile into L2 so the ring only sees L2 latency
@@ -992,6 +1010,7 @@ struct ScreenPlan {
   int trackers;  // candidate lists per (row, split): 2 for FILT 3, else 1
   size_t smem;
   int fb_cap, fb_splits;
+  int tail_splits, full_units, tail_tps;   // hybrid tail (ScreenParams); tail_splits 0 = off
 };
 
 static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
@@ -1077,6 +1096,35 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
     pl->splits = (pl->n_tiles + pl->tiles_per_split - 1) / pl->tiles_per_split;
   }
   pl->trackers = pl->filt == 3 ? 2 : 1;
+  // Hybrid tail.  More query tiles than SMs run in waves of sm_count CTAs; when the last wave is
+  // partly empty (125k queries: 489 CTA pairs on 74 pair slots = 6 full waves + 45 pairs; 250k
+  // queries: 13 waves + 15 pairs) its query tiles are cut into 2-4 bank ranges so that the idle
+  // SMs take part.  Only those rows pay for restarted k-th-best chains and extra lists.
+  pl->tail_splits = 0; pl->full_units = 0; pl->tail_tps = 0;
+  static const int tail_env = [] {
+    const char* e = getenv("EXB_SCREEN_TAIL");   // A/B: 0 = off
+    return e ? atoi(e) : 1;
+  }();
+  if (tail_env && pl->filt == 2 && pl->splits == 1) {
+    const int slots = sm_count() / pl->cg, units = pl->m_tiles / pl->cg;
+    const int full = units / slots * slots, rem = units - full;
+    // ts ranges per tail tile -> the tail takes ceil(rem * ts / slots) rounds of 1/ts wave
+    int ts = 0;
+    double best = 0.8;   // worth it only if the tail shrinks to < 0.8 of a wave
+    for (int c = 2; c <= 4 && rem > 0; ++c) {
+      const double cost = (double)((rem * c + slots - 1) / slots) / c;
+      if (cost < best - 1e-9) {
+        best = cost;
+        ts = c;
+      }
+    }
+    if (full > 0 && ts >= 2 && pl->n_tiles / ts >= 256) {
+      pl->tail_splits = ts;
+      pl->full_units = full;
+      pl->tail_tps = (pl->n_tiles + ts - 1) / ts;
+      pl->splits = ts;          // candidate lists per row (rows of full units use list 0 only)
+    }
+  }
   const size_t fixed = (size_t)pl->nkc * SCR_A_CHUNK_BYTES +
                        (pl->filt == 3 ? 8 * (SCR_N / 2) * 4 : 2 * SCR_CAP * SCR_M * 4 + 2 * SCR_N * 4) +
                        (2 * SCR_MAX_STAGES + 5) * 8 + 16 + 1024;
@@ -1417,6 +1465,14 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
     sp.cand_cnt = lo->cnt;
   }
   dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
+  sp.tail_splits = pl.tail_splits; sp.full_units = pl.full_units; sp.tail_tps = pl.tail_tps;
+  if (pl.tail_splits > 0) {
+    const int units = pl.m_tiles / pl.cg;
+    grid = dim3((unsigned)((pl.full_units + (units - pl.full_units) * pl.tail_splits) * pl.cg), 1);
+    sp.tiles_per_split = pl.n_tiles;
+    // rows scanned by a full unit never touch lists 1..: their counts must read as empty
+    EXB_CUDA(cudaMemsetAsync(sp.cand_cnt, 0, (size_t)nq * pl.splits * sizeof(int), st));
+  }
   sp.lists = pl.splits * pl.trackers;
   // sample tiles that seed the k-th-best chain before the real scan (FILT 3): ~1.5 % extra MMA
   // work buys roughly half the list insertions

@@ -380,3 +380,26 @@ def test_rnd_reward_large_and_unaligned():
             assert abs(float(rms.S) - float(st.S)) <= 1e-5 * abs(float(st.S))
         else:
             assert torch.isnan(r).all() and torch.isnan(want_r).all()
+
+
+@pytest.mark.parametrize("b,d,k", [(300, 600, 12), (260, 1024, 5), (400, 64, 20), (300, 32, 32),
+                                   (130, 3 * 8 * 8, 12)])
+def test_auto_mode_outside_the_screen_limits(b, d, k):
+    """rep_dim > 512 or k > 16 are outside the tcgen05 screen: mode='auto' must route them to the
+    exact fp32 kernel (same results), mode='screened' must refuse loudly; a 3-D rep is flattened
+    like the reference's .view(b, 1, -1) (utils/utils.py:293-294)."""
+    x = reps(77, b, d)
+    if d == 3 * 8 * 8:
+        x = x.reshape(b, 3, 8, 8)
+    xd = x.to(DEV)
+    dist, idx = xb.knn_topk(xd, xd, k)
+    assert_knn_matches(x.reshape(b, -1), x.reshape(b, -1), k, dist, idx)
+    pbe = xb.PBE(xb.RMS(DEV), 0.0, k, True, True, DEV)
+    got = pbe(xd)
+    want = pbe_reward(x, x, RmsState(), k, True, True, 0.0)
+    np.testing.assert_allclose(got.cpu().numpy(), want.numpy(), rtol=1e-5, atol=1e-7)
+    if d > 512 or k > 16:
+        with pytest.raises(ValueError):
+            xb.knn_topk(xd, xd, k, mode="screened")
+    with pytest.raises(ValueError):
+        xb.knn_topk(xd, xd, 33)
