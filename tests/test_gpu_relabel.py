@@ -131,3 +131,47 @@ def test_query_block_against_long_bank_wave_splits():
     sub = torch.arange(0, nq, 250)
     qc, bc = q.cpu(), bank.cpu()
     assert_knn_matches(qc[sub], bc, k, d_s[sub.to(DEV)], i_s[sub.to(DEV)])
+
+
+@pytest.mark.parametrize("nq", [20224, 26624, 19000 + 77])
+def test_hybrid_tail_grids_equal_exact_kernel(nq):
+    """Query blocks whose last wave of CTA pairs is partly empty (5, 30 and ~1 pairs on 74 slots):
+    the screen cuts those tiles' scans into 4 / 2 / 4 bank ranges (hybrid tail).  Distances must
+    equal the exact fp32 kernel bit for bit up to fp32 ulps, index sets up to near-ties, and rows of
+    full units and of tail units must both be right (first, middle and last rows checked against
+    the oracle)."""
+    nb, dim, k = 300000, 32, 12
+    bank = reps(17, nb, dim).to(DEV)
+    q = reps(18, nq, dim).to(DEV)
+    d_s, i_s = xb.knn_topk(q, bank, k, mode="screened")
+    assert xb.knn.screened_status(DEV)[1] == 0
+    d_e, i_e = xb.knn_topk(q, bank, k, mode="exact")
+    np.testing.assert_allclose(d_s.cpu().numpy(), d_e.cpu().numpy(), rtol=1e-6)
+    diff = (i_s.sort(dim=1).values != i_e.sort(dim=1).values).any(dim=1).sum().item()
+    assert diff <= max(1, nq // 1000)
+    sub = torch.cat([torch.arange(0, 64), torch.arange(nq // 2, nq // 2 + 64),
+                     torch.arange(nq - 64, nq)])
+    assert_knn_matches(q.cpu()[sub], bank.cpu(), k, d_s[sub.to(DEV)], i_s[sub.to(DEV)])
+
+
+def test_randomized_shapes_screened_equals_exact():
+    """40 random (nq, nb, dim, k) shapes across the kernel variants (latency chain, FILT 1/2/3,
+    single CTA / CTA pair, ragged last tiles): screened == exact kernel."""
+    rng = np.random.default_rng(2026)
+    for it in range(40):
+        nq = int(rng.integers(1, 5000))
+        nb = int(rng.integers(1, 60000)) if it % 3 else int(rng.integers(1, 3000))
+        dim = int(rng.choice([1, 3, 10, 24, 50, 64, 65, 128, 200, 256, 500, 512]))
+        k = int(rng.integers(1, 17))
+        if k > nb:
+            k = nb
+        g = torch.Generator().manual_seed(it)
+        q = torch.tanh(torch.randn(nq, dim, generator=g)).to(DEV)
+        b = torch.tanh(torch.randn(nb, dim, generator=g)).to(DEV)
+        d_s, i_s = xb.knn_topk(q, b, k, mode="screened")
+        assert xb.knn.screened_status(DEV)[1] == 0, (nq, nb, dim, k)
+        d_e, i_e = xb.knn_topk(q, b, k, mode="exact")
+        np.testing.assert_allclose(d_s.cpu().numpy(), d_e.cpu().numpy(), rtol=2e-6, atol=1e-7,
+                                   err_msg=str((nq, nb, dim, k)))
+        diff = (i_s.sort(dim=1).values != i_e.sort(dim=1).values).any(dim=1).sum().item()
+        assert diff <= max(1, nq // 500), (nq, nb, dim, k, diff)
