@@ -175,3 +175,50 @@ def test_randomized_shapes_screened_equals_exact():
                                    err_msg=str((nq, nb, dim, k)))
         diff = (i_s.sort(dim=1).values != i_e.sort(dim=1).values).any(dim=1).sum().item()
         assert diff <= max(1, nq // 500), (nq, nb, dim, k, diff)
+
+
+def test_c5_full_size_properties():
+    """BASELINE config 5 at full size (10^6 x 10^6, rep 512, k = 12, avg + rms) on one GPU, checked
+    through size-independent properties + a 48-query slice against the oracle (the full oracle
+    would take CPU-days): self-match first with distance exactly 0, ascending distances, distinct
+    in-range indices, returned distances equal to a direct recompute of the returned pairs,
+    rewards equal to the reference formula applied to the returned distances (fp64 on the GPU),
+    RMS state = moments of all N*k distances, no undecided rows."""
+    n, dim, k = 1_000_000, 512, 12
+    g = torch.Generator(device=DEV).manual_seed(5)
+    rep = torch.tanh(torch.randn(n, dim, generator=g, device=DEV))
+    args = types.SimpleNamespace(knn_k=k, knn_avg=True, knn_rms=True, knn_clip=0.0)
+    rms = xb.RMS(DEV)
+    reward, dist, idx = xb.relabel_apt_reward(rep, args, rms=rms, mode="screened", return_knn=True)
+    und, invalid, _, _ = xb.knn.screened_status(DEV)
+    assert invalid == 0 and und == 0
+    assert reward.shape == (n, 1) and dist.shape == (n, k) and idx.shape == (n, k)
+    assert torch.equal(idx[:, 0], torch.arange(n, dtype=torch.int32, device=DEV))
+    assert not dist[:, 0].any()
+    assert bool((dist[:, 1:] >= dist[:, :-1]).all())
+    assert bool((idx >= 0).all()) and bool((idx < n).all())
+    srt = idx.sort(dim=1).values
+    assert bool((srt[:, 1:] != srt[:, :-1]).all())
+    # returned distances are the direct-difference distances of the returned pairs
+    rows = torch.randint(0, n, (4096,), generator=g, device=DEV)
+    nb_rows = idx[rows].long()
+    direct = torch.norm(rep[rows][:, None, :] - rep[nb_rows.reshape(-1)].reshape(4096, k, dim),
+                        dim=2, p=2)
+    np.testing.assert_allclose(dist[rows].cpu().numpy(), direct.cpu().numpy(), rtol=2e-6, atol=1e-6)
+    # epilogue + RMS (utils/utils.py:264-276, 309-318) recomputed in fp64 from the returned dists
+    d64 = dist.double().reshape(-1)
+    bs, n0 = float(d64.numel()), 1e-4
+    mean, var = d64.mean(), d64.var(unbiased=True)
+    m_new = 0.0 + (mean - 0.0) * bs / (n0 + bs)
+    s_new = (1.0 * n0 + var * bs + mean * mean * n0 * bs / (n0 + bs)) / (n0 + bs)
+    assert abs(float(rms.M) - float(m_new)) <= 1e-6 * float(m_new)
+    assert abs(float(rms.S) - float(s_new)) <= 1e-5 * float(s_new)
+    assert rms.n == n0 + bs
+    want = torch.log((dist.double() / float(rms.M)).clamp_min(0).mean(dim=1, keepdim=True) + 1.0)
+    np.testing.assert_allclose(reward.cpu().numpy(), want.float().cpu().numpy(), rtol=1e-5)
+    # oracle slice: the reference formula (tiled) for 48 queries against the whole bank
+    sub = torch.arange(0, n, n // 48)[:48]
+    rep_cpu = rep.cpu()
+    od, oi = knn_smallest(rep_cpu[sub], rep_cpu, k)
+    assert_knn_matches(rep_cpu[sub], rep_cpu, k, dist[sub.to(DEV)], idx[sub.to(DEV)],
+                       oracle=(od, oi))
