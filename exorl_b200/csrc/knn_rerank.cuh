@@ -433,8 +433,15 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
     } else {
       if (lane == 0) {
         const int pos = atomicAdd(&p.status->n_fallback, 1);
-        if (pos < p.fallback_cap) p.fallback_rows[pos] = (int)row;
-        else p.status->invalid = 1;
+        if (pos < p.fallback_cap) {
+          p.fallback_rows[pos] = (int)row;
+        } else {
+          // more undecided rows than the device-side fallback holds (heavily duplicated data, or
+          // values outside the fp16 range): flag the row so that the host can recompute it with
+          // the exact kernel (exorl_b200/knn.py:_repair_overflow_rows) — never a silent result
+          p.status->invalid = 1;
+          p.out_idx[(int64_t)row * p.k] = -1;
+        }
       }
       return 0.f;
     }

@@ -83,6 +83,7 @@ def knn_topk(source, target, k, idx_base=0, mode="auto"):
                 _lib.ptr(src), nq, pre_s.operand, _lib.ptr(tgt), nb, pre_t.operand, dim, k,
                 int(idx_base), _lib.ptr(dist), _lib.ptr(idx), _lib.ptr(ws), ws.numel(),
                 _lib.stream_ptr(dev)))
+            _repair_overflow_rows(src, tgt, k, idx_base, dist, idx, "knn_screened")
             return dist, idx
         use_screen = mode == "screened" or (mode == "auto" and _screen_ok(nq, nb, dim, k))
         if use_screen:
@@ -93,6 +94,7 @@ def knn_topk(source, target, k, idx_base=0, mode="auto"):
             _lib.check(lib.exb_knn_screened_f32(
                 _lib.ptr(src), nq, _lib.ptr(tgt), nb, dim, k, int(idx_base), int(same),
                 _lib.ptr(dist), _lib.ptr(idx), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+            _repair_overflow_rows(src, tgt, k, idx_base, dist, idx, "knn_screened")
         else:
             need = lib.exb_knn_exact_workspace_bytes(nq, nb, dim, k)
             ws, _ = _lib.Workspace.get(dev, "knn_exact", need)
@@ -100,6 +102,33 @@ def knn_topk(source, target, k, idx_base=0, mode="auto"):
                 _lib.ptr(src), nq, _lib.ptr(tgt), nb, dim, k, int(idx_base), _lib.ptr(dist),
                 _lib.ptr(idx), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
     return dist, idx
+
+
+def _streaming(nq, nb, dim, k):
+    """True when the screened call runs the dataset-scale (streaming) kernels; the per-update
+    chain recomputes undecided rows inline and needs no host check."""
+    if dim > _lib.SCREEN_MAX_DIM or k > _lib.SCREEN_MAX_K:
+        return False
+    return int(_lib.load().exb_knn_screen_lists_count(nq, nb, dim, k)) > 0
+
+
+def _repair_overflow_rows(src, tgt, k, idx_base, dist, idx, ws_key):
+    """Dataset-scale screened calls only: rows the screen could not certify are recomputed on
+    the device by the exact kernel, up to 4096 of them; if there were more (heavily duplicated
+    rows, values outside the fp16 range) the rerank marks the rest with idx[:, 0] = -1 and raises
+    the status flag.  Read the flag (one stream sync per dataset-scale call) and recompute those
+    rows with the exact fp32 kernel, so the result is always the exact path's."""
+    nq, nb, dim = src.size(0), tgt.size(0), src.size(1)
+    if not _streaming(nq, nb, dim, k):
+        return
+    if screened_status(src.device, key=ws_key)[1] == 0:
+        return
+    rows = (idx[:, 0] < 0).nonzero().flatten()
+    for c in range(0, rows.numel(), 8192):
+        sel = rows[c:c + 8192]
+        d, i = knn_topk(src[sel], tgt, k, idx_base=idx_base, mode="exact")
+        dist[sel] = d
+        idx[sel] = i
 
 
 SCREEN_CAP = 24   # EXB_SCREEN_CAP: candidate slots per list
@@ -177,6 +206,13 @@ def knn_rerank_lists(source, bank, k, val, idx, cnt, shard_lo, ha, ea, scalars):
             _lib.ptr(val.contiguous()), _lib.ptr(idx.contiguous()), _lib.ptr(cnt.contiguous()),
             lo, _lib.ptr(ha.contiguous()), _lib.ptr(ea.contiguous()), _lib.ptr(scalars),
             _lib.ptr(dist), _lib.ptr(out_i), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+        if screened_status(dev, key="knn_rerank_lists")[1] != 0:   # see _repair_overflow_rows
+            rows = (out_i[:, 0] < 0).nonzero().flatten()
+            for c in range(0, rows.numel(), 8192):
+                sel = rows[c:c + 8192]
+                d, i = knn_topk(src[sel], tgt, k, mode="exact")
+                dist[sel] = d
+                out_i[sel] = i
     return dist, out_i
 
 
@@ -313,6 +349,14 @@ def compute_apt_reward(source, target, args, rms=None, mode="auto", return_knn=F
             raise ValueError("knn_rms=True needs an RMS state object")
         if rms.M.numel() != 1 or not rms.M.is_cuda:
             raise ValueError("the RMS state used by PBE must have shape (1,) on the GPU")
+    if nq > 0 and mode != "exact" and _streaming(nq, nb, dim, k):
+        # dataset-scale input: kNN (with the host-side overflow check) then the epilogue; the
+        # one-call fused chain below is for per-update sizes
+        a = pre_s if pre_s is not None else src
+        b = a if same else (pre_t if pre_s is not None else tgt)
+        d_, i_ = knn_topk(a, b, k, mode="screened")
+        out = _reward_from_knn(d_, k, knn_avg, knn_rms, knn_clip, rms)
+        return (out, d_, i_) if return_knn else out
     with torch.cuda.device(dev):
         out = torch.empty(nq, 1, dtype=torch.float32, device=dev)
         dist = torch.empty(nq, k, dtype=torch.float32, device=dev)

@@ -222,3 +222,32 @@ def test_c5_full_size_properties():
     od, oi = knn_smallest(rep_cpu[sub], rep_cpu, k)
     assert_knn_matches(rep_cpu[sub], rep_cpu, k, dist[sub.to(DEV)], idx[sub.to(DEV)],
                        oracle=(od, oi))
+
+
+@pytest.mark.parametrize("kind", ["duplicates", "out_of_range"])
+def test_more_undecided_rows_than_the_device_fallback_holds(kind):
+    """Dataset-scale input on which the screen cannot certify > 4096 rows: 6000 identical rows
+    (each has 6000 neighbours at distance 0, far more than a candidate list holds) or values
+    outside the fp16 range (every row undecided).  The device-side fallback takes 4096 rows; the
+    rest is flagged and recomputed by the exact kernel from the host — results must equal the
+    exact path, never silently wrong."""
+    n, dim, k = 20000, 64, 12
+    x = reps(23, n, dim)
+    if kind == "duplicates":
+        x[5000:11000] = x[4999]
+    else:
+        x = x * 1.0e5
+    xd = x.to(DEV)
+    d_s, i_s = xb.knn_topk(xd, xd, k, mode="screened")
+    und, invalid, _, _ = xb.knn.screened_status(DEV)
+    assert invalid == 1 and und > 4096
+    assert bool((i_s >= 0).all()) and bool((i_s < n).all())
+    d_e, i_e = xb.knn_topk(xd, xd, k, mode="exact")
+    np.testing.assert_allclose(d_s.cpu().numpy(), d_e.cpu().numpy(), rtol=1e-6, atol=1e-6)
+    if kind == "duplicates":
+        assert not d_s[5000:11000].any()          # k duplicates at distance exactly 0
+    # the reward path takes the same route (compute_apt_reward at dataset scale)
+    args = types.SimpleNamespace(knn_k=k, knn_avg=True, knn_rms=True, knn_clip=0.0)
+    r_s = xb.compute_apt_reward(xd, xd, args, rms=xb.RMS(DEV))
+    r_e = xb.compute_apt_reward(xd, xd, args, rms=xb.RMS(DEV), mode="exact")
+    np.testing.assert_allclose(r_s.cpu().numpy(), r_e.cpu().numpy(), rtol=1e-5, atol=1e-7)
