@@ -36,13 +36,24 @@ def main():
             e1.record()
             torch.cuda.synchronize()
         und, invalid, pairs, _ = xb.knn.screened_status(dev)
+        why = None
+        if os.environ.get("EXB_SCREEN_TRACE"):
+            import ctypes
+            from exorl_b200 import _lib
+            ws, _ = _lib.Workspace.get(dev, "knn_screened", 1024)
+            out = (ctypes.c_int64 * 16)()
+            _lib.check(_lib.load().exb_debug_trace_sync(_lib.ptr(ws), out, _lib.stream_ptr(dev)))
+            t = list(out)
+            why = {"undecided": t[0], "list_overflow": t[1], "fewer_than_k": t[2],
+                   "fp16_range": t[3], "survivors_gt_64": t[4],
+                   "last": {"row": t[12], "why": t[13], "total": t[14], "n_surv": t[15]}}
         d_e, i_e = xb.knn_topk(p.rep, p.rep, 12, mode="exact")
         same = bool(torch.allclose(d, d_e, rtol=1e-6, atol=1e-6))
         print(json.dumps({"rows": obs.size(0), "walk_step": step, "ms": e0.elapsed_time(e1),
                           "undecided_rows": und, "overflowed_device_fallback": invalid,
                           "rerank_pairs_per_row": pairs / obs.size(0),
                           "median_knn_dist": float(d[:, 1:].median()),
-                          "equals_exact_kernel": same}), flush=True)
+                          "equals_exact_kernel": same, "why": why}), flush=True)
 
 
 if __name__ == "__main__":

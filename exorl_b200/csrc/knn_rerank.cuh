@@ -417,6 +417,14 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
     p.trace[13] = why;
     p.trace[14] = total;
     p.trace[15] = n_surv;
+    // histogram of the reasons (EXB_SCREEN_TRACE=1): [0] undecided rows, [1] a screen list
+    // overflowed, [2] fewer than k candidates, [3] fp16 range, [4] more than RR_SURV survivors
+    unsigned long long* h = reinterpret_cast<unsigned long long*>(p.trace);
+    atomicAdd(h + 0, 1ull);
+    if (why & 1) atomicAdd(h + 1, 1ull);
+    if (why & 2) atomicAdd(h + 2, 1ull);
+    if (why & 4) atomicAdd(h + 3, 1ull);
+    if (why & 8) atomicAdd(h + 4, 1ull);
   }
   if (tr && lane == 0) p.trace[10] = clock_now();
 

@@ -182,6 +182,7 @@ struct ScreenParams {
   // tile each; the query tiles of the partly filled last wave are cut into tail_splits bank
   // ranges of tail_tps tiles so that the idle SMs of that wave share their scans.  0 = off.
   int tail_splits, full_units, tail_tps;
+  int chain_reset;        // 1 = drop the seed chain after the seed phase (default); 0 = A/B only
 };
 
 // Per-row candidate state of one epilogue thread.  The k best scores seen so far are kept sorted
@@ -236,6 +237,20 @@ __device__ __forceinline__ void chain_push(ListState& s, float x) {
 #pragma unroll
   for (int i = SCR_MAX_K - 1; i > 0; --i) s.tv[i] = fmaxf(s.tv[i], fminf(s.tv[i - 1], x));
   s.tv[0] = fmaxf(s.tv[0], x);
+}
+
+// After the seed phase the chain holds GROUP MAXIMA (one score per 4 columns) of the sample
+// tiles.  That is a valid lower bound of the k-th best, but when a row's true neighbours sit in
+// consecutive columns of those tiles (trajectory data: consecutive states are near-duplicates) it
+// is far too loose, and because the sample tiles' scores could not be pushed a second time it
+// stayed loose: whole query tiles overflowed their lists (18 % of the rows of a 200-episode
+// random-walk set, 93 % with 10x smaller steps; profiles/r01i_trajectory_*.jsonl).  So the seed
+// chain only fixes the initial tkeep; the main phase starts an EMPTY chain and pushes every
+// inserted score exactly once (each column is visited once), which makes tk the exact k-th best.
+__device__ __forceinline__ void chain_reset(ListState& s, int k) {
+#pragma unroll
+  for (int i = 0; i < SCR_MAX_K; ++i) s.tv[i] = (i < SCR_MAX_K - k) ? FLT_MAX : -FLT_MAX;
+  s.tk = -FLT_MAX;
 }
 
 __device__ __forceinline__ void refresh_threshold(ListState& s) {
@@ -770,10 +785,13 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
           if (ch + 2 < NCH) tmem_ld32(t_row + (ch + 2) * 32, ra);
           seed_chunk(st, rb, hn + (ch + 1) * 32);
         }
-        if (jj == n_seed - 1) refresh_threshold(st);
+        if (jj == n_seed - 1) {
+          refresh_threshold(st);
+          if (p.chain_reset) chain_reset(st, p.k);
+        }
       } else {
-        // main phase; the sample tiles' scores are already in the chain (push them once only)
-        const bool push = jj >= 2 * n_seed;
+        // main phase: every inserted score goes through the (fresh) chain exactly once
+        const bool push = p.chain_reset ? true : jj >= 2 * n_seed;
 #pragma unroll 1
         for (int ch = 0; ch < NCH; ch += 2) {
           tmem_ld_wait();
@@ -860,8 +878,9 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
       const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)as * SCR_N;
       if (p.debug != 1) {
         uint32_t ra[32], rb[32];
-        // `first`: scores of these tiles are already in the chain (seeded), do not push them again
-        const bool first = n_seed > 0 ? (jj < 2 * n_seed) : (j == 0);
+        // the seed chain is dropped after the seed phase (chain_reset), so every score of the main
+        // phase is pushed exactly once
+        const bool first = p.chain_reset ? false : (n_seed > 0 ? (jj < 2 * n_seed) : (j == 0));
         const bool seed_now = n_seed > 0 ? (jj < n_seed) : (j == 0);
         if (seed_now && p.debug == 0) {
           // seed pass: group maxima -> chain only.  Without sample tiles (n_seed == 0) this is a
@@ -876,7 +895,10 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
             if (ch + 2 < SCR_N / 32) tmem_ld32(t_row + (ch + 2) * 32, ra);
             seed_chunk(st, rb, hn + (ch + 1) * 32);
           }
-          if (n_seed == 0 || jj == n_seed - 1) refresh_threshold(st);
+          if (n_seed == 0 || jj == n_seed - 1) {
+            refresh_threshold(st);
+            if (p.chain_reset) chain_reset(st, p.k);
+          }
         }
         if (jj >= n_seed) {
         // Software-pipelined drain: the TMEM load of chunk c+1 is in flight while chunk c is
@@ -1466,6 +1488,11 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
   }
   dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
   sp.tail_splits = pl.tail_splits; sp.full_units = pl.full_units; sp.tail_tps = pl.tail_tps;
+  static const int chain_reset_env = [] {
+    const char* e = getenv("EXB_SCREEN_CHAINRESET");   // A/B: 0 = keep the seed chain (old scheme)
+    return e ? atoi(e) : 1;
+  }();
+  sp.chain_reset = chain_reset_env;
   if (pl.tail_splits > 0) {
     const int units = pl.m_tiles / pl.cg;
     grid = dim3((unsigned)((pl.full_units + (units - pl.full_units) * pl.tail_splits) * pl.cg), 1);
