@@ -112,23 +112,71 @@ def _streaming(nq, nb, dim, k):
     return int(_lib.load().exb_knn_screen_lists_count(nq, nb, dim, k)) > 0
 
 
+_repair_depth = 0        # nesting of the strided re-screen below (host-side, single thread)
+STRIDED_BANKS = 8
+
+
+def _topk_merge(dist_lists, idx_lists, k):
+    """(G, n, k) per-part lists -> (n, k) global k smallest (exb_topk_merge)."""
+    lib = _lib.load()
+    g, n, _ = dist_lists.shape
+    dev = dist_lists.device
+    out_d = torch.empty(n, k, dtype=torch.float32, device=dev)
+    out_i = torch.empty(n, k, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(lib.exb_topk_merge(_lib.ptr(dist_lists.contiguous()),
+                                      _lib.ptr(idx_lists.contiguous()), g, n, k, _lib.ptr(out_d),
+                                      _lib.ptr(out_i), _lib.stream_ptr(dev)))
+    return out_d, out_i
+
+
+def _recompute_rows(src, tgt, k, idx_base, dist, idx, rows):
+    """Exact result for the flagged `rows`.  Few rows: the exact fp32 kernel.  Many rows (dense
+    data: more bank rows inside a row's screening margin than its candidate lists hold — e.g.
+    trajectories whose consecutive states are near-duplicates): re-screen them against
+    STRIDED_BANKS interleaved sub-banks bank[r::P].  Each sub-bank is P times less dense, so the
+    lists fit again; the union of the per-sub-bank k nearest contains the global k nearest, and
+    exb_topk_merge selects them — still exact, at about the cost of one more screened pass instead
+    of a CUDA-core scan of the whole bank per row."""
+    global _repair_depth
+    nb = tgt.size(0)
+    p = STRIDED_BANKS
+    if rows.numel() <= 4096 or _repair_depth >= 2 or nb < p * max(256, k):
+        for c in range(0, rows.numel(), 8192):
+            sel = rows[c:c + 8192]
+            d, i = knn_topk(src[sel], tgt, k, idx_base=idx_base, mode="exact")
+            dist[sel] = d
+            idx[sel] = i
+        return
+    q = src[rows].contiguous()
+    dl, il = [], []
+    _repair_depth += 1
+    try:
+        for r in range(p):
+            d_r, i_r = knn_topk(q, tgt[r::p].contiguous(), k, mode="screened")
+            dl.append(d_r)
+            il.append(i_r * p + (r + int(idx_base)))
+    finally:
+        _repair_depth -= 1
+    d, i = _topk_merge(torch.stack(dl), torch.stack(il), k)
+    dist[rows] = d
+    idx[rows] = i
+
+
 def _repair_overflow_rows(src, tgt, k, idx_base, dist, idx, ws_key):
     """Dataset-scale screened calls only: rows the screen could not certify are recomputed on
     the device by the exact kernel, up to 4096 of them; if there were more (heavily duplicated
-    rows, values outside the fp16 range) the rerank marks the rest with idx[:, 0] = -1 and raises
-    the status flag.  Read the flag (one stream sync per dataset-scale call) and recompute those
-    rows with the exact fp32 kernel, so the result is always the exact path's."""
+    or very dense rows, values outside the fp16 range) the rerank marks the rest with
+    idx[:, 0] = -1 and raises the status flag.  Read the flag (one stream sync per dataset-scale
+    call) and recompute those rows (_recompute_rows), so the result is always the exact path's."""
     nq, nb, dim = src.size(0), tgt.size(0), src.size(1)
     if not _streaming(nq, nb, dim, k):
         return
-    if screened_status(src.device, key=ws_key)[1] == 0:
+    st = screened_status(src.device, key=ws_key)
+    if st[1] == 0:
         return
     rows = (idx[:, 0] < 0).nonzero().flatten()
-    for c in range(0, rows.numel(), 8192):
-        sel = rows[c:c + 8192]
-        d, i = knn_topk(src[sel], tgt, k, idx_base=idx_base, mode="exact")
-        dist[sel] = d
-        idx[sel] = i
+    _recompute_rows(src, tgt, k, idx_base, dist, idx, rows)
 
 
 SCREEN_CAP = 24   # EXB_SCREEN_CAP: candidate slots per list
@@ -208,11 +256,7 @@ def knn_rerank_lists(source, bank, k, val, idx, cnt, shard_lo, ha, ea, scalars):
             _lib.ptr(dist), _lib.ptr(out_i), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
         if screened_status(dev, key="knn_rerank_lists")[1] != 0:   # see _repair_overflow_rows
             rows = (out_i[:, 0] < 0).nonzero().flatten()
-            for c in range(0, rows.numel(), 8192):
-                sel = rows[c:c + 8192]
-                d, i = knn_topk(src[sel], tgt, k, mode="exact")
-                dist[sel] = d
-                out_i[sel] = i
+            _recompute_rows(src, tgt, k, 0, dist, out_i, rows)
     return dist, out_i
 
 
