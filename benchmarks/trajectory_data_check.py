@@ -56,5 +56,38 @@ def main():
                           "equals_exact_kernel": same, "why": why}), flush=True)
 
 
+def per_update():
+    """Per-update chain (B = 1024) on the same kinds of data: one whole episode (1024 consecutive
+    states) as the batch."""
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device=dev).manual_seed(1)
+    w = torch.randn(512, 24, generator=g, device=dev) / 24 ** 0.5
+    z = torch.zeros(512, device=dev)
+    for step in (0.05, 0.005, 0.0):
+        obs = torch.randn(1, 24, generator=g, device=dev) + torch.cumsum(
+            step * torch.randn(1024, 24, generator=g, device=dev), dim=0)
+        if step == 0.0:
+            obs = torch.randn(1024, 24, generator=g, device=dev)
+        rep = xb.icm_get_rep((w, z, torch.ones(512, device=dev), z), obs).rep
+        pbe = xb.PBE(xb.RMS(dev), 0.0, 12, True, True, dev)
+        ts = []
+        for _ in range(20):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            r = pbe(rep)
+            e1.record()
+            e1.synchronize()
+            ts.append(e0.elapsed_time(e1) * 1e3)
+        und = xb.knn.screened_status(dev, key="apt_reward")[0]
+        pe = xb.PBE(xb.RMS(dev), 0.0, 12, True, True, dev)
+        pe.mode = "exact"
+        for _ in range(20):
+            re_ = pe(rep)
+        same = bool(torch.allclose(r, re_, rtol=1e-5, atol=1e-7))
+        print(json.dumps({"per_update_batch": 1024, "walk_step": step, "us_median": sorted(ts)[10],
+                          "rows_recomputed_inline": und, "equals_exact_path": same}), flush=True)
+
+
 if __name__ == "__main__":
+    per_update()
     main()
