@@ -89,5 +89,8 @@ def per_update():
 
 
 if __name__ == "__main__":
+    import sys
     per_update()
+    if "--per-update-only" in sys.argv:
+        sys.exit(0)
     main()

@@ -244,8 +244,11 @@ knn_screen_lat_kernel(const __grid_constant__ CUtensorMap tmap_q,
       }
       // Chain fed with maxima of column pairs: its k-th entry is the k-th best of 32 real scores,
       // a lower bound of the true k-th best (conservative threshold) at half the min/max work.
+      // Pairs are (c, c + 32), not neighbours: in a batch of consecutive trajectory states a row's
+      // k nearest are adjacent columns, and adjacent pairs would hide half of them (the chain's
+      // k-th entry drops to about the 2k-th best and the list overflows its capacity).
 #pragma unroll
-      for (int c = 0; c < 32; ++c) chain_push_ks<KS>(tv, fmaxf(sc[2 * c], sc[2 * c + 1]));
+      for (int c = 0; c < 32; ++c) chain_push_ks<KS>(tv, fmaxf(sc[c], sc[32 + c]));
       st.tk = tv[KS - 1];
       if (st.tk > -FLT_MAX) st.tkeep = fmaxf(st.tkeep, keep_threshold(st));
       if (tr && j == 0 && et == 0) p.trace[4] = clock_now();

@@ -61,6 +61,7 @@ struct RerankParams {
   const PrepScalars* qsc;    // !LAT
   const PrepScalars* bsc;    // !LAT
   const float* bank_max;     // LAT: {EB, HBmax}
+  int split_cols;            // LAT: bank columns per split (tiles_per_split * 64)
   float* out_dist;
   int* out_idx;
   int* fallback_rows;        // !LAT
@@ -219,6 +220,19 @@ __device__ __forceinline__ void exact_scan(const float (&q)[16], const float* __
       }
     }
   }
+}
+
+// Rare path of the per-update chain, kept out of line so that it does not weigh on the register
+// allocation of the common one: exact distances of `count` bank rows (list[c], or base + c when
+// list is null) inserted into `top`.
+template <int NI>
+__device__ __noinline__ void scan_insert(const float (&q)[16], const float* __restrict__ B,
+                                         int dim, int k, int lane, int count, const int* list,
+                                         int base, WarpTopK& top) {
+  float sv[2];
+  int si[2];
+  exact_scan<NI, false>(q, B, dim, k, lane, count,
+                        [list, base](int c) { return list ? list[c] : base + c; }, top, sv, si);
 }
 
 // One warp, one query row.  Returns (in lanes < k) the row's k smallest distances, ascending.
@@ -434,10 +448,58 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
   int si[2] = {INT_MAX, INT_MAX};
   if (undecided) {
     if constexpr (LAT) {
-      // rare: recompute this row against the whole bank here (no fallback launches in the chain)
+      // rare: recompute this row here (no fallback launches in the chain)
       if (lane == 0) atomicAdd(&p.status->n_fallback, 1);
-      exact_scan<NI, false>(q, p.B, dim, k, lane, (int)p.nb, [](int c) { return c; }, top, sv,
-                             si);
+      // copies for the out-of-line calls: q and top themselves stay in registers
+      float qq[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) qq[i] = q[i];
+      WarpTopK tt;
+      tt.init();
+      if ((why & 4) || !(ea_row < INFINITY)) {
+        // outside the fp16 range: no screened score means anything, scan the whole bank
+        scan_insert<NI>(qq, p.B, dim, k, lane, (int)p.nb, nullptr, 0, tt);
+      } else {
+        // Only the splits whose list overflowed lost entries.  Every split's k-th chain entry is
+        // still a lower bound of the k-th best score, so the best of them gives a valid (looser)
+        // keep threshold: the complete lists are filtered with it, the overflowed splits' column
+        // ranges are scanned whole.
+        float t0 = (lane < splits) ? my_tk : -FLT_MAX;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) t0 = fmaxf(t0, __shfl_xor_sync(full, t0, off));
+        ListState st;
+        st.ha = ha_row;
+        st.e2 = 2.f * (ea_row + eb_max);
+        st.dl = (st.ha + hb_max) * SCR_ACC_EPS;
+        st.tk = t0;
+        const float tkeep0 = (t0 > -FLT_MAX) ? keep_threshold(st) : -FLT_MAX;
+        unsigned ovf = __ballot_sync(full, lane < splits && my_cnt < 0);
+        while (ovf) {
+          const int sp = __ffs(ovf) - 1;
+          ovf &= ovf - 1;
+          const int lo = sp * p.split_cols;
+          const int cnt = min((int)p.nb - lo, p.split_cols);
+          if (cnt > 0) scan_insert<NI>(qq, p.B, dim, k, lane, cnt, nullptr, lo, tt);
+        }
+        int n = 0;
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < RR_PER_LANE; ++i) {
+          const bool keep = ei[i] >= 0 && ev[i] >= tkeep0;
+          const unsigned m = __ballot_sync(full, keep);
+          if (n + __popc(m) > RR_SURV) {
+            __syncwarp();
+            scan_insert<NI>(qq, p.B, dim, k, lane, n, s_surv[wib], 0, tt);
+            __syncwarp();
+            n = 0;
+          }
+          if (keep) s_surv[wib][n + __popc(m & ((1u << lane) - 1u))] = ei[i];
+          n += __popc(m);
+        }
+        __syncwarp();
+        if (n > 0) scan_insert<NI>(qq, p.B, dim, k, lane, n, s_surv[wib], 0, tt);
+      }
+      top = tt;
     } else {
       if (lane == 0) {
         const int pos = atomicAdd(&p.status->n_fallback, 1);

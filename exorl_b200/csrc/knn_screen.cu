@@ -1364,6 +1364,7 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
   rp.out_idx = out_idx; rp.fallback_rows = w.fb_rows; rp.fallback_cap = pl.fb_cap;
   rp.status = w.status; rp.trace = trace_on ? w.trace : nullptr;
   rp.pbe.on = 0;
+  rp.split_cols = pl.lat ? pl.tiles_per_split * LAT_N : 0;
   rp.lists_per_shard = rp.splits;
   rp.shard_rows = 0;
   for (int i = 0; i < 16; ++i) rp.shard_lo[i] = 0;

@@ -194,6 +194,39 @@ def test_screened_handles_many_ties_through_fallback():
     assert und == 256 and invalid == 0
 
 
+@pytest.mark.parametrize("where", [(100, 140), (40, 90), (0, 300)])
+def test_per_update_rows_recomputed_over_the_overflowed_splits_only(where):
+    """A tight cluster of batch rows overflows the screen's list for the bank ranges (splits) that
+    hold it.  Those rows are recomputed inline from the overflowed ranges + the other splits'
+    complete lists; results stay equal to the oracle, PBE included."""
+    lo, hi = where
+    x = reps(17, 1024, 512)
+    g = torch.Generator().manual_seed(5)
+    x[lo:hi] = x[lo] + 1e-3 * torch.randn(hi - lo, 512, generator=g)
+    xd = x.to(DEV)
+    dist, idx = xb.knn_topk(xd, xd, 12, mode="screened")
+    und, invalid, _, _ = xknn.screened_status(torch.device(DEV))
+    # (a cluster of 300 sits inside the screening margin of every row of concentrated random reps)
+    assert invalid == 0 and 0 < und and (und < 1024 or hi - lo > 100)
+    assert_knn_matches(x, x, 12, dist, idx)
+    p = _pbe(0.0, 12, True, True, "screened")
+    st = RmsState()
+    _close(p(xd).cpu().numpy(), pbe_reward(x, x, st, 12, True, True, 0.0).numpy())
+
+
+def test_per_update_batch_of_consecutive_trajectory_states():
+    """One whole episode as the batch: a row's nearest neighbours are the adjacent bank columns."""
+    g = torch.Generator().manual_seed(3)
+    walk = torch.cumsum(0.05 * torch.randn(1024, 24, generator=g), 0)
+    w = torch.randn(24, 512, generator=g) / 24 ** 0.5
+    x = torch.tanh(torch.nn.functional.layer_norm(walk @ w, (512,)))
+    xd = x.to(DEV)
+    dist, idx = xb.knn_topk(xd, xd, 12, mode="screened")
+    und, invalid, _, _ = xknn.screened_status(torch.device(DEV))
+    assert invalid == 0 and und <= 128
+    assert_knn_matches(x, x, 12, dist, idx)
+
+
 def test_screened_range_fallback_for_unbounded_reps():
     """Values outside fp16 range cannot be screened; the call must still return exact results."""
     x = reps(12, 300, 32, "raw") * 1e5
