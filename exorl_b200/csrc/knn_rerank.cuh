@@ -357,9 +357,10 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
       const int msel = (k + rsel - 1) / rsel;
       const float mine = (lane < splits) ? my_tr : -FLT_MAX;
       int above = 0;       // how many splits' values beat this lane's (ties broken by lane id)
-      for (int s2 = 0; s2 < splits; ++s2) {
+#pragma unroll
+      for (int s2 = 0; s2 < 16; ++s2) {    // splits <= 16; unrolled so that the shuffles pipeline
         const float o = __shfl_sync(full, mine, s2);
-        above += (o > mine || (o == mine && s2 < lane)) ? 1 : 0;
+        above += (s2 < splits && (o > mine || (o == mine && s2 < lane))) ? 1 : 0;
       }
       const unsigned who = __ballot_sync(full, lane < splits && above == msel - 1);
       if (who != 0u) t0 = fmaxf(t0, __shfl_sync(full, mine, __ffs(who) - 1));
