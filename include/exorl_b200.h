@@ -85,8 +85,10 @@ int exb_knn_screened_f32(const float* src, int64_t nq, const float* bank, int64_
                          int32_t* out_idx, void* workspace, size_t workspace_bytes,
                          exb_stream_t stream);
 /* Device-side status word of the last screened call that used `workspace`:
- *   [0] undecided rows sent to the exact fallback, [1] non-zero if they exceeded capacity or
- *   the fp16 range check failed (results invalid -> use exb_knn_exact_f32), [2] candidate
+ *   [0] undecided rows sent to the exact fallback, [1] non-zero if they exceeded the
+ *   fallback's capacity (4096 rows per call): exactly those rows are left uncomputed and
+ *   marked with out_idx[row * k] = -1, every other row is final — recompute the marked rows
+ *   with exb_knn_exact_f32 (exorl_b200/knn.py:_repair_overflow_rows does), [2] candidate
  *   pairs reranked.  Copies 4 ints to host and synchronises `stream`. */
 int exb_knn_screened_status_sync(const void* workspace, int32_t host_status[4],
                                  exb_stream_t stream);
