@@ -30,7 +30,7 @@ def build_library(force=False, verbose=False):
     LIB_DIR.mkdir(exist_ok=True)
     obj_dir = PKG / "build"
     obj_dir.mkdir(exist_ok=True)
-    headers = list(CSRC.glob("*.cuh")) + [PKG.parent / "include" / "exorl_b200.h"]
+    headers = list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.h")) + [PKG.parent / "include" / "exorl_b200.h"]
     jobs = []
     for src in _sources():
         obj = obj_dir / (src.stem + ".o")

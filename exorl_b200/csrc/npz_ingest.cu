@@ -9,12 +9,16 @@
 //
 // Host-only code (zlib raw inflate); lives in the same shared library as the kernels.
 #include "common.cuh"
+#include "fast_inflate.h"
 #include <fcntl.h>
+#include <stdlib.h>
 #include <string.h>
 #include <sys/mman.h>
 #include <sys/stat.h>
 #include <unistd.h>
 #include <zlib.h>
+#include <algorithm>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -24,6 +28,7 @@ struct NpzMember {
   std::string name;        // without the ".npy" suffix
   int method;              // 0 = stored, 8 = deflate
   uint64_t comp_size, raw_size, data_off;
+  uint32_t crc;            // CRC-32 of the raw member (header + payload), from the directory
   // parsed from the .npy header
   std::string descr;
   bool fortran;
@@ -45,13 +50,25 @@ static inline uint32_t rd32(const uint8_t* p) {
 static inline uint64_t rd64(const uint8_t* p) { return (uint64_t)rd32(p) | ((uint64_t)rd32(p + 4) << 32); }
 
 // Inflate (or copy) `want` raw bytes of a member starting at raw offset `skip` into dst.
+// `crc` (optional) receives the CRC-32 of everything read, skipped bytes included.
 static int member_read(const NpzFile& f, const NpzMember& m, uint64_t skip, uint8_t* dst,
-                       uint64_t want) {
+                       uint64_t want, uint32_t* crc = nullptr) {
   if (m.data_off + m.comp_size > f.size) return EXB_EINVAL;
   const uint8_t* src = f.base + m.data_off;
+  uLong c = crc32(0L, Z_NULL, 0);
+  auto crc_add = [&](const uint8_t* p, uint64_t n) {
+    while (crc && n) {
+      const uInt step = n < (1u << 30) ? (uInt)n : (1u << 30);
+      c = crc32(c, p, step);
+      p += step;
+      n -= step;
+    }
+  };
   if (m.method == 0) {
     if (skip + want > m.comp_size) return EXB_EINVAL;
     memcpy(dst, src + skip, want);
+    crc_add(src, skip + want);
+    if (crc) *crc = (uint32_t)c;
     return EXB_OK;
   }
   z_stream zs;
@@ -67,6 +84,7 @@ static int member_read(const NpzFile& f, const NpzMember& m, uint64_t skip, uint
     zs.avail_out = (uInt)n;
     rc = inflate(&zs, Z_NO_FLUSH);
     skip -= n - zs.avail_out;
+    crc_add(scratch, n - zs.avail_out);
     if (zs.avail_out != 0 && rc != Z_OK) break;
   }
   uint64_t left = want;
@@ -82,7 +100,34 @@ static int member_read(const NpzFile& f, const NpzMember& m, uint64_t skip, uint
     if (got == 0 && rc != Z_OK) break;
   }
   inflateEnd(&zs);
+  crc_add(dst, want - left);
+  if (crc) *crc = (uint32_t)c;
   return (left == 0 && skip == 0) ? EXB_OK : EXB_EINVAL;
+}
+
+// Whole deflated member -> payload in dst, through the fast decoder (fast_inflate.h).  EXB_OK only
+// when the stream decoded cleanly AND its CRC-32 matches the directory's; anything else makes the
+// caller take the zlib path.
+static int member_read_fast(const NpzFile& f, const NpzMember& m, uint8_t* dst) {
+  if (m.method != 8 || m.data_off + m.comp_size > f.size || m.raw_size > (1ull << 40))
+    return EXB_EUNSUPPORTED;
+  static thread_local std::unique_ptr<finf::Tables> tables;
+  static thread_local std::vector<uint8_t> staging;
+  if (!tables) tables.reset(new finf::Tables);
+  if (staging.size() < m.raw_size + 8) staging.resize(m.raw_size + 8);
+  int rc = EXB_EINVAL;
+  if (finf::inflate_all(f.base + m.data_off, m.comp_size, staging.data(), m.raw_size,
+                        tables.get()) == 0) {
+    uLong c = crc32(0L, Z_NULL, 0);
+    for (uint64_t o = 0; o < m.raw_size; o += 1u << 30)
+      c = crc32(c, staging.data() + o, (uInt)std::min<uint64_t>(1u << 30, m.raw_size - o));
+    if ((uint32_t)c == m.crc) {
+      memcpy(dst, staging.data() + m.header_len, m.payload);
+      rc = EXB_OK;
+    }
+  }
+  if (staging.size() > (8u << 20)) std::vector<uint8_t>().swap(staging);   // keep small ones only
+  return rc;
 }
 
 // {'descr': '<f4', 'fortran_order': False, 'shape': (1001, 24), }
@@ -150,6 +195,7 @@ static int npz_parse(NpzFile* f) {
     if (p + 46 > f->size || rd32(f->base + p) != 0x02014b50u) return EXB_EINVAL;
     NpzMember m;
     m.method = rd16(f->base + p + 10);
+    m.crc = rd32(f->base + p + 16);
     m.comp_size = rd32(f->base + p + 20);
     m.raw_size = rd32(f->base + p + 24);
     const uint16_t nlen = rd16(f->base + p + 28), xlen = rd16(f->base + p + 30),
@@ -255,9 +301,30 @@ extern "C" int exb_npz_read(void* handle, int i, void* host_dst, int64_t dst_byt
   const NpzMember& m = f->members[i];
   EXB_CHECK_ARG(dst_bytes == (int64_t)m.payload, "array '%s': destination has %lld bytes, need %llu",
                 m.name.c_str(), (long long)dst_bytes, (unsigned long long)m.payload);
-  const int rc = member_read(*f, m, m.header_len, static_cast<uint8_t*>(host_dst), m.payload);
-  if (rc != EXB_OK) set_error("array '%s': corrupt or truncated stream", m.name.c_str());
-  return rc;
+  // EXB_NPZ_FAST_INFLATE: 1 (default) fast decoder with zlib behind it, 0 zlib only, 2 fast decoder
+  // only (tests: a member it cannot decode is an error instead of a silent slow path)
+  static const int fast_on = [] {
+    const char* e = getenv("EXB_NPZ_FAST_INFLATE");
+    return e ? atoi(e) : 1;
+  }();
+  if (fast_on && m.method == 8) {
+    if (member_read_fast(*f, m, static_cast<uint8_t*>(host_dst)) == EXB_OK) return EXB_OK;
+    if (fast_on == 2) {
+      set_error("array '%s': fast decoder failed (strict mode)", m.name.c_str());
+      return EXB_EINVAL;
+    }
+  }
+  uint32_t crc = 0;
+  const int rc = member_read(*f, m, m.header_len, static_cast<uint8_t*>(host_dst), m.payload, &crc);
+  if (rc != EXB_OK) {
+    set_error("array '%s': corrupt or truncated stream", m.name.c_str());
+    return rc;
+  }
+  if (crc != m.crc) {   // np.load (zipfile) raises BadZipFile "Bad CRC-32" here
+    set_error("array '%s': bad CRC-32 (file %08x, data %08x)", m.name.c_str(), m.crc, crc);
+    return EXB_EINVAL;
+  }
+  return EXB_OK;
 }
 
 extern "C" void exb_npz_close(void* handle) {
