@@ -53,7 +53,7 @@ static inline uint64_t rd64(const uint8_t* p) { return (uint64_t)rd32(p) | ((uin
 // `crc` (optional) receives the CRC-32 of everything read, skipped bytes included.
 static int member_read(const NpzFile& f, const NpzMember& m, uint64_t skip, uint8_t* dst,
                        uint64_t want, uint32_t* crc = nullptr) {
-  if (m.data_off + m.comp_size > f.size) return EXB_EINVAL;
+  if (m.data_off > f.size || m.comp_size > f.size - m.data_off) return EXB_EINVAL;
   const uint8_t* src = f.base + m.data_off;
   uLong c = crc32(0L, Z_NULL, 0);
   auto crc_add = [&](const uint8_t* p, uint64_t n) {
@@ -109,7 +109,8 @@ static int member_read(const NpzFile& f, const NpzMember& m, uint64_t skip, uint
 // when the stream decoded cleanly AND its CRC-32 matches the directory's; anything else makes the
 // caller take the zlib path.
 static int member_read_fast(const NpzFile& f, const NpzMember& m, uint8_t* dst) {
-  if (m.method != 8 || m.data_off + m.comp_size > f.size || m.raw_size > (1ull << 40))
+  if (m.method != 8 || m.data_off > f.size || m.comp_size > f.size - m.data_off ||
+      m.raw_size > (1ull << 40))
     return EXB_EUNSUPPORTED;
   static thread_local std::unique_ptr<finf::Tables> tables;
   static thread_local std::vector<uint8_t> staging;
@@ -149,7 +150,9 @@ static bool parse_npy_header(const uint8_t* h, size_t n, NpzMember* m) {
   m->descr = d.substr(p + 1, q - p - 1);
   p = d.find("'fortran_order'");
   if (p == std::string::npos) return false;
-  m->fortran = d.compare(d.find_first_not_of(": ", p + 15), 4, "True") == 0;
+  p = d.find_first_not_of(": ", p + 15);
+  if (p == std::string::npos) return false;
+  m->fortran = d.compare(p, 4, "True") == 0;
   p = d.find("'shape'");
   if (p == std::string::npos) return false;
   p = d.find('(', p);
@@ -208,6 +211,7 @@ static int npz_parse(NpzFile* f) {
     const uint8_t* x = f->base + p + 46 + nlen;
     for (size_t i = 0; i + 4 <= xlen;) {
       const uint16_t id = rd16(x + i), sz = rd16(x + i + 2);
+      if (i + 4 + sz > xlen) return EXB_EINVAL;     // extra record runs past the extra field
       if (id == 1) {
         size_t o = i + 4;
         if (m.raw_size == 0xffffffffu && o + 8 <= i + 4 + sz) { m.raw_size = rd64(x + o); o += 8; }
@@ -216,8 +220,13 @@ static int npz_parse(NpzFile* f) {
       }
       i += 4 + sz;
     }
-    if (lho + 30 > f->size || rd32(f->base + lho) != 0x04034b50u) return EXB_EINVAL;
+    if (lho > f->size || f->size - lho < 30 || rd32(f->base + lho) != 0x04034b50u)
+      return EXB_EINVAL;
     m.data_off = lho + 30 + rd16(f->base + lho + 26) + rd16(f->base + lho + 28);
+    // overflow-safe: the member's bytes lie inside the mapping, and a deflate stream expands at
+    // most 1032:1, so a directory claiming more than that is damaged (bounds every allocation)
+    if (m.data_off > f->size || m.comp_size > f->size - m.data_off) return EXB_EINVAL;
+    if (m.raw_size / 1032 > m.comp_size + 1) return EXB_EINVAL;
     if (m.method != 0 && m.method != 8) return EXB_EUNSUPPORTED;
     if (m.name.size() > 4 && m.name.compare(m.name.size() - 4, 4, ".npy") == 0)
       m.name.resize(m.name.size() - 4);
@@ -237,7 +246,23 @@ static int npz_parse(NpzFile* f) {
 
 using namespace exb;
 
-extern "C" int exb_npz_open(const char* path, void** handle, int* n_arrays) {
+// No C++ exception may cross the C ABI (std::bad_alloc from a staging buffer, std::length_error /
+// out_of_range from header parsing of a damaged file): they become EXB_EINVAL like every other
+// unreadable archive, which the loader treats as the reference treats a failed load_episode
+// (/root/reference/utils/replay_buffer.py:173-176).
+template <typename F>
+static int no_throw(const char* what, F&& body) {
+  try {
+    return body();
+  } catch (const std::exception& e) {
+    set_error("%s: %s", what, e.what());
+  } catch (...) {
+    set_error("%s: unknown C++ exception", what);
+  }
+  return EXB_EINVAL;
+}
+
+static int npz_open_impl(const char* path, void** handle, int* n_arrays) {
   EXB_CHECK_ARG(path && handle && n_arrays, "null pointer");
   const int fd = open(path, O_RDONLY);
   if (fd < 0) {
@@ -271,7 +296,7 @@ extern "C" int exb_npz_open(const char* path, void** handle, int* n_arrays) {
   return EXB_OK;
 }
 
-extern "C" int exb_npz_info(void* handle, int i, exb_npz_array* out) {
+static int npz_info_impl(void* handle, int i, exb_npz_array* out) {
   EXB_CHECK_ARG(handle && out, "null pointer");
   const NpzFile* f = static_cast<const NpzFile*>(handle);
   EXB_CHECK_ARG(i >= 0 && i < (int)f->members.size(), "array index %d out of range", i);
@@ -294,7 +319,7 @@ extern "C" int exb_npz_info(void* handle, int i, exb_npz_array* out) {
   return EXB_OK;
 }
 
-extern "C" int exb_npz_read(void* handle, int i, void* host_dst, int64_t dst_bytes) {
+static int npz_read_impl(void* handle, int i, void* host_dst, int64_t dst_bytes) {
   EXB_CHECK_ARG(handle && host_dst, "null pointer");
   const NpzFile* f = static_cast<const NpzFile*>(handle);
   EXB_CHECK_ARG(i >= 0 && i < (int)f->members.size(), "array index %d out of range", i);
@@ -332,4 +357,16 @@ extern "C" void exb_npz_close(void* handle) {
   NpzFile* f = static_cast<NpzFile*>(handle);
   munmap(const_cast<uint8_t*>(f->base), f->size);
   delete f;
+}
+
+extern "C" int exb_npz_open(const char* path, void** handle, int* n_arrays) {
+  return no_throw("exb_npz_open", [&] { return npz_open_impl(path, handle, n_arrays); });
+}
+
+extern "C" int exb_npz_info(void* handle, int i, exb_npz_array* out) {
+  return no_throw("exb_npz_info", [&] { return npz_info_impl(handle, i, out); });
+}
+
+extern "C" int exb_npz_read(void* handle, int i, void* host_dst, int64_t dst_bytes) {
+  return no_throw("exb_npz_read", [&] { return npz_read_impl(handle, i, host_dst, dst_bytes); });
 }

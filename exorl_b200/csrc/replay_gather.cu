@@ -61,7 +61,11 @@ __device__ __forceinline__ int64_t draw_row(int64_t s, uint64_t seed, uint64_t c
     k1 += 0xBB67AE85u;
   }
   const int64_t ep = (int64_t)(((uint64_t)c[0] * (uint64_t)n_episodes) >> 32);
-  const uint64_t span = (uint64_t)(__ldg(eps_len + ep) - nstep + 1);
+  // An episode shorter than nstep has no valid start (the reference raises ValueError from
+  // np.random.randint, :222); the host mirror raises before launching (replay.py:_check_spans).
+  // The clamp only keeps a direct C caller's reads inside the episode's own rows.
+  const int32_t span_i = __ldg(eps_len + ep) - nstep + 1;
+  const uint64_t span = (uint64_t)(span_i > 1 ? span_i : 1);
   const int64_t idx = (int64_t)(((uint64_t)c[1] * span) >> 32) + 1;
   if (episode) *episode = (int32_t)ep;
   return __ldg(eps_start + ep) + idx;

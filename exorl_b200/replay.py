@@ -16,127 +16,93 @@ import torch
 
 from . import _lib
 from . import ingest
+from .residency import EpisodeStore
 
 _CORE = ("observation", "action", "reward", "discount")
-
-
-def _episode_len(episode):
-    # rows - 1: row 0 is the dummy first transition (utils/replay_buffer.py:13-15)
-    return next(iter(episode.values())).shape[0] - 1
-
-
-def _load_npz(path):
-    """One episode file -> dict of (pinned) CPU tensors, via the native reader."""
-    return ingest.read_episode(path)
 
 
 def _as_tensor(a):
     return a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a))
 
 
-class DeviceReplayBuffer:
-    """Flat struct-of-arrays episode store in HBM with FIFO eviction by episode.
+class DeviceReplayBuffer(EpisodeStore):
+    """Flat struct-of-arrays episode store in HBM.
 
     Row layout: an episode of length L occupies L+1 consecutive rows of every column (row 0 of
-    the episode is the dummy first step).  Rows are allocated from a ring so that evicting the
-    oldest episode (utils/replay_buffer.py:178-182) frees the space that is reused next.
-    """
+    the episode is the dummy first step).  Which episodes are resident, where their rows are and
+    when the columns grow or compact is `residency.EpisodeStore` (the reference's sorted-name
+    eviction, utils/replay_buffer.py:172-190); this class holds the device columns and the
+    sampling kernels."""
 
     def __init__(self, device, max_size, nstep, discount, meta_names=(), capacity_rows=None):
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("exorl_b200: DeviceReplayBuffer needs a CUDA device (no CPU path)")
-        self.max_size = int(max_size)
+        super().__init__(max_size, capacity_rows)
         self.nstep = int(nstep)
         self.discount = float(discount)
         self.meta_names = tuple(meta_names)
-        self.capacity_rows = capacity_rows
         self.cols = {}            # name -> (capacity_rows, *shape) device tensor
-        self.size = 0             # transitions currently held
-        self.episodes = []        # FIFO of dicts(key, start, len) in insertion order
-        self._head = 0            # next free row in the ring
-        self._tables_dirty = True
         self._eps_start = None
         self._eps_len = None
-        self._sorted_keys = []
+        self._min_len = 0
 
-    # -- storage ----------------------------------------------------------------------------
-    def _allocate(self, episode):
-        eps_len = _episode_len(episode)
-        if self.capacity_rows is None:
-            per = eps_len + 1
-            n_eps = self.max_size // max(eps_len, 1) + 2
-            self.capacity_rows = n_eps * per + per
+    # -- column memory (EpisodeStore hooks) ---------------------------------------------------
+    @property
+    def _has_columns(self):
+        return bool(self.cols)
+
+    def _alloc_columns(self, episode, capacity):
         for name in (*_CORE, *self.meta_names):
             a = _as_tensor(episode[name])
-            self.cols[name] = torch.empty((self.capacity_rows, *a.shape[1:]), dtype=a.dtype,
+            self.cols[name] = torch.empty((capacity, *a.shape[1:]), dtype=a.dtype,
                                           device=self.device)
 
-    def _evict_oldest(self):
-        old = self.episodes.pop(0)
-        self.size -= old["len"]
-        self._tables_dirty = True
-        return old
+    def _grow_columns(self, capacity):
+        for name, old in self.cols.items():
+            new = torch.empty((capacity, *old.shape[1:]), dtype=old.dtype, device=self.device)
+            new[:old.shape[0]].copy_(old)
+            self.cols[name] = new
 
-    def _reserve(self, rows):
-        """Start row of a free contiguous range of `rows`, evicting oldest episodes if needed.
+    def _move_rows(self, old, new, rows):
+        for col in self.cols.values():
+            src = col[old:old + rows]
+            col[new:new + rows].copy_(src.clone() if new + rows > old else src)
 
-        Ring invariant: live rows run from tail = episodes[0].start forward (wrapping) to
-        _head.  head > tail: live is [tail, head), free is [head, cap) and [0, tail).
-        head <= tail: the allocator has wrapped, free is [head, tail)."""
-        if rows > self.capacity_rows:
-            raise RuntimeError(f"episode of {rows} rows exceeds buffer capacity {self.capacity_rows}")
-        while True:
-            if not self.episodes:
-                self._head = 0
-                return 0
-            tail = self.episodes[0]["start"]
-            if self._head > tail:
-                if self._head + rows <= self.capacity_rows:
-                    return self._head
-                if rows <= tail:
-                    return 0
-            elif self._head + rows <= tail:
-                return self._head
-            self._evict_oldest()
-
-    def add_episode(self, episode, key=None):
-        """Append one episode (dict of numpy arrays with L+1 rows), evicting from the front while
-        `eps_len + size > max_size` like utils/replay_buffer.py:178-182."""
-        eps_len = _episode_len(episode)
-        if not self.cols:
-            self._allocate(episode)
-        while self.episodes and eps_len + self.size > self.max_size:
-            self._evict_oldest()
-        start = self._reserve(eps_len + 1)
+    def _write_rows(self, start, episode, rows):
         for name, col in self.cols.items():
             a = _as_tensor(episode[name])
-            if a.shape[0] != eps_len + 1:
-                raise ValueError(f"column {name}: {a.shape[0]} rows, expected {eps_len + 1}")
+            if a.shape[0] != rows:
+                raise ValueError(f"column {name}: {a.shape[0]} rows, expected {rows}")
             # pinned staging (ingest.read_episode) -> asynchronous DMA on the current stream; the
             # staging tensor stays referenced by `episode` until the caller drops it, and the
             # caching host allocator does not reuse a pinned block with a copy in flight
-            col[start:start + eps_len + 1].copy_(a, non_blocking=a.is_pinned())
-        self._head = start + eps_len + 1
-        self.episodes.append({"key": key if key is not None else len(self.episodes),
-                              "start": start, "len": eps_len})
-        self.size += eps_len
-        self._tables_dirty = True
+            col[start:start + rows].copy_(a, non_blocking=a.is_pinned())
 
     def _tables(self):
-        """Episode tables ordered like the reference's sorted `_episode_fns` (:184-185)."""
+        """Device episode tables in the order of the reference's sorted `_episode_fns` (:184)."""
         if self._tables_dirty:
-            order = sorted(range(len(self.episodes)), key=lambda i: str(self.episodes[i]["key"]))
-            self._sorted = [self.episodes[i] for i in order]
-            starts = np.array([e["start"] for e in self._sorted], np.int64)
-            lens = np.array([e["len"] for e in self._sorted], np.int32)
+            eps = self.episodes
+            starts = np.array([e["start"] for e in eps], np.int64)
+            lens = np.array([e["len"] for e in eps], np.int32)
             self._eps_start = torch.from_numpy(starts).to(self.device)
             self._eps_len = torch.from_numpy(lens).to(self.device)
+            self._min_len = int(lens.min()) if len(eps) else 0
             self._tables_dirty = False
-        return self._sorted, self._eps_start, self._eps_len
+        return self.episodes, self._eps_start, self._eps_len
 
-    def __len__(self):
-        return self.size
+    def _check_spans(self, offline):
+        """The reference draws `np.random.randint(0, eps_len - nstep + 1)` (:222; `eps_len`
+        offline, :90), which raises ValueError for an episode with no valid start.  There the
+        error depends on which episode is drawn; here any resident episode that short raises."""
+        eps, _, _ = self._tables()
+        if not eps:
+            raise RuntimeError("replay buffer is empty")
+        need = 1 if offline else self.nstep
+        if self._min_len < need:
+            short = next(e for e in eps if e["len"] < need)
+            raise ValueError(f"low >= high: episode {short['key']} has {short['len']} steps, "
+                             f"fewer than nstep={need}")
 
     # -- relabelling (the step after the kNN reward path, SURVEY.md §8f.4) ------------------------
     def live_rows(self):
@@ -179,9 +145,8 @@ class DeviceReplayBuffer:
     def draw_rows_philox(self, batch, seed, call, offline=False):
         """Device index draw: uniform episode, then uniform start (range of :222 / :90)."""
         lib = _lib.load()
+        self._check_spans(offline)
         eps, starts, lens = self._tables()
-        if not eps:
-            raise RuntimeError("replay buffer is empty")
         rows = torch.empty(batch, dtype=torch.int64, device=self.device)
         with torch.cuda.device(self.device):
             _lib.check(lib.exb_replay_draw(
@@ -199,7 +164,7 @@ class DeviceReplayBuffer:
         for b in range(batch):
             e = random.choice(eps)
             span = e["len"] if offline else e["len"] - self.nstep + 1
-            rows[b] = e["start"] + np.random.randint(0, span) + 1
+            rows[b] = e["start"] + np.random.randint(0, span) + 1   # ValueError if span <= 0
         return torch.from_numpy(rows).pin_memory().to(self.device, non_blocking=True)
 
     def rows_from_draws(self, draws):
@@ -252,9 +217,8 @@ class DeviceReplayBuffer:
         """Index draw + gather as ONE kernel launch (exb_replay_sample): same result as
         `gather(draw_rows_philox(batch, seed, call))`."""
         lib = _lib.load()
+        self._check_spans(offline)
         eps, starts, lens = self._tables()
-        if not eps:
-            raise RuntimeError("replay buffer is empty")
         out, cols, n_cols, nstep = self._outputs(batch, offline)
         rows = torch.empty(batch, dtype=torch.int64, device=self.device) if return_rows else None
         with torch.cuda.device(self.device):
@@ -266,16 +230,39 @@ class DeviceReplayBuffer:
         return (out, rows) if return_rows else out
 
 
+def _eps_idx_len(fn):
+    # `episode_{idx}_{len}.npz` (utils/replay_buffer.py:146-149); ValueError on other names, as
+    # the reference's `int(x) for x in eps_fn.stem.split('_')[1:]` (:67, :203)
+    idx, eps_len = [int(x) for x in fn.stem.split("_")[1:]]
+    return idx, eps_len
+
+
+class _Worker:
+    """One DataLoader worker of the reference: its own episode set (files with
+    `eps_idx % num_workers == worker_id`, :68-69, :204-205), size cap `max_size // num_workers`
+    (:262) and fetch counter (:164, :195-197)."""
+
+    def __init__(self, wid, buffer, fetch_every):
+        self.wid = wid
+        self.buffer = buffer
+        self.since_fetch = fetch_every
+        self.loaded = False
+
+
 class DeviceReplayLoader:
     """Iterable that yields batches forever, like the DataLoader the reference builds
-    (utils/replay_buffer.py:246-277).  `num_workers` only scales `max_size` the way the
-    reference's per-worker split does; there are no worker processes."""
+    (utils/replay_buffer.py:246-277).  The reference's `num_workers` worker processes become
+    `num_workers` partitions of the device store: batch i is drawn from partition i % W (a
+    DataLoader takes whole batches from its workers in turn), and each partition fetches, caps
+    and evicts on its own like a worker does.  There are no processes; `buffer` is partition 0."""
 
-    def __init__(self, buffer, batch_size, replay_dir=None, offline=False, save_snapshot=True,
+    def __init__(self, buffers, batch_size, replay_dir=None, offline=False, save_snapshot=True,
                  fetch_every=1000, sampler="philox", seed=None):
         if sampler not in ("philox", "reference_rng"):
             raise ValueError("sampler must be 'philox' or 'reference_rng'")
-        self.buffer = buffer
+        if isinstance(buffers, DeviceReplayBuffer):
+            buffers = [buffers]
+        self.workers = [_Worker(w, b, fetch_every) for w, b in enumerate(buffers)]
         self.batch_size = int(batch_size)
         self.replay_dir = pathlib.Path(replay_dir) if replay_dir is not None else None
         self.offline = offline
@@ -283,59 +270,98 @@ class DeviceReplayLoader:
         self.fetch_every = fetch_every
         self.sampler = sampler
         self.seed = int(seed if seed is not None else np.random.randint(0, 2 ** 31 - 1))
-        self._since_fetch = fetch_every
-        self._seen = set()
         self._calls = 0
-        self._loaded = False
+
+    @property
+    def buffer(self):
+        return self.workers[0].buffer
+
+    @property
+    def buffers(self):
+        return [w.buffer for w in self.workers]
+
+    def resident_files(self):
+        """Names of the resident episode files per partition, in the reference's sorted order
+        (`ReplayBuffer._episode_fns` of worker w)."""
+        return [[pathlib.Path(str(e["key"])).name for e in w.buffer.episodes]
+                for w in self.workers]
 
     # -- ingestion ---------------------------------------------------------------------------
-    def _try_fetch(self):
-        """Online: newest-first scan of the replay dir for unseen episodes
-        (utils/replay_buffer.py:192-212)."""
-        if self._since_fetch < self.fetch_every or self.replay_dir is None:
+    def _try_fetch(self, worker):
+        """`ReplayBuffer._try_fetch` + `_store_episode` (utils/replay_buffer.py:172-212) for one
+        partition: newest-first scan of the directory, stop at the first file that is already
+        resident (:206) or that would take this fetch over the cap (:208); every stored episode
+        evicts the first of the sorted resident names while over the cap and UNLINKS the evicted
+        file (:178-182); a file that cannot be read ends the fetch (:211-212)."""
+        if worker.since_fetch < self.fetch_every or self.replay_dir is None:
             return
-        self._since_fetch = 0
-        new = []
-        fetched = 0
+        worker.since_fetch = 0
+        buf, n_workers = worker.buffer, len(self.workers)
+        todo, fetched = [], 0
         for fn in sorted(self.replay_dir.glob("*.npz"), reverse=True):
-            eps_len = int(fn.stem.split("_")[2])
-            if fn in self._seen:
+            eps_idx, eps_len = _eps_idx_len(fn)
+            if eps_idx % n_workers != worker.wid:
+                continue
+            if str(fn) in buf._index:
                 break
-            if fetched + eps_len > self.buffer.max_size:
+            if fetched + eps_len > buf.max_size:
                 break
             fetched += eps_len
-            new.append(fn)
-        try:              # the reference stores them in this (newest-first) order too
-            for fn, episode in ingest.read_episodes(new):
-                self.buffer.add_episode(episode, key=str(fn))
-                self._seen.add(fn)
-                if not self.save_snapshot:
-                    fn.unlink(missing_ok=True)
-        except (ValueError, RuntimeError, OSError):
-            pass          # a half-written file: stop here, like the `break` of :206-209
-
-    def _load_offline(self):
-        """Offline: sorted scan until the size cap (utils/replay_buffer.py:57-75)."""
-        for fn, episode in ingest.read_episodes(sorted(self.replay_dir.glob("*.npz"))):
-            if self.buffer.size > self.buffer.max_size:
+            todo.append(fn)
+        if todo and not buf._has_columns:
+            buf.reserve_rows(sum(_eps_idx_len(fn)[1] + 1 for fn in todo))
+        it = ingest.read_episodes(todo)
+        while True:
+            try:
+                fn, episode = next(it)
+            except StopIteration:
                 break
-            self.buffer.add_episode(episode, key=str(fn))
-        self._loaded = True
+            except (ValueError, OSError, EOFError):
+                break     # a half-written or damaged file: `_store_episode` returned False
+            for old in buf.add_episode(episode, key=str(fn)):
+                pathlib.Path(old["key"]).unlink(missing_ok=True)
+            if not self.save_snapshot:
+                fn.unlink(missing_ok=True)
+
+    def _load_offline(self, worker):
+        """`OfflineReplayBuffer._load` (utils/replay_buffer.py:57-75): sorted scan; the size test
+        comes BEFORE each file (:65-66), so loading stops once the partition holds more than its
+        cap — the first episodes are kept, the cap is overshot by at most one episode, nothing
+        is evicted and nothing further is read."""
+        buf, n_workers = worker.buffer, len(self.workers)
+        todo, size = [], 0
+        for fn in sorted(self.replay_dir.glob("*.npz")):
+            if size > buf.max_size:
+                break
+            eps_idx, eps_len = _eps_idx_len(fn)
+            if eps_idx % n_workers != worker.wid:
+                continue
+            todo.append(fn)
+            size += eps_len     # the name's length field; the loop below re-checks on real sizes
+        if todo:
+            buf.reserve_rows(sum(_eps_idx_len(fn)[1] + 1 for fn in todo))
+        for fn, episode in ingest.read_episodes(todo):
+            if buf.size > buf.max_size:
+                break
+            buf.add_episode(episode, key=str(fn), evict=False)
+        worker.loaded = True
 
     # -- iteration ---------------------------------------------------------------------------
     def sample(self):
+        worker = self.workers[self._calls % len(self.workers)]
         if self.offline:
-            if not self._loaded:
-                self._load_offline()
+            if not worker.loaded:
+                self._load_offline(worker)
         else:
-            self._try_fetch()
-            self._since_fetch += self.batch_size
+            self._try_fetch(worker)
+            worker.since_fetch += self.batch_size
         self._calls += 1
+        buf = worker.buffer
         if self.sampler == "philox":
-            return self.buffer.sample_philox(self.batch_size, self.seed, self._calls - 1,
-                                             offline=self.offline)
-        rows = self.buffer.draw_rows_reference_rng(self.batch_size, offline=self.offline)
-        return self.buffer.gather(rows, offline=self.offline)
+            return buf.sample_philox(self.batch_size, self.seed, self._calls - 1,
+                                     offline=self.offline)
+        rows = buf.draw_rows_reference_rng(self.batch_size, offline=self.offline)
+        return buf.gather(rows, offline=self.offline)
 
     def __iter__(self):
         while True:
@@ -351,10 +377,10 @@ def make_replay_loader(storage, max_size, batch_size, num_workers, save_snapshot
     """Same positional signature as utils/replay_buffer.py:260-277.  `storage` exposes
     `_replay_dir` and `_meta_specs` (objects with `.name`)."""
     workers = max(1, num_workers)
-    cap = (max_size // workers) * workers      # the reference caps each worker at max_size//W
     meta = tuple(spec.name for spec in storage._meta_specs)
-    buf = DeviceReplayBuffer(_device(device), cap, nstep, discount, meta_names=meta)
-    return DeviceReplayLoader(buf, batch_size, replay_dir=storage._replay_dir, offline=False,
+    bufs = [DeviceReplayBuffer(_device(device), max_size // workers, nstep, discount,
+                               meta_names=meta) for _ in range(workers)]
+    return DeviceReplayLoader(bufs, batch_size, replay_dir=storage._replay_dir, offline=False,
                               save_snapshot=save_snapshot, fetch_every=1000, sampler=sampler,
                               seed=seed)
 
@@ -364,7 +390,7 @@ def make_offline_replay_loader(env, replay_dir, max_size, batch_size, num_worker
     """Same positional signature as utils/replay_buffer.py:246-258.  `env` is accepted and
     unused: extrinsic relabelling through MuJoCo physics (:31-42) is outside this path."""
     workers = max(1, num_workers)
-    cap = (max_size // workers) * workers
-    buf = DeviceReplayBuffer(_device(device), cap, 1, discount)
-    return DeviceReplayLoader(buf, batch_size, replay_dir=replay_dir, offline=True,
+    bufs = [DeviceReplayBuffer(_device(device), max_size // workers, 1, discount)
+            for _ in range(workers)]
+    return DeviceReplayLoader(bufs, batch_size, replay_dir=replay_dir, offline=True,
                               sampler=sampler, seed=seed)

@@ -217,6 +217,95 @@ def gen_replay(ref_replay):
     np.savez_compressed(OUT / "replay_reference.npz", **out)
 
 
+RESIDENCY_ONLINE = {
+    # name: (max_size, num_workers, save_snapshot, rounds of [(eps_idx, eps_len), ...])
+    # Every round first writes its files, then each worker fetches once (:192-212).
+    "w1_snapshot": (50, 1, True, [[(0, 10), (1, 12), (2, 9), (3, 11), (4, 10)],
+                                  [(5, 10), (6, 14)],
+                                  [(7, 8), (8, 10), (9, 10), (10, 10), (11, 12)],   # 9 -> 10: names sort as text
+                                  [(12, 30)],
+                                  [(13, 10), (14, 10), (15, 10), (16, 10), (17, 10), (18, 10), (19, 10)]]),
+    "w1_no_snapshot": (40, 1, False, [[(0, 10), (1, 10), (2, 10)], [(3, 15), (4, 15)],
+                                      [(5, 10), (6, 7), (7, 13)], [(8, 10), (9, 10), (10, 10)]]),
+    "w2_snapshot": (60, 2, True, [[(0, 10), (1, 10), (2, 10), (3, 10)],
+                                  [(4, 12), (5, 9), (6, 11), (7, 10), (8, 10)],
+                                  [(9, 10), (10, 10), (11, 10), (12, 10), (13, 10)],
+                                  [(14, 25), (15, 25), (16, 5)]]),
+    "first_fetch_over_cap": (35, 1, True, [[(e, 10) for e in range(8)], [(8, 10)], [(9, 10), (10, 10)]]),
+}
+RESIDENCY_OFFLINE = {
+    # name: (max_size as passed to the factory, num_workers, [(eps_idx, eps_len), ...])
+    "w1_cap_inside": (45, 1, [(e, 10) for e in range(12)]),
+    "w1_ragged": (30, 1, [(0, 7), (1, 12), (2, 9), (3, 3), (4, 20), (5, 8), (6, 10)]),
+    "w2": (50, 2, [(e, 10 + e % 3) for e in range(14)]),
+    "under_cap": (1000, 1, [(e, 10) for e in range(5)]),
+}
+
+
+def residency_episode(eps_idx, eps_len):
+    """The (tiny) episode written for a residency scenario; the tests rebuild the same files."""
+    rng = np.random.default_rng(1000 + eps_idx)
+    return synth_episode(rng, eps_len, (3,), np.float32, terminal=False, with_meta=False)
+
+
+def gen_residency(ref_replay):
+    """Which episode files the reference keeps resident and which it leaves on disk.
+
+    Online: ReplayBuffer._try_fetch/_store_episode (utils/replay_buffer.py:172-212) over a
+    directory that grows between fetches — sorted-name eviction with unlink, save_snapshot on and
+    off, one and two DataLoader workers (the worker id the reference reads from
+    torch.utils.data.get_worker_info() is supplied by patching that function, nothing in the
+    reference is modified).  Offline: OfflineReplayBuffer._load (:57-75) over directories larger
+    and smaller than the cap."""
+    import json
+    import torch.utils.data as tud
+    real_info = tud.get_worker_info
+    out = {"online": {}, "offline": {}}
+    try:
+        for name, (max_size, workers, snapshot, rounds) in RESIDENCY_ONLINE.items():
+            with tempfile.TemporaryDirectory() as td:
+                td = pathlib.Path(td)
+                storage = types.SimpleNamespace(_replay_dir=td, _meta_specs=())
+                bufs = [ref_replay.ReplayBuffer(storage, max_size // workers, workers, 3, 0.99,
+                                                fetch_every=1000, save_snapshot=snapshot)
+                        for _ in range(workers)]
+                log = []
+                for files in rounds:
+                    for eps_idx, eps_len in files:
+                        ref_replay.save_episode(residency_episode(eps_idx, eps_len),
+                                                td / f"episode_{eps_idx}_{eps_len}.npz")
+                    for w, buf in enumerate(bufs):
+                        tud.get_worker_info = lambda w=w: types.SimpleNamespace(id=w)
+                        buf._samples_since_last_fetch = buf._fetch_every
+                        buf._try_fetch()
+                    log.append({"written": files,
+                                "resident": [[fn.name for fn in b._episode_fns] for b in bufs],
+                                "size": [b._size for b in bufs],
+                                "on_disk": sorted(fn.name for fn in td.glob("*.npz"))})
+                out["online"][name] = {"max_size": max_size, "num_workers": workers,
+                                       "save_snapshot": snapshot, "rounds": log}
+        for name, (max_size, workers, files) in RESIDENCY_OFFLINE.items():
+            with tempfile.TemporaryDirectory() as td:
+                td = pathlib.Path(td)
+                for eps_idx, eps_len in files:
+                    ref_replay.save_episode(residency_episode(eps_idx, eps_len),
+                                            td / f"episode_{eps_idx}_{eps_len}.npz")
+                resident, size = [], []
+                for w in range(workers):
+                    tud.get_worker_info = lambda w=w: types.SimpleNamespace(id=w)
+                    off = ref_replay.OfflineReplayBuffer(None, td, max_size // workers, workers,
+                                                         0.99)
+                    off._load(relable=False)
+                    resident.append([fn.name for fn in off._episode_fns])
+                    size.append(off._size)
+                out["offline"][name] = {"max_size": max_size, "num_workers": workers,
+                                        "files": files, "resident": resident, "size": size}
+    finally:
+        tud.get_worker_info = real_info
+    (OUT / "residency_reference.json").write_text(json.dumps(out, indent=1) + "\n")
+    print("residency scenarios:", len(out["online"]), "online,", len(out["offline"]), "offline")
+
+
 def load_reference_icm(ref_utils):
     """class ICM of agents/unsupervised_learning/icm_apt.py:10-52, executed from the reference's
     own source text (the module imports hydra / the `utils` package / .ddpg, absent here, so only
@@ -309,6 +398,9 @@ if __name__ == "__main__":
     if "--rep-only" in sys.argv:
         gen_rep(ref_utils)
         sys.exit(0)
+    if "--residency-only" in sys.argv:
+        gen_residency(ref_replay)
+        sys.exit(0)
     if "--rnd-only" in sys.argv:
         gen_rnd(ref_utils)
         sys.exit(0)
@@ -319,5 +411,6 @@ if __name__ == "__main__":
     gen_knn_dists(ref_utils)
     gen_proto()
     gen_replay(ref_replay)
+    gen_residency(ref_replay)
     for f in sorted(OUT.glob("*.npz")):
         print(f.name, f.stat().st_size)

@@ -171,7 +171,7 @@ def test_loader_dropin_signature_and_reference_rng_parity(tmp_path):
     assert disc.shape == (1024, 1) and nobs.shape == (1024, 24) and skill.shape == (1024, 4)
 
 
-def test_offline_loader_and_fifo_eviction(tmp_path):
+def test_offline_loader_and_sorted_name_eviction(tmp_path):
     rng = np.random.default_rng(8)
     eps = []
     for e in range(6):
@@ -182,7 +182,7 @@ def test_offline_loader_and_fifo_eviction(tmp_path):
                                            device=DEV, seed=1)
     obs, act, rew, disc, nobs = next(iter(loader))
     assert obs.shape == (32, 24) and torch.all(disc == np.float32(0.99))
-    # FIFO eviction by episode at max_size (utils/replay_buffer.py:178-182)
+    # eviction by episode at max_size, first of the sorted names (utils/replay_buffer.py:178-185)
     buf = xb.DeviceReplayBuffer(DEV, 35, 3, 0.99)
     for e, ep in enumerate(eps):
         buf.add_episode(ep, key=f"episode_{e}_10.npz")
@@ -298,3 +298,128 @@ def test_relabel_rewards_and_export_roundtrip(tmp_path):
             assert np.array_equal(got[name], ep[name]), (k, name)
     with pytest.raises(ValueError):
         buf.relabel_rewards(new_r[:-1])
+
+
+def _residency_scenarios(kind):
+    import json
+    path = pathlib.Path(__file__).resolve().parent / "golden" / "residency_reference.json"
+    return sorted(json.loads(path.read_text())[kind].items())
+
+
+def _check_device_rows(buf, written):
+    for e in buf.episodes:
+        want = written[pathlib.Path(str(e["key"])).name]
+        lo, hi = e["start"], e["start"] + e["len"] + 1
+        for name, col in buf.cols.items():
+            assert np.array_equal(col[lo:hi].cpu().numpy(), want[name]), (e["key"], name)
+
+
+@pytest.mark.parametrize("name,sc", _residency_scenarios("online"))
+def test_online_residency_matches_reference_fixture(tmp_path, name, sc):
+    """make_replay_loader over a growing directory: resident files per worker partition, sizes
+    and on-disk leftovers after every fetch round equal what the reference's ReplayBuffer did
+    (fixture recorded by oracle/gen_golden.py:gen_residency; utils/replay_buffer.py:172-212)."""
+    from oracle.gen_golden import residency_episode
+    storage = types.SimpleNamespace(_replay_dir=pathlib.Path(tmp_path), _meta_specs=())
+    loader = xb.make_replay_loader(storage, sc["max_size"], 1000, sc["num_workers"],
+                                   sc["save_snapshot"], 3, 0.99, device=DEV, seed=3)
+    written = {}
+    for r, rnd in enumerate(sc["rounds"]):
+        for eps_idx, eps_len in rnd["written"]:
+            fn = f"episode_{eps_idx}_{eps_len}.npz"
+            written[fn] = residency_episode(eps_idx, eps_len)
+            write_episode_npz(written[fn], tmp_path / fn)
+        # batch 1000 = fetch_every: every batch of a partition is preceded by a fetch
+        batches = [next(iter(loader)) for _ in range(sc["num_workers"])]
+        assert all(b[0].shape == (1000, 3) for b in batches)
+        assert loader.resident_files() == rnd["resident"], (name, r)
+        assert [b.size for b in loader.buffers] == rnd["size"], (name, r)
+        assert sorted(f.name for f in tmp_path.glob("*.npz")) == rnd["on_disk"], (name, r)
+        for b in loader.buffers:
+            _check_device_rows(b, written)
+
+
+@pytest.mark.parametrize("name,sc", _residency_scenarios("offline"))
+def test_offline_residency_matches_reference_fixture(tmp_path, name, sc):
+    """make_offline_replay_loader over a directory larger than the cap keeps the FIRST episodes
+    (sorted names), overshooting the cap by at most one episode, like
+    OfflineReplayBuffer._load (utils/replay_buffer.py:57-75)."""
+    from oracle.gen_golden import residency_episode
+    written = {}
+    for eps_idx, eps_len in sc["files"]:
+        fn = f"episode_{eps_idx}_{eps_len}.npz"
+        written[fn] = residency_episode(eps_idx, eps_len)
+        write_episode_npz(written[fn], tmp_path / fn)
+    loader = xb.make_offline_replay_loader(None, pathlib.Path(tmp_path), sc["max_size"], 64,
+                                           sc["num_workers"], 0.99, device=DEV, seed=1)
+    it = iter(loader)
+    for _ in range(sc["num_workers"]):
+        obs, act, rew, disc, nobs = next(it)
+        assert obs.shape == (64, 3)
+    assert loader.resident_files() == sc["resident"]
+    assert [b.size for b in loader.buffers] == sc["size"]
+    assert len(list(tmp_path.glob("*.npz"))) == len(sc["files"])
+    for b in loader.buffers:
+        _check_device_rows(b, written)
+
+
+def test_batches_of_a_partitioned_loader_come_from_one_partition_each(tmp_path):
+    """num_workers = 2: batch i is drawn from partition i % 2, whose episodes are the files with
+    eps_idx % 2 == partition (utils/replay_buffer.py:204-205 + DataLoader's round-robin)."""
+    for e in range(6):
+        ep = _synth(np.random.default_rng(e), 10)
+        ep["observation"][:] = e            # the observation value names its episode
+        write_episode_npz(ep, tmp_path / f"episode_{e}_10.npz")
+    storage = types.SimpleNamespace(_replay_dir=pathlib.Path(tmp_path), _meta_specs=())
+    loader = xb.make_replay_loader(storage, 1000, 256, 2, True, 3, 0.99, device=DEV, seed=9)
+    it = iter(loader)
+    for i in range(4):
+        obs = next(it)[0]
+        seen = set(obs[:, 0].cpu().numpy().astype(int).tolist())
+        assert seen == {e for e in range(6) if e % 2 == i % 2}, (i, seen)
+
+
+def test_episode_shorter_than_nstep_raises_like_the_reference():
+    """np.random.randint(0, eps_len - nstep + 1) raises ValueError when an episode has no valid
+    start (utils/replay_buffer.py:222); every sampler does the same before launching."""
+    rng = np.random.default_rng(12)
+    buf = _buffer([_synth(rng, 10), _synth(rng, 2)], 3)
+    for call in (lambda: buf.sample_philox(8, 1, 0), lambda: buf.draw_rows_philox(8, 1, 0)):
+        with pytest.raises(ValueError, match="low >= high"):
+            call()
+    random.seed(0)
+    np.random.seed(0)
+    with pytest.raises(ValueError):
+        buf.draw_rows_reference_rng(64)
+    # the same episodes are fine for a one-step (offline) draw and for nstep 2
+    out = buf.sample_philox(8, 1, 0, offline=True)
+    assert out[0].shape == (8, 24)
+    ok = _buffer([_synth(rng, 10), _synth(rng, 2)], 2)
+    (obs, act, rew, disc, nobs), rows = ok.sample_philox(512, 1, 0, return_rows=True)
+    st = {e["start"]: e["len"] for e in ok.episodes}
+    short_start = next(s for s, L in st.items() if L == 2)
+    in_short = (rows >= short_start) & (rows <= short_start + 2)
+    assert in_short.any() and torch.all(rows[in_short] == short_start + 1)
+
+
+def test_store_growth_and_compaction_on_device():
+    """The device columns grow from a small first allocation and compact when fragmented;
+    sampled transitions still equal the oracle's afterwards."""
+    rng = np.random.default_rng(13)
+    buf = xb.DeviceReplayBuffer(DEV, 2000, 3, 0.99)
+    eps = {}
+    cap0 = None
+    for i in rng.permutation(200):
+        L = int(rng.choice((5, 12, 40)))
+        key = f"episode_{i:03d}_{L}.npz"
+        eps[key] = _synth(rng, L)
+        buf.add_episode(eps[key], key=key)
+        cap0 = cap0 or buf.capacity_rows
+    assert buf.capacity_rows > cap0 and 1900 < buf.size <= 2000
+    sorted_eps, _, _ = buf._tables()
+    draws = [(pos, 1) for pos in range(len(sorted_eps))]
+    out = buf.gather(buf.rows_from_draws(draws))
+    for s, (pos, idx) in enumerate(draws):
+        want = nstep_transition(eps[sorted_eps[pos]["key"]], idx, 3, 0.99)
+        for j in range(5):
+            assert np.array_equal(out[j][s].cpu().numpy(), np.asarray(want[j]))
