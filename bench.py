@@ -42,6 +42,10 @@ def parse():
     ap.add_argument("--cpu-queries", type=int, default=128,
                     help="queries of the bounded CPU-baseline sample (vs the full bank)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true",
+                    help="skip the C1-C4 block (BASELINE configs 1-4) of the 1-GPU line")
+    ap.add_argument("--no-exchange-ab", action="store_true",
+                    help="skip the one-step timings of the bank-sharded exchanges (N > 1)")
     ap.add_argument("--stage-times", action="store_true",
                     help="after the timed runs, one extra step with per-stage CUDA events (stderr)")
     return ap.parse_args()
@@ -105,7 +109,9 @@ def run_reference(a, rank):
     dt = sum(times)
     value = q * a.steps / dt
     sample = (f"{q} queries per step against the full {a.n}-row bank (reference formula "
-              f"utils/utils.py:293-319, tiled), scaled per query")
+              f"utils/utils.py:293-319, tiled), scaled per query; the per-query cost is flat in "
+              f"the slice size (every query scans the whole bank), so SURVEY 8d's 4096-query "
+              f"slice (minutes per step) would measure the same rate")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus,
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * dt / a.steps,
@@ -206,7 +212,11 @@ def run_ours(a, rank, world, local_rank):
                         "cores": torch.get_num_threads(), "kind": "port",
                         "sample": (f"{a.cpu_queries} queries against the full {a.n}-row bank with "
                                    f"the reference formula (tiled torch CPU), {dt:.1f} s, scaled "
-                                   f"per query")}
+                                   f"per query; SURVEY 8d's 4096-query slice would take "
+                                   f"{4096 / a.cpu_queries * dt / 60:.0f} min on these cores, the "
+                                   f"per-query cost is flat in the slice size (every query "
+                                   f"scans the whole bank), so the bounded sample measures the "
+                                   f"same rate")}
 
     def barrier():
         if world > 1:
@@ -262,6 +272,24 @@ def run_ours(a, rank, world, local_rank):
     barrier()
     ms_e2e = max_over_ranks(e0.elapsed_time(e1))
 
+    # N > 1: the bank-sharded partitions of north_star (per-shard top-k -> NCCL exchange -> merge),
+    # one warm + one timed step each, beside the partition the headline uses
+    exchange_ab = None
+    if world > 1 and not a.no_exchange_ab:
+        exchange_ab = {}
+        for ex in ("lists", "all_to_all", "all_gather"):
+            try:
+                xb.relabel_apt_reward(rep, args, rms=rms, exchange=ex, mode="screened")
+                barrier()
+                e0.record()
+                xb.relabel_apt_reward(rep, args, rms=rms, exchange=ex, mode="screened")
+                e1.record()
+                barrier()
+                exchange_ab[ex] = max_over_ranks(e0.elapsed_time(e1))
+            except Exception as e:          # keep the headline line even if one form fails
+                exchange_ab[ex] = f"failed: {type(e).__name__}: {e}"[:200]
+                barrier()
+
     if a.stage_times:
         from exorl_b200.relabel import StageTimer
         tmr = StageTimer()
@@ -270,6 +298,17 @@ def run_ours(a, rank, world, local_rank):
         if rank == 0:
             print("stage times (ms): " + json.dumps({k: round(v, 3) for k, v in st.items()}),
                   file=sys.stderr)
+
+    secondary = None
+    if world == 1 and not a.no_secondary:
+        # BASELINE configs 1-4 (per-update latencies, replay gather GB/s), each with its own
+        # clock record; the C5 tensors are released first (C4 holds a 63.6 GB pixel buffer)
+        del rep
+        torch.cuda.empty_cache()
+        from benchmarks import secondary as sec
+        torch.set_num_threads(os.cpu_count() or 1)
+        secondary = sec.run_all(dev, lambda: ClockSampler(dev.index),
+                                cpu=not a.no_cpu_baseline)
 
     if rank == 0:
         sustained, burst, src = peaks()
@@ -310,6 +349,11 @@ def run_ours(a, rank, world, local_rank):
                          **screen_traffic(a.n, nb_local, a.dim)},
             "cpu_baseline": cpu_baseline,
         }
+        if exchange_ab is not None:
+            out["exchange_ab"] = {"unit": "ms per step (one timed step each, max over ranks)",
+                                  "headline_exchange": a.exchange, **exchange_ab}
+        if secondary is not None:
+            out["secondary"] = secondary
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

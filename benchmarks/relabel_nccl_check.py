@@ -36,7 +36,7 @@ def main():
     # single-shard truth on this rank's GPU (no collectives involved)
     d0, i0 = knn_topk(rep, rep, a.k, mode="screened")
     rms0 = xb.RMS(dev)
-    r0 = _reward_from_knn(d0, a.k, True, True, 0.0, rms0)
+    r0 = _reward_from_knn(d0, a.k, True, True, 0.0, rms0.M, rms0.S, rms0._n)
 
     ok = True
     # "prepared": the same set handed over as a PreparedRep (exb_knn_prep_f16 here; the rep

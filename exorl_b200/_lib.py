@@ -59,15 +59,15 @@ SIGNATURES = {
     "exb_topk_merge": (_c.c_int, [_vp, _vp, _c.c_int, _i64, _c.c_int, _vp, _vp, _vp]),
     "exb_pbe_workspace_bytes": (_sz, [_i64, _c.c_int]),
     "exb_pbe_workspace_init": (_c.c_int, [_vp, _sz, _vp]),
-    "exb_pbe_reward": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _c.c_int, _f32, _vp, _vp, _f64,
-                                  _vp, _vp, _vp, _vp, _sz, _vp]),
+    "exb_pbe_reward": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _c.c_int, _f32, _vp, _vp, _vp,
+                                  _vp, _vp, _sz, _vp]),
     "exb_pbe_moments": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _vp, _vp, _sz, _vp]),
     "exb_pbe_finish": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _c.c_int, _f32, _vp, _vp, _vp,
-                                  _f64, _vp, _vp, _vp, _vp]),
+                                  _vp, _vp, _vp]),
     "exb_apt_reward_workspace_bytes": (_sz, [_i64, _i64, _c.c_int, _c.c_int]),
     "exb_apt_reward_f32": (_c.c_int, [_vp, _i64, _vp, _i64, _c.c_int, _c.c_int, _c.c_int, _c.c_int,
-                                      _c.c_int, _c.c_int, _f32, _vp, _vp, _f64, _vp, _vp, _vp, _vp,
-                                      _vp, _vp, _sz, _vp]),
+                                      _c.c_int, _c.c_int, _f32, _vp, _vp, _vp, _vp, _vp, _vp,
+                                      _vp, _sz, _vp]),
     "exb_rep_trunk_smem_bytes": (_sz, [_c.c_int, _c.c_int]),
     "exb_rep_trunk_f32": (_c.c_int, [_vp, _i64, _c.c_int, _vp, _vp, _vp, _vp, _f32, _c.c_int,
                                      _vp, _op_p, _vp]),
@@ -76,11 +76,11 @@ SIGNATURES = {
     "exb_knn_screened_pre_f32": (_c.c_int, [_vp, _i64, _op_p, _vp, _i64, _op_p, _c.c_int,
                                             _c.c_int, _i32, _vp, _vp, _vp, _sz, _vp]),
     "exb_apt_reward_pre_f32": (_c.c_int, [_vp, _i64, _op_p, _vp, _i64, _op_p, _c.c_int, _c.c_int,
-                                          _c.c_int, _c.c_int, _f32, _vp, _vp, _f64, _vp, _vp,
-                                          _vp, _vp, _vp, _vp, _sz, _vp]),
-    "exb_rms_update": (_c.c_int, [_vp, _i64, _vp, _vp, _f64, _vp, _vp, _vp, _sz, _vp]),
-    "exb_rnd_reward_f32": (_c.c_int, [_vp, _vp, _i64, _c.c_int, _f32, _vp, _vp, _f64, _vp, _vp,
-                                      _vp, _vp, _vp, _sz, _vp]),
+                                          _c.c_int, _c.c_int, _f32, _vp, _vp, _vp, _vp, _vp,
+                                          _vp, _vp, _sz, _vp]),
+    "exb_rms_update": (_c.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "exb_rnd_reward_f32": (_c.c_int, [_vp, _vp, _i64, _c.c_int, _f32, _vp, _vp, _vp, _vp, _vp,
+                                      _vp, _sz, _vp]),
     "exb_take_kth": (_c.c_int, [_vp, _i64, _c.c_int, _vp, _vp]),
     "exb_replay_gather": (_c.c_int, [_vp, _i64, _c.POINTER(GatherCol), _c.c_int, _vp, _vp,
                                      _c.c_int, _c.c_int, _f32, _vp, _vp, _vp]),

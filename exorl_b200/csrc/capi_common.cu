@@ -23,7 +23,7 @@ int sm_count() {
 }
 }  // namespace exb
 
-extern "C" int exb_abi_version(void) { return 1; }
+extern "C" int exb_abi_version(void) { return 2; }
 extern "C" const char* exb_last_error(void) { return exb::g_err; }
 extern "C" int exb_device_info(int* sms, int* cc) {
   int dev = 0, n = 0, maj = 0, min = 0;

@@ -1428,7 +1428,7 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
     EXB_LAUNCH_CHECK();
     if (pbe && pbe->use_rms)
       return launch_pbe_finish(out_dist, nq, k, pbe->avg, 1, pbe->use_clip, pbe->clip,
-                               pbe->rms.m_out, pbe->out_reward, st);
+                               pbe->rms.m, pbe->out_reward, st);
     return EXB_OK;
   }
 
@@ -1744,8 +1744,7 @@ extern "C" size_t exb_apt_reward_workspace_bytes(int64_t nq, int64_t nb, int dim
 
 static int apt_reward_impl(const float* src, int64_t nq, const float* bank, int64_t nb,
                            int dim, int k, int src_is_bank, int mode, int avg, int use_rms,
-                           float clip, const float* rms_m_in, const float* rms_s_in,
-                           double rms_n, float* rms_m_out, float* rms_s_out,
+                           float clip, float* rms_m, float* rms_s, double* rms_n,
                            float* out_reward, float* out_dist, int32_t* out_idx,
                            void* workspace, size_t workspace_bytes, exb_stream_t stream,
                            const exb_operand* pre_q, const exb_operand* pre_b) {
@@ -1753,7 +1752,7 @@ static int apt_reward_impl(const float* src, int64_t nq, const float* bank, int6
   EXB_CHECK_ARG(nq > 0 && nb > 0 && dim > 0, "empty input");
   EXB_CHECK_ARG(k >= 1 && k <= EXB_MAX_K, "k=%d outside [1,%d]", k, EXB_MAX_K);
   EXB_CHECK_ARG(mode >= 0 && mode <= 2, "mode must be 0 (auto), 1 (exact) or 2 (screened)");
-  EXB_CHECK_ARG(!use_rms || (rms_m_in && rms_s_in && rms_m_out && rms_s_out),
+  EXB_CHECK_ARG(!use_rms || (rms_m && rms_s && rms_n),
                 "use_rms needs the RMS state pointers");
   if (k > nb) {
     set_error("selected index k out of range (k=%d > bank rows=%lld)", k, (long long)nb);
@@ -1775,7 +1774,7 @@ static int apt_reward_impl(const float* src, int64_t nq, const float* bank, int6
   if (screen) {
     FusedPbe f;
     f.on = 1; f.avg = avg; f.use_rms = use_rms; f.use_clip = clip >= 0.0f; f.clip = clip;
-    f.rms = RmsParams{rms_m_in, rms_s_in, rms_n, rms_m_out, rms_s_out};
+    f.rms = RmsParams{rms_m, rms_s, rms_n};
     f.out_reward = out_reward; f.partials = nullptr;
     bool fused = false;
     rc = screened_impl(src, nq, bank, nb, dim, k, 0, src_is_bank, out_dist, out_idx, workspace,
@@ -1786,26 +1785,23 @@ static int apt_reward_impl(const float* src, int64_t nq, const float* bank, int6
                            stream);
     if (rc) return rc;
   }
-  return exb_pbe_reward(out_dist, nq, k, avg, use_rms, clip, rms_m_in, rms_s_in, rms_n, rms_m_out,
-                        rms_s_out, out_reward, pbe_ws, pbe_bytes, stream);
+  return exb_pbe_reward(out_dist, nq, k, avg, use_rms, clip, rms_m, rms_s, rms_n, out_reward, pbe_ws, pbe_bytes, stream);
 }
 
 extern "C" int exb_apt_reward_f32(const float* src, int64_t nq, const float* bank, int64_t nb,
                                   int dim, int k, int src_is_bank, int mode, int avg, int use_rms,
-                                  float clip, const float* rms_m_in, const float* rms_s_in,
-                                  double rms_n, float* rms_m_out, float* rms_s_out,
+                                  float clip, float* rms_m, float* rms_s, double* rms_n,
                                   float* out_reward, float* out_dist, int32_t* out_idx,
                                   void* workspace, size_t workspace_bytes, exb_stream_t stream) {
   return apt_reward_impl(src, nq, bank, nb, dim, k, src_is_bank, mode, avg, use_rms, clip,
-                         rms_m_in, rms_s_in, rms_n, rms_m_out, rms_s_out, out_reward, out_dist,
+                         rms_m, rms_s, rms_n, out_reward, out_dist,
                          out_idx, workspace, workspace_bytes, stream, nullptr, nullptr);
 }
 
 extern "C" int exb_apt_reward_pre_f32(const float* src, int64_t nq, const exb_operand* src_op,
                                       const float* bank, int64_t nb, const exb_operand* bank_op,
                                       int dim, int k, int avg, int use_rms, float clip,
-                                      const float* rms_m_in, const float* rms_s_in, double rms_n,
-                                      float* rms_m_out, float* rms_s_out, float* out_reward,
+                                      float* rms_m, float* rms_s, double* rms_n, float* out_reward,
                                       float* out_dist, int32_t* out_idx, void* workspace,
                                       size_t workspace_bytes, exb_stream_t stream) {
   EXB_CHECK_ARG(bank_op && bank_op->f16 && bank_op->half_norm && bank_op->round_err &&
@@ -1817,8 +1813,7 @@ extern "C" int exb_apt_reward_pre_f32(const float* src, int64_t nq, const exb_op
                   src_op->scalars, "src_op missing (src is not the bank)");
   EXB_CHECK_ARG((((uintptr_t)bank_op->f16 | (uintptr_t)(same ? bank_op : src_op)->f16) & 127) == 0,
                 "prepared fp16 operands must be 128-byte aligned (TMA)");
-  return apt_reward_impl(src, nq, bank, nb, dim, k, same ? 1 : 0, 2, avg, use_rms, clip, rms_m_in,
-                         rms_s_in, rms_n, rms_m_out, rms_s_out, out_reward, out_dist, out_idx,
+  return apt_reward_impl(src, nq, bank, nb, dim, k, same ? 1 : 0, 2, avg, use_rms, clip, rms_m, rms_s, rms_n, out_reward, out_dist, out_idx,
                          workspace, workspace_bytes, stream, same ? bank_op : src_op, bank_op);
 }
 

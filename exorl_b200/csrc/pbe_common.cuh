@@ -8,12 +8,12 @@ namespace exb {
 
 constexpr int PBE_THREADS = 256;
 
+// The running-moment state of the reference's RMS object, resident on the device and updated in
+// place: M and S are the fp32 (1,) tensors RMS.M / RMS.S, n is RMS.n as one fp64 word.
 struct RmsParams {
-  const float* m_in;
-  const float* s_in;
-  double n;
-  float* m_out;
-  float* s_out;
+  float* m;
+  float* s;
+  double* n;
 };
 
 // values entering the moments: avg -> all nq*k, else column k-1 of each row
@@ -49,7 +49,7 @@ __device__ __forceinline__ double2 block_sum2(double2 v, double2* smem) {
 // utils/utils.py:264-276 on scalars.  sums = {count, sum, sumsq}.
 __device__ __forceinline__ void rms_apply(const double* sums, const RmsParams& p) {
   const double bs = sums[0], sum = sums[1], sumsq = sums[2];
-  const double M = (double)*p.m_in, S = (double)*p.s_in, n = p.n;
+  const double M = (double)*p.m, S = (double)*p.s, n = *p.n;
   const double mean = sum / bs;
   // torch.var(unbiased): NaN for a single element, like the reference.
   const double var = (bs > 1.0) ? fmax(sumsq - sum * mean, 0.0) / (bs - 1.0) : (double)NAN;
@@ -57,8 +57,9 @@ __device__ __forceinline__ void rms_apply(const double* sums, const RmsParams& p
   const double delta = mean - M;
   const double new_m = M + delta * bs / tot;
   const double new_s = (S * n + var * bs + delta * delta * n * bs / tot) / tot;
-  *p.m_out = (float)new_m;
-  *p.s_out = (float)new_s;
+  *p.m = (float)new_m;
+  *p.s = (float)new_s;
+  *p.n = tot;       // utils/utils.py:274
 }
 
 // torch.maximum(t, 0) propagates NaN (0/0 when every distance is 0, e.g. k = 1 on source =

@@ -5,8 +5,10 @@
 // mean over k, log(1 + r)), which the reference runs as ~25 launch-bound ATen kernels.
 //
 // State convention (include/exorl_b200.h): M and S are the fp32 (1,) tensors the reference
-// exposes, n is the python float passed by value.  Sums are accumulated in fp64 and the updated
-// M, S are rounded to fp32, like the reference's fp32 tensors.
+// exposes, n is the reference's python float held as one fp64 word on the device; all three are
+// updated in place (n += count, utils/utils.py:274), so a call has no by-value argument that
+// changes from step to step and can be replayed from a CUDA graph.  Sums are accumulated in fp64
+// and the updated M, S are rounded to fp32, like the reference's fp32 tensors.
 #include "common.cuh"
 #include "pbe_common.cuh"
 #include <math.h>
@@ -96,7 +98,7 @@ pbe_small_kernel(const float* __restrict__ dist, int64_t nq, int k, int avg, int
     }
     __syncthreads();
   }
-  const float m = use_rms ? *p.m_out : 1.0f;
+  const float m = use_rms ? *p.m : 1.0f;
   for (int64_t i = threadIdx.x; i < nq; i += PBE_SMALL_THREADS)
     out[i] = pbe_row(dist + i * k, k, avg, use_rms ? 1.f : 0.f, m, use_clip, clip);
 }
@@ -175,15 +177,14 @@ extern "C" int exb_pbe_workspace_init(void* workspace, size_t workspace_bytes,
 }
 
 extern "C" int exb_pbe_reward(const float* knn_dist, int64_t nq, int k, int avg, int use_rms,
-                              float clip, const float* rms_m_in, const float* rms_s_in,
-                              double rms_n, float* rms_m_out, float* rms_s_out,
+                              float clip, float* rms_m, float* rms_s, double* rms_n,
                               float* out_reward, void* workspace, size_t workspace_bytes,
                               exb_stream_t stream) {
   EXB_CHECK_ARG(knn_dist && out_reward && nq > 0 && k >= 1, "bad arguments");
-  EXB_CHECK_ARG(!use_rms || (rms_m_in && rms_s_in && rms_m_out && rms_s_out),
+  EXB_CHECK_ARG(!use_rms || (rms_m && rms_s && rms_n),
                 "use_rms needs the RMS state pointers");
   cudaStream_t st = (cudaStream_t)stream;
-  RmsParams p{rms_m_in, rms_s_in, rms_n, rms_m_out, rms_s_out};
+  RmsParams p{rms_m, rms_s, rms_n};
   const int use_clip = clip >= 0.0f;
   const int64_t count = avg ? nq * k : nq;
   if (nq * k <= PBE_SMALL_LIMIT) {
@@ -201,7 +202,7 @@ extern "C" int exb_pbe_reward(const float* knn_dist, int64_t nq, int k, int avg,
     EXB_LAUNCH_CHECK();
   }
   pbe_finish_kernel<<<(unsigned)((nq + PBE_THREADS - 1) / PBE_THREADS), PBE_THREADS, 0, st>>>(
-      knn_dist, nq, k, avg, use_rms, use_clip, clip, rms_m_out, out_reward);
+      knn_dist, nq, k, avg, use_rms, use_clip, clip, rms_m, out_reward);
   EXB_LAUNCH_CHECK();
   return EXB_OK;
 }
@@ -214,7 +215,7 @@ extern "C" int exb_pbe_moments(const float* knn_dist, int64_t nq, int k, int avg
   int rc = carve_pbe(workspace, workspace_bytes, &w);
   if (rc) return rc;
   const int64_t count = avg ? nq * k : nq;
-  RmsParams p{nullptr, nullptr, 0.0, nullptr, nullptr};
+  RmsParams p{nullptr, nullptr, nullptr};
   pbe_moments_kernel<<<moments_blocks(count), PBE_THREADS, 0, (cudaStream_t)stream>>>(
       knn_dist, count, k, avg, w.partials, w.ticket, out_sums, 0, p);
   EXB_LAUNCH_CHECK();
@@ -222,33 +223,29 @@ extern "C" int exb_pbe_moments(const float* knn_dist, int64_t nq, int k, int avg
 }
 
 extern "C" int exb_pbe_finish(const float* knn_dist, int64_t nq, int k, int avg, int use_rms,
-                              float clip, const double* sums, const float* rms_m_in,
-                              const float* rms_s_in, double rms_n, float* rms_m_out,
-                              float* rms_s_out, float* out_reward, exb_stream_t stream) {
+                              float clip, const double* sums, float* rms_m, float* rms_s, double* rms_n, float* out_reward, exb_stream_t stream) {
   EXB_CHECK_ARG(knn_dist && out_reward && nq > 0 && k >= 1, "bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
   if (use_rms) {
-    EXB_CHECK_ARG(sums && rms_m_in && rms_s_in && rms_m_out && rms_s_out,
+    EXB_CHECK_ARG(sums && rms_m && rms_s && rms_n,
                   "use_rms needs sums and the RMS state pointers");
-    RmsParams p{rms_m_in, rms_s_in, rms_n, rms_m_out, rms_s_out};
+    RmsParams p{rms_m, rms_s, rms_n};
     rms_apply_kernel<<<1, 32, 0, st>>>(sums, p);
     EXB_LAUNCH_CHECK();
   }
   pbe_finish_kernel<<<(unsigned)((nq + PBE_THREADS - 1) / PBE_THREADS), PBE_THREADS, 0, st>>>(
-      knn_dist, nq, k, avg, use_rms, clip >= 0.0f, clip, rms_m_out, out_reward);
+      knn_dist, nq, k, avg, use_rms, clip >= 0.0f, clip, rms_m, out_reward);
   EXB_LAUNCH_CHECK();
   return EXB_OK;
 }
 
-extern "C" int exb_rms_update(const float* x, int64_t n, const float* rms_m_in,
-                              const float* rms_s_in, double rms_n, float* rms_m_out,
-                              float* rms_s_out, void* workspace, size_t workspace_bytes,
+extern "C" int exb_rms_update(const float* x, int64_t n, float* rms_m, float* rms_s, double* rms_n, void* workspace, size_t workspace_bytes,
                               exb_stream_t stream) {
-  EXB_CHECK_ARG(x && n > 0 && rms_m_in && rms_s_in && rms_m_out && rms_s_out, "bad arguments");
+  EXB_CHECK_ARG(x && n > 0 && rms_m && rms_s && rms_n, "bad arguments");
   PbeWs w;
   int rc = carve_pbe(workspace, workspace_bytes, &w);
   if (rc) return rc;
-  RmsParams p{rms_m_in, rms_s_in, rms_n, rms_m_out, rms_s_out};
+  RmsParams p{rms_m, rms_s, rms_n};
   pbe_moments_kernel<<<moments_blocks(n), PBE_THREADS, 0, (cudaStream_t)stream>>>(
       x, n, 1, 1, w.partials, w.ticket, w.sums, 1, p);
   EXB_LAUNCH_CHECK();
@@ -352,25 +349,23 @@ __global__ void rnd_scale_kernel(const float* __restrict__ err, int64_t n, float
 }  // namespace exb
 
 extern "C" int exb_rnd_reward_f32(const float* prediction, const float* target, int64_t n,
-                                  int dim, float scale, const float* rms_m_in,
-                                  const float* rms_s_in, double rms_n, float* rms_m_out,
-                                  float* rms_s_out, float* out_error, float* out_reward,
+                                  int dim, float scale, float* rms_m, float* rms_s, double* rms_n, float* out_error, float* out_reward,
                                   void* workspace, size_t workspace_bytes, exb_stream_t stream) {
   EXB_CHECK_ARG(prediction && target && out_error && out_reward && n > 0 && dim > 0,
                 "bad arguments");
-  EXB_CHECK_ARG(rms_m_in && rms_s_in && rms_m_out && rms_s_out, "RMS state pointers missing");
+  EXB_CHECK_ARG(rms_m && rms_s && rms_n, "RMS state pointers missing");
   PbeWs w;
   int rc = carve_pbe(workspace, workspace_bytes, &w);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  RmsParams p{rms_m_in, rms_s_in, rms_n, rms_m_out, rms_s_out};
+  RmsParams p{rms_m, rms_s, rms_n};
   int64_t blocks = (n + PBE_THREADS / 32 - 1) / (PBE_THREADS / 32);
   const int64_t cap = 4LL * sm_count();
   if (blocks > cap) blocks = cap;
   rnd_error_moments_kernel<<<(unsigned)blocks, PBE_THREADS, 0, st>>>(
       prediction, target, n, dim, out_error, w.partials, w.ticket, w.sums, p);
   EXB_LAUNCH_CHECK();
-  rnd_scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out_error, n, scale, rms_s_out,
+  rnd_scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out_error, n, scale, rms_s,
                                                                out_reward);
   EXB_LAUNCH_CHECK();
   return EXB_OK;

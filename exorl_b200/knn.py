@@ -12,6 +12,7 @@ import ctypes
 import torch
 
 from . import _lib
+from . import ops  # noqa: F401  (registers torch.ops.exorl_b200.*)
 
 _MODES = ("auto", "exact", "screened")
 
@@ -46,44 +47,68 @@ def knn_topk(source, target, k, idx_base=0, mode="auto"):
     "selected index k out of range" when k > b2 like the reference's topk.
     mode: "exact" = fp32 CUDA-core kernel; "screened" = tcgen05 fp16 screening + exact fp32
     recompute of the survivors (same results); "auto" picks by shape.
-    """
+    Thin caller of torch.ops.exorl_b200.knn_topk (ops.py)."""
     if mode not in _MODES:
         raise ValueError(f"mode must be one of {_MODES}")
-    lib = _lib.load()
     same = target is source
     pre_s, pre_t = _prepared_pair(source, target)
     if pre_s is not None:
-        source, target = pre_s.rep, pre_t.rep
+        return _knn_topk_prepared(pre_s, pre_t, int(k), idx_base, mode)
     src = _as_rows(source, "source")
     tgt = src if same else _as_rows(target, "target")
+    _check_pair(src, tgt, int(k))
+    return ops.call(torch.ops.exorl_b200.knn_topk, _knn_topk_impl, src, tgt, int(k),
+                    int(idx_base), mode, same)
+
+
+def _check_pair(src, tgt, k):
     if src.size(1) != tgt.size(1):
         raise RuntimeError(f"feature sizes differ: {src.size(1)} vs {tgt.size(1)}")
     if src.device != tgt.device:
         raise RuntimeError("source and target must be on the same device")
-    k = int(k)
-    nq, nb, dim = src.size(0), tgt.size(0), src.size(1)
-    if k > nb:
+    if k > tgt.size(0):
         raise RuntimeError("selected index k out of range")
     if k < 1 or k > _lib.MAX_K:
         raise ValueError(f"exorl_b200: knn_k={k} outside [1, {_lib.MAX_K}]")
+
+
+def _knn_topk_prepared(pre_s, pre_t, k, idx_base, mode):
+    """knn_topk on operands a rep producer already prepared (rep.PreparedRep)."""
+    lib = _lib.load()
+    if mode == "exact":
+        raise ValueError("exorl_b200: a PreparedRep is consumed by the screened path")
+    src, tgt = _as_rows(pre_s.rep, "source"), _as_rows(pre_t.rep, "target")
+    _check_pair(src, tgt, k)
+    nq, nb, dim = src.size(0), tgt.size(0), src.size(1)
     dev = src.device
     with torch.cuda.device(dev):
         dist = torch.empty(nq, k, dtype=torch.float32, device=dev)
         idx = torch.empty(nq, k, dtype=torch.int32, device=dev)
         if nq == 0:
             return dist, idx
-        if pre_s is not None:
-            if mode == "exact":
-                raise ValueError("exorl_b200: a PreparedRep is consumed by the screened path")
-            need = lib.exb_knn_screened_workspace_bytes(nq, nb, dim, k)
-            if need == 0:
-                raise ValueError(f"exorl_b200: screened kNN does not support dim={dim}, k={k}")
-            ws, _ = _lib.Workspace.get(dev, "knn_screened", need)
-            _lib.check(lib.exb_knn_screened_pre_f32(
-                _lib.ptr(src), nq, pre_s.operand, _lib.ptr(tgt), nb, pre_t.operand, dim, k,
-                int(idx_base), _lib.ptr(dist), _lib.ptr(idx), _lib.ptr(ws), ws.numel(),
-                _lib.stream_ptr(dev)))
-            _repair_overflow_rows(src, tgt, k, idx_base, dist, idx, "knn_screened")
+        need = lib.exb_knn_screened_workspace_bytes(nq, nb, dim, k)
+        if need == 0:
+            raise ValueError(f"exorl_b200: screened kNN does not support dim={dim}, k={k}")
+        ws, _ = _lib.Workspace.get(dev, "knn_screened", need)
+        _lib.check(lib.exb_knn_screened_pre_f32(
+            _lib.ptr(src), nq, pre_s.operand, _lib.ptr(tgt), nb, pre_t.operand, dim, k,
+            int(idx_base), _lib.ptr(dist), _lib.ptr(idx), _lib.ptr(ws), ws.numel(),
+            _lib.stream_ptr(dev)))
+        _repair_overflow_rows(src, tgt, k, idx_base, dist, idx, "knn_screened")
+    return dist, idx
+
+
+def _knn_topk_impl(src, tgt, k, idx_base, mode, same):
+    """CUDA implementation of torch.ops.exorl_b200.knn_topk: contiguous fp32 (b, c) rows in."""
+    lib = _lib.load()
+    if same:
+        tgt = src
+    nq, nb, dim = src.size(0), tgt.size(0), src.size(1)
+    dev = src.device
+    with torch.cuda.device(dev):
+        dist = torch.empty(nq, k, dtype=torch.float32, device=dev)
+        idx = torch.empty(nq, k, dtype=torch.int32, device=dev)
+        if nq == 0:
             return dist, idx
         use_screen = mode == "screened" or (mode == "auto" and _screen_ok(nq, nb, dim, k))
         if use_screen:
@@ -288,66 +313,88 @@ def _pbe_ws(dev):
 class RMS(object):
     """running mean and std — drop-in for utils/utils.py:257-276.
 
-    M and S are tensors on `device`, n is a python float; the object is a plain picklable
-    Python object (snapshots pickle the whole agent)."""
+    M and S are tensors on `device`; `n` reads as the reference's python float.  Its value is
+    held in one fp64 word on the device (`_n`) next to M and S, and all three are updated IN
+    PLACE by the kernels: an update has no host-side value that changes from call to call, so it
+    can sit inside a `torch.compile`d graph or a CUDA graph.  Reading `.n` copies the word back
+    (a sync; logging and pickling only — the hot path never reads it).  The object pickles as
+    {M, S, n} (snapshots pickle the whole agent)."""
 
     def __init__(self, device, epsilon=1e-4, shape=(1,)):
         self.M = torch.zeros(shape).to(device)
         self.S = torch.ones(shape).to(device)
-        self.n = epsilon
+        self._n = torch.full((1,), epsilon, dtype=torch.float64).to(device)
+
+    @property
+    def n(self):
+        return float(self._n.item())
+
+    @n.setter
+    def n(self, value):
+        self._n.fill_(float(value))
+
+    def __getstate__(self):
+        return {"M": self.M, "S": self.S, "n": self.n}
+
+    def __setstate__(self, state):
+        self.M, self.S = state["M"], state["S"]
+        self._n = torch.full((1,), state["n"], dtype=torch.float64, device=self.M.device)
 
     def __call__(self, x):
         bs = x.size(0)
         if (self.M.numel() == 1 and x.is_cuda and x.dtype == torch.float32
                 and x.numel() == bs and self.M.is_cuda):
-            lib = _lib.load()
-            dev = x.device
-            xc = x.detach().reshape(-1).contiguous()
-            new_m = torch.empty_like(self.M)
-            new_s = torch.empty_like(self.S)
-            with torch.cuda.device(dev):
-                ws = _pbe_ws(dev)
-                _lib.check(lib.exb_rms_update(
-                    _lib.ptr(xc), bs, _lib.ptr(self.M), _lib.ptr(self.S), float(self.n),
-                    _lib.ptr(new_m), _lib.ptr(new_s), _lib.ptr(ws), ws.numel(),
-                    _lib.stream_ptr(dev)))
+            ops.call(torch.ops.exorl_b200.rms_update, _rms_update_impl,
+                     x.detach().reshape(-1).contiguous(), self.M, self.S, self._n)
         else:
-            # general-shape states (not on the kNN path): same formula with device torch ops
+            # general-shape states (not on the kNN path): same formula with torch ops on
+            # whatever device the state lives on
+            n = self.n
             delta = torch.mean(x, dim=0) - self.M
-            new_m = self.M + delta * bs / (self.n + bs)
-            new_s = (self.S * self.n + torch.var(x, dim=0) * bs
-                     + torch.square(delta) * self.n * bs / (self.n + bs)) / (self.n + bs)
-        self.M = new_m
-        self.S = new_s
-        self.n += bs
+            new_m = self.M + delta * bs / (n + bs)
+            new_s = (self.S * n + torch.var(x, dim=0) * bs
+                     + torch.square(delta) * n * bs / (n + bs)) / (n + bs)
+            self.M = new_m
+            self.S = new_s
+            self._n += bs
         return self.M, self.S
 
 
-def _reward_from_knn(dist, k, knn_avg, knn_rms, knn_clip, rms):
+def _rms_update_impl(x, rms_m, rms_s, rms_n):
+    lib = _lib.load()
+    dev = x.device
+    with torch.cuda.device(dev):
+        ws = _pbe_ws(dev)
+        _lib.check(lib.exb_rms_update(_lib.ptr(x), x.numel(), _lib.ptr(rms_m), _lib.ptr(rms_s),
+                                      _lib.ptr(rms_n), _lib.ptr(ws), ws.numel(),
+                                      _lib.stream_ptr(dev)))
+
+
+def _check_rms(rms):
+    if rms is None:
+        raise ValueError("knn_rms=True needs an RMS state object")
+    if rms.M.numel() != 1 or not rms.M.is_cuda:
+        raise ValueError("the RMS state used by PBE must have shape (1,) on the GPU")
+
+
+def _rms_ptrs(knn_rms, rms_m, rms_s, rms_n):
+    if not knn_rms:
+        return (None, None, None)
+    return (_lib.ptr(rms_m), _lib.ptr(rms_s), _lib.ptr(rms_n))
+
+
+def _reward_from_knn(dist, k, knn_avg, knn_rms, knn_clip, rms_m, rms_s, rms_n):
+    """RMS update + PBE epilogue on (nq, k) distances; the state tensors are updated in place."""
     lib = _lib.load()
     dev = dist.device
     nq = dist.size(0)
     out = torch.empty(nq, 1, dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
         ws = _pbe_ws(dev)
-        if knn_rms:
-            if rms is None:
-                raise ValueError("knn_rms=True needs an RMS state object")
-            if rms.M.numel() != 1 or not rms.M.is_cuda:
-                raise ValueError("the RMS state used by PBE must have shape (1,) on the GPU")
-            new_m = torch.empty_like(rms.M)
-            new_s = torch.empty_like(rms.S)
-            args = (_lib.ptr(rms.M), _lib.ptr(rms.S), float(rms.n), _lib.ptr(new_m),
-                    _lib.ptr(new_s))
-        else:
-            args = (None, None, 0.0, None, None)
         _lib.check(lib.exb_pbe_reward(
             _lib.ptr(dist), nq, k, int(bool(knn_avg)), int(bool(knn_rms)), float(knn_clip),
-            *args, _lib.ptr(out), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
-    if knn_rms:
-        # utils/utils.py:272-274: rebind M, S and advance n by the number of values seen
-        rms.M, rms.S = new_m, new_s
-        rms.n += nq * k if knn_avg else nq
+            *_rms_ptrs(knn_rms, rms_m, rms_s, rms_n), _lib.ptr(out), _lib.ptr(ws), ws.numel(),
+            _lib.stream_ptr(dev)))
     return out
 
 
@@ -359,13 +406,13 @@ def compute_apt_reward(source, target, args, rms=None, mode="auto", return_knn=F
 
     `args` exposes knn_k, knn_avg, knn_rms, knn_clip (and optionally .rms); this is the
     signature the computation had before the reference folded it into PBE.__call__
-    (utils/utils.py:289-319, where source = target = rep).  One C call (exb_apt_reward_f32):
-    for per-update sizes a 3-launch chain prep -> tcgen05 screen -> rerank + RMS/epilogue."""
+    (utils/utils.py:289-319, where source = target = rep).  Thin caller of
+    torch.ops.exorl_b200.apt_reward: one C call (exb_apt_reward_f32), for per-update sizes a
+    short chain prep -> tcgen05 screen -> rerank + RMS/epilogue."""
     if mode not in _MODES:
         raise ValueError(f"mode must be one of {_MODES}")
     if rms is None:
         rms = getattr(args, "rms", None)
-    lib = _lib.load()
     k = int(args.knn_k)
     knn_avg, knn_rms, knn_clip = bool(args.knn_avg), bool(args.knn_rms), float(args.knn_clip)
     same = target is source
@@ -376,45 +423,51 @@ def compute_apt_reward(source, target, args, rms=None, mode="auto", return_knn=F
         source, target = pre_s.rep, pre_t.rep
     src = _as_rows(source, "source")
     tgt = src if same else _as_rows(target, "target")
-    if src.size(1) != tgt.size(1):
-        raise RuntimeError(f"feature sizes differ: {src.size(1)} vs {tgt.size(1)}")
-    if src.device != tgt.device:
-        raise RuntimeError("source and target must be on the same device")
-    nq, nb, dim = src.size(0), tgt.size(0), src.size(1)
-    if k > nb:
-        raise RuntimeError("selected index k out of range")
-    if k < 1 or k > _lib.MAX_K:
-        raise ValueError(f"exorl_b200: knn_k={k} outside [1, {_lib.MAX_K}]")
-    if mode == "screened" and (dim > _lib.SCREEN_MAX_DIM or k > _lib.SCREEN_MAX_K):
-        raise ValueError(f"exorl_b200: screened kNN does not support dim={dim}, k={k}")
-    dev = src.device
+    _check_pair(src, tgt, k)
+    if mode == "screened" and (src.size(1) > _lib.SCREEN_MAX_DIM or k > _lib.SCREEN_MAX_K):
+        raise ValueError(f"exorl_b200: screened kNN does not support dim={src.size(1)}, k={k}")
     if knn_rms:
-        if rms is None:
-            raise ValueError("knn_rms=True needs an RMS state object")
-        if rms.M.numel() != 1 or not rms.M.is_cuda:
-            raise ValueError("the RMS state used by PBE must have shape (1,) on the GPU")
+        _check_rms(rms)
+        m, s_, n = rms.M, rms.S, rms._n
+    else:
+        m, s_, n = src.new_empty(0), src.new_empty(0), src.new_empty(0)   # unused placeholders
+    if pre_s is not None:
+        out, dist, idx = _apt_reward_impl(src, tgt, m, s_, n, k, knn_avg, knn_rms, knn_clip,
+                                          mode, same, pre=(pre_s, pre_t))
+    else:
+        out, dist, idx = ops.call(torch.ops.exorl_b200.apt_reward, _apt_reward_impl, src, tgt,
+                                  m, s_, n, k, knn_avg, knn_rms, knn_clip, mode, same)
+    return (out, dist, idx) if return_knn else out
+
+
+def _apt_reward_impl(src, tgt, rms_m, rms_s, rms_n, k, knn_avg, knn_rms, knn_clip, mode, same,
+                     pre=None):
+    """CUDA implementation of torch.ops.exorl_b200.apt_reward (and, with `pre`, of the same call
+    on operands a rep producer prepared).  RMS state tensors are updated in place."""
+    lib = _lib.load()
+    if same:
+        tgt = src
+    pre_s, pre_t = pre if pre is not None else (None, None)
+    nq, nb, dim = src.size(0), tgt.size(0), src.size(1)
+    dev = src.device
     if nq > 0 and mode != "exact" and _streaming(nq, nb, dim, k):
         # dataset-scale input: kNN (with the host-side overflow check) then the epilogue; the
         # one-call fused chain below is for per-update sizes
-        a = pre_s if pre_s is not None else src
-        b = a if same else (pre_t if pre_s is not None else tgt)
-        d_, i_ = knn_topk(a, b, k, mode="screened")
-        out = _reward_from_knn(d_, k, knn_avg, knn_rms, knn_clip, rms)
-        return (out, d_, i_) if return_knn else out
+        if pre_s is not None:
+            d_, i_ = _knn_topk_prepared(pre_s, pre_t, k, 0, "screened")
+        else:
+            d_, i_ = _knn_topk_impl(src, tgt, k, 0, "screened", same)
+        out = _reward_from_knn(d_, k, knn_avg, knn_rms, knn_clip, rms_m, rms_s, rms_n)
+        return out, d_, i_
     with torch.cuda.device(dev):
         out = torch.empty(nq, 1, dtype=torch.float32, device=dev)
         dist = torch.empty(nq, k, dtype=torch.float32, device=dev)
         idx = torch.empty(nq, k, dtype=torch.int32, device=dev)
         if nq == 0:
-            return (out, dist, idx) if return_knn else out
+            return out, dist, idx
         need = lib.exb_apt_reward_workspace_bytes(nq, nb, dim, k)
         ws, _ = _lib.Workspace.get(dev, "apt_reward", need, zero_init=True)
-        if knn_rms:
-            new_m, new_s = torch.empty_like(rms.M), torch.empty_like(rms.S)
-            st = (_lib.ptr(rms.M), _lib.ptr(rms.S), float(rms.n), _lib.ptr(new_m),
-                  _lib.ptr(new_s))
-        else:
-            st = (None, None, 0.0, None, None)
+        st = _rms_ptrs(knn_rms, rms_m, rms_s, rms_n)
         if pre_s is not None:
             if dim > _lib.SCREEN_MAX_DIM or k > _lib.SCREEN_MAX_K:
                 raise ValueError(f"exorl_b200: screened kNN does not support dim={dim}, k={k}")
@@ -427,11 +480,7 @@ def compute_apt_reward(source, target, args, rms=None, mode="auto", return_knn=F
                 _lib.ptr(src), nq, _lib.ptr(tgt), nb, dim, k, int(same), _MODE_ID[mode],
                 int(knn_avg), int(knn_rms), knn_clip, *st, _lib.ptr(out), _lib.ptr(dist),
                 _lib.ptr(idx), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
-    if knn_rms:
-        # utils/utils.py:272-274: rebind M, S and advance n by the number of values seen
-        rms.M, rms.S = new_m, new_s
-        rms.n += nq * k if knn_avg else nq
-    return (out, dist, idx) if return_knn else out
+    return out, dist, idx
 
 
 class PBE(object):
@@ -456,10 +505,9 @@ def rnd_intr_reward(prediction, target, rms, rnd_scale=1.0):
     """RND reward from the predictor / target network outputs — replaces the arithmetic of
     RND.forward's last line (agents/unsupervised_learning/rnd.py:52-54) and of
     RNDAgent.compute_intr_reward (:94-99): prediction_error = mean((target - prediction)^2, -1),
-    `rms(prediction_error)` (state rebound and n advanced like utils/utils.py:272-274),
+    `rms(prediction_error)` (state M, S, n updated like utils/utils.py:272-274),
     reward = rnd_scale * prediction_error / (sqrt(var) + 1e-8).
-    Returns (reward (n, 1), prediction_error (n, 1))."""
-    lib = _lib.load()
+    Returns (reward (n, 1), prediction_error (n, 1)).  torch.ops.exorl_b200.rnd_reward."""
     pred = _as_rows(prediction, "prediction")
     tgt = _as_rows(target, "target")
     if pred.shape != tgt.shape:
@@ -467,6 +515,12 @@ def rnd_intr_reward(prediction, target, rms, rnd_scale=1.0):
                            f"tensor b {tuple(pred.shape)}")
     if rms.M.numel() != 1 or not rms.M.is_cuda:
         raise ValueError("the RMS state used by RND must have shape (1,) on the GPU")
+    return ops.call(torch.ops.exorl_b200.rnd_reward, _rnd_reward_impl, pred, tgt, rms.M, rms.S,
+                    rms._n, float(rnd_scale))
+
+
+def _rnd_reward_impl(pred, tgt, rms_m, rms_s, rms_n, rnd_scale):
+    lib = _lib.load()
     n, dim = pred.shape
     dev = pred.device
     with torch.cuda.device(dev):
@@ -474,14 +528,11 @@ def rnd_intr_reward(prediction, target, rms, rnd_scale=1.0):
         reward = torch.empty(n, 1, dtype=torch.float32, device=dev)
         if n == 0:
             return reward, err
-        new_m, new_s = torch.empty_like(rms.M), torch.empty_like(rms.S)
         ws = _pbe_ws(dev)
         _lib.check(lib.exb_rnd_reward_f32(
-            _lib.ptr(pred), _lib.ptr(tgt), n, dim, float(rnd_scale), _lib.ptr(rms.M),
-            _lib.ptr(rms.S), float(rms.n), _lib.ptr(new_m), _lib.ptr(new_s), _lib.ptr(err),
-            _lib.ptr(reward), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
-    rms.M, rms.S = new_m, new_s
-    rms.n += n
+            _lib.ptr(pred), _lib.ptr(tgt), n, dim, float(rnd_scale), _lib.ptr(rms_m),
+            _lib.ptr(rms_s), _lib.ptr(rms_n), _lib.ptr(err), _lib.ptr(reward), _lib.ptr(ws),
+            ws.numel(), _lib.stream_ptr(dev)))
     return reward, err
 
 
@@ -494,12 +545,31 @@ def proto_enqueue(queue, queue_ptr, z, candidates):
 
 def proto_knn_reward(z, queue, topk, mode="auto"):
     """Distance of every z row to its topk-th nearest queue row, (B, 1) — replaces
-    proto.py:115-118 (no RMS, no clip, no log)."""
+    proto.py:115-118 (no RMS, no clip, no log).  torch.ops.exorl_b200.proto_reward."""
+    if mode not in _MODES:
+        raise ValueError(f"mode must be one of {_MODES}")
+    pre_s, pre_t = _prepared_pair(z, queue)
+    if pre_s is not None:
+        dist, _ = _knn_topk_prepared(pre_s, pre_t, int(topk), 0, mode)
+        return _take_kth(dist, int(topk))
+    src = _as_rows(z, "z")
+    tgt = _as_rows(queue, "queue")
+    _check_pair(src, tgt, int(topk))
+    return ops.call(torch.ops.exorl_b200.proto_reward, _proto_reward_impl, src, tgt, int(topk),
+                    mode)
+
+
+def _take_kth(dist, k):
     lib = _lib.load()
-    k = int(topk)
-    dist, _ = knn_topk(z, queue, k, mode=mode)
     out = torch.empty(dist.size(0), 1, dtype=torch.float32, device=dist.device)
+    if dist.size(0) == 0:
+        return out
     with torch.cuda.device(dist.device):
         _lib.check(lib.exb_take_kth(_lib.ptr(dist), dist.size(0), k, _lib.ptr(out),
                                     _lib.stream_ptr(dist.device)))
     return out
+
+
+def _proto_reward_impl(z, queue, topk, mode):
+    dist, _ = _knn_topk_impl(z, queue, topk, 0, mode, False)
+    return _take_kth(dist, topk)

@@ -90,17 +90,11 @@ def _cuda_finish(knn_dist, k, avg, use_rms, clip, sums, rms):
     n = knn_dist.size(0)
     out = torch.empty(n, 1, dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
-        if use_rms:
-            new_m, new_s = torch.empty_like(rms.M), torch.empty_like(rms.S)
-            st = (_lib.ptr(rms.M), _lib.ptr(rms.S), float(rms.n), _lib.ptr(new_m),
-                  _lib.ptr(new_s))
-        else:
-            st = (None, None, 0.0, None, None)
+        # RMS state (M, S, n) is updated in place on the device from the combined sums
+        st = (_lib.ptr(rms.M), _lib.ptr(rms.S), _lib.ptr(rms._n)) if use_rms else (None,) * 3
         _lib.check(lib.exb_pbe_finish(_lib.ptr(knn_dist), n, k, int(avg), int(use_rms),
                                       float(clip), _lib.ptr(sums) if use_rms else None, *st,
                                       _lib.ptr(out), _lib.stream_ptr(dev)))
-    if use_rms:
-        rms.M, rms.S = new_m, new_s
     return out
 
 
@@ -138,7 +132,8 @@ class _CudaStages:
 
     @staticmethod
     def reward(knn_dist, k, avg, use_rms, clip, rms):
-        return _reward_from_knn(knn_dist, k, avg, use_rms, clip, rms)
+        st = (rms.M, rms.S, rms._n) if use_rms else (None,) * 3
+        return _reward_from_knn(knn_dist, k, avg, use_rms, clip, *st)
 
 
 def reps_from_host(rep_host, out=None, group=None):
@@ -195,9 +190,7 @@ def _finish_block(d_mine, i_mine, n, lo, hi, in_split, world, k, avg, use_rms, c
         dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
     tm("rms_allreduce")
     r_mine = stages.finish(d_mine, k, avg, use_rms, clip, sums, rms)
-    tm("finish")
-    if use_rms:
-        rms.n += n * k if avg else n
+    tm("finish")       # `finish` also advances rms.n by the global count (sums[0])
     # variable block sizes: gather padded to the largest block
     mx = max(in_split)
     pad = torch.zeros((mx, 1), dtype=r_mine.dtype, device=r_mine.device)

@@ -16,6 +16,7 @@ import torch
 
 from . import _lib
 from . import ingest
+from . import ops  # noqa: F401  (registers torch.ops.exorl_b200.*)
 from .residency import EpisodeStore
 
 _CORE = ("observation", "action", "reward", "discount")
@@ -215,19 +216,53 @@ class DeviceReplayBuffer(EpisodeStore):
 
     def sample_philox(self, batch, seed, call, offline=False, return_rows=False):
         """Index draw + gather as ONE kernel launch (exb_replay_sample): same result as
-        `gather(draw_rows_philox(batch, seed, call))`."""
-        lib = _lib.load()
+        `gather(draw_rows_philox(batch, seed, call))`.  Thin caller of
+        torch.ops.exorl_b200.replay_sample."""
         self._check_spans(offline)
-        eps, starts, lens = self._tables()
-        out, cols, n_cols, nstep = self._outputs(batch, offline)
-        rows = torch.empty(batch, dtype=torch.int64, device=self.device) if return_rows else None
-        with torch.cuda.device(self.device):
-            _lib.check(lib.exb_replay_sample(
-                ctypes.c_uint64(seed), ctypes.c_uint64(call), _lib.ptr(starts), _lib.ptr(lens),
-                len(eps), batch, cols, n_cols, _lib.ptr(self.cols["reward"]),
-                _lib.ptr(self.cols["discount"]), nstep, 0 if offline else 1, self.discount,
-                _lib.ptr(out[2]), _lib.ptr(out[3]), _lib.ptr(rows), _lib.stream_ptr(self.device)))
-        return (out, rows) if return_rows else out
+        _, starts, lens = self._tables()
+        nstep = 1 if offline else self.nstep
+        obs_src, act_src = self.cols["observation"], self.cols["action"]
+        if self.cols["reward"][0].numel() != 1 or self.cols["reward"].dtype != torch.float32:
+            raise ValueError("reward/discount columns must be float32 of shape (1,) per step")
+        metas = [] if offline else [self.cols[name] for name in self.meta_names]
+        cols = [obs_src, act_src, obs_src, *metas]
+        offsets = [-1, 0, nstep - 1] + [-1] * len(metas)
+        out = ops.call(
+            torch.ops.exorl_b200.replay_sample, _replay_sample_impl, cols, offsets, self.cols["reward"], self.cols["discount"], starts, lens, int(batch),
+            _as_i64(seed), _as_i64(call), nstep, 0 if offline else 1, self.discount)
+        obs, act, nobs = out[0], out[1], out[2]
+        rew, disc, rows = out[-3], out[-2], out[-1]
+        batch_out = (obs, act, rew, disc, nobs, *out[3:-3])
+        return (batch_out, rows) if return_rows else batch_out
+
+
+def _as_i64(v):
+    """64-bit seed / call counter as the signed int an op schema carries (two's complement)."""
+    v = int(v) & (2 ** 64 - 1)
+    return v - 2 ** 64 if v >= 2 ** 63 else v
+
+
+def _replay_sample_impl(columns, row_offsets, reward, discount, eps_start, eps_len, batch, seed,
+                        call, nstep, nstep_mode, gamma):
+    """CUDA implementation of torch.ops.exorl_b200.replay_sample: one exb_replay_sample launch."""
+    lib = _lib.load()
+    dev = reward.device
+    outs = [torch.empty((batch, *c.shape[1:]), dtype=c.dtype, device=dev) for c in columns]
+    rew = torch.empty((batch, *reward.shape[1:]), dtype=torch.float32, device=dev)
+    disc = torch.empty_like(rew)
+    rows = torch.empty(batch, dtype=torch.int64, device=dev)
+    cols = (_lib.GatherCol * len(columns))()
+    for c, src, dst, off in zip(cols, columns, outs, row_offsets):
+        c.src, c.dst = src.data_ptr(), dst.data_ptr()
+        c.row_bytes = src[0].numel() * src.element_size()
+        c.row_offset = int(off)
+    with torch.cuda.device(dev):
+        _lib.check(lib.exb_replay_sample(
+            ctypes.c_uint64(seed & (2 ** 64 - 1)), ctypes.c_uint64(call & (2 ** 64 - 1)),
+            _lib.ptr(eps_start), _lib.ptr(eps_len), eps_len.numel(), batch, cols, len(columns),
+            _lib.ptr(reward), _lib.ptr(discount), nstep, nstep_mode, gamma, _lib.ptr(rew),
+            _lib.ptr(disc), _lib.ptr(rows), _lib.stream_ptr(dev)))
+    return [*outs, rew, disc, rows]
 
 
 def _eps_idx_len(fn):

@@ -201,10 +201,11 @@ int exb_knn_rerank_lists_f32(const float* src, int64_t nq, const float* bank, in
  *   knn_dist [nq,k] ascending.  avg != 0: all nq*k values enter the running moments and the
  *   reward is the mean over k; avg == 0: column k-1 only.  use_rms: update state (M,S,n) then
  *   divide by the UPDATED mean.  clip >= 0: max(r - clip, 0).  reward = log(r + 1), [nq].
- *   RMS state: rms_m_in / rms_s_in are the fp32 (1,) tensors RMS.M / RMS.S on the device, rms_n
- *   is RMS.n (a python float in the reference, passed by value); the updated moments are written
- *   to rms_m_out / rms_s_out (may alias the inputs).  The caller advances n += count itself,
- *   like utils/utils.py:274.  When use_rms == 0 the state pointers may be NULL.
+ *   RMS state, all on the device and updated IN PLACE: rms_m / rms_s are the fp32 (1,) tensors
+ *   RMS.M / RMS.S, rms_n is RMS.n (a python float in the reference) as one fp64 word; a call
+ *   leaves M', S' and n + count (utils/utils.py:272-274) there.  No argument changes from one
+ *   update to the next, so the per-update chain can be replayed from a CUDA graph.  When
+ *   use_rms == 0 the state pointers may be NULL.
  * exb_pbe_moments exposes a shard's plain sums {count, sum, sum of squares} (fp64) so that ranks
  * can all-reduce(SUM) them before exb_pbe_finish; exb_pbe_reward does everything on one device.
  * The workspace carries a ticket word: zero it once with exb_pbe_workspace_init.
@@ -212,19 +213,16 @@ int exb_knn_rerank_lists_f32(const float* src, int64_t nq, const float* bank, in
 size_t exb_pbe_workspace_bytes(int64_t nq, int k);
 int exb_pbe_workspace_init(void* workspace, size_t workspace_bytes, exb_stream_t stream);
 int exb_pbe_reward(const float* knn_dist, int64_t nq, int k, int avg, int use_rms, float clip,
-                   const float* rms_m_in, const float* rms_s_in, double rms_n, float* rms_m_out,
-                   float* rms_s_out, float* out_reward /* [nq] */, void* workspace,
+                   float* rms_m, float* rms_s, double* rms_n, float* out_reward /* [nq] */, void* workspace,
                    size_t workspace_bytes, exb_stream_t stream);
 int exb_pbe_moments(const float* knn_dist, int64_t nq, int k, int avg,
                     double* out_sums /* device double[3] = count, sum, sumsq */, void* workspace,
                     size_t workspace_bytes, exb_stream_t stream);
 int exb_pbe_finish(const float* knn_dist, int64_t nq, int k, int avg, int use_rms, float clip,
                    const double* sums /* device double[3], already combined */,
-                   const float* rms_m_in, const float* rms_s_in, double rms_n, float* rms_m_out,
-                   float* rms_s_out, float* out_reward, exb_stream_t stream);
+                   float* rms_m, float* rms_s, double* rms_n, float* out_reward, exb_stream_t stream);
 /* RMS.__call__ on an (n, 1) fp32 column (utils/utils.py:264-276), e.g. for RND (rnd.py:96). */
-int exb_rms_update(const float* x, int64_t n, const float* rms_m_in, const float* rms_s_in,
-                   double rms_n, float* rms_m_out, float* rms_s_out, void* workspace,
+int exb_rms_update(const float* x, int64_t n, float* rms_m, float* rms_s, double* rms_n, void* workspace,
                    size_t workspace_bytes, exb_stream_t stream);
 
 /* --------------------------------------------------------------------------------------------
@@ -235,22 +233,19 @@ int exb_rms_update(const float* x, int64_t n, const float* rms_m_in, const float
  * prep -> tcgen05 screen -> rerank, with the RMS/epilogue executed by the last rerank block.
  * out_dist / out_idx [nq,k] are also produced (the neighbours the reference discards, :297).
  * The workspace must be zeroed ONCE after allocation (it carries the epilogue's ticket word);
- * RMS state convention as for exb_pbe_reward (caller advances n).
+ * RMS state convention as for exb_pbe_reward (in place, on the device).
  * ------------------------------------------------------------------------------------------ */
 size_t exb_apt_reward_workspace_bytes(int64_t nq, int64_t nb, int dim, int k);
 int exb_apt_reward_f32(const float* src, int64_t nq, const float* bank, int64_t nb, int dim, int k,
                        int src_is_bank, int mode, int avg, int use_rms, float clip,
-                       const float* rms_m_in, const float* rms_s_in, double rms_n,
-                       float* rms_m_out, float* rms_s_out, float* out_reward /* [nq] */,
+                       float* rms_m, float* rms_s, double* rms_n, float* out_reward /* [nq] */,
                        float* out_dist /* [nq,k] */, int32_t* out_idx /* [nq,k] */,
                        void* workspace, size_t workspace_bytes, exb_stream_t stream);
 
 /* exb_apt_reward_f32 on caller-prepared operands (rep producers above); screened mode only. */
 int exb_apt_reward_pre_f32(const float* src, int64_t nq, const exb_operand* src_op,
                            const float* bank, int64_t nb, const exb_operand* bank_op, int dim,
-                           int k, int avg, int use_rms, float clip, const float* rms_m_in,
-                           const float* rms_s_in, double rms_n, float* rms_m_out,
-                           float* rms_s_out, float* out_reward, float* out_dist,
+                           int k, int avg, int use_rms, float clip, float* rms_m, float* rms_s, double* rms_n, float* out_reward, float* out_dist,
                            int32_t* out_idx, void* workspace, size_t workspace_bytes,
                            exb_stream_t stream);
 
@@ -258,10 +253,9 @@ int exb_apt_reward_pre_f32(const float* src, int64_t nq, const exb_operand* src_
  *   out_error[i]  = mean_c (target[i,c] - prediction[i,c])^2      (rnd.py:52-54)
  *   (M, S) <- RMS update with x = out_error, bs = n                (rnd.py:96, utils.py:264-276)
  *   out_reward[i] = scale * out_error[i] / (sqrt(S_updated) + 1e-8) (rnd.py:97-98)
- * workspace: exb_pbe_workspace_bytes, zeroed once; the caller advances n += rows itself. */
+ * workspace: exb_pbe_workspace_bytes, zeroed once; RMS state in place as above. */
 int exb_rnd_reward_f32(const float* prediction, const float* target, int64_t n, int dim,
-                       float scale, const float* rms_m_in, const float* rms_s_in, double rms_n,
-                       float* rms_m_out, float* rms_s_out, float* out_error /* [n] */,
+                       float scale, float* rms_m, float* rms_s, double* rms_n, float* out_error /* [n] */,
                        float* out_reward /* [n] */, void* workspace, size_t workspace_bytes,
                        exb_stream_t stream);
 

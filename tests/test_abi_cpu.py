@@ -23,7 +23,7 @@ def test_library_loads_and_exports_every_declared_symbol():
     assert len(names) >= 15
     for n in names:
         assert hasattr(lib, n), f"{n} declared in the header but not exported"
-    assert lib.exb_abi_version() == 1
+    assert lib.exb_abi_version() == 2
 
 
 def test_binding_table_matches_header():

@@ -147,7 +147,7 @@ def test_loader_dropin_signature_and_reference_rng_parity(tmp_path):
         eps.append(ep)
     storage = types.SimpleNamespace(_replay_dir=pathlib.Path(tmp_path),
                                     _meta_specs=(types.SimpleNamespace(name="skill"),))
-    loader = xb.make_replay_loader(storage, 1000000, 16, 4, True, 3, 0.99, device=DEV,
+    loader = xb.make_replay_loader(storage, 1000000, 16, 1, True, 3, 0.99, device=DEV,
                                    sampler="reference_rng")
     random.seed(11)
     np.random.seed(11)
@@ -164,8 +164,10 @@ def test_loader_dropin_signature_and_reference_rng_parity(tmp_path):
             want = nstep_transition(eps[e], idx, 3, 0.99, ("skill",))
             for j in range(6):
                 assert np.array_equal(batch[j][s].cpu().numpy(), np.asarray(want[j]))
-    # philox loader: yields forever, right shapes/dtypes
+    # philox loader with the reference's default of 4 workers (pretrain.yaml:33): yields forever,
+    # right shapes/dtypes, every batch from one worker partition
     loader2 = xb.make_replay_loader(storage, 1000000, 1024, 4, True, 3, 0.99, device=DEV, seed=5)
+    assert len(loader2.buffers) == 4
     obs, act, rew, disc, nobs, skill = next(iter(loader2))
     assert obs.shape == (1024, 24) and act.shape == (1024, 6) and rew.shape == (1024, 1)
     assert disc.shape == (1024, 1) and nobs.shape == (1024, 24) and skill.shape == (1024, 4)

@@ -106,6 +106,7 @@ class _OracleStages:
             rms.M = torch.tensor([m + delta * bs / (n + bs)], dtype=torch.float32)
             rms.S = torch.tensor([(sv * n + var * bs + delta * delta * n * bs / (n + bs))
                                   / (n + bs)], dtype=torch.float32)
+            rms.n = n + bs          # the stage owns the whole state update (M, S and n)
             r = r / rms.M
         if clip >= 0:
             r = torch.clamp(r - clip, min=0)
@@ -116,10 +117,7 @@ class _OracleStages:
     @staticmethod
     def reward(knn_dist, k, avg, use_rms, clip, rms):
         sums = _OracleStages.sums(knn_dist, k, avg)
-        out = _OracleStages.finish(knn_dist, k, avg, use_rms, clip, sums, rms)
-        if use_rms:
-            rms.n += knn_dist.size(0) * (k if avg else 1)
-        return out
+        return _OracleStages.finish(knn_dist, k, avg, use_rms, clip, sums, rms)
 
 
 def _worker(rank, world, port, exchange, n, q):
