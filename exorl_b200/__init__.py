@@ -4,6 +4,7 @@ Drop-in surface of the reference's hot path:
   RMS, PBE                      <- utils/utils.py:257-319
   compute_apt_reward            <- the pre-refactor name of the same computation (source != target)
   proto_knn_reward, proto_enqueue <- agents/unsupervised_learning/proto.py:110-118
+  proto_sample_enqueue          <- proto.py:105-112 (candidate sampling fused with the queue write)
   rnd_intr_reward               <- RND error + RMS normalisation, agents/unsupervised_learning/rnd.py:52-54,94-99
   make_replay_loader, make_offline_replay_loader <- utils/replay_buffer.py:246-277
   icm_get_rep, normalize_rep    <- ICM.trunk (icm_apt.py:17-18,50-52), F.normalize (proto.py:104):
@@ -11,7 +12,7 @@ Drop-in surface of the reference's hot path:
   read_episode(s)               <- load_episode, utils/replay_buffer.py:26-29 (native .npz reader)
 """
 from .knn import (RMS, PBE, compute_apt_reward, knn_topk, proto_knn_reward, proto_enqueue,
-                  rnd_intr_reward)
+                  proto_sample_enqueue, rnd_intr_reward)
 from .replay import (DeviceReplayBuffer, DeviceReplayLoader, make_replay_loader,
                      make_offline_replay_loader)
 from .relabel import relabel_apt_reward, reps_from_host
@@ -19,7 +20,7 @@ from .ingest import read_episode, read_episodes
 from .rep import PreparedRep, icm_get_rep, ln_tanh_rep, normalize_rep, prepare_rep
 
 __all__ = ["RMS", "PBE", "compute_apt_reward", "knn_topk", "proto_knn_reward", "proto_enqueue",
-           "rnd_intr_reward",
+           "proto_sample_enqueue", "rnd_intr_reward",
            "DeviceReplayBuffer", "DeviceReplayLoader", "make_replay_loader",
            "make_offline_replay_loader", "relabel_apt_reward", "reps_from_host", "read_episode", "read_episodes",
            "PreparedRep", "icm_get_rep", "ln_tanh_rep", "normalize_rep", "prepare_rep"]

@@ -543,6 +543,64 @@ def proto_enqueue(queue, queue_ptr, z, candidates):
     return (queue_ptr + n) % queue.shape[0]
 
 
+_proto_calls = 0
+
+
+def proto_sample_enqueue(z, protos, queue, queue_ptr, noise=None, seed=0, call=None):
+    """Candidate sampling + queue write of ProtoAgent.compute_intr_reward (proto.py:105-112) in
+    one kernel: `scores = protos(z).T; prob = softmax(scores, 1); candidates =
+    Categorical(prob).sample(); queue[ptr:ptr+P] = z[candidates]`.  `protos` is the prototype
+    nn.Linear (bias-free) or its (P, dim) weight.  torch draws the sample as the exponential race
+    argmax(probs / q), q ~ Exp(1); `noise` (P, B) supplies q (parity with a recorded reference
+    stream), otherwise q comes from the device Philox stream keyed by (seed, call) — `call`
+    defaults to a process-wide counter so that successive calls draw fresh noise.
+    Returns (new queue_ptr, candidates (P,) int64).  torch.ops.exorl_b200.proto_sample."""
+    global _proto_calls
+    w = protos.weight if hasattr(protos, "weight") else protos
+    zr = _as_rows(z, "z")
+    wr = _as_rows(w, "protos")
+    if wr.size(1) != zr.size(1):
+        raise RuntimeError(f"mat1 and mat2 shapes cannot be multiplied ({zr.size(0)}x{zr.size(1)} "
+                           f"and {wr.size(1)}x{wr.size(0)})")
+    _lib.require_cuda(queue, "queue")
+    if (queue.dtype != torch.float32 or not queue.is_contiguous() or queue.dim() != 2
+            or queue.size(1) != zr.size(1)):
+        raise ValueError("queue must be a contiguous float32 (queue_size, dim) tensor")
+    n_protos = wr.size(0)
+    ptr = int(queue_ptr)
+    if ptr + n_protos > queue.size(0):
+        # the reference's slice assignment fails the same way when the slice is clipped
+        raise RuntimeError(f"The expanded size of the tensor ({queue.size(0) - ptr}) must match "
+                           f"the existing size ({n_protos}) at non-singleton dimension 0")
+    if noise is None:
+        noise_t = zr.new_empty(0)
+        if call is None:
+            call = _proto_calls
+            _proto_calls += 1
+    else:
+        noise_t = _as_rows(noise, "noise")
+        if noise_t.shape != (n_protos, zr.size(0)):
+            raise ValueError(f"noise must have shape ({n_protos}, {zr.size(0)})")
+        call = 0 if call is None else call
+    cand = ops.call(torch.ops.exorl_b200.proto_sample, _proto_sample_impl, zr, wr, queue, ptr,
+                    noise_t, int(seed), int(call))
+    return (ptr + n_protos) % queue.size(0), cand
+
+
+def _proto_sample_impl(z, protos, queue, queue_ptr, noise, seed, call):
+    lib = _lib.load()
+    dev = z.device
+    n_protos, dim = protos.shape
+    cand = torch.empty(n_protos, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(lib.exb_proto_sample_f32(
+            _lib.ptr(z), z.size(0), _lib.ptr(protos), n_protos, dim,
+            _lib.ptr(noise) if noise.numel() else None, ctypes.c_uint64(seed & (2 ** 64 - 1)),
+            ctypes.c_uint64(call & (2 ** 64 - 1)), _lib.ptr(queue), queue.size(0),
+            int(queue_ptr), _lib.ptr(cand), None, _lib.stream_ptr(dev)))
+    return cand
+
+
 def proto_knn_reward(z, queue, topk, mode="auto"):
     """Distance of every z row to its topk-th nearest queue row, (B, 1) — replaces
     proto.py:115-118 (no RMS, no clip, no log).  torch.ops.exorl_b200.proto_reward."""

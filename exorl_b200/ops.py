@@ -9,6 +9,7 @@ implementation of one reference call site, registered with `torch.library` toget
   exorl_b200::apt_reward    utils/utils.py:289-319 = PBE.__call__ / compute_apt_reward;
                             call sites icm_apt.py:96-100, aps.py:167-172
   exorl_b200::proto_reward  proto.py:115-118
+  exorl_b200::proto_sample  proto.py:105-111 (candidate per prototype + queue write)
   exorl_b200::rms_update    utils/utils.py:264-276 (RMS.__call__ on an (n, 1) column; rnd.py:96)
   exorl_b200::rnd_reward    rnd.py:52-54, 94-99
   exorl_b200::replay_sample utils/replay_buffer.py:214-235 / :87-96 (index draw + gather of a batch)
@@ -80,6 +81,19 @@ def proto_reward(z: torch.Tensor, queue: torch.Tensor, topk: int, knn_mode: str)
 @proto_reward.register_fake
 def _(z, queue, topk, knn_mode):
     return z.new_empty((z.shape[0], 1), dtype=torch.float32)
+
+
+@torch.library.custom_op(f"{_NS}::proto_sample", mutates_args=("queue",), device_types="cuda")
+def proto_sample(z: torch.Tensor, protos: torch.Tensor, queue: torch.Tensor, queue_ptr: int,
+                 noise: torch.Tensor, seed: int, call: int) -> torch.Tensor:
+    """proto.py:105-111: one batch row per prototype (exponential race on softmax(protos(z).T)),
+    written into queue[queue_ptr : queue_ptr + P].  `noise` of numel 0 = Philox (seed, call)."""
+    return _knn()._proto_sample_impl(z, protos, queue, queue_ptr, noise, seed, call)
+
+
+@proto_sample.register_fake
+def _(z, protos, queue, queue_ptr, noise, seed, call):
+    return z.new_empty((protos.shape[0],), dtype=torch.int64)
 
 
 @torch.library.custom_op(f"{_NS}::rms_update", mutates_args=("rms_m", "rms_s", "rms_n"),

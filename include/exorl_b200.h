@@ -259,6 +259,22 @@ int exb_rnd_reward_f32(const float* prediction, const float* target, int64_t n, 
                        float* out_reward /* [n] */, void* workspace, size_t workspace_bytes,
                        exb_stream_t stream);
 
+/* ProtoRL candidate sampling fused with the queue write.  Replaces proto.py:105-112:
+ *   scores = protos(z).T; prob = softmax(scores, dim=1); candidates = Categorical(prob).sample();
+ *   queue[ptr:ptr+P] = z[candidates]
+ * z [batch, dim] (unit rows), protos [n_protos, dim] = the nn.Linear weight (no bias).
+ * torch's one-sample multinomial is the exponential race argmax(probs / q), q ~ Exp(1): `noise`
+ * [n_protos, batch] supplies q (parity with a recorded reference stream); noise == NULL draws q
+ * from Philox4x32-10 keyed by (seed, call).  out_candidates [n_protos] int64 (batch row per
+ * prototype); out_prob [n_protos] (optional) = the renormalised probability of the chosen row.
+ * queue (optional) [queue_rows, dim]: rows [queue_ptr, queue_ptr + n_protos) are overwritten;
+ * the slice must fit (the reference's slice assignment raises otherwise) — the caller advances
+ * the pointer, (ptr + P) % queue_rows, like proto.py:112. */
+int exb_proto_sample_f32(const float* z, int64_t batch, const float* protos, int n_protos, int dim,
+                         const float* noise, uint64_t seed, uint64_t call, float* queue,
+                         int64_t queue_rows, int64_t queue_ptr, int64_t* out_candidates,
+                         float* out_prob, exb_stream_t stream);
+
 /* ProtoRL reward: k-th smallest distance only, no RMS/clip/log (proto.py:115-118). */
 int exb_take_kth(const float* knn_dist, int64_t nq, int k, float* out /* [nq] */,
                  exb_stream_t stream);

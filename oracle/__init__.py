@@ -11,7 +11,7 @@ against the known-answer vectors recorded in SURVEY.md §8c.  The reference ship
 own for this path, so there are no upstream golden vectors to pin against.
 """
 from .pbe_oracle import (rms_step, pbe_reward, knn_smallest, proto_reward, proto_enqueue,
-                         rnd_reward, RmsState)
+                         proto_candidates, rnd_reward, RmsState)
 from .rep_oracle import icm_trunk_rep, l2_normalize
 from .replay_oracle import (nstep_transition, onestep_transition, episode_length,
                             flatten_episodes, write_episode_npz, read_episode_npz,

@@ -130,6 +130,41 @@ def gen_proto():
     np.savez_compressed(OUT / "proto_reference.npz", **out)
 
 
+def gen_proto_sampling():
+    """proto.py:102-112 evaluated verbatim (normalize, protos(z).T, softmax, Categorical.sample,
+    queue slice write) under a recorded seed; the Exp(1) tensor torch.multinomial consumed is
+    re-drawn from the same seed and stored, and checked to reproduce the sample."""
+    import torch.distributions as pyd
+    out = {}
+    for tag, (b, n_protos, dim, qsize, ptr, temp) in {
+            "small": (192, 64, 128, 256, 64, 1.0), "peaked": (160, 32, 64, 128, 96, 20.0),
+            "odd": (77, 24, 50, 96, 0, 3.0)}.items():
+        g = torch.Generator().manual_seed(500 + b)
+        z = torch.nn.functional.normalize(torch.randn(b, dim, generator=g), dim=1, p=2)
+        protos = torch.nn.Linear(dim, n_protos, bias=False)
+        with torch.no_grad():
+            w = torch.nn.functional.normalize(torch.randn(n_protos, dim, generator=g), dim=1, p=2)
+            protos.weight.copy_(w * temp)       # temp > 1: sharper softmax (trained prototypes)
+            queue = torch.nn.functional.normalize(torch.randn(qsize, dim, generator=g), dim=1)
+            queue_before = queue.clone()
+            torch.manual_seed(900 + b)
+            scores = protos(z).T
+            prob = torch.nn.functional.softmax(scores, dim=1)
+            candidates = pyd.Categorical(prob).sample()
+            queue[ptr:ptr + n_protos] = z[candidates]
+            new_ptr = (ptr + n_protos) % queue.shape[0]
+            torch.manual_seed(900 + b)
+            noise = torch.empty_like(prob).exponential_(1)
+            probs = pyd.Categorical(prob).probs
+            assert torch.equal(torch.argmax(probs / noise, dim=1), candidates)
+        out[f"{tag}_z"], out[f"{tag}_w"] = z.numpy(), protos.weight.detach().numpy()
+        out[f"{tag}_noise"], out[f"{tag}_prob"] = noise.numpy(), probs.numpy()
+        out[f"{tag}_candidates"] = candidates.numpy()
+        out[f"{tag}_queue_before"], out[f"{tag}_queue_after"] = queue_before.numpy(), queue.numpy()
+        out[f"{tag}_ptr"] = np.array([ptr, new_ptr])
+    np.savez_compressed(OUT / "proto_sampling_reference.npz", **out)
+
+
 def synth_episode(rng, eps_len, obs_shape, obs_dtype, terminal, with_meta):
     n = eps_len + 1
     if obs_dtype == np.uint8:
@@ -398,6 +433,9 @@ if __name__ == "__main__":
     if "--rep-only" in sys.argv:
         gen_rep(ref_utils)
         sys.exit(0)
+    if "--proto-sampling-only" in sys.argv:
+        gen_proto_sampling()
+        sys.exit(0)
     if "--residency-only" in sys.argv:
         gen_residency(ref_replay)
         sys.exit(0)
@@ -410,6 +448,7 @@ if __name__ == "__main__":
     gen_pbe(ref_utils)
     gen_knn_dists(ref_utils)
     gen_proto()
+    gen_proto_sampling()
     gen_replay(ref_replay)
     gen_residency(ref_replay)
     for f in sorted(OUT.glob("*.npz")):

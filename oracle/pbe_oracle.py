@@ -114,6 +114,23 @@ def proto_enqueue(queue: torch.Tensor, ptr: int, rows: torch.Tensor):
     return (ptr + n) % queue.size(0)
 
 
+def proto_candidates(z: torch.Tensor, protos_weight: torch.Tensor, noise: torch.Tensor):
+    """One batch row per prototype, with the sampling noise made explicit.
+
+    Follows /root/reference/agents/unsupervised_learning/proto.py:105-107:
+    ``scores = protos(z).T`` (bias-free nn.Linear), ``prob = softmax(scores, dim=1)``,
+    ``Categorical(prob).sample()``.  Categorical renormalises its probs (``probs /
+    probs.sum(-1, keepdim=True)``) and torch.multinomial with one sample is the exponential
+    race ``argmax(probs / q)`` with ``q = empty_like(probs).exponential_(1)`` drawn from the
+    generator; ``noise`` is that q (tests/test_oracle_pins.py checks the restatement against the
+    reference lines run under the seed that produced the recorded q).
+    """
+    scores = torch.nn.functional.linear(z, protos_weight).T
+    prob = torch.nn.functional.softmax(scores, dim=1)
+    prob = prob / prob.sum(-1, keepdim=True)
+    return torch.argmax(prob / noise, dim=1), prob
+
+
 def proto_reward(z: torch.Tensor, queue: torch.Tensor, topk: int):
     """ProtoRL intrinsic reward: distance to the topk-th nearest queue entry, shape (B, 1).
 

@@ -9,7 +9,7 @@ import pytest
 import torch
 
 from oracle import (RmsState, rms_step, pbe_reward, knn_smallest, proto_reward, proto_enqueue,
-                    nstep_transition, onestep_transition)
+                    proto_candidates, nstep_transition, onestep_transition)
 
 REP4 = torch.tensor([[0., 0.], [3., 4.], [6., 8.], [0., 1.]])
 
@@ -200,3 +200,19 @@ def test_golden_rnd_reward_bitwise(golden, tag):
         assert np.array_equal(r.numpy(), g[f"{tag}_reward{call}"])
         m, s, n = g[f"{tag}_state{call}"]
         assert float(st.M) == m and float(st.S) == s and st.n == n
+
+
+@pytest.mark.parametrize("tag", ["small", "peaked", "odd"])
+def test_proto_candidate_sampling_pinned_to_reference(golden, tag):
+    """oracle.proto_candidates (softmax -> Categorical renormalisation -> exponential race on the
+    recorded noise) returns the candidates the reference's proto.py:105-107 sampled, bitwise equal
+    probabilities included, and the queue write of :110-112 gives the recorded queue."""
+    g = golden("proto_sampling_reference.npz")
+    z, w = torch.from_numpy(g[f"{tag}_z"]), torch.from_numpy(g[f"{tag}_w"])
+    cand, prob = proto_candidates(z, w, torch.from_numpy(g[f"{tag}_noise"]))
+    assert np.array_equal(cand.numpy(), g[f"{tag}_candidates"])
+    assert np.array_equal(prob.numpy(), g[f"{tag}_prob"])
+    queue = torch.from_numpy(g[f"{tag}_queue_before"]).clone()
+    ptr, new_ptr = (int(v) for v in g[f"{tag}_ptr"])
+    assert proto_enqueue(queue, ptr, z[cand]) == new_ptr
+    assert np.array_equal(queue.numpy(), g[f"{tag}_queue_after"])
