@@ -46,6 +46,8 @@ def parse():
                     help="skip the C1-C4 block (BASELINE configs 1-4) of the 1-GPU line")
     ap.add_argument("--no-exchange-ab", action="store_true",
                     help="skip the one-step timings of the bank-sharded exchanges (N > 1)")
+    ap.add_argument("--no-balance", action="store_true",
+                    help="equal query blocks per rank instead of rate-proportional ones (A/B)")
     ap.add_argument("--stage-times", action="store_true",
                     help="after the timed runs, one extra step with per-stage CUDA events (stderr)")
     return ap.parse_args()
@@ -233,12 +235,15 @@ def run_ours(a, rank, world, local_rank):
     rms = xb.RMS(dev)
 
     def step():
-        return xb.relabel_apt_reward(rep, args, rms=rms, exchange=a.exchange, mode="screened")
+        return xb.relabel_apt_reward(rep, args, rms=rms, exchange=a.exchange, mode="screened",
+                                     balance=not a.no_balance)
 
     def step_e2e():
-        # every rank copies its own rows from pinned host memory, NVLink all-gathers the rest
-        xb.reps_from_host(rep_host, out=rep)
-        r = step()
+        # host buffers in, host buffer out: every rank copies ITS rows from pinned host memory,
+        # prepares them, the fp16 operand is all-gathered over NVLink and the screen starts while
+        # the fp32 rows follow behind it (relabel_apt_reward_from_host)
+        r = xb.relabel_apt_reward_from_host(rep_host, args, rms=rms, rep_out=rep,
+                                            balance=not a.no_balance)
         reward_host.copy_(r, non_blocking=True)
 
     for _ in range(a.warmup):
@@ -310,6 +315,12 @@ def run_ours(a, rank, world, local_rank):
         secondary = sec.run_all(dev, lambda: ClockSampler(dev.index),
                                 cpu=not a.no_cpu_baseline)
 
+    query_blocks = None
+    if world > 1 and a.exchange in ("auto", "queries"):
+        from exorl_b200 import relabel as xrel
+        bal = xrel.query_balance(None, a.n, world, a.k)
+        query_blocks = {"balance": not a.no_balance,
+                        "rows_per_rank": [hi - lo for lo, hi in bal.bounds]}
     if rank == 0:
         sustained, burst, src = peaks()
         nb_local = a.n // world
@@ -332,7 +343,8 @@ def run_ours(a, rank, world, local_rank):
                            if a.exchange in ("auto", "queries") else " (bank sharded)")),
                        "l2": "inputs (2 GB fp32 + 1 GB fp16 bank) larger than the 126 MB L2; "
                              "no flush needed",
-                       "undecided_rows_last_step": und, "invalid": invalid},
+                       "undecided_rows_last_step": und, "invalid": invalid,
+                       **({"query_blocks": query_blocks} if query_blocks else {})},
             "clocks": clocks,
             "e2e": {"value": a.n * a.steps / (ms_e2e * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": rep_host.numel() * 4,   # whole job: each rank its shard

@@ -41,9 +41,16 @@ def main():
     ok = True
     # "prepared": the same set handed over as a PreparedRep (exb_knn_prep_f16 here; the rep
     # producers emit the same operand), query-block partition
-    for exchange in ("queries", "prepared", "lists", "auto", "all_to_all", "all_gather"):
+    rep_host = rep.cpu().pin_memory()
+    from exorl_b200 import relabel as xrel
+    # "queries" runs three times so that the rate-proportional query blocks (QueryBalance) have
+    # moved away from the equal split by the last run; "from_host" is the end-to-end pipeline
+    for exchange in ("queries", "queries", "queries", "from_host", "from_host", "prepared",
+                     "lists", "auto", "all_to_all", "all_gather"):
         rms = xb.RMS(dev)
-        if exchange == "prepared":
+        if exchange == "from_host":
+            out = xb.relabel_apt_reward_from_host(rep_host, args, rms=rms, return_knn=True)
+        elif exchange == "prepared":
             out = xb.relabel_apt_reward(xb.prepare_rep(rep), args, rms=rms, exchange="queries",
                                         return_knn=True)
         else:
@@ -56,9 +63,10 @@ def main():
         assert rms.n == rms0.n
         if exchange == "all_gather":            # every rank holds all rows
             lo, hi = 0, a.n
+        elif exchange in ("queries", "auto", "prepared", "from_host"):
+            lo, hi = xrel.last_query_block["lo"], xrel.last_query_block["hi"]   # balanced block
         else:                                    # rank r finalised query block r
-            from exorl_b200.relabel import shard_bounds
-            lo, hi = shard_bounds(a.n, world, rank)
+            lo, hi = xrel.shard_bounds(a.n, world, rank)
         np.testing.assert_allclose(d.cpu().numpy(), d0[lo:hi].cpu().numpy(), rtol=1e-6)
         same = (i.sort(dim=1).values == i0[lo:hi].sort(dim=1).values).all(dim=1)
         bad = int((~same).sum())
@@ -70,7 +78,7 @@ def main():
         assert all(float(x) == float(lst[0]) for x in lst), "ranks disagree"
         if rank == 0:
             print(f"[nccl check] world={world} n={a.n} exchange={exchange}: OK "
-                  f"(rows with near-tie swaps: {bad})", flush=True)
+                  f"(rows with near-tie swaps: {bad}; rank-0 block [{lo}, {hi}))", flush=True)
     dist.destroy_process_group()
     return 0 if ok else 1
 

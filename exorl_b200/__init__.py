@@ -15,12 +15,12 @@ from .knn import (RMS, PBE, compute_apt_reward, knn_topk, proto_knn_reward, prot
                   proto_sample_enqueue, rnd_intr_reward)
 from .replay import (DeviceReplayBuffer, DeviceReplayLoader, make_replay_loader,
                      make_offline_replay_loader)
-from .relabel import relabel_apt_reward, reps_from_host
+from .relabel import relabel_apt_reward, relabel_apt_reward_from_host, reps_from_host
 from .ingest import read_episode, read_episodes
 from .rep import PreparedRep, icm_get_rep, ln_tanh_rep, normalize_rep, prepare_rep
 
 __all__ = ["RMS", "PBE", "compute_apt_reward", "knn_topk", "proto_knn_reward", "proto_enqueue",
            "proto_sample_enqueue", "rnd_intr_reward",
            "DeviceReplayBuffer", "DeviceReplayLoader", "make_replay_loader",
-           "make_offline_replay_loader", "relabel_apt_reward", "reps_from_host", "read_episode", "read_episodes",
+           "make_offline_replay_loader", "relabel_apt_reward", "relabel_apt_reward_from_host", "reps_from_host", "read_episode", "read_episodes",
            "PreparedRep", "icm_get_rep", "ln_tanh_rep", "normalize_rep", "prepare_rep"]

@@ -120,6 +120,30 @@ def _cuda_block_knn(rep, lo, hi, k, mode):
     return knn_topk(_shard(rep, lo, hi), rep, k, mode=mode)
 
 
+class _CudaStopwatch:
+    """Device time of the block kNN of one step, read without a sync at the start of the next."""
+
+    def __init__(self):
+        self.e0 = torch.cuda.Event(enable_timing=True)
+        self.e1 = torch.cuda.Event(enable_timing=True)
+        self.armed = False
+
+    def start(self):
+        self.e0.record()
+
+    def stop(self):
+        self.e1.record()
+        self.armed = True
+
+    def elapsed_ms(self):
+        """Milliseconds of the last start/stop pair, or 0.0 if there is none or it has not
+        finished on the device yet."""
+        if not self.armed or not self.e1.query():
+            return 0.0
+        self.armed = False
+        return float(self.e0.elapsed_time(self.e1))
+
+
 class _CudaStages:
     local_knn = staticmethod(_cuda_local_knn)
     block_knn = staticmethod(_cuda_block_knn)
@@ -129,11 +153,78 @@ class _CudaStages:
     merge = staticmethod(_cuda_merge)
     sums = staticmethod(_cuda_sums)
     finish = staticmethod(_cuda_finish)
+    stopwatch = _CudaStopwatch
 
     @staticmethod
     def reward(knn_dist, k, avg, use_rms, clip, rms):
         st = (rms.M, rms.S, rms._n) if use_rms else (None,) * 3
         return _reward_from_knn(knn_dist, k, avg, use_rms, clip, *st)
+
+
+def balanced_bounds(n, shares, quantum=256, min_rows=1):
+    """Contiguous row blocks [cut[r], cut[r+1]) with sizes proportional to `shares`, cut at
+    multiples of `quantum` rows (one CTA pair of the screening kernel owns 256 query rows).
+    Falls back to the equal split when a block would get fewer than `min_rows` rows."""
+    world = len(shares)
+    tot = float(sum(shares))
+    cuts, acc = [0], 0.0
+    for r in range(world - 1):
+        acc += shares[r] / tot
+        cuts.append(min(n, max(cuts[-1], int(round(acc * n / quantum)) * quantum)))
+    cuts.append(n)
+    if any(b - a < max(min_rows, 1) for a, b in zip(cuts[:-1], cuts[1:])):
+        return [shard_bounds(n, world, r) for r in range(world)]
+    return list(zip(cuts[:-1], cuts[1:]))
+
+
+class QueryBalance:
+    """Per-rank query-block sizes of the 'queries' partition, proportional to each rank's
+    measured kNN rate (rows per millisecond) in the previous step.
+
+    Under the 1 kW power cap the GPUs of one box settle at different SM clocks (driver record of
+    round 1: per-rank minimum 1 237-1 252 MHz against a median of 1 402-1 462), so equal blocks
+    make every step wait for the slowest rank.  Each rank times its block kNN with CUDA events;
+    the time of step s rides along in the RMS-sums all-reduce of step s+1 (no extra collective,
+    no host sync), so every rank derives the SAME bounds for step s+2.  Damped (`gain`) because
+    the kernel's time is not exactly linear in its rows (waves of 148 CTA pairs)."""
+
+    def __init__(self, n, world, quantum=256, min_rows=1, gain=0.7):
+        self.n, self.world, self.quantum, self.min_rows, self.gain = n, world, quantum, min_rows, gain
+        self.shares = [1.0 / world] * world
+        self.bounds = [shard_bounds(n, world, r) for r in range(world)]
+        self.prev_bounds = None       # bounds of the previous call (what the stopwatch timed)
+        self.pending = None           # (device vector of the ranks' times, bounds they timed)
+        self.watch = None
+
+    def settle(self):
+        """Fold in the times the previous call all-reduced (identical on every rank, so every
+        rank derives the same bounds); by now that call's kernels have long finished."""
+        if self.pending is not None:
+            (times, timed_bounds), self.pending = self.pending, None
+            self.update(times.tolist(), timed_bounds)
+
+    def update(self, times_ms, timed_bounds):
+        """`times_ms[r]` = rank r's block time under `timed_bounds` (0 = not measured)."""
+        if timed_bounds is None or any(t <= 0.0 for t in times_ms):
+            return
+        rates = [(b - a) / t for (a, b), t in zip(timed_bounds, times_ms)]
+        tot = sum(rates)
+        target = [r / tot for r in rates]
+        self.shares = [(1 - self.gain) * s + self.gain * t for s, t in zip(self.shares, target)]
+        self.bounds = balanced_bounds(self.n, self.shares, self.quantum, self.min_rows)
+
+
+_balances = {}
+
+
+def query_balance(group, n, world, k):
+    key = (id(group) if group is not None else 0, n, world, k)
+    if key not in _balances:
+        _balances[key] = QueryBalance(n, world, min_rows=k)
+    return _balances[key]
+
+
+last_query_block = {}     # {"lo", "hi"} of this rank's query block in the last balanced call
 
 
 def reps_from_host(rep_host, out=None, group=None):
@@ -180,13 +271,23 @@ class StageTimer:
 
 
 def _finish_block(d_mine, i_mine, n, lo, hi, in_split, world, k, avg, use_rms, clip, rms, group,
-                  stages, tm, return_knn):
+                  stages, tm, return_knn, balance=None, prev_ms=0.0):
     """Global RMS update from all-reduced sums, epilogue of this rank's query block, rewards
-    all-gathered so that every rank returns the full (N, 1)."""
+    all-gathered so that every rank returns the full (N, 1).  With `balance`, this rank's block
+    time of the previous step rides along in the same all-reduce and re-sizes the next blocks."""
     my_n = hi - lo
     sums = None
-    if use_rms:
-        sums = stages.sums(d_mine, k, avg)                      # {count, sum, sumsq} of my block
+    if balance is not None:
+        rank = dist.get_rank(group)
+        vec = torch.zeros(4 + world, dtype=torch.float64, device=d_mine.device)
+        if use_rms:
+            vec[:3] = stages.sums(d_mine, k, avg)               # {count, sum, sumsq} of my block
+        vec[4 + rank] = prev_ms
+        dist.all_reduce(vec, op=dist.ReduceOp.SUM, group=group)
+        sums = vec[:3] if use_rms else None
+        times = vec[4:]
+    elif use_rms:
+        sums = stages.sums(d_mine, k, avg)
         dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
     tm("rms_allreduce")
     r_mine = stages.finish(d_mine, k, avg, use_rms, clip, sums, rms)
@@ -199,13 +300,17 @@ def _finish_block(d_mine, i_mine, n, lo, hi, in_split, world, k, avg, use_rms, c
     dist.all_gather_into_tensor(gathered, pad, group=group)
     reward = torch.cat([gathered[r * mx:r * mx + in_split[r]] for r in range(world)], dim=0)
     tm("reward_allgather")
+    if balance is not None:
+        # read at the start of the next call (no sync in this one); the times are those of the
+        # PREVIOUS call's blocks
+        balance.pending = (times, balance.prev_bounds)
     if return_knn:
         return reward, d_mine, i_mine
     return reward
 
 
 def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="auto",
-                       return_knn=False, stages=_CudaStages, timer=None):
+                       return_knn=False, stages=_CudaStages, timer=None, balance=True):
     """APT reward (N, 1) of every row of `rep` against all N rows, identical on every rank.
 
     `rep` is the (N, c) fp32 rep tensor or a PreparedRep (exorl_b200.rep: e.g. icm_get_rep of the
@@ -214,7 +319,9 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="a
 
     `args` exposes knn_k, knn_avg, knn_rms, knn_clip like PBE; `rms` is the running-moment state
     (updated once with bs = N*k in avg mode, N otherwise).  Works without an initialised process
-    group (single shard)."""
+    group (single shard).  `balance`: in the 'queries' partition, size the per-rank query blocks
+    by the ranks' measured rates (QueryBalance) instead of equally; with `return_knn` the rows of
+    the returned block are `relabel.last_query_block`."""
     if exchange not in ("auto", "lists", "all_gather", "all_to_all", "queries"):
         raise ValueError("exchange must be 'auto', 'lists', 'all_gather', 'all_to_all' or "
                          "'queries'")
@@ -254,11 +361,29 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="a
         exchange = "all_to_all"
 
     if world > 1 and exchange == "queries":
-        in_split = [b - a for a, b in (shard_bounds(n, world, r) for r in range(world))]
+        bal = query_balance(group, n, world, k) if balance else None
+        if bal is not None:
+            bal.settle()
+        bounds = bal.bounds if bal else [shard_bounds(n, world, r) for r in range(world)]
+        in_split = [b - a for a, b in bounds]
+        lo, hi = bounds[rank]
+        last_query_block.update(lo=lo, hi=hi)
+        prev_ms = 0.0
+        if bal is not None:
+            if bal.watch is None and hasattr(stages, "stopwatch"):
+                bal.watch = stages.stopwatch()
+            if bal.watch is not None:
+                prev_ms = bal.watch.elapsed_ms()     # last step's block, under bal.timed_bounds
+                bal.watch.start()
         d_mine, i_mine = stages.block_knn(rep, lo, hi, k, mode)
+        if bal is not None and bal.watch is not None:
+            bal.watch.stop()
         tm("block_knn")
-        return _finish_block(d_mine, i_mine, n, lo, hi, in_split, world, k, avg, use_rms, clip, rms,
-                             group, stages, tm, return_knn)
+        out = _finish_block(d_mine, i_mine, n, lo, hi, in_split, world, k, avg, use_rms, clip,
+                            rms, group, stages, tm, return_knn, balance=bal, prev_ms=prev_ms)
+        if bal is not None:
+            bal.prev_bounds = bounds      # the time read at the next call was measured on these
+        return out
 
     if world > 1 and exchange == "lists":
         bounds = [shard_bounds(n, world, r) for r in range(world)]
@@ -311,3 +436,93 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="a
     tm("merge")
     return _finish_block(d_mine, i_mine, n, lo, hi, in_split, world, k, avg, use_rms, clip, rms,
                          group, stages, tm, return_knn)
+
+
+_side_streams = {}
+
+
+def _side_stream(dev):
+    key = dev.index if dev.index is not None else torch.cuda.current_device()
+    if key not in _side_streams:
+        _side_streams[key] = torch.cuda.Stream(dev)
+    return _side_streams[key]
+
+
+def relabel_apt_reward_from_host(rep_host, args, rms=None, group=None, rep_out=None,
+                                 return_knn=False, balance=True):
+    """`relabel_apt_reward` for reps that live in (pinned) HOST memory — the end-to-end form of
+    config 5: (N, c) fp32 rows in, (N, 1) rewards out, identical on every rank.
+
+    Pipeline per rank r of G (query-block partition, whole bank on every rank):
+      1. H2D of ITS N/G rows only (PCIe), 2. exb_knn_prep_f16 of those rows,
+      3. all-gather of the fp16 operand + row norms over NVLink (1 GB instead of the 2 GB of fp32
+         rows; the scalars are MAX-reduced), 4. the tcgen05 screen of its query block against the
+         whole bank starts, while 5. the fp32 rows — needed only by the exact rerank — are
+         all-gathered behind it on the NCCL stream, 6. rerank, global RMS, epilogue, rewards.
+    So the screen waits for N/G rows of PCIe + 1 GB of NVLink instead of for all 2 GB twice.
+    Uneven shards (N % G != 0) take the plain path (reps_from_host + relabel_apt_reward)."""
+    from .knn import knn_screen_lists, knn_rerank_lists
+    if rms is None:
+        rms = getattr(args, "rms", None)
+    k, avg, use_rms, clip = int(args.knn_k), bool(args.knn_avg), bool(args.knn_rms), args.knn_clip
+    distributed = dist.is_available() and dist.is_initialized()
+    world = dist.get_world_size(group) if distributed else 1
+    rank = dist.get_rank(group) if distributed else 0
+    n, dim = rep_host.shape
+    dev = torch.device("cuda", torch.cuda.current_device()) if rep_out is None else rep_out.device
+    if rep_out is None:
+        rep_out = torch.empty((n, dim), dtype=torch.float32, device=dev)
+    lists = screen_lists_count(max(n // world, 1), n, dim, k)
+    if n % world != 0 or lists == 0 or lists > 16:
+        rep = reps_from_host(rep_host, out=rep_out, group=group)
+        return relabel_apt_reward(rep, args, rms=rms, group=group, mode="screened",
+                                  return_knn=return_knn, balance=balance)
+    lib = _lib.load()
+    lo, hi = shard_bounds(n, world, rank)
+    with torch.cuda.device(dev):
+        pre = PreparedRep(n, dim, dev, rep=rep_out)
+        rep_out[lo:hi].copy_(rep_host[lo:hi], non_blocking=True)                        # 1
+        _lib.check(lib.exb_knn_prep_f16(                                                 # 2
+            _lib.ptr(rep_out[lo:hi]), hi - lo, dim, _lib.ptr(pre.f16[lo:hi]),
+            _lib.ptr(pre.half_norm[lo:hi]), _lib.ptr(pre.round_err[lo:hi]),
+            _lib.ptr(pre.scalars), _lib.stream_ptr(dev)))
+        fp32_rows = None
+        if world > 1:
+            dist.all_gather_into_tensor(pre.f16, pre.f16[lo:hi], group=group)            # 3
+            dist.all_gather_into_tensor(pre.half_norm, pre.half_norm[lo:hi], group=group)
+            dist.all_gather_into_tensor(pre.round_err, pre.round_err[lo:hi], group=group)
+            dist.all_reduce(pre.scalars, op=dist.ReduceOp.MAX, group=group)   # >= 0 floats as i32
+            side = _side_stream(dev)                                                     # 5
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                fp32_rows = dist.all_gather_into_tensor(rep_out, rep_out[lo:hi], group=group,
+                                                        async_op=True)
+        bal = query_balance(group, n, world, k) if (balance and world > 1) else None
+        if bal is not None:
+            bal.settle()
+        bounds = bal.bounds if bal else [shard_bounds(n, world, r) for r in range(world)]
+        qlo, qhi = bounds[rank]
+        last_query_block.update(lo=qlo, hi=qhi)
+        prev_ms = 0.0
+        if bal is not None:
+            if bal.watch is None:
+                bal.watch = _CudaStopwatch()
+            prev_ms = bal.watch.elapsed_ms()
+            bal.watch.start()
+        block = pre if (qlo, qhi) == (0, n) else pre.rows(qlo, qhi)
+        val, idx, cnt, ha, ea, sc = knn_screen_lists(block, pre, k)                      # 4
+        if bal is not None:
+            bal.watch.stop()
+        if fp32_rows is not None:
+            fp32_rows.wait()              # the current stream waits for the fp32 bank rows
+        d_mine, i_mine = knn_rerank_lists(rep_out if block is pre else rep_out[qlo:qhi], rep_out,
+                                          k, val[None], idx[None], cnt[None], [0], ha, ea, sc)
+        if world == 1:
+            reward = _CudaStages.reward(d_mine, k, avg, use_rms, clip, rms)
+            return (reward, d_mine, i_mine) if return_knn else reward
+        out = _finish_block(d_mine, i_mine, n, qlo, qhi, [b - a for a, b in bounds], world, k,
+                            avg, use_rms, clip, rms, group, _CudaStages, lambda name: None,
+                            return_knn, balance=bal, prev_ms=prev_ms)
+        if bal is not None:
+            bal.prev_bounds = bounds
+        return out

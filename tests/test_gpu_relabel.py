@@ -51,23 +51,35 @@ def test_relabel_single_process_matches_oracle():
     assert_knn_matches(x, x, 12, d, i, oracle=knn)
 
 
-def test_medium_bank_screened_equals_exact_kernel():
-    """32 768 x 32 768 x 512 (SURVEY §8c full-N check size): the tcgen05 path and the fp32
-    CUDA-core path agree; a 256-query subset is checked against the oracle."""
-    n = 32768
-    x = reps(5, n, 512)
+def _scale_bank(g):
+    """The seeded bank a scale fixture was computed on (oracle/gen_scale_golden.py:bank); the
+    stored fp64 sum tells a different host random stream from a kNN defect."""
+    n, dim = int(g["n"]), int(g["dim"])
+    gen = torch.Generator().manual_seed(int(g["seed"]))
+    x = torch.tanh(torch.randn(n, dim, generator=gen))
+    assert abs(float(x.double().sum()) - float(g["bank_sum"])) <= 1e-6 * n, \
+        "host RNG stream differs from the authoring container's"
+    return x
+
+
+def test_medium_bank_all_queries_vs_oracle_fixture(golden):
+    """32 768 x 32 768 x 512 (SURVEY §8c full-N check): EVERY query's k nearest from the tcgen05
+    path against the tiled reference formula (tests/golden/knn_scale_32k.npz, computed by
+    oracle/gen_scale_golden.py from utils/utils.py:293-300), and the fp32 CUDA-core path too."""
+    g = golden("knn_scale_32k.npz")
+    x = _scale_bank(g)
+    n, k = x.size(0), int(g["k"])
+    oracle = (torch.from_numpy(g["dist"]), torch.from_numpy(g["idx"]).long())
     xd = x.to(DEV)
-    d_s, i_s = xb.knn_topk(xd, xd, 12, mode="screened")
+    d_s, i_s = xb.knn_topk(xd, xd, k, mode="screened")
     from exorl_b200 import knn as xknn
     und, invalid, pairs, _ = xknn.screened_status(torch.device(DEV))
     assert invalid == 0 and und < n // 100
-    d_e, i_e = xb.knn_topk(xd, xd, 12, mode="exact")
+    ties = assert_knn_matches(x, x, k, d_s, i_s, oracle=oracle)
+    assert ties <= n // 1000
+    d_e, i_e = xb.knn_topk(xd, xd, k, mode="exact")
+    assert_knn_matches(x, x, k, d_e, i_e, oracle=oracle)
     np.testing.assert_allclose(d_s.cpu().numpy(), d_e.cpu().numpy(), rtol=1e-6)
-    diff = (i_s.sort(dim=1).values != i_e.sort(dim=1).values).any(dim=1).sum().item()
-    assert diff <= n // 1000          # only fp32 near-ties may differ between summation orders
-    sub = torch.arange(0, n, n // 256)[:256]
-    od, oi = knn_smallest(x[sub], x, 12)
-    assert_knn_matches(x[sub], x, 12, d_s[sub.to(DEV)], i_s[sub.to(DEV)], oracle=(od, oi))
 
 
 @pytest.mark.parametrize("world", [2, 8])
@@ -177,16 +189,18 @@ def test_randomized_shapes_screened_equals_exact():
         assert diff <= max(1, nq // 500), (nq, nb, dim, k, diff)
 
 
-def test_c5_full_size_properties():
+def test_c5_full_size_properties(golden):
     """BASELINE config 5 at full size (10^6 x 10^6, rep 512, k = 12, avg + rms) on one GPU, checked
-    through size-independent properties + a 48-query slice against the oracle (the full oracle
-    would take CPU-days): self-match first with distance exactly 0, ascending distances, distinct
-    in-range indices, returned distances equal to a direct recompute of the returned pairs,
-    rewards equal to the reference formula applied to the returned distances (fp64 on the GPU),
-    RMS state = moments of all N*k distances, no undecided rows."""
-    n, dim, k = 1_000_000, 512, 12
-    g = torch.Generator(device=DEV).manual_seed(5)
-    rep = torch.tanh(torch.randn(n, dim, generator=g, device=DEV))
+    through size-independent properties + a 4 096-query slice against the oracle fixture (the full
+    oracle would take CPU-days): self-match first with distance exactly 0, ascending distances,
+    distinct in-range indices, returned distances equal to a direct recompute of the returned
+    pairs, rewards equal to the reference formula applied to the returned distances (fp64 on the
+    GPU), RMS state = moments of all N*k distances, no undecided rows."""
+    g = golden("knn_scale_1m.npz")
+    rep_cpu = _scale_bank(g)                 # tanh(randn(10^6, 512)), seed 5 (SURVEY §8d C5)
+    n, dim, k = rep_cpu.size(0), rep_cpu.size(1), int(g["k"])
+    assert (n, dim, k) == (1_000_000, 512, 12)
+    rep = rep_cpu.to(DEV)
     args = types.SimpleNamespace(knn_k=k, knn_avg=True, knn_rms=True, knn_clip=0.0)
     rms = xb.RMS(DEV)
     reward, dist, idx = xb.relabel_apt_reward(rep, args, rms=rms, mode="screened", return_knn=True)
@@ -200,7 +214,8 @@ def test_c5_full_size_properties():
     srt = idx.sort(dim=1).values
     assert bool((srt[:, 1:] != srt[:, :-1]).all())
     # returned distances are the direct-difference distances of the returned pairs
-    rows = torch.randint(0, n, (4096,), generator=g, device=DEV)
+    rows = torch.randint(0, n, (4096,), generator=torch.Generator(device=DEV).manual_seed(5),
+                         device=DEV)
     nb_rows = idx[rows].long()
     direct = torch.norm(rep[rows][:, None, :] - rep[nb_rows.reshape(-1)].reshape(4096, k, dim),
                         dim=2, p=2)
@@ -216,12 +231,12 @@ def test_c5_full_size_properties():
     assert rms.n == n0 + bs
     want = torch.log((dist.double() / float(rms.M)).clamp_min(0).mean(dim=1, keepdim=True) + 1.0)
     np.testing.assert_allclose(reward.cpu().numpy(), want.float().cpu().numpy(), rtol=1e-5)
-    # oracle slice: the reference formula (tiled) for 48 queries against the whole bank
-    sub = torch.arange(0, n, n // 48)[:48]
-    rep_cpu = rep.cpu()
-    od, oi = knn_smallest(rep_cpu[sub], rep_cpu, k)
+    # oracle slice: the reference formula (tiled) for a fixed 4 096-query slice against the whole
+    # bank (tests/golden/knn_scale_1m.npz; ~40 CPU-minutes in oracle/gen_scale_golden.py)
+    sub = torch.from_numpy(g["rows"])
+    oracle = (torch.from_numpy(g["dist"]), torch.from_numpy(g["idx"]).long())
     assert_knn_matches(rep_cpu[sub], rep_cpu, k, dist[sub.to(DEV)], idx[sub.to(DEV)],
-                       oracle=(od, oi))
+                       oracle=oracle)
 
 
 @pytest.mark.parametrize("kind", ["duplicates", "out_of_range"])
@@ -290,3 +305,24 @@ def test_dense_trajectory_data_is_rescreened_not_scanned():
     assert diff <= E * L // 500
     assert sum(1 for c in calls if c[0] == "screened") >= 8       # the strided re-screen ran
     assert sum(c[1] for c in calls if c[0] == "exact") <= E * L // 10
+
+
+@pytest.mark.parametrize("n,dim", [(40000, 64), (20000, 512)])
+def test_relabel_from_host_pipeline_equals_device_resident_call(n, dim):
+    """relabel_apt_reward_from_host (pinned host rows -> H2D -> prep -> screen-only -> exact
+    rerank; on N ranks the collectives slot in between) returns what relabel_apt_reward returns
+    for device-resident reps, RMS state included."""
+    x = reps(17, n, dim)
+    args = types.SimpleNamespace(knn_k=12, knn_avg=True, knn_rms=True, knn_clip=0.0)
+    rms_a, rms_b = xb.RMS(DEV), xb.RMS(DEV)
+    want, wd, wi = xb.relabel_apt_reward(x.to(DEV), args, rms=rms_a, mode="screened",
+                                         return_knn=True)
+    host = x.pin_memory()
+    with torch.cuda.device(DEV):
+        got, gd, gi = xb.relabel_apt_reward_from_host(host, args, rms=rms_b, return_knn=True)
+    np.testing.assert_allclose(got.cpu().numpy(), want.cpu().numpy(), rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(gd.cpu().numpy(), wd.cpu().numpy(), rtol=1e-6)
+    diff = (gi.sort(dim=1).values != wi.sort(dim=1).values).any(dim=1).sum().item()
+    assert diff <= n // 1000
+    assert rms_a.n == rms_b.n
+    np.testing.assert_allclose(float(rms_a.M), float(rms_b.M), rtol=1e-6)

@@ -187,3 +187,90 @@ def test_reps_from_host_shards_then_gathers(n):
         p.join(timeout=60)
         assert p.exitcode == 0
     assert all(ok for _, ok in res)
+
+
+class _FakeWatch:
+    """Stopwatch whose 'device time' is rows x a per-rank cost: rank 1 is twice as slow."""
+    cost = {0: 1.0, 1: 2.0}
+
+    def __init__(self):
+        self.rows = 0
+        self.t = 0.0
+
+    def start(self):
+        pass
+
+    def stop(self):
+        from exorl_b200 import relabel
+        b = relabel.last_query_block
+        self.t = (b["hi"] - b["lo"]) * self.cost[dist.get_rank()]
+
+    def elapsed_ms(self):
+        t, self.t = self.t, 0.0
+        return t
+
+
+def _balance_worker(rank, world, port, n, steps, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from exorl_b200 import relabel
+
+        class Stages(_OracleStages):
+            stopwatch = _FakeWatch
+
+        g = torch.Generator().manual_seed(5)
+        rep = torch.tanh(torch.randn(n, 16, generator=g))
+        args = types.SimpleNamespace(knn_k=4, knn_avg=True, knn_rms=True, knn_clip=0.0)
+        blocks, rewards = [], []
+        for _ in range(steps):
+            rms = types.SimpleNamespace(M=torch.zeros(1), S=torch.ones(1), n=1e-4)
+            r = relabel.relabel_apt_reward(rep, args, rms=rms, exchange="queries", stages=Stages)
+            rewards.append(r.numpy())
+            blocks.append((relabel.last_query_block["lo"], relabel.last_query_block["hi"]))
+        q.put((rank, blocks, rewards))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_query_blocks_follow_the_measured_rates_and_results_do_not_change():
+    """QueryBalance: rank 1 takes twice as long per row, so its query block shrinks towards one
+    third of the rows (cut at multiples of the 256-row quantum); rewards stay those of the
+    unsharded computation at every step and identical on both ranks."""
+    from oracle import RmsState, pbe_reward
+    n, steps = 4096, 7
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_balance_worker, args=(r, 2, port, n, steps, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=300) for _ in range(2)], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    g = torch.Generator().manual_seed(5)
+    rep = torch.tanh(torch.randn(n, 16, generator=g))
+    want = pbe_reward(rep, rep, RmsState(), 4, True, True, 0.0).numpy()
+    (_, b0, r0), (_, b1, r1) = res
+    assert b0[0] == (0, n // 2) and b1[0] == (n // 2, n)               # first step: equal split
+    for s in range(steps):
+        assert b0[s][1] == b1[s][0] and b0[s][0] == 0 and b1[s][1] == n    # a partition
+        assert b0[s][1] % 256 == 0
+        np.testing.assert_allclose(r0[s], want, rtol=1e-5, atol=1e-7)
+        np.testing.assert_array_equal(r0[s], r1[s])
+    share1 = (b1[-1][1] - b1[-1][0]) / n
+    assert abs(share1 - 1 / 3) < 0.07, (b0, b1)
+
+
+def test_balanced_bounds_quantum_and_fallback():
+    from exorl_b200.relabel import balanced_bounds, shard_bounds
+    b = balanced_bounds(1_000_000, [1.0, 1.1, 0.9, 1.0], quantum=256, min_rows=12)
+    assert b[0][0] == 0 and b[-1][1] == 1_000_000
+    assert all(x[1] == y[0] for x, y in zip(b, b[1:]))
+    assert all(x[1] % 256 == 0 for x in b[:-1])
+    sizes = [hi - lo for lo, hi in b]
+    assert sizes[1] > sizes[0] > sizes[2] and abs(sizes[0] - 250_000) < 512
+    # a block that would fall below min_rows -> equal split
+    assert balanced_bounds(100, [1.0, 1e-6], quantum=256, min_rows=12) == \
+        [shard_bounds(100, 2, r) for r in range(2)]
