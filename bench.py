@@ -46,8 +46,10 @@ def parse():
                     help="skip the C1-C4 block (BASELINE configs 1-4) of the 1-GPU line")
     ap.add_argument("--no-exchange-ab", action="store_true",
                     help="skip the one-step timings of the bank-sharded exchanges (N > 1)")
-    ap.add_argument("--no-balance", action="store_true",
-                    help="equal query blocks per rank instead of rate-proportional ones (A/B)")
+    ap.add_argument("--balance", action="store_true",
+                    help="rate-proportional query blocks per rank instead of equal ones (A/B)")
+    ap.add_argument("--observe-balance", action="store_true",
+                    help="equal query blocks, but collect and report the per-rank block times")
     ap.add_argument("--stage-times", action="store_true",
                     help="after the timed runs, one extra step with per-stage CUDA events (stderr)")
     return ap.parse_args()
@@ -187,6 +189,11 @@ def run_ours(a, rank, world, local_rank):
 
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
+    # stdout carries exactly ONE line (the contract): libraries that write to fd 1 (NCCL prints
+    # its version banner there at some NCCL_DEBUG levels) are sent to stderr instead
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         # NCCL prints its version banner to STDOUT at NCCL_DEBUG=VERSION; keep stdout to the one
         # JSON line of the contract
@@ -233,17 +240,18 @@ def run_ours(a, rank, world, local_rank):
         return ms
 
     rms = xb.RMS(dev)
+    balance = "observe" if a.observe_balance else a.balance
 
     def step():
         return xb.relabel_apt_reward(rep, args, rms=rms, exchange=a.exchange, mode="screened",
-                                     balance=not a.no_balance)
+                                     balance=balance)
 
     def step_e2e():
         # host buffers in, host buffer out: every rank copies ITS rows from pinned host memory,
         # prepares them, the fp16 operand is all-gathered over NVLink and the screen starts while
         # the fp32 rows follow behind it (relabel_apt_reward_from_host)
         r = xb.relabel_apt_reward_from_host(rep_host, args, rms=rms, rep_out=rep,
-                                            balance=not a.no_balance)
+                                            balance=balance)
         reward_host.copy_(r, non_blocking=True)
 
     for _ in range(a.warmup):
@@ -300,9 +308,13 @@ def run_ours(a, rank, world, local_rank):
         tmr = StageTimer()
         xb.relabel_apt_reward(rep, args, rms=rms, exchange=a.exchange, mode="screened", timer=tmr)
         st = tmr.summary()
-        if rank == 0:
-            print("stage times (ms): " + json.dumps({k: round(v, 3) for k, v in st.items()}),
-                  file=sys.stderr)
+        tmr2 = StageTimer()
+        xb.relabel_apt_reward_from_host(rep_host, args, rms=rms, rep_out=rep, balance=balance,
+                                        timer=tmr2)
+        st2 = tmr2.summary()
+        print(f"rank {rank} stage times (ms): " + json.dumps({k: round(v, 3) for k, v in st.items()})
+              + " | from_host: " + json.dumps({k: round(v, 3) for k, v in st2.items()}),
+              file=sys.stderr, flush=True)
 
     secondary = None
     if world == 1 and not a.no_secondary:
@@ -319,8 +331,10 @@ def run_ours(a, rank, world, local_rank):
     if world > 1 and a.exchange in ("auto", "queries"):
         from exorl_b200 import relabel as xrel
         bal = xrel.query_balance(None, a.n, world, a.k)
-        query_blocks = {"balance": not a.no_balance,
+        query_blocks = {"balance": balance,
                         "rows_per_rank": [hi - lo for lo, hi in bal.bounds]}
+        if a.observe_balance or a.stage_times:
+            query_blocks["log_rows_ms"] = bal.log[-12:]
     if rank == 0:
         sustained, burst, src = peaks()
         nb_local = a.n // world
@@ -366,7 +380,8 @@ def run_ours(a, rank, world, local_rank):
                                   "headline_exchange": a.exchange, **exchange_ab}
         if secondary is not None:
             out["secondary"] = secondary
-        print(json.dumps(out))
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(out) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
 

@@ -43,9 +43,9 @@ def main():
     # producers emit the same operand), query-block partition
     rep_host = rep.cpu().pin_memory()
     from exorl_b200 import relabel as xrel
-    # "queries" runs three times so that the rate-proportional query blocks (QueryBalance) have
+    # "balanced" runs three times so that the rate-proportional query blocks (QueryBalance) have
     # moved away from the equal split by the last run; "from_host" is the end-to-end pipeline
-    for exchange in ("queries", "queries", "queries", "from_host", "from_host", "prepared",
+    for exchange in ("queries", "balanced", "balanced", "balanced", "from_host", "prepared",
                      "lists", "auto", "all_to_all", "all_gather"):
         rms = xb.RMS(dev)
         if exchange == "from_host":
@@ -53,6 +53,9 @@ def main():
         elif exchange == "prepared":
             out = xb.relabel_apt_reward(xb.prepare_rep(rep), args, rms=rms, exchange="queries",
                                         return_knn=True)
+        elif exchange == "balanced":
+            out = xb.relabel_apt_reward(rep, args, rms=rms, exchange="queries", mode="screened",
+                                        return_knn=True, balance=True)
         else:
             out = xb.relabel_apt_reward(rep, args, rms=rms, exchange=exchange, mode="screened",
                                         return_knn=True)
@@ -63,7 +66,7 @@ def main():
         assert rms.n == rms0.n
         if exchange == "all_gather":            # every rank holds all rows
             lo, hi = 0, a.n
-        elif exchange in ("queries", "auto", "prepared", "from_host"):
+        elif exchange in ("queries", "balanced", "auto", "prepared", "from_host"):
             lo, hi = xrel.last_query_block["lo"], xrel.last_query_block["hi"]   # balanced block
         else:                                    # rank r finalised query block r
             lo, hi = xrel.shard_bounds(a.n, world, rank)

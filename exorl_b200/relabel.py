@@ -181,31 +181,58 @@ class QueryBalance:
     """Per-rank query-block sizes of the 'queries' partition, proportional to each rank's
     measured kNN rate (rows per millisecond) in the previous step.
 
-    Under the 1 kW power cap the GPUs of one box settle at different SM clocks (driver record of
-    round 1: per-rank minimum 1 237-1 252 MHz against a median of 1 402-1 462), so equal blocks
-    make every step wait for the slowest rank.  Each rank times its block kNN with CUDA events;
+    Meant for ranks that differ PERSISTENTLY (mixed parts, a throttled GPU).  On one box of
+    8 x B200 under the 1 kW power cap they do not: measured per-rank block times at equal blocks
+    are 89-98 ms with a different slowest rank every step (12 steps x 8 ranks in
+    profiles/r02b_balance_observe_n8.json; per-rank means within 1.5 %), so the step pays for the
+    maximum of eight noisy times whatever the split, and chasing last step's rates only adds
+    noise (97.3 vs 96.3 ms per step).  Hence off by default.  Each rank times its block kNN with
+    CUDA events;
     the time of step s rides along in the RMS-sums all-reduce of step s+1 (no extra collective,
     no host sync), so every rank derives the SAME bounds for step s+2.  Damped (`gain`) because
     the kernel's time is not exactly linear in its rows (waves of 148 CTA pairs)."""
 
     def __init__(self, n, world, quantum=256, min_rows=1, gain=0.7):
         self.n, self.world, self.quantum, self.min_rows, self.gain = n, world, quantum, min_rows, gain
+        self.observe_only = False     # collect the times, keep the equal split (measurements)
+        self.log = []                 # (rows per rank, ms per rank) of every settled step
         self.shares = [1.0 / world] * world
         self.bounds = [shard_bounds(n, world, r) for r in range(world)]
         self.prev_bounds = None       # bounds of the previous call (what the stopwatch timed)
-        self.pending = None           # (device vector of the ranks' times, bounds they timed)
+        self.pending = []             # (step, host copy of the ranks' times, bounds they timed)
+        self.step = 0
         self.watch = None
 
+    def push(self, times, timed_bounds):
+        """Queue the all-reduced per-rank times of this call (a device vector) for a later call:
+        an asynchronous copy into pinned memory, never a sync."""
+        if times.is_cuda:
+            host = torch.empty(times.shape, dtype=times.dtype, pin_memory=True)
+            host.copy_(times, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+        else:
+            host, ev = times.clone(), None
+        self.pending.append((self.step, host, ev, timed_bounds))
+
     def settle(self):
-        """Fold in the times the previous call all-reduced (identical on every rank, so every
-        rank derives the same bounds); by now that call's kernels have long finished."""
-        if self.pending is not None:
-            (times, timed_bounds), self.pending = self.pending, None
-            self.update(times.tolist(), timed_bounds)
+        """Fold in the times all-reduced TWO calls ago.  A fixed lag, not "whatever has arrived",
+        because every rank must apply the same updates at the same step to derive the same
+        bounds; two calls back the copy has always landed (the host runs at most one step
+        ahead of the device through the rewards it returns), so the wait below is a formality."""
+        self.step += 1
+        while self.pending and self.pending[0][0] <= self.step - 2:
+            _, host, ev, timed_bounds = self.pending.pop(0)
+            if ev is not None:
+                ev.synchronize()
+            self.update(host.tolist(), timed_bounds)
 
     def update(self, times_ms, timed_bounds):
         """`times_ms[r]` = rank r's block time under `timed_bounds` (0 = not measured)."""
         if timed_bounds is None or any(t <= 0.0 for t in times_ms):
+            return
+        self.log.append(([b - a for a, b in timed_bounds], [round(t, 3) for t in times_ms]))
+        if self.observe_only:
             return
         rates = [(b - a) / t for (a, b), t in zip(timed_bounds, times_ms)]
         tot = sum(rates)
@@ -303,14 +330,14 @@ def _finish_block(d_mine, i_mine, n, lo, hi, in_split, world, k, avg, use_rms, c
     if balance is not None:
         # read at the start of the next call (no sync in this one); the times are those of the
         # PREVIOUS call's blocks
-        balance.pending = (times, balance.prev_bounds)
+        balance.push(times, balance.prev_bounds)
     if return_knn:
         return reward, d_mine, i_mine
     return reward
 
 
 def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="auto",
-                       return_knn=False, stages=_CudaStages, timer=None, balance=True):
+                       return_knn=False, stages=_CudaStages, timer=None, balance=False):
     """APT reward (N, 1) of every row of `rep` against all N rows, identical on every rank.
 
     `rep` is the (N, c) fp32 rep tensor or a PreparedRep (exorl_b200.rep: e.g. icm_get_rep of the
@@ -320,8 +347,10 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="a
     `args` exposes knn_k, knn_avg, knn_rms, knn_clip like PBE; `rms` is the running-moment state
     (updated once with bs = N*k in avg mode, N otherwise).  Works without an initialised process
     group (single shard).  `balance`: in the 'queries' partition, size the per-rank query blocks
-    by the ranks' measured rates (QueryBalance) instead of equally; with `return_knn` the rows of
-    the returned block are `relabel.last_query_block`."""
+    by the ranks' measured rates (QueryBalance) instead of equally — off by default: on 8 x B200
+    the per-rank times fluctuate from step to step (power cap) rather than differing persistently,
+    so following them loses (profiles/r02b_balance_observe_n8.json); "observe" only records the
+    times.  With `return_knn` the rows of the returned block are `relabel.last_query_block`."""
     if exchange not in ("auto", "lists", "all_gather", "all_to_all", "queries"):
         raise ValueError("exchange must be 'auto', 'lists', 'all_gather', 'all_to_all' or "
                          "'queries'")
@@ -363,6 +392,7 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="a
     if world > 1 and exchange == "queries":
         bal = query_balance(group, n, world, k) if balance else None
         if bal is not None:
+            bal.observe_only = balance == "observe"
             bal.settle()
         bounds = bal.bounds if bal else [shard_bounds(n, world, r) for r in range(world)]
         in_split = [b - a for a, b in bounds]
@@ -449,7 +479,7 @@ def _side_stream(dev):
 
 
 def relabel_apt_reward_from_host(rep_host, args, rms=None, group=None, rep_out=None,
-                                 return_knn=False, balance=True):
+                                 return_knn=False, balance=False, timer=None):
     """`relabel_apt_reward` for reps that live in (pinned) HOST memory — the end-to-end form of
     config 5: (N, c) fp32 rows in, (N, 1) rewards out, identical on every rank.
 
@@ -479,13 +509,17 @@ def relabel_apt_reward_from_host(rep_host, args, rms=None, group=None, rep_out=N
                                   return_knn=return_knn, balance=balance)
     lib = _lib.load()
     lo, hi = shard_bounds(n, world, rank)
+    tm = timer.mark if timer is not None else (lambda name: None)
     with torch.cuda.device(dev):
         pre = PreparedRep(n, dim, dev, rep=rep_out)
+        tm("start")
         rep_out[lo:hi].copy_(rep_host[lo:hi], non_blocking=True)                        # 1
+        tm("h2d_own_rows")
         _lib.check(lib.exb_knn_prep_f16(                                                 # 2
             _lib.ptr(rep_out[lo:hi]), hi - lo, dim, _lib.ptr(pre.f16[lo:hi]),
             _lib.ptr(pre.half_norm[lo:hi]), _lib.ptr(pre.round_err[lo:hi]),
             _lib.ptr(pre.scalars), _lib.stream_ptr(dev)))
+        tm("prep_own_rows")
         fp32_rows = None
         if world > 1:
             dist.all_gather_into_tensor(pre.f16, pre.f16[lo:hi], group=group)            # 3
@@ -497,8 +531,10 @@ def relabel_apt_reward_from_host(rep_host, args, rms=None, group=None, rep_out=N
             with torch.cuda.stream(side):
                 fp32_rows = dist.all_gather_into_tensor(rep_out, rep_out[lo:hi], group=group,
                                                         async_op=True)
+            tm("allgather_f16_operand")
         bal = query_balance(group, n, world, k) if (balance and world > 1) else None
         if bal is not None:
+            bal.observe_only = balance == "observe"
             bal.settle()
         bounds = bal.bounds if bal else [shard_bounds(n, world, r) for r in range(world)]
         qlo, qhi = bounds[rank]
@@ -513,16 +549,19 @@ def relabel_apt_reward_from_host(rep_host, args, rms=None, group=None, rep_out=N
         val, idx, cnt, ha, ea, sc = knn_screen_lists(block, pre, k)                      # 4
         if bal is not None:
             bal.watch.stop()
+        tm("screen")
         if fp32_rows is not None:
             fp32_rows.wait()              # the current stream waits for the fp32 bank rows
+        tm("wait_f32_rows")
         d_mine, i_mine = knn_rerank_lists(rep_out if block is pre else rep_out[qlo:qhi], rep_out,
                                           k, val[None], idx[None], cnt[None], [0], ha, ea, sc)
+        tm("rerank")
         if world == 1:
             reward = _CudaStages.reward(d_mine, k, avg, use_rms, clip, rms)
             return (reward, d_mine, i_mine) if return_knn else reward
         out = _finish_block(d_mine, i_mine, n, qlo, qhi, [b - a for a, b in bounds], world, k,
-                            avg, use_rms, clip, rms, group, _CudaStages, lambda name: None,
-                            return_knn, balance=bal, prev_ms=prev_ms)
+                            avg, use_rms, clip, rms, group, _CudaStages, tm, return_knn,
+                            balance=bal, prev_ms=prev_ms)
         if bal is not None:
             bal.prev_bounds = bounds
         return out

@@ -225,7 +225,8 @@ def _balance_worker(rank, world, port, n, steps, q):
         blocks, rewards = [], []
         for _ in range(steps):
             rms = types.SimpleNamespace(M=torch.zeros(1), S=torch.ones(1), n=1e-4)
-            r = relabel.relabel_apt_reward(rep, args, rms=rms, exchange="queries", stages=Stages)
+            r = relabel.relabel_apt_reward(rep, args, rms=rms, exchange="queries", stages=Stages,
+                                           balance=True)
             rewards.append(r.numpy())
             blocks.append((relabel.last_query_block["lo"], relabel.last_query_block["hi"]))
         q.put((rank, blocks, rewards))
