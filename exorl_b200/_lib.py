@@ -82,6 +82,8 @@ SIGNATURES = {
     "exb_rnd_reward_f32": (_c.c_int, [_vp, _vp, _i64, _c.c_int, _f32, _vp, _vp, _vp, _vp, _vp,
                                       _vp, _sz, _vp]),
     "exb_take_kth": (_c.c_int, [_vp, _i64, _c.c_int, _vp, _vp]),
+    "exb_proto_reward_f32": (_c.c_int, [_vp, _i64, _vp, _i64, _c.c_int, _c.c_int, _c.c_int, _vp, _vp,
+                                        _vp, _vp, _sz, _vp]),
     "exb_proto_sample_f32": (_c.c_int, [_vp, _i64, _vp, _c.c_int, _c.c_int, _vp, _u64, _u64, _vp,
                                         _i64, _i64, _vp, _vp, _vp]),
     "exb_replay_gather": (_c.c_int, [_vp, _i64, _c.POINTER(GatherCol), _c.c_int, _vp, _vp,

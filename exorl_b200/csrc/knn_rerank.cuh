@@ -29,6 +29,7 @@ struct RerankStatus {   // device, zeroed per call (24 bytes: the prep kernel cl
 // updated mean of ALL rows, so it stays a separate, fully parallel launch.)
 struct FusedPbe {
   int on, avg, use_rms, use_clip;
+  int raw_kth;           // no RMS, no clip, no log: reward = the k-th distance (proto.py:117-118)
   float clip;
   RmsParams rms;
   float* out_reward;     // [nq]
@@ -564,7 +565,8 @@ knn_rerank_kernel(const RerankParams p) {
           acc += v;
           r = v;
         }
-        if (lane == 0) f.out_reward[row] = logf((f.avg ? acc / (float)k : r) + 1.0f);
+        if (lane == 0)
+          f.out_reward[row] = f.raw_kth ? r : logf((f.avg ? acc / (float)k : r) + 1.0f);
       }
       return;
     }

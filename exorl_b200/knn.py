@@ -629,5 +629,21 @@ def _take_kth(dist, k):
 
 
 def _proto_reward_impl(z, queue, topk, mode):
-    dist, _ = _knn_topk_impl(z, queue, topk, 0, mode, False)
-    return _take_kth(dist, topk)
+    """CUDA implementation of torch.ops.exorl_b200.proto_reward (exb_proto_reward_f32)."""
+    lib = _lib.load()
+    nq, nb, dim = z.size(0), queue.size(0), z.size(1)
+    if nq == 0 or (mode != "exact" and _streaming(nq, nb, dim, topk)):
+        # dataset-scale input: kNN with the host-side overflow check, then the k-th column
+        dist, _ = _knn_topk_impl(z, queue, topk, 0, mode, False)
+        return _take_kth(dist, topk)
+    dev = z.device
+    with torch.cuda.device(dev):
+        out = torch.empty(nq, 1, dtype=torch.float32, device=dev)
+        dist = torch.empty(nq, topk, dtype=torch.float32, device=dev)
+        idx = torch.empty(nq, topk, dtype=torch.int32, device=dev)
+        need = lib.exb_apt_reward_workspace_bytes(nq, nb, dim, topk)
+        ws, _ = _lib.Workspace.get(dev, "apt_reward", need, zero_init=True)
+        _lib.check(lib.exb_proto_reward_f32(
+            _lib.ptr(z), nq, _lib.ptr(queue), nb, dim, topk, _MODE_ID[mode], _lib.ptr(out),
+            _lib.ptr(dist), _lib.ptr(idx), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+    return out

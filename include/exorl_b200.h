@@ -275,6 +275,14 @@ int exb_proto_sample_f32(const float* z, int64_t batch, const float* protos, int
                          int64_t queue_rows, int64_t queue_ptr, int64_t* out_candidates,
                          float* out_prob, exb_stream_t stream);
 
+/* ProtoRL reward as ONE call (proto.py:115-118): out_reward[i] = distance of z[i] to its k-th
+ * nearest queue row; the neighbours are also returned.  mode and workspace as exb_apt_reward_f32
+ * (exb_apt_reward_workspace_bytes). */
+int exb_proto_reward_f32(const float* z, int64_t nq, const float* queue, int64_t nb, int dim, int k,
+                         int mode, float* out_reward /* [nq] */, float* out_dist /* [nq,k] */,
+                         int32_t* out_idx /* [nq,k] */, void* workspace, size_t workspace_bytes,
+                         exb_stream_t stream);
+
 /* ProtoRL reward: k-th smallest distance only, no RMS/clip/log (proto.py:115-118). */
 int exb_take_kth(const float* knn_dist, int64_t nq, int k, float* out /* [nq] */,
                  exb_stream_t stream);

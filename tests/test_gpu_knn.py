@@ -190,7 +190,7 @@ def test_screened_handles_many_ties_through_fallback():
     q = torch.zeros(1024, 128)                            # every queue row at distance 1
     got = xb.proto_knn_reward(z.to(DEV), q.to(DEV), 3, mode="screened")
     _close(got.cpu().numpy(), proto_reward(z, q, 3).numpy())
-    und, invalid, _, _ = xknn.screened_status(torch.device(DEV))
+    und, invalid, _, _ = xknn.screened_status(torch.device(DEV), key="apt_reward")
     assert und == 256 and invalid == 0
 
 
@@ -436,3 +436,51 @@ def test_auto_mode_outside_the_screen_limits(b, d, k):
             xb.knn_topk(xd, xd, k, mode="screened")
     with pytest.raises(ValueError):
         xb.knn_topk(xd, xd, 33)
+
+
+def test_library_graph_cache_hits_misses_and_bypass():
+    """The per-update chain is replayed from a graph cached inside the library, keyed by the
+    call's pointers and shapes.  Same tensor again -> cache hit (the RMS state still advances,
+    it lives on the device); a stream of never-repeating tensors -> the cache gives up and the
+    plain launch chain serves the calls; results equal the oracle's either way."""
+    p = _pbe(0.0, 12, True, True)
+    st = RmsState()
+    x = reps(321, 512, 64)
+    xd = x.to(DEV)
+    out = torch.empty(0)
+    for call in range(6):                       # first call captures, the rest replay
+        got = p(xd)
+        want = pbe_reward(x, x, st, 12, True, True, 0.0)
+        _close(got.cpu().numpy(), want.numpy())
+        assert p.rms.n == st.n
+    keep = []                                   # hold every tensor: no address is ever reused
+    for call in range(40):
+        y = reps(400 + call, 256, 32)
+        keep.append(y.to(DEV))
+        got = p(keep[-1])
+        keep.append(got)
+        want = pbe_reward(y, y, st, 12, True, True, 0.0)
+        _close(got.cpu().numpy(), want.numpy())
+    got = p(xd)                                 # and the first tensor still works afterwards
+    _close(got.cpu().numpy(), pbe_reward(x, x, st, 12, True, True, 0.0).numpy())
+    assert p.rms.n == st.n
+    # inside a caller's CUDA graph the kernels are captured into THAT graph
+    pg = _pbe(0.0, 12, True, True)
+    stg = RmsState()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        pg(xd)
+    torch.cuda.current_stream().wait_stream(s)
+    rms_step_calls = 1
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        r = pg(xd)
+    for _ in range(3):
+        g.replay()
+        rms_step_calls += 1
+    torch.cuda.synchronize()
+    for _ in range(rms_step_calls):
+        want = pbe_reward(x, x, stg, 12, True, True, 0.0)
+    _close(r.cpu().numpy(), want.numpy())
+    assert pg.rms.n == stg.n
