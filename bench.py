@@ -341,9 +341,10 @@ def run_ours(a, rank, world, local_rank):
         kernel_ms = sum(kms[i] for i in range(kn.value)) / max(kn.value, 1)
         flops = 2.0 * a.n * nb_local * a.dim
         achieved = flops / (kernel_ms * 1e-3) / 1e12 if kernel_ms > 0 else 0.0
-        # kernels per step: prep, screen, rerank, exact-fallback, fallback-merge, [merge, moments,
-        # rms-apply] or [moments], finish
-        launches_per_step = 7 if world == 1 else 9
+        # kernels per step: colstats (one per row set), colstats-reduce, affine, prep (one per row
+        # set), screen, rerank, exact-fallback, fallback-merge, [merge, moments, rms-apply] or
+        # [moments], finish
+        launches_per_step = 10 if world == 1 else 14
         out = {
             "metric": METRIC, "value": a.n * a.steps / (ms * 1e-3), "unit": UNIT,
             "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms / a.steps,

@@ -17,7 +17,8 @@ from .replay import (DeviceReplayBuffer, DeviceReplayLoader, make_replay_loader,
                      make_offline_replay_loader)
 from .relabel import relabel_apt_reward, relabel_apt_reward_from_host, reps_from_host
 from .ingest import read_episode, read_episodes
-from .rep import PreparedRep, icm_get_rep, ln_tanh_rep, normalize_rep, prepare_rep
+from .rep import (PreparedRep, icm_get_rep, ln_tanh_rep, normalize_rep, prepare_rep,
+                  column_affine, column_stats)
 
 __all__ = ["RMS", "PBE", "compute_apt_reward", "knn_topk", "proto_knn_reward", "proto_enqueue",
            "proto_sample_enqueue", "rnd_intr_reward",

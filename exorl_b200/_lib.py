@@ -92,16 +92,22 @@ SIGNATURES = {
     "exb_replay_sample": (_c.c_int, [_u64, _u64, _vp, _vp, _i64, _i64, _c.POINTER(GatherCol),
                                      _c.c_int, _vp, _vp, _c.c_int, _c.c_int, _f32, _vp, _vp, _vp,
                                      _vp]),
+    "exb_knn_colstats_workspace_bytes": (_sz, [_i64, _c.c_int]),
+    "exb_knn_colstats_f32": (_c.c_int, [_vp, _i64, _c.c_int, _vp, _vp, _sz, _vp]),
+    "exb_knn_affine_from_stats": (_c.c_int, [_vp, _c.c_double, _c.c_int, _vp, _vp]),
+    "exb_knn_prep_affine_f16": (_c.c_int, [_vp, _i64, _c.c_int, _vp, _vp, _vp, _vp, _vp, _vp]),
     "exb_npz_open": (_c.c_int, [_c.c_char_p, _c.POINTER(_vp), _c.POINTER(_c.c_int)]),
     "exb_npz_info": (_c.c_int, [_vp, _c.c_int, _c.POINTER(NpzArray)]),
     "exb_npz_read": (_c.c_int, [_vp, _c.c_int, _vp, _i64]),
     "exb_npz_close": (None, [_vp]),
+    "exb_npz_set_inflate_mode": (_c.c_int, [_c.c_int]),
 }
 
 EXB_OK, EXB_EINVAL, EXB_EKRANGE, EXB_EUNSUPPORTED, EXB_ECUDA, EXB_EFALLBACK = range(6)
 MAX_K = 32
 SCREEN_MAX_K = 16
 SCREEN_MAX_DIM = 512
+AFFINE_FLOATS = SCREEN_MAX_DIM + 8
 
 _lock = threading.Lock()
 _lib = None

@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <stdarg.h>
+#include <stdlib.h>
 #include "../../include/exorl_b200.h"
 
 namespace exb {
@@ -47,6 +48,20 @@ struct Carver {
 };
 
 int sm_count();
+
+// A/B switches of the bring-up work (EXB_SCREEN_*, EXB_PDL, EXB_TRUNK_*, EXB_GATHER_BULK).  The
+// product library does not read the environment: knob() returns the default unless the library
+// is built with -DEXB_DEBUG_KNOBS (EXB_EXTRA_NVCC_FLAGS=-DEXB_DEBUG_KNOBS python -m
+// exorl_b200._build --force), which benchmarks/screen_scaling.py and the trace scripts ask for.
+static inline int knob(const char* name, int dflt) {
+#ifdef EXB_DEBUG_KNOBS
+  const char* e = getenv(name);
+  return e ? atoi(e) : dflt;
+#else
+  (void)name;
+  return dflt;
+#endif
+}
 
 // Scalars of a prepared fp16 kNN operand (exb_knn_prep_f16 and the rep producers), max-accumulated
 // over the rows of a call; device struct, zeroed by the caller.

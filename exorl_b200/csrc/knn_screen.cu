@@ -84,6 +84,18 @@ constexpr float SCR_ACC_EPS = 1.0f / 16384.0f + 1.0f / 262144.0f;
 // ------------------------------------------------------------------------------------------
 // PrepScalars {err_max, hn_max, range_flag, pad}: common.cuh (shared with rep_producer.cu)
 
+// Affine record of a range-proof call (device, AFF_FLOATS floats): [0, dim) the column shift mu,
+// [AFF_SCALE] the power-of-two scale s, [AFF_ON] != 0 when the transform applies, [AFF_SPREAD]
+// max |x - mu| it was derived from.  The screen sees s (x - mu): distances are translation
+// invariant and scale by s, the certificate of DESIGN.md §4 is scale free, and the rerank
+// recomputes the survivors from the caller's fp32 rows, so ANY (mu, s) gives the exact answer —
+// the choice only decides how much of the fp16 format the rows use.
+constexpr int AFF_SCALE = EXB_SCREEN_MAX_DIM;
+constexpr int AFF_ON = EXB_SCREEN_MAX_DIM + 1;
+constexpr int AFF_SPREAD = EXB_SCREEN_MAX_DIM + 2;
+constexpr int AFF_FLOATS = EXB_AFFINE_FLOATS;
+constexpr float AFF_EXTRA_REL = 1.0f / 4194304.0f;   // 2^-22, see OpOut::extra_rel
+
 // One warp per row.  VEC: dim % 4 == 0 and 16-byte aligned rows -> every lane issues all of its
 // float4 loads up front (<= 4 for dim <= 512) instead of a dependent scalar loop.  A row with a
 // value outside the fp16 range gets round_err = +inf (the screen then keeps nothing certain for
@@ -93,13 +105,17 @@ __global__ void __launch_bounds__(256)
 knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
                 __half* __restrict__ out, float* __restrict__ half_norm,
                 float* __restrict__ round_err, PrepScalars* __restrict__ sc,
-                unsigned long long* __restrict__ zero16) {
+                unsigned long long* __restrict__ zero16, const float* __restrict__ aff) {
   pdl_launch_dependents();   // per-update chain: the screen's blocks may set up while this runs
   if (zero16 != nullptr && blockIdx.x == 0 && threadIdx.x < 3) zero16[threadIdx.x] = 0ull;
   const int lane = threadIdx.x & 31;
   const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= n) return;
   const float* xr = x + row * dim;
+  // affine-prepared operand (range-proof screen, see colstats below): rows become
+  // s * fl(x - mu) with the call's column shift mu and power-of-two scale s
+  const bool affine = aff != nullptr && aff[AFF_ON] != 0.f;
+  const float scale = affine ? aff[AFF_SCALE] : 1.f;
   if constexpr (VEC) {
     // shared with the rep producers (prep_row.cuh): bit-identical operands
     const float4* x4 = reinterpret_cast<const float4*>(xr);
@@ -110,7 +126,22 @@ knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
       const int c = lane + 32 * i;
       v[0][i] = (c < nv) ? __ldg(x4 + c) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    const OpOut op{out, half_norm, round_err, sc, dpad};
+    OpOut op{out, half_norm, round_err, sc, dpad};
+    if (affine) {
+      const float4* m4 = reinterpret_cast<const float4*>(aff);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int c = lane + 32 * i;
+        if (c < nv) {
+          const float4 m = m4[c];
+          v[0][i].x = __fmul_rn(__fsub_rn(v[0][i].x, m.x), scale);
+          v[0][i].y = __fmul_rn(__fsub_rn(v[0][i].y, m.y), scale);
+          v[0][i].z = __fmul_rn(__fsub_rn(v[0][i].z, m.z), scale);
+          v[0][i].w = __fmul_rn(__fsub_rn(v[0][i].w, m.w), scale);
+        }
+      }
+      op.extra_rel = AFF_EXTRA_REL;
+    }
     emit_rows<1, 4, false>(v, lane, dim, row, 1, nullptr, op);
   } else {
     // scalar path (dim % 4 != 0): fp32 throughout, norm sum rounded to nearest, error sum rounded
@@ -120,6 +151,7 @@ knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
     bool bad = false;
     for (int c = lane; c < dpad; c += 32) {
       float v = (c < dim) ? xr[c] : 0.f;
+      if (affine && c < dim) v = __fmul_rn(__fsub_rn(v, aff[c]), scale);
       bad |= !(fabsf(v) <= 65504.f);
       const __half h = __float2half_rn(v);
       const float hf = __half2float(h);
@@ -136,7 +168,8 @@ knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
     bad = __any_sync(0xffffffffu, bad);
     if (lane == 0) {
       const float hn = bad ? 0.f : 0.5f * nn;
-      const float er = bad ? INFINITY : __fsqrt_ru(ee);   // rounded up: the bound stays rigorous
+      float er = bad ? INFINITY : __fsqrt_ru(ee);   // rounded up: the bound stays rigorous
+      if (affine && !bad) er = affine_round_err(er, nn, AFF_EXTRA_REL);
       half_norm[row] = hn;
       round_err[row] = er;
       if (sc) {
@@ -149,6 +182,167 @@ knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
         if (bad) atomicExch(&sc->range_flag, 1);
       }
     }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Column statistics -> affine record (range-proof screen).
+//
+// One streaming pass over the rows: per-column sum, min and max.  colstats_kernel<E> (E = float4
+// for 16-byte rows, float otherwise) lets thread t own element-column t % ncol of every
+// (blockDim / ncol)-th row of its block's stripe; the row groups of a block are combined in a
+// fixed order and the block writes one partial [3][dim].  colstats_reduce_kernel adds the
+// partials in block order (fp64 sum), so the statistics — and with them the operand — do not
+// depend on scheduling.  affine_kernel turns {sum, min, max} into the record: mu = sum / n,
+// A = max_c max(max_c - mu_c, mu_c - min_c) rounded up, s = 2^(6 - floor(log2 A)) so that
+// s * A lies in [64, 128) (fp16 normal range 2^-14 .. 65504: 9 binades of headroom above, 20
+// below).  Non-finite statistics (a NaN / inf anywhere) leave the transform off; the range flag
+// of the prep then routes the call as before.
+// ------------------------------------------------------------------------------------------
+constexpr int CS_MAX_BLOCKS = 592;      // 4 x 148
+constexpr int CS_ROWS_PER_BLOCK = 256;
+
+// fminf / fmaxf drop a NaN operand; a NaN stays visible through the sum (NaN + x = NaN)
+__device__ __forceinline__ void cs_merge(float& s, float& lo, float& hi, float s2, float lo2,
+                                         float hi2) {
+  s += s2;
+  lo = fminf(lo, lo2);
+  hi = fmaxf(hi, hi2);
+}
+__device__ __forceinline__ void cs_merge(float4& s, float4& lo, float4& hi, const float4 s2,
+                                         const float4 lo2, const float4 hi2) {
+  cs_merge(s.x, lo.x, hi.x, s2.x, lo2.x, hi2.x);
+  cs_merge(s.y, lo.y, hi.y, s2.y, lo2.y, hi2.y);
+  cs_merge(s.z, lo.z, hi.z, s2.z, lo2.z, hi2.z);
+  cs_merge(s.w, lo.w, hi.w, s2.w, lo2.w, hi2.w);
+}
+__device__ __forceinline__ void cs_init(float4& s, float4& lo, float4& hi) {
+  s = make_float4(0.f, 0.f, 0.f, 0.f);
+  lo = make_float4(INFINITY, INFINITY, INFINITY, INFINITY);
+  hi = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+}
+__device__ __forceinline__ void cs_init(float& s, float& lo, float& hi) {
+  s = 0.f; lo = INFINITY; hi = -INFINITY;
+}
+
+// part: [gridDim.x][3][ncol] elements of E (sum, min, max); dynamic smem = 3 * ncol * sizeof(E)
+template <typename E>
+__global__ void __launch_bounds__(512)
+colstats_kernel(const E* __restrict__ x, int64_t n, int ncol, int64_t rows_per_block,
+                E* __restrict__ part) {
+  extern __shared__ __align__(16) unsigned char cs_smem[];
+  E* s_sum = reinterpret_cast<E*>(cs_smem);
+  E* s_lo = s_sum + ncol;
+  E* s_hi = s_lo + ncol;
+  const int groups = blockDim.x / ncol;          // row groups of this block (>= 1)
+  const int g = threadIdx.x / ncol, c = threadIdx.x - g * ncol;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = min(n, r0 + rows_per_block);
+  E sm, lo, hi;
+  cs_init(sm, lo, hi);
+  if (g < groups) {
+    const int64_t st = groups;
+    int64_t r = r0 + g;
+    for (; r + 3 * st < r1; r += 4 * st) {       // four independent loads in flight per thread
+      const E v0 = __ldg(x + r * ncol + c);
+      const E v1 = __ldg(x + (r + st) * ncol + c);
+      const E v2 = __ldg(x + (r + 2 * st) * ncol + c);
+      const E v3 = __ldg(x + (r + 3 * st) * ncol + c);
+      cs_merge(sm, lo, hi, v0, v0, v0);
+      cs_merge(sm, lo, hi, v1, v1, v1);
+      cs_merge(sm, lo, hi, v2, v2, v2);
+      cs_merge(sm, lo, hi, v3, v3, v3);
+    }
+    for (; r < r1; r += st) {
+      const E v = __ldg(x + r * ncol + c);
+      cs_merge(sm, lo, hi, v, v, v);
+    }
+  }
+  for (int gg = 0; gg < groups; ++gg) {          // fixed combination order
+    if (g == gg) {
+      if (gg == 0) {
+        s_sum[c] = sm; s_lo[c] = lo; s_hi[c] = hi;
+      } else {
+        E a = s_sum[c], b = s_lo[c], d = s_hi[c];
+        cs_merge(a, b, d, sm, lo, hi);
+        s_sum[c] = a; s_lo[c] = b; s_hi[c] = d;
+      }
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x < ncol) {
+    E* o = part + (int64_t)blockIdx.x * 3 * ncol;
+    o[c] = s_sum[c];
+    o[ncol + c] = s_lo[c];
+    o[2 * ncol + c] = s_hi[c];
+  }
+}
+
+// stats: [3][dim] floats (sum, min, max) over the partials of up to two row sets; one thread per
+// column.  A partial block is [3][dim] floats whatever E was (float4 columns are 4 float columns).
+__global__ void colstats_reduce_kernel(const float* __restrict__ part_a, int blocks_a,
+                                       const float* __restrict__ part_b, int blocks_b, int dim,
+                                       float* __restrict__ stats) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= dim) return;
+  double sm = 0.0;
+  float lo = INFINITY, hi = -INFINITY;
+  for (int side = 0; side < 2; ++side) {
+    const float* p = side ? part_b : part_a;
+    const int nblk = side ? blocks_b : blocks_a;
+    for (int b = 0; b < nblk; ++b) {
+      const float* q = p + (int64_t)b * 3 * dim;
+      sm += (double)q[c];
+      lo = fminf(lo, q[dim + c]);
+      hi = fmaxf(hi, q[2 * dim + c]);
+    }
+  }
+  stats[c] = (float)sm;
+  stats[dim + c] = lo;
+  stats[2 * dim + c] = hi;
+}
+
+// One block of EXB_SCREEN_MAX_DIM threads.
+__global__ void __launch_bounds__(EXB_SCREEN_MAX_DIM)
+affine_kernel(const float* __restrict__ stats, double n_rows, int dim, float* __restrict__ aff) {
+  __shared__ float s_max[EXB_SCREEN_MAX_DIM / 32];
+  __shared__ int s_bad[EXB_SCREEN_MAX_DIM / 32];
+  const int c = threadIdx.x;
+  float mu = 0.f, spread = 0.f;
+  int bad = 0;
+  if (c < dim) {
+    const float sm = stats[c], lo = stats[dim + c], hi = stats[2 * dim + c];
+    mu = (float)((double)sm / n_rows);
+    // mu may fall outside [lo, hi] by rounding: take the larger one-sided distance, rounded up
+    spread = fmaxf(__fsub_ru(hi, mu), __fsub_ru(mu, lo));
+    bad = !(fabsf(sm) < INFINITY) || !(fabsf(lo) < INFINITY) || !(fabsf(hi) < INFINITY) ||
+          !(spread < INFINITY);
+  }
+  float wm = spread;
+  int wb = bad;
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    wm = fmaxf(wm, __shfl_xor_sync(0xffffffffu, wm, off));
+    wb |= __shfl_xor_sync(0xffffffffu, wb, off);
+  }
+  if ((c & 31) == 0) { s_max[c >> 5] = wm; s_bad[c >> 5] = wb; }
+  __syncthreads();
+  float a = 0.f;
+  int any_bad = 0;
+  for (int w = 0; w < EXB_SCREEN_MAX_DIM / 32; ++w) { a = fmaxf(a, s_max[w]); any_bad |= s_bad[w]; }
+  const bool on = !any_bad && a > 0.f;
+  float scale = 1.f;
+  if (on) {
+    int e = 6 - ilogbf(a);                       // s * a in [64, 128)
+    e = e < -100 ? -100 : (e > 100 ? 100 : e);
+    scale = ldexpf(1.f, e);
+  }
+  aff[c] = (on && c < dim) ? mu : 0.f;
+  if (c == 0) {
+    aff[AFF_SCALE] = scale;
+    aff[AFF_ON] = on ? 1.f : 0.f;
+    aff[AFF_SPREAD] = a;
+    for (int i = AFF_SPREAD + 1; i < AFF_FLOATS; ++i) aff[i] = 0.f;
   }
 }
 
@@ -1048,10 +1242,7 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
   if (fbs * k > 512) fbs = 512 / k;
   pl->fb_splits = fbs < 1 ? 1 : fbs;
   // ---- latency mode: few query tiles, a bank that one wave of 64-row tiles (x <= 8) covers
-  static const int lat_enabled = [] {
-    const char* e = getenv("EXB_SCREEN_LAT");
-    return e ? atoi(e) : 1;
-  }();
+  static const int lat_enabled = knob("EXB_SCREEN_LAT", 1);
   pl->lat = false;
   {
     const int mt = (int)((nq + SCR_M - 1) / SCR_M);
@@ -1078,10 +1269,7 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
   pl->m_tiles = (int)((nq + SCR_M - 1) / SCR_M);
   // CTA pairs (cta_group::2) halve each CTA's share of the bank-tile traffic and leave room for a
   // 4-deep TMA ring; EXB_SCREEN_CG=1 forces the single-CTA kernel (A/B measurements).
-  static const int forced_cg = [] {
-    const char* e = getenv("EXB_SCREEN_CG");
-    return e ? atoi(e) : 0;
-  }();
+  static const int forced_cg = knob("EXB_SCREEN_CG", 0);
   pl->cg = (forced_cg == 1 || forced_cg == 2) ? forced_cg : (pl->m_tiles >= 2 ? 2 : 1);
   pl->m_tiles = (pl->m_tiles + pl->cg - 1) / pl->cg * pl->cg;
   int splits = sm_count() / pl->m_tiles;
@@ -1094,10 +1282,7 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
     // do not finish in lock-step, so the wave model does not hold, and every extra range restarts
     // the k-th-best chain.  Kept as an A/B knob only (EXB_SCREEN_WAVESPLITS=1..4).
     splits = 1;
-    static const int wave_splits = [] {
-      const char* e = getenv("EXB_SCREEN_WAVESPLITS");
-      return e ? atoi(e) : 0;
-    }();
+    static const int wave_splits = knob("EXB_SCREEN_WAVESPLITS", 0);
     if (wave_splits > 0) splits = wave_splits > 4 ? 4 : wave_splits;
     if (splits > pl->n_tiles) splits = pl->n_tiles;
   }
@@ -1109,8 +1294,7 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
   // -> 2 (four epilogue warps: fewest instructions, the kernel is power-bound there; measured 762
   // vs 769 ms on 1M rows).  EXB_SCREEN_FILTER=2|3 forces one of them (A/B).
   static const int long_filt = [] {
-    const char* e = getenv("EXB_SCREEN_FILTER");
-    const int v = e ? atoi(e) : 0;
+    const int v = knob("EXB_SCREEN_FILTER", 0);
     return (v == 2 || v == 3) ? v : 0;
   }();
   pl->filt = pl->tiles_per_split <= 16 ? 1
@@ -1125,10 +1309,7 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
   // queries: 13 waves + 15 pairs) its query tiles are cut into 2-4 bank ranges so that the idle
   // SMs take part.  Only those rows pay for restarted k-th-best chains and extra lists.
   pl->tail_splits = 0; pl->full_units = 0; pl->tail_tps = 0;
-  static const int tail_env = [] {
-    const char* e = getenv("EXB_SCREEN_TAIL");   // A/B: 0 = off
-    return e ? atoi(e) : 1;
-  }();
+  static const int tail_env = knob("EXB_SCREEN_TAIL", 1);   // A/B: 0 = off
   if (tail_env && pl->filt == 2 && pl->splits == 1) {
     const int slots = sm_count() / pl->cg, units = pl->m_tiles / pl->cg;
     const int full = units / slots * slots, rem = units - full;
@@ -1189,10 +1370,7 @@ static void launch_rerank(const RerankParams& rp, unsigned grid, int ni, cudaStr
 template <typename... KArgs, typename... Args>
 static cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
                               cudaStream_t st, Args... args) {
-  static const int pdl_on = [] {
-    const char* e = getenv("EXB_PDL");
-    return e ? atoi(e) : 0;
-  }();
+  static const int pdl_on = knob("EXB_PDL", 0);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;
@@ -1224,6 +1402,10 @@ struct ScreenWs {
   double2* pbe_partials;   // fused per-update epilogue: one per rerank block
   float* fb_d2;
   int* fb_idx;
+  float* aff;         // streaming: affine record of the call (AFF_FLOATS)
+  float* cs_stats;    // streaming: [3][dim] column statistics
+  float* cs_part_b;   // streaming: [CS_MAX_BLOCKS][3][dim] partials of the bank / of the queries
+  float* cs_part_q;
 };
 
 static size_t carve_screen(void* ws, int64_t nq, int64_t nb, const ScreenPlan& pl, int k,
@@ -1252,19 +1434,63 @@ static size_t carve_screen(void* ws, int64_t nq, int64_t nb, const ScreenPlan& p
   o->fb_rows = cv.take<int>(pl.fb_cap);
   o->fb_d2 = cv.take<float>((size_t)pl.fb_cap * pl.fb_splits * k);
   o->fb_idx = cv.take<int>((size_t)pl.fb_cap * pl.fb_splits * k);
+  const size_t part = pl.lat ? 0 : (size_t)CS_MAX_BLOCKS * 3 * pl.dpad;
+  o->aff = cv.take<float>(pl.lat ? 0 : AFF_FLOATS);
+  o->cs_stats = cv.take<float>(pl.lat ? 0 : 3 * (size_t)pl.dpad);
+  o->cs_part_b = cv.take<float>(part);
+  o->cs_part_q = cv.take<float>(same ? 0 : part);
   return cv.off + 256;
 }
 
 static int launch_prep(const float* x, int64_t n, int dim, int dpad, __half* out, float* hn,
                        float* er, PrepScalars* sc, cudaStream_t st,
-                       unsigned long long* zero16 = nullptr) {
+                       unsigned long long* zero16 = nullptr, const float* aff = nullptr) {
   const bool vec = (dim % 4 == 0) && (((uintptr_t)x & 15) == 0) && dim <= 512;
   if (vec)
     knn_prep_kernel<true><<<(unsigned)((n + 7) / 8), 256, 0, st>>>(x, n, dim, dpad, out, hn,
-                                                                   er, sc, zero16);
+                                                                   er, sc, zero16, aff);
   else
     knn_prep_kernel<false><<<(unsigned)((n + 7) / 8), 256, 0, st>>>(x, n, dim, dpad, out, hn,
-                                                                    er, sc, zero16);
+                                                                    er, sc, zero16, aff);
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}
+
+// Blocks launch_colstats uses for n rows (partials it writes: that many x [3][dim] floats).
+static int colstats_blocks(int64_t n) {
+  const int64_t b = (n + CS_ROWS_PER_BLOCK - 1) / CS_ROWS_PER_BLOCK;
+  return (int)(b < 1 ? 1 : (b > CS_MAX_BLOCKS ? CS_MAX_BLOCKS : b));
+}
+
+static int launch_colstats(const float* x, int64_t n, int dim, float* part, cudaStream_t st) {
+  const int blocks = colstats_blocks(n);
+  const int64_t rpb = (n + blocks - 1) / blocks;
+  if ((dim % 4 == 0) && (((uintptr_t)x & 15) == 0)) {
+    const int ncol = dim / 4;                   // <= 128 float4 columns, 256 threads
+    colstats_kernel<float4><<<blocks, 256, 3 * ncol * sizeof(float4), st>>>(
+        reinterpret_cast<const float4*>(x), n, ncol, rpb, reinterpret_cast<float4*>(part));
+  } else {
+    colstats_kernel<float><<<blocks, 512, 3 * dim * sizeof(float), st>>>(x, n, dim, rpb, part);
+  }
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}
+
+// Affine record of a call from its row sets (queries == nullptr: one set).
+static int launch_affine(const float* bank, int64_t nb, const float* queries, int64_t nq, int dim,
+                         float* part_b, float* part_q, float* stats, float* aff,
+                         cudaStream_t st) {
+  int rc = launch_colstats(bank, nb, dim, part_b, st);
+  if (rc) return rc;
+  if (queries) {
+    rc = launch_colstats(queries, nq, dim, part_q, st);
+    if (rc) return rc;
+  }
+  colstats_reduce_kernel<<<(dim + 127) / 128, 128, 0, st>>>(
+      part_b, colstats_blocks(nb), part_q, queries ? colstats_blocks(nq) : 0, dim, stats);
+  EXB_LAUNCH_CHECK();
+  affine_kernel<<<1, EXB_SCREEN_MAX_DIM, 0, st>>>(stats, (double)nb + (queries ? (double)nq : 0.0),
+                                                  dim, aff);
   EXB_LAUNCH_CHECK();
   return EXB_OK;
 }
@@ -1280,6 +1506,52 @@ extern "C" int exb_knn_prep_f16(const float* x, int64_t n, int dim, void* out_f1
                 "bad arguments");
   return launch_prep(x, n, dim, dim_pad(dim), static_cast<__half*>(out_f16), half_norm,
                      round_err, reinterpret_cast<PrepScalars*>(scalars), (cudaStream_t)stream);
+}
+
+extern "C" size_t exb_knn_colstats_workspace_bytes(int64_t n, int dim) {
+  if (n < 1 || dim < 1 || dim > EXB_SCREEN_MAX_DIM) return 0;
+  return (size_t)colstats_blocks(n) * 3 * dim * sizeof(float) + 256;
+}
+
+extern "C" int exb_knn_colstats_f32(const float* x, int64_t n, int dim, float* stats,
+                                    void* workspace, size_t workspace_bytes,
+                                    exb_stream_t stream) {
+  EXB_CHECK_ARG(x && stats && workspace && n > 0, "bad arguments");
+  EXB_CHECK_ARG(dim >= 1 && dim <= EXB_SCREEN_MAX_DIM, "dim %d outside [1, %d]", dim,
+                EXB_SCREEN_MAX_DIM);
+  EXB_CHECK_ARG(workspace_bytes >= exb_knn_colstats_workspace_bytes(n, dim) &&
+                ((uintptr_t)workspace & 15) == 0, "workspace too small or unaligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  float* part = static_cast<float*>(workspace);
+  const int rc = launch_colstats(x, n, dim, part, st);
+  if (rc) return rc;
+  colstats_reduce_kernel<<<(dim + 127) / 128, 128, 0, st>>>(part, colstats_blocks(n), nullptr, 0,
+                                                            dim, stats);
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}
+
+extern "C" int exb_knn_affine_from_stats(const float* stats, double n_rows, int dim,
+                                         float* affine, exb_stream_t stream) {
+  EXB_CHECK_ARG(stats && affine && n_rows >= 1.0, "bad arguments");
+  EXB_CHECK_ARG(dim >= 1 && dim <= EXB_SCREEN_MAX_DIM, "dim %d outside [1, %d]", dim,
+                EXB_SCREEN_MAX_DIM);
+  EXB_CHECK_ARG(((uintptr_t)affine & 15) == 0, "affine record must be 16-byte aligned");
+  affine_kernel<<<1, EXB_SCREEN_MAX_DIM, 0, (cudaStream_t)stream>>>(stats, n_rows, dim, affine);
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}
+
+extern "C" int exb_knn_prep_affine_f16(const float* x, int64_t n, int dim, const float* affine,
+                                       void* out_f16, float* half_norm, float* round_err,
+                                       float* scalars, exb_stream_t stream) {
+  EXB_CHECK_ARG(x && affine && out_f16 && half_norm && round_err && scalars && n > 0 && dim > 0,
+                "bad arguments");
+  EXB_CHECK_ARG(dim <= EXB_SCREEN_MAX_DIM, "dim %d > %d", dim, EXB_SCREEN_MAX_DIM);
+  EXB_CHECK_ARG(((uintptr_t)affine & 15) == 0, "affine record must be 16-byte aligned");
+  return launch_prep(x, n, dim, dim_pad(dim), static_cast<__half*>(out_f16), half_norm,
+                     round_err, reinterpret_cast<PrepScalars*>(scalars), (cudaStream_t)stream,
+                     nullptr, affine);
 }
 
 extern "C" size_t exb_knn_screened_workspace_bytes(int64_t nq, int64_t nb, int dim, int k) {
@@ -1465,10 +1737,7 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
     }
   }
 
-  static const int trace_on = [] {
-    const char* e = getenv("EXB_SCREEN_TRACE");
-    return e ? atoi(e) : 0;
-  }();
+  static const int trace_on = knob("EXB_SCREEN_TRACE", 0);
   const bool vec = (dim % 4 == 0) && (((uintptr_t)src | (uintptr_t)bank) & 15) == 0;
   const int ni = vec ? (dim + 127) / 128 : 0;   // float4 loads per lane and row (0 = scalar path)
   RerankParams rp;
@@ -1574,10 +1843,23 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
   EXB_CUDA(cudaMemsetAsync(workspace, 0, 1024 + 64, st));
   int rc = EXB_OK;
   if (!pre) {
-    rc = launch_prep(bank, nb, dim, pl.dpad, w.b16, w.hb, w.eb, w.bsc, st);
+    // range-proof screen: the operands are s (x - mu) with the call's own column means and a
+    // power-of-two scale (one extra streaming pass over the rows; any (mu, s) is exact, this
+    // one keeps shifted / large / tiny reps inside the fp16 format).  Not for the screen-only
+    // form: the lists of several shards are compared by score and must share one transform —
+    // exb_knn_colstats_f32 / exb_knn_affine_from_stats / exb_knn_prep_affine_f16 give a caller
+    // that shards the bank the pieces to agree on one.
+    const float* aff = nullptr;
+    if (!lo) {
+      rc = launch_affine(bank, nb, same ? nullptr : src, nq, dim, w.cs_part_b, w.cs_part_q,
+                         w.cs_stats, w.aff, st);
+      if (rc) return rc;
+      aff = w.aff;
+    }
+    rc = launch_prep(bank, nb, dim, pl.dpad, w.b16, w.hb, w.eb, w.bsc, st, nullptr, aff);
     if (rc) return rc;
     if (!same) {
-      rc = launch_prep(src, nq, dim, pl.dpad, w.q16, w.ha, w.ea, w.qsc, st);
+      rc = launch_prep(src, nq, dim, pl.dpad, w.q16, w.ha, w.ea, w.qsc, st, nullptr, aff);
       if (rc) return rc;
     }
   }
@@ -1608,15 +1890,9 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
   sp.ha = w.ha; sp.ea = w.ea; sp.hb = w.hb; sp.bsc = w.bsc;
   sp.nq = nq; sp.nb = nb; sp.nkc = pl.nkc; sp.n_tiles = pl.n_tiles;
   sp.tiles_per_split = pl.tiles_per_split; sp.splits = pl.splits; sp.k = k;
-  static const int dbg = [] {
-    const char* e = getenv("EXB_SCREEN_DEBUG");
-    return e ? atoi(e) : 0;
-  }();
+  static const int dbg = knob("EXB_SCREEN_DEBUG", 0);
   sp.debug = dbg;
-  static const int pf = [] {
-    const char* e = getenv("EXB_SCREEN_PREFETCH");   // measured: hurts (L2->SM bandwidth), so off
-    return e ? atoi(e) : 0;
-  }();
+  static const int pf = knob("EXB_SCREEN_PREFETCH", 0);   // measured: hurts (L2->SM bandwidth), so off
   sp.prefetch = pf;
   sp.stats = trace_on ? w.trace : nullptr;
   sp.stages = pl.stages; sp.cand_val = w.cand_val; sp.cand_idx = w.cand_idx; sp.cand_cnt = w.cand_cnt;
@@ -1627,10 +1903,7 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
   }
   dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
   sp.tail_splits = pl.tail_splits; sp.full_units = pl.full_units; sp.tail_tps = pl.tail_tps;
-  static const int chain_reset_env = [] {
-    const char* e = getenv("EXB_SCREEN_CHAINRESET");   // A/B: 0 = keep the seed chain (old scheme)
-    return e ? atoi(e) : 1;
-  }();
+  static const int chain_reset_env = knob("EXB_SCREEN_CHAINRESET", 1);   // A/B: 0 = keep the seed chain (old scheme)
   sp.chain_reset = chain_reset_env;
   if (pl.tail_splits > 0) {
     const int units = pl.m_tiles / pl.cg;
@@ -1642,26 +1915,19 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
   sp.lists = pl.splits * pl.trackers;
   // sample tiles that seed the k-th-best chain before the real scan (FILT 3): ~1.5 % extra MMA
   // work buys roughly half the list insertions
-  static const int seed_env = [] {
-    const char* e = getenv("EXB_SCREEN_SEED");
-    return e ? atoi(e) : 0;
-  }();
+  static const int seed_env = knob("EXB_SCREEN_SEED", 0);
   int seed_tiles = seed_env != 0 ? seed_env : pl.tiles_per_split / 16;
   if (seed_env == 0) seed_tiles = seed_tiles < 2 ? 2 : (seed_tiles > 32 ? 32 : seed_tiles);
   if (seed_tiles < 0) seed_tiles = 0;      // EXB_SCREEN_SEED=-1: no sample tiles
   sp.seed_tiles = pl.filt >= 2 ? seed_tiles : 0;
   static const int scan_cap_env = [] {
-    const char* e = getenv("EXB_SCREEN_SCANCAP");   // A/B: repack period of the scratch lists
-    const int v = e ? atoi(e) : SCR_SCAN_CAP;
+    const int v = knob("EXB_SCREEN_SCANCAP", SCR_SCAN_CAP);   // A/B: repack period of the scratch lists
     return v < 16 ? 16 : (v > SCR_SCAN_CAP ? SCR_SCAN_CAP : v);
   }();
   sp.scan_cap = scan_cap_env;
   sp.scan_val = w.scan_val;
   sp.scan_idx = w.scan_idx;
-  static const int share_head = [] {
-    const char* e = getenv("EXB_SCREEN_HEAD");   // A/B: 0 = every CTA scans from its first tile
-    return e ? atoi(e) : 1;
-  }();
+  static const int share_head = knob("EXB_SCREEN_HEAD", 1);   // A/B: 0 = every CTA scans from its first tile
   sp.head = share_head ? w.head : nullptr;
   const int filt = pl.filt;
   const unsigned threads = filt == 3 ? SCR_THREADS_V3 : SCR_THREADS;

@@ -9,6 +9,7 @@
 //
 // Host-only code (zlib raw inflate); lives in the same shared library as the kernels.
 #include "common.cuh"
+#include <atomic>
 #include "fast_inflate.h"
 #include <fcntl.h>
 #include <stdlib.h>
@@ -319,6 +320,8 @@ static int npz_info_impl(void* handle, int i, exb_npz_array* out) {
   return EXB_OK;
 }
 
+static std::atomic<int> g_inflate_mode{1};
+
 static int npz_read_impl(void* handle, int i, void* host_dst, int64_t dst_bytes) {
   EXB_CHECK_ARG(handle && host_dst, "null pointer");
   const NpzFile* f = static_cast<const NpzFile*>(handle);
@@ -326,12 +329,9 @@ static int npz_read_impl(void* handle, int i, void* host_dst, int64_t dst_bytes)
   const NpzMember& m = f->members[i];
   EXB_CHECK_ARG(dst_bytes == (int64_t)m.payload, "array '%s': destination has %lld bytes, need %llu",
                 m.name.c_str(), (long long)dst_bytes, (unsigned long long)m.payload);
-  // EXB_NPZ_FAST_INFLATE: 1 (default) fast decoder with zlib behind it, 0 zlib only, 2 fast decoder
-  // only (tests: a member it cannot decode is an error instead of a silent slow path)
-  static const int fast_on = [] {
-    const char* e = getenv("EXB_NPZ_FAST_INFLATE");
-    return e ? atoi(e) : 1;
-  }();
+  // 1 (default) fast decoder with zlib behind it, 0 zlib only, 2 fast decoder only (tests: a
+  // member it cannot decode is an error instead of a silent slow path): exb_npz_set_inflate_mode
+  const int fast_on = g_inflate_mode.load(std::memory_order_relaxed);
   if (fast_on && m.method == 8) {
     if (member_read_fast(*f, m, static_cast<uint8_t*>(host_dst)) == EXB_OK) return EXB_OK;
     if (fast_on == 2) {
@@ -369,4 +369,10 @@ extern "C" int exb_npz_info(void* handle, int i, exb_npz_array* out) {
 
 extern "C" int exb_npz_read(void* handle, int i, void* host_dst, int64_t dst_bytes) {
   return no_throw("exb_npz_read", [&] { return npz_read_impl(handle, i, host_dst, dst_bytes); });
+}
+
+extern "C" int exb_npz_set_inflate_mode(int mode) {
+  const int prev = g_inflate_mode.load(std::memory_order_relaxed);
+  if (mode >= 0 && mode <= 2) g_inflate_mode.store(mode, std::memory_order_relaxed);
+  return prev;
 }

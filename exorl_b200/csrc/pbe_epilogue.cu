@@ -112,10 +112,7 @@ __global__ void take_kth_kernel(const float* __restrict__ dist, int64_t nq, int 
 // per-row finish after the fused rerank + moments kernel of the per-update chain (knn_screen.cu)
 int launch_pbe_finish(const float* dist, int64_t nq, int k, int avg, int use_rms, int use_clip,
                       float clip, const float* m_ptr, float* out, cudaStream_t st) {
-  static const int pdl_on = [] {
-    const char* e = getenv("EXB_PDL");
-    return e ? atoi(e) : 0;
-  }();
+  static const int pdl_on = knob("EXB_PDL", 0);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)((nq + 127) / 128));
   cfg.blockDim = dim3(128);

@@ -20,7 +20,18 @@ struct OpOut {
   float* er;          // [n]
   PrepScalars* sc;    // max-accumulated over rows (and calls); may be null
   int dpad;
+  // The rows are s * fl(x - mu) of an affine-prepared operand (PrepAffine): fl(x - mu) carries a
+  // relative rounding error <= 2^-24 per element against the exact difference, so
+  // || s (x - mu) - v ||_2 <= 2^-24 ||v|| <= 2^-24 (||v^|| + round_err); extra_rel = 2^-22 (slack
+  // for the round-to-nearest norm sum) adds that to round_err.  0 = plain rows (no term added:
+  // the producers' operands stay bit-identical to exb_knn_prep_f16).
+  float extra_rel = 0.f;
 };
+
+// round_err of an affine-prepared row (see OpOut::extra_rel); nn = ||v^||^2, every step rounded up
+__device__ __forceinline__ float affine_round_err(float er, float nn, float extra_rel) {
+  return __fadd_ru(er, __fmul_ru(extra_rel, __fadd_ru(__fsqrt_ru(nn), er)));
+}
 
 // v[r][i] = float4 chunk c = lane + 32 i of row row0 + r (zero for c >= dim/4).  Rows r >= rows
 // are computed but not stored.  FULL: dim == dpad == NCH * 128 (no column guards).
@@ -92,6 +103,7 @@ __device__ __forceinline__ void emit_rows(const float4 (&v)[R][NCH], int lane, i
     if (lane == r) {
       hn = bad ? 0.f : 0.5f * nn[r];
       er = bad ? INFINITY : __fsqrt_ru(ee[r]);   // rounded up: the bound stays rigorous
+      if (op.extra_rel != 0.f && !bad) er = affine_round_err(er, nn[r], op.extra_rel);
     }
     any_bad |= bad && r < rows;
   }

@@ -470,18 +470,14 @@ extern "C" int exb_rep_trunk_f32(const float* obs, int64_t n, int in_dim, const 
   // rows per warp step: 4 (128 registers, two blocks per SM) measured 1.24 ms per 10^6 walker
   // rows against 1.49 ms for 8 (255 registers, one block per SM); EXB_TRUNK_R=8 for A/B
   static const int r4 = [] {
-    const char* e = getenv("EXB_TRUNK_R");
-    return e ? atoi(e) != 8 : 1;
+    return knob("EXB_TRUNK_R", 4) != 8;
   }();
   // per-update batches: one row per warp so that a 1024-row batch runs as 1024 short warps over
   // all SMs instead of 256 long ones (16.4 us per 1024 x 24 -> 512 call with R = 4)
   // measured on B200, 1024 x 24 -> 512: the no-staging kernel takes 22.5 us against 14.3 us for
   // the shared-memory kernel with one row per warp (its per-lane weight reads cost 32 sectors per
   // load instruction), so it is an A/B knob only (EXB_TRUNK_SMALL=1)
-  static const int small_on = [] {
-    const char* e = getenv("EXB_TRUNK_SMALL");
-    return e ? atoi(e) : 0;
-  }();
+  static const int small_on = knob("EXB_TRUNK_SMALL", 0);
   if (small_on && n <= 8192 && (in_dim & 3) == 0 &&
       (((uintptr_t)weight | (uintptr_t)obs) & 15) == 0)
     return launch_trunk_small(obs, n, in_dim, weight, bias, ln_weight, ln_bias, ln_eps, rep_dim,

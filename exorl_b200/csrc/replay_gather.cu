@@ -302,8 +302,7 @@ static int launch_gather(const int64_t* rows, const GatherDraw& draw, int64_t ba
     // Measured on B200 (C4, B = 1024 frames of 63 504 B, device time incl. the draw kernel):
     // 128-bit SIMT copies 54.3 us (74 % of the HBM copy peak), bulk-copy ring 60.2 us (67 %).
     // The SIMT path is therefore the default; EXB_GATHER_BULK=1 selects the bulk engine.
-    const char* e = getenv("EXB_GATHER_BULK");
-    return e ? atoi(e) : 0;
+    return knob("EXB_GATHER_BULK", 0);
   }();
   GatherPlan g;
   BulkCols bk;

@@ -36,7 +36,17 @@ def _prepared_pair(source, target):
         return None, None
     if target is source:
         return source, source
-    return (source if ps else prepare_rep(source)), (target if pt else prepare_rep(target))
+    if ps and pt:
+        a, b = source.affine, target.affine
+        if (a is None) != (b is None) or (a is not None and a is not b and not torch.equal(a, b)):
+            raise ValueError("exorl_b200: the two PreparedReps were prepared with different "
+                             "affine records (rep.prepare_rep(..., affine=other.affine))")
+        return source, target
+    # the raw side is prepared with the other side's transform: scores are only comparable
+    # between operands of one (mu, s)
+    if ps:
+        return source, prepare_rep(target, affine=source.affine)
+    return prepare_rep(source, affine=target.affine), target
 
 
 def knn_topk(source, target, k, idx_base=0, mode="auto"):

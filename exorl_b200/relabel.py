@@ -29,7 +29,7 @@ import torch
 import torch.distributed as dist
 
 from . import _lib
-from .rep import PreparedRep
+from .rep import PreparedRep, column_affine
 from .knn import (knn_topk, _reward_from_knn, _pbe_ws, knn_screen_lists, knn_rerank_lists,
                   screen_lists_count)
 
@@ -484,7 +484,8 @@ def relabel_apt_reward_from_host(rep_host, args, rms=None, group=None, rep_out=N
     config 5: (N, c) fp32 rows in, (N, 1) rewards out, identical on every rank.
 
     Pipeline per rank r of G (query-block partition, whole bank on every rank):
-      1. H2D of ITS N/G rows only (PCIe), 2. exb_knn_prep_f16 of those rows,
+      1. H2D of ITS N/G rows only (PCIe), 2. exb_knn_prep_affine_f16 of those rows with the
+         set's affine record (column statistics of its rows, all-reduced),
       3. all-gather of the fp16 operand + row norms over NVLink (1 GB instead of the 2 GB of fp32
          rows; the scalars are MAX-reduced), 4. the tcgen05 screen of its query block against the
          whole bank starts, while 5. the fp32 rows — needed only by the exact rerank — are
@@ -515,8 +516,12 @@ def relabel_apt_reward_from_host(rep_host, args, rms=None, group=None, rep_out=N
         tm("start")
         rep_out[lo:hi].copy_(rep_host[lo:hi], non_blocking=True)                        # 1
         tm("h2d_own_rows")
-        _lib.check(lib.exb_knn_prep_f16(                                                 # 2
-            _lib.ptr(rep_out[lo:hi]), hi - lo, dim, _lib.ptr(pre.f16[lo:hi]),
+        # range-proof operand: one affine record (column means + power-of-two scale) for the
+        # whole set — per-rank column statistics, three dim-sized all-reduces
+        aff = column_affine(rep_out[lo:hi], distributed=world > 1, group=group, n_total=n)
+        pre.affine = aff
+        _lib.check(lib.exb_knn_prep_affine_f16(                                          # 2
+            _lib.ptr(rep_out[lo:hi]), hi - lo, dim, _lib.ptr(aff), _lib.ptr(pre.f16[lo:hi]),
             _lib.ptr(pre.half_norm[lo:hi]), _lib.ptr(pre.round_err[lo:hi]),
             _lib.ptr(pre.scalars), _lib.stream_ptr(dev)))
         tm("prep_own_rows")

@@ -48,6 +48,7 @@ class PreparedRep:
         self.half_norm = buf[n * 2 * dpad:n * (2 * dpad + 4)].view(torch.float32)
         self.round_err = buf[n * (2 * dpad + 4):].view(torch.float32)
         self.scalars = self._zeroed_scalars(dev)
+        self.affine = None    # affine record the operand was prepared with (prepare_rep)
         self._c = _lib.Operand(self.f16.data_ptr(), self.half_norm.data_ptr(),
                                self.round_err.data_ptr(), self.scalars.data_ptr())
 
@@ -58,6 +59,7 @@ class PreparedRep:
         v.rep, v.f16 = self.rep[lo:hi], self.f16[lo:hi]
         v.half_norm, v.round_err = self.half_norm[lo:hi], self.round_err[lo:hi]
         v.scalars = self.scalars
+        v.affine = self.affine
         v._c = _lib.Operand(v.f16.data_ptr(), v.half_norm.data_ptr(), v.round_err.data_ptr(),
                             v.scalars.data_ptr())
         return v
@@ -161,16 +163,77 @@ def normalize_rep(x, eps=1e-12):
     return out
 
 
-def prepare_rep(rep):
-    """Prepared operand of an existing fp32 rep (exb_knn_prep_f16), e.g. the Proto queue."""
+def column_stats(rows):
+    """(3, dim) fp32 per-column {sum, min, max} of `rows` (exb_knn_colstats_f32; deterministic).
+    Shards combine with SUM / MIN / MAX."""
+    lib = _lib.load()
+    rows = _f32c(rows, "rows")
+    rows = rows.reshape(rows.size(0), -1)
+    n, dim = rows.shape
+    dev = rows.device
+    with torch.cuda.device(dev):
+        stats = torch.empty(3, dim, dtype=torch.float32, device=dev)
+        need = lib.exb_knn_colstats_workspace_bytes(n, dim)
+        if need == 0:
+            raise ValueError(f"exorl_b200: column statistics need 1 <= dim <= "
+                             f"{_lib.SCREEN_MAX_DIM} and n >= 1 (got n={n}, dim={dim})")
+        ws, _ = _lib.Workspace.get(dev, "colstats", need)
+        _lib.check(lib.exb_knn_colstats_f32(_lib.ptr(rows), n, dim, _lib.ptr(stats),
+                                            _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+    return stats
+
+
+def column_affine(rows, distributed=False, group=None, n_total=None):
+    """Affine record (mu, s) of the range-proof screen for a row set (include/exorl_b200.h,
+    "Range-proof operands"): the screen then runs on s * (x - mu).  With `group` the statistics
+    (a process group; None = this process's rows only) the statistics of every rank's rows are
+    combined (three small all-reduces), so all ranks derive the SAME
+    record for the union of their rows; `n_total` = rows in the union (default: summed)."""
+    import torch.distributed as dist
+    lib = _lib.load()
+    stats = column_stats(rows)
+    n = float(rows.size(0))
+    dev = stats.device
+    if distributed and dist.get_world_size(group) > 1:
+        dist.all_reduce(stats[0], op=dist.ReduceOp.SUM, group=group)
+        dist.all_reduce(stats[1], op=dist.ReduceOp.MIN, group=group)
+        dist.all_reduce(stats[2], op=dist.ReduceOp.MAX, group=group)
+        if n_total is None:
+            cnt = torch.tensor([n], dtype=torch.float64, device=dev)
+            dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
+            n_total = float(cnt.item())
+    n = float(n_total) if n_total is not None else n
+    with torch.cuda.device(dev):
+        aff = torch.empty(_lib.AFFINE_FLOATS, dtype=torch.float32, device=dev)
+        _lib.check(lib.exb_knn_affine_from_stats(_lib.ptr(stats), n, stats.size(1), _lib.ptr(aff),
+                                                 _lib.stream_ptr(dev)))
+    return aff
+
+
+def prepare_rep(rep, affine=None, out=None):
+    """Prepared operand of an existing fp32 rep (exb_knn_prep_f16), e.g. the Proto queue.
+    `affine`: None = the rows as they are; "auto" = range-proof operand from the rep's own column
+    statistics (column_affine); a record tensor = that transform (both operands of a kNN call
+    must share one — knn_topk prepares the other side with the PreparedRep's record)."""
     lib = _lib.load()
     rep = _f32c(rep, "rep")
     rep = rep.reshape(rep.size(0), -1)
     n, dim = rep.shape
     dev = rep.device
+    if isinstance(affine, str):
+        if affine != "auto":
+            raise ValueError("affine must be None, 'auto' or an affine record tensor")
+        affine = column_affine(rep) if (n and dim <= _lib.SCREEN_MAX_DIM) else None
     with torch.cuda.device(dev):
-        out = PreparedRep(n, dim, dev, rep=rep)
-        if n:
+        if out is None:
+            out = PreparedRep(n, dim, dev, rep=rep)
+        out.affine = affine
+        if n and affine is not None:
+            _lib.check(lib.exb_knn_prep_affine_f16(
+                _lib.ptr(rep), n, dim, _lib.ptr(affine), _lib.ptr(out.f16),
+                _lib.ptr(out.half_norm), _lib.ptr(out.round_err), _lib.ptr(out.scalars),
+                _lib.stream_ptr(dev)))
+        elif n:
             _lib.check(lib.exb_knn_prep_f16(_lib.ptr(rep), n, dim, _lib.ptr(out.f16),
                                             _lib.ptr(out.half_norm), _lib.ptr(out.round_err),
                                             _lib.ptr(out.scalars), _lib.stream_ptr(dev)))

@@ -77,6 +77,33 @@ int exb_knn_prep_f16(const float* x, int64_t n, int dim, void* out_f16 /* [n, di
                      float* half_norm /* [n] */, float* round_err /* [n] */,
                      float* scalars /* 16 bytes */, exb_stream_t stream);
 
+/* Range-proof operands.  The screen may run on s * (x - mu) instead of x for any column shift mu
+ * and power-of-two scale s shared by both operands: distances are translation invariant and
+ * scale by s, the screening certificate is scale free, and the survivors are recomputed from the
+ * caller's fp32 rows — the result is the exact path's, the transform only decides how much of
+ * the fp16 format the rows use (reps with a large common offset, |x| > 65504 or |x| << 1e-4
+ * would otherwise lose the screen and fall to the CUDA-core kernel).  exb_knn_screened_f32
+ * derives (mu, s) itself for dataset-scale calls (one extra pass over the rows).  The pieces, for
+ * callers that prepare operands themselves or shard the rows over ranks:
+ *   exb_knn_colstats_f32       stats[3][dim] = per-column {sum, min, max} of x (deterministic);
+ *                              combine shards with SUM / MIN / MAX
+ *   exb_knn_affine_from_stats  affine[EXB_AFFINE_FLOATS] = {mu[0..dim), 0.., s at
+ *                              [EXB_SCREEN_MAX_DIM], on-flag, spread}: mu = sum / n_rows,
+ *                              s * max|x - mu| in [64, 128); non-finite statistics -> identity
+ *   exb_knn_prep_affine_f16    exb_knn_prep_f16 of s * (x - mu); round_err includes the fp32
+ *                              rounding of the subtraction.
+ * affine records are device memory, 16-byte aligned.  Nothing here synchronises. */
+#define EXB_AFFINE_FLOATS (EXB_SCREEN_MAX_DIM + 8)
+size_t exb_knn_colstats_workspace_bytes(int64_t n, int dim);
+int exb_knn_colstats_f32(const float* x, int64_t n, int dim, float* stats /* [3, dim] */,
+                         void* workspace, size_t workspace_bytes, exb_stream_t stream);
+int exb_knn_affine_from_stats(const float* stats /* [3, dim] */, double n_rows, int dim,
+                              float* affine /* [EXB_AFFINE_FLOATS] */, exb_stream_t stream);
+int exb_knn_prep_affine_f16(const float* x, int64_t n, int dim, const float* affine,
+                            void* out_f16 /* [n, dim_pad] */, float* half_norm /* [n] */,
+                            float* round_err /* [n] */, float* scalars /* 16 bytes */,
+                            exb_stream_t stream);
+
 size_t exb_knn_screened_workspace_bytes(int64_t nq, int64_t nb, int dim, int k);
 /* src_is_bank != 0 tells the call that src and bank are the same tensor (PBE: source = target,
  * utils/utils.py:290) so the fp16 operand is prepared once. */
@@ -355,6 +382,11 @@ int exb_npz_info(void* handle, int i, exb_npz_array* out);
 /* Inflate array i into host_dst (dst_bytes must equal nbytes). */
 int exb_npz_read(void* handle, int i, void* host_dst, int64_t dst_bytes);
 void exb_npz_close(void* handle);
+/* Decoder used by exb_npz_read for deflated members, process-wide: 1 (default) = the library's
+ * own raw-deflate decoder with zlib behind it (a stream it rejects or whose CRC-32 differs is
+ * decoded again by zlib), 0 = zlib only, 2 = own decoder only (a stream it cannot decode is an
+ * error; test use).  Returns the previous mode; other values leave the mode unchanged. */
+int exb_npz_set_inflate_mode(int mode);
 
 #ifdef __cplusplus
 }

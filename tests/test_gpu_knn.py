@@ -484,3 +484,95 @@ def test_library_graph_cache_hits_misses_and_bypass():
         want = pbe_reward(x, x, stg, 12, True, True, 0.0)
     _close(r.cpu().numpy(), want.numpy())
     assert pg.rms.n == stg.n
+
+
+# ------------------------------------------------------------- range-proof operands (affine)
+@pytest.mark.parametrize("n,dim", [(5000, 512), (3001, 50), (700, 130), (300, 4)])
+def test_column_stats_and_affine_record(n, dim):
+    """exb_knn_colstats_f32 / exb_knn_affine_from_stats: per-column sum / min / max of the rows,
+    mu = sum / n, and a power-of-two scale that puts max |x - mu| into [64, 128)."""
+    from exorl_b200 import _lib
+    x = reps(3, n, dim, "raw") * 37.0 + 1000.0
+    xd = x.to(DEV)
+    st = xb.column_stats(xd).cpu()
+    np.testing.assert_allclose(st[0].numpy(), x.double().sum(0).numpy(), rtol=1e-6)
+    assert torch.equal(st[1], x.min(0).values) and torch.equal(st[2], x.max(0).values)
+    assert torch.equal(xb.column_stats(xd).cpu(), st)            # deterministic
+    aff = xb.column_affine(xd).cpu()
+    mu, s, on = aff[:dim], float(aff[_lib.SCREEN_MAX_DIM]), float(aff[_lib.SCREEN_MAX_DIM + 1])
+    assert on == 1.0 and torch.all(aff[dim:_lib.SCREEN_MAX_DIM] == 0)
+    np.testing.assert_allclose(mu.numpy(), x.double().mean(0).numpy(), rtol=1e-6)
+    spread = float((x.double() - mu.double()).abs().max())
+    assert np.log2(s) == round(np.log2(s)) and 64.0 <= s * spread * (1 - 1e-6) and s * spread < 128.0 * (1 + 1e-6)
+    # non-finite rows switch the transform off (the prep's range flag then routes the call)
+    xd2 = xd.clone()
+    xd2[n // 2, dim // 2] = float("inf")
+    a2 = xb.column_affine(xd2).cpu()
+    assert float(a2[_lib.SCREEN_MAX_DIM + 1]) == 0.0 and float(a2[_lib.SCREEN_MAX_DIM]) == 1.0
+    xd2[n // 2, dim // 2] = float("nan")
+    assert float(xb.column_affine(xd2).cpu()[_lib.SCREEN_MAX_DIM + 1]) == 0.0
+
+
+@pytest.mark.parametrize("n,dim,offset,scale", [(1000, 512, 1000.0, 1.0), (777, 50, -3e4, 1e5),
+                                                (640, 130, 0.0, 1e-7)])
+def test_affine_operand_is_the_rounded_transform_with_a_rigorous_error_bound(n, dim, offset, scale):
+    """exb_knn_prep_affine_f16: operand = fp16(s * fl(x - mu)); round_err bounds the distance of
+    the fp16 row from the EXACT s * (x - mu) (fp64), including the fp32 subtraction rounding."""
+    from exorl_b200 import _lib, rep as xrep
+    x = reps(17, n, dim, "raw") * scale + offset
+    xd = x.to(DEV)
+    pre = xrep.prepare_rep(xd, affine="auto")
+    aff = pre.affine.cpu()
+    mu, s = aff[:dim], float(aff[_lib.SCREEN_MAX_DIM])
+    assert float(aff[_lib.SCREEN_MAX_DIM + 1]) == 1.0
+    y32 = (x - mu) * s                                   # fp32, same two roundings as the kernel
+    assert torch.equal(pre.f16[:, :dim].cpu(), y32.half())
+    exact = (x.double() - mu.double()) * s
+    want_er = ((exact - y32.half().double()) ** 2).sum(1).sqrt()
+    got_er = pre.round_err.cpu().double()
+    assert torch.all(got_er >= want_er)
+    assert torch.all(got_er <= want_er * 1.01 + 1e-3 * float(want_er.max()))
+    assert int(pre.scalars.cpu()[2]) == 0
+    want_hn = 0.5 * (y32.half().double() ** 2).sum(1)
+    assert torch.all((pre.half_norm.cpu().double() - want_hn).abs() <= want_hn * 2.0 ** -19)
+
+
+@pytest.mark.parametrize("offset,scale", [(0.0, 1e5), (1000.0, 1.0), (0.0, 1e-6), (-5e6, 300.0)])
+def test_dataset_scale_screen_is_range_proof(offset, scale):
+    """Reps with a large common offset, beyond the fp16 range or far below it: the dataset-scale
+    screened call centres and scales its operands, so NO row leaves the tensor-core
+    path (0 undecided rows, no host repair) and the result is the oracle's."""
+    n, dim, k = 12000, 64, 12
+    x = reps(23, n, dim, "raw") * scale + offset
+    xd = x.to(DEV)
+    assert xknn._streaming(n, n, dim, k)
+    dist, idx = xb.knn_topk(xd, xd, k, mode="screened")
+    und, invalid, _, _ = xknn.screened_status(torch.device(DEV))
+    assert und == 0 and invalid == 0
+    sl = slice(0, 1500)
+    assert_knn_matches(x[sl], x, k, dist[sl], idx[sl])
+    de, ie = xb.knn_topk(xd, xd, k, mode="exact")
+    np.testing.assert_allclose(dist.cpu().numpy(), de.cpu().numpy(), rtol=1e-6)
+    assert (idx != ie).any(dim=1).sum().item() <= 4          # fp32 near-ties only
+    # source != target takes the statistics of both row sets
+    q = x[:3000] * 1.0 + 0.25 * scale
+    d2, i2 = xb.knn_topk(q.to(DEV), xd, k, mode="screened")
+    und, invalid, _, _ = xknn.screened_status(torch.device(DEV))
+    assert und <= 15 and invalid == 0      # a few rows with > 24 near-equidistant candidates
+    assert_knn_matches(q[:800], x, k, d2[:800], i2[:800])
+
+
+def test_prepared_operands_must_share_one_affine_record():
+    from exorl_b200 import rep as xrep
+    x = (reps(5, 9000, 64, "raw") + 500.0).to(DEV)
+    y = (reps(6, 9000, 64, "raw") + 500.0).to(DEV)
+    px = xrep.prepare_rep(x, affine="auto")
+    # a raw second operand is prepared with px's record
+    d1, i1 = xb.knn_topk(y, px, 5, mode="screened")
+    d0, i0 = xb.knn_topk(y, x, 5, mode="exact")
+    np.testing.assert_allclose(d1.cpu().numpy(), d0.cpu().numpy(), rtol=1e-6)
+    py = xrep.prepare_rep(y, affine="auto")
+    with pytest.raises(ValueError, match="affine"):
+        xb.knn_topk(py, px, 5)
+    with pytest.raises(ValueError, match="affine"):
+        xb.knn_topk(xrep.prepare_rep(y), px, 5)

@@ -206,19 +206,23 @@ def test_payload_corruption_is_detected_by_crc(tmp_path, level):
 
 
 def test_zlib_path_gives_the_same_bytes(tmp_path):
-    """EXB_NPZ_FAST_INFLATE=0 (read once per process) selects the zlib decoder: same arrays."""
-    import subprocess
-    import sys
+    """exb_npz_set_inflate_mode: 2 = own decoder only (no zlib behind it), 1 = default, 0 = zlib
+    only — the same arrays from all three."""
+    import hashlib
+    from exorl_b200 import _lib
+    lib = _lib.load()
     rng = np.random.default_rng(5)
     fn = tmp_path / "episode_0_1000.npz"
     write_episode_npz(_episode(rng, 1000), fn)
-    code = ("import sys, hashlib; sys.path.insert(0, %r); from exorl_b200 import ingest; "
-            "ep = ingest.read_episode(%r, pin=False); "
-            "print(hashlib.sha256(b''.join(ep[k].numpy().tobytes() for k in sorted(ep))).hexdigest())"
-            % (str(pathlib.Path(__file__).resolve().parent.parent), str(fn)))
     outs = []
-    for flag in ("2", "1", "0"):   # 2 = fast decoder only (no zlib behind it)
-        env = dict(__import__("os").environ, EXB_NPZ_FAST_INFLATE=flag)
-        outs.append(subprocess.run([sys.executable, "-c", code], env=env, check=True,
-                                   capture_output=True, text=True).stdout.strip())
+    prev = lib.exb_npz_set_inflate_mode(1)
+    try:
+        for mode in (2, 1, 0):
+            lib.exb_npz_set_inflate_mode(mode)
+            ep = ingest.read_episode(fn, pin=False)
+            outs.append(hashlib.sha256(b"".join(ep[k].numpy().tobytes()
+                                                for k in sorted(ep))).hexdigest())
+        assert lib.exb_npz_set_inflate_mode(7) == 0      # out of range: unchanged
+    finally:
+        lib.exb_npz_set_inflate_mode(prev)
     assert outs[0] == outs[1] == outs[2] and len(outs[0]) == 64
