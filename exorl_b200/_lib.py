@@ -72,6 +72,9 @@ SIGNATURES = {
     "exb_rep_trunk_f32": (_c.c_int, [_vp, _i64, _c.c_int, _vp, _vp, _vp, _vp, _f32, _c.c_int,
                                      _vp, _op_p, _vp]),
     "exb_rep_ln_tanh_f32": (_c.c_int, [_vp, _i64, _c.c_int, _vp, _vp, _f32, _vp, _op_p, _vp]),
+    "exb_rep_trunk_wide_workspace_bytes": (_sz, [_i64, _c.c_int, _c.c_int]),
+    "exb_rep_trunk_wide_f32": (_c.c_int, [_vp, _i64, _c.c_int, _vp, _vp, _vp, _vp, _f32, _c.c_int,
+                                          _vp, _op_p, _vp, _sz, _vp]),
     "exb_rep_normalize_f32": (_c.c_int, [_vp, _i64, _c.c_int, _f32, _vp, _op_p, _vp]),
     "exb_knn_screened_pre_f32": (_c.c_int, [_vp, _i64, _op_p, _vp, _i64, _op_p, _c.c_int,
                                             _c.c_int, _i32, _vp, _vp, _vp, _sz, _vp]),

@@ -35,6 +35,7 @@
 #include "common.cuh"
 #include "prep_row.cuh"
 #include "tc_ptx.cuh"
+#include "tmap_host.cuh"
 #include <cuda.h>
 #include <cuda_fp16.h>
 #include <float.h>
@@ -1169,44 +1170,10 @@ namespace exb {
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
-                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
-                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  if (!fn) {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) ==
-            cudaSuccess &&
-        qres == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-  }
-  return fn;
-}
-
 // fp16 [rows, dpad] row-major -> tiles of box_rows x 64 columns, 128-byte swizzle, zero OOB fill
 static int make_tmap(CUtensorMap* map, const void* ptr, int64_t rows, int dpad, int box_rows) {
-  EncodeTiledFn enc = encode_fn();
-  if (!enc) {
-    set_error("cuTensorMapEncodeTiled entry point unavailable");
-    return EXB_ECUDA;
-  }
-  const cuuint64_t dims[2] = {(cuuint64_t)dpad, (cuuint64_t)rows};
-  const cuuint64_t strides[1] = {(cuuint64_t)dpad * 2};
-  const cuuint32_t box[2] = {(cuuint32_t)SCR_KC, (cuuint32_t)box_rows};
-  const cuuint32_t estr[2] = {1, 1};
-  const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(ptr), dims,
-                         strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
-    set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
-    return EXB_ECUDA;
-  }
-  return EXB_OK;
+  return tmap_encode_2d(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, ptr, rows, dpad,
+                        (int64_t)dpad * 2, SCR_KC, box_rows);
 }
 
 // Optional CUDA-event bracket around every screening-kernel launch (bench.py's roofline leg).

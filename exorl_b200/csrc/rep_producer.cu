@@ -15,6 +15,8 @@
 // (tests/test_gpu_rep.py asserts it) and the screening certificate of DESIGN.md §4 carries over.
 #include "common.cuh"
 #include "prep_row.cuh"
+#include "rep_gemm.cuh"
+#include <algorithm>
 #include <cuda_fp16.h>
 #include <math.h>
 #include <stdlib.h>
@@ -297,12 +299,15 @@ rep_trunk_small_kernel(const float* __restrict__ obs, int64_t n, int in_dim,
   emit_rows<1, NCH, FULL>(v, lane, dim, row, 1, out_rep, op);
 }
 
-// LayerNorm -> Tanh on given pre-activations, one warp per row (in place allowed).
+// LayerNorm -> Tanh on given pre-activations, one warp per row (in place allowed).  The
+// pre-activation of a row is bias (optional) + the sum of `nparts` partial rows `part_stride`
+// floats apart, added in part order (the split-K partial tiles of trunk_gemm_kernel).
 template <int NCH>
 __global__ void __launch_bounds__(RP_WARPS * 32)
 rep_ln_tanh_kernel(const float* __restrict__ pre, int64_t n, int dim,
                    const float* __restrict__ ln_w, const float* __restrict__ ln_b, float eps,
-                   float* out_rep, OpOut op) {
+                   float* out_rep, OpOut op, const float* __restrict__ bias = nullptr,
+                   int nparts = 1, int64_t part_stride = 0) {
   const int lane = threadIdx.x & 31;
   const int64_t row = (int64_t)blockIdx.x * RP_WARPS + (threadIdx.x >> 5);
   if (row >= n) return;
@@ -313,6 +318,27 @@ rep_ln_tanh_kernel(const float* __restrict__ pre, int64_t n, int dim,
   for (int i = 0; i < NCH; ++i) {
     const int c = lane + 32 * i;
     v[0][i] = (c < nv) ? x4[c] : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (int s = 1; s < nparts; ++s) {
+    const float4* y4 = reinterpret_cast<const float4*>(pre + (int64_t)s * part_stride + row * dim);
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nv) {
+        const float4 y = y4[c];
+        v[0][i].x += y.x; v[0][i].y += y.y; v[0][i].z += y.z; v[0][i].w += y.w;
+      }
+    }
+  }
+  if (bias != nullptr) {
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nv) {
+        const float4 b = __ldg(reinterpret_cast<const float4*>(bias) + c);
+        v[0][i].x += b.x; v[0][i].y += b.y; v[0][i].z += b.z; v[0][i].w += b.w;
+      }
+    }
   }
   ln_tanh_rows<1, NCH, false>(v, lane, dim, reinterpret_cast<const float4*>(ln_w),
                               reinterpret_cast<const float4*>(ln_b), eps);
@@ -492,6 +518,25 @@ extern "C" int exb_rep_trunk_f32(const float* obs, int64_t n, int in_dim, const 
                          out_rep, op, (cudaStream_t)stream);
 }
 
+static int launch_ln_tanh(const float* pre, int64_t n, int rep_dim, const float* ln_weight,
+                          const float* ln_bias, float ln_eps, float* out_rep, const OpOut& op,
+                          const float* bias, int nparts, int64_t part_stride, cudaStream_t st) {
+  const unsigned grid = (unsigned)((n + RP_WARPS - 1) / RP_WARPS);
+#define EXB_LN_CASE(NCH)                                                                        \
+  rep_ln_tanh_kernel<NCH><<<grid, RP_WARPS * 32, 0, st>>>(pre, n, rep_dim, ln_weight, ln_bias,  \
+                                                          ln_eps, out_rep, op, bias, nparts,    \
+                                                          part_stride)
+  switch ((rep_dim / 4 + 31) / 32) {
+    case 1: EXB_LN_CASE(1); break;
+    case 2: EXB_LN_CASE(2); break;
+    case 3: EXB_LN_CASE(3); break;
+    default: EXB_LN_CASE(4); break;
+  }
+#undef EXB_LN_CASE
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}
+
 extern "C" int exb_rep_ln_tanh_f32(const float* pre, int64_t n, int rep_dim,
                                    const float* ln_weight, const float* ln_bias, float ln_eps,
                                    float* out_rep, const exb_operand* out_op,
@@ -504,16 +549,99 @@ extern "C" int exb_rep_ln_tanh_f32(const float* pre, int64_t n, int rep_dim,
   OpOut op;
   rc = make_op(out_op, rep_dim, &op);
   if (rc) return rc;
-  const unsigned grid = (unsigned)((n + RP_WARPS - 1) / RP_WARPS);
-  cudaStream_t st = (cudaStream_t)stream;
-  switch ((rep_dim / 4 + 31) / 32) {
-    case 1: rep_ln_tanh_kernel<1><<<grid, RP_WARPS * 32, 0, st>>>(pre, n, rep_dim, ln_weight, ln_bias, ln_eps, out_rep, op); break;
-    case 2: rep_ln_tanh_kernel<2><<<grid, RP_WARPS * 32, 0, st>>>(pre, n, rep_dim, ln_weight, ln_bias, ln_eps, out_rep, op); break;
-    case 3: rep_ln_tanh_kernel<3><<<grid, RP_WARPS * 32, 0, st>>>(pre, n, rep_dim, ln_weight, ln_bias, ln_eps, out_rep, op); break;
-    default: rep_ln_tanh_kernel<4><<<grid, RP_WARPS * 32, 0, st>>>(pre, n, rep_dim, ln_weight, ln_bias, ln_eps, out_rep, op); break;
+  return launch_ln_tanh(pre, n, rep_dim, ln_weight, ln_bias, ln_eps, out_rep, op, nullptr, 1, 0,
+                        (cudaStream_t)stream);
+}
+
+// ---- wide trunk: tcgen05 3xTF32 GEMM (rep_gemm.cuh) + split sum / bias / LayerNorm / Tanh / emit
+struct WidePlan {
+  int m_tiles, n_tiles, chunks, splits, chunks_per_split;
+  size_t wlo_floats, part_floats;
+};
+
+static bool wide_plan(int64_t n, int in_dim, int rep_dim, WidePlan* pl) {
+  if (n < 1 || in_dim < 4 || (in_dim & 3) || rep_dim < 4 || rep_dim > EXB_SCREEN_MAX_DIM ||
+      (rep_dim & 3) || n > (1LL << 31) - TG_M)
+    return false;
+  pl->m_tiles = (int)((n + TG_M - 1) / TG_M);
+  pl->n_tiles = (rep_dim + TG_N - 1) / TG_N;
+  pl->chunks = (in_dim + TG_KC - 1) / TG_KC;
+  // split K until one wave of CTAs (one per SM: 193 KB of shared memory each) is full, with at
+  // least two accumulation windows per split
+  int64_t tiles = (int64_t)pl->m_tiles * pl->n_tiles;
+  int splits = (int)(sm_count() / tiles);
+  const int max_splits = pl->chunks / (2 * TG_WIN_CHUNKS);
+  if (splits > max_splits) splits = max_splits;
+  if (splits > 32) splits = 32;
+  if (splits < 1) splits = 1;
+  pl->chunks_per_split = (pl->chunks + splits - 1) / splits;
+  pl->splits = (pl->chunks + pl->chunks_per_split - 1) / pl->chunks_per_split;
+  pl->wlo_floats = (size_t)rep_dim * in_dim;
+  pl->part_floats = (size_t)pl->splits * n * rep_dim;
+  return true;
+}
+
+extern "C" size_t exb_rep_trunk_wide_workspace_bytes(int64_t n, int in_dim, int rep_dim) {
+  WidePlan pl;
+  if (!wide_plan(n, in_dim, rep_dim, &pl)) return 0;
+  return align_up(pl.wlo_floats * 4, 256) + align_up(pl.part_floats * 4, 256) + 256;
+}
+
+extern "C" int exb_rep_trunk_wide_f32(const float* obs, int64_t n, int in_dim,
+                                      const float* weight, const float* bias,
+                                      const float* ln_weight, const float* ln_bias, float ln_eps,
+                                      int rep_dim, float* out_rep, const exb_operand* out_op,
+                                      void* workspace, size_t workspace_bytes,
+                                      exb_stream_t stream) {
+  int rc = check_rep_args(obs, n, rep_dim, out_rep, out_op);
+  if (rc) return rc;
+  EXB_CHECK_ARG(weight && bias && ln_weight && ln_bias && workspace, "bad arguments");
+  EXB_CHECK_ARG((((uintptr_t)weight | (uintptr_t)bias | (uintptr_t)ln_weight |
+                  (uintptr_t)ln_bias | (uintptr_t)workspace) & 15) == 0,
+                "weight / bias / LayerNorm vectors / workspace must be 16-byte aligned");
+  WidePlan pl;
+  if (!wide_plan(n, in_dim, rep_dim, &pl)) {
+    set_error("wide trunk needs in_dim %% 4 == 0 (TMA row pitch), got in_dim=%d rep_dim=%d", in_dim,
+              rep_dim);
+    return EXB_EUNSUPPORTED;
   }
+  EXB_CHECK_ARG(workspace_bytes >= exb_rep_trunk_wide_workspace_bytes(n, in_dim, rep_dim),
+                "workspace too small");
+  OpOut op;
+  rc = make_op(out_op, rep_dim, &op);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  Carver cv(workspace);
+  float* wlo = cv.take<float>(pl.wlo_floats);
+  float* part = cv.take<float>(pl.part_floats);
+  const int64_t n4 = (int64_t)pl.wlo_floats / 4;
+  tf32_lo_kernel<<<(unsigned)std::min<int64_t>((n4 + 255) / 256, 148 * 16), 256, 0, st>>>(
+      reinterpret_cast<const float4*>(weight), n4, reinterpret_cast<float4*>(wlo));
   EXB_LAUNCH_CHECK();
-  return EXB_OK;
+  CUtensorMap t_obs, t_w, t_wlo;
+  rc = tmap_encode_2d(&t_obs, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, obs, n, in_dim,
+                      (int64_t)in_dim * 4, TG_KC, TG_M);
+  if (rc) return rc;
+  rc = tmap_encode_2d(&t_w, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, weight, rep_dim, in_dim,
+                      (int64_t)in_dim * 4, TG_KC, TG_N);
+  if (rc) return rc;
+  rc = tmap_encode_2d(&t_wlo, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, wlo, rep_dim, in_dim,
+                      (int64_t)in_dim * 4, TG_KC, TG_N);
+  if (rc) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    EXB_CUDA(cudaFuncSetAttribute(trunk_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  TG_SMEM_BYTES));
+    attr_set = true;
+  }
+  TrunkGemmParams gp;
+  gp.part = part; gp.n = n; gp.dim = rep_dim; gp.chunks = pl.chunks;
+  gp.chunks_per_split = pl.chunks_per_split;
+  const dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.n_tiles, (unsigned)pl.splits);
+  trunk_gemm_kernel<<<grid, TG_THREADS, TG_SMEM_BYTES, st>>>(t_obs, t_w, t_wlo, gp);
+  EXB_LAUNCH_CHECK();
+  return launch_ln_tanh(part, n, rep_dim, ln_weight, ln_bias, ln_eps, out_rep, op, bias, pl.splits,
+                        (int64_t)n * rep_dim, st);
 }
 
 extern "C" int exb_rep_normalize_f32(const float* x, int64_t n, int dim, float eps,

@@ -124,7 +124,8 @@ def icm_get_rep(icm, obs):
 
     `icm`: the ICM module, its trunk, or (weight, bias, ln_weight, ln_bias[, eps]).  Narrow inputs
     (state observations) run the Linear inside the kernel with W^T in shared memory; wide inputs
-    (the 39200-wide pixel encoder output) run the Linear as a library GEMM and fuse the rest."""
+    (the 39200-wide pixel encoder output) run it as a 3xTF32 tcgen05 GEMM (csrc/rep_gemm.cuh)
+    followed by one bias + LayerNorm + Tanh + operand pass."""
     lib = _lib.load()
     w, b, g, be, eps = _trunk_params(icm)
     obs = _f32c(obs, "obs")
@@ -135,9 +136,22 @@ def icm_get_rep(icm, obs):
     if w.size(1) != in_dim:
         raise RuntimeError(f"mat1 and mat2 shapes cannot be multiplied ({n}x{in_dim} and "
                            f"{w.size(1)}x{dim})")
-    if lib.exb_rep_trunk_smem_bytes(in_dim, dim) > 232448:
-        return ln_tanh_rep(torch.addmm(b, obs, w.t()), g, be, eps)
     dev = obs.device
+    if lib.exb_rep_trunk_smem_bytes(in_dim, dim) > 232448:
+        need = lib.exb_rep_trunk_wide_workspace_bytes(n, in_dim, dim) if n else 0
+        if n and need == 0:
+            # in_dim % 4 != 0 (no TMA row pitch) or rep_dim outside the producers' range: the
+            # Linear as a library GEMM, the rest fused
+            return ln_tanh_rep(torch.addmm(b, obs, w.t()), g, be, eps)
+        with torch.cuda.device(dev):
+            out = PreparedRep(n, dim, dev)
+            if n:
+                ws, _ = _lib.Workspace.get(dev, "trunk_wide", need)
+                _lib.check(lib.exb_rep_trunk_wide_f32(
+                    _lib.ptr(obs), n, in_dim, _lib.ptr(w), _lib.ptr(b), _lib.ptr(g), _lib.ptr(be),
+                    eps, dim, _lib.ptr(out.rep), out.operand, _lib.ptr(ws), ws.numel(),
+                    _lib.stream_ptr(dev)))
+        return out
     with torch.cuda.device(dev):
         out = PreparedRep(n, dim, dev)
         if n:

@@ -169,6 +169,22 @@ int exb_rep_trunk_f32(const float* obs, int64_t n, int in_dim, const float* weig
 int exb_rep_ln_tanh_f32(const float* pre, int64_t n, int rep_dim, const float* ln_weight,
                         const float* ln_bias, float ln_eps, float* out_rep,
                         const exb_operand* out_op, exb_stream_t stream);
+
+/* exb_rep_trunk_f32 for input widths whose W^T does not fit shared memory (pixel APT: the
+ * 39 200-wide encoder output, ddpg.py:23-24 -> icm_apt.py:17-18): the Linear runs on the tensor
+ * cores as a 3xTF32 tcgen05 GEMM (fp32-class accuracy: operands split into tf32 hi + lo parts,
+ * accumulation windows of 128 input columns promoted to fp32 registers; split-K partial tiles
+ * summed in order), then bias + LayerNorm + Tanh + operand emit in one pass.  in_dim % 4 == 0,
+ * rows 16-byte aligned; EXB_EUNSUPPORTED otherwise (run the Linear as a library GEMM and call
+ * exb_rep_ln_tanh_f32).  workspace: exb_rep_trunk_wide_workspace_bytes (the weight's lo part and
+ * the split-K partials). */
+size_t exb_rep_trunk_wide_workspace_bytes(int64_t n, int in_dim, int rep_dim);
+int exb_rep_trunk_wide_f32(const float* obs, int64_t n, int in_dim, const float* weight,
+                           const float* bias, const float* ln_weight, const float* ln_bias,
+                           float ln_eps, int rep_dim, float* out_rep,
+                           const exb_operand* out_op, void* workspace, size_t workspace_bytes,
+                           exb_stream_t stream);
+
 int exb_rep_normalize_f32(const float* x, int64_t n, int dim, float eps, float* out_rep,
                           const exb_operand* out_op, exb_stream_t stream);
 int exb_knn_screened_pre_f32(const float* src, int64_t nq, const exb_operand* src_op,

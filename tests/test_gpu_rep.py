@@ -89,6 +89,8 @@ def test_apt_reward_from_obs_matches_reference(golden, tag):
 @pytest.mark.parametrize("n,in_dim,dim", [(1, 24, 512), (7, 24, 512), (8, 24, 512), (1027, 24, 512),
                                           (300, 3, 4), (513, 96, 256), (4099, 24, 384),
                                           (100, 110, 512), (64, 39200, 512),
+                                          (1024, 39200, 512), (300, 5000, 132), (129, 1028, 512),
+                                          (77, 39201, 64),
                                           (9001, 24, 512), (8195, 17, 128), (8194, 6, 36)])
 def test_icm_trunk_shapes_vs_oracle(n, in_dim, dim):
     g = torch.Generator().manual_seed(n + in_dim)
@@ -99,7 +101,10 @@ def test_icm_trunk_shapes_vs_oracle(n, in_dim, dim):
     lnb = 0.1 * torch.randn(dim, generator=g)
     want = icm_trunk_rep(obs, w, b, lnw, lnb, 1e-5)
     p = xb.icm_get_rep((w.to(DEV), b.to(DEV), lnw.to(DEV), lnb.to(DEV)), obs.to(DEV))
-    tol = dict(rtol=1e-5, atol=2e-6) if in_dim < 1000 else dict(rtol=1e-4, atol=2e-5)
+    # wide inputs run the Linear as a 3xTF32 tensor-core GEMM (fp32-class); in_dim % 4 != 0 falls
+    # back to the library GEMM, whose summation order is further from the CPU reference's
+    tol = dict(rtol=1e-5, atol=2e-6) if in_dim < 1000 else (
+        dict(rtol=1e-5, atol=4e-6) if in_dim % 4 == 0 else dict(rtol=1e-4, atol=2e-5))
     np.testing.assert_allclose(p.rep.cpu().numpy(), want.numpy(), **tol)
     _assert_operand_is_prep_of_rep(p)
 
