@@ -81,10 +81,17 @@ def per_update():
         und = xb.knn.screened_status(dev, key="apt_reward")[0]
         pe = xb.PBE(xb.RMS(dev), 0.0, 12, True, True, dev)
         pe.mode = "exact"
+        te = []
         for _ in range(20):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
             re_ = pe(rep)
+            e1.record()
+            e1.synchronize()
+            te.append(e0.elapsed_time(e1) * 1e3)
         same = bool(torch.allclose(r, re_, rtol=1e-5, atol=1e-7))
         print(json.dumps({"per_update_batch": 1024, "walk_step": step, "us_median": sorted(ts)[10],
+                          "exact_path_us_median": sorted(te)[10],
                           "rows_recomputed_inline": und, "equals_exact_path": same}), flush=True)
 
 

@@ -236,18 +236,23 @@ __device__ __noinline__ void scan_insert(const float (&q)[16], const float* __re
                         [list, base](int c) { return list ? list[c] : base + c; }, top, sv, si);
 }
 
-// One warp, one query row.  Returns (in lanes < k) the row's k smallest distances, ascending.
+// One warp, one query row: leaves the row's k smallest SQUARED distances (ascending, lane r = the
+// r-th) in `top` and the query row in `q`.  Returns false when the row has no result here (!LAT:
+// it went to the fallback list).  LAT: `need` receives the bank ranges that still have to be
+// scanned for this row — bit sp = the columns of split sp, RR_NEED_ALL = the whole bank — which
+// the block then scans cooperatively (coop_scan).
+constexpr unsigned RR_NEED_ALL = 0xffffffffu;
 template <bool LAT, int NI, bool SH = false>
-__device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, int lane, int wib,
-                                            int (&s_surv)[RR_WARPS][RR_SURV],
-                                            float (&s_val)[RR_WARPS][RR_SURV]) {
+__device__ __forceinline__ bool rerank_row(const RerankParams& p, int64_t row, int lane, int wib,
+                                           int (&s_surv)[RR_WARPS][RR_SURV],
+                                           float (&s_val)[RR_WARPS][RR_SURV], float (&q)[16],
+                                           WarpTopK& top, unsigned& need) {
   const unsigned full = 0xffffffffu;
   const bool tr = p.trace != nullptr && row == 0;
   if (tr && lane == 0) p.trace[8] = clock_now();
   const int k = p.k, splits = p.splits, dim = p.dim;
 
   // query row into registers first: its latency hides behind the list gathering
-  float q[16];
   if constexpr (NI > 0) {
     const float4* q4 = reinterpret_cast<const float4*>(p.Q + row * dim);
     const int nv = dim >> 2;
@@ -444,13 +449,15 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
   }
   if (tr && lane == 0) p.trace[10] = clock_now();
 
-  WarpTopK top;
   top.init();
   float sv[2] = {FLT_MAX, FLT_MAX};
   int si[2] = {INT_MAX, INT_MAX};
   if (undecided) {
     if constexpr (LAT) {
-      // rare: recompute this row here (no fallback launches in the chain)
+      // rare: recompute this row inside the chain (no fallback launches).  The bank ranges it
+      // lost are recorded in `need` and scanned by the whole block together (coop_scan): with
+      // every row of a batch undecided, per-warp scans re-read the bank once per ROW from L2
+      // (1024 x 2 MB: 369 us); the block-wide scan reads it once per 4 rows.
       if (lane == 0) atomicAdd(&p.status->n_fallback, 1);
       // copies for the out-of-line calls: q and top themselves stay in registers
       float qq[16];
@@ -460,7 +467,7 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
       tt.init();
       if ((why & 4) || !(ea_row < INFINITY)) {
         // outside the fp16 range: no screened score means anything, scan the whole bank
-        scan_insert<NI>(qq, p.B, dim, k, lane, (int)p.nb, nullptr, 0, tt);
+        need = RR_NEED_ALL;
       } else {
         // Only the splits whose list overflowed lost entries.  Every split's k-th chain entry is
         // still a lower bound of the k-th best score, so the best of them gives a valid (looser)
@@ -475,14 +482,7 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
         st.dl = (st.ha + hb_max) * SCR_ACC_EPS;
         st.tk = t0;
         const float tkeep0 = (t0 > -FLT_MAX) ? keep_threshold(st) : -FLT_MAX;
-        unsigned ovf = __ballot_sync(full, lane < splits && my_cnt < 0);
-        while (ovf) {
-          const int sp = __ffs(ovf) - 1;
-          ovf &= ovf - 1;
-          const int lo = sp * p.split_cols;
-          const int cnt = min((int)p.nb - lo, p.split_cols);
-          if (cnt > 0) scan_insert<NI>(qq, p.B, dim, k, lane, cnt, nullptr, lo, tt);
-        }
+        need = __ballot_sync(full, lane < splits && my_cnt < 0);   // splits <= 16: never NEED_ALL
         int n = 0;
         __syncwarp();
 #pragma unroll
@@ -515,7 +515,7 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
           p.out_idx[(int64_t)row * p.k] = -1;
         }
       }
-      return 0.f;
+      return false;
     }
   } else {
     // survivors' exact distances stay distributed over the lanes, then one bitonic sort
@@ -528,13 +528,136 @@ __device__ __forceinline__ float rerank_row(const RerankParams& p, int64_t row, 
     top.i = si[0];
     if (lane == 0) atomicAdd(&p.status->pairs, (unsigned long long)n_surv);
   }
-  const float dist = sqrtf(top.v);
-  if (lane < k) {
-    p.out_dist[row * k + lane] = dist;
-    p.out_idx[row * k + lane] = top.i + p.idx_base;
-  }
   if (tr && lane == 0) p.trace[11] = clock_now();
+  return true;
+}
+
+// sqrt + store of a finished row; returns the row's distances (lane r = the r-th smallest).
+__device__ __forceinline__ float rerank_store(const RerankParams& p, int64_t row, int lane,
+                                              const WarpTopK& top) {
+  const float dist = sqrtf(top.v);
+  if (lane < p.k) {
+    p.out_dist[row * p.k + lane] = dist;
+    p.out_idx[row * p.k + lane] = top.i + p.idx_base;
+  }
   return dist;
+}
+
+// Block-cooperative exact scan of the bank ranges the block's rows still need (per-update chain).
+// Every warp passes its row's `need` mask (0 = nothing); the union of the ranges is streamed
+// through shared memory in tiles of RR_COOP_ROWS bank rows (consecutive rows are one contiguous
+// piece of memory) with cp.async into two buffers — tile t+1 is in flight while tile t is
+// scored — and each warp whose mask covers the tile's range takes the tile's distances into its
+// top-k with the arithmetic of exact_scan.  Must be called by all threads of the block.
+constexpr int RR_COOP_ROWS = 8;
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+template <int NI>
+__device__ __noinline__ void coop_scan(const RerankParams& p, const float (&q)[16], WarpTopK& top,
+                                       unsigned need, int lane, int wib, float* s_tile,
+                                       unsigned* s_need) {
+  const unsigned full = 0xffffffffu;
+  if (lane == 0) s_need[wib] = need;
+  __syncthreads();
+  unsigned uni = 0;
+#pragma unroll
+  for (int w = 0; w < RR_WARPS; ++w) uni |= s_need[w];
+  if (uni == 0) return;                               // block-uniform
+  const int dim = p.dim, k = p.k, nb = (int)p.nb;
+  const bool all = uni == RR_NEED_ALL;                // some row needs the whole bank
+  const int split_cols = max(p.split_cols, RR_COOP_ROWS);   // a multiple of 64 in the chain
+  constexpr int TILE_FLOATS = RR_COOP_ROWS * EXB_SCREEN_MAX_DIM;
+  // a tile lies inside one split's column range (split_cols % RR_COOP_ROWS == 0)
+  auto wanted = [&](int r0) { return all || ((uni >> min(r0 / split_cols, 31)) & 1u); };
+  auto fetch = [&](int r0, float* dst) {              // rows [r0, r0 + RR_COOP_ROWS) ∩ bank
+    const int n_el = min(RR_COOP_ROWS, nb - r0) * dim;
+    const float* src = p.B + (int64_t)r0 * dim;
+    if constexpr (NI > 0) {
+      for (int i = threadIdx.x; i < (n_el >> 2); i += RR_WARPS * 32)
+        cp_async16(dst + 4 * i, src + 4 * i);
+    } else {
+      for (int i = threadIdx.x; i < n_el; i += RR_WARPS * 32) dst[i] = __ldg(src + i);
+    }
+    cp_async_commit();
+  };
+  auto next_tile = [&](int r0) {                      // first wanted tile at or after r0, else nb
+    while (r0 < nb && !wanted(r0)) r0 += RR_COOP_ROWS;
+    return r0;
+  };
+  float thr = __shfl_sync(full, top.v, k - 1);       // warp-uniform: current k-th smallest
+  int buf = 0;
+  int r0 = next_tile(0);
+  if (r0 < nb) fetch(r0, s_tile);
+  while (r0 < nb) {
+    cp_async_wait_all();
+    __syncthreads();                                  // tile r0 landed; everyone left tile r0 - 1
+    const int r1 = next_tile(r0 + RR_COOP_ROWS);
+    if (r1 < nb) fetch(r1, s_tile + (buf ^ 1) * TILE_FLOATS);
+    const float* tile = s_tile + buf * TILE_FLOATS;
+    const int rows = min(RR_COOP_ROWS, nb - r0);
+    const bool mine = need == RR_NEED_ALL || ((need >> min(r0 / split_cols, 31)) & 1u);
+    if (mine) {
+      float a[RR_COOP_ROWS];
+#pragma unroll
+      for (int u = 0; u < RR_COOP_ROWS; ++u) a[u] = 0.f;
+      if constexpr (NI > 0) {
+        const int nv = dim >> 2;
+        const float4* t4 = reinterpret_cast<const float4*>(tile);
+#pragma unroll
+        for (int i = 0; i < NI; ++i) {
+          const int c = lane + 32 * i;
+          const bool ok = c < nv;
+          const int cc = ok ? c : 0;
+#pragma unroll
+          for (int u = 0; u < RR_COOP_ROWS; ++u) {
+            const float4 bv = t4[min(u, rows - 1) * nv + cc];
+            float d = q[4 * i] - bv.x;
+            float t = d * d;
+            d = q[4 * i + 1] - bv.y;
+            t = fmaf(d, d, t);
+            d = q[4 * i + 2] - bv.z;
+            t = fmaf(d, d, t);
+            d = q[4 * i + 3] - bv.w;
+            t = fmaf(d, d, t);
+            a[u] += ok ? t : 0.f;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int c = lane + 32 * i;
+          if (c < dim) {
+#pragma unroll
+            for (int u = 0; u < RR_COOP_ROWS; ++u) {
+              const float d = q[i] - tile[min(u, rows - 1) * dim + c];
+              a[u] = fmaf(d, d, a[u]);
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1)
+#pragma unroll
+        for (int u = 0; u < RR_COOP_ROWS; ++u) a[u] += __shfl_xor_sync(full, a[u], off);
+      // a[u] and thr are warp-uniform: most candidates are rejected without a shuffle
+      bool changed = false;
+#pragma unroll
+      for (int u = 0; u < RR_COOP_ROWS; ++u)
+        if (u < rows && a[u] <= thr) {
+          top.insert(a[u], r0 + u, k, lane);
+          changed = true;
+        }
+      if (changed) thr = __shfl_sync(full, top.v, k - 1);
+    }
+    buf ^= 1;
+    r0 = r1;
+  }
+  __syncthreads();
 }
 
 template <bool LAT, int NI, bool SH = false>
@@ -550,7 +673,18 @@ knn_rerank_kernel(const RerankParams p) {
     pdl_launch_dependents();
   }
   float dist = 0.f;
-  if (active) dist = rerank_row<LAT, NI, SH>(p, row, lane, wib, s_surv, s_val);
+  float q[16];
+  WarpTopK top;
+  unsigned need = 0;
+  bool done = false;
+  if (active) done = rerank_row<LAT, NI, SH>(p, row, lane, wib, s_surv, s_val, q, top, need);
+  if constexpr (LAT) {
+    // rows that lost bank ranges: scanned by the block together (block-uniform call)
+    __shared__ __align__(16) float s_tile[2 * RR_COOP_ROWS * EXB_SCREEN_MAX_DIM];
+    __shared__ unsigned s_need[RR_WARPS];
+    coop_scan<NI>(p, q, top, active ? need : 0u, lane, wib, s_tile, s_need);
+  }
+  if (active && done) dist = rerank_store(p, row, lane, top);
   if constexpr (LAT) {
     if (!p.pbe.on) return;
     const FusedPbe& f = p.pbe;

@@ -576,3 +576,31 @@ def test_prepared_operands_must_share_one_affine_record():
         xb.knn_topk(py, px, 5)
     with pytest.raises(ValueError, match="affine"):
         xb.knn_topk(xrep.prepare_rep(y), px, 5)
+
+
+@pytest.mark.parametrize("n,nb,dim,k,scale", [(1024, 1024, 512, 12, 1.0), (300, 700, 50, 5, 1e5),
+                                              (257, 1024, 130, 12, 1e6), (640, 640, 64, 3, 1.0)])
+def test_per_update_block_cooperative_scan(n, nb, dim, k, scale):
+    """Every row of a per-update batch undecided (a dense random walk: all pairs inside the fp16
+    margin; or values outside the fp16 range): the rerank blocks scan the bank ranges their rows
+    lost TOGETHER through shared memory (coop_scan).  Result = the exact path's, vector and scalar
+    row layouts, source != bank, ragged sizes."""
+    g = torch.Generator().manual_seed(n + dim)
+    if scale == 1.0:
+        walk = torch.randn(1, 24, generator=g) + torch.cumsum(
+            0.005 * torch.randn(max(n, nb), 24, generator=g), 0)
+        w = torch.randn(24, dim, generator=g) / 24 ** 0.5
+        x = torch.tanh(torch.nn.functional.layer_norm(walk @ w, (dim,)))
+    else:
+        x = torch.randn(max(n, nb), dim, generator=g) * scale
+    src, bank = x[:n].contiguous(), x[:nb].contiguous()
+    sd, bd = src.to(DEV), bank.to(DEV)
+    if n == nb:
+        bd = sd
+    assert not xknn._streaming(n, nb, dim, k)
+    dist, idx = xb.knn_topk(sd, bd, k, mode="screened")
+    und, invalid, _, _ = xknn.screened_status(torch.device(DEV))
+    assert invalid == 0 and und >= n // 2
+    de, ie = xb.knn_topk(sd, bd, k, mode="exact")
+    np.testing.assert_allclose(dist.cpu().numpy(), de.cpu().numpy(), rtol=1e-6)
+    assert_knn_matches(src, bank, k, dist, idx)
