@@ -1,5 +1,7 @@
 // Error plumbing + device info for the C ABI (include/exorl_b200.h).
 #include "common.cuh"
+#include <mutex>
+#include <string.h>
 
 namespace exb {
 static thread_local char g_err[512] = "";
@@ -8,6 +10,18 @@ void set_error(const char* fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
+}
+namespace {
+struct KnobEntry { char name[48]; int value; };
+KnobEntry g_knobs[32];
+int g_n_knobs = 0;
+std::mutex g_knob_mu;
+}  // namespace
+bool knob_lookup(const char* name, int* value) {
+  std::lock_guard<std::mutex> lock(g_knob_mu);
+  for (int i = 0; i < g_n_knobs; ++i)
+    if (strcmp(g_knobs[i].name, name) == 0) { *value = g_knobs[i].value; return true; }
+  return false;
 }
 int sm_count() {
   static int cached = 0;
@@ -33,5 +47,16 @@ extern "C" int exb_device_info(int* sms, int* cc) {
   EXB_CUDA(cudaDeviceGetAttribute(&min, cudaDevAttrComputeCapabilityMinor, dev));
   if (sms) *sms = n;
   if (cc) *cc = maj * 10 + min;
+  return EXB_OK;
+}
+
+extern "C" int exb_debug_knob_set(const char* name, int value) {
+  EXB_CHECK_ARG(name && strlen(name) < 48, "bad knob name");
+  std::lock_guard<std::mutex> lock(exb::g_knob_mu);
+  for (int i = 0; i < exb::g_n_knobs; ++i)
+    if (strcmp(exb::g_knobs[i].name, name) == 0) { exb::g_knobs[i].value = value; return EXB_OK; }
+  EXB_CHECK_ARG(exb::g_n_knobs < 32, "knob table full");
+  strcpy(exb::g_knobs[exb::g_n_knobs].name, name);
+  exb::g_knobs[exb::g_n_knobs++].value = value;
   return EXB_OK;
 }

@@ -49,18 +49,21 @@ struct Carver {
 
 int sm_count();
 
-// A/B switches of the bring-up work (EXB_SCREEN_*, EXB_PDL, EXB_TRUNK_*, EXB_GATHER_BULK).  The
-// product library does not read the environment: knob() returns the default unless the library
-// is built with -DEXB_DEBUG_KNOBS (EXB_EXTRA_NVCC_FLAGS=-DEXB_DEBUG_KNOBS python -m
-// exorl_b200._build --force), which benchmarks/screen_scaling.py and the trace scripts ask for.
+// A/B switches of the bring-up work (EXB_SCREEN_*, EXB_PDL, EXB_TRUNK_*, EXB_GATHER_BULK,
+// EXB_CHAIN_*).  The product library does not read the environment: knob() returns the value a
+// measurement script set through exb_debug_knob_set() before the first use of the switch (values
+// are latched at first use), else the default.  A library built with -DEXB_DEBUG_KNOBS
+// (EXB_EXTRA_NVCC_FLAGS=-DEXB_DEBUG_KNOBS python -m exorl_b200._build --force) also reads the
+// environment variable of the same name.
+bool knob_lookup(const char* name, int* value);
 static inline int knob(const char* name, int dflt) {
+  int v = 0;
+  if (knob_lookup(name, &v)) return v;
 #ifdef EXB_DEBUG_KNOBS
   const char* e = getenv(name);
-  return e ? atoi(e) : dflt;
-#else
-  (void)name;
-  return dflt;
+  if (e) return atoi(e);
 #endif
+  return dflt;
 }
 
 // Scalars of a prepared fp16 kNN operand (exb_knn_prep_f16 and the rep producers), max-accumulated

@@ -56,11 +56,15 @@ __device__ __forceinline__ void chain_push_ks(float (&tv)[KS], float x) {
   }
 }
 
-template <int KS>
-__global__ void __launch_bounds__(LAT_THREADS, 1)
-knn_screen_lat_kernel(const __grid_constant__ CUtensorMap tmap_q,
-                      const __grid_constant__ CUtensorMap tmap_b, const LatParams p) {
-  extern __shared__ uint8_t smem_raw[];
+// The kernel body as a function of (query tile, bank split): knn_screen_lat_kernel runs it on a
+// (m_tiles, splits) grid of LAT_THREADS threads; the fused per-update chain (knn_chain.cuh) runs
+// it as its second phase on 256-thread blocks (warps >= 6 only take part in the block barriers).
+// CHAINED: no programmatic-dependent-launch calls, a proxy fence in front of the TMA loads (the
+// operands were written by other blocks of the SAME kernel before a grid barrier).
+template <int KS, bool CHAINED>
+__device__ __forceinline__ void lat_screen_body(const CUtensorMap& tmap_q, const CUtensorMap& tmap_b,
+                                                const LatParams& p, uint8_t* smem_raw,
+                                                const int m_tile, const int split) {
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
   uint8_t* sm = smem_raw + (base - raw);
@@ -85,11 +89,10 @@ knn_screen_lat_kernel(const __grid_constant__ CUtensorMap tmap_q,
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(sm + bar_off + 8 * 13);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m_tile = blockIdx.x, split = blockIdx.y;
   const int t_begin = split * p.tiles_per_split;
   const int t_end = min(p.n_tiles, t_begin + p.tiles_per_split);
   const int n_local = max(t_end - t_begin, 0);
-  const bool tr = p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0;
+  const bool tr = p.trace != nullptr && m_tile == 0 && split == 0;
   if (tr && threadIdx.x == 0) p.trace[0] = clock_now();
 
   if (threadIdx.x == 0) {
@@ -110,12 +113,15 @@ knn_screen_lat_kernel(const __grid_constant__ CUtensorMap tmap_q,
   const uint32_t tmem_base = *s_tmem;
   // barriers, TMEM and descriptors are ready: let the rerank's blocks be scheduled, then wait for
   // the producer of the operands (prep / rep producer) to finish before the first global read
-  pdl_launch_dependents();
-  pdl_wait();
+  if constexpr (!CHAINED) {
+    pdl_launch_dependents();
+    pdl_wait();
+  }
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0 && n_local > 0) {
+      if constexpr (CHAINED) fence_proxy_async_all();   // generic-proxy writes -> TMA reads
       for (int j = 0; j < n_local; ++j) {
         const int brow = (t_begin + j) * LAT_N;
         if (j > 0) mbar_wait(bar_bempty, (uint32_t)(j - 1) & 1u);   // MMAs of tile j-1 done
@@ -155,7 +161,7 @@ knn_screen_lat_kernel(const __grid_constant__ CUtensorMap tmap_q,
         if (tr && j == 0) p.trace[2] = clock_now();
       }
     }
-  } else {
+  } else if (warp < 6) {
     // ===================== epilogue: exact running k-th best + candidate lists =====================
     const int quad = warp & 3;                    // TMEM lane quadrant this warp may access
     const int e = quad * 32 + lane;               // row inside the tile
@@ -188,7 +194,7 @@ knn_screen_lat_kernel(const __grid_constant__ CUtensorMap tmap_q,
     asm volatile("bar.sync 1, 128;" ::: "memory");
     eb_max = fmaxf(fmaxf(s_red[0], s_red[1]), fmaxf(s_red[2], s_red[3]));
     hb_max = fmaxf(fmaxf(s_red[4], s_red[5]), fmaxf(s_red[6], s_red[7]));
-    if (et == 0 && blockIdx.x == 0 && blockIdx.y == 0) {
+    if (et == 0 && m_tile == 0 && split == 0) {
       p.bank_max[0] = eb_max;
       p.bank_max[1] = hb_max;
       if (p.zero_status != nullptr) {
@@ -320,6 +326,14 @@ knn_screen_lat_kernel(const __grid_constant__ CUtensorMap tmap_q,
     tc_fence_after();
     tmem_dealloc_cols(tmem_base, LAT_TMEM_COLS);
   }
+}
+
+template <int KS>
+__global__ void __launch_bounds__(LAT_THREADS, 1)
+knn_screen_lat_kernel(const __grid_constant__ CUtensorMap tmap_q,
+                      const __grid_constant__ CUtensorMap tmap_b, const LatParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  lat_screen_body<KS, false>(tmap_q, tmap_b, p, smem_raw, (int)blockIdx.x, (int)blockIdx.y);
 }
 
 }  // namespace exb

@@ -243,10 +243,10 @@ __device__ __noinline__ void scan_insert(const float (&q)[16], const float* __re
 // the block then scans cooperatively (coop_scan).
 constexpr unsigned RR_NEED_ALL = 0xffffffffu;
 template <bool LAT, int NI, bool SH = false>
-__device__ __forceinline__ bool rerank_row(const RerankParams& p, int64_t row, int lane, int wib,
-                                           int (&s_surv)[RR_WARPS][RR_SURV],
-                                           float (&s_val)[RR_WARPS][RR_SURV], float (&q)[16],
+__device__ __forceinline__ bool rerank_row(const RerankParams& p, int64_t row, int lane,
+                                           int* surv_w, float* val_w, float (&q)[16],
                                            WarpTopK& top, unsigned& need) {
+  // surv_w / val_w: this warp's RR_SURV-entry scratch rows in shared memory
   const unsigned full = 0xffffffffu;
   const bool tr = p.trace != nullptr && row == 0;
   if (tr && lane == 0) p.trace[8] = clock_now();
@@ -377,20 +377,20 @@ __device__ __forceinline__ bool rerank_row(const RerankParams& p, int64_t row, i
       const bool keep = ei[i] >= 0 && ev[i] >= t0;
       const unsigned m = __ballot_sync(full, keep);
       const int pos = n0 + __popc(m & ((1u << lane) - 1u));
-      if (keep && pos < RR_SURV) s_val[wib][pos] = ev[i];
+      if (keep && pos < RR_SURV) val_w[pos] = ev[i];
       n0 += __popc(m);
     }
     __syncwarp();
     float kth = -FLT_MAX;
     if (n0 <= 32) {
-      float xv[2] = {(lane < n0) ? -s_val[wib][lane] : FLT_MAX, FLT_MAX};
+      float xv[2] = {(lane < n0) ? -val_w[lane] : FLT_MAX, FLT_MAX};
       int xi[2] = {lane, lane};
       bitonic_pairs_asc<32>(xv, xi, lane);     // ascending on the negated scores
       kth = -__shfl_sync(full, xv[0], k - 1);
     } else if (n0 <= RR_SURV) {
       // one 64-element bitonic sort instead of k dependent arg-max rounds
-      float x0 = (lane < n0) ? s_val[wib][lane] : -FLT_MAX;
-      float x1 = (lane + 32 < n0) ? s_val[wib][lane + 32] : -FLT_MAX;
+      float x0 = (lane < n0) ? val_w[lane] : -FLT_MAX;
+      float x1 = (lane + 32 < n0) ? val_w[lane + 32] : -FLT_MAX;
       bitonic64_desc(x0, x1, lane);
       kth = __shfl_sync(full, x0, k - 1);      // k <= 16: always in slot 0
     } else {
@@ -427,7 +427,7 @@ __device__ __forceinline__ bool rerank_row(const RerankParams& p, int64_t row, i
       const bool keep = ei[i] >= 0 && ev[i] >= tkeep;
       const unsigned m = __ballot_sync(full, keep);
       const int pos = n_surv + __popc(m & ((1u << lane) - 1u));
-      if (keep && pos < RR_SURV) s_surv[wib][pos] = ei[i];
+      if (keep && pos < RR_SURV) surv_w[pos] = ei[i];
       n_surv += __popc(m);
     }
     if (n_surv > RR_SURV) { undecided = true; why |= 8; }
@@ -491,15 +491,15 @@ __device__ __forceinline__ bool rerank_row(const RerankParams& p, int64_t row, i
           const unsigned m = __ballot_sync(full, keep);
           if (n + __popc(m) > RR_SURV) {
             __syncwarp();
-            scan_insert<NI>(qq, p.B, dim, k, lane, n, s_surv[wib], 0, tt);
+            scan_insert<NI>(qq, p.B, dim, k, lane, n, surv_w, 0, tt);
             __syncwarp();
             n = 0;
           }
-          if (keep) s_surv[wib][n + __popc(m & ((1u << lane) - 1u))] = ei[i];
+          if (keep) surv_w[n + __popc(m & ((1u << lane) - 1u))] = ei[i];
           n += __popc(m);
         }
         __syncwarp();
-        if (n > 0) scan_insert<NI>(qq, p.B, dim, k, lane, n, s_surv[wib], 0, tt);
+        if (n > 0) scan_insert<NI>(qq, p.B, dim, k, lane, n, surv_w, 0, tt);
       }
       top = tt;
     } else {
@@ -519,7 +519,7 @@ __device__ __forceinline__ bool rerank_row(const RerankParams& p, int64_t row, i
     }
   } else {
     // survivors' exact distances stay distributed over the lanes, then one bitonic sort
-    const int* surv = s_surv[wib];
+    const int* surv = surv_w;
     exact_scan<NI, true>(q, p.B, dim, k, lane, n_surv, [surv](int c) { return surv[c]; }, top,
                           sv, si);
     if (n_surv <= 32) bitonic_pairs_asc<32>(sv, si, lane);
@@ -557,7 +557,7 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-template <int NI>
+template <int NI, int NW = RR_WARPS>
 __device__ __noinline__ void coop_scan(const RerankParams& p, const float (&q)[16], WarpTopK& top,
                                        unsigned need, int lane, int wib, float* s_tile,
                                        unsigned* s_need) {
@@ -566,7 +566,7 @@ __device__ __noinline__ void coop_scan(const RerankParams& p, const float (&q)[1
   __syncthreads();
   unsigned uni = 0;
 #pragma unroll
-  for (int w = 0; w < RR_WARPS; ++w) uni |= s_need[w];
+  for (int w = 0; w < NW; ++w) uni |= s_need[w];
   if (uni == 0) return;                               // block-uniform
   const int dim = p.dim, k = p.k, nb = (int)p.nb;
   const bool all = uni == RR_NEED_ALL;                // some row needs the whole bank
@@ -578,10 +578,10 @@ __device__ __noinline__ void coop_scan(const RerankParams& p, const float (&q)[1
     const int n_el = min(RR_COOP_ROWS, nb - r0) * dim;
     const float* src = p.B + (int64_t)r0 * dim;
     if constexpr (NI > 0) {
-      for (int i = threadIdx.x; i < (n_el >> 2); i += RR_WARPS * 32)
+      for (int i = threadIdx.x; i < (n_el >> 2); i += NW * 32)
         cp_async16(dst + 4 * i, src + 4 * i);
     } else {
-      for (int i = threadIdx.x; i < n_el; i += RR_WARPS * 32) dst[i] = __ldg(src + i);
+      for (int i = threadIdx.x; i < n_el; i += NW * 32) dst[i] = __ldg(src + i);
     }
     cp_async_commit();
   };
@@ -677,7 +677,7 @@ knn_rerank_kernel(const RerankParams p) {
   WarpTopK top;
   unsigned need = 0;
   bool done = false;
-  if (active) done = rerank_row<LAT, NI, SH>(p, row, lane, wib, s_surv, s_val, q, top, need);
+  if (active) done = rerank_row<LAT, NI, SH>(p, row, lane, s_surv[wib], s_val[wib], q, top, need);
   if constexpr (LAT) {
     // rows that lost bank ranges: scanned by the block together (block-uniform call)
     __shared__ __align__(16) float s_tile[2 * RR_COOP_ROWS * EXB_SCREEN_MAX_DIM];

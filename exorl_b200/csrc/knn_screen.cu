@@ -37,6 +37,7 @@
 #include "tc_ptx.cuh"
 #include "tmap_host.cuh"
 #include <cuda.h>
+#include <algorithm>
 #include <cuda_fp16.h>
 #include <float.h>
 #include <limits.h>
@@ -102,16 +103,12 @@ constexpr float AFF_EXTRA_REL = 1.0f / 4194304.0f;   // 2^-22, see OpOut::extra_
 // value outside the fp16 range gets round_err = +inf (the screen then keeps nothing certain for
 // it and every row falls to the exact kernel) in addition to the range flag.
 template <bool VEC>
-__global__ void __launch_bounds__(256)
-knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
-                __half* __restrict__ out, float* __restrict__ half_norm,
-                float* __restrict__ round_err, PrepScalars* __restrict__ sc,
-                unsigned long long* __restrict__ zero16, const float* __restrict__ aff) {
-  pdl_launch_dependents();   // per-update chain: the screen's blocks may set up while this runs
-  if (zero16 != nullptr && blockIdx.x == 0 && threadIdx.x < 3) zero16[threadIdx.x] = 0ull;
-  const int lane = threadIdx.x & 31;
-  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
-  if (row >= n) return;
+__device__ __forceinline__ void prep_one_row(const float* __restrict__ x, int64_t row, int dim,
+                                             int dpad, __half* __restrict__ out,
+                                             float* __restrict__ half_norm,
+                                             float* __restrict__ round_err,
+                                             PrepScalars* __restrict__ sc,
+                                             const float* __restrict__ aff, int lane) {
   const float* xr = x + row * dim;
   // affine-prepared operand (range-proof screen, see colstats below): rows become
   // s * fl(x - mu) with the call's column shift mu and power-of-two scale s
@@ -184,6 +181,19 @@ knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
       }
     }
   }
+}
+
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+knn_prep_kernel(const float* __restrict__ x, int64_t n, int dim, int dpad,
+                __half* __restrict__ out, float* __restrict__ half_norm,
+                float* __restrict__ round_err, PrepScalars* __restrict__ sc,
+                unsigned long long* __restrict__ zero16, const float* __restrict__ aff) {
+  pdl_launch_dependents();   // per-update chain: the screen's blocks may set up while this runs
+  if (zero16 != nullptr && blockIdx.x == 0 && threadIdx.x < 3) zero16[threadIdx.x] = 0ull;
+  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= n) return;
+  prep_one_row<VEC>(x, row, dim, dpad, out, half_norm, round_err, sc, aff, threadIdx.x & 31);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1164,6 +1174,7 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
 
 #include "knn_lat.cuh"
 #include "knn_rerank.cuh"
+#include "knn_chain.cuh"
 
 namespace exb {
 
@@ -1397,7 +1408,9 @@ static size_t carve_screen(void* ws, int64_t nq, int64_t nb, const ScreenPlan& p
   o->cand_tr = cv.take<float>((size_t)nq * lists);
   o->scan_val = cv.take<float>(pl.filt == 3 ? (size_t)nq * lists * SCR_SCAN_CAP : 0);
   o->scan_idx = cv.take<int>(pl.filt == 3 ? (size_t)nq * lists * SCR_SCAN_CAP : 0);
-  o->pbe_partials = cv.take<double2>(pl.lat ? (size_t)((nq + RR_WARPS - 1) / RR_WARPS) : 1);
+  // one per rerank block of the launch chain, or one per block of the fused chain kernel
+  o->pbe_partials = cv.take<double2>(
+      pl.lat ? std::max<size_t>((size_t)((nq + RR_WARPS - 1) / RR_WARPS), 256) : 1);
   o->fb_rows = cv.take<int>(pl.fb_cap);
   o->fb_d2 = cv.take<float>((size_t)pl.fb_cap * pl.fb_splits * k);
   o->fb_idx = cv.take<int>((size_t)pl.fb_cap * pl.fb_splits * k);
@@ -1663,6 +1676,70 @@ struct ListsOut {
   void* scalars;   // 16 bytes: PrepScalars of the bank (query-side range flag folded in)
 };
 
+// Grid-barrier words of the fused chain kernel: a per-device pool of 64 {arrivals, generation}
+// pairs in device memory, zeroed once (a barrier leaves its pair clean), handed out round-robin so
+// that chains running concurrently on different streams do not share a pair.  nullptr: the
+// device cannot launch cooperatively / allocation failed / switched off -> the launch chain.
+static unsigned* chain_gbar_slot() {
+  // Off by default — measured on B200 (profiles/r02f_chain_trace.txt): in-kernel 31.0 us in a hot
+  // loop (prep 0.7, barrier 2.5, screen 6.5, barrier 3.5, rerank 10.7, barrier 2.9, finish 4.2)
+  // and 47.5 us after an L2 flush, against 30.7 us for the graph-replayed launch chain under the
+  // same flush: a grid barrier costs about what a kernel boundary inside a graph does, and the
+  // phases run slower than the standalone kernels (one 254-register block per SM).
+  static const int fused_on = knob("EXB_CHAIN_FUSED", 0);
+  if (!fused_on) return nullptr;
+  static std::mutex mu;
+  static unsigned* pool[64] = {};
+  static int state[64] = {};          // 0 = untried, 1 = ready, -1 = unavailable
+  static unsigned next[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> lock(mu);
+  if (state[dev] == 0) {
+    int coop = 0;
+    state[dev] = -1;
+    if (cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev) == cudaSuccess && coop &&
+        cudaMalloc(&pool[dev], 64 * 2 * sizeof(unsigned)) == cudaSuccess) {
+      if (cudaMemset(pool[dev], 0, 64 * 2 * sizeof(unsigned)) == cudaSuccess) state[dev] = 1;
+    }
+    cudaGetLastError();
+  }
+  if (state[dev] != 1) return nullptr;
+  return pool[dev] + 2 * (next[dev]++ % 64);
+}
+
+template <int KS, int NI>
+static int launch_chain_one(const CUtensorMap& tq, const CUtensorMap& tb, const ChainParams& cp,
+                            int grid, size_t smem, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    EXB_CUDA(cudaFuncSetAttribute(apt_chain_kernel<KS, NI>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(CH_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  EXB_CUDA(cudaLaunchKernelEx(&cfg, apt_chain_kernel<KS, NI>, tq, tb, cp));
+  return EXB_OK;
+}
+
+// Instantiated for the two per-update shapes of the benchmark configs only (C1: k = 12, rep 512;
+// C2: k = 3, dim 128); other shapes report "not available" and take the launch chain.
+static int launch_chain_kernel(const CUtensorMap& tq, const CUtensorMap& tb, const ChainParams& cp,
+                               int grid, size_t smem, int k, int ni, cudaStream_t st) {
+  if (k > 4 && k <= 12 && ni == 4) return launch_chain_one<12, 4>(tq, tb, cp, grid, smem, st);
+  if (k <= 4 && ni == 1) return launch_chain_one<4, 1>(tq, tb, cp, grid, smem, st);
+  return EXB_EUNSUPPORTED;
+}
+
 static int screened_impl(const float* src, int64_t nq, const float* bank, int64_t nb, int dim,
                          int k, int32_t idx_base, int src_is_bank, float* out_dist,
                          int32_t* out_idx, void* workspace, size_t workspace_bytes,
@@ -1748,8 +1825,41 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
       lat_attr_set = true;
     }
+    // ONE cooperative kernel (knn_chain.cuh) when the device can hold its grid; else (or with
+    // EXB_CHAIN_FUSED=0 in a knob build) the launch chain below
+    unsigned* gbar = trace_on ? nullptr : chain_gbar_slot();
     auto run_chain = [&](cudaStream_t st) -> int {
     int rc = EXB_OK;
+    if (gbar != nullptr) {
+      CUtensorMap tq, tb;
+      rc = make_tmap(&tq, w.q16, nq, pl.dpad, SCR_M);
+      if (rc) return rc;
+      rc = make_tmap(&tb, w.b16, nb, pl.dpad, LAT_N);
+      if (rc) return rc;
+      ChainParams cp;
+      cp.bank = bank; cp.src = src; cp.nb = nb; cp.nq = nq; cp.dim = dim; cp.dpad = pl.dpad;
+      cp.same = same ? 1 : 0; cp.do_prep = pre ? 0 : 1;
+      cp.vec = ((dim % 4 == 0) && (((uintptr_t)src | (uintptr_t)bank) & 15) == 0 && dim <= 512) ? 1 : 0;
+      cp.b16 = w.b16; cp.hb = w.hb; cp.eb = w.eb; cp.q16 = w.q16; cp.ha = w.ha; cp.ea = w.ea;
+      LatParams& lp = cp.lp;
+      lp.ha = w.ha; lp.ea = w.ea; lp.hb = w.hb; lp.eb = w.eb; lp.nq = nq; lp.nb = nb;
+      lp.nkc = pl.nkc; lp.n_tiles = pl.n_tiles; lp.tiles_per_split = pl.tiles_per_split;
+      lp.splits = pl.splits; lp.k = k; lp.cand_val = w.cand_val; lp.cand_idx = w.cand_idx;
+      lp.cand_cnt = w.cand_cnt; lp.cand_tk = w.cand_tk; lp.cand_tr = w.cand_tr;
+      lp.rsel = (k + pl.splits - 1) / pl.splits; lp.bank_max = reinterpret_cast<float*>(w.bsc);
+      lp.trace = nullptr; lp.zero_status = nullptr;
+      cp.rp = rp;
+      cp.m_tiles = pl.m_tiles; cp.splits = pl.splits; cp.gbar = gbar;
+      static const int chain_trace = knob("EXB_CHAIN_TRACE", 0);
+      cp.trace = chain_trace ? w.trace : nullptr;
+      const int64_t row_blocks = (std::max(nq, nb) + CH_WARPS - 1) / CH_WARPS;
+      const int grid = std::max<int>(pl.m_tiles * pl.splits,
+                                     (int)std::min<int64_t>(row_blocks, sm_count()));
+      const size_t smem = std::max<size_t>(pl.smem, CH_P2_SMEM + 1024);
+      rc = launch_chain_kernel(tq, tb, cp, grid, smem, k, ni, st);
+      if (rc != EXB_EUNSUPPORTED) return rc;
+      rc = EXB_OK;                                   // shape without a fused instance
+    }
     if (!pre) {
       rc = launch_prep(bank, nb, dim, pl.dpad, w.b16, w.hb, w.eb, nullptr, st,
                        reinterpret_cast<unsigned long long*>(w.status));

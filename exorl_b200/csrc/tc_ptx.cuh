@@ -39,6 +39,11 @@ __device__ __forceinline__ void fence_barrier_init() {
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
+// all state spaces: orders earlier generic-proxy accesses (as observed by this thread, e.g. global
+// writes of other CTAs acquired through a barrier) before later async-proxy ones (TMA loads)
+__device__ __forceinline__ void fence_proxy_async_all() {
+  asm volatile("fence.proxy.async;" ::: "memory");
+}
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1,
                                             uint32_t bar) {
   asm volatile(

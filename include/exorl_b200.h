@@ -132,6 +132,11 @@ int exb_knn_screened_status_sync(const void* workspace, int32_t host_status[4],
  * data, [6] MMA issuer total, [7] CTAs that issued MMAs. */
 int exb_debug_trace_sync(const void* workspace, int64_t host_ns[16], exb_stream_t stream);
 
+/* Measurement scripts only: set an A/B switch of the library (EXB_SCREEN_*, EXB_CHAIN_*, EXB_PDL,
+ * ...; csrc/common.cuh) before the first call that consults it.  The product never reads the
+ * environment. */
+int exb_debug_knob_set(const char* name, int value);
+
 /* Measurement hook (bench.py): when enabled, every screening-kernel launch is bracketed by CUDA
  * events on its own stream (up to 64 launches); collect returns their durations in ms. */
 int exb_profile_begin(int enable);
