@@ -4,6 +4,8 @@
   C2  Proto 1024 z (128) vs 2048 queue, topk 3      per-call latency
   C3  walker-state replay sample B=1024, nstep 3    per-batch latency, + sample -> trunk -> PBE
   C4  pixel replay sample B=1024 / 256 from a 1M-transition uint8 (9,84,84) buffer: GB/s vs HBM peak
+  C4b the pixel path's rep producer: ICM trunk 39200 -> 512 as a 3xTF32 tcgen05 GEMM, vs torch fp32
+  C5r range-proof screen: 131072 x 131072 kNN on bounded reps vs the same reps * 1e5 + offset
 
 `run_all()` is what `bench.py --gpus 1` embeds as the `"secondary"` object of its JSON line; run as
 a script it prints one JSON line per case.  Every case: the public call a user makes, CUDA events
@@ -267,11 +269,93 @@ def c4(tm, n_trans=1_000_000, cpu=True):
     return out
 
 
-def run_all(dev, sampler_factory=None, cases=("C1", "C2", "C3", "C4"), min_seconds=2.0,
+def tensor_peak():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"], \
+            "measured (MEASURED_PEAKS.json bf16_tflops burst) / 2: tf32 runs at half the bf16 rate"
+    except Exception:
+        return 2250.0, "fallback (B200_PROFILING.md nominal bf16) / 2"
+
+
+def c4b(tm, cpu=True):
+    """C4's rep producer: the 39 200-wide pixel-encoder output through the ICM trunk
+    (icm_apt.py:17-18) into PBE — the wide Linear as a 3xTF32 tcgen05 GEMM (csrc/rep_gemm.cuh)."""
+    import exorl_b200 as xb
+    from exorl_b200 import rep as xrep
+    dev = tm.dev
+    g = torch.Generator().manual_seed(6)
+    in_dim, dim, n = 39200, 512, 1024
+    obs = torch.relu(torch.randn(n, in_dim, generator=g)).to(dev)
+    w = (torch.randn(dim, in_dim, generator=g) / in_dim ** 0.5).to(dev)
+    b = (0.1 * torch.randn(dim, generator=g)).to(dev)
+    lnw, lnb = torch.ones(dim, device=dev), torch.zeros(dim, device=dev)
+    peak, peak_src = tensor_peak()
+    out = {"workload": f"C4b pixel APT rep producer: ICM trunk Linear({in_dim} -> {dim}) + "
+                       f"LayerNorm + Tanh + kNN operand on a {n}-row batch of encoder features "
+                       "(relu(randn) seed 6), fp32 parity (rep rtol 1e-5)",
+           "l2": L2_POLICY, "algorithmic_flops": 2.0 * n * in_dim * dim}
+    r = tm.run(lambda: xb.icm_get_rep((w, b, lnw, lnb), obs))
+    alg_tf = out["algorithmic_flops"] / (r["us_median"] * 1e-6) / 1e12
+    r["roofline"] = {"bound": "tensor", "kernel": "trunk_gemm_kernel (3xTF32 tcgen05)",
+                     "achieved": 3 * alg_tf, "peak": peak / 2, "unit": "TFLOP/s",
+                     "frac": 3 * alg_tf / (peak / 2), "peak_source": peak_src,
+                     "algorithmic_tflops": alg_tf,
+                     "note": "achieved = EXECUTED tf32 flops (3 MMAs per product term: hi*hi, "
+                             "hi*lo, lo*hi) over the whole call (weight split + GEMM + LayerNorm "
+                             "pass); algorithmic_tflops counts 2*n*K*D once", "traffic": None}
+    out["tcgen05_3xtf32"] = r
+    out["torch_fp32_addmm_then_ln"] = tm.run(
+        lambda: xrep.ln_tanh_rep(torch.addmm(b, obs, w.t()), lnw, lnb))
+    pbe = xb.PBE(xb.RMS(dev), 0.0, 12, True, True, dev)
+    out["trunk_then_pbe"] = tm.run(lambda: pbe(xb.icm_get_rep((w, b, lnw, lnb), obs)))
+    ref = torch.tanh(torch.nn.functional.layer_norm(obs.double() @ w.double().t() + b.double(),
+                                                    (dim,), lnw.double(), lnb.double(), 1e-5))
+    got = xb.icm_get_rep((w, b, lnw, lnb), obs).rep.double()
+    out["max_abs_err_vs_fp64"] = float((got - ref).abs().max())
+    out["us"] = r["us_median"]
+    out["roofline"] = r["roofline"]
+    if cpu:
+        oc, wc, bc = obs.cpu(), w.cpu(), b.cpu()
+        t0 = time.perf_counter()
+        torch.tanh(torch.nn.functional.layer_norm(torch.addmm(bc, oc, wc.t()), (dim,)))
+        out["cpu_reference_us"] = (time.perf_counter() - t0) * 1e6
+        out["cpu_cores"] = torch.get_num_threads()
+    return out
+
+
+def c5r(tm, cpu=True):
+    """Range-proof screen A/B at dataset scale: the same reps bounded (tanh) and times 1e5 +
+    offset (outside the fp16 range: before the affine operands every row fell to the CUDA-core
+    exact kernel)."""
+    import exorl_b200 as xb
+    from exorl_b200 import knn as xknn
+    dev = tm.dev
+    g = torch.Generator().manual_seed(8)
+    n, dim, k = 131072, 512, 12
+    x = torch.tanh(torch.randn(n, dim, generator=g)).to(dev)
+    y = x * 1e5 + 3e6
+    out = {"workload": f"C5r range-proof screen: {n} x {n} kNN (rep {dim}, k={k}) on tanh(randn) "
+                       "reps (seed 8) and on the same reps * 1e5 + 3e6",
+           "l2": "inputs (268 MB fp32 + 134 MB fp16) larger than the 126 MB L2"}
+    small = Timer(dev, tm.sampler_factory, min_seconds=1.0, min_iters=5, max_iters=40)
+    small.flush = lambda: None
+    out["bounded"] = small.run(lambda: xb.knn_topk(x, x, k, mode="screened"), warm=2)
+    out["times_1e5_plus_offset"] = small.run(lambda: xb.knn_topk(y, y, k, mode="screened"), warm=2)
+    st = xknn.screened_status(dev)
+    out["undecided_rows_scaled"] = int(st[0])
+    out["ratio"] = out["times_1e5_plus_offset"]["us_median"] / out["bounded"]["us_median"]
+    d0, i0 = xb.knn_topk(x[:4096], x, k, mode="screened")
+    d1, i1 = xb.knn_topk(y[:4096], y, k, mode="screened")
+    out["same_neighbours"] = bool((i0 == i1).float().mean() > 0.999)
+    out["us"] = out["times_1e5_plus_offset"]["us_median"]
+    return out
+
+
+def run_all(dev, sampler_factory=None, cases=("C1", "C2", "C3", "C4", "C4b", "C5r"), min_seconds=2.0,
             c4_transitions=1_000_000, cpu=True):
     tm = Timer(dev, sampler_factory, min_seconds=min_seconds)
     fns = {"C1": c1, "C2": c2, "C3": c3,
-           "C4": lambda t, cpu=True: c4(t, c4_transitions, cpu=cpu)}
+           "C4": lambda t, cpu=True: c4(t, c4_transitions, cpu=cpu), "C4b": c4b, "C5r": c5r}
     out = {}
     for name in cases:
         out[name] = fns[name](tm, cpu=cpu)
@@ -280,7 +364,7 @@ def run_all(dev, sampler_factory=None, cases=("C1", "C2", "C3", "C4"), min_secon
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("--cases", default="C1,C2,C3,C4")
+    ap.add_argument("--cases", default="C1,C2,C3,C4,C4b,C5r")
     ap.add_argument("--c4-transitions", type=int, default=1_000_000)
     ap.add_argument("--min-seconds", type=float, default=2.0)
     ap.add_argument("--no-cpu", action="store_true")
