@@ -198,14 +198,51 @@ def _recompute_rows(src, tgt, k, idx_base, dist, idx, rows):
     idx[rows] = i
 
 
+OVERFLOW_POLICY = "sync"
+
+
+def set_overflow_policy(policy):
+    """What a dataset-scale screened call does about rows beyond the device-side fallback (more
+    than 4096 undecided rows: heavily duplicated or very dense data, non-finite values).
+      "sync" (default): read the call's status word — ONE stream synchronisation per
+               dataset-scale call, after all of its kernels are enqueued — and recompute the
+               flagged rows before returning, so the result is always the exact path's;
+      "flag":  never synchronise (the call only enqueues work and can sit inside a CUDA graph or
+               a multi-stream pipeline); such rows come back with idx[:, 0] == -1 and are the
+               caller's to repair with `repair_flagged(...)` once it synchronises anyway.
+    Per-update calls recompute undecided rows inline and never synchronise under either policy.
+    Returns the previous policy."""
+    global OVERFLOW_POLICY
+    if policy not in ("sync", "flag"):
+        raise ValueError("policy must be 'sync' or 'flag'")
+    prev, OVERFLOW_POLICY = OVERFLOW_POLICY, policy
+    return prev
+
+
+def repair_flagged(source, target, k, dist, idx, idx_base=0):
+    """Recompute in place the rows a "flag"-policy call marked with idx[:, 0] == -1 (synchronises).
+    Returns the number of rows repaired."""
+    src = _as_rows(source, "source")
+    tgt = src if target is source else _as_rows(target, "target")
+    rows = (idx[:, 0] < 0).nonzero().flatten()
+    if rows.numel():
+        prev = set_overflow_policy("sync")     # the re-screens inside must repair their own rows
+        try:
+            _recompute_rows(src, tgt, int(k), idx_base, dist, idx, rows)
+        finally:
+            set_overflow_policy(prev)
+    return int(rows.numel())
+
+
 def _repair_overflow_rows(src, tgt, k, idx_base, dist, idx, ws_key):
     """Dataset-scale screened calls only: rows the screen could not certify are recomputed on
     the device by the exact kernel, up to 4096 of them; if there were more (heavily duplicated
     or very dense rows, values outside the fp16 range) the rerank marks the rest with
-    idx[:, 0] = -1 and raises the status flag.  Read the flag (one stream sync per dataset-scale
-    call) and recompute those rows (_recompute_rows), so the result is always the exact path's."""
+    idx[:, 0] = -1 and raises the status flag.  Policy "sync": read the flag (one stream sync per
+    dataset-scale call) and recompute those rows (_recompute_rows), so the result is always the
+    exact path's.  Policy "flag": leave them marked (set_overflow_policy)."""
     nq, nb, dim = src.size(0), tgt.size(0), src.size(1)
-    if not _streaming(nq, nb, dim, k):
+    if OVERFLOW_POLICY == "flag" or not _streaming(nq, nb, dim, k):
         return
     st = screened_status(src.device, key=ws_key)
     if st[1] == 0:

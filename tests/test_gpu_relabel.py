@@ -239,11 +239,12 @@ def test_c5_full_size_properties(golden):
                        oracle=oracle)
 
 
-@pytest.mark.parametrize("kind", ["duplicates", "out_of_range"])
+@pytest.mark.parametrize("kind", ["duplicates", "outlier"])
 def test_more_undecided_rows_than_the_device_fallback_holds(kind, monkeypatch):
     """Dataset-scale input on which the screen cannot certify > 4096 rows: 6000 identical rows
-    (each has 6000 neighbours at distance 0, far more than a candidate list holds) or values
-    outside the fp16 range (every row undecided).  The device-side fallback takes 4096 rows; the
+    (each has 6000 neighbours at distance 0, far more than a candidate list holds) or one
+    element 1e15 times the others (the call's power-of-two scale then pushes every other value
+    below the fp16 range: every row undecided).  The device-side fallback takes 4096 rows; the
     rest is flagged and recomputed from the host (strided sub-bank re-screen, exact kernel at the
     bottom) — results must equal the exact path, never silently wrong."""
     n, dim, k = 20000, 64, 12
@@ -251,7 +252,7 @@ def test_more_undecided_rows_than_the_device_fallback_holds(kind, monkeypatch):
     if kind == "duplicates":
         x[5000:11000] = x[4999]
     else:
-        x = x * 1.0e5
+        x[123, 7] = 1.0e15
     xd = x.to(DEV)
     from exorl_b200 import knn as xknn
     flagged = []
@@ -273,6 +274,18 @@ def test_more_undecided_rows_than_the_device_fallback_holds(kind, monkeypatch):
     r_s = xb.compute_apt_reward(xd, xd, args, rms=xb.RMS(DEV))
     r_e = xb.compute_apt_reward(xd, xd, args, rms=xb.RMS(DEV), mode="exact")
     np.testing.assert_allclose(r_s.cpu().numpy(), r_e.cpu().numpy(), rtol=1e-5, atol=1e-7)
+    # policy "flag": the call never synchronises; the rows come back marked and are repaired later
+    prev = xknn.set_overflow_policy("flag")
+    try:
+        before = len(flagged)
+        d_f, i_f = xb.knn_topk(xd, xd, k, mode="screened")
+        assert len(flagged) == before
+        n_marked = int((i_f[:, 0] < 0).sum())
+        assert n_marked == flagged[0]
+        assert xknn.repair_flagged(xd, xd, k, d_f, i_f) == n_marked
+        np.testing.assert_allclose(d_f.cpu().numpy(), d_e.cpu().numpy(), rtol=1e-6, atol=1e-6)
+    finally:
+        xknn.set_overflow_policy(prev)
 
 
 def test_dense_trajectory_data_is_rescreened_not_scanned():
