@@ -96,6 +96,9 @@ SIGNATURES = {
     "exb_replay_sample": (_c.c_int, [_u64, _u64, _vp, _vp, _i64, _i64, _c.POINTER(GatherCol),
                                      _c.c_int, _vp, _vp, _c.c_int, _c.c_int, _f32, _vp, _vp, _vp,
                                      _vp]),
+    "exb_knn_sym_workspace_bytes": (_sz, [_i64, _c.c_int, _c.c_int, _c.c_int, _c.c_int]),
+    "exb_knn_sym_f32": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _i32, _vp, _i64, _c.c_int,
+                                   _c.c_int, _vp, _vp, _vp, _sz, _vp]),
     "exb_knn_colstats_workspace_bytes": (_sz, [_i64, _c.c_int]),
     "exb_knn_colstats_f32": (_c.c_int, [_vp, _i64, _c.c_int, _vp, _vp, _sz, _vp]),
     "exb_knn_affine_from_stats": (_c.c_int, [_vp, _c.c_double, _c.c_int, _vp, _vp]),

@@ -390,6 +390,23 @@ struct ScreenParams {
   // ranges of tail_tps tiles so that the idle SMs of that wave share their scans.  0 = off.
   int tail_splits, full_units, tail_tps;
   int chain_reset;        // 1 = drop the seed chain after the seed phase (default); 0 = A/B only
+  // FILT 4 (symmetric screen, source == bank): every query tile pair scans the bank tiles from its
+  // own upwards; an accumulator element g_ij is tested in both directions against the rows' fixed
+  // thresholds and logged per (row, column half): direct hits (bank row j for query i) and
+  // transposed hits (bank row i for query j).  log_cap slots per log; count -1 = overflowed.
+  const float* sym_tkeep; // [n] stateless keep thresholds
+  float* dlog_val;        // [n, 2, log_cap] direct hits: score g - hb_j
+  int* dlog_idx;          //                  bank row j
+  int* dlog_cnt;          // [n, 2]
+  int log_cap;
+  // transposed hits go to ONE append buffer (hub rows are candidates of thousands of rows: a
+  // per-row log cannot be sized): entries (query row j, score g - hb_i, bank row i), staged per
+  // warp in shared memory and appended 64+ at a time with one atomicAdd on tq_count
+  int* tq_target;
+  float* tq_val;
+  int* tq_src;
+  unsigned long long* tq_count;   // entries appended (may exceed tq_cap: the excess is dropped)
+  long long tq_cap;
 };
 
 // Per-row candidate state of one epilogue thread.  The k best scores seen so far are kept sorted
@@ -733,11 +750,115 @@ __device__ __forceinline__ void filter_chunk_g(ListState& st, const uint32_t (&r
   }
 }
 
+// FILT 4: per-warp staging queue of transposed hits in shared memory (see ScreenParams).
+constexpr int SYM_QCAP = 128;
+struct SymQueue {
+  int* target; float* val; int* src; int* n;            // shared memory, this warp's
+  int* g_target; float* g_val; int* g_src;              // the global append buffer
+  unsigned long long* g_count;
+  long long g_cap;
+};
+__device__ __forceinline__ void sym_queue_flush(const SymQueue& q, int lane) {
+  __syncwarp();
+  const int cnt = min(*reinterpret_cast<volatile int*>(q.n), SYM_QCAP);
+  if (cnt > 0) {
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(q.g_count, (unsigned long long)cnt);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    for (int e = lane; e < cnt; e += 32) {
+      const long long at = (long long)base + e;
+      if (at < q.g_cap) {
+        q.g_target[at] = q.target[e];
+        q.g_val[at] = q.val[e];
+        q.g_src[at] = q.src[e];
+      }
+    }
+  }
+  __syncwarp();
+  if (lane == 0) *q.n = 0;
+  __syncwarp();
+}
+__device__ __forceinline__ void sym_queue_push(const SymQueue& q, int target, float v, int src) {
+  const int slot = atomicAdd(q.n, 1);
+  if (slot < SYM_QCAP) {
+    q.target[slot] = target;
+    q.val[slot] = v;
+    q.src[slot] = src;
+  } else {                                  // queue full inside one chunk (dense data): direct
+    const long long at = (long long)atomicAdd(q.g_count, 1ull);
+    if (at < q.g_cap) {
+      q.g_target[at] = target;
+      q.g_val[at] = v;
+      q.g_src[at] = src;
+    }
+  }
+}
+
+// FILT 4: one 32-column chunk tested in both directions against fixed thresholds (thread = row i
+// of the query tile = bank row i; column c = bank row j = query row j):
+//   direct      s_ij = g - hb_j >= tkeep_i          -> (s_ij, j) into row i's direct log
+//   transposed  s_ji = g - hb_i >= tkeep_j, tested as g - tkeep_j >= hb_i (the 4e-6 relative slack
+//               of the thresholds covers the different rounding) -> (j, s_ji, i) into the queue:
+//               "bank row i is a candidate of query row j"
+// nd counts every direct hit; entries beyond cap are dropped and the log reads as overflowed.
+__device__ __forceinline__ void sym_chunk(const uint32_t (&r)[32], const float* hn_chunk,
+                                          const float* tk_chunk, float tkeep_i, float hb_t,
+                                          float hb_i, int col0, int cap, float* dv, int* di,
+                                          int& nd, const SymQueue& sq, int row, int lane) {
+  const float4* hn4 = reinterpret_cast<const float4*>(hn_chunk);
+  const float4* tk4 = reinterpret_cast<const float4*>(tk_chunk);
+  float gd[8], gt[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    const float4 h = hn4[q], t = tk4[q];
+    const float a0 = __uint_as_float(r[4 * q]), a1 = __uint_as_float(r[4 * q + 1]);
+    const float a2 = __uint_as_float(r[4 * q + 2]), a3 = __uint_as_float(r[4 * q + 3]);
+    gd[q] = fmaxf(fmaxf(a0 - h.x, a1 - h.y), fmaxf(a2 - h.z, a3 - h.w));
+    gt[q] = fmaxf(fmaxf(a0 - t.x, a1 - t.y), fmaxf(a2 - t.z, a3 - t.w));
+  }
+  const float md = fmaxf(fmaxf(fmaxf(gd[0], gd[1]), fmaxf(gd[2], gd[3])),
+                         fmaxf(fmaxf(gd[4], gd[5]), fmaxf(gd[6], gd[7])));
+  const float mt = fmaxf(fmaxf(fmaxf(gt[0], gt[1]), fmaxf(gt[2], gt[3])),
+                         fmaxf(fmaxf(gt[4], gt[5]), fmaxf(gt[6], gt[7])));
+  if (__any_sync(0xffffffffu, md >= tkeep_i || mt >= hb_t)) {
+    uint32_t gm = 0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q)
+      gm |= ((gd[q] >= tkeep_i ? 1u : 0u) | (gt[q] >= hb_t ? 0x100u : 0u)) << q;
+#pragma unroll 1
+    while (gm) {
+      const int b = __ffs(gm) - 1;
+      gm &= gm - 1;
+      const int q = b & 7;
+      const bool transposed = b >= 8;
+      uint32_t u[4];
+      select_group(r, q, u);
+      const float4 c = transposed ? tk4[q] : hn4[q];
+      const float bound = transposed ? hb_t : tkeep_i;
+      const float sv[4] = {__uint_as_float(u[0]) - c.x, __uint_as_float(u[1]) - c.y,
+                           __uint_as_float(u[2]) - c.z, __uint_as_float(u[3]) - c.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (sv[i] >= bound) {
+          if (transposed) {
+            sym_queue_push(sq, col0 + 4 * q + i, __uint_as_float(u[i]) - hb_i, row);
+          } else {
+            if (nd < cap) { dv[nd] = sv[i]; di[nd] = col0 + 4 * q + i; }
+            ++nd;
+          }
+        }
+      }
+    }
+    __syncwarp();
+    if (*reinterpret_cast<volatile int*>(sq.n) >= 64) sym_queue_flush(sq, lane);
+  }
+}
+
 // FILT 1: seed + inline appends (short scans); 2: sample-tile seed + per-thread hit loop;
 // 3: as 2 with EIGHT epilogue warps — two trackers per query row, one per 128-column half of
 // the bank tile, lists in global memory, no barrier between the epilogue warps.
 template <int CG, int FILT>
-__global__ void __launch_bounds__(FILT == 3 ? SCR_THREADS_V3 : SCR_THREADS, 1)
+__global__ void __launch_bounds__(FILT >= 3 ? SCR_THREADS_V3 : SCR_THREADS, 1)
 knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
                   const __grid_constant__ CUtensorMap tmap_b, const ScreenParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -752,11 +873,14 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
   const int nkc = p.nkc, stages = p.stages;
   const uint32_t a_off = 0;
   const uint32_t b_off = a_off + (uint32_t)nkc * SCR_A_CHUNK_BYTES;
-  constexpr bool V3 = FILT == 3;
+  constexpr bool SYM = FILT == 4;
+  constexpr bool V3 = FILT == 3 || SYM;          // eight epilogue warps, no shared-memory lists
   const uint32_t lv_off = b_off + (uint32_t)stages * B_STAGE;
   const uint32_t li_off = lv_off + (V3 ? 0 : SCR_CAP * SCR_M * 4);
   const uint32_t hn_off = li_off + (V3 ? 0 : SCR_CAP * SCR_M * 4);
-  const uint32_t bar_off = hn_off + (V3 ? 8 * (SCR_N / 2) * 4 : 2 * SCR_N * 4);
+  const uint32_t sq_off = hn_off + 16 * (SCR_N / 2) * 4;   // SYM: per-warp hit queues
+  const uint32_t bar_off = SYM ? sq_off + 8 * (SYM_QCAP * 12 + 16)
+                               : hn_off + (V3 ? 8 * (SCR_N / 2) * 4 : 2 * SCR_N * 4);
   float* s_lv = reinterpret_cast<float*>(sm + lv_off);
   int* s_li = reinterpret_cast<int*>(sm + li_off);
   float* s_hn = reinterpret_cast<float*>(sm + hn_off);
@@ -788,6 +912,11 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
       t_end = min(p.n_tiles, t_begin + p.tail_tps);
       head_slot = 1 + split;
     }
+  }
+  if constexpr (SYM) {
+    // own bank tile (SCR_N = CG * SCR_M rows: the pair's query rows ARE that tile) and upwards
+    t_begin = m_tile / CG;
+    t_end = p.n_tiles;
   }
   const int n_local = max(t_end - t_begin, 0);
 
@@ -830,7 +959,7 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
     return t_begin + tt;
   };
   // FILT 3: the first n_seed tiles are scored twice (seed phase, then again in the main phase)
-  const int n_seed = (FILT >= 2) ? min(p.seed_tiles, n_local) : 0;
+  const int n_seed = (FILT >= 2 && !SYM) ? min(p.seed_tiles, n_local) : 0;
   const int n_total = n_local + n_seed;
   auto tile_seq = [&](int jj) { return tile_of(jj < n_seed ? jj : jj - n_seed); };
 
@@ -919,6 +1048,94 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
         atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + 7), 1ull);
       }
     }
+  } else if constexpr (SYM) {
+    // ===================== symmetric epilogue, eight warps: (lane quadrant, column half) ========
+    const int quad = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int e = quad * 32 + lane;
+    const int64_t row = (int64_t)m_tile * SCR_M + e;
+    const bool row_ok = row < p.nq;
+    const int cap = p.log_cap;
+    const int64_t o = (row_ok ? row : 0) * 2 + half;
+    float* dv = p.dlog_val + o * cap;
+    int* di = p.dlog_idx + o * cap;
+    SymQueue sq;
+    {
+      uint8_t* qb = sm + sq_off + (warp - 2) * (SYM_QCAP * 12 + 16);
+      sq.target = reinterpret_cast<int*>(qb);
+      sq.val = reinterpret_cast<float*>(qb + SYM_QCAP * 4);
+      sq.src = reinterpret_cast<int*>(qb + SYM_QCAP * 8);
+      sq.n = reinterpret_cast<int*>(qb + SYM_QCAP * 12);
+      sq.g_target = p.tq_target; sq.g_val = p.tq_val; sq.g_src = p.tq_src;
+      sq.g_count = p.tq_count; sq.g_cap = p.tq_cap;
+      if (lane == 0) *sq.n = 0;
+      __syncwarp();
+    }
+    // rows past nq: unreachable thresholds in both directions
+    const float tkeep_i = row_ok ? __ldg(p.sym_tkeep + row) : FLT_MAX;
+    const float hb_i = row_ok ? __ldg(p.ha + row) : INFINITY;     // this row as a BANK row
+    int nd = 0;
+    float* hn = s_hn + (warp - 2) * (SCR_N / 2);                  // 128 bank half norms
+    float* tk = s_hn + (8 + warp - 2) * (SCR_N / 2);              // 128 column-row thresholds
+    auto load4 = [&](const float* arr, int t, float fill) -> float4 {
+      const int64_t c0 = (int64_t)t * SCR_N + half * (SCR_N / 2) + 4 * lane;
+      float4 h;
+      if (c0 + 3 < p.nb) {
+        h = __ldg(reinterpret_cast<const float4*>(arr + c0));
+      } else {
+        h.x = (c0 < p.nb) ? arr[c0] : fill;
+        h.y = (c0 + 1 < p.nb) ? arr[c0 + 1] : fill;
+        h.z = (c0 + 2 < p.nb) ? arr[c0 + 2] : fill;
+        h.w = (c0 + 3 < p.nb) ? arr[c0 + 3] : fill;
+      }
+      return h;
+    };
+    float4 hnext = make_float4(0.f, 0.f, 0.f, 0.f), tnext = hnext;
+    if (n_total > 0) {
+      hnext = load4(p.hb, tile_seq(0), INFINITY);
+      tnext = load4(p.sym_tkeep, tile_seq(0), INFINITY);
+    }
+    constexpr int NCH = SCR_N / 2 / 32;
+    for (int jj = 0; jj < n_total; ++jj) {
+      const int t = tile_seq(jj);
+      const int as = jj & 1;
+      const bool diag = t == t_begin;            // own tile: the direct test covers both orders
+      __syncwarp();
+      reinterpret_cast<float4*>(hn)[lane] = hnext;
+      reinterpret_cast<float4*>(tk)[lane] = tnext;
+      __syncwarp();
+      if (jj + 1 < n_total) {
+        hnext = load4(p.hb, tile_seq(jj + 1), INFINITY);
+        tnext = load4(p.sym_tkeep, tile_seq(jj + 1), INFINITY);
+      }
+      mbar_wait(bar_tfull(as), ((uint32_t)jj >> 1) & 1u);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)as * SCR_N +
+                             (uint32_t)half * (SCR_N / 2);
+      const int col_base = t * SCR_N + half * (SCR_N / 2);
+      const float hb_t = diag ? INFINITY : hb_i;  // transposed test off on the diagonal tile
+      uint32_t ra[32], rb[32];
+      tmem_ld32(t_row, ra);
+#pragma unroll 1
+      for (int ch = 0; ch < NCH; ch += 2) {
+        tmem_ld_wait();
+        tmem_ld32(t_row + (ch + 1) * 32, rb);
+        sym_chunk(ra, hn + ch * 32, tk + ch * 32, tkeep_i, hb_t, hb_i, col_base + ch * 32, cap, dv,
+                  di, nd, sq, (int)row, lane);
+        tmem_ld_wait();
+        if (ch + 2 < NCH) tmem_ld32(t_row + (ch + 2) * 32, ra);
+        sym_chunk(rb, hn + (ch + 1) * 32, tk + (ch + 1) * 32, tkeep_i, hb_t, hb_i,
+                  col_base + (ch + 1) * 32, cap, dv, di, nd, sq, (int)row, lane);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if constexpr (CG == 2) mbar_arrive_leader(bar_tempty(as));
+        else mbar_arrive(bar_tempty(as));
+      }
+    }
+    sym_queue_flush(sq, lane);
+    if (row_ok) p.dlog_cnt[o] = nd > cap ? -1 : nd;
   } else if constexpr (V3) {
     // ===================== epilogue, eight warps: (lane quadrant, column half) ================
     const int quad = warp & 3;                    // TMEM lane quadrant this warp may access
@@ -1175,6 +1392,7 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
 #include "knn_lat.cuh"
 #include "knn_rerank.cuh"
 #include "knn_chain.cuh"
+#include "knn_sym.cuh"
 
 namespace exb {
 
@@ -2048,6 +2266,195 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
 
   // undecided rows -> exact kernel, indirect through the device-side row list / count
   return launch_exact(src, nq, bank, nb, dim, k, idx_base, out_dist, out_idx, w.fb_d2, w.fb_idx,
+                      pl.fb_splits, w.fb_rows, &w.status->n_fallback, pl.fb_cap, st);
+}
+
+// ------------------------------------------------------------------------------------------
+// Symmetric screen (knn_sym.cuh): source == bank at dataset scale.
+// ------------------------------------------------------------------------------------------
+struct SymPlan {
+  int dpad, nkc, m_tiles, n_tiles, stages;
+  size_t smem;
+  int fb_cap, fb_splits;
+};
+
+static bool sym_plan(int64_t n, int dim, int k, SymPlan* pl) {
+  if (dim < 1 || dim > EXB_SCREEN_MAX_DIM || k < 1 || k > SCR_MAX_K || n < 4 * SCR_N ||
+      n >= (1LL << 31) || k > n)
+    return false;
+  pl->dpad = dim_pad(dim);
+  pl->nkc = pl->dpad / SCR_KC;
+  pl->n_tiles = (int)((n + SCR_N - 1) / SCR_N);
+  pl->m_tiles = 2 * pl->n_tiles;               // CTA pairs: query rows of pair u = bank tile u
+  pl->fb_cap = (int)(n < FALLBACK_CAP ? n : FALLBACK_CAP);
+  int fbs = (int)((n + 127) / 128);
+  if (fbs > FALLBACK_SPLITS) fbs = FALLBACK_SPLITS;
+  if (fbs * k > 512) fbs = 512 / k;
+  pl->fb_splits = fbs < 1 ? 1 : fbs;
+  const size_t fixed = (size_t)pl->nkc * SCR_A_CHUNK_BYTES + 16 * (SCR_N / 2) * 4 +
+                       8 * (SYM_QCAP * 12 + 16) + (2 * SCR_MAX_STAGES + 5) * 8 + 16 + 1024;
+  const int b_stage = SCR_B_STAGE_BYTES / 2;
+  int stages = (int)((SCR_SMEM_LIMIT - fixed) / b_stage);
+  if (stages > SCR_MAX_STAGES) stages = SCR_MAX_STAGES;
+  if (stages < 2) return false;
+  pl->stages = stages;
+  pl->smem = fixed + (size_t)stages * b_stage;
+  return true;
+}
+
+struct SymWs {
+  RerankStatus* status;
+  PrepScalars* bsc;
+  __half* b16;
+  float *hb, *eb, *aff, *cs_stats, *cs_part, *tkeep;
+  float *dlog_val, *tq_val, *rval, *fb_d2;
+  int *dlog_idx, *tq_target, *tq_src, *ridx, *dlog_cnt, *rcnt, *fb_rows, *fb_idx;
+  unsigned long long* tq_count;
+  long long tq_cap;
+};
+
+static size_t carve_sym(void* ws, int64_t n, const SymPlan& pl, int k, int log_cap, int rcap,
+                        SymWs* o) {
+  Carver cv(ws ? ws : reinterpret_cast<void*>(256));
+  o->status = cv.take<RerankStatus>(1);
+  cv.take<PrepScalars>(1);                     // (slot of the query scalars in carve_screen)
+  o->bsc = cv.take<PrepScalars>(1);
+  cv.take<long long>(16);
+  o->b16 = cv.take<__half>((size_t)n * pl.dpad);
+  o->hb = cv.take<float>(n);
+  o->eb = cv.take<float>(n);
+  o->aff = cv.take<float>(AFF_FLOATS);
+  o->cs_stats = cv.take<float>(3 * (size_t)pl.dpad);
+  o->cs_part = cv.take<float>((size_t)CS_MAX_BLOCKS * 3 * pl.dpad);
+  o->tkeep = cv.take<float>(n);
+  o->dlog_val = cv.take<float>((size_t)n * 2 * log_cap);
+  o->dlog_idx = cv.take<int>((size_t)n * 2 * log_cap);
+  // transposed hits: every row receives rcap / 3 on average by the caller's sizing (rcap = 3x
+  // the expectation of a row that receives ALL its candidates); half of all candidates travel
+  o->tq_cap = (long long)n * (rcap / 3 + 16);
+  o->tq_target = cv.take<int>((size_t)o->tq_cap);
+  o->tq_val = cv.take<float>((size_t)o->tq_cap);
+  o->tq_src = cv.take<int>((size_t)o->tq_cap);
+  o->tq_count = cv.take<unsigned long long>(2);
+  o->dlog_cnt = cv.take<int>((size_t)n * 2);
+  o->rval = cv.take<float>((size_t)n * rcap);
+  o->ridx = cv.take<int>((size_t)n * rcap);
+  o->rcnt = cv.take<int>(n);
+  o->fb_rows = cv.take<int>(pl.fb_cap);
+  o->fb_d2 = cv.take<float>((size_t)pl.fb_cap * pl.fb_splits * k);
+  o->fb_idx = cv.take<int>((size_t)pl.fb_cap * pl.fb_splits * k);
+  return cv.off + 256;
+}
+
+extern "C" size_t exb_knn_sym_workspace_bytes(int64_t n, int dim, int k, int log_cap,
+                                              int recv_cap) {
+  SymPlan pl;
+  if (!sym_plan(n, dim, k, &pl) || log_cap < 32 || recv_cap < 32) return 0;
+  SymWs w;
+  return carve_sym(nullptr, n, pl, k, log_cap, recv_cap, &w);
+}
+
+extern "C" int exb_knn_sym_f32(const float* rep, int64_t n, int dim, int k, int32_t idx_base,
+                               const float* d_sample, int64_t d_stride, int log_cap, int recv_cap,
+                               float* out_dist, int32_t* out_idx, void* workspace,
+                               size_t workspace_bytes, exb_stream_t stream) {
+  EXB_CHECK_ARG(rep && d_sample && out_dist && out_idx && workspace, "null pointer");
+  SymPlan pl;
+  if (!sym_plan(n, dim, k, &pl) || log_cap < 32 || recv_cap < 32) {
+    set_error("symmetric screen needs n >= %d, dim <= %d, k <= %d (got n=%lld dim=%d k=%d)",
+              4 * SCR_N, EXB_SCREEN_MAX_DIM, SCR_MAX_K, (long long)n, dim, k);
+    return EXB_EUNSUPPORTED;
+  }
+  SymWs w;
+  const size_t need = carve_sym(nullptr, n, pl, k, log_cap, recv_cap, &w);
+  EXB_CHECK_ARG(workspace_bytes >= need, "workspace too small: %zu < %zu", workspace_bytes, need);
+  EXB_CHECK_ARG(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  carve_sym(workspace, n, pl, k, log_cap, recv_cap, &w);
+  cudaStream_t st = (cudaStream_t)stream;
+  EXB_CUDA(cudaMemsetAsync(workspace, 0, 1024 + 64, st));
+  EXB_CUDA(cudaMemsetAsync(w.rcnt, 0, (size_t)n * sizeof(int), st));
+  EXB_CUDA(cudaMemsetAsync(w.tq_count, 0, 16, st));
+  int rc = launch_affine(rep, n, nullptr, 0, dim, w.cs_part, nullptr, w.cs_stats, w.aff, st);
+  if (rc) return rc;
+  rc = launch_prep(rep, n, dim, pl.dpad, w.b16, w.hb, w.eb, w.bsc, st, nullptr, w.aff);
+  if (rc) return rc;
+  SymThresholdParams tp;
+  tp.d_sample = d_sample; tp.stride = d_stride; tp.ha = w.hb; tp.ea = w.eb; tp.bsc = w.bsc;
+  tp.aff = w.aff; tp.tkeep = w.tkeep; tp.n = n;
+  sym_threshold_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(tp);
+  EXB_LAUNCH_CHECK();
+
+  CUtensorMap tq, tb;
+  rc = make_tmap(&tq, w.b16, n, pl.dpad, SCR_M);
+  if (rc) return rc;
+  rc = make_tmap(&tb, w.b16, n, pl.dpad, SCR_N / 2);
+  if (rc) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    EXB_CUDA(cudaFuncSetAttribute(knn_screen_kernel<2, 4>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, SCR_SMEM_LIMIT));
+    attr_set = true;
+  }
+  ScreenParams sp;
+  memset(&sp, 0, sizeof(sp));
+  sp.ha = w.hb; sp.ea = w.eb; sp.hb = w.hb; sp.bsc = w.bsc;
+  sp.nq = n; sp.nb = n; sp.nkc = pl.nkc; sp.n_tiles = pl.n_tiles;
+  sp.tiles_per_split = pl.n_tiles; sp.splits = 1; sp.k = k; sp.stages = pl.stages;
+  sp.lists = 2; sp.head = nullptr;
+  sp.sym_tkeep = w.tkeep; sp.dlog_val = w.dlog_val; sp.dlog_idx = w.dlog_idx;
+  sp.dlog_cnt = w.dlog_cnt; sp.log_cap = log_cap;
+  sp.tq_target = w.tq_target; sp.tq_val = w.tq_val; sp.tq_src = w.tq_src;
+  sp.tq_count = w.tq_count; sp.tq_cap = w.tq_cap;
+  {
+    const bool prof = g_prof.on && g_prof.n < 64;
+    if (prof) EXB_CUDA(cudaEventRecord(g_prof.e0[g_prof.n], st));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)pl.m_tiles, 1);
+    cfg.blockDim = dim3(SCR_THREADS_V3);
+    cfg.dynamicSmemBytes = pl.smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    EXB_CUDA(cudaLaunchKernelEx(&cfg, knn_screen_kernel<2, 4>, tq, tb, sp));
+    if (prof) EXB_CUDA(cudaEventRecord(g_prof.e1[g_prof.n++], st));
+  }
+  SymLists sl;
+  sl.dlog_val = w.dlog_val; sl.dlog_idx = w.dlog_idx; sl.dlog_cnt = w.dlog_cnt;
+  sl.log_cap = log_cap; sl.tq_target = w.tq_target; sl.tq_val = w.tq_val; sl.tq_src = w.tq_src;
+  sl.tq_count = w.tq_count; sl.tq_cap = w.tq_cap;
+  sl.rval = w.rval; sl.ridx = w.ridx; sl.rcnt = w.rcnt; sl.rcap = recv_cap;
+  sym_scatter_kernel<<<148 * 8, 256, 0, st>>>(sl, w.status);
+  EXB_LAUNCH_CHECK();
+  static const int sym_stats = knob("EXB_SYM_STATS", 0);
+  if (sym_stats) {   // counts into the 16 trace words (exb_debug_trace_sync), zeroed by the memset
+    sym_stats_kernel<<<(unsigned)((2 * n + 255) / 256), 256, 0, st>>>(
+        sl, n, reinterpret_cast<long long*>(static_cast<char*>(workspace) + 768));
+    EXB_LAUNCH_CHECK();
+  }
+
+  const bool vec = (dim % 4 == 0) && (((uintptr_t)rep) & 15) == 0;
+  const int ni = vec ? (dim + 127) / 128 : 0;
+  RerankParams rp;
+  memset(&rp, 0, sizeof(rp));
+  rp.Q = rep; rp.B = rep; rp.nq = n; rp.nb = n; rp.dim = dim; rp.k = k; rp.idx_base = idx_base;
+  rp.splits = 2; rp.ha = w.hb; rp.ea = w.eb; rp.qsc = w.bsc; rp.bsc = w.bsc;
+  rp.out_dist = out_dist; rp.out_idx = out_idx; rp.fallback_rows = w.fb_rows;
+  rp.fallback_cap = pl.fb_cap; rp.status = w.status;
+  const unsigned rr_grid = (unsigned)((n + RR_WARPS - 1) / RR_WARPS);
+  switch (ni) {
+    case 1: knn_rerank_sym_kernel<1><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp, sl); break;
+    case 2: knn_rerank_sym_kernel<2><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp, sl); break;
+    case 3: knn_rerank_sym_kernel<3><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp, sl); break;
+    case 4: knn_rerank_sym_kernel<4><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp, sl); break;
+    default: knn_rerank_sym_kernel<0><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp, sl); break;
+  }
+  EXB_LAUNCH_CHECK();
+  return launch_exact(rep, n, rep, n, dim, k, idx_base, out_dist, out_idx, w.fb_d2, w.fb_idx,
                       pl.fb_splits, w.fb_rows, &w.status->n_fallback, pl.fb_cap, st);
 }
 

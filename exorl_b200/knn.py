@@ -108,13 +108,68 @@ def _knn_topk_prepared(pre_s, pre_t, k, idx_base, mode):
     return dist, idx
 
 
-def _knn_topk_impl(src, tgt, k, idx_base, mode, same):
+# Symmetric screen (csrc/knn_sym.cuh): a set against itself at dataset scale.
+SYM_ENABLED = True
+SYM_MIN_ROWS = 65536          # below, the sample pre-pass is too large a share of the work
+SYM_SAMPLE_MAX = 65536
+sym_last = {}                 # diagnostics of the last symmetric call (sizes, fallback reason)
+
+
+def _sym_sample_rows(n):
+    return int(min(SYM_SAMPLE_MAX, max(4096, n // 16)))
+
+
+def _knn_topk_sym(src, k, idx_base):
+    """kNN of `src` against itself through the symmetric screen, or None when the pass reports
+    that it cannot certify the result (a transposed log overflowed: hub rows, heavy duplication)
+    — the caller then runs the full screen."""
+    lib = _lib.load()
+    n, dim = src.shape
+    dev = src.device
+    stride = max(1, n // _sym_sample_rows(n))
+    sample = src[::stride].contiguous()
+    # exact distance of every row to its k-th nearest SAMPLE row: an upper bound of its true
+    # k-th-neighbour distance, which fixes the row's keep threshold for the symmetric pass
+    d_s, _ = _knn_topk_impl(src, sample, k, 0, "screened", False, allow_sym=False)
+    expected = 1.3 * k * n / sample.size(0)          # candidates per row the thresholds admit
+    log_cap = int(-(-(3 * expected / 2 + 96) // 8) * 8)      # direct log per (row, column half)
+    recv_cap = int(-(-(3 * expected + 96) // 8) * 8)         # received list per row
+    with torch.cuda.device(dev):
+        dist = torch.empty(n, k, dtype=torch.float32, device=dev)
+        idx = torch.empty(n, k, dtype=torch.int32, device=dev)
+        need = lib.exb_knn_sym_workspace_bytes(n, dim, k, log_cap, recv_cap)
+        if need == 0:
+            return None
+        ws, _ = _lib.Workspace.get(dev, "knn_sym", need)
+        _lib.check(lib.exb_knn_sym_f32(
+            _lib.ptr(src), n, dim, k, int(idx_base), _lib.ptr(d_s[:, k - 1:]), k, log_cap,
+            recv_cap, _lib.ptr(dist), _lib.ptr(idx), _lib.ptr(ws), ws.numel(),
+            _lib.stream_ptr(dev)))
+    st = screened_status(dev, key="knn_sym")
+    sym_last.update(n=n, sample_rows=sample.size(0), log_cap=log_cap, recv_cap=recv_cap,
+                    undecided=st[0], status=st[1])
+    if st[1] & 2:
+        return None
+    if st[1] & 1:
+        rows = (idx[:, 0] < 0).nonzero().flatten()
+        _recompute_rows(src, src, k, idx_base, dist, idx, rows)
+    return dist, idx
+
+
+def _knn_topk_impl(src, tgt, k, idx_base, mode, same, allow_sym=True):
     """CUDA implementation of torch.ops.exorl_b200.knn_topk: contiguous fp32 (b, c) rows in."""
     lib = _lib.load()
     if same:
         tgt = src
     nq, nb, dim = src.size(0), tgt.size(0), src.size(1)
     dev = src.device
+    if (same and allow_sym and SYM_ENABLED and mode != "exact" and nq >= SYM_MIN_ROWS
+            and OVERFLOW_POLICY == "sync" and _repair_depth == 0
+            and dim <= _lib.SCREEN_MAX_DIM and k <= _lib.SCREEN_MAX_K and nq > 4 * k):
+        out = _knn_topk_sym(src, k, idx_base)
+        if out is not None:
+            return out
+        sym_last["fell_back_to_full_screen"] = True
     with torch.cuda.device(dev):
         dist = torch.empty(nq, k, dtype=torch.float32, device=dev)
         idx = torch.empty(nq, k, dtype=torch.int32, device=dev)

@@ -104,6 +104,24 @@ int exb_knn_prep_affine_f16(const float* x, int64_t n, int dim, const float* aff
                             float* round_err /* [n] */, float* scalars /* 16 bytes */,
                             exb_stream_t stream);
 
+/* Symmetric screen: kNN of a set against ITSELF (PBE / the relabel: utils/utils.py:290,
+ * source = target) at dataset scale with HALF the tensor-core work of exb_knn_screened_f32 — the
+ * product a^_i . a^_j serves the pairs (i, j) and (j, i), so only tile pairs I <= J are
+ * multiplied.  d_sample[i * d_stride] = exact distance of row i to its k-th nearest row inside a
+ * sample of the same set (any subset; e.g. exb_knn_screened_f32 of the set against every 32nd
+ * row): it fixes every row's keep threshold before the pass.  log_cap / recv_cap: slots of the
+ * per-(row, column half) hit logs and of the per-row received-hit list (about 3x the expected
+ * k * n / sample_rows / 4 and k * n / sample_rows / 2 entries).  Same results as the other
+ * paths; rows whose logs overflow are recomputed by the exact kernel (up to 4096; more -> status
+ * flag bit 0 as for exb_knn_screened_f32), a transposed log that overflows sets status flag bit
+ * 1 (the call must be repeated with exb_knn_screened_f32).  Status: exb_knn_screened_status_sync
+ * on the workspace.  Needs n >= 1024, dim <= EXB_SCREEN_MAX_DIM, k <= 16. */
+size_t exb_knn_sym_workspace_bytes(int64_t n, int dim, int k, int log_cap, int recv_cap);
+int exb_knn_sym_f32(const float* rep, int64_t n, int dim, int k, int32_t idx_base,
+                    const float* d_sample, int64_t d_stride, int log_cap, int recv_cap,
+                    float* out_dist /* [n,k] */, int32_t* out_idx /* [n,k] */, void* workspace,
+                    size_t workspace_bytes, exb_stream_t stream);
+
 size_t exb_knn_screened_workspace_bytes(int64_t nq, int64_t nb, int dim, int k);
 /* src_is_bank != 0 tells the call that src and bank are the same tensor (PBE: source = target,
  * utils/utils.py:290) so the fp16 operand is prepared once. */

@@ -339,3 +339,71 @@ def test_relabel_from_host_pipeline_equals_device_resident_call(n, dim):
     assert diff <= n // 1000
     assert rms_a.n == rms_b.n
     np.testing.assert_allclose(float(rms_a.M), float(rms_b.M), rtol=1e-6)
+
+
+# ------------------------------------------------------------------ symmetric screen (knn_sym.cuh)
+@pytest.fixture
+def sym_on():
+    from exorl_b200 import knn as xknn
+    prev = (xknn.SYM_ENABLED, xknn.SYM_MIN_ROWS)
+    xknn.SYM_ENABLED, xknn.SYM_MIN_ROWS = True, 1024
+    xknn.sym_last.clear()
+    yield xknn
+    xknn.SYM_ENABLED, xknn.SYM_MIN_ROWS = prev
+
+
+@pytest.mark.parametrize("n,dim,k,kind", [(20000, 64, 12, "tanh"), (9001, 512, 12, "tanh"),
+                                          (12345, 50, 5, "raw"), (16384, 128, 3, "unit"),
+                                          (6000, 130, 16, "tanh")])
+def test_symmetric_screen_equals_full_screen_and_oracle(sym_on, n, dim, k, kind):
+    """A set against itself through the symmetric screen (half the tile pairs, thresholds fixed
+    from a sample pre-pass, direct + transposed hit logs): the result must be the full screen's
+    — and the oracle's on a query slice — for ragged sizes, vector and scalar row layouts."""
+    x = reps(41, n, dim, kind)
+    xd = x.to(DEV)
+    d_s, i_s = xb.knn_topk(xd, xd, k, mode="screened")
+    assert sym_on.sym_last.get("n") == n and "fell_back_to_full_screen" not in sym_on.sym_last
+    assert sym_on.sym_last["status"] == 0
+    sym_on.SYM_ENABLED = False
+    d_f, i_f = xb.knn_topk(xd, xd, k, mode="screened")
+    assert torch.equal(d_s, d_f)
+    assert (i_s != i_f).any(dim=1).sum().item() <= 2          # exact ties only
+    sl = slice(n - 700, n)                                    # late rows: candidates arrive transposed
+    assert_knn_matches(x[sl], x, k, d_s[sl], i_s[sl])
+    assert_knn_matches(x[:300], x, k, d_s[:300], i_s[:300])
+
+
+def test_symmetric_screen_on_shifted_scaled_and_duplicated_rows(sym_on):
+    """Range-proof operands carry over (thresholds are formed in the operand space), and rows whose
+    logs overflow (6000 duplicates) are recomputed — or the pass reports itself invalid and the
+    full screen runs; either way the exact path's result."""
+    n, dim, k = 24000, 64, 12
+    x = reps(43, n, dim, "raw") * 1e5 + 3e6
+    xd = x.to(DEV)
+    d_s, i_s = xb.knn_topk(xd, xd, k, mode="screened")
+    assert sym_on.sym_last["status"] == 0 and sym_on.sym_last["undecided"] == 0
+    d_e, i_e = xb.knn_topk(xd, xd, k, mode="exact")
+    np.testing.assert_allclose(d_s.cpu().numpy(), d_e.cpu().numpy(), rtol=1e-6)
+    assert (i_s != i_e).any(dim=1).sum().item() <= 8
+    y = reps(44, n, dim)
+    y[5000:11000] = y[4999]
+    yd = y.to(DEV)
+    sym_on.sym_last.clear()
+    d_s, i_s = xb.knn_topk(yd, yd, k, mode="screened")
+    d_e, i_e = xb.knn_topk(yd, yd, k, mode="exact")
+    np.testing.assert_allclose(d_s.cpu().numpy(), d_e.cpu().numpy(), rtol=1e-6, atol=1e-6)
+    assert not d_s[5000:11000].any()
+
+
+def test_symmetric_screen_relabel_reward_matches_oracle(sym_on):
+    n, dim, k = 16000, 512, 12
+    x = reps(45, n, dim)
+    args = types.SimpleNamespace(knn_k=k, knn_avg=True, knn_rms=True, knn_clip=0.0)
+    rms = xb.RMS(DEV)
+    r = xb.relabel_apt_reward(x.to(DEV), args, rms=rms)
+    assert sym_on.sym_last.get("n") == n and sym_on.sym_last["status"] == 0
+    sl = slice(0, 400)
+    st = RmsState()
+    want = pbe_reward(x, x, st, k, True, True, 0.0)
+    np.testing.assert_allclose(r.cpu().numpy()[sl], want.numpy()[sl], rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(float(rms.M), float(st.M), rtol=1e-6)
