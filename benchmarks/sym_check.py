@@ -33,6 +33,8 @@ def main():
     ap.add_argument("--iters", type=int, default=3)
     ap.add_argument("--exact-max", type=int, default=140000)
     ap.add_argument("--kind", default="tanh")
+    ap.add_argument("--sample-max", type=int, default=0, help="override knn.SYM_SAMPLE_MAX")
+    ap.add_argument("--no-full", action="store_true", help="skip the full-screen comparison")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     import ctypes
@@ -50,10 +52,19 @@ def main():
                 0.05 * torch.randn(n // 1000 + 1, 1000, 24, generator=g, device=dev), dim=1)
             x = torch.tanh(torch.nn.functional.layer_norm(obs.reshape(-1, 24)[:n] @ w, (a.dim,)))
         xknn.SYM_MIN_ROWS = 1024
+        if a.sample_max:
+            xknn.SYM_SAMPLE_MAX = a.sample_max
         xknn.SYM_ENABLED = True
         xknn.sym_last.clear()
         t_sym, (d_s, i_s) = timed(lambda: xb.knn_topk(x, x, a.k, mode="screened"), a.iters)
         info = dict(xknn.sym_last)
+        # one more call with the library's event brackets around the two screen launches
+        kms, kn = (ctypes.c_float * 64)(), ctypes.c_int(0)
+        _lib.check(lib.exb_profile_begin(1))
+        xb.knn_topk(x, x, a.k, mode="screened")
+        _lib.check(lib.exb_profile_collect_sync(kms, 64, ctypes.byref(kn)))
+        _lib.check(lib.exb_profile_begin(0))
+        info["screen_launch_ms"] = [round(kms[i], 3) for i in range(kn.value)]
         ws, _ = _lib.Workspace.get(dev, "knn_sym", 1024)
         tr = (ctypes.c_int64 * 16)()
         _lib.check(lib.exb_debug_trace_sync(_lib.ptr(ws), tr, _lib.stream_ptr(dev)))
@@ -63,12 +74,13 @@ def main():
                           "received_mean": t[4] / n, "received_max": t[5],
                           "direct_overflowed": t[6]}
         xknn.SYM_ENABLED = False
-        t_full, (d_f, i_f) = timed(lambda: xb.knn_topk(x, x, a.k, mode="screened"), a.iters)
-        out = {"n": n, "dim": a.dim, "k": a.k, "kind": a.kind, "sym_ms": t_sym, "full_ms": t_full,
-               "speedup": t_full / t_sym, "sym_info": info,
-               "dist_equal_full": bool(torch.equal(d_s, d_f)),
-               "idx_rows_differing_from_full": int((i_s != i_f).any(dim=1).sum()),
-               "max_abs_dist_diff_vs_full": float((d_s - d_f).abs().max())}
+        out = {"n": n, "dim": a.dim, "k": a.k, "kind": a.kind, "sym_ms": t_sym, "sym_info": info}
+        if not a.no_full:
+            t_full, (d_f, i_f) = timed(lambda: xb.knn_topk(x, x, a.k, mode="screened"), a.iters)
+            out.update({"full_ms": t_full, "speedup": t_full / t_sym,
+                        "dist_equal_full": bool(torch.equal(d_s, d_f)),
+                        "idx_rows_differing_from_full": int((i_s != i_f).any(dim=1).sum()),
+                        "max_abs_dist_diff_vs_full": float((d_s - d_f).abs().max())})
         if n <= a.exact_max:
             d_e, i_e = xb.knn_topk(x, x, a.k, mode="exact")
             out["max_abs_dist_diff_vs_exact"] = float((d_s - d_e).abs().max())

@@ -504,7 +504,9 @@ def relabel_apt_reward_from_host(rep_host, args, rms=None, group=None, rep_out=N
     if rep_out is None:
         rep_out = torch.empty((n, dim), dtype=torch.float32, device=dev)
     lists = screen_lists_count(max(n // world, 1), n, dim, k)
-    if n % world != 0 or lists == 0 or lists > 16:
+    if world == 1 or n % world != 0 or lists == 0 or lists > 16:
+        # one GPU: nothing to pipeline against — copy, then the device path (which takes the
+        # symmetric screen for a set against itself)
         rep = reps_from_host(rep_host, out=rep_out, group=group)
         return relabel_apt_reward(rep, args, rms=rms, group=group, mode="screened",
                                   return_knn=return_knn, balance=balance)

@@ -204,8 +204,10 @@ def test_c5_full_size_properties(golden):
     args = types.SimpleNamespace(knn_k=k, knn_avg=True, knn_rms=True, knn_clip=0.0)
     rms = xb.RMS(DEV)
     reward, dist, idx = xb.relabel_apt_reward(rep, args, rms=rms, mode="screened", return_knn=True)
-    und, invalid, _, _ = xb.knn.screened_status(DEV)
-    assert invalid == 0 and und == 0
+    # a set against itself at this size takes the symmetric screen (knn_sym.cuh): its status
+    sym = xb.knn.sym_last
+    assert sym.get("n") == n and "fell_back_to_full_screen" not in sym
+    assert sym["status"] == 0 and sym["undecided"] == 0
     assert reward.shape == (n, 1) and dist.shape == (n, k) and idx.shape == (n, k)
     assert torch.equal(idx[:, 0], torch.arange(n, dtype=torch.int32, device=DEV))
     assert not dist[:, 0].any()
@@ -366,8 +368,9 @@ def test_symmetric_screen_equals_full_screen_and_oracle(sym_on, n, dim, k, kind)
     assert sym_on.sym_last["status"] == 0
     sym_on.SYM_ENABLED = False
     d_f, i_f = xb.knn_topk(xd, xd, k, mode="screened")
-    assert torch.equal(d_s, d_f)
-    assert (i_s != i_f).any(dim=1).sum().item() <= 2          # exact ties only
+    # bit-equal unless one of the two paths sent a row to the exact kernel (other summation order)
+    np.testing.assert_allclose(d_s.cpu().numpy(), d_f.cpu().numpy(), rtol=1e-6, atol=1e-7)
+    assert (i_s != i_f).any(dim=1).sum().item() <= max(2, n // 2000)   # fp32 near-ties only
     sl = slice(n - 700, n)                                    # late rows: candidates arrive transposed
     assert_knn_matches(x[sl], x, k, d_s[sl], i_s[sl])
     assert_knn_matches(x[:300], x, k, d_s[:300], i_s[:300])
