@@ -338,7 +338,8 @@ def run_ours(a, rank, world, local_rank):
     if rank == 0:
         sustained, burst, src = peaks()
         nb_local = a.n // world
-        sym = (world == 1 and xknn.sym_last.get("n") == a.n
+        sym = (xknn.sym_last.get("n") == a.n and xknn.sym_last.get("world", 1) == world
+               and a.exchange in ("auto", "queries")
                and "fell_back_to_full_screen" not in xknn.sym_last and kn.value == 2 * a.steps)
         flops = 2.0 * a.n * nb_local * a.dim          # algorithmic: every (query, bank row) pair
         sym_info = None
@@ -349,7 +350,8 @@ def run_ours(a, rank, world, local_rank):
             pre_ms = sum(kms[i] for i in range(0, kn.value, 2)) / a.steps
             kernel_ms = sum(kms[i] for i in range(1, kn.value, 2)) / a.steps
             t = (a.n + 255) // 256
-            executed = 2.0 * 256 * 256 * a.dim * (t * (t + 1) / 2)
+            executed = 2.0 * 256 * 256 * a.dim * (t * (t + 1) / 2) / world   # this rank's tile pairs
+            flops = flops                                  # (algorithmic share of a rank: N * N/G)
             s_rows = xknn.sym_last["sample_rows"]
             achieved = executed / (kernel_ms * 1e-3) / 1e12
             und, invalid = xknn.sym_last["undecided"], xknn.sym_last["status"]
@@ -358,7 +360,7 @@ def run_ours(a, rank, world, local_rank):
                 "executed_flops_per_launch": executed,
                 "executed_over_algorithmic": executed / flops,
                 "sample_prepass": {"rows": s_rows, "kernel_ms": pre_ms,
-                                   "flops": 2.0 * a.n * s_rows * a.dim},
+                                   "flops": 2.0 * (a.n / world) * s_rows * a.dim},
                 "algorithmic_tflops_equivalent_of_both_launches":
                     flops / ((kernel_ms + pre_ms) * 1e-3) / 1e12,
                 "note": "frac = EXECUTED flops of the symmetric kernel / its time / peak; the "
@@ -373,7 +375,7 @@ def run_ours(a, rank, world, local_rank):
         # symmetric path (1 GPU): sample gather, [colstats x2, reduce, affine, prep x2, screen,
         # rerank, exact, merge] of the pre-pass, [colstats, reduce, affine, prep, threshold, screen,
         # scatter, rerank, exact, merge], moments, finish
-        launches_per_step = (23 if sym else 10) if world == 1 else 14
+        launches_per_step = (23 if sym else 10) if world == 1 else (25 if sym else 14)
         out = {
             "metric": METRIC, "value": a.n * a.steps / (ms * 1e-3), "unit": UNIT,
             "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms / a.steps,
@@ -384,6 +386,8 @@ def run_ours(a, rank, world, local_rank):
             "config": {"workload": workload(a), "n": a.n, "dim": a.dim, "k": a.k,
                        "parallelism": (f"{world} GPU(s), exchange={a.exchange}" + (
                            "" if world == 1 else
+                           " (symmetric screen: every unordered tile pair on one rank, transposed "
+                           "hits exchanged all-to-all)" if sym else
                            " (query blocks over the ranks, whole bank on every rank)"
                            if a.exchange in ("auto", "queries") else " (bank sharded)")),
                        "l2": "inputs (2 GB fp32 + 1 GB fp16 bank) larger than the 126 MB L2; "

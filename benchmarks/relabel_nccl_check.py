@@ -24,6 +24,8 @@ def main():
     ap.add_argument("--rows", dest="n", type=int, default=20000)
     ap.add_argument("--dim", type=int, default=512)
     ap.add_argument("--k", type=int, default=12)
+    ap.add_argument("--sym-min-rows", type=int, default=1024,
+                    help="knn.SYM_MIN_ROWS for the 'sym' legs (the symmetric screen over the ranks)")
     a = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
@@ -33,7 +35,9 @@ def main():
     rep = torch.tanh(torch.randn(a.n, a.dim, generator=g)).to(dev)
     args = types.SimpleNamespace(knn_k=a.k, knn_avg=True, knn_rms=True, knn_clip=0.0)
 
-    # single-shard truth on this rank's GPU (no collectives involved)
+    # single-shard truth on this rank's GPU (no collectives involved; full screen)
+    from exorl_b200 import knn as xknn
+    xknn.SYM_ENABLED = False
     d0, i0 = knn_topk(rep, rep, a.k, mode="screened")
     rms0 = xb.RMS(dev)
     r0 = _reward_from_knn(d0, a.k, True, True, 0.0, rms0.M, rms0.S, rms0._n)
@@ -45,10 +49,18 @@ def main():
     from exorl_b200 import relabel as xrel
     # "balanced" runs three times so that the rate-proportional query blocks (QueryBalance) have
     # moved away from the equal split by the last run; "from_host" is the end-to-end pipeline
-    for exchange in ("queries", "balanced", "balanced", "balanced", "from_host", "prepared",
-                     "lists", "auto", "all_to_all", "all_gather"):
+    for exchange in ("sym", "sym", "queries", "balanced", "balanced", "balanced", "from_host",
+                     "prepared", "lists", "auto", "all_to_all", "all_gather"):
         rms = xb.RMS(dev)
-        if exchange == "from_host":
+        xknn.SYM_ENABLED = exchange == "sym"
+        xknn.SYM_MIN_ROWS = a.sym_min_rows
+        if exchange == "sym":
+            xknn.sym_last.clear()
+            out = xb.relabel_apt_reward(rep, args, rms=rms, exchange="queries", mode="screened",
+                                        return_knn=True)
+            assert xknn.sym_last.get("world") == world, xknn.sym_last
+            assert "fell_back_to_full_screen" not in xknn.sym_last, xknn.sym_last
+        elif exchange == "from_host":
             out = xb.relabel_apt_reward_from_host(rep_host, args, rms=rms, return_knn=True)
         elif exchange == "prepared":
             out = xb.relabel_apt_reward(xb.prepare_rep(rep), args, rms=rms, exchange="queries",
@@ -66,7 +78,7 @@ def main():
         assert rms.n == rms0.n
         if exchange == "all_gather":            # every rank holds all rows
             lo, hi = 0, a.n
-        elif exchange in ("queries", "balanced", "auto", "prepared", "from_host"):
+        elif exchange in ("sym", "queries", "balanced", "auto", "prepared", "from_host"):
             lo, hi = xrel.last_query_block["lo"], xrel.last_query_block["hi"]   # balanced block
         else:                                    # rank r finalised query block r
             lo, hi = xrel.shard_bounds(a.n, world, rank)

@@ -31,6 +31,12 @@ class Operand(_c.Structure):
 _op_p = _c.POINTER(Operand)
 
 # name -> (restype, argtypes); mirrors include/exorl_b200.h one to one
+class SymHits(_c.Structure):
+    """exb_sym_hits: the transposed hits a symmetric screen call left in its workspace."""
+    _fields_ = [("target", _c.c_void_p), ("val", _c.c_void_p), ("src", _c.c_void_p),
+                ("count", _c.c_void_p), ("capacity", _c.c_longlong)]
+
+
 SIGNATURES = {
     "exb_abi_version": (_c.c_int, []),
     "exb_last_error": (_c.c_char_p, []),
@@ -99,6 +105,13 @@ SIGNATURES = {
     "exb_knn_sym_workspace_bytes": (_sz, [_i64, _c.c_int, _c.c_int, _c.c_int, _c.c_int]),
     "exb_knn_sym_f32": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _i32, _vp, _i64, _c.c_int,
                                    _c.c_int, _vp, _vp, _vp, _sz, _vp]),
+    "exb_knn_sym_screen_f32": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _vp, _i64, _c.c_int,
+                                          _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int,
+                                          _c.c_int, _vp, _sz, _c.POINTER(SymHits), _vp]),
+    "exb_knn_sym_scatter": (_c.c_int, [_i64, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _vp, _vp,
+                                       _vp, _i64, _vp, _vp]),
+    "exb_knn_sym_rerank_f32": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _i32, _c.c_int, _c.c_int,
+                                          _i64, _i64, _vp, _vp, _vp, _vp]),
     "exb_knn_colstats_workspace_bytes": (_sz, [_i64, _c.c_int]),
     "exb_knn_colstats_f32": (_c.c_int, [_vp, _i64, _c.c_int, _vp, _vp, _sz, _vp]),
     "exb_knn_affine_from_stats": (_c.c_int, [_vp, _c.c_double, _c.c_int, _vp, _vp]),

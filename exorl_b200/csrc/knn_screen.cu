@@ -394,6 +394,12 @@ struct ScreenParams {
   // own upwards; an accumulator element g_ij is tested in both directions against the rows' fixed
   // thresholds and logged per (row, column half): direct hits (bank row j for query i) and
   // transposed hits (bank row i for query j).  log_cap slots per log; count -1 = overflowed.
+  // Query tile pairs [sym_pair_lo, sym_pair_lo + gridDim.x / CG) of this launch; pair u scans the
+  // bank tiles u, u + 1, ... (cyclic, modulo n_tiles), (sym_span_end - u) of them, plus
+  // sym_extra more for the pairs u >= sym_mid_pair.  One GPU: pair_lo 0, span_end n_tiles, no
+  // extra.  Several GPUs (relabel.py): rank r owns a block of pairs and the block pairs
+  // (r, r), (r, r + 1), ..., cyclically half way round, the antipodal block split in halves.
+  int sym_pair_lo, sym_span_end, sym_mid_pair, sym_extra;
   const float* sym_tkeep; // [n] stateless keep thresholds
   float* dlog_val;        // [n, 2, log_cap] direct hits: score g - hb_j
   int* dlog_idx;          //                  bank row j
@@ -914,9 +920,10 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
     }
   }
   if constexpr (SYM) {
-    // own bank tile (SCR_N = CG * SCR_M rows: the pair's query rows ARE that tile) and upwards
+    // own bank tile (SCR_N = CG * SCR_M rows: the pair's query rows ARE that tile) and onwards
+    m_tile += p.sym_pair_lo * CG;
     t_begin = m_tile / CG;
-    t_end = p.n_tiles;
+    t_end = p.sym_span_end + (t_begin >= p.sym_mid_pair ? p.sym_extra : 0);   // may pass n_tiles
   }
   const int n_local = max(t_end - t_begin, 0);
 
@@ -956,7 +963,9 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
   auto tile_of = [&](int j) {   // j-th tile of this CTA's scan
     int tt = start + j;
     if (tt >= n_local) tt -= n_local;
-    return t_begin + tt;
+    tt += t_begin;
+    if constexpr (SYM) { if (tt >= p.n_tiles) tt -= p.n_tiles; }   // cyclic over the bank
+    return tt;
   };
   // FILT 3: the first n_seed tiles are scored twice (seed phase, then again in the main phase)
   const int n_seed = (FILT >= 2 && !SYM) ? min(p.seed_tiles, n_local) : 0;
@@ -1099,7 +1108,7 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
     for (int jj = 0; jj < n_total; ++jj) {
       const int t = tile_seq(jj);
       const int as = jj & 1;
-      const bool diag = t == t_begin;            // own tile: the direct test covers both orders
+      const bool diag = jj == 0;                 // own tile: the direct test covers both orders
       __syncwarp();
       reinterpret_cast<float4*>(hn)[lane] = hnext;
       reinterpret_cast<float4*>(tk)[lane] = tnext;
@@ -2354,23 +2363,31 @@ extern "C" size_t exb_knn_sym_workspace_bytes(int64_t n, int dim, int k, int log
   return carve_sym(nullptr, n, pl, k, log_cap, recv_cap, &w);
 }
 
-extern "C" int exb_knn_sym_f32(const float* rep, int64_t n, int dim, int k, int32_t idx_base,
-                               const float* d_sample, int64_t d_stride, int log_cap, int recv_cap,
-                               float* out_dist, int32_t* out_idx, void* workspace,
-                               size_t workspace_bytes, exb_stream_t stream) {
-  EXB_CHECK_ARG(rep && d_sample && out_dist && out_idx && workspace, "null pointer");
+struct SymSpan {            // which tile pairs a launch takes (ScreenParams::sym_*)
+  int pair_lo, pair_hi, span_end, mid_pair, extra;
+};
+
+// Phase 1: operand, thresholds, symmetric screen of the pairs of `sp_`; leaves the direct logs
+// and the append buffer of transposed hits in the workspace.
+static int sym_screen_phase(const float* rep, int64_t n, int dim, int k, const float* d_sample,
+                            int64_t d_stride, int log_cap, int recv_cap, const SymSpan& span,
+                            void* workspace, size_t workspace_bytes, cudaStream_t st,
+                            SymPlan* pl_out, SymWs* w_out) {
   SymPlan pl;
   if (!sym_plan(n, dim, k, &pl) || log_cap < 32 || recv_cap < 32) {
     set_error("symmetric screen needs n >= %d, dim <= %d, k <= %d (got n=%lld dim=%d k=%d)",
               4 * SCR_N, EXB_SCREEN_MAX_DIM, SCR_MAX_K, (long long)n, dim, k);
     return EXB_EUNSUPPORTED;
   }
+  EXB_CHECK_ARG(span.pair_lo >= 0 && span.pair_lo < span.pair_hi && span.pair_hi <= pl.n_tiles &&
+                span.span_end >= span.pair_hi && span.extra >= 0 &&
+                span.span_end - span.pair_lo + span.extra <= pl.n_tiles,
+                "bad tile span");
   SymWs w;
   const size_t need = carve_sym(nullptr, n, pl, k, log_cap, recv_cap, &w);
   EXB_CHECK_ARG(workspace_bytes >= need, "workspace too small: %zu < %zu", workspace_bytes, need);
   EXB_CHECK_ARG(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
   carve_sym(workspace, n, pl, k, log_cap, recv_cap, &w);
-  cudaStream_t st = (cudaStream_t)stream;
   EXB_CUDA(cudaMemsetAsync(workspace, 0, 1024 + 64, st));
   EXB_CUDA(cudaMemsetAsync(w.rcnt, 0, (size_t)n * sizeof(int), st));
   EXB_CUDA(cudaMemsetAsync(w.tq_count, 0, 16, st));
@@ -2401,6 +2418,8 @@ extern "C" int exb_knn_sym_f32(const float* rep, int64_t n, int dim, int k, int3
   sp.nq = n; sp.nb = n; sp.nkc = pl.nkc; sp.n_tiles = pl.n_tiles;
   sp.tiles_per_split = pl.n_tiles; sp.splits = 1; sp.k = k; sp.stages = pl.stages;
   sp.lists = 2; sp.head = nullptr;
+  sp.sym_pair_lo = span.pair_lo; sp.sym_span_end = span.span_end;
+  sp.sym_mid_pair = span.mid_pair; sp.sym_extra = span.extra;
   sp.sym_tkeep = w.tkeep; sp.dlog_val = w.dlog_val; sp.dlog_idx = w.dlog_idx;
   sp.dlog_cnt = w.dlog_cnt; sp.log_cap = log_cap;
   sp.tq_target = w.tq_target; sp.tq_val = w.tq_val; sp.tq_src = w.tq_src;
@@ -2409,7 +2428,7 @@ extern "C" int exb_knn_sym_f32(const float* rep, int64_t n, int dim, int k, int3
     const bool prof = g_prof.on && g_prof.n < 64;
     if (prof) EXB_CUDA(cudaEventRecord(g_prof.e0[g_prof.n], st));
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)pl.m_tiles, 1);
+    cfg.gridDim = dim3((unsigned)(2 * (span.pair_hi - span.pair_lo)), 1);
     cfg.blockDim = dim3(SCR_THREADS_V3);
     cfg.dynamicSmemBytes = pl.smem;
     cfg.stream = st;
@@ -2423,12 +2442,67 @@ extern "C" int exb_knn_sym_f32(const float* rep, int64_t n, int dim, int k, int3
     EXB_CUDA(cudaLaunchKernelEx(&cfg, knn_screen_kernel<2, 4>, tq, tb, sp));
     if (prof) EXB_CUDA(cudaEventRecord(g_prof.e1[g_prof.n++], st));
   }
+  *pl_out = pl;
+  *w_out = w;
+  return EXB_OK;
+}
+
+static SymLists sym_lists(const SymWs& w, int log_cap, int recv_cap) {
   SymLists sl;
   sl.dlog_val = w.dlog_val; sl.dlog_idx = w.dlog_idx; sl.dlog_cnt = w.dlog_cnt;
   sl.log_cap = log_cap; sl.tq_target = w.tq_target; sl.tq_val = w.tq_val; sl.tq_src = w.tq_src;
   sl.tq_count = w.tq_count; sl.tq_cap = w.tq_cap;
   sl.rval = w.rval; sl.ridx = w.ridx; sl.rcnt = w.rcnt; sl.rcap = recv_cap;
-  sym_scatter_kernel<<<148 * 8, 256, 0, st>>>(sl, w.status);
+  return sl;
+}
+
+// Phase 3: rerank rows [row_lo, row_hi) from their direct logs + received lists.
+static int sym_rerank_phase(const float* rep, int64_t n, int dim, int k, int32_t idx_base,
+                            int64_t row_lo, int64_t row_hi, float* out_dist, int32_t* out_idx,
+                            const SymPlan& pl, const SymWs& w, const SymLists& sl,
+                            cudaStream_t st) {
+  const bool vec = (dim % 4 == 0) && (((uintptr_t)rep) & 15) == 0;
+  const int ni = vec ? (dim + 127) / 128 : 0;
+  RerankParams rp;
+  memset(&rp, 0, sizeof(rp));
+  rp.Q = rep; rp.B = rep; rp.nq = row_hi; rp.nb = n; rp.dim = dim; rp.k = k;
+  rp.idx_base = idx_base;
+  rp.splits = 2; rp.ha = w.hb; rp.ea = w.eb; rp.qsc = w.bsc; rp.bsc = w.bsc;
+  // outputs are [row_hi - row_lo, k] arrays of the caller: address them by global row
+  rp.out_dist = out_dist - row_lo * k; rp.out_idx = out_idx - row_lo * k;
+  rp.fallback_rows = w.fb_rows;
+  rp.fallback_cap = pl.fb_cap; rp.status = w.status;
+  const int64_t rows = row_hi - row_lo;
+  const unsigned rr_grid = (unsigned)((rows + RR_WARPS - 1) / RR_WARPS);
+  switch (ni) {
+    case 1: knn_rerank_sym_kernel<1><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp, sl, row_lo); break;
+    case 2: knn_rerank_sym_kernel<2><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp, sl, row_lo); break;
+    case 3: knn_rerank_sym_kernel<3><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp, sl, row_lo); break;
+    case 4: knn_rerank_sym_kernel<4><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp, sl, row_lo); break;
+    default: knn_rerank_sym_kernel<0><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp, sl, row_lo); break;
+  }
+  EXB_LAUNCH_CHECK();
+  // undecided rows (global row ids in the list) -> exact kernel, written through the same
+  // row-offset output views
+  return launch_exact(rep, row_hi, rep, n, dim, k, idx_base, rp.out_dist, rp.out_idx, w.fb_d2,
+                      w.fb_idx, pl.fb_splits, w.fb_rows, &w.status->n_fallback, pl.fb_cap, st);
+}
+
+extern "C" int exb_knn_sym_f32(const float* rep, int64_t n, int dim, int k, int32_t idx_base,
+                               const float* d_sample, int64_t d_stride, int log_cap, int recv_cap,
+                               float* out_dist, int32_t* out_idx, void* workspace,
+                               size_t workspace_bytes, exb_stream_t stream) {
+  EXB_CHECK_ARG(rep && d_sample && out_dist && out_idx && workspace, "null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  SymPlan pl;
+  SymWs w;
+  const int tiles = (int)((n + SCR_N - 1) / SCR_N);
+  const SymSpan span = {0, tiles, tiles, tiles, 0};
+  int rc = sym_screen_phase(rep, n, dim, k, d_sample, d_stride, log_cap, recv_cap, span,
+                            workspace, workspace_bytes, st, &pl, &w);
+  if (rc) return rc;
+  const SymLists sl = sym_lists(w, log_cap, recv_cap);
+  sym_scatter_kernel<<<148 * 8, 256, 0, st>>>(sl, sl.tq_target, sl.tq_val, sl.tq_src, -1, w.status);
   EXB_LAUNCH_CHECK();
   static const int sym_stats = knob("EXB_SYM_STATS", 0);
   if (sym_stats) {   // counts into the 16 trace words (exb_debug_trace_sync), zeroed by the memset
@@ -2436,26 +2510,59 @@ extern "C" int exb_knn_sym_f32(const float* rep, int64_t n, int dim, int k, int3
         sl, n, reinterpret_cast<long long*>(static_cast<char*>(workspace) + 768));
     EXB_LAUNCH_CHECK();
   }
+  return sym_rerank_phase(rep, n, dim, k, idx_base, 0, n, out_dist, out_idx, pl, w, sl, st);
+}
 
-  const bool vec = (dim % 4 == 0) && (((uintptr_t)rep) & 15) == 0;
-  const int ni = vec ? (dim + 127) / 128 : 0;
-  RerankParams rp;
-  memset(&rp, 0, sizeof(rp));
-  rp.Q = rep; rp.B = rep; rp.nq = n; rp.nb = n; rp.dim = dim; rp.k = k; rp.idx_base = idx_base;
-  rp.splits = 2; rp.ha = w.hb; rp.ea = w.eb; rp.qsc = w.bsc; rp.bsc = w.bsc;
-  rp.out_dist = out_dist; rp.out_idx = out_idx; rp.fallback_rows = w.fb_rows;
-  rp.fallback_cap = pl.fb_cap; rp.status = w.status;
-  const unsigned rr_grid = (unsigned)((n + RR_WARPS - 1) / RR_WARPS);
-  switch (ni) {
-    case 1: knn_rerank_sym_kernel<1><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp, sl); break;
-    case 2: knn_rerank_sym_kernel<2><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp, sl); break;
-    case 3: knn_rerank_sym_kernel<3><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp, sl); break;
-    case 4: knn_rerank_sym_kernel<4><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp, sl); break;
-    default: knn_rerank_sym_kernel<0><<<rr_grid, RR_WARPS * 32, 0, st>>>(rp, sl); break;
-  }
+// ---- the same in three calls, for ranks that each own a block of the tile pairs (relabel.py):
+// screen -> [exchange of the transposed hits between the ranks] -> scatter -> rerank.
+extern "C" int exb_knn_sym_screen_f32(const float* rep, int64_t n, int dim, int k,
+                                      const float* d_sample, int64_t d_stride, int log_cap,
+                                      int recv_cap, int pair_lo, int pair_hi, int span_end,
+                                      int mid_pair, int extra_tiles, void* workspace,
+                                      size_t workspace_bytes, exb_sym_hits* hits,
+                                      exb_stream_t stream) {
+  EXB_CHECK_ARG(rep && d_sample && workspace && hits, "null pointer");
+  SymPlan pl;
+  SymWs w;
+  const SymSpan span = {pair_lo, pair_hi, span_end, mid_pair, extra_tiles};
+  const int rc = sym_screen_phase(rep, n, dim, k, d_sample, d_stride, log_cap, recv_cap, span,
+                                  workspace, workspace_bytes, (cudaStream_t)stream, &pl, &w);
+  if (rc) return rc;
+  hits->target = w.tq_target; hits->val = w.tq_val; hits->src = w.tq_src;
+  hits->count = w.tq_count; hits->capacity = w.tq_cap;
+  return EXB_OK;
+}
+
+extern "C" int exb_knn_sym_scatter(int64_t n, int dim, int k, int log_cap, int recv_cap,
+                                   const int32_t* target, const float* val, const int32_t* src,
+                                   int64_t n_hits, void* workspace, exb_stream_t stream) {
+  EXB_CHECK_ARG(workspace && n_hits >= 0 && (n_hits == 0 || (target && val && src)),
+                "bad arguments");
+  SymPlan pl;
+  SymWs w;
+  EXB_CHECK_ARG(sym_plan(n, dim, k, &pl), "bad sizes");
+  carve_sym(workspace, n, pl, k, log_cap, recv_cap, &w);
+  if (n_hits == 0) return EXB_OK;
+  const SymLists sl = sym_lists(w, log_cap, recv_cap);
+  sym_scatter_kernel<<<148 * 8, 256, 0, (cudaStream_t)stream>>>(sl, target, val, src, n_hits,
+                                                                 w.status);
   EXB_LAUNCH_CHECK();
-  return launch_exact(rep, n, rep, n, dim, k, idx_base, out_dist, out_idx, w.fb_d2, w.fb_idx,
-                      pl.fb_splits, w.fb_rows, &w.status->n_fallback, pl.fb_cap, st);
+  return EXB_OK;
+}
+
+extern "C" int exb_knn_sym_rerank_f32(const float* rep, int64_t n, int dim, int k,
+                                      int32_t idx_base, int log_cap, int recv_cap, int64_t row_lo,
+                                      int64_t row_hi, float* out_dist, int32_t* out_idx,
+                                      void* workspace, exb_stream_t stream) {
+  EXB_CHECK_ARG(rep && out_dist && out_idx && workspace && row_lo >= 0 && row_lo < row_hi &&
+                row_hi <= n, "bad arguments");
+  SymPlan pl;
+  SymWs w;
+  EXB_CHECK_ARG(sym_plan(n, dim, k, &pl), "bad sizes");
+  carve_sym(workspace, n, pl, k, log_cap, recv_cap, &w);
+  const SymLists sl = sym_lists(w, log_cap, recv_cap);
+  return sym_rerank_phase(rep, n, dim, k, idx_base, row_lo, row_hi, out_dist, out_idx, pl, w, sl,
+                          (cudaStream_t)stream);
 }
 
 extern "C" int exb_knn_screened_f32(const float* src, int64_t nq, const float* bank, int64_t nb,

@@ -73,20 +73,26 @@ struct SymLists {
   int rcap;
 };
 
-// One thread per appended transposed hit: entry -> slot atomicAdd(rcnt[target]) of its row.
+// One thread per transposed hit: entry -> slot atomicAdd(rcnt[target]) of its row.  n_hits < 0:
+// the entries are the workspace's own append buffer (count on the device); else `n_hits` entries
+// of the given arrays (hits received from other ranks).
 __global__ void __launch_bounds__(256)
-sym_scatter_kernel(const SymLists l, RerankStatus* status) {
-  const unsigned long long total = *l.tq_count;
-  if (blockIdx.x == 0 && threadIdx.x == 0 && total > (unsigned long long)l.tq_cap)
-    atomicOr(&status->invalid, SYM_INVALID);    // hits were dropped: nobody can be certified
-  const long long n_ent = (long long)min(total, (unsigned long long)l.tq_cap);
+sym_scatter_kernel(const SymLists l, const int* __restrict__ target, const float* __restrict__ val,
+                   const int* __restrict__ src, long long n_hits, RerankStatus* status) {
+  long long n_ent = n_hits;
+  if (n_hits < 0) {
+    const unsigned long long total = *l.tq_count;
+    if (blockIdx.x == 0 && threadIdx.x == 0 && total > (unsigned long long)l.tq_cap)
+      atomicOr(&status->invalid, SYM_INVALID);    // hits were dropped: nobody can be certified
+    n_ent = (long long)min(total, (unsigned long long)l.tq_cap);
+  }
   for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n_ent;
        e += (long long)gridDim.x * blockDim.x) {
-    const int target = l.tq_target[e];
-    const int pos = atomicAdd(l.rcnt + target, 1);
+    const int t = target[e];
+    const int pos = atomicAdd(l.rcnt + t, 1);
     if (pos < l.rcap) {
-      l.rval[(int64_t)target * l.rcap + pos] = l.tq_val[e];
-      l.ridx[(int64_t)target * l.rcap + pos] = l.tq_src[e];
+      l.rval[(int64_t)t * l.rcap + pos] = val[e];
+      l.ridx[(int64_t)t * l.rcap + pos] = src[e];
     }
   }
 }
@@ -126,11 +132,11 @@ struct WarpTopScores {
 // One warp per row.  Same outputs / fallback protocol as knn_rerank_kernel<false, NI>.
 template <int NI>
 __global__ void __launch_bounds__(RR_WARPS * 32)
-knn_rerank_sym_kernel(const RerankParams p, const SymLists l) {
+knn_rerank_sym_kernel(const RerankParams p, const SymLists l, const int64_t row_lo) {
   __shared__ int s_surv[RR_WARPS][RR_SURV];
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  const int64_t row = (int64_t)blockIdx.x * RR_WARPS + wib;
+  const int64_t row = row_lo + (int64_t)blockIdx.x * RR_WARPS + wib;   // rows [row_lo, p.nq)
   if (row >= p.nq) return;
   const int k = p.k, dim = p.dim;
   float q[16];

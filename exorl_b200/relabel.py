@@ -25,6 +25,8 @@ reference formula cannot be evaluated (it materialises an (N, N, c) tensor); SUR
 The three compute stages are injectable so the partition/exchange logic can be exercised with
 the gloo backend on CPU (tests/test_relabel_gloo.py); the defaults are the CUDA kernels.
 """
+import ctypes
+
 import torch
 import torch.distributed as dist
 
@@ -336,6 +338,126 @@ def _finish_block(d_mine, i_mine, n, lo, hi, in_split, world, k, avg, use_rms, c
     return reward
 
 
+# ------------------------------------------------------------------------------------------
+# Symmetric screen over several GPUs (csrc/knn_sym.cuh, include/exorl_b200.h "three calls")
+# ------------------------------------------------------------------------------------------
+def sym_tile_blocks(n, world, tile=256):
+    """Tile-aligned row blocks: rank r owns the query tile pairs [tb[r], tb[r + 1]) (tiles of
+    `tile` rows) = the rows [min(n, tile * tb[r]), min(n, tile * tb[r + 1]))."""
+    tiles = (n + tile - 1) // tile
+    tb = [(r * tiles) // world for r in range(world + 1)]
+    return tiles, tb, [min(n, tile * t) for t in tb]
+
+
+def sym_span(tb, world, rank):
+    """(pair_lo, pair_hi, span_end, mid_pair, extra_tiles) of `rank`: its pairs scan their own
+    block from the diagonal on, then the next blocks cyclically — (world - 1) // 2 whole blocks
+    and, for an even world, half of the antipodal block pair: ranks below world / 2 take the
+    first half of the antipodal block's tiles with ALL their pairs, the others take the WHOLE
+    antipodal block with the second half of their pairs only.  Every unordered tile pair is
+    multiplied exactly once (tests/test_relabel_gloo.py checks the coverage)."""
+    size = [tb[r + 1] - tb[r] for r in range(world)]
+    lo, hi = tb[rank], tb[rank + 1]
+    whole = (world - 1) // 2
+    span_end = hi + sum(size[(rank + s) % world] for s in range(1, whole + 1))
+    mid, extra = hi, 0
+    if world % 2 == 0 and world > 1:
+        anti = (rank + world // 2) % world
+        if rank < world // 2:
+            span_end += size[anti] // 2                    # first half of its tiles, every pair
+        else:
+            half_anti_of_me = size[rank] // 2              # what rank `anti` takes of MY tiles
+            mid = lo + half_anti_of_me                     # ... so my pairs from there on take
+            extra = size[anti]                             # the whole antipodal block
+    return lo, hi, span_end, mid, extra
+
+
+def _sym_queries_knn(rep, k, world, rank, group, tm):
+    """kNN of this rank's (tile-aligned) query block through the symmetric screen spread over
+    the ranks.  Returns (dist, idx, row_bounds) or None when any rank reports the pass invalid
+    (the caller then runs the full screen).  Collectives: d_sample all-reduce (4N bytes), hit
+    counts all-to-all, the hits themselves all-to-all (12 bytes each, ~ k N^2 / (2 S world))."""
+    from . import knn as xknn
+    lib = _lib.load()
+    n, dim = rep.shape
+    dev = rep.device
+    tiles, tb, rb = sym_tile_blocks(n, world)
+    lo, hi = rb[rank], rb[rank + 1]
+    stride = max(1, n // xknn._sym_sample_rows(n))
+    sample = rep[::stride].contiguous()
+    d_loc, _ = xknn._knn_topk_impl(rep[lo:hi], sample, k, 0, "screened", False, allow_sym=False)
+    d_all = torch.zeros(n, dtype=torch.float32, device=dev)
+    d_all[lo:hi] = d_loc[:, k - 1]
+    dist.all_reduce(d_all, op=dist.ReduceOp.SUM, group=group)
+    tm("sym_sample_prepass")
+    expected = 1.3 * k * n / sample.size(0)
+    log_cap = int(-(-(3 * expected / 2 + 96) // 8) * 8)
+    recv_cap = int(-(-(3 * expected + 96) // 8) * 8)
+    pair_lo, pair_hi, span_end, mid, extra = sym_span(tb, world, rank)
+    with torch.cuda.device(dev):
+        need = lib.exb_knn_sym_workspace_bytes(n, dim, k, log_cap, recv_cap)
+        if need == 0:
+            return None
+        ws, _ = _lib.Workspace.get(dev, "knn_sym", need)
+        hits = _lib.SymHits()
+        _lib.check(lib.exb_knn_sym_screen_f32(
+            _lib.ptr(rep), n, dim, k, _lib.ptr(d_all), 1, log_cap, recv_cap, pair_lo, pair_hi,
+            span_end, mid, extra, _lib.ptr(ws), ws.numel(), ctypes.byref(hits),
+            _lib.stream_ptr(dev)))
+        base = ws.data_ptr()
+
+        def view(ptr, count, dtype):
+            off = ptr - base
+            return ws[off:off + 4 * count].view(dtype)
+        cnt = ws[hits.count - base:hits.count - base + 8].view(torch.int64)
+        n_hits = int(cnt.item())                                   # sync: the screen is done
+        tm("sym_screen")
+        bad = torch.tensor([1 if n_hits > hits.capacity else 0], device=dev)
+        n_hits = min(n_hits, hits.capacity)
+        tgt = view(hits.target, n_hits, torch.int32)
+        val = view(hits.val, n_hits, torch.float32)
+        src = view(hits.src, n_hits, torch.int32)
+        # route every hit to the rank that owns its query row
+        edges = torch.tensor(rb[1:-1], dtype=torch.int32, device=dev)
+        # (a counting partition: one mask + compaction per destination is cheaper than a sort of
+        # 10^7..10^8 keys)
+        dest = torch.bucketize(tgt, edges, right=True)
+        packed = torch.stack([tgt, val.view(torch.int32), src], dim=1)
+        parts = [packed[(dest == r).nonzero().flatten()] for r in range(world)]
+        sc = [p.size(0) for p in parts]
+        counts = torch.tensor(sc, dtype=torch.int64, device=dev)
+        recv_counts = torch.empty_like(counts)
+        dist.all_to_all_single(recv_counts, counts, group=group)
+        rc_ = recv_counts.tolist()
+        recv = torch.empty((sum(rc_), 3), dtype=torch.int32, device=dev)
+        dist.all_to_all_single(recv, torch.cat(parts, dim=0), rc_, sc, group=group)
+        tm("sym_hit_exchange")
+        r_t = recv[:, 0].contiguous()
+        r_v = recv[:, 1].contiguous().view(torch.float32)
+        r_s = recv[:, 2].contiguous()
+        _lib.check(lib.exb_knn_sym_scatter(n, dim, k, log_cap, recv_cap, _lib.ptr(r_t),
+                                           _lib.ptr(r_v), _lib.ptr(r_s), recv.size(0),
+                                           _lib.ptr(ws), _lib.stream_ptr(dev)))
+        d_mine = torch.empty(hi - lo, k, dtype=torch.float32, device=dev)
+        i_mine = torch.empty(hi - lo, k, dtype=torch.int32, device=dev)
+        _lib.check(lib.exb_knn_sym_rerank_f32(_lib.ptr(rep), n, dim, k, 0, log_cap, recv_cap, lo,
+                                              hi, _lib.ptr(d_mine), _lib.ptr(i_mine),
+                                              _lib.ptr(ws), _lib.stream_ptr(dev)))
+    st = xknn.screened_status(dev, key="knn_sym")
+    bad[0] |= 1 if (st[1] & 2) else 0
+    dist.all_reduce(bad, op=dist.ReduceOp.MAX, group=group)
+    xknn.sym_last.update(n=n, sample_rows=sample.size(0), log_cap=log_cap, recv_cap=recv_cap,
+                         undecided=st[0], status=st[1], world=world, hits_sent=n_hits)
+    if int(bad.item()):
+        xknn.sym_last["fell_back_to_full_screen"] = True
+        return None
+    if st[1] & 1:
+        rows = (i_mine[:, 0] < 0).nonzero().flatten()
+        xknn._recompute_rows(rep[lo:hi], rep, k, 0, d_mine, i_mine, rows)
+    tm("sym_rerank")
+    return d_mine, i_mine, rb
+
+
 def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="auto",
                        return_knn=False, stages=_CudaStages, timer=None, balance=False):
     """APT reward (N, 1) of every row of `rep` against all N rows, identical on every rank.
@@ -389,6 +511,20 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="a
     elif exchange == "auto":
         exchange = "all_to_all"
 
+    if (world > 1 and exchange == "queries" and stages is _CudaStages and mode != "exact"
+            and not balance and not isinstance(rep, PreparedRep)):
+        from . import knn as xknn
+        if (xknn.SYM_ENABLED and n >= xknn.SYM_MIN_ROWS and xknn.OVERFLOW_POLICY == "sync"
+                and rep.size(1) <= _lib.SCREEN_MAX_DIM and k <= _lib.SCREEN_MAX_K):
+            # a set against itself: every unordered tile pair on exactly one rank (K1s)
+            out = _sym_queries_knn(_as_rows_f32(rep), k, world, rank, group, tm)
+            if out is not None:
+                d_mine, i_mine, rb = out
+                lo, hi = rb[rank], rb[rank + 1]
+                last_query_block.update(lo=lo, hi=hi)
+                in_split = [rb[r + 1] - rb[r] for r in range(world)]
+                return _finish_block(d_mine, i_mine, n, lo, hi, in_split, world, k, avg, use_rms,
+                                     clip, rms, group, stages, tm, return_knn)
     if world > 1 and exchange == "queries":
         bal = query_balance(group, n, world, k) if balance else None
         if bal is not None:
@@ -471,6 +607,13 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="a
 _side_streams = {}
 
 
+def _as_rows_f32(rep):
+    rep = rep.detach()
+    if rep.dtype != torch.float32:
+        rep = rep.float()
+    return rep.reshape(rep.size(0), -1).contiguous()
+
+
 def _side_stream(dev):
     key = dev.index if dev.index is not None else torch.cuda.current_device()
     if key not in _side_streams:
@@ -504,7 +647,11 @@ def relabel_apt_reward_from_host(rep_host, args, rms=None, group=None, rep_out=N
     if rep_out is None:
         rep_out = torch.empty((n, dim), dtype=torch.float32, device=dev)
     lists = screen_lists_count(max(n // world, 1), n, dim, k)
-    if world == 1 or n % world != 0 or lists == 0 or lists > 16:
+    from . import knn as xknn
+    sym = (xknn.SYM_ENABLED and n >= xknn.SYM_MIN_ROWS and xknn.OVERFLOW_POLICY == "sync"
+           and dim <= _lib.SCREEN_MAX_DIM and k <= _lib.SCREEN_MAX_K and not balance)
+    if world == 1 or sym or n % world != 0 or lists == 0 or lists > 16:
+        # symmetric screen (half the tensor-core work) beats the overlap of the pipeline below
         # one GPU: nothing to pipeline against — copy, then the device path (which takes the
         # symmetric screen for a set against itself)
         rep = reps_from_host(rep_host, out=rep_out, group=group)

@@ -122,6 +122,36 @@ int exb_knn_sym_f32(const float* rep, int64_t n, int dim, int k, int32_t idx_bas
                     float* out_dist /* [n,k] */, int32_t* out_idx /* [n,k] */, void* workspace,
                     size_t workspace_bytes, exb_stream_t stream);
 
+/* The same in three calls, for ranks that each own a block of the tile pairs (the multi-GPU
+ * relabel, exorl_b200/relabel.py): every rank holds the whole set and passes the same d_sample;
+ * rank r screens the query tile pairs [pair_lo, pair_hi) (tiles of 256 rows), pair u against the
+ * bank tiles u, u+1, ... cyclically, (span_end - u) of them plus extra_tiles for u >= mid_pair
+ * — so that every unordered tile pair is multiplied on exactly one rank.  The call leaves the
+ * direct logs of its rows and the transposed hits (query row, score, bank row) it found for ANY
+ * row in `hits` (device arrays inside the workspace; *count entries, read it after a sync).  The
+ * ranks exchange the hits by owner of the query row, hand what they received (and their own) to
+ * exb_knn_sym_scatter, and finish their rows with exb_knn_sym_rerank_f32 (outputs
+ * [row_hi - row_lo, k]).  Status word as for exb_knn_sym_f32; the caller must also treat
+ * *count > capacity as "invalid". */
+typedef struct {
+  int32_t* target;             /* query row the hit belongs to (global row id) */
+  float* val;                  /* screened score */
+  int32_t* src;                /* bank row (global row id) */
+  unsigned long long* count;   /* device: entries appended (may exceed capacity: excess dropped) */
+  long long capacity;
+} exb_sym_hits;
+int exb_knn_sym_screen_f32(const float* rep, int64_t n, int dim, int k, const float* d_sample,
+                           int64_t d_stride, int log_cap, int recv_cap, int pair_lo, int pair_hi,
+                           int span_end, int mid_pair, int extra_tiles, void* workspace,
+                           size_t workspace_bytes, exb_sym_hits* hits, exb_stream_t stream);
+int exb_knn_sym_scatter(int64_t n, int dim, int k, int log_cap, int recv_cap,
+                        const int32_t* target, const float* val, const int32_t* src,
+                        int64_t n_hits, void* workspace, exb_stream_t stream);
+int exb_knn_sym_rerank_f32(const float* rep, int64_t n, int dim, int k, int32_t idx_base,
+                           int log_cap, int recv_cap, int64_t row_lo, int64_t row_hi,
+                           float* out_dist, int32_t* out_idx, void* workspace,
+                           exb_stream_t stream);
+
 size_t exb_knn_screened_workspace_bytes(int64_t nq, int64_t nb, int dim, int k);
 /* src_is_bank != 0 tells the call that src and bank are the same tensor (PBE: source = target,
  * utils/utils.py:290) so the fp16 operand is prepared once. */

@@ -75,3 +75,32 @@ def test_rms_general_shape_cpu_formula():
     m, s = r(x)
     assert m.shape == (3,) and r.n == pytest.approx(4.0001)
     assert torch.allclose(m, x.mean(0) * 4 / 4.0001, rtol=1e-6)
+
+
+def test_symmetric_multi_gpu_spans_cover_every_tile_pair_exactly_once():
+    """relabel.sym_span: over all ranks, every unordered pair of bank tiles {I, J} (I != J) is
+    scanned exactly once (by a pair-CTA of tile I scanning tile J or the other way round) and
+    every diagonal tile exactly once; the per-rank work is balanced."""
+    from exorl_b200.relabel import sym_tile_blocks, sym_span
+    for n, world in ((1_000_000, 8), (1_000_000, 2), (1_000_000, 4), (300_000, 3), (70_000, 5),
+                     (9_000, 7), (4_096, 2), (262_144, 6), (5_000, 1)):
+        tiles, tb, rb = sym_tile_blocks(n, world)
+        assert rb[0] == 0 and rb[-1] == n and tb[-1] == tiles
+        seen = {}
+        work = []
+        for r in range(world):
+            lo, hi, span_end, mid, extra = sym_span(tb, world, r)
+            assert (lo, hi) == (tb[r], tb[r + 1])
+            w = 0
+            for u in range(lo, hi):
+                length = span_end - u + (extra if u >= mid else 0)
+                assert 1 <= length <= tiles
+                for j in range(length):
+                    t = (u + j) % tiles
+                    key = (min(u, t), max(u, t))
+                    seen[key] = seen.get(key, 0) + 1
+                w += length
+            work.append(w)
+        assert len(seen) == tiles * (tiles + 1) // 2, (n, world)
+        assert set(seen.values()) == {1}, (n, world)
+        assert max(work) <= 1.05 * (sum(work) / world) + 2 * tiles / world + 8, (n, world, work)
