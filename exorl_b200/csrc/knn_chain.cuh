@@ -152,7 +152,14 @@ apt_chain_kernel(const __grid_constant__ CUtensorMap tmap_q,
     if (active)
       rerank_row<true, NI, false>(p, row, lane, s_surv + warp * RR_SURV, s_val + warp * RR_SURV, q,
                                   top, need);
-    coop_scan<NI, CH_WARPS>(p, q, top, active ? need : 0u, lane, warp, s_tile, s_need);
+    {
+      float qq[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) qq[i] = q[i];
+      WarpTopK tt = top;
+      coop_scan<NI, CH_WARPS>(p, qq, tt, active ? need : 0u, lane, warp, s_tile, s_need);
+      top = tt;
+    }
     float dist = 0.f;
     if (active) dist = rerank_store(p, row, lane, top);
     if (!f.on) continue;

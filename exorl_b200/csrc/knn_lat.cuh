@@ -44,6 +44,10 @@ struct LatParams {
   long long* trace;  // optional phase timestamps (debug)
   unsigned long long* zero_status;   // caller-prepared operands: nobody ran prep (which zeroes the
                                      // 24-byte rerank status), so block (0,0) does it here
+  int* coop_flags;   // [m_tiles, splits, 4]: every epilogue warp writes (unconditionally, so that
+                     // nothing has to be zeroed) whether one of its rows lost a bank range — list
+                     // overflow, operand outside the fp16 range; the rerank blocks of the query
+                     // tile then scan cooperatively (knn_rerank.cuh:coop_scan), else they skip it
 };
 
 template <int KS>
@@ -283,6 +287,10 @@ __device__ __forceinline__ void lat_screen_body(const CUtensorMap& tmap_q, const
 
     if (n_local > 1) list_compact<LAT_LS>(st, lv, li);
     const bool overflow = st.dropped > -FLT_MAX && st.dropped >= st.tkeep;
+    if (p.coop_flags != nullptr) {
+      const bool lost = __any_sync(0xffffffffu, row_ok && (overflow || !(st.e2 < INFINITY)));
+      if (lane == 0) p.coop_flags[(m_tile * p.splits + split) * 4 + (warp - 2)] = lost ? 1 : 0;
+    }
     if (row_ok) {
       const int64_t o = row * p.splits + split;
       p.cand_cnt[o] = overflow ? -1 : st.n;

@@ -63,6 +63,7 @@ struct RerankParams {
   const PrepScalars* bsc;    // !LAT
   const float* bank_max;     // LAT: {EB, HBmax}
   int split_cols;            // LAT: bank columns per split (tiles_per_split * 64)
+  const int* coop_flags;     // LAT: [m_tiles, splits, 4] written by the latency screen (LatParams)
   float* out_dist;
   int* out_idx;
   int* fallback_rows;        // !LAT
@@ -679,10 +680,31 @@ knn_rerank_kernel(const RerankParams p) {
   bool done = false;
   if (active) done = rerank_row<LAT, NI, SH>(p, row, lane, s_surv[wib], s_val[wib], q, top, need);
   if constexpr (LAT) {
-    // rows that lost bank ranges: scanned by the block together (block-uniform call)
-    __shared__ __align__(16) float s_tile[2 * RR_COOP_ROWS * EXB_SCREEN_MAX_DIM];
-    __shared__ unsigned s_need[RR_WARPS];
-    coop_scan<NI>(p, q, top, active ? need : 0u, lane, wib, s_tile, s_need);
+    // rows that lost bank ranges: scanned by the block together.  Whether ANY row of this query
+    // tile did is known from the flags the latency screen wrote (the 4 rows of a block lie in
+    // one 128-row tile, so every warp reads the same words: block-uniform without a barrier) —
+    // the common case skips the scan and its barriers.
+    bool any_lost = true;
+    if (p.coop_flags != nullptr) {
+      const int m_tile = (int)(((int64_t)blockIdx.x * RR_WARPS) / SCR_M);
+      const int nflag = p.splits * 4;                         // <= 64
+      const int* fl = p.coop_flags + (int64_t)m_tile * nflag;
+      const int f0 = lane < nflag ? __ldcg(fl + lane) : 0;
+      const int f1 = lane + 32 < nflag ? __ldcg(fl + lane + 32) : 0;
+      any_lost = __any_sync(0xffffffffu, (f0 | f1) != 0);
+    }
+    if (any_lost) {
+      __shared__ __align__(16) float s_tile[2 * RR_COOP_ROWS * EXB_SCREEN_MAX_DIM];
+      __shared__ unsigned s_need[RR_WARPS];
+      // copies for the out-of-line call: q and top themselves stay in registers on the common
+      // path (a reference to them would put them in local memory for the whole kernel)
+      float qq[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) qq[i] = q[i];
+      WarpTopK tt = top;
+      coop_scan<NI>(p, qq, tt, active ? need : 0u, lane, wib, s_tile, s_need);
+      top = tt;
+    }
   }
   if (active && done) dist = rerank_store(p, row, lane, top);
   if constexpr (LAT) {

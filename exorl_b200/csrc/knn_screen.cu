@@ -1607,6 +1607,7 @@ struct ScreenWs {
   double2* pbe_partials;   // fused per-update epilogue: one per rerank block
   float* fb_d2;
   int* fb_idx;
+  int* coop_flags;    // per-update chain: [m_tiles, splits, 4] (LatParams::coop_flags)
   float* aff;         // streaming: affine record of the call (AFF_FLOATS)
   float* cs_stats;    // streaming: [3][dim] column statistics
   float* cs_part_b;   // streaming: [CS_MAX_BLOCKS][3][dim] partials of the bank / of the queries
@@ -1641,6 +1642,7 @@ static size_t carve_screen(void* ws, int64_t nq, int64_t nb, const ScreenPlan& p
   o->fb_rows = cv.take<int>(pl.fb_cap);
   o->fb_d2 = cv.take<float>((size_t)pl.fb_cap * pl.fb_splits * k);
   o->fb_idx = cv.take<int>((size_t)pl.fb_cap * pl.fb_splits * k);
+  o->coop_flags = cv.take<int>(pl.lat ? (size_t)pl.m_tiles * pl.splits * 4 : 0);
   const size_t part = pl.lat ? 0 : (size_t)CS_MAX_BLOCKS * 3 * pl.dpad;
   o->aff = cv.take<float>(pl.lat ? 0 : AFF_FLOATS);
   o->cs_stats = cv.take<float>(pl.lat ? 0 : 3 * (size_t)pl.dpad);
@@ -2020,6 +2022,7 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
   rp.status = w.status; rp.trace = trace_on ? w.trace : nullptr;
   rp.pbe.on = 0;
   rp.split_cols = pl.lat ? pl.tiles_per_split * LAT_N : 0;
+  rp.coop_flags = pl.lat ? w.coop_flags : nullptr;
   rp.lists_per_shard = rp.splits;
   rp.shard_rows = 0;
   for (int i = 0; i < 16; ++i) rp.shard_lo[i] = 0;
@@ -2074,8 +2077,9 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
       lp.splits = pl.splits; lp.k = k; lp.cand_val = w.cand_val; lp.cand_idx = w.cand_idx;
       lp.cand_cnt = w.cand_cnt; lp.cand_tk = w.cand_tk; lp.cand_tr = w.cand_tr;
       lp.rsel = (k + pl.splits - 1) / pl.splits; lp.bank_max = reinterpret_cast<float*>(w.bsc);
-      lp.trace = nullptr; lp.zero_status = nullptr;
+      lp.trace = nullptr; lp.zero_status = nullptr; lp.coop_flags = nullptr;
       cp.rp = rp;
+      cp.rp.coop_flags = nullptr;                  // the fused kernel always runs the barriers
       cp.m_tiles = pl.m_tiles; cp.splits = pl.splits; cp.gbar = gbar;
       static const int chain_trace = knob("EXB_CHAIN_TRACE", 0);
       cp.trace = chain_trace ? w.trace : nullptr;
@@ -2109,6 +2113,7 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
     lp.rsel = (k + pl.splits - 1) / pl.splits; lp.bank_max = reinterpret_cast<float*>(w.bsc);
     lp.trace = trace_on ? w.trace : nullptr;
     lp.zero_status = pre ? reinterpret_cast<unsigned long long*>(w.status) : nullptr;
+    lp.coop_flags = w.coop_flags;
     dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
     const bool prof = g_prof.on && g_prof.n < 64;
     if (prof) EXB_CUDA(cudaEventRecord(g_prof.e0[g_prof.n], st));
