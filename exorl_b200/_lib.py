@@ -193,6 +193,14 @@ class Workspace:
             cls._cache[k] = buf
         return buf, fresh
 
+    @classmethod
+    def size(cls, device, key):
+        """Bytes of the cached workspace (0 if none)."""
+        dev = torch.device(device)
+        k = (dev.index if dev.index is not None else torch.cuda.current_device(), key)
+        buf = cls._cache.get(k)
+        return 0 if buf is None else int(buf.numel())
+
 
 def require_cuda(t, name):
     if not (isinstance(t, torch.Tensor) and t.is_cuda):

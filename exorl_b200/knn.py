@@ -113,12 +113,28 @@ SYM_ENABLED = True
 SYM_MIN_ROWS = 200_000        # measured on B200 (rep 512, k 12): 1.06x at 131k rows, 1.33x at
                               # 262k, 1.50x at 1M; below, the sample pre-pass and the hit logs
                               # cost what the halved MMA work saves
-SYM_SAMPLE_MAX = 65536
+SYM_SAMPLE_MAX = 1 << 22      # (measurement scripts lower it to study the hit rate)
+SYM_MEM_FRACTION = 0.6        # of the free device memory the hit logs may take; else full screen
 sym_last = {}                 # diagnostics of the last symmetric call (sizes, fallback reason)
 
 
 def _sym_sample_rows(n):
+    """Rows of the sample pre-pass: 1/16 of the set.  The rate of hits per accumulator element is
+    k / sample_rows whatever n is, and the symmetric kernel's epilogue pays per hit (measured at
+    1M rows: 407 / 475 / 517 ms for 62 500 / 33 334 / 16 394 sample rows), while the pre-pass
+    costs sample_rows / n of a full screen — 1/16 is the measured optimum."""
     return int(min(SYM_SAMPLE_MAX, max(4096, n // 16)))
+
+
+def _sym_fits(dev, need):
+    """The hit logs are ~18 GB per million rows (rep 512, k 12): take the symmetric path only
+    when they fit beside what is already resident (a workspace of that size that already exists is
+    reused)."""
+    have = _lib.Workspace.size(dev, "knn_sym")
+    if have >= need:
+        return True
+    free, _ = torch.cuda.mem_get_info(dev)
+    return need - have <= SYM_MEM_FRACTION * free
 
 
 def _knn_topk_sym(src, k, idx_base):
@@ -140,7 +156,8 @@ def _knn_topk_sym(src, k, idx_base):
         dist = torch.empty(n, k, dtype=torch.float32, device=dev)
         idx = torch.empty(n, k, dtype=torch.int32, device=dev)
         need = lib.exb_knn_sym_workspace_bytes(n, dim, k, log_cap, recv_cap)
-        if need == 0:
+        if need == 0 or not _sym_fits(dev, need):
+            sym_last.update(n=n, workspace_bytes=need, no_room=True)
             return None
         ws, _ = _lib.Workspace.get(dev, "knn_sym", need)
         _lib.check(lib.exb_knn_sym_f32(

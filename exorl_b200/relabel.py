@@ -396,7 +396,10 @@ def _sym_queries_knn(rep, k, world, rank, group, tm):
     pair_lo, pair_hi, span_end, mid, extra = sym_span(tb, world, rank)
     with torch.cuda.device(dev):
         need = lib.exb_knn_sym_workspace_bytes(n, dim, k, log_cap, recv_cap)
-        if need == 0:
+        fits = torch.tensor([1 if (need and xknn._sym_fits(dev, need)) else 0], device=dev)
+        dist.all_reduce(fits, op=dist.ReduceOp.MIN, group=group)     # all ranks or none
+        if not int(fits.item()):
+            xknn.sym_last.update(n=n, workspace_bytes=need, no_room=True)
             return None
         ws, _ = _lib.Workspace.get(dev, "knn_sym", need)
         hits = _lib.SymHits()
