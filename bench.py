@@ -44,6 +44,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true",
                     help="skip the C1-C4 block (BASELINE configs 1-4) of the 1-GPU line")
+    ap.add_argument("--no-full-ab", action="store_true",
+                    help="skip the full-screen A/B steps (symmetric path switched off)")
     ap.add_argument("--no-exchange-ab", action="store_true",
                     help="skip the one-step timings of the bank-sharded exchanges (N > 1)")
     ap.add_argument("--balance", action="store_true",
@@ -285,6 +287,34 @@ def run_ours(a, rank, world, local_rank):
     barrier()
     ms_e2e = max_over_ranks(e0.elapsed_time(e1))
 
+    # the FULL screen on the same inputs (symmetric path switched off): one warm + two timed steps,
+    # so that the line itself shows what halving the tile pairs buys and that the full kernel still
+    # sits at the tensor roofline
+    full_ab = None
+    if not a.no_full_ab and xknn.sym_last.get("n") == a.n:
+        prev_sym = xknn.SYM_ENABLED
+        xknn.SYM_ENABLED = False
+        try:
+            step()
+            barrier()
+            _lib.check(lib.exb_profile_begin(1))
+            e0.record()
+            step()
+            step()
+            e1.record()
+            barrier()
+            ms_full = max_over_ranks(e0.elapsed_time(e1)) / 2
+            fk = (ctypes.c_float * 64)()
+            fn_ = ctypes.c_int(0)
+            _lib.check(lib.exb_profile_collect_sync(fk, 64, ctypes.byref(fn_)))
+            _lib.check(lib.exb_profile_begin(0))
+            k_ms = sum(fk[i] for i in range(fn_.value)) / max(fn_.value, 1)
+            full_ab = {"ms_per_step": ms_full, "queries_per_s": a.n / (ms_full * 1e-3),
+                       "kernel": "knn_screen_kernel (all tile pairs)", "kernel_ms": k_ms,
+                       "kernel_tflops": 2.0 * a.n * (a.n // world) * a.dim / (k_ms * 1e-3) / 1e12}
+        finally:
+            xknn.SYM_ENABLED = prev_sym
+
     # N > 1: the bank-sharded partitions of north_star (per-shard top-k -> NCCL exchange -> merge),
     # one warm + one timed step each, beside the partition the headline uses
     exchange_ab = None
@@ -413,6 +443,10 @@ def run_ours(a, rank, world, local_rank):
                          **({"traffic": None} if sym else screen_traffic(a.n, nb_local, a.dim))},
             "cpu_baseline": cpu_baseline,
         }
+        if full_ab is not None:
+            sustained_, _, _ = peaks()
+            full_ab["frac_of_sustained_peak"] = full_ab["kernel_tflops"] / sustained_
+            out["full_screen_ab"] = full_ab
         if exchange_ab is not None:
             out["exchange_ab"] = {"unit": "ms per step (one timed step each, max over ranks)",
                                   "headline_exchange": a.exchange, **exchange_ab}
