@@ -372,91 +372,132 @@ def sym_span(tb, world, rank):
     return lo, hi, span_end, mid, extra
 
 
-def _sym_queries_knn(rep, k, world, rank, group, tm):
+class _CudaSymBackend:
+    """The device side of the symmetric screen over several ranks (C entries exb_knn_sym_*).
+    tests/test_relabel_gloo.py swaps in a CPU stand-in with the same contract to exercise the
+    partition / exchange logic of `_sym_queries_knn` under gloo."""
+    tile = 256
+
+    def __init__(self, rep, k):
+        from . import knn as xknn
+        self.xknn, self.lib = xknn, _lib.load()
+        self.rep, self.k = rep, k
+        self.n, self.dim = rep.shape
+        self.dev = rep.device
+
+    def sample_rows(self):
+        return self.xknn._sym_sample_rows(self.n)
+
+    def sample_distances(self, lo, hi, sample):
+        d, _ = self.xknn._knn_topk_impl(self.rep[lo:hi], sample, self.k, 0, "screened", False,
+                                        allow_sym=False)
+        return d[:, self.k - 1]
+
+    def room(self, expected):
+        self.log_cap = int(-(-(3 * expected / 2 + 96) // 8) * 8)
+        self.recv_cap = int(-(-(3 * expected + 96) // 8) * 8)
+        self.need = self.lib.exb_knn_sym_workspace_bytes(self.n, self.dim, self.k, self.log_cap,
+                                                         self.recv_cap)
+        return bool(self.need) and self.xknn._sym_fits(self.dev, self.need)
+
+    def screen(self, d_all, span):
+        """-> (target, val, src) int32 / f32 / int32 device vectors of the transposed hits this
+        rank found (for ANY row), and whether the append buffer overflowed.  Synchronises."""
+        lib, dev = self.lib, self.dev
+        pair_lo, pair_hi, span_end, mid, extra = span
+        with torch.cuda.device(dev):
+            self.ws, _ = _lib.Workspace.get(dev, "knn_sym", self.need)
+            ws = self.ws
+            hits = _lib.SymHits()
+            _lib.check(lib.exb_knn_sym_screen_f32(
+                _lib.ptr(self.rep), self.n, self.dim, self.k, _lib.ptr(d_all), 1, self.log_cap,
+                self.recv_cap, pair_lo, pair_hi, span_end, mid, extra, _lib.ptr(ws), ws.numel(),
+                ctypes.byref(hits), _lib.stream_ptr(dev)))
+            base = ws.data_ptr()
+            cnt = ws[hits.count - base:hits.count - base + 8].view(torch.int64)
+            n_hits = int(cnt.item())                               # sync: the screen is done
+            over = n_hits > hits.capacity
+            n_hits = min(n_hits, hits.capacity)
+
+            def view(ptr, dtype):
+                off = ptr - base
+                return ws[off:off + 4 * n_hits].view(dtype)
+            return (view(hits.target, torch.int32), view(hits.val, torch.float32),
+                    view(hits.src, torch.int32)), over
+
+    def scatter_rerank(self, r_t, r_v, r_s, lo, hi):
+        """Received hits into the rows' lists, then the exact top-k of rows [lo, hi).
+        -> (dist, idx, undecided_rows, status_flags)"""
+        lib, dev, k = self.lib, self.dev, self.k
+        with torch.cuda.device(dev):
+            _lib.check(lib.exb_knn_sym_scatter(self.n, self.dim, k, self.log_cap, self.recv_cap,
+                                               _lib.ptr(r_t), _lib.ptr(r_v), _lib.ptr(r_s),
+                                               r_t.numel(), _lib.ptr(self.ws),
+                                               _lib.stream_ptr(dev)))
+            d_mine = torch.empty(hi - lo, k, dtype=torch.float32, device=dev)
+            i_mine = torch.empty(hi - lo, k, dtype=torch.int32, device=dev)
+            _lib.check(lib.exb_knn_sym_rerank_f32(
+                _lib.ptr(self.rep), self.n, self.dim, k, 0, self.log_cap, self.recv_cap, lo, hi,
+                _lib.ptr(d_mine), _lib.ptr(i_mine), _lib.ptr(self.ws), _lib.stream_ptr(dev)))
+        st = self.xknn.screened_status(dev, key="knn_sym")
+        return d_mine, i_mine, st[0], st[1]
+
+    def repair(self, lo, hi, d_mine, i_mine):
+        rows = (i_mine[:, 0] < 0).nonzero().flatten()
+        self.xknn._recompute_rows(self.rep[lo:hi], self.rep, self.k, 0, d_mine, i_mine, rows)
+
+
+def _sym_queries_knn(rep, k, world, rank, group, tm, backend=None):
     """kNN of this rank's (tile-aligned) query block through the symmetric screen spread over
     the ranks.  Returns (dist, idx, row_bounds) or None when any rank reports the pass invalid
     (the caller then runs the full screen).  Collectives: d_sample all-reduce (4N bytes), hit
     counts all-to-all, the hits themselves all-to-all (12 bytes each, ~ k N^2 / (2 S world))."""
     from . import knn as xknn
-    lib = _lib.load()
-    n, dim = rep.shape
+    be = backend if backend is not None else _CudaSymBackend(rep, k)
+    n = rep.size(0)
     dev = rep.device
-    tiles, tb, rb = sym_tile_blocks(n, world)
+    tiles, tb, rb = sym_tile_blocks(n, world, be.tile)
     lo, hi = rb[rank], rb[rank + 1]
-    stride = max(1, n // xknn._sym_sample_rows(n))
+    stride = max(1, n // be.sample_rows())
     sample = rep[::stride].contiguous()
-    d_loc, _ = xknn._knn_topk_impl(rep[lo:hi], sample, k, 0, "screened", False, allow_sym=False)
     d_all = torch.zeros(n, dtype=torch.float32, device=dev)
-    d_all[lo:hi] = d_loc[:, k - 1]
+    d_all[lo:hi] = be.sample_distances(lo, hi, sample)
     dist.all_reduce(d_all, op=dist.ReduceOp.SUM, group=group)
     tm("sym_sample_prepass")
-    expected = 1.3 * k * n / sample.size(0)
-    log_cap = int(-(-(3 * expected / 2 + 96) // 8) * 8)
-    recv_cap = int(-(-(3 * expected + 96) // 8) * 8)
-    pair_lo, pair_hi, span_end, mid, extra = sym_span(tb, world, rank)
-    with torch.cuda.device(dev):
-        need = lib.exb_knn_sym_workspace_bytes(n, dim, k, log_cap, recv_cap)
-        fits = torch.tensor([1 if (need and xknn._sym_fits(dev, need)) else 0], device=dev)
-        dist.all_reduce(fits, op=dist.ReduceOp.MIN, group=group)     # all ranks or none
-        if not int(fits.item()):
-            xknn.sym_last.update(n=n, workspace_bytes=need, no_room=True)
-            return None
-        ws, _ = _lib.Workspace.get(dev, "knn_sym", need)
-        hits = _lib.SymHits()
-        _lib.check(lib.exb_knn_sym_screen_f32(
-            _lib.ptr(rep), n, dim, k, _lib.ptr(d_all), 1, log_cap, recv_cap, pair_lo, pair_hi,
-            span_end, mid, extra, _lib.ptr(ws), ws.numel(), ctypes.byref(hits),
-            _lib.stream_ptr(dev)))
-        base = ws.data_ptr()
-
-        def view(ptr, count, dtype):
-            off = ptr - base
-            return ws[off:off + 4 * count].view(dtype)
-        cnt = ws[hits.count - base:hits.count - base + 8].view(torch.int64)
-        n_hits = int(cnt.item())                                   # sync: the screen is done
-        tm("sym_screen")
-        bad = torch.tensor([1 if n_hits > hits.capacity else 0], device=dev)
-        n_hits = min(n_hits, hits.capacity)
-        tgt = view(hits.target, n_hits, torch.int32)
-        val = view(hits.val, n_hits, torch.float32)
-        src = view(hits.src, n_hits, torch.int32)
-        # route every hit to the rank that owns its query row
-        edges = torch.tensor(rb[1:-1], dtype=torch.int32, device=dev)
-        # (a counting partition: one mask + compaction per destination is cheaper than a sort of
-        # 10^7..10^8 keys)
-        dest = torch.bucketize(tgt, edges, right=True)
-        packed = torch.stack([tgt, val.view(torch.int32), src], dim=1)
-        parts = [packed[(dest == r).nonzero().flatten()] for r in range(world)]
-        sc = [p.size(0) for p in parts]
-        counts = torch.tensor(sc, dtype=torch.int64, device=dev)
-        recv_counts = torch.empty_like(counts)
-        dist.all_to_all_single(recv_counts, counts, group=group)
-        rc_ = recv_counts.tolist()
-        recv = torch.empty((sum(rc_), 3), dtype=torch.int32, device=dev)
-        dist.all_to_all_single(recv, torch.cat(parts, dim=0), rc_, sc, group=group)
-        tm("sym_hit_exchange")
-        r_t = recv[:, 0].contiguous()
-        r_v = recv[:, 1].contiguous().view(torch.float32)
-        r_s = recv[:, 2].contiguous()
-        _lib.check(lib.exb_knn_sym_scatter(n, dim, k, log_cap, recv_cap, _lib.ptr(r_t),
-                                           _lib.ptr(r_v), _lib.ptr(r_s), recv.size(0),
-                                           _lib.ptr(ws), _lib.stream_ptr(dev)))
-        d_mine = torch.empty(hi - lo, k, dtype=torch.float32, device=dev)
-        i_mine = torch.empty(hi - lo, k, dtype=torch.int32, device=dev)
-        _lib.check(lib.exb_knn_sym_rerank_f32(_lib.ptr(rep), n, dim, k, 0, log_cap, recv_cap, lo,
-                                              hi, _lib.ptr(d_mine), _lib.ptr(i_mine),
-                                              _lib.ptr(ws), _lib.stream_ptr(dev)))
-    st = xknn.screened_status(dev, key="knn_sym")
-    bad[0] |= 1 if (st[1] & 2) else 0
+    fits = torch.tensor([1 if be.room(1.3 * k * n / sample.size(0)) else 0], device=dev)
+    dist.all_reduce(fits, op=dist.ReduceOp.MIN, group=group)          # all ranks or none
+    if not int(fits.item()):
+        xknn.sym_last.update(n=n, no_room=True)
+        return None
+    (tgt, val, src), over = be.screen(d_all, sym_span(tb, world, rank))
+    tm("sym_screen")
+    bad = torch.tensor([1 if over else 0], device=dev)
+    # route every hit to the rank that owns its query row (a counting partition: one mask +
+    # compaction per destination is cheaper than a sort of 10^7..10^8 keys)
+    edges = torch.tensor(rb[1:-1], dtype=torch.int32, device=dev)
+    dest = torch.bucketize(tgt, edges, right=True)
+    packed = torch.stack([tgt, val.view(torch.int32), src], dim=1)
+    parts = [packed[(dest == r).nonzero().flatten()] for r in range(world)]
+    sc = [p.size(0) for p in parts]
+    counts = torch.tensor(sc, dtype=torch.int64, device=dev)
+    recv_counts = torch.empty_like(counts)
+    dist.all_to_all_single(recv_counts, counts, group=group)
+    rc_ = recv_counts.tolist()
+    recv = torch.empty((sum(rc_), 3), dtype=torch.int32, device=dev)
+    dist.all_to_all_single(recv, torch.cat(parts, dim=0), rc_, sc, group=group)
+    tm("sym_hit_exchange")
+    d_mine, i_mine, und, status = be.scatter_rerank(
+        recv[:, 0].contiguous(), recv[:, 1].contiguous().view(torch.float32),
+        recv[:, 2].contiguous(), lo, hi)
+    bad[0] |= 1 if (status & 2) else 0
     dist.all_reduce(bad, op=dist.ReduceOp.MAX, group=group)
-    xknn.sym_last.update(n=n, sample_rows=sample.size(0), log_cap=log_cap, recv_cap=recv_cap,
-                         undecided=st[0], status=st[1], world=world, hits_sent=n_hits)
+    xknn.sym_last.update(n=n, sample_rows=sample.size(0), undecided=und, status=status,
+                         world=world, hits_sent=int(tgt.numel()))
     if int(bad.item()):
         xknn.sym_last["fell_back_to_full_screen"] = True
         return None
-    if st[1] & 1:
-        rows = (i_mine[:, 0] < 0).nonzero().flatten()
-        xknn._recompute_rows(rep[lo:hi], rep, k, 0, d_mine, i_mine, rows)
+    if status & 1:
+        be.repair(lo, hi, d_mine, i_mine)
     tm("sym_rerank")
     return d_mine, i_mine, rb
 
@@ -514,13 +555,17 @@ def relabel_apt_reward(rep, args, rms=None, group=None, exchange="auto", mode="a
     elif exchange == "auto":
         exchange = "all_to_all"
 
-    if (world > 1 and exchange == "queries" and stages is _CudaStages and mode != "exact"
-            and not balance and not isinstance(rep, PreparedRep)):
+    sym_backend = getattr(stages, "sym_backend", None)     # tests: CPU stand-in (gloo)
+    if (world > 1 and exchange == "queries" and (stages is _CudaStages or sym_backend)
+            and mode != "exact" and not balance and not isinstance(rep, PreparedRep)):
         from . import knn as xknn
-        if (xknn.SYM_ENABLED and n >= xknn.SYM_MIN_ROWS and xknn.OVERFLOW_POLICY == "sync"
+        if sym_backend or (
+                xknn.SYM_ENABLED and n >= xknn.SYM_MIN_ROWS and xknn.OVERFLOW_POLICY == "sync"
                 and rep.size(1) <= _lib.SCREEN_MAX_DIM and k <= _lib.SCREEN_MAX_K):
             # a set against itself: every unordered tile pair on exactly one rank (K1s)
-            out = _sym_queries_knn(_as_rows_f32(rep), k, world, rank, group, tm)
+            rows = _as_rows_f32(rep)
+            out = _sym_queries_knn(rows, k, world, rank, group, tm,
+                                   backend=sym_backend(rows, k) if sym_backend else None)
             if out is not None:
                 d_mine, i_mine, rb = out
                 lo, hi = rb[rank], rb[rank + 1]

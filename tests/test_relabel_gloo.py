@@ -275,3 +275,120 @@ def test_balanced_bounds_quantum_and_fallback():
     # a block that would fall below min_rows -> equal split
     assert balanced_bounds(100, [1.0, 1e-6], quantum=256, min_rows=12) == \
         [shard_bounds(100, 2, r) for r in range(2)]
+
+
+# ---------------------------------------------------------------- symmetric screen over the ranks
+class _OracleSymBackend:
+    """CPU stand-in of relabel._CudaSymBackend with tiles of 4 rows: direct candidates are kept
+    per row, transposed hits are returned as (query row, -dist^2, bank row) for ANY row, exactly
+    like the CUDA screen; what is under test is `_sym_queries_knn`'s span assignment, routing of
+    the hits to the owner of their row, and the all-to-all layouts."""
+    tile = 4
+
+    def __init__(self, rep, k):
+        self.rep, self.k, self.n = rep, k, rep.size(0)
+        self.direct = {}
+
+    def sample_rows(self):
+        return max(2 * self.k, self.n // 4)
+
+    def sample_distances(self, lo, hi, sample):
+        d = torch.cdist(self.rep[lo:hi].double(), sample.double())
+        return d.topk(self.k, dim=1, largest=False).values[:, -1].float() * 1.0001
+
+    def room(self, expected):
+        return True
+
+    def screen(self, d_all, span):
+        pair_lo, pair_hi, span_end, mid, extra = span
+        n, t = self.n, self.tile
+        tiles = (n + t - 1) // t
+        full = torch.cdist(self.rep.double(), self.rep.double())
+        tg, va, sr = [], [], []
+        for u in range(pair_lo, pair_hi):
+            length = span_end - u + (extra if u >= mid else 0)
+            for j in range(length):
+                tt = (u + j) % tiles
+                for i in range(u * t, min(n, (u + 1) * t)):
+                    for c in range(tt * t, min(n, (tt + 1) * t)):
+                        dd = float(full[i, c])
+                        if dd <= float(d_all[i]):
+                            self.direct.setdefault(i, []).append((dd, c))
+                        if tt != u and dd <= float(d_all[c]):
+                            tg.append(c); va.append(-dd * dd); sr.append(i)
+        return (torch.tensor(tg, dtype=torch.int32), torch.tensor(va, dtype=torch.float32),
+                torch.tensor(sr, dtype=torch.int32)), False
+
+    def scatter_rerank(self, r_t, r_v, r_s, lo, hi):
+        cand = {i: list(self.direct.get(i, [])) for i in range(lo, hi)}
+        for tgt, v, s in zip(r_t.tolist(), r_v.tolist(), r_s.tolist()):
+            assert lo <= tgt < hi, "a hit was routed to a rank that does not own its row"
+            cand[tgt].append(((-v) ** 0.5, s))
+        d = torch.empty(hi - lo, self.k)
+        ix = torch.empty(hi - lo, self.k, dtype=torch.int32)
+        for i in range(lo, hi):
+            rows = sorted(set(c for _, c in cand[i]))
+            assert len(rows) == len(cand[i]), "a (row, bank row) pair was covered twice"
+            dd = torch.norm(self.rep[i][None, :] - self.rep[rows], dim=1, p=2)
+            o = torch.argsort(dd, stable=True)[:self.k]
+            d[i - lo], ix[i - lo] = dd[o], torch.tensor(rows, dtype=torch.int32)[o]
+        return d, ix, 0, 0
+
+    def repair(self, lo, hi, d_mine, i_mine):
+        raise AssertionError("nothing to repair in the stand-in")
+
+
+class _OracleStagesSym(_OracleStages):
+    sym_backend = _OracleSymBackend
+
+
+def _sym_worker(rank, world, port, n, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from exorl_b200 import knn as xknn
+        from exorl_b200.relabel import relabel_apt_reward, last_query_block
+        g = torch.Generator().manual_seed(5)
+        rep = torch.tanh(torch.randn(n, 16, generator=g))
+        args = types.SimpleNamespace(knn_k=4, knn_avg=True, knn_rms=True, knn_clip=0.0)
+        rms = types.SimpleNamespace(M=torch.zeros(1), S=torch.ones(1), n=1e-4)
+        xknn.sym_last.clear()
+        r, d, i = relabel_apt_reward(rep, args, rms=rms, exchange="queries",
+                                     stages=_OracleStagesSym, return_knn=True)
+        assert xknn.sym_last.get("world") == world
+        q.put((rank, r.numpy(), float(rms.M), float(rms.S), rms.n, d.numpy(), i.numpy(),
+               last_query_block["lo"], last_query_block["hi"]))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n", [(2, 64), (2, 51), (3, 70), (4, 96)])
+def test_symmetric_screen_over_ranks_equals_unsharded(world, n):
+    """Every unordered tile pair on exactly one rank, transposed hits routed to the owner of
+    their row with an all-to-all: rewards, RMS state and every rank's own (dist, idx) block equal
+    the unsharded oracle."""
+    from oracle import RmsState, pbe_reward, knn_smallest
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_sym_worker, args=(r, world, port, n, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=180) for _ in range(world)], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    g = torch.Generator().manual_seed(5)
+    rep = torch.tanh(torch.randn(n, 16, generator=g))
+    st = RmsState()
+    want = pbe_reward(rep, rep, st, 4, True, True, 0.0).numpy()
+    od, oi = knn_smallest(rep, rep, 4)
+    covered = 0
+    for rank, r, m, s, cnt, d, i, lo, hi in res:
+        np.testing.assert_allclose(r, want, rtol=1e-5, atol=1e-7)
+        assert m == pytest.approx(float(st.M), rel=1e-5) and s == pytest.approx(float(st.S), rel=1e-4)
+        assert cnt == pytest.approx(st.n)
+        np.testing.assert_allclose(d, od[lo:hi].numpy(), rtol=1e-5, atol=1e-6)
+        assert (np.sort(i, axis=1) == np.sort(oi[lo:hi].numpy(), axis=1)).all()
+        covered += hi - lo
+    assert covered == n
