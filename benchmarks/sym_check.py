@@ -35,12 +35,16 @@ def main():
     ap.add_argument("--kind", default="tanh")
     ap.add_argument("--sample-max", type=int, default=0, help="override knn.SYM_SAMPLE_MAX")
     ap.add_argument("--no-full", action="store_true", help="skip the full-screen comparison")
+    ap.add_argument("--knob", action="append", default=[], help="NAME=VALUE for exb_debug_knob_set")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     import ctypes
     from exorl_b200 import _lib
     lib = _lib.load()
     lib.exb_debug_knob_set(b"EXB_SYM_STATS", 1)
+    for kv in a.knob:
+        name, val = kv.split("=")
+        lib.exb_debug_knob_set(name.encode(), int(val))
     for n in a.sizes:
         g = torch.Generator(device=dev).manual_seed(5)
         x = torch.randn(n, a.dim, generator=g, device=dev)

@@ -756,22 +756,23 @@ __device__ __forceinline__ void filter_chunk_g(ListState& st, const uint32_t (&r
   }
 }
 
-// FILT 4: per-warp staging queue of transposed hits in shared memory (see ScreenParams).
+// FILT 4: per-warp staging queue of transposed hits in shared memory (see ScreenParams); the entry
+// count lives in a warp-uniform register of the owning warp.
 constexpr int SYM_QCAP = 128;
 struct SymQueue {
-  int* target; float* val; int* src; int* n;            // shared memory, this warp's
+  int* target; float* val; int* src;                    // shared memory, this warp's
+  float* scratch;                                       // 32 floats: one lane's chunk, see sym_chunk
   int* g_target; float* g_val; int* g_src;              // the global append buffer
   unsigned long long* g_count;
   long long g_cap;
 };
-__device__ __forceinline__ void sym_queue_flush(const SymQueue& q, int lane) {
+__device__ __forceinline__ void sym_queue_flush(const SymQueue& q, int& qn, int lane) {
   __syncwarp();
-  const int cnt = min(*reinterpret_cast<volatile int*>(q.n), SYM_QCAP);
-  if (cnt > 0) {
+  if (qn > 0) {
     unsigned long long base = 0;
-    if (lane == 0) base = atomicAdd(q.g_count, (unsigned long long)cnt);
+    if (lane == 0) base = atomicAdd(q.g_count, (unsigned long long)qn);
     base = __shfl_sync(0xffffffffu, base, 0);
-    for (int e = lane; e < cnt; e += 32) {
+    for (int e = lane; e < qn; e += 32) {
       const long long at = (long long)base + e;
       if (at < q.g_cap) {
         q.g_target[at] = q.target[e];
@@ -781,23 +782,7 @@ __device__ __forceinline__ void sym_queue_flush(const SymQueue& q, int lane) {
     }
   }
   __syncwarp();
-  if (lane == 0) *q.n = 0;
-  __syncwarp();
-}
-__device__ __forceinline__ void sym_queue_push(const SymQueue& q, int target, float v, int src) {
-  const int slot = atomicAdd(q.n, 1);
-  if (slot < SYM_QCAP) {
-    q.target[slot] = target;
-    q.val[slot] = v;
-    q.src[slot] = src;
-  } else {                                  // queue full inside one chunk (dense data): direct
-    const long long at = (long long)atomicAdd(q.g_count, 1ull);
-    if (at < q.g_cap) {
-      q.g_target[at] = target;
-      q.g_val[at] = v;
-      q.g_src[at] = src;
-    }
-  }
+  qn = 0;
 }
 
 // FILT 4: one 32-column chunk tested in both directions against fixed thresholds (thread = row i
@@ -806,11 +791,22 @@ __device__ __forceinline__ void sym_queue_push(const SymQueue& q, int target, fl
 //   transposed  s_ji = g - hb_i >= tkeep_j, tested as g - tkeep_j >= hb_i (the 4e-6 relative slack
 //               of the thresholds covers the different rounding) -> (j, s_ji, i) into the queue:
 //               "bank row i is a candidate of query row j"
-// nd counts every direct hit; entries beyond cap are dropped and the log reads as overflowed.
+// Fast path: group maxima of both differences, one vote.  Hit path, WARP-COOPERATIVE: a lane whose
+// row has a hit parks its 32 accumulators in shared memory and the whole warp — lane c = column c
+// — redoes that row's two tests in parallel, so a hit costs ~60 warp instructions instead of a
+// ~200-instruction serial walk by one lane with 31 idle (measured at 1M rows: the serial hit path
+// was 97 ms of the kernel's 445).  nd counts every direct hit; entries beyond cap are dropped and
+// the log reads as overflowed.
+struct SymRow {          // per-lane constants of the lane's query row
+  float tkeep_i, hb_t, hb_i;
+  int row;
+};
 __device__ __forceinline__ void sym_chunk(const uint32_t (&r)[32], const float* hn_chunk,
-                                          const float* tk_chunk, float tkeep_i, float hb_t,
-                                          float hb_i, int col0, int cap, float* dv, int* di,
-                                          int& nd, const SymQueue& sq, int row, int lane) {
+                                          const float* tk_chunk, const SymRow& me, int col0,
+                                          int cap, float* dlog_val, int* dlog_idx, int half,
+                                          int& nd, const SymQueue& sq, int& qn, int lane,
+                                          bool record = true) {
+  const unsigned full = 0xffffffffu;
   const float4* hn4 = reinterpret_cast<const float4*>(hn_chunk);
   const float4* tk4 = reinterpret_cast<const float4*>(tk_chunk);
   float gd[8], gt[8];
@@ -826,38 +822,52 @@ __device__ __forceinline__ void sym_chunk(const uint32_t (&r)[32], const float* 
                          fmaxf(fmaxf(gd[4], gd[5]), fmaxf(gd[6], gd[7])));
   const float mt = fmaxf(fmaxf(fmaxf(gt[0], gt[1]), fmaxf(gt[2], gt[3])),
                          fmaxf(fmaxf(gt[4], gt[5]), fmaxf(gt[6], gt[7])));
-  if (__any_sync(0xffffffffu, md >= tkeep_i || mt >= hb_t)) {
-    uint32_t gm = 0;
-#pragma unroll
-    for (int q = 0; q < 8; ++q)
-      gm |= ((gd[q] >= tkeep_i ? 1u : 0u) | (gt[q] >= hb_t ? 0x100u : 0u)) << q;
+  unsigned hl = __ballot_sync(full, md >= me.tkeep_i || mt >= me.hb_t);
+  if (hl == 0u || !record) return;
+  const unsigned lt = (1u << lane) - 1u;
+  const float h_c = hn_chunk[lane], t_c = tk_chunk[lane];   // this lane's column
 #pragma unroll 1
-    while (gm) {
-      const int b = __ffs(gm) - 1;
-      gm &= gm - 1;
-      const int q = b & 7;
-      const bool transposed = b >= 8;
-      uint32_t u[4];
-      select_group(r, q, u);
-      const float4 c = transposed ? tk4[q] : hn4[q];
-      const float bound = transposed ? hb_t : tkeep_i;
-      const float sv[4] = {__uint_as_float(u[0]) - c.x, __uint_as_float(u[1]) - c.y,
-                           __uint_as_float(u[2]) - c.z, __uint_as_float(u[3]) - c.w};
+  while (hl) {                                   // warp-uniform: the lanes (rows) with a hit
+    const int L = __ffs(hl) - 1;
+    hl &= hl - 1;
+    if (qn > SYM_QCAP - 32) sym_queue_flush(sq, qn, lane);
+    if (lane == L) {
+      uint4* s4 = reinterpret_cast<uint4*>(sq.scratch);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        if (sv[i] >= bound) {
-          if (transposed) {
-            sym_queue_push(sq, col0 + 4 * q + i, __uint_as_float(u[i]) - hb_i, row);
-          } else {
-            if (nd < cap) { dv[nd] = sv[i]; di[nd] = col0 + 4 * q + i; }
-            ++nd;
-          }
-        }
-      }
+      for (int q = 0; q < 8; ++q) s4[q] = make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]);
     }
     __syncwarp();
-    if (*reinterpret_cast<volatile int*>(sq.n) >= 64) sym_queue_flush(sq, lane);
+    const float g = sq.scratch[lane];
+    const float tkeep_L = __shfl_sync(full, me.tkeep_i, L);
+    const float hbt_L = __shfl_sync(full, me.hb_t, L);
+    const int row_L = __shfl_sync(full, me.row, L);
+    const float sd = g - h_c;
+    const bool hit_d = sd >= tkeep_L;
+    const bool hit_t = (g - t_c) >= hbt_L;
+    const unsigned m_d = __ballot_sync(full, hit_d), m_t = __ballot_sync(full, hit_t);
+    if (m_d) {
+      const int nd_L = __shfl_sync(full, nd, L);
+      const int pos = nd_L + __popc(m_d & lt);
+      if (hit_d && pos < cap) {
+        const int64_t o = ((int64_t)row_L * 2 + half) * cap + pos;
+        dlog_val[o] = sd;
+        dlog_idx[o] = col0 + lane;
+      }
+      if (lane == L) nd += __popc(m_d);
+    }
+    if (m_t) {
+      const float hbi_L = __shfl_sync(full, me.hb_i, L);
+      const int slot = qn + __popc(m_t & lt);      // < SYM_QCAP by the flush above
+      if (hit_t) {
+        sq.target[slot] = col0 + lane;
+        sq.val[slot] = g - hbi_L;
+        sq.src[slot] = row_L;
+      }
+      qn += __popc(m_t);
+    }
+    __syncwarp();                                // the scratch row is free again
   }
+  if (qn >= 64) sym_queue_flush(sq, qn, lane);
 }
 
 // FILT 1: seed + inline appends (short scans); 2: sample-tile seed + per-thread hit loop;
@@ -885,7 +895,7 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
   const uint32_t li_off = lv_off + (V3 ? 0 : SCR_CAP * SCR_M * 4);
   const uint32_t hn_off = li_off + (V3 ? 0 : SCR_CAP * SCR_M * 4);
   const uint32_t sq_off = hn_off + 16 * (SCR_N / 2) * 4;   // SYM: per-warp hit queues
-  const uint32_t bar_off = SYM ? sq_off + 8 * (SYM_QCAP * 12 + 16)
+  const uint32_t bar_off = SYM ? sq_off + 8 * (SYM_QCAP * 12 + 128)
                                : hn_off + (V3 ? 8 * (SCR_N / 2) * 4 : 2 * SCR_N * 4);
   float* s_lv = reinterpret_cast<float*>(sm + lv_off);
   int* s_li = reinterpret_cast<int*>(sm + li_off);
@@ -1066,23 +1076,23 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
     const bool row_ok = row < p.nq;
     const int cap = p.log_cap;
     const int64_t o = (row_ok ? row : 0) * 2 + half;
-    float* dv = p.dlog_val + o * cap;
-    int* di = p.dlog_idx + o * cap;
     SymQueue sq;
     {
-      uint8_t* qb = sm + sq_off + (warp - 2) * (SYM_QCAP * 12 + 16);
+      uint8_t* qb = sm + sq_off + (warp - 2) * (SYM_QCAP * 12 + 128);
       sq.target = reinterpret_cast<int*>(qb);
       sq.val = reinterpret_cast<float*>(qb + SYM_QCAP * 4);
       sq.src = reinterpret_cast<int*>(qb + SYM_QCAP * 8);
-      sq.n = reinterpret_cast<int*>(qb + SYM_QCAP * 12);
+      sq.scratch = reinterpret_cast<float*>(qb + SYM_QCAP * 12);
       sq.g_target = p.tq_target; sq.g_val = p.tq_val; sq.g_src = p.tq_src;
       sq.g_count = p.tq_count; sq.g_cap = p.tq_cap;
-      if (lane == 0) *sq.n = 0;
-      __syncwarp();
     }
+    int qn = 0;                                   // queued transposed hits (warp-uniform)
     // rows past nq: unreachable thresholds in both directions
-    const float tkeep_i = row_ok ? __ldg(p.sym_tkeep + row) : FLT_MAX;
-    const float hb_i = row_ok ? __ldg(p.ha + row) : INFINITY;     // this row as a BANK row
+    SymRow me;
+    me.tkeep_i = row_ok ? __ldg(p.sym_tkeep + row) : FLT_MAX;
+    me.hb_i = row_ok ? __ldg(p.ha + row) : INFINITY;              // this row as a BANK row
+    me.hb_t = me.hb_i;
+    me.row = (int)(row_ok ? row : 0);
     int nd = 0;
     float* hn = s_hn + (warp - 2) * (SCR_N / 2);                  // 128 bank half norms
     float* tk = s_hn + (8 + warp - 2) * (SCR_N / 2);              // 128 column-row thresholds
@@ -1122,19 +1132,19 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
       const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)as * SCR_N +
                              (uint32_t)half * (SCR_N / 2);
       const int col_base = t * SCR_N + half * (SCR_N / 2);
-      const float hb_t = diag ? INFINITY : hb_i;  // transposed test off on the diagonal tile
+      me.hb_t = diag ? INFINITY : me.hb_i;        // transposed test off on the diagonal tile
       uint32_t ra[32], rb[32];
       tmem_ld32(t_row, ra);
 #pragma unroll 1
       for (int ch = 0; ch < NCH; ch += 2) {
         tmem_ld_wait();
         tmem_ld32(t_row + (ch + 1) * 32, rb);
-        sym_chunk(ra, hn + ch * 32, tk + ch * 32, tkeep_i, hb_t, hb_i, col_base + ch * 32, cap, dv,
-                  di, nd, sq, (int)row, lane);
+        sym_chunk(ra, hn + ch * 32, tk + ch * 32, me, col_base + ch * 32, cap, p.dlog_val,
+                  p.dlog_idx, half, nd, sq, qn, lane, p.debug != 3);
         tmem_ld_wait();
         if (ch + 2 < NCH) tmem_ld32(t_row + (ch + 2) * 32, ra);
-        sym_chunk(rb, hn + (ch + 1) * 32, tk + (ch + 1) * 32, tkeep_i, hb_t, hb_i,
-                  col_base + (ch + 1) * 32, cap, dv, di, nd, sq, (int)row, lane);
+        sym_chunk(rb, hn + (ch + 1) * 32, tk + (ch + 1) * 32, me, col_base + (ch + 1) * 32, cap,
+                  p.dlog_val, p.dlog_idx, half, nd, sq, qn, lane, p.debug != 3);
       }
       tc_fence_before();
       __syncwarp();
@@ -1143,7 +1153,7 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
         else mbar_arrive(bar_tempty(as));
       }
     }
-    sym_queue_flush(sq, lane);
+    sym_queue_flush(sq, qn, lane);
     if (row_ok) p.dlog_cnt[o] = nd > cap ? -1 : nd;
   } else if constexpr (V3) {
     // ===================== epilogue, eight warps: (lane quadrant, column half) ================
@@ -2306,7 +2316,7 @@ static bool sym_plan(int64_t n, int dim, int k, SymPlan* pl) {
   if (fbs * k > 512) fbs = 512 / k;
   pl->fb_splits = fbs < 1 ? 1 : fbs;
   const size_t fixed = (size_t)pl->nkc * SCR_A_CHUNK_BYTES + 16 * (SCR_N / 2) * 4 +
-                       8 * (SYM_QCAP * 12 + 16) + (2 * SCR_MAX_STAGES + 5) * 8 + 16 + 1024;
+                       8 * (SYM_QCAP * 12 + 128) + (2 * SCR_MAX_STAGES + 5) * 8 + 16 + 1024;
   const int b_stage = SCR_B_STAGE_BYTES / 2;
   int stages = (int)((SCR_SMEM_LIMIT - fixed) / b_stage);
   if (stages > SCR_MAX_STAGES) stages = SCR_MAX_STAGES;
@@ -2423,6 +2433,8 @@ static int sym_screen_phase(const float* rep, int64_t n, int dim, int k, const f
   sp.nq = n; sp.nb = n; sp.nkc = pl.nkc; sp.n_tiles = pl.n_tiles;
   sp.tiles_per_split = pl.n_tiles; sp.splits = 1; sp.k = k; sp.stages = pl.stages;
   sp.lists = 2; sp.head = nullptr;
+  static const int sym_debug = knob("EXB_SYM_DEBUG", 0);   // 3 = measure without the hit path
+  sp.debug = sym_debug;
   sp.sym_pair_lo = span.pair_lo; sp.sym_span_end = span.span_end;
   sp.sym_mid_pair = span.mid_pair; sp.sym_extra = span.extra;
   sp.sym_tkeep = w.tkeep; sp.dlog_val = w.dlog_val; sp.dlog_idx = w.dlog_idx;
