@@ -63,7 +63,9 @@ def per_update():
     g = torch.Generator(device=dev).manual_seed(1)
     w = torch.randn(512, 24, generator=g, device=dev) / 24 ** 0.5
     z = torch.zeros(512, device=dev)
-    for step in (0.05, 0.005, 0.0):
+    import itertools
+    for block_scan, step in itertools.product((False, True), (0.05, 0.005, 0.0)):
+        xb.knn.set_per_update_scan(block_scan)
         obs = torch.randn(1, 24, generator=g, device=dev) + torch.cumsum(
             step * torch.randn(1024, 24, generator=g, device=dev), dim=0)
         if step == 0.0:
@@ -90,7 +92,8 @@ def per_update():
             e1.synchronize()
             te.append(e0.elapsed_time(e1) * 1e3)
         same = bool(torch.allclose(r, re_, rtol=1e-5, atol=1e-7))
-        print(json.dumps({"per_update_batch": 1024, "walk_step": step, "us_median": sorted(ts)[10],
+        print(json.dumps({"per_update_batch": 1024, "walk_step": step,
+                          "block_cooperative_scan": block_scan, "us_median": sorted(ts)[10],
                           "exact_path_us_median": sorted(te)[10],
                           "rows_recomputed_inline": und, "equals_exact_path": same}), flush=True)
 

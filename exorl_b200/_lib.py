@@ -60,6 +60,7 @@ SIGNATURES = {
                                             _vp, _vp, _vp, _vp, _sz, _vp]),
     "exb_knn_screened_status_sync": (_c.c_int, [_vp, _c.POINTER(_i32), _vp]),
     "exb_debug_trace_sync": (_c.c_int, [_vp, _c.POINTER(_i64), _vp]),
+    "exb_knn_set_per_update_scan": (_c.c_int, [_c.c_int]),
     "exb_debug_knob_set": (_c.c_int, [_c.c_char_p, _c.c_int]),
     "exb_profile_begin": (_c.c_int, [_c.c_int]),
     "exb_profile_collect_sync": (_c.c_int, [_c.POINTER(_f32), _c.c_int, _c.POINTER(_c.c_int)]),

@@ -150,7 +150,8 @@ apt_chain_kernel(const __grid_constant__ CUtensorMap tmap_q,
     WarpTopK top;
     unsigned need = 0;
     if (active)
-      rerank_row<true, NI, false>(p, row, lane, s_surv + warp * RR_SURV, s_val + warp * RR_SURV, q,
+      rerank_row<true, NI, false, true>(p, row, lane, s_surv + warp * RR_SURV,
+                                        s_val + warp * RR_SURV, q,
                                   top, need);
     {
       float qq[16];

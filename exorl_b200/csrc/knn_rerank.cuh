@@ -243,7 +243,7 @@ __device__ __noinline__ void scan_insert(const float (&q)[16], const float* __re
 // scanned for this row — bit sp = the columns of split sp, RR_NEED_ALL = the whole bank — which
 // the block then scans cooperatively (coop_scan).
 constexpr unsigned RR_NEED_ALL = 0xffffffffu;
-template <bool LAT, int NI, bool SH = false>
+template <bool LAT, int NI, bool SH = false, bool COOP = false>
 __device__ __forceinline__ bool rerank_row(const RerankParams& p, int64_t row, int lane,
                                            int* surv_w, float* val_w, float (&q)[16],
                                            WarpTopK& top, unsigned& need) {
@@ -468,7 +468,8 @@ __device__ __forceinline__ bool rerank_row(const RerankParams& p, int64_t row, i
       tt.init();
       if ((why & 4) || !(ea_row < INFINITY)) {
         // outside the fp16 range: no screened score means anything, scan the whole bank
-        need = RR_NEED_ALL;
+        if constexpr (COOP) need = RR_NEED_ALL;
+        else scan_insert<NI>(qq, p.B, dim, k, lane, (int)p.nb, nullptr, 0, tt);
       } else {
         // Only the splits whose list overflowed lost entries.  Every split's k-th chain entry is
         // still a lower bound of the k-th best score, so the best of them gives a valid (looser)
@@ -483,7 +484,18 @@ __device__ __forceinline__ bool rerank_row(const RerankParams& p, int64_t row, i
         st.dl = (st.ha + hb_max) * SCR_ACC_EPS;
         st.tk = t0;
         const float tkeep0 = (t0 > -FLT_MAX) ? keep_threshold(st) : -FLT_MAX;
-        need = __ballot_sync(full, lane < splits && my_cnt < 0);   // splits <= 16: never NEED_ALL
+        unsigned ovf = __ballot_sync(full, lane < splits && my_cnt < 0);   // splits <= 16
+        if constexpr (COOP) {
+          need = ovf;                              // scanned by the block together (coop_scan)
+        } else {
+          while (ovf) {
+            const int sp = __ffs(ovf) - 1;
+            ovf &= ovf - 1;
+            const int lo = sp * p.split_cols;
+            const int cnt = min((int)p.nb - lo, p.split_cols);
+            if (cnt > 0) scan_insert<NI>(qq, p.B, dim, k, lane, cnt, nullptr, lo, tt);
+          }
+        }
         int n = 0;
         __syncwarp();
 #pragma unroll
@@ -661,7 +673,11 @@ __device__ __noinline__ void coop_scan(const RerankParams& p, const float (&q)[1
   __syncthreads();
 }
 
-template <bool LAT, int NI, bool SH = false>
+// COOP (LAT only): rows that lost bank ranges are scanned by the block together (coop_scan)
+// instead of by their own warp.  A separate instance because its presence alone costs the common
+// path 1.3 us (146 instead of 104 registers, 35 KB of static shared memory, a jump over the scan
+// code: 15.9 vs 14.6 us for the C1 rerank, ncu) — the chain launches it only on request.
+template <bool LAT, int NI, bool SH = false, bool COOP = false>
 __global__ void __launch_bounds__(RR_WARPS * 32)
 knn_rerank_kernel(const RerankParams p) {
   __shared__ int s_surv[RR_WARPS][RR_SURV];
@@ -678,21 +694,24 @@ knn_rerank_kernel(const RerankParams p) {
   WarpTopK top;
   unsigned need = 0;
   bool done = false;
-  if (active) done = rerank_row<LAT, NI, SH>(p, row, lane, s_surv[wib], s_val[wib], q, top, need);
-  if constexpr (LAT) {
-    // rows that lost bank ranges: scanned by the block together.  Whether ANY row of this query
-    // tile did is known from the flags the latency screen wrote (the 4 rows of a block lie in
-    // one 128-row tile, so every warp reads the same words: block-uniform without a barrier) —
-    // the common case skips the scan and its barriers.
-    bool any_lost = true;
+  // COOP: whether ANY row of this query tile lost a bank range is known from the flags the latency
+  // screen wrote (the 4 rows of a block lie in one 128-row tile, so every warp reads the same
+  // words: block-uniform without a barrier).  Loaded first: the round trip hides behind the row.
+  int f0 = 1, f1 = 0;
+  if constexpr (LAT && COOP) {
     if (p.coop_flags != nullptr) {
       const int m_tile = (int)(((int64_t)blockIdx.x * RR_WARPS) / SCR_M);
       const int nflag = p.splits * 4;                         // <= 64
       const int* fl = p.coop_flags + (int64_t)m_tile * nflag;
-      const int f0 = lane < nflag ? __ldcg(fl + lane) : 0;
-      const int f1 = lane + 32 < nflag ? __ldcg(fl + lane + 32) : 0;
-      any_lost = __any_sync(0xffffffffu, (f0 | f1) != 0);
+      f0 = lane < nflag ? __ldcg(fl + lane) : 0;
+      f1 = lane + 32 < nflag ? __ldcg(fl + lane + 32) : 0;
     }
+  }
+  if (active)
+    done = rerank_row<LAT, NI, SH, COOP>(p, row, lane, s_surv[wib], s_val[wib], q, top, need);
+  if constexpr (LAT && COOP) {
+    // the common case skips the scan and its barriers
+    const bool any_lost = __any_sync(0xffffffffu, (f0 | f1) != 0);
     if (any_lost) {
       __shared__ __align__(16) float s_tile[2 * RR_COOP_ROWS * EXB_SCREEN_MAX_DIM];
       __shared__ unsigned s_need[RR_WARPS];

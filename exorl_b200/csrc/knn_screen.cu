@@ -38,6 +38,7 @@
 #include "tmap_host.cuh"
 #include <cuda.h>
 #include <algorithm>
+#include <atomic>
 #include <cuda_fp16.h>
 #include <float.h>
 #include <limits.h>
@@ -1557,15 +1558,15 @@ static bool make_plan(int64_t nq, int64_t nb, int dim, int k, ScreenPlan* pl) {
   return true;
 }
 
-template <bool LAT, bool SH = false>
+template <bool LAT, bool SH = false, bool COOP = false>
 static void launch_rerank(const RerankParams& rp, unsigned grid, int ni, cudaStream_t st) {
   if constexpr (LAT) {   // per-update chain: dependent launch behind the latency screen
     switch (ni) {
-      case 1: launch_pdl(knn_rerank_kernel<LAT, 1, SH>, dim3(grid), dim3(RR_WARPS * 32), 0, st, rp); break;
-      case 2: launch_pdl(knn_rerank_kernel<LAT, 2, SH>, dim3(grid), dim3(RR_WARPS * 32), 0, st, rp); break;
-      case 3: launch_pdl(knn_rerank_kernel<LAT, 3, SH>, dim3(grid), dim3(RR_WARPS * 32), 0, st, rp); break;
-      case 4: launch_pdl(knn_rerank_kernel<LAT, 4, SH>, dim3(grid), dim3(RR_WARPS * 32), 0, st, rp); break;
-      default: launch_pdl(knn_rerank_kernel<LAT, 0, SH>, dim3(grid), dim3(RR_WARPS * 32), 0, st, rp); break;
+      case 1: launch_pdl(knn_rerank_kernel<LAT, 1, SH, COOP>, dim3(grid), dim3(RR_WARPS * 32), 0, st, rp); break;
+      case 2: launch_pdl(knn_rerank_kernel<LAT, 2, SH, COOP>, dim3(grid), dim3(RR_WARPS * 32), 0, st, rp); break;
+      case 3: launch_pdl(knn_rerank_kernel<LAT, 3, SH, COOP>, dim3(grid), dim3(RR_WARPS * 32), 0, st, rp); break;
+      case 4: launch_pdl(knn_rerank_kernel<LAT, 4, SH, COOP>, dim3(grid), dim3(RR_WARPS * 32), 0, st, rp); break;
+      default: launch_pdl(knn_rerank_kernel<LAT, 0, SH, COOP>, dim3(grid), dim3(RR_WARPS * 32), 0, st, rp); break;
     }
     return;
   }
@@ -1577,6 +1578,11 @@ static void launch_rerank(const RerankParams& rp, unsigned grid, int ni, cudaStr
     default: knn_rerank_kernel<LAT, 0, SH><<<grid, RR_WARPS * 32, 0, st>>>(rp); break;
   }
 }
+
+// Per-update chain: how rows that lost bank ranges are recomputed inside the rerank — 0 (default)
+// every row's own warp scans its ranges, 1 the rerank block scans the union together
+// (knn_rerank.cuh:coop_scan).  Process-wide, set through exb_knn_set_per_update_scan.
+static std::atomic<int> g_coop_scan{0};
 
 // Launch with programmatic stream serialization (see common.cuh) when EXB_PDL=1.  Measured on
 // B200 (profiles/r01g_secondary_pdl.jsonl vs _nopdl): C1 39.9 us either way (stream), 36.9 vs
@@ -1808,7 +1814,7 @@ struct ChainKey {
   const void *rms_m, *rms_s, *rms_n, *out_reward;
   int64_t nq, nb;
   int dim, k, idx_base, same, device;
-  int pbe_on, avg, use_rms, use_clip, raw_kth;
+  int pbe_on, avg, use_rms, use_clip, raw_kth, coop;
   float clip;
 };
 
@@ -2067,6 +2073,7 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
     }
     // ONE cooperative kernel (knn_chain.cuh) when the device can hold its grid; else (or with
     // EXB_CHAIN_FUSED=0 in a knob build) the launch chain below
+    const bool coop = g_coop_scan.load(std::memory_order_relaxed) != 0;
     unsigned* gbar = trace_on ? nullptr : chain_gbar_slot();
     auto run_chain = [&](cudaStream_t st) -> int {
     int rc = EXB_OK;
@@ -2123,7 +2130,7 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
     lp.rsel = (k + pl.splits - 1) / pl.splits; lp.bank_max = reinterpret_cast<float*>(w.bsc);
     lp.trace = trace_on ? w.trace : nullptr;
     lp.zero_status = pre ? reinterpret_cast<unsigned long long*>(w.status) : nullptr;
-    lp.coop_flags = w.coop_flags;
+    lp.coop_flags = coop ? w.coop_flags : nullptr;
     dim3 grid((unsigned)pl.m_tiles, (unsigned)pl.splits);
     const bool prof = g_prof.on && g_prof.n < 64;
     if (prof) EXB_CUDA(cudaEventRecord(g_prof.e0[g_prof.n], st));
@@ -2132,7 +2139,8 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
     else EXB_CUDA(launch_pdl(knn_screen_lat_kernel<16>, grid, dim3(LAT_THREADS), pl.smem, st, tq, tb, lp));
     EXB_LAUNCH_CHECK();
     if (prof) EXB_CUDA(cudaEventRecord(g_prof.e1[g_prof.n++], st));
-    launch_rerank<true>(rp, rr_grid, ni, st);
+    if (coop) launch_rerank<true, false, true>(rp, rr_grid, ni, st);
+    else launch_rerank<true>(rp, rr_grid, ni, st);
     EXB_LAUNCH_CHECK();
     if (pbe && pbe->use_rms)
       return launch_pbe_finish(out_dist, nq, k, pbe->avg, 1, pbe->use_clip, pbe->clip,
@@ -2144,7 +2152,7 @@ static int screened_impl(const float* src, int64_t nq, const float* bank, int64_
       memset(&key, 0, sizeof(key));
       key.src = src; key.bank = bank; key.nq = nq; key.nb = nb; key.dim = dim; key.k = k;
       key.idx_base = idx_base; key.same = same; key.out_dist = out_dist; key.out_idx = out_idx;
-      key.ws = workspace;
+      key.ws = workspace; key.coop = coop ? 1 : 0;
       if (pre) { key.pre_b = pre_b->f16; key.pre_q = (same ? pre_b : pre_q)->f16; }
       if (pbe) {
         key.pbe_on = 1; key.avg = pbe->avg; key.use_rms = pbe->use_rms;
@@ -2870,6 +2878,10 @@ extern "C" int exb_proto_reward_f32(const float* z, int64_t nq, const float* que
     if (rc) return rc;
   }
   return exb_take_kth(out_dist, nq, k, out_reward, stream);
+}
+
+extern "C" int exb_knn_set_per_update_scan(int block_cooperative) {
+  return g_coop_scan.exchange(block_cooperative ? 1 : 0, std::memory_order_relaxed);
 }
 
 extern "C" int exb_knn_screened_status_sync(const void* workspace, int32_t host_status[4],

@@ -293,6 +293,14 @@ def set_overflow_policy(policy):
     return prev
 
 
+def set_per_update_scan(block_cooperative):
+    """How the per-update chain recomputes rows the latency screen could not certify: False
+    (default) each row's own warp scans the bank ranges it lost; True the rows of a rerank block
+    scan them together (exb_knn_set_per_update_scan: 273 vs 369 us when every row of a 1024-row
+    batch is undecided, +1.3 us on ordinary batches).  Returns the previous setting."""
+    return bool(_lib.load().exb_knn_set_per_update_scan(1 if block_cooperative else 0))
+
+
 def repair_flagged(source, target, k, dist, idx, idx_base=0):
     """Recompute in place the rows a "flag"-policy call marked with idx[:, 0] == -1 (synchronises).
     Returns the number of rows repaired."""

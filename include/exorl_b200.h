@@ -180,6 +180,15 @@ int exb_knn_screened_status_sync(const void* workspace, int32_t host_status[4],
  * data, [6] MMA issuer total, [7] CTAs that issued MMAs. */
 int exb_debug_trace_sync(const void* workspace, int64_t host_ns[16], exb_stream_t stream);
 
+/* Per-update chain (exb_apt_reward_f32 / exb_proto_reward_f32 / exb_knn_screened_f32 on per-update
+ * sizes): how rows the latency screen could not certify are recomputed inside the rerank kernel.
+ * 0 (default): each row's own warp scans the bank ranges it lost.  1: the rows of a rerank block
+ * scan the union of their ranges together through shared memory — 273 instead of 369 us when
+ * EVERY row of a 1024-row batch is undecided (a whole trajectory as the batch, reps outside the
+ * fp16 range), at 1.3 us more on ordinary batches (C1 32.0 instead of 30.7 us).  Same results.
+ * Process-wide; returns the previous setting. */
+int exb_knn_set_per_update_scan(int block_cooperative);
+
 /* Measurement scripts only: set an A/B switch of the library (EXB_SCREEN_*, EXB_CHAIN_*, EXB_PDL,
  * ...; csrc/common.cuh) before the first call that consults it.  The product never reads the
  * environment. */

@@ -578,13 +578,23 @@ def test_prepared_operands_must_share_one_affine_record():
         xb.knn_topk(xrep.prepare_rep(y), px, 5)
 
 
+@pytest.mark.parametrize("block_scan", [True, False])
 @pytest.mark.parametrize("n,nb,dim,k,scale", [(1024, 1024, 512, 12, 1.0), (300, 700, 50, 5, 1e5),
                                               (257, 1024, 130, 12, 1e6), (640, 640, 64, 3, 1.0)])
-def test_per_update_block_cooperative_scan(n, nb, dim, k, scale):
+def test_per_update_block_cooperative_scan(n, nb, dim, k, scale, block_scan):
     """Every row of a per-update batch undecided (a dense random walk: all pairs inside the fp16
-    margin; or values outside the fp16 range): the rerank blocks scan the bank ranges their rows
-    lost TOGETHER through shared memory (coop_scan).  Result = the exact path's, vector and scalar
-    row layouts, source != bank, ragged sizes."""
+    margin; or values outside the fp16 range).  set_per_update_scan(True): the rerank blocks scan
+    the bank ranges their rows lost TOGETHER through shared memory (coop_scan); False (default):
+    every row's own warp does.  Result = the exact path's either way, vector and scalar row
+    layouts, source != bank, ragged sizes."""
+    prev = xknn.set_per_update_scan(block_scan)
+    try:
+        _check_all_rows_undecided(n, nb, dim, k, scale)
+    finally:
+        xknn.set_per_update_scan(prev)
+
+
+def _check_all_rows_undecided(n, nb, dim, k, scale):
     g = torch.Generator().manual_seed(n + dim)
     if scale == 1.0:
         walk = torch.randn(1, 24, generator=g) + torch.cumsum(
