@@ -69,6 +69,8 @@ SIGNATURES = {
     "exb_pbe_workspace_init": (_c.c_int, [_vp, _sz, _vp]),
     "exb_pbe_reward": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _c.c_int, _f32, _vp, _vp, _vp,
                                   _vp, _vp, _sz, _vp]),
+    "exb_pbe_reward_noalloc": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _c.c_int, _f32, _vp,
+                                          _vp, _vp, _vp, _vp]),
     "exb_pbe_moments": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _vp, _vp, _sz, _vp]),
     "exb_pbe_finish": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _c.c_int, _f32, _vp, _vp, _vp,
                                   _vp, _vp, _vp]),

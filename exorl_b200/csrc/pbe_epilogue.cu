@@ -367,3 +367,80 @@ extern "C" int exb_rnd_reward_f32(const float* prediction, const float* target, 
   EXB_LAUNCH_CHECK();
   return EXB_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// exb_pbe_reward for callers that may not allocate (no counterpart in the reference):
+// the same two launches as exb_pbe_reward's large path
+// (pbe_moments_kernel -> pbe_finish_kernel), with the moments kernel's scratch (ticket word,
+// sums, per-block partials) in a file-scope device array instead of a caller workspace.  Every
+// GPU that loads the library holds the array (PBE_NOALLOC_SCRATCH_BYTES = 16.5 KB) until exit.
+// The host side never hands the array's NAME to a kernel (in host code that is a host-side
+// stand-in, not a device address): the address comes from cudaGetSymbolAddress, once per device
+// with that device current, and is cached here.
+// ------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace {
+
+constexpr int PBE_NOALLOC_MAX_BLOCKS = 1024;   // partial slots; a launch uses <= 4 x SM count
+constexpr int PBE_NOALLOC_MAX_DEVICES = 64;
+constexpr size_t PBE_NOALLOC_SCRATCH_BYTES =
+    256 /*ticket*/ + 256 /*sums*/ + PBE_NOALLOC_MAX_BLOCKS * sizeof(double2);
+
+static __device__ __align__(256) unsigned char g_pbe_noalloc_scratch[PBE_NOALLOC_SCRATCH_BYTES];
+
+// Device address of the array on the CURRENT device (set-up on the first call per device).
+int pbe_noalloc_scratch(unsigned char** out) {
+  static std::mutex mu;
+  static unsigned char* ptrs[PBE_NOALLOC_MAX_DEVICES] = {};
+  int dev = -1;
+  EXB_CUDA(cudaGetDevice(&dev));
+  EXB_CHECK_ARG(dev >= 0 && dev < PBE_NOALLOC_MAX_DEVICES, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    void* p = nullptr;
+    EXB_CUDA(cudaGetSymbolAddress(&p, g_pbe_noalloc_scratch));
+    EXB_CHECK_ARG(p != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+    ptrs[dev] = static_cast<unsigned char*>(p);
+  }
+  *out = ptrs[dev];
+  return EXB_OK;
+}
+
+}  // namespace
+
+extern "C" int exb_pbe_reward_noalloc(const float* knn_dist, int64_t nq, int k, int avg,
+                                      int use_rms, float clip, float* rms_m, float* rms_s,
+                                      double* rms_n, float* out_reward, exb_stream_t stream) {
+  EXB_CHECK_ARG(knn_dist && out_reward && nq > 0 && k >= 1, "bad arguments");
+  EXB_CHECK_ARG(!use_rms || (rms_m && rms_s && rms_n),
+                "use_rms needs the RMS state pointers");
+  EXB_CHECK_ARG(nq <= EXB_PBE_NOALLOC_MAX_VALUES / k,
+                "exb_pbe_reward_noalloc: nq * k = %lld x %d exceeds the static scratch's limit of "
+                "%lld values (use exb_pbe_reward with a caller workspace)",
+                (long long)nq, k, (long long)EXB_PBE_NOALLOC_MAX_VALUES);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int use_clip = clip >= 0.0f;
+  if (use_rms) {
+    unsigned char* scratch = nullptr;
+    int rc = pbe_noalloc_scratch(&scratch);
+    if (rc) return rc;
+    const int64_t count = avg ? nq * k : nq;
+    const int blocks = moments_blocks(count);
+    EXB_CHECK_ARG(blocks <= PBE_NOALLOC_MAX_BLOCKS, "unexpected SM count");
+    unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
+    double* sums = reinterpret_cast<double*>(scratch + 256);
+    double2* partials = reinterpret_cast<double2*>(scratch + 512);
+    // the array keeps the last call's contents: the ticket must start at zero (a call that
+    // was aborted mid-kernel would otherwise poison every later one)
+    EXB_CUDA(cudaMemsetAsync(ticket, 0, 256, st));
+    RmsParams p{rms_m, rms_s, rms_n};
+    pbe_moments_kernel<<<blocks, PBE_THREADS, 0, st>>>(knn_dist, count, k, avg, partials, ticket,
+                                                       sums, 1, p);
+    EXB_LAUNCH_CHECK();
+  }
+  pbe_finish_kernel<<<(unsigned)((nq + PBE_THREADS - 1) / PBE_THREADS), PBE_THREADS, 0, st>>>(
+      knn_dist, nq, k, avg, use_rms, use_clip, clip, rms_m, out_reward);
+  EXB_LAUNCH_CHECK();
+  return EXB_OK;
+}

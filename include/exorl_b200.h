@@ -330,6 +330,24 @@ int exb_pbe_finish(const float* knn_dist, int64_t nq, int k, int avg, int use_rm
 int exb_rms_update(const float* x, int64_t n, float* rms_m, float* rms_s, double* rms_n, void* workspace,
                    size_t workspace_bytes, exb_stream_t stream);
 
+/* exb_pbe_reward without a workspace argument and without any allocation.  This entry point has
+ * no counterpart in the reference: it was added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, results and RMS state convention as exb_pbe_reward;
+ * the moments kernel's scratch (ticket word, sums, per-block partials) lives in a 16.5 KB
+ * file-scope device array that every GPU loading the library holds until exit.  Limit:
+ * nq * k <= EXB_PBE_NOALLOC_MAX_VALUES, beyond it the call fails with EXB_EINVAL and a message
+ * in exb_last_error().  The call makes no cudaMalloc / cudaFree / allocating library call; the
+ * first call on each device also looks up the array's address (cudaGetSymbolAddress), so make
+ * that first call outside stream capture.  All calls on a device share the one array, which
+ * keeps the previous call's contents (the ticket word is cleared on `stream` by every call):
+ * calls that overlap on the GPU — different streams, or graphs replayed concurrently — race on
+ * it; serialise them or use exb_pbe_reward with one workspace per stream. */
+#define EXB_PBE_NOALLOC_MAX_VALUES (1LL << 24)
+int exb_pbe_reward_noalloc(const float* knn_dist, int64_t nq, int k, int avg, int use_rms,
+                           float clip, float* rms_m, float* rms_s, double* rms_n,
+                           float* out_reward /* [nq] */, exb_stream_t stream);
+
 /* --------------------------------------------------------------------------------------------
  * PBE.__call__ as ONE call: replaces utils/utils.py:289-319 end to end (distance + topk, RMS
  * update, divide by the updated mean, clip, mean over k, log(1 + r)); compute_apt_reward(source,
