@@ -405,7 +405,9 @@ def run_ours(a, rank, world, local_rank):
         # symmetric path (1 GPU): sample gather, [colstats x2, reduce, affine, prep x2, screen,
         # rerank, exact, merge] of the pre-pass, [colstats, reduce, affine, prep, threshold, screen,
         # scatter, rerank, exact, merge], moments, finish
-        launches_per_step = (23 if sym else 10) if world == 1 else (25 if sym else 14)
+        peer = sym and xknn.sym_last.get("exchange") == "peer_memory"   # + the routing-table kernel
+        launches_per_step = ((23 if sym else 10) if world == 1 else
+                             ((26 if peer else 25) if sym else 14))
         out = {
             "metric": METRIC, "value": a.n * a.steps / (ms * 1e-3), "unit": UNIT,
             "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms / a.steps,
@@ -416,6 +418,9 @@ def run_ours(a, rank, world, local_rank):
             "config": {"workload": workload(a), "n": a.n, "dim": a.dim, "k": a.k,
                        "parallelism": (f"{world} GPU(s), exchange={a.exchange}" + (
                            "" if world == 1 else
+                           " (symmetric screen: every unordered tile pair on one rank, transposed "
+                           "hits appended to the owner rank's buffer over NVLink peer memory "
+                           "inside the screen kernel)" if peer else
                            " (symmetric screen: every unordered tile pair on one rank, transposed "
                            "hits exchanged all-to-all)" if sym else
                            " (query blocks over the ranks, whole bank on every rank)"

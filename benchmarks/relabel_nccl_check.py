@@ -26,6 +26,8 @@ def main():
     ap.add_argument("--k", type=int, default=12)
     ap.add_argument("--sym-min-rows", type=int, default=1024,
                     help="knn.SYM_MIN_ROWS for the 'sym' legs (the symmetric screen over the ranks)")
+    ap.add_argument("--allow-a2a", action="store_true",
+                    help="do not insist that the 'sym' legs used the peer-memory exchange")
     a = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
@@ -49,17 +51,26 @@ def main():
     from exorl_b200 import relabel as xrel
     # "balanced" runs three times so that the rate-proportional query blocks (QueryBalance) have
     # moved away from the equal split by the last run; "from_host" is the end-to-end pipeline
-    for exchange in ("sym", "sym", "queries", "balanced", "balanced", "balanced", "from_host",
+    # "sym": the symmetric screen over the ranks with the hit exchange inside the kernel (NVLink
+    # peer memory), twice (buffers reused); "sym_a2a": the same with the all-to-all exchange
+    for exchange in ("sym", "sym", "sym_a2a", "queries", "balanced", "balanced", "balanced", "from_host",
                      "prepared", "lists", "auto", "all_to_all", "all_gather"):
         rms = xb.RMS(dev)
-        xknn.SYM_ENABLED = exchange == "sym"
+        xknn.SYM_ENABLED = exchange in ("sym", "sym_a2a")
         xknn.SYM_MIN_ROWS = a.sym_min_rows
-        if exchange == "sym":
+        if exchange in ("sym", "sym_a2a"):
             xknn.sym_last.clear()
+            xrel.SYM_PEER_MEMORY = exchange == "sym"
             out = xb.relabel_apt_reward(rep, args, rms=rms, exchange="queries", mode="screened",
                                         return_knn=True)
+            xrel.SYM_PEER_MEMORY = True
             assert xknn.sym_last.get("world") == world, xknn.sym_last
             assert "fell_back_to_full_screen" not in xknn.sym_last, xknn.sym_last
+            want = "peer_memory" if exchange == "sym" and not a.allow_a2a else None
+            assert want is None or xknn.sym_last.get("exchange") == want, xknn.sym_last
+            if rank == 0:
+                print(f"[nccl check] symmetric exchange: {xknn.sym_last.get('exchange')}",
+                      flush=True)
         elif exchange == "from_host":
             out = xb.relabel_apt_reward_from_host(rep_host, args, rms=rms, return_knn=True)
         elif exchange == "prepared":
@@ -78,7 +89,7 @@ def main():
         assert rms.n == rms0.n
         if exchange == "all_gather":            # every rank holds all rows
             lo, hi = 0, a.n
-        elif exchange in ("sym", "queries", "balanced", "auto", "prepared", "from_host"):
+        elif exchange in ("sym", "sym_a2a", "queries", "balanced", "auto", "prepared", "from_host"):
             lo, hi = xrel.last_query_block["lo"], xrel.last_query_block["hi"]   # balanced block
         else:                                    # rank r finalised query block r
             lo, hi = xrel.shard_bounds(a.n, world, rank)

@@ -37,6 +37,8 @@ class SymHits(_c.Structure):
                 ("count", _c.c_void_p), ("capacity", _c.c_longlong)]
 
 
+SYM_MAX_RANKS = 8      # EXB_SYM_MAX_RANKS
+
 SIGNATURES = {
     "exb_abi_version": (_c.c_int, []),
     "exb_last_error": (_c.c_char_p, []),
@@ -113,6 +115,17 @@ SIGNATURES = {
                                           _c.c_int, _vp, _sz, _c.POINTER(SymHits), _vp]),
     "exb_knn_sym_scatter": (_c.c_int, [_i64, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _vp, _vp,
                                        _vp, _i64, _vp, _vp]),
+    "exb_knn_sym_screen_peer_f32": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _vp, _i64, _c.c_int,
+                                               _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int,
+                                               _c.c_int, _c.c_int, _c.POINTER(SymHits),
+                                               _c.POINTER(_c.c_int32), _vp, _sz, _vp]),
+    "exb_knn_sym_scatter_hits": (_c.c_int, [_i64, _c.c_int, _c.c_int, _c.c_int, _c.c_int,
+                                            _c.POINTER(SymHits), _vp, _vp]),
+    "exb_peer_buffer_alloc": (_c.c_int, [_sz, _c.POINTER(_vp), _c.c_char_p]),
+    "exb_peer_buffer_open": (_c.c_int, [_c.c_char_p, _c.POINTER(_vp)]),
+    "exb_peer_buffer_close": (_c.c_int, [_vp]),
+    "exb_peer_buffer_free": (_c.c_int, [_vp]),
+    "exb_peer_buffer_clear": (_c.c_int, [_vp, _sz, _vp]),
     "exb_knn_sym_rerank_f32": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _i32, _c.c_int, _c.c_int,
                                           _i64, _i64, _vp, _vp, _vp, _vp]),
     "exb_knn_colstats_workspace_bytes": (_sz, [_i64, _c.c_int]),

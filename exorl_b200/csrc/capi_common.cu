@@ -60,3 +60,53 @@ extern "C" int exb_debug_knob_set(const char* name, int value) {
   exb::g_knobs[exb::g_n_knobs++].value = value;
   return EXB_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// Peer-visible device buffers (multi-GPU symmetric screen, knn_screen.cu): plain cudaMalloc
+// memory exported through CUDA IPC, so that the screen kernel of ANOTHER rank's process can
+// append the hits it finds for this rank's rows straight into this rank's memory over NVLink.
+// (Memory of torch's caching allocator cannot be used: its IPC export maps the whole allocator
+// block and kernel stores through that mapping faulted on the B200 boxes.)
+// ------------------------------------------------------------------------------------------
+extern "C" int exb_peer_buffer_alloc(size_t bytes, void** ptr, unsigned char* handle64) {
+  EXB_CHECK_ARG(bytes > 0 && ptr && handle64, "bad arguments");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  void* p = nullptr;
+  EXB_CUDA(cudaMalloc(&p, bytes));
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    exb::set_error("cudaIpcGetMemHandle -> %s", cudaGetErrorString(e));
+    return EXB_ECUDA;
+  }
+  memcpy(handle64, &h, 64);
+  *ptr = p;
+  return EXB_OK;
+}
+
+extern "C" int exb_peer_buffer_open(const unsigned char* handle64, void** ptr) {
+  EXB_CHECK_ARG(handle64 && ptr, "bad arguments");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  void* p = nullptr;
+  EXB_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  *ptr = p;
+  return EXB_OK;
+}
+
+extern "C" int exb_peer_buffer_close(void* ptr) {
+  if (ptr) EXB_CUDA(cudaIpcCloseMemHandle(ptr));
+  return EXB_OK;
+}
+
+extern "C" int exb_peer_buffer_free(void* ptr) {
+  if (ptr) EXB_CUDA(cudaFree(ptr));
+  return EXB_OK;
+}
+
+extern "C" int exb_peer_buffer_clear(void* ptr, size_t bytes, exb_stream_t stream) {
+  EXB_CHECK_ARG(ptr && bytes > 0, "bad arguments");
+  EXB_CUDA(cudaMemsetAsync(ptr, 0, bytes, (cudaStream_t)stream));
+  return EXB_OK;
+}

@@ -361,6 +361,7 @@ affine_kernel(const float* __restrict__ stats, double n_rows, int dim, float* __
 // ------------------------------------------------------------------------------------------
 // screening kernel
 // ------------------------------------------------------------------------------------------
+struct SymPeerTable;   // multi-GPU symmetric screen, below
 struct ScreenParams {
   const float* ha;        // [nq] query half norms
   const float* ea;        // [nq] query rounding errors
@@ -414,7 +415,27 @@ struct ScreenParams {
   int* tq_src;
   unsigned long long* tq_count;   // entries appended (may exceed tq_cap: the excess is dropped)
   long long tq_cap;
+  // Several GPUs with peer-mapped memory (null = the one buffer above): the hits found for the
+  // rows of bank tile t are appended to the buffer of the rank that OWNS those rows, straight
+  // over NVLink — the exchange step of the multi-GPU relabel happens inside this kernel.
+  const SymPeerTable* sym_peers;
 };
+
+// Device-resident routing table of the multi-GPU symmetric screen: rank r owns the bank tiles
+// [tile_lo[r], tile_lo[r + 1]); target/val/src/count/cap describe ITS append buffer as mapped in
+// this process (CUDA IPC, capi_common.cu: exb_peer_buffer_*; the own rank's entry is local).
+struct SymPeerTable {
+  int ranks, pad;
+  int tile_lo[EXB_SYM_MAX_RANKS + 2];
+  int* target[EXB_SYM_MAX_RANKS];
+  float* val[EXB_SYM_MAX_RANKS];
+  int* src[EXB_SYM_MAX_RANKS];
+  unsigned long long* count[EXB_SYM_MAX_RANKS];
+  long long cap[EXB_SYM_MAX_RANKS];
+};
+__global__ void sym_peer_table_kernel(const SymPeerTable t, SymPeerTable* out) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) *out = t;
+}
 
 // Per-row candidate state of one epilogue thread.  The k best scores seen so far are kept sorted
 // (descending) in registers by a branch-free min/max chain, so the running k-th best `tk` costs no
@@ -766,12 +787,15 @@ struct SymQueue {
   int* g_target; float* g_val; int* g_src;              // the global append buffer
   unsigned long long* g_count;
   long long g_cap;
+  bool sys;                                             // the buffer may be another GPU's memory
 };
 __device__ __forceinline__ void sym_queue_flush(const SymQueue& q, int& qn, int lane) {
   __syncwarp();
   if (qn > 0) {
     unsigned long long base = 0;
-    if (lane == 0) base = atomicAdd(q.g_count, (unsigned long long)qn);
+    if (lane == 0)
+      base = q.sys ? atomicAdd_system(q.g_count, (unsigned long long)qn)
+                   : atomicAdd(q.g_count, (unsigned long long)qn);
     base = __shfl_sync(0xffffffffu, base, 0);
     for (int e = lane; e < qn; e += 32) {
       const long long at = (long long)base + e;
@@ -1086,7 +1110,11 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
       sq.scratch = reinterpret_cast<float*>(qb + SYM_QCAP * 12);
       sq.g_target = p.tq_target; sq.g_val = p.tq_val; sq.g_src = p.tq_src;
       sq.g_count = p.tq_count; sq.g_cap = p.tq_cap;
+      sq.sys = false;
     }
+    // peer routing: [dest_lo, dest_hi) = bank tiles of the rank the queue currently drains to
+    const SymPeerTable* pt = p.sym_peers;
+    int dest_lo = 0, dest_hi = pt != nullptr ? 0 : 0x7fffffff;
     int qn = 0;                                   // queued transposed hits (warp-uniform)
     // rows past nq: unreachable thresholds in both directions
     SymRow me;
@@ -1120,6 +1148,15 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
       const int t = tile_seq(jj);
       const int as = jj & 1;
       const bool diag = jj == 0;                 // own tile: the direct test covers both orders
+      if (t < dest_lo || t >= dest_hi) {         // (peer table only) rows of another rank from here
+        sym_queue_flush(sq, qn, lane);
+        int r = 0;
+        while (r + 1 < pt->ranks && t >= pt->tile_lo[r + 1]) ++r;
+        dest_lo = pt->tile_lo[r]; dest_hi = pt->tile_lo[r + 1];
+        sq.g_target = pt->target[r]; sq.g_val = pt->val[r]; sq.g_src = pt->src[r];
+        sq.g_count = pt->count[r]; sq.g_cap = pt->cap[r];
+        sq.sys = true;
+      }
       __syncwarp();
       reinterpret_cast<float4*>(hn)[lane] = hnext;
       reinterpret_cast<float4*>(tk)[lane] = tnext;
@@ -2343,6 +2380,7 @@ struct SymWs {
   int *dlog_idx, *tq_target, *tq_src, *ridx, *dlog_cnt, *rcnt, *fb_rows, *fb_idx;
   unsigned long long* tq_count;
   long long tq_cap;
+  SymPeerTable* peers;
 };
 
 static size_t carve_sym(void* ws, int64_t n, const SymPlan& pl, int k, int log_cap, int rcap,
@@ -2375,6 +2413,7 @@ static size_t carve_sym(void* ws, int64_t n, const SymPlan& pl, int k, int log_c
   o->fb_rows = cv.take<int>(pl.fb_cap);
   o->fb_d2 = cv.take<float>((size_t)pl.fb_cap * pl.fb_splits * k);
   o->fb_idx = cv.take<int>((size_t)pl.fb_cap * pl.fb_splits * k);
+  o->peers = cv.take<SymPeerTable>(1);
   return cv.off + 256;
 }
 
@@ -2388,6 +2427,7 @@ extern "C" size_t exb_knn_sym_workspace_bytes(int64_t n, int dim, int k, int log
 
 struct SymSpan {            // which tile pairs a launch takes (ScreenParams::sym_*)
   int pair_lo, pair_hi, span_end, mid_pair, extra;
+  const SymPeerTable* peers;   // host copy of the routing table, or null (one append buffer)
 };
 
 // Phase 1: operand, thresholds, symmetric screen of the pairs of `sp_`; leaves the direct logs
@@ -2449,6 +2489,11 @@ static int sym_screen_phase(const float* rep, int64_t n, int dim, int k, const f
   sp.dlog_cnt = w.dlog_cnt; sp.log_cap = log_cap;
   sp.tq_target = w.tq_target; sp.tq_val = w.tq_val; sp.tq_src = w.tq_src;
   sp.tq_count = w.tq_count; sp.tq_cap = w.tq_cap;
+  if (span.peers != nullptr) {
+    sym_peer_table_kernel<<<1, 32, 0, st>>>(*span.peers, w.peers);
+    EXB_LAUNCH_CHECK();
+    sp.sym_peers = w.peers;
+  }
   {
     const bool prof = g_prof.on && g_prof.n < 64;
     if (prof) EXB_CUDA(cudaEventRecord(g_prof.e0[g_prof.n], st));
@@ -2522,7 +2567,7 @@ extern "C" int exb_knn_sym_f32(const float* rep, int64_t n, int dim, int k, int3
   SymPlan pl;
   SymWs w;
   const int tiles = (int)((n + SCR_N - 1) / SCR_N);
-  const SymSpan span = {0, tiles, tiles, tiles, 0};
+  const SymSpan span = {0, tiles, tiles, tiles, 0, nullptr};
   int rc = sym_screen_phase(rep, n, dim, k, d_sample, d_stride, log_cap, recv_cap, span,
                             workspace, workspace_bytes, st, &pl, &w);
   if (rc) return rc;
@@ -2549,12 +2594,69 @@ extern "C" int exb_knn_sym_screen_f32(const float* rep, int64_t n, int dim, int 
   EXB_CHECK_ARG(rep && d_sample && workspace && hits, "null pointer");
   SymPlan pl;
   SymWs w;
-  const SymSpan span = {pair_lo, pair_hi, span_end, mid_pair, extra_tiles};
+  const SymSpan span = {pair_lo, pair_hi, span_end, mid_pair, extra_tiles, nullptr};
   const int rc = sym_screen_phase(rep, n, dim, k, d_sample, d_stride, log_cap, recv_cap, span,
                                   workspace, workspace_bytes, (cudaStream_t)stream, &pl, &w);
   if (rc) return rc;
   hits->target = w.tq_target; hits->val = w.tq_val; hits->src = w.tq_src;
   hits->count = w.tq_count; hits->capacity = w.tq_cap;
+  return EXB_OK;
+}
+
+// Peer-memory variant: the kernel appends every hit to the buffer of the rank that owns its query
+// row (peer_hits[r], mapped into this process), so no exchange step follows — after a barrier
+// across the ranks every rank scatters ITS buffer (exb_knn_sym_scatter_hits) and reranks.
+extern "C" int exb_knn_sym_screen_peer_f32(const float* rep, int64_t n, int dim, int k,
+                                           const float* d_sample, int64_t d_stride, int log_cap,
+                                           int recv_cap, int pair_lo, int pair_hi, int span_end,
+                                           int mid_pair, int extra_tiles, int n_ranks,
+                                           const exb_sym_hits* peer_hits, const int32_t* tile_lo,
+                                           void* workspace, size_t workspace_bytes,
+                                           exb_stream_t stream) {
+  EXB_CHECK_ARG(rep && d_sample && workspace && peer_hits && tile_lo, "null pointer");
+  EXB_CHECK_ARG(n_ranks >= 1 && n_ranks <= EXB_SYM_MAX_RANKS, "1 <= n_ranks <= %d",
+                EXB_SYM_MAX_RANKS);
+  SymPeerTable tbl;
+  memset(&tbl, 0, sizeof(tbl));
+  tbl.ranks = n_ranks;
+  for (int r = 0; r <= n_ranks; ++r) {
+    EXB_CHECK_ARG(tile_lo[r] >= 0 && (r == 0 || tile_lo[r] >= tile_lo[r - 1]),
+                  "tile_lo must be non-decreasing");
+    tbl.tile_lo[r] = tile_lo[r];
+  }
+  EXB_CHECK_ARG(tile_lo[0] == 0 && (int64_t)tile_lo[n_ranks] * SCR_N >= n,
+                "tile_lo must cover tiles [0, ceil(n / %d))", SCR_N);
+  for (int r = 0; r < n_ranks; ++r) {
+    const exb_sym_hits& h = peer_hits[r];
+    EXB_CHECK_ARG(h.target && h.val && h.src && h.count && h.capacity > 0,
+                  "peer_hits[%d] incomplete", r);
+    tbl.target[r] = h.target; tbl.val[r] = h.val; tbl.src[r] = h.src;
+    tbl.count[r] = h.count; tbl.cap[r] = h.capacity;
+  }
+  SymPlan pl;
+  SymWs w;
+  const SymSpan span = {pair_lo, pair_hi, span_end, mid_pair, extra_tiles, &tbl};
+  return sym_screen_phase(rep, n, dim, k, d_sample, d_stride, log_cap, recv_cap, span, workspace,
+                          workspace_bytes, (cudaStream_t)stream, &pl, &w);
+}
+
+// Scatter of a hit buffer whose entry count lives on the device (this rank's peer-visible
+// buffer after the barrier): count > capacity sets status flag bit 1 (invalid pass).
+extern "C" int exb_knn_sym_scatter_hits(int64_t n, int dim, int k, int log_cap, int recv_cap,
+                                        const exb_sym_hits* hits, void* workspace,
+                                        exb_stream_t stream) {
+  EXB_CHECK_ARG(workspace && hits && hits->target && hits->val && hits->src && hits->count &&
+                hits->capacity > 0, "bad arguments");
+  SymPlan pl;
+  SymWs w;
+  EXB_CHECK_ARG(sym_plan(n, dim, k, &pl), "bad sizes");
+  carve_sym(workspace, n, pl, k, log_cap, recv_cap, &w);
+  SymLists sl = sym_lists(w, log_cap, recv_cap);
+  sl.tq_count = hits->count;
+  sl.tq_cap = hits->capacity;
+  sym_scatter_kernel<<<148 * 8, 256, 0, (cudaStream_t)stream>>>(sl, hits->target, hits->val,
+                                                                 hits->src, -1, w.status);
+  EXB_LAUNCH_CHECK();
   return EXB_OK;
 }
 

@@ -341,6 +341,12 @@ def _finish_block(d_mine, i_mine, n, lo, hi, in_split, world, k, avg, use_rms, c
 # ------------------------------------------------------------------------------------------
 # Symmetric screen over several GPUs (csrc/knn_sym.cuh, include/exorl_b200.h "three calls")
 # ------------------------------------------------------------------------------------------
+# Exchange of the symmetric screen's transposed hits between the ranks: True = inside the screen
+# kernel over NVLink peer memory (exb_knn_sym_screen_peer_f32), False = counting partition +
+# all_to_all_single after it.  Falls back to the latter when peer mapping is refused.
+SYM_PEER_MEMORY = True
+
+
 def sym_tile_blocks(n, world, tile=256):
     """Tile-aligned row blocks: rank r owns the query tile pairs [tb[r], tb[r + 1]) (tiles of
     `tile` rows) = the rows [min(n, tile * tb[r]), min(n, tile * tb[r + 1]))."""
@@ -425,15 +431,98 @@ class _CudaSymBackend:
             return (view(hits.target, torch.int32), view(hits.val, torch.float32),
                     view(hits.src, torch.int32)), over
 
+    # ---- peer-memory exchange: the screen kernel appends every hit straight into the buffer of
+    # the rank that owns its query row (NVLink stores), so no all-to-all follows the screen
+    _peer = {}     # device index -> {"cap", "own" (ptr), "handle", "mapped" {rank: ptr}, "hits"}
+
+    @staticmethod
+    def _hits_at(base, cap):
+        """exb_sym_hits of a peer buffer: count word, then target / val / src arrays of `cap`."""
+        return _lib.SymHits(base + 256, base + 256 + 4 * cap, base + 256 + 8 * cap, base, cap)
+
+    def open_peers(self, group, world, rank, rows_max):
+        """Make sure every rank owns a peer-visible hit buffer for `rows_max` rows and that all
+        are mapped here; zero the own count on the current stream.  The capacity is the same
+        function of (n, world, recv_cap) on every rank, so all ranks (re)allocate together and
+        the handle exchange (all_gather_object) is collective.  False when the hardware or the
+        driver refuses peer mapping (the caller falls back to the all-to-all path)."""
+        lib, dev = self.lib, self.dev
+        cap = -(-int(rows_max * (self.recv_cap // 3 + 16)) // 64) * 64
+        st = self._peer.get(dev.index)
+        with torch.cuda.device(dev):
+            if st is None or st["cap"] < cap or st["world"] != world:
+                if st is not None:
+                    torch.cuda.synchronize(dev)
+                    for q in st["mapped"].values():
+                        lib.exb_peer_buffer_close(q)
+                    dist.barrier(group=group)                    # every peer unmapped
+                    lib.exb_peer_buffer_free(st["own"])
+                    self._peer.pop(dev.index)
+                own = ctypes.c_void_p()
+                handle = ctypes.create_string_buffer(64)
+                rc = lib.exb_peer_buffer_alloc(256 + 12 * cap, ctypes.byref(own), handle)
+                mine = (rc, handle.raw, cap)
+                everyone = [None] * world
+                dist.all_gather_object(everyone, mine, group=group)
+                ok = all(e[0] == 0 and e[2] == cap for e in everyone)
+                mapped = {}
+                if ok:
+                    for r, (_, h, _) in enumerate(everyone):
+                        if r == rank:
+                            continue
+                        q = ctypes.c_void_p()
+                        if lib.exb_peer_buffer_open(h, ctypes.byref(q)) != 0:
+                            ok = False
+                            break
+                        mapped[r] = q.value
+                flag = [None] * world
+                dist.all_gather_object(flag, ok, group=group)
+                if not all(flag):
+                    for q in mapped.values():
+                        lib.exb_peer_buffer_close(q)
+                    dist.barrier(group=group)
+                    if rc == 0:
+                        lib.exb_peer_buffer_free(own)
+                    return False
+                hits = (_lib.SymHits * world)()
+                for r in range(world):
+                    hits[r] = self._hits_at(own.value if r == rank else mapped[r], cap)
+                st = {"cap": cap, "world": world, "own": own.value, "mapped": mapped,
+                      "hits": hits, "rank": rank}
+                self._peer[dev.index] = st
+            _lib.check(lib.exb_peer_buffer_clear(st["own"], 256, _lib.stream_ptr(dev)))
+        self.peer = st
+        return True
+
+    def screen_peer(self, d_all, span, tile_lo):
+        """The screen with the exchange inside the kernel; asynchronous."""
+        lib, dev, st = self.lib, self.dev, self.peer
+        pair_lo, pair_hi, span_end, mid, extra = span
+        with torch.cuda.device(dev):
+            self.ws, _ = _lib.Workspace.get(dev, "knn_sym", self.need)
+            ws = self.ws
+            tl = (ctypes.c_int32 * len(tile_lo))(*tile_lo)
+            _lib.check(lib.exb_knn_sym_screen_peer_f32(
+                _lib.ptr(self.rep), self.n, self.dim, self.k, _lib.ptr(d_all), 1, self.log_cap,
+                self.recv_cap, pair_lo, pair_hi, span_end, mid, extra, st["world"], st["hits"],
+                tl, _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+
     def scatter_rerank(self, r_t, r_v, r_s, lo, hi):
         """Received hits into the rows' lists, then the exact top-k of rows [lo, hi).
+        r_t None: the hits are this rank's peer buffer (count on the device).
         -> (dist, idx, undecided_rows, status_flags)"""
         lib, dev, k = self.lib, self.dev, self.k
         with torch.cuda.device(dev):
-            _lib.check(lib.exb_knn_sym_scatter(self.n, self.dim, k, self.log_cap, self.recv_cap,
-                                               _lib.ptr(r_t), _lib.ptr(r_v), _lib.ptr(r_s),
-                                               r_t.numel(), _lib.ptr(self.ws),
-                                               _lib.stream_ptr(dev)))
+            if r_t is None:
+                st = self.peer
+                _lib.check(lib.exb_knn_sym_scatter_hits(
+                    self.n, self.dim, k, self.log_cap, self.recv_cap,
+                    ctypes.byref(st["hits"][st["rank"]]), _lib.ptr(self.ws), _lib.stream_ptr(dev)))
+            else:
+                _lib.check(lib.exb_knn_sym_scatter(self.n, self.dim, k, self.log_cap,
+                                                   self.recv_cap, _lib.ptr(r_t), _lib.ptr(r_v),
+                                                   _lib.ptr(r_s), r_t.numel(), _lib.ptr(self.ws),
+                                                   _lib.stream_ptr(dev)))
             d_mine = torch.empty(hi - lo, k, dtype=torch.float32, device=dev)
             i_mine = torch.empty(hi - lo, k, dtype=torch.int32, device=dev)
             _lib.check(lib.exb_knn_sym_rerank_f32(
@@ -450,8 +539,11 @@ class _CudaSymBackend:
 def _sym_queries_knn(rep, k, world, rank, group, tm, backend=None):
     """kNN of this rank's (tile-aligned) query block through the symmetric screen spread over
     the ranks.  Returns (dist, idx, row_bounds) or None when any rank reports the pass invalid
-    (the caller then runs the full screen).  Collectives: d_sample all-reduce (4N bytes), hit
-    counts all-to-all, the hits themselves all-to-all (12 bytes each, ~ k N^2 / (2 S world))."""
+    (the caller then runs the full screen).  Collectives: d_sample all-reduce (4N bytes); the
+    hits (12 bytes each, ~ k N^2 / (2 S world) per rank) travel INSIDE the screen kernel — it
+    appends each one to the owner rank's peer-mapped buffer over NVLink — with two one-word
+    all-reduces as barriers around it; without peer memory (SYM_PEER_MEMORY off, mapping
+    refused, CPU stand-in): hit counts all-to-all + the hits all-to-all after a partition."""
     from . import knn as xknn
     be = backend if backend is not None else _CudaSymBackend(rep, k)
     n = rep.size(0)
@@ -460,15 +552,36 @@ def _sym_queries_knn(rep, k, world, rank, group, tm, backend=None):
     lo, hi = rb[rank], rb[rank + 1]
     stride = max(1, n // be.sample_rows())
     sample = rep[::stride].contiguous()
-    d_all = torch.zeros(n, dtype=torch.float32, device=dev)
-    d_all[lo:hi] = be.sample_distances(lo, hi, sample)
-    dist.all_reduce(d_all, op=dist.ReduceOp.SUM, group=group)
-    tm("sym_sample_prepass")
     fits = torch.tensor([1 if be.room(1.3 * k * n / sample.size(0)) else 0], device=dev)
     dist.all_reduce(fits, op=dist.ReduceOp.MIN, group=group)          # all ranks or none
     if not int(fits.item()):
         xknn.sym_last.update(n=n, no_room=True)
         return None
+    # the own hit buffer is cleared on this stream BEFORE the all-reduce below, which therefore
+    # doubles as the barrier "nobody appends to a buffer that is not cleared yet"
+    peer = (SYM_PEER_MEMORY and hasattr(be, "open_peers") and world <= _lib.SYM_MAX_RANKS
+            and be.open_peers(group, world, rank, max(rb[r + 1] - rb[r] for r in range(world))))
+    d_all = torch.zeros(n, dtype=torch.float32, device=dev)
+    d_all[lo:hi] = be.sample_distances(lo, hi, sample)
+    dist.all_reduce(d_all, op=dist.ReduceOp.SUM, group=group)
+    tm("sym_sample_prepass")
+    if peer:
+        be.screen_peer(d_all, sym_span(tb, world, rank), tb)
+        bad = torch.zeros(1, dtype=torch.int64, device=dev)
+        dist.all_reduce(bad, op=dist.ReduceOp.MAX, group=group)   # barrier: every screen is done
+        tm("sym_screen")
+        d_mine, i_mine, und, status = be.scatter_rerank(None, None, None, lo, hi)
+        bad[0] = 1 if (status & 2) else 0
+        dist.all_reduce(bad, op=dist.ReduceOp.MAX, group=group)
+        xknn.sym_last.update(n=n, sample_rows=sample.size(0), undecided=und, status=status,
+                             world=world, exchange="peer_memory")
+        if int(bad.item()):
+            xknn.sym_last["fell_back_to_full_screen"] = True
+            return None
+        if status & 1:
+            be.repair(lo, hi, d_mine, i_mine)
+        tm("sym_rerank")
+        return d_mine, i_mine, rb
     (tgt, val, src), over = be.screen(d_all, sym_span(tb, world, rank))
     tm("sym_screen")
     bad = torch.tensor([1 if over else 0], device=dev)
@@ -492,7 +605,7 @@ def _sym_queries_knn(rep, k, world, rank, group, tm, backend=None):
     bad[0] |= 1 if (status & 2) else 0
     dist.all_reduce(bad, op=dist.ReduceOp.MAX, group=group)
     xknn.sym_last.update(n=n, sample_rows=sample.size(0), undecided=und, status=status,
-                         world=world, hits_sent=int(tgt.numel()))
+                         world=world, hits_sent=int(tgt.numel()), exchange="all_to_all")
     if int(bad.item()):
         xknn.sym_last["fell_back_to_full_screen"] = True
         return None

@@ -147,6 +147,38 @@ int exb_knn_sym_screen_f32(const float* rep, int64_t n, int dim, int k, const fl
 int exb_knn_sym_scatter(int64_t n, int dim, int k, int log_cap, int recv_cap,
                         const int32_t* target, const float* val, const int32_t* src,
                         int64_t n_hits, void* workspace, exb_stream_t stream);
+
+/* The exchange step inside the screen kernel (NVLink peer memory).  Every rank owns a
+ * peer-visible hit buffer (exb_peer_buffer_alloc below, opened by the other ranks' processes with
+ * exb_peer_buffer_open) described by an exb_sym_hits; peer_hits[r] (host array, n_ranks entries,
+ * pointers as mapped in THIS process) is rank r's, tile_lo[r] .. tile_lo[r + 1] (host array,
+ * n_ranks + 1 entries, tiles of 256 rows) the bank tiles whose rows rank r owns.  The kernel
+ * appends each transposed hit straight to the buffer of the owner of its query row (plain stores
+ * + one system-scope atomic per ~64 hits), so there is no all-to-all afterwards: every rank
+ * zeroes its own *count before the pass (with a barrier in between: nobody may append before
+ * the clear), and after a barrier behind the screen it hands its own buffer to
+ * exb_knn_sym_scatter_hits (the count is read on the device; count > capacity sets status flag
+ * bit 1) and finishes with exb_knn_sym_rerank_f32. */
+#define EXB_SYM_MAX_RANKS 8
+int exb_knn_sym_screen_peer_f32(const float* rep, int64_t n, int dim, int k,
+                                const float* d_sample, int64_t d_stride, int log_cap,
+                                int recv_cap, int pair_lo, int pair_hi, int span_end,
+                                int mid_pair, int extra_tiles, int n_ranks,
+                                const exb_sym_hits* peer_hits, const int32_t* tile_lo,
+                                void* workspace, size_t workspace_bytes, exb_stream_t stream);
+int exb_knn_sym_scatter_hits(int64_t n, int dim, int k, int log_cap, int recv_cap,
+                             const exb_sym_hits* hits, void* workspace, exb_stream_t stream);
+
+/* Peer-visible device memory: cudaMalloc + CUDA IPC.  alloc returns the device pointer and a
+ * 64-byte handle to send to the other ranks' processes (any transport); open maps a handle of
+ * ANOTHER process into this one (peer access over NVLink is enabled on first use; opening a
+ * handle in the process that made it is an error — use the pointer); close unmaps, free releases
+ * (after every peer closed).  clear = cudaMemsetAsync(ptr, 0, bytes) on `stream`. */
+int exb_peer_buffer_alloc(size_t bytes, void** ptr, unsigned char* handle64);
+int exb_peer_buffer_open(const unsigned char* handle64, void** ptr);
+int exb_peer_buffer_close(void* ptr);
+int exb_peer_buffer_free(void* ptr);
+int exb_peer_buffer_clear(void* ptr, size_t bytes, exb_stream_t stream);
 int exb_knn_sym_rerank_f32(const float* rep, int64_t n, int dim, int k, int32_t idx_base,
                            int log_cap, int recv_cap, int64_t row_lo, int64_t row_hi,
                            float* out_dist, int32_t* out_idx, void* workspace,
