@@ -336,13 +336,19 @@ def run_ours(a, rank, world, local_rank):
     if a.stage_times:
         from exorl_b200.relabel import StageTimer
         tmr = StageTimer()
+        _lib.check(lib.exb_profile_begin(1))       # this rank's screen-kernel times beside them
         xb.relabel_apt_reward(rep, args, rms=rms, exchange=a.exchange, mode="screened", timer=tmr)
         st = tmr.summary()
+        sk = (ctypes.c_float * 64)()
+        sn = ctypes.c_int(0)
+        _lib.check(lib.exb_profile_collect_sync(sk, 64, ctypes.byref(sn)))
+        _lib.check(lib.exb_profile_begin(0))
+        st["screen_kernels_ms"] = [round(sk[i], 3) for i in range(sn.value)]
         tmr2 = StageTimer()
         xb.relabel_apt_reward_from_host(rep_host, args, rms=rms, rep_out=rep, balance=balance,
                                         timer=tmr2)
         st2 = tmr2.summary()
-        print(f"rank {rank} stage times (ms): " + json.dumps({k: round(v, 3) for k, v in st.items()})
+        print(f"rank {rank} stage times (ms): " + json.dumps({k: (round(v, 3) if isinstance(v, float) else v) for k, v in st.items()})
               + " | from_host: " + json.dumps({k: round(v, 3) for k, v in st2.items()}),
               file=sys.stderr, flush=True)
 

@@ -956,6 +956,15 @@ knn_screen_kernel(const __grid_constant__ CUtensorMap tmap_q,
   }
   if constexpr (SYM) {
     // own bank tile (SCR_N = CG * SCR_M rows: the pair's query rows ARE that tile) and onwards
+    // Launch order = longest scan first: the scan length falls with the pair index, except that
+    // the pairs from sym_mid_pair on carry sym_extra more tiles (ranks of the upper half of an
+    // even world) — those go first, i.e. the local pair index is rotated by (mid - lo).
+    if (p.sym_extra > 0) {
+      const int n_pairs = (int)gridDim.x / CG;
+      int lp = m_tile / CG + (p.sym_mid_pair - p.sym_pair_lo);
+      if (lp >= n_pairs) lp -= n_pairs;
+      m_tile = lp * CG + m_tile % CG;
+    }
     m_tile += p.sym_pair_lo * CG;
     t_begin = m_tile / CG;
     t_end = p.sym_span_end + (t_begin >= p.sym_mid_pair ? p.sym_extra : 0);   // may pass n_tiles
