@@ -410,3 +410,77 @@ def test_symmetric_screen_relabel_reward_matches_oracle(sym_on):
     want = pbe_reward(x, x, st, k, True, True, 0.0)
     np.testing.assert_allclose(r.cpu().numpy()[sl], want.numpy()[sl], rtol=1e-5, atol=1e-7)
     np.testing.assert_allclose(float(rms.M), float(st.M), rtol=1e-6)
+
+
+@pytest.mark.parametrize("world", [2, 3, 4])
+def test_symmetric_peer_routing_all_ranks_on_one_gpu(world):
+    """The multi-GPU form with the exchange inside the kernel (exb_knn_sym_screen_peer_f32 ->
+    exb_knn_sym_scatter_hits -> exb_knn_sym_rerank_f32), every "rank" played by this one GPU:
+    rank r screens its span with the table of all ranks' hit buffers, each hit must land in the
+    buffer of the owner of its query row, and the reranked blocks together must be the full
+    screen's result.  (Across processes the buffers are CUDA-IPC mappings:
+    benchmarks/relabel_nccl_check.py.)"""
+    import ctypes
+    from exorl_b200 import _lib, knn as xknn
+    from exorl_b200.relabel import sym_tile_blocks, sym_span, _CudaSymBackend
+    n, dim, k = 20000, 64, 12
+    x = reps(47, n, dim)
+    xd = x.to(DEV)
+    lib = _lib.load()
+    prev = xknn.SYM_ENABLED
+    xknn.SYM_ENABLED = False
+    try:
+        d_f, i_f = xb.knn_topk(xd, xd, k, mode="screened")
+        sample = xd[::16].contiguous()
+        d_all = xb.knn_topk(xd, sample, k, mode="screened")[0][:, k - 1].contiguous()
+    finally:
+        xknn.SYM_ENABLED = prev
+    expected = 1.3 * k * n / sample.size(0)
+    log_cap = int(-(-(3 * expected / 2 + 96) // 8) * 8)
+    recv_cap = int(-(-(3 * expected + 96) // 8) * 8)
+    need = lib.exb_knn_sym_workspace_bytes(n, dim, k, log_cap, recv_cap)
+    assert need > 0
+    tiles, tb, rb = sym_tile_blocks(n, world)
+    rows_max = max(rb[r + 1] - rb[r] for r in range(world))
+    cap = -(-int(rows_max * (recv_cap // 3 + 16)) // 64) * 64
+    with torch.cuda.device(DEV):
+        ws = [torch.zeros(need, dtype=torch.uint8, device=DEV) for _ in range(world)]
+        bufs = [torch.zeros(256 + 12 * cap, dtype=torch.uint8, device=DEV) for _ in range(world)]
+        hits = (_lib.SymHits * world)()
+        for r in range(world):
+            hits[r] = _CudaSymBackend._hits_at(bufs[r].data_ptr(), cap)
+        tl = (ctypes.c_int32 * (world + 1))(*tb)
+        st = _lib.stream_ptr(DEV)
+        for r in range(world):
+            lo, hi, span_end, mid, extra = sym_span(tb, world, r)
+            _lib.check(lib.exb_knn_sym_screen_peer_f32(
+                _lib.ptr(xd), n, dim, k, _lib.ptr(d_all), 1, log_cap, recv_cap, lo, hi, span_end,
+                mid, extra, world, hits, tl, _lib.ptr(ws[r]), need, st))
+        torch.cuda.synchronize()
+        total = 0
+        for r in range(world):                      # every hit sits with the owner of its row
+            cnt = int(bufs[r][:8].view(torch.int64).item())
+            assert 0 < cnt <= cap
+            tgt = bufs[r][256:256 + 4 * cnt].view(torch.int32)
+            assert int(tgt.min()) >= rb[r] and int(tgt.max()) < rb[r + 1]
+            total += cnt
+        assert total > n * k // 4                   # about half of all candidates travel
+        d_parts, i_parts = [], []
+        for r in range(world):
+            _lib.check(lib.exb_knn_sym_scatter_hits(n, dim, k, log_cap, recv_cap,
+                                                    ctypes.byref(hits[r]), _lib.ptr(ws[r]), st))
+            d_r = torch.empty(rb[r + 1] - rb[r], k, dtype=torch.float32, device=DEV)
+            i_r = torch.empty(rb[r + 1] - rb[r], k, dtype=torch.int32, device=DEV)
+            _lib.check(lib.exb_knn_sym_rerank_f32(_lib.ptr(xd), n, dim, k, 0, log_cap, recv_cap,
+                                                  rb[r], rb[r + 1], _lib.ptr(d_r), _lib.ptr(i_r),
+                                                  _lib.ptr(ws[r]), st))
+            status = (ctypes.c_int32 * 4)()
+            _lib.check(lib.exb_knn_screened_status_sync(_lib.ptr(ws[r]), status, st))
+            assert status[1] == 0, f"rank {r}: status flags {status[1]}"
+            assert status[0] == 0 or (i_r[:, 0] < 0).sum().item() == 0   # fallbacks were recomputed
+            d_parts.append(d_r)
+            i_parts.append(i_r)
+        d_s, i_s = torch.cat(d_parts), torch.cat(i_parts)
+    np.testing.assert_allclose(d_s.cpu().numpy(), d_f.cpu().numpy(), rtol=1e-6, atol=1e-7)
+    assert (i_s.long() != i_f.long()).any(dim=1).sum().item() <= max(2, n // 2000)
+    assert_knn_matches(x[n - 500:], x, k, d_s[n - 500:], i_s[n - 500:])
