@@ -53,10 +53,11 @@ def main():
     # moved away from the equal split by the last run; "from_host" is the end-to-end pipeline
     # "sym": the symmetric screen over the ranks with the hit exchange inside the kernel (NVLink
     # peer memory), twice (buffers reused); "sym_a2a": the same with the all-to-all exchange
-    for exchange in ("sym", "sym", "sym_a2a", "queries", "balanced", "balanced", "balanced", "from_host",
+    # "sym_from_host": the end-to-end form — rows uploaded in chunks behind the sample pre-pass
+    for exchange in ("sym", "sym", "sym_a2a", "sym_from_host", "sym_from_host", "queries", "balanced", "balanced", "balanced", "from_host",
                      "prepared", "lists", "auto", "all_to_all", "all_gather"):
         rms = xb.RMS(dev)
-        xknn.SYM_ENABLED = exchange in ("sym", "sym_a2a")
+        xknn.SYM_ENABLED = exchange in ("sym", "sym_a2a", "sym_from_host")
         xknn.SYM_MIN_ROWS = a.sym_min_rows
         if exchange in ("sym", "sym_a2a"):
             xknn.sym_last.clear()
@@ -71,6 +72,15 @@ def main():
             if rank == 0:
                 print(f"[nccl check] symmetric exchange: {xknn.sym_last.get('exchange')}",
                       flush=True)
+        elif exchange == "sym_from_host":
+            xknn.sym_last.clear()
+            scratch = torch.zeros_like(rep)            # the rows must really come from the host
+            out = xb.relabel_apt_reward_from_host(rep_host, args, rms=rms, rep_out=scratch,
+                                                  return_knn=True)
+            assert xknn.sym_last.get("world") == world, xknn.sym_last
+            assert "fell_back_to_full_screen" not in xknn.sym_last, xknn.sym_last
+            assert torch.equal(scratch, rep)
+            del scratch
         elif exchange == "from_host":
             out = xb.relabel_apt_reward_from_host(rep_host, args, rms=rms, return_knn=True)
         elif exchange == "prepared":
@@ -89,7 +99,7 @@ def main():
         assert rms.n == rms0.n
         if exchange == "all_gather":            # every rank holds all rows
             lo, hi = 0, a.n
-        elif exchange in ("sym", "sym_a2a", "queries", "balanced", "auto", "prepared", "from_host"):
+        elif exchange in ("sym", "sym_a2a", "sym_from_host", "queries", "balanced", "auto", "prepared", "from_host"):
             lo, hi = xrel.last_query_block["lo"], xrel.last_query_block["hi"]   # balanced block
         else:                                    # rank r finalised query block r
             lo, hi = xrel.shard_bounds(a.n, world, rank)

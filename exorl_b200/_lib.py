@@ -126,6 +126,7 @@ SIGNATURES = {
     "exb_peer_buffer_close": (_c.c_int, [_vp]),
     "exb_peer_buffer_free": (_c.c_int, [_vp]),
     "exb_peer_buffer_clear": (_c.c_int, [_vp, _sz, _vp]),
+    "exb_h2d_rows_2d": (_c.c_int, [_vp, _vp, _i64, _i64, _i64, _vp]),
     "exb_knn_sym_rerank_f32": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _i32, _c.c_int, _c.c_int,
                                           _i64, _i64, _vp, _vp, _vp, _vp]),
     "exb_knn_colstats_workspace_bytes": (_sz, [_i64, _c.c_int]),

@@ -110,3 +110,16 @@ extern "C" int exb_peer_buffer_clear(void* ptr, size_t bytes, exb_stream_t strea
   EXB_CUDA(cudaMemsetAsync(ptr, 0, bytes, (cudaStream_t)stream));
   return EXB_OK;
 }
+
+// Strided rows of a (pinned) host matrix into a dense device matrix: one 2-D DMA on `stream`
+// (the sample of the symmetric screen = every stride-th rep row, uploaded ahead of the rows).
+extern "C" int exb_h2d_rows_2d(void* dst, const void* src_host, int64_t rows, int64_t row_bytes,
+                               int64_t src_pitch_bytes, exb_stream_t stream) {
+  EXB_CHECK_ARG(dst && src_host && rows >= 0 && row_bytes > 0 && src_pitch_bytes >= row_bytes,
+                "bad arguments");
+  if (rows == 0) return EXB_OK;
+  EXB_CUDA(cudaMemcpy2DAsync(dst, (size_t)row_bytes, src_host, (size_t)src_pitch_bytes,
+                             (size_t)row_bytes, (size_t)rows, cudaMemcpyHostToDevice,
+                             (cudaStream_t)stream));
+  return EXB_OK;
+}

@@ -137,18 +137,29 @@ def _sym_fits(dev, need):
     return need - have <= SYM_MEM_FRACTION * free
 
 
-def _knn_topk_sym(src, k, idx_base):
+def _knn_topk_sym(src, k, idx_base, feed=None):
     """kNN of `src` against itself through the symmetric screen, or None when the pass reports
     that it cannot certify the result (a transposed log overflowed: hub rows, heavy duplication)
-    — the caller then runs the full screen."""
+    — the caller then runs the full screen.  `feed` (relabel._HostFeed): the rows of `src` are
+    still on their way from the host; the sample pre-pass runs chunk by chunk behind the
+    upload and only the symmetric pass itself waits for all of them."""
     lib = _lib.load()
     n, dim = src.shape
     dev = src.device
     stride = max(1, n // _sym_sample_rows(n))
-    sample = src[::stride].contiguous()
     # exact distance of every row to its k-th nearest SAMPLE row: an upper bound of its true
     # k-th-neighbour distance, which fixes the row's keep threshold for the symmetric pass
-    d_s, _ = _knn_topk_impl(src, sample, k, 0, "screened", False, allow_sym=False)
+    if feed is None:
+        sample = src[::stride].contiguous()
+        d_s, _ = _knn_topk_impl(src, sample, k, 0, "screened", False, allow_sym=False)
+    else:
+        sample = feed.sample(stride)
+        d_s = torch.empty(n, k, dtype=torch.float32, device=dev)
+        for a, b in feed.start(0, n):
+            feed.wait(a, b)
+            d_s[a:b] = _knn_topk_impl(src[a:b], sample, k, 0, "screened", False,
+                                      allow_sym=False)[0]
+        feed.wait_all()
     expected = 1.3 * k * n / sample.size(0)          # candidates per row the thresholds admit
     log_cap = int(-(-(3 * expected / 2 + 96) // 8) * 8)      # direct log per (row, column half)
     recv_cap = int(-(-(3 * expected + 96) // 8) * 8)         # received list per row

@@ -280,6 +280,85 @@ def reps_from_host(rep_host, out=None, group=None):
     return out
 
 
+class _HostFeed:
+    """Rows of a pinned host matrix on their way to `rep_out` while the symmetric path already
+    works (relabel_apt_reward_from_host): the sample (every stride-th row) goes first as one 2-D
+    DMA, then this rank's rows in chunks on a copy stream with an event each — the sample
+    pre-pass of a chunk waits for that chunk only — and, for several ranks, the all-gather of the
+    fp32 rows over NVLink behind the last chunk; only the symmetric pass waits for everything."""
+
+    def __init__(self, rep_host, rep_out, group, world, rank):
+        self.h, self.d = rep_host, rep_out
+        self.n, self.dim = rep_host.shape
+        self.dev = rep_out.device
+        self.group, self.world, self.rank = group, world, rank
+        self.lo, self.hi = shard_bounds(self.n, world, rank)
+        self.copy = _side_stream(self.dev)
+        self.copy.wait_stream(torch.cuda.current_stream(self.dev))   # earlier readers of rep_out
+        self.events, self.gather = [], None
+
+    @staticmethod
+    def usable(rep_host, n, world):
+        return (rep_host.is_pinned() and rep_host.dtype == torch.float32
+                and rep_host.is_contiguous() and rep_host.dim() == 2 and n % world == 0)
+
+    def sample(self, stride):
+        """rep[::stride] on the device: every rank uploads the sample rows of ITS shard and the
+        parts are all-gathered (padded to the largest part)."""
+        lib, dev, world, dim = _lib.load(), self.dev, self.world, self.dim
+        first = [-(-shard_bounds(self.n, world, r)[0] // stride) * stride for r in range(world)]
+        counts = [max(0, -(-(shard_bounds(self.n, world, r)[1] - first[r]) // stride))
+                  for r in range(world)]
+        s_max = max(counts)
+        buf = torch.empty((world, s_max, dim), dtype=torch.float32, device=dev)
+        mine = buf[self.rank]
+        with torch.cuda.stream(self.copy):
+            _lib.check(lib.exb_h2d_rows_2d(
+                _lib.ptr(mine), ctypes.c_void_p(self.h.data_ptr() + first[self.rank] * dim * 4),
+                counts[self.rank], dim * 4, stride * dim * 4,
+                ctypes.c_void_p(self.copy.cuda_stream)))
+            ev = torch.cuda.Event()
+            ev.record(self.copy)
+        torch.cuda.current_stream(dev).wait_event(ev)
+        if world == 1:
+            return buf[0]
+        dist.all_gather_into_tensor(buf.view(world * s_max, dim), mine, group=self.group)
+        if all(c == s_max for c in counts):
+            return buf.view(world * s_max, dim)
+        return torch.cat([buf[r, :counts[r]] for r in range(world)], dim=0)
+
+    def start(self, qlo, qhi):
+        """Enqueue the upload of this rank's shard plus the rows of its query block [qlo, qhi)
+        outside it (tile alignment: < 256 rows; the all-gather rewrites them with the same
+        bytes) and the all-gather behind it.  -> the chunks of [qlo, qhi) in arrival order."""
+        a, b = min(self.lo, qlo), max(self.hi, qhi)
+        n_chunks = max(1, min(8, (b - a) // 60000))
+        cuts = [a + (b - a) * c // n_chunks for c in range(n_chunks + 1)]
+        with torch.cuda.stream(self.copy):
+            for ca, cb in zip(cuts[:-1], cuts[1:]):
+                self.d[ca:cb].copy_(self.h[ca:cb], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self.copy)
+                self.events.append((ca, cb, ev))
+            if self.world > 1:
+                self.gather = dist.all_gather_into_tensor(self.d, self.d[self.lo:self.hi],
+                                                          group=self.group, async_op=True)
+        return [(max(ca, qlo), min(cb, qhi)) for ca, cb, _ in self.events
+                if max(ca, qlo) < min(cb, qhi)]
+
+    def wait(self, a, b):
+        cur = torch.cuda.current_stream(self.dev)
+        for ca, cb, ev in self.events:
+            if ca < b and cb > a:
+                cur.wait_event(ev)
+
+    def wait_all(self):
+        self.wait(0, self.n)
+        if self.gather is not None:
+            self.gather.wait()
+            self.gather = None
+
+
 class StageTimer:
     """Optional CUDA-event stopwatch for the relabel stages (bench.py --stage-times)."""
 
@@ -345,6 +424,9 @@ def _finish_block(d_mine, i_mine, n, lo, hi, in_split, world, k, avg, use_rms, c
 # kernel over NVLink peer memory (exb_knn_sym_screen_peer_f32), False = counting partition +
 # all_to_all_single after it.  Falls back to the latter when peer mapping is refused.
 SYM_PEER_MEMORY = True
+# relabel_apt_reward_from_host on the symmetric path: True = upload in chunks behind the sample
+# pre-pass (_HostFeed), False = upload (+ all-gather), then the device path.
+SYM_HOST_PIPELINE = True
 
 
 def sym_tile_blocks(n, world, tile=256):
@@ -536,7 +618,7 @@ class _CudaSymBackend:
         self.xknn._recompute_rows(self.rep[lo:hi], self.rep, self.k, 0, d_mine, i_mine, rows)
 
 
-def _sym_queries_knn(rep, k, world, rank, group, tm, backend=None):
+def _sym_queries_knn(rep, k, world, rank, group, tm, backend=None, feed=None):
     """kNN of this rank's (tile-aligned) query block through the symmetric screen spread over
     the ranks.  Returns (dist, idx, row_bounds) or None when any rank reports the pass invalid
     (the caller then runs the full screen).  Collectives: d_sample all-reduce (4N bytes); the
@@ -551,8 +633,8 @@ def _sym_queries_knn(rep, k, world, rank, group, tm, backend=None):
     tiles, tb, rb = sym_tile_blocks(n, world, be.tile)
     lo, hi = rb[rank], rb[rank + 1]
     stride = max(1, n // be.sample_rows())
-    sample = rep[::stride].contiguous()
-    fits = torch.tensor([1 if be.room(1.3 * k * n / sample.size(0)) else 0], device=dev)
+    n_sample = -(-n // stride)
+    fits = torch.tensor([1 if be.room(1.3 * k * n / n_sample) else 0], device=dev)
     dist.all_reduce(fits, op=dist.ReduceOp.MIN, group=group)          # all ranks or none
     if not int(fits.item()):
         xknn.sym_last.update(n=n, no_room=True)
@@ -562,8 +644,18 @@ def _sym_queries_knn(rep, k, world, rank, group, tm, backend=None):
     peer = (SYM_PEER_MEMORY and hasattr(be, "open_peers") and world <= _lib.SYM_MAX_RANKS
             and be.open_peers(group, world, rank, max(rb[r + 1] - rb[r] for r in range(world))))
     d_all = torch.zeros(n, dtype=torch.float32, device=dev)
-    d_all[lo:hi] = be.sample_distances(lo, hi, sample)
+    if feed is None:
+        sample = rep[::stride].contiguous()
+        d_all[lo:hi] = be.sample_distances(lo, hi, sample)
+    else:
+        # rows still arriving from the host (_HostFeed): pre-pass chunk by chunk behind the upload
+        sample = feed.sample(stride)
+        for a, b in feed.start(lo, hi):
+            feed.wait(a, b)
+            d_all[a:b] = be.sample_distances(a, b, sample)
     dist.all_reduce(d_all, op=dist.ReduceOp.SUM, group=group)
+    if feed is not None:
+        feed.wait_all()                   # the symmetric pass reads every row
     tm("sym_sample_prepass")
     if peer:
         be.screen_peer(d_all, sym_span(tb, world, rank), tb)
@@ -811,6 +903,40 @@ def relabel_apt_reward_from_host(rep_host, args, rms=None, group=None, rep_out=N
     from . import knn as xknn
     sym = (xknn.SYM_ENABLED and n >= xknn.SYM_MIN_ROWS and xknn.OVERFLOW_POLICY == "sync"
            and dim <= _lib.SCREEN_MAX_DIM and k <= _lib.SCREEN_MAX_K and not balance)
+    tm = timer.mark if timer is not None else (lambda name: None)
+    if sym and SYM_HOST_PIPELINE and _HostFeed.usable(rep_host, n, world):
+        # symmetric screen with the upload (and the NVLink all-gather of the fp32 rows) hidden
+        # behind its sample pre-pass
+        with torch.cuda.device(dev):
+            feed = _HostFeed(rep_host, rep_out, group, world, rank)
+            tm("start")
+            if world == 1:
+                out = xknn._knn_topk_sym(rep_out, k, 0, feed=feed)
+                tm("sym_knn")
+                if out is not None:
+                    reward = _CudaStages.reward(out[0], k, avg, use_rms, clip, rms)
+                    return (reward, out[0], out[1]) if return_knn else reward
+            else:
+                out = _sym_queries_knn(rep_out, k, world, rank, group, tm, feed=feed)
+                if out is not None:
+                    d_mine, i_mine, rb = out
+                    last_query_block.update(lo=rb[rank], hi=rb[rank + 1])
+                    return _finish_block(d_mine, i_mine, n, rb[rank], rb[rank + 1],
+                                         [rb[r + 1] - rb[r] for r in range(world)], world, k, avg,
+                                         use_rms, clip, rms, group, _CudaStages, tm, return_knn)
+            # the symmetric pass could not certify its result (or had no room): full screen
+            xknn.sym_last["fell_back_to_full_screen"] = True
+            if feed.events:
+                feed.wait_all()
+            else:
+                reps_from_host(rep_host, out=rep_out, group=group)
+            prev = xknn.SYM_ENABLED
+            xknn.SYM_ENABLED = False
+            try:
+                return relabel_apt_reward(rep_out, args, rms=rms, group=group, mode="screened",
+                                          return_knn=return_knn, balance=balance)
+            finally:
+                xknn.SYM_ENABLED = prev
     if world == 1 or sym or n % world != 0 or lists == 0 or lists > 16:
         # symmetric screen (half the tensor-core work) beats the overlap of the pipeline below
         # one GPU: nothing to pipeline against — copy, then the device path (which takes the
@@ -820,7 +946,6 @@ def relabel_apt_reward_from_host(rep_host, args, rms=None, group=None, rep_out=N
                                   return_knn=return_knn, balance=balance)
     lib = _lib.load()
     lo, hi = shard_bounds(n, world, rank)
-    tm = timer.mark if timer is not None else (lambda name: None)
     with torch.cuda.device(dev):
         pre = PreparedRep(n, dim, dev, rep=rep_out)
         tm("start")

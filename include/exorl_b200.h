@@ -179,6 +179,13 @@ int exb_peer_buffer_open(const unsigned char* handle64, void** ptr);
 int exb_peer_buffer_close(void* ptr);
 int exb_peer_buffer_free(void* ptr);
 int exb_peer_buffer_clear(void* ptr, size_t bytes, exb_stream_t stream);
+
+/* Rows src_host + i * src_pitch_bytes (i < rows, row_bytes each; pinned host memory) into the
+ * dense device matrix dst [rows, row_bytes] with one asynchronous 2-D DMA on `stream`.  The
+ * end-to-end relabel uploads the symmetric screen's sample (every stride-th row of the host-
+ * resident reps, the rows utils/utils.py:290 would score) ahead of the row chunks with it. */
+int exb_h2d_rows_2d(void* dst, const void* src_host, int64_t rows, int64_t row_bytes,
+                    int64_t src_pitch_bytes, exb_stream_t stream);
 int exb_knn_sym_rerank_f32(const float* rep, int64_t n, int dim, int k, int32_t idx_base,
                            int log_cap, int recv_cap, int64_t row_lo, int64_t row_hi,
                            float* out_dist, int32_t* out_idx, void* workspace,

@@ -484,3 +484,31 @@ def test_symmetric_peer_routing_all_ranks_on_one_gpu(world):
     np.testing.assert_allclose(d_s.cpu().numpy(), d_f.cpu().numpy(), rtol=1e-6, atol=1e-7)
     assert (i_s.long() != i_f.long()).any(dim=1).sum().item() <= max(2, n // 2000)
     assert_knn_matches(x[n - 500:], x, k, d_s[n - 500:], i_s[n - 500:])
+
+
+def test_from_host_symmetric_pipeline_matches_device_path(sym_on):
+    """relabel_apt_reward_from_host on the symmetric path: the rows arrive in chunks (two here)
+    behind the sample pre-pass, the sample itself as one strided 2-D DMA; same rewards, same
+    neighbours and the same device copy of the rows as upload-then-compute."""
+    from exorl_b200 import relabel as xrel
+    n, dim, k = 130000, 64, 12
+    x = reps(48, n, dim)
+    xh = x.pin_memory()
+    args = types.SimpleNamespace(knn_k=k, knn_avg=True, knn_rms=True, knn_clip=0.0)
+    rms_a, rms_b = xb.RMS(DEV), xb.RMS(DEV)
+    out_a = torch.zeros(n, dim, device=DEV)
+    r_a, d_a, i_a = xb.relabel_apt_reward_from_host(xh, args, rms=rms_a, rep_out=out_a,
+                                                    return_knn=True)
+    assert sym_on.sym_last.get("n") == n and "fell_back_to_full_screen" not in sym_on.sym_last
+    assert torch.equal(out_a.cpu(), x)
+    prev = xrel.SYM_HOST_PIPELINE
+    xrel.SYM_HOST_PIPELINE = False
+    try:
+        r_b, d_b, i_b = xb.relabel_apt_reward_from_host(xh, args, rms=rms_b, return_knn=True)
+    finally:
+        xrel.SYM_HOST_PIPELINE = prev
+    np.testing.assert_allclose(r_a.cpu().numpy(), r_b.cpu().numpy(), rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(d_a.cpu().numpy(), d_b.cpu().numpy(), rtol=1e-6, atol=1e-7)
+    assert (i_a != i_b).any(dim=1).sum().item() <= n // 2000
+    np.testing.assert_allclose(float(rms_a.M), float(rms_b.M), rtol=1e-6)
+    assert_knn_matches(x[n - 300:], x, k, d_a[n - 300:], i_a[n - 300:])
