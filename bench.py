@@ -272,6 +272,11 @@ def run_ours(a, rank, world, local_rank):
     kms = (ctypes.c_float * 64)()
     kn = ctypes.c_int(0)
     _lib.check(lib.exb_profile_collect_sync(kms, 64, ctypes.byref(kn)))
+    from exorl_b200 import knn as xknn
+    if a.stage_times:          # every rank's screen launches of the timed steps, in launch order
+        print(f"rank {rank} timed-loop screen kernels (ms): "
+              + json.dumps([round(kms[i], 3) for i in range(kn.value)])
+              + f" rows_per_rank={xknn.sym_last.get('rows_per_rank')}", file=sys.stderr, flush=True)
     _lib.check(lib.exb_profile_begin(0))
     clocks = sampler.stop() if sampler else None
     from exorl_b200 import knn as xknn
@@ -377,6 +382,11 @@ def run_ours(a, rank, world, local_rank):
         sym = (xknn.sym_last.get("n") == a.n and xknn.sym_last.get("world", 1) == world
                and a.exchange in ("auto", "queries")
                and "fell_back_to_full_screen" not in xknn.sym_last and kn.value == 2 * a.steps)
+        if sym and query_blocks is not None and xknn.sym_last.get("rows_per_rank"):
+            # symmetric path: tile blocks re-cut every step from the ranks' screen rates of the step before
+            query_blocks.update(balance="screen rates of the previous step (sym_balanced_blocks)",
+                                rows_per_rank=xknn.sym_last["rows_per_rank"],
+                                screen_ns_per_tile_pair=xknn.sym_last["screen_ns_per_tile_pair"])
         flops = 2.0 * a.n * nb_local * a.dim          # algorithmic: every (query, bank row) pair
         sym_info = None
         if sym:
@@ -387,6 +397,16 @@ def run_ours(a, rank, world, local_rank):
             kernel_ms = sum(kms[i] for i in range(1, kn.value, 2)) / a.steps
             t = (a.n + 255) // 256
             executed = 2.0 * 256 * 256 * a.dim * (t * (t + 1) / 2) / world   # this rank's tile pairs
+            if world > 1 and xknn.sym_last.get("rows_per_rank"):
+                # rate-balanced blocks: rank 0's own tile products under the LAST step's blocks
+                # (they move by ~1 % from step to step with the measured rates)
+                from exorl_b200.relabel import sym_span
+                tb_ = [0]
+                for r_ in xknn.sym_last["rows_per_rank"]:
+                    tb_.append(tb_[-1] + (r_ + 255) // 256)
+                lo_, hi_, end_, mid_, extra_ = sym_span(tb_, world, 0)
+                executed = 2.0 * 256 * 256 * a.dim * sum(
+                    end_ - u + (extra_ if u >= mid_ else 0) for u in range(lo_, hi_))
             flops = flops                                  # (algorithmic share of a rank: N * N/G)
             s_rows = xknn.sym_last["sample_rows"]
             achieved = executed / (kernel_ms * 1e-3) / 1e12

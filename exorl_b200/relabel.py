@@ -427,6 +427,10 @@ SYM_PEER_MEMORY = True
 # relabel_apt_reward_from_host on the symmetric path: True = upload in chunks behind the sample
 # pre-pass (_HostFeed), False = upload (+ all-gather), then the device path.
 SYM_HOST_PIPELINE = True
+# Symmetric screen over several GPUs: size the ranks' tile blocks by the rate each GPU's screen
+# showed in the previous step (sym_balanced_blocks) instead of equally.
+SYM_RATE_BALANCE = True
+SYM_BALANCE_MAX_SKEW = 0.12
 
 
 def sym_tile_blocks(n, world, tile=256):
@@ -458,6 +462,74 @@ def sym_span(tb, world, rank):
             mid = lo + half_anti_of_me                     # ... so my pairs from there on take
             extra = size[anti]                             # the whole antipodal block
     return lo, hi, span_end, mid, extra
+
+
+def _sym_work(size, world, r):
+    """Tile products of rank r under sym_span for (real-valued) block sizes `size`."""
+    whole = (world - 1) // 2
+    w = size[r] * size[r] / 2 + size[r] * sum(size[(r + s) % world] for s in range(1, whole + 1))
+    if world % 2 == 0 and world > 1:
+        anti = (r + world // 2) % world
+        w += size[r] * size[anti] / 2       # either all pairs x half block or half the pairs x block
+    return w
+
+
+def sym_balanced_blocks(tiles, world, ms, max_skew=SYM_BALANCE_MAX_SKEW):
+    """Tile blocks tb[0..world] sized so that every rank's symmetric screen takes the same time,
+    from the time per tile product `ms[r]` each rank's screen needed in the previous step: B200s
+    under their power cap differ by several per cent in sustained clock, persistently, and the
+    slowest rank sets the step time.  Sizes
+    stay within (1 +- max_skew) of the equal split (the peer hit buffers are sized for that).
+    Pure and deterministic: every rank computes the same blocks from the all-gathered times."""
+    eq = tiles / world
+    if world == 1 or min(ms) <= 0 or eq < 8:
+        return [(r * tiles) // world for r in range(world + 1)]
+    rate = [1.0 / m for m in ms]
+    mean_rate = sum(rate) / world
+    rate = [x / mean_rate for x in rate]
+    lo_s, hi_s = eq * (1 - max_skew), eq * (1 + max_skew)
+    size = [eq] * world
+    for _ in range(60):
+        t = [_sym_work(size, world, r) / rate[r] for r in range(world)]
+        mean_t = sum(t) / world
+        size = [sz * (mean_t / tt) for sz, tt in zip(size, t)]
+        for _ in range(world + 1):        # back onto {sum = tiles, lo_s <= size <= hi_s}
+            size = [min(hi_s, max(lo_s, sz)) for sz in size]
+            excess = tiles - sum(size)
+            free = [i for i, sz in enumerate(size) if (sz < hi_s if excess > 0 else sz > lo_s)]
+            if abs(excess) < 1e-9 or not free:
+                break
+            for i in free:
+                size[i] += excess / len(free)
+    cuts = [0.0]
+    for sz in size:
+        cuts.append(cuts[-1] + sz)
+    tb = [int(round(c)) for c in cuts]
+    tb[0], tb[-1] = 0, tiles
+    return tb
+
+
+def _sym_span_work(span):
+    """Tile products of a span (pair_lo, pair_hi, span_end, mid_pair, extra)."""
+    lo, hi, end, mid, extra = span
+    return sum(end - u + (extra if u >= mid else 0) for u in range(lo, hi))
+
+
+_sym_pending = {}      # key -> (start event, end event, tile products) of the last screen
+_sym_unit = {}         # key -> smoothed ms per tile product of this rank's screen
+
+
+def _sym_unit_time(key):
+    """This rank's screen time per tile product, from the stopwatch of the previous step with
+    the same sizes (0.0 = no history yet -> equal blocks)."""
+    pend = _sym_pending.pop(key, None)
+    if pend is not None:
+        e0, e1, work = pend
+        e1.synchronize()                  # long done: the previous step's results were read
+        u = e0.elapsed_time(e1) / max(work, 1)
+        old = _sym_unit.get(key)
+        _sym_unit[key] = u if old is None else 0.5 * old + 0.5 * u
+    return _sym_unit.get(key, 0.0)
 
 
 class _CudaSymBackend:
@@ -631,18 +703,38 @@ def _sym_queries_knn(rep, k, world, rank, group, tm, backend=None, feed=None):
     n = rep.size(0)
     dev = rep.device
     tiles, tb, rb = sym_tile_blocks(n, world, be.tile)
-    lo, hi = rb[rank], rb[rank + 1]
     stride = max(1, n // be.sample_rows())
     n_sample = -(-n // stride)
-    fits = torch.tensor([1 if be.room(1.3 * k * n / n_sample) else 0], device=dev)
-    dist.all_reduce(fits, op=dist.ReduceOp.MIN, group=group)          # all ranks or none
-    if not int(fits.item()):
+    # one collective + one host sync up front: "does the workspace fit everywhere" and, for the
+    # rate balance, the time per tile product every rank's screen needed in the PREVIOUS step
+    rebalance = SYM_RATE_BALANCE and rep.is_cuda and world > 1
+    key = (n, rep.size(1), k, world, rank)
+    unit = _sym_unit_time(key) if rebalance else 0.0
+    mine = torch.tensor([1.0 if be.room(1.3 * k * n / n_sample) else 0.0, unit],
+                        dtype=torch.float64, device=dev)
+    everyone = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(everyone, mine, group=group)
+    everyone = torch.stack(everyone).tolist()
+    if not all(e[0] for e in everyone):                               # all ranks or none
         xknn.sym_last.update(n=n, no_room=True)
         return None
+    units = [e[1] for e in everyone]
+    if rebalance and min(units) > 0:
+        # B200s under their power cap sustain clocks that differ by several per cent from GPU to
+        # GPU, persistently: slow ranks get fewer tiles so that the screens end together
+        tb = sym_balanced_blocks(tiles, world, units)
+        rb = [min(n, be.tile * t) for t in tb]
+    lo, hi = rb[rank], rb[rank + 1]
+    xknn.sym_last.update(rows_per_rank=[rb[r + 1] - rb[r] for r in range(world)],
+                         screen_ns_per_tile_pair=[round(1e6 * u, 3) for u in units])
+    rows_bound = -(-n // world)
+    if rebalance:                         # blocks may grow by SYM_BALANCE_MAX_SKEW (+ rounding)
+        rows_bound = int(rows_bound * (1 + SYM_BALANCE_MAX_SKEW))
+    rows_bound += 2 * be.tile
     # the own hit buffer is cleared on this stream BEFORE the all-reduce below, which therefore
     # doubles as the barrier "nobody appends to a buffer that is not cleared yet"
     peer = (SYM_PEER_MEMORY and hasattr(be, "open_peers") and world <= _lib.SYM_MAX_RANKS
-            and be.open_peers(group, world, rank, max(rb[r + 1] - rb[r] for r in range(world))))
+            and be.open_peers(group, world, rank, rows_bound))
     d_all = torch.zeros(n, dtype=torch.float32, device=dev)
     if feed is None:
         sample = rep[::stride].contiguous()
@@ -657,8 +749,15 @@ def _sym_queries_knn(rep, k, world, rank, group, tm, backend=None, feed=None):
     if feed is not None:
         feed.wait_all()                   # the symmetric pass reads every row
     tm("sym_sample_prepass")
+    span = sym_span(tb, world, rank)
+    if rebalance:                         # stopwatch around this rank's screen, read next step
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
     if peer:
-        be.screen_peer(d_all, sym_span(tb, world, rank), tb)
+        be.screen_peer(d_all, span, tb)
+        if rebalance:
+            e1.record()
+            _sym_pending[key] = (e0, e1, _sym_span_work(span))
         bad = torch.zeros(1, dtype=torch.int64, device=dev)
         dist.all_reduce(bad, op=dist.ReduceOp.MAX, group=group)   # barrier: every screen is done
         tm("sym_screen")
@@ -674,7 +773,10 @@ def _sym_queries_knn(rep, k, world, rank, group, tm, backend=None, feed=None):
             be.repair(lo, hi, d_mine, i_mine)
         tm("sym_rerank")
         return d_mine, i_mine, rb
-    (tgt, val, src), over = be.screen(d_all, sym_span(tb, world, rank))
+    (tgt, val, src), over = be.screen(d_all, span)
+    if rebalance:
+        e1.record()
+        _sym_pending[key] = (e0, e1, _sym_span_work(span))
     tm("sym_screen")
     bad = torch.tensor([1 if over else 0], device=dev)
     # route every hit to the rank that owns its query row (a counting partition: one mask +

@@ -104,3 +104,43 @@ def test_symmetric_multi_gpu_spans_cover_every_tile_pair_exactly_once():
         assert len(seen) == tiles * (tiles + 1) // 2, (n, world)
         assert set(seen.values()) == {1}, (n, world)
         assert max(work) <= 1.05 * (sum(work) / world) + 2 * tiles / world + 8, (n, world, work)
+
+
+def test_symmetric_rate_balanced_blocks_cover_once_and_equalise_time():
+    """relabel.sym_balanced_blocks: blocks re-cut from per-rank times (slow GPUs get fewer tiles)
+    still give every unordered tile pair to exactly one rank, stay within the skew bound the hit
+    buffers are sized for, and equalise work x time-per-unit-of-work across the ranks."""
+    from exorl_b200.relabel import sym_balanced_blocks, sym_span, SYM_BALANCE_MAX_SKEW
+    cases = [(600, 8, [7.13, 6.82, 7.77, 7.80, 7.52, 7.68, 7.26, 7.69]),
+             (391, 2, [29.6, 27.0]), (400, 4, [1.0, 1.3, 0.9, 1.0]), (350, 3, [1.0, 1.05, 1.2]),
+             (256, 8, [1.0] * 8), (300, 5, [1.0, 5.0, 1.0, 1.0, 1.0])]
+    for tiles, world, ms in cases:
+        tb = sym_balanced_blocks(tiles, world, ms)
+        assert tb == sym_balanced_blocks(tiles, world, list(ms))        # deterministic
+        assert tb[0] == 0 and tb[-1] == tiles and all(b > a for a, b in zip(tb, tb[1:]))
+        eq = tiles / world
+        for a, b in zip(tb, tb[1:]):
+            assert eq * (1 - SYM_BALANCE_MAX_SKEW) - 1.5 <= b - a <= eq * (1 + SYM_BALANCE_MAX_SKEW) + 1.5
+        seen, work = {}, []
+        for r in range(world):
+            lo, hi, span_end, mid, extra = sym_span(tb, world, r)
+            w = 0
+            for u in range(lo, hi):
+                length = span_end - u + (extra if u >= mid else 0)
+                assert 1 <= length <= tiles
+                for j in range(length):
+                    t = (u + j) % tiles
+                    key = (min(u, t), max(u, t))
+                    seen[key] = seen.get(key, 0) + 1
+                w += length
+            work.append(w)
+        assert len(seen) == tiles * (tiles + 1) // 2 and set(seen.values()) == {1}, (tiles, world)
+        t_bal = [w * m for w, m in zip(work, ms)]
+        if max(ms) / min(ms) < 1 + SYM_BALANCE_MAX_SKEW:       # inside the clamp: times equalised
+            assert max(t_bal) <= 1.03 * min(t_bal) + 3 * tiles * max(ms) / world, (tiles, world)
+        eq_tb = [(r * tiles) // world for r in range(world + 1)]
+        t_eq = []
+        for r in range(world):
+            lo, hi, span_end, mid, extra = sym_span(eq_tb, world, r)
+            t_eq.append(sum(span_end - u + (extra if u >= mid else 0) for u in range(lo, hi)) * ms[r])
+        assert max(t_bal) <= max(t_eq) * 1.005, (tiles, world, max(t_bal), max(t_eq))
