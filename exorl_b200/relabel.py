@@ -528,7 +528,10 @@ def _sym_unit_time(key):
         e1.synchronize()                  # long done: the previous step's results were read
         u = e0.elapsed_time(e1) / max(work, 1)
         old = _sym_unit.get(key)
-        _sym_unit[key] = u if old is None else 0.5 * old + 0.5 * u
+        # first measurement as it is, then a slow average: the rates differ persistently from GPU
+        # to GPU (what the blocks should follow) AND fluctuate by a few per cent from step to step
+        # (what they should not)
+        _sym_unit[key] = u if old is None else 0.7 * old + 0.3 * u
     return _sym_unit.get(key, 0.0)
 
 
