@@ -62,12 +62,13 @@ def workload(a):
             f"clip 0, reps = tanh(randn) seed 5")
 
 
-def screen_traffic(nq, nb, dim):
+def screen_traffic(nq, nb, dim, name="screen_traffic.json"):
     """dram__bytes_read.sum + dram__bytes_write.sum of one screening launch from the committed
-    `ncu --set full` capture (profiles/screen_traffic.json) when it is of this launch shape."""
+    `ncu --set full` capture (profiles/screen_traffic.json; sym_screen_traffic.json for the
+    symmetric screen) when it is of this launch shape."""
     try:
         t = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles",
-                                        "screen_traffic.json")))
+                                        name)))
         if (t["n_queries"], t["n_bank"], t["dim"]) == (nq, nb, dim):
             return {"traffic": t["traffic_bytes_per_launch"], "traffic_unit": "bytes",
                     "traffic_source": t["source"]}
@@ -471,7 +472,8 @@ def run_ours(a, rank, world, local_rank):
                          "kernel_ms": kernel_ms, "launches_timed": kn.value,
                          "algorithmic_flops_per_launch": flops,
                          **({k: v for k, v in sym_info.items() if k != "kernel"} if sym else {}),
-                         **({"traffic": None} if sym else screen_traffic(a.n, nb_local, a.dim))},
+                         **(screen_traffic(a.n, nb_local, a.dim, "sym_screen_traffic.json") if sym
+                            else screen_traffic(a.n, nb_local, a.dim))},
             "cpu_baseline": cpu_baseline,
         }
         if full_ab is not None:
