@@ -118,7 +118,9 @@ SIGNATURES = {
     "exb_knn_sym_screen_peer_f32": (_c.c_int, [_vp, _i64, _c.c_int, _c.c_int, _vp, _i64, _c.c_int,
                                                _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int,
                                                _c.c_int, _c.c_int, _c.POINTER(SymHits),
-                                               _c.POINTER(_c.c_int32), _vp, _sz, _vp]),
+                                               _c.POINTER(_c.c_int32), _c.c_int, _vp, _sz, _vp]),
+    "exb_knn_sym_operand_slots": (_c.c_int, [_i64, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _vp,
+                                             _sz, _op_p, _c.POINTER(_vp)]),
     "exb_knn_sym_scatter_hits": (_c.c_int, [_i64, _c.c_int, _c.c_int, _c.c_int, _c.c_int,
                                             _c.POINTER(SymHits), _vp, _vp]),
     "exb_peer_buffer_alloc": (_c.c_int, [_sz, _c.POINTER(_vp), _c.c_char_p]),

@@ -2437,6 +2437,7 @@ extern "C" size_t exb_knn_sym_workspace_bytes(int64_t n, int dim, int k, int log
 struct SymSpan {            // which tile pairs a launch takes (ScreenParams::sym_*)
   int pair_lo, pair_hi, span_end, mid_pair, extra;
   const SymPeerTable* peers;   // host copy of the routing table, or null (one append buffer)
+  bool operand_ready;          // the caller filled the operand slots (exb_knn_sym_operand_slots)
 };
 
 // Phase 1: operand, thresholds, symmetric screen of the pairs of `sp_`; leaves the direct logs
@@ -2460,13 +2461,23 @@ static int sym_screen_phase(const float* rep, int64_t n, int dim, int k, const f
   EXB_CHECK_ARG(workspace_bytes >= need, "workspace too small: %zu < %zu", workspace_bytes, need);
   EXB_CHECK_ARG(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
   carve_sym(workspace, n, pl, k, log_cap, recv_cap, &w);
-  EXB_CUDA(cudaMemsetAsync(workspace, 0, 1024 + 64, st));
+  int rc = EXB_OK;
+  if (span.operand_ready) {
+    // operand, norms, scalars and affine record are in their slots already (each rank prepared
+    // its shard, the shards were all-gathered): clear the status and trace words only
+    EXB_CUDA(cudaMemsetAsync(w.status, 0, 256, st));
+    EXB_CUDA(cudaMemsetAsync(static_cast<char*>(workspace) + 768, 0, 256, st));   // b16 at 1024
+  } else {
+    EXB_CUDA(cudaMemsetAsync(workspace, 0, 1024 + 64, st));
+  }
   EXB_CUDA(cudaMemsetAsync(w.rcnt, 0, (size_t)n * sizeof(int), st));
   EXB_CUDA(cudaMemsetAsync(w.tq_count, 0, 16, st));
-  int rc = launch_affine(rep, n, nullptr, 0, dim, w.cs_part, nullptr, w.cs_stats, w.aff, st);
-  if (rc) return rc;
-  rc = launch_prep(rep, n, dim, pl.dpad, w.b16, w.hb, w.eb, w.bsc, st, nullptr, w.aff);
-  if (rc) return rc;
+  if (!span.operand_ready) {
+    rc = launch_affine(rep, n, nullptr, 0, dim, w.cs_part, nullptr, w.cs_stats, w.aff, st);
+    if (rc) return rc;
+    rc = launch_prep(rep, n, dim, pl.dpad, w.b16, w.hb, w.eb, w.bsc, st, nullptr, w.aff);
+    if (rc) return rc;
+  }
   SymThresholdParams tp;
   tp.d_sample = d_sample; tp.stride = d_stride; tp.ha = w.hb; tp.ea = w.eb; tp.bsc = w.bsc;
   tp.aff = w.aff; tp.tkeep = w.tkeep; tp.n = n;
@@ -2576,7 +2587,7 @@ extern "C" int exb_knn_sym_f32(const float* rep, int64_t n, int dim, int k, int3
   SymPlan pl;
   SymWs w;
   const int tiles = (int)((n + SCR_N - 1) / SCR_N);
-  const SymSpan span = {0, tiles, tiles, tiles, 0, nullptr};
+  const SymSpan span = {0, tiles, tiles, tiles, 0, nullptr, false};
   int rc = sym_screen_phase(rep, n, dim, k, d_sample, d_stride, log_cap, recv_cap, span,
                             workspace, workspace_bytes, st, &pl, &w);
   if (rc) return rc;
@@ -2603,7 +2614,7 @@ extern "C" int exb_knn_sym_screen_f32(const float* rep, int64_t n, int dim, int 
   EXB_CHECK_ARG(rep && d_sample && workspace && hits, "null pointer");
   SymPlan pl;
   SymWs w;
-  const SymSpan span = {pair_lo, pair_hi, span_end, mid_pair, extra_tiles, nullptr};
+  const SymSpan span = {pair_lo, pair_hi, span_end, mid_pair, extra_tiles, nullptr, false};
   const int rc = sym_screen_phase(rep, n, dim, k, d_sample, d_stride, log_cap, recv_cap, span,
                                   workspace, workspace_bytes, (cudaStream_t)stream, &pl, &w);
   if (rc) return rc;
@@ -2620,8 +2631,8 @@ extern "C" int exb_knn_sym_screen_peer_f32(const float* rep, int64_t n, int dim,
                                            int recv_cap, int pair_lo, int pair_hi, int span_end,
                                            int mid_pair, int extra_tiles, int n_ranks,
                                            const exb_sym_hits* peer_hits, const int32_t* tile_lo,
-                                           void* workspace, size_t workspace_bytes,
-                                           exb_stream_t stream) {
+                                           int operand_ready, void* workspace,
+                                           size_t workspace_bytes, exb_stream_t stream) {
   EXB_CHECK_ARG(rep && d_sample && workspace && peer_hits && tile_lo, "null pointer");
   EXB_CHECK_ARG(n_ranks >= 1 && n_ranks <= EXB_SYM_MAX_RANKS, "1 <= n_ranks <= %d",
                 EXB_SYM_MAX_RANKS);
@@ -2644,9 +2655,32 @@ extern "C" int exb_knn_sym_screen_peer_f32(const float* rep, int64_t n, int dim,
   }
   SymPlan pl;
   SymWs w;
-  const SymSpan span = {pair_lo, pair_hi, span_end, mid_pair, extra_tiles, &tbl};
+  const SymSpan span = {pair_lo, pair_hi, span_end, mid_pair, extra_tiles, &tbl,
+                        operand_ready != 0};
   return sym_screen_phase(rep, n, dim, k, d_sample, d_stride, log_cap, recv_cap, span, workspace,
                           workspace_bytes, (cudaStream_t)stream, &pl, &w);
+}
+
+// Where the symmetric screen keeps its operand inside the workspace, for callers that fill it
+// themselves (every rank prepares ITS rows with exb_knn_prep_affine_f16 straight into these
+// arrays, the shards are all-gathered over NVLink behind the sample pre-pass, the scalars are
+// MAX-reduced) and then pass operand_ready = 1 to exb_knn_sym_screen_peer_f32.
+extern "C" int exb_knn_sym_operand_slots(int64_t n, int dim, int k, int log_cap, int recv_cap,
+                                         void* workspace, size_t workspace_bytes,
+                                         exb_operand* slots, float** affine_slot) {
+  EXB_CHECK_ARG(workspace && slots && affine_slot, "null pointer");
+  SymPlan pl;
+  SymWs w;
+  EXB_CHECK_ARG(sym_plan(n, dim, k, &pl) && log_cap >= 32 && recv_cap >= 32, "bad sizes");
+  const size_t need = carve_sym(nullptr, n, pl, k, log_cap, recv_cap, &w);
+  EXB_CHECK_ARG(workspace_bytes >= need, "workspace too small: %zu < %zu", workspace_bytes, need);
+  carve_sym(workspace, n, pl, k, log_cap, recv_cap, &w);
+  slots->f16 = w.b16;
+  slots->half_norm = w.hb;
+  slots->round_err = w.eb;
+  slots->scalars = w.bsc;
+  *affine_slot = w.aff;
+  return EXB_OK;
 }
 
 // Scatter of a hit buffer whose entry count lives on the device (this rank's peer-visible

@@ -430,6 +430,9 @@ SYM_HOST_PIPELINE = True
 # Symmetric screen over several GPUs: size the ranks' tile blocks by the rate each GPU's screen
 # showed in the previous step (sym_balanced_blocks) instead of equally.
 SYM_RATE_BALANCE = True
+# ... and prepare the screen's fp16 operand N / G rows per rank + all-gather (behind the sample
+# pre-pass) instead of all N rows on every rank (device-resident reps, equal shards).
+SYM_SHARDED_PREP = True
 SYM_BALANCE_MAX_SKEW = 0.12
 
 
@@ -651,6 +654,47 @@ class _CudaSymBackend:
         self.peer = st
         return True
 
+    operand_work = None    # pending all-gathers of a sharded operand preparation
+
+    def prepare_shard(self, group, world, rank):
+        """Operand of the symmetric screen, every rank its N / world rows: one affine record from
+        all-reduced column statistics, exb_knn_prep_affine_f16 straight into the workspace's
+        operand arrays, the shards all-gathered over NVLink (asynchronously: the sample pre-pass
+        runs meanwhile; `screen_peer` waits) and the scalars MAX-reduced — instead of every rank
+        preparing all N rows.  Needs equal shards."""
+        lib, dev, n, dim = self.lib, self.dev, self.n, self.dim
+        if n % world != 0:
+            return False
+        lo, hi = shard_bounds(n, world, rank)
+        with torch.cuda.device(dev):
+            self.ws, _ = _lib.Workspace.get(dev, "knn_sym", self.need)
+            ws = self.ws
+            slots, aff_p = _lib.Operand(), ctypes.c_void_p()
+            _lib.check(lib.exb_knn_sym_operand_slots(n, dim, self.k, self.log_cap, self.recv_cap,
+                                                     _lib.ptr(ws), ws.numel(),
+                                                     ctypes.byref(slots), ctypes.byref(aff_p)))
+            base = ws.data_ptr()
+            dpad = -(-dim // 64) * 64
+
+            def view(ptr, nbytes, dtype):
+                return ws[ptr - base:ptr - base + nbytes].view(dtype)
+            f16 = view(slots.f16, n * dpad * 2, torch.float16).view(n, dpad)
+            hn = view(slots.half_norm, n * 4, torch.float32)
+            er = view(slots.round_err, n * 4, torch.float32)
+            sc = view(slots.scalars, 16, torch.int32)
+            aff = view(aff_p.value, _lib.AFFINE_FLOATS * 4, torch.float32)
+            sc.zero_()
+            aff.copy_(column_affine(self.rep[lo:hi], distributed=True, group=group, n_total=n))
+            _lib.check(lib.exb_knn_prep_affine_f16(
+                _lib.ptr(self.rep[lo:hi]), hi - lo, dim, _lib.ptr(aff), _lib.ptr(f16[lo:hi]),
+                _lib.ptr(hn[lo:hi]), _lib.ptr(er[lo:hi]), _lib.ptr(sc), _lib.stream_ptr(dev)))
+            self.operand_work = [
+                dist.all_gather_into_tensor(f16, f16[lo:hi], group=group, async_op=True),
+                dist.all_gather_into_tensor(hn, hn[lo:hi], group=group, async_op=True),
+                dist.all_gather_into_tensor(er, er[lo:hi], group=group, async_op=True),
+                dist.all_reduce(sc, op=dist.ReduceOp.MAX, group=group, async_op=True)]
+        return True
+
     def screen_peer(self, d_all, span, tile_lo):
         """The screen with the exchange inside the kernel; asynchronous."""
         lib, dev, st = self.lib, self.dev, self.peer
@@ -658,11 +702,16 @@ class _CudaSymBackend:
         with torch.cuda.device(dev):
             self.ws, _ = _lib.Workspace.get(dev, "knn_sym", self.need)
             ws = self.ws
+            ready = self.operand_work is not None
+            if ready:
+                for w in self.operand_work:
+                    w.wait()
+                self.operand_work = None
             tl = (ctypes.c_int32 * len(tile_lo))(*tile_lo)
             _lib.check(lib.exb_knn_sym_screen_peer_f32(
                 _lib.ptr(self.rep), self.n, self.dim, self.k, _lib.ptr(d_all), 1, self.log_cap,
                 self.recv_cap, pair_lo, pair_hi, span_end, mid, extra, st["world"], st["hits"],
-                tl, _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
+                tl, int(ready), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)))
 
     def scatter_rerank(self, r_t, r_v, r_s, lo, hi):
         """Received hits into the rows' lists, then the exact top-k of rows [lo, hi).
@@ -738,6 +787,8 @@ def _sym_queries_knn(rep, k, world, rank, group, tm, backend=None, feed=None):
     # doubles as the barrier "nobody appends to a buffer that is not cleared yet"
     peer = (SYM_PEER_MEMORY and hasattr(be, "open_peers") and world <= _lib.SYM_MAX_RANKS
             and be.open_peers(group, world, rank, rows_bound))
+    if peer and feed is None and SYM_SHARDED_PREP:
+        be.prepare_shard(group, world, rank)      # all-gathers run behind the pre-pass
     d_all = torch.zeros(n, dtype=torch.float32, device=dev)
     if feed is None:
         sample = rep[::stride].contiguous()

@@ -165,7 +165,17 @@ int exb_knn_sym_screen_peer_f32(const float* rep, int64_t n, int dim, int k,
                                 int recv_cap, int pair_lo, int pair_hi, int span_end,
                                 int mid_pair, int extra_tiles, int n_ranks,
                                 const exb_sym_hits* peer_hits, const int32_t* tile_lo,
-                                void* workspace, size_t workspace_bytes, exb_stream_t stream);
+                                int operand_ready, void* workspace, size_t workspace_bytes,
+                                exb_stream_t stream);
+/* operand_ready != 0: the caller has filled the screen's operand inside the workspace — the
+ * arrays exb_knn_sym_operand_slots returns (f16 [n, dim_pad], half_norm [n], round_err [n],
+ * scalars 16 bytes zeroed before the first row is prepared, affine record EXB_AFFINE_FLOATS) —
+ * so that G ranks prepare N/G rows each (exb_knn_prep_affine_f16 with one affine record from
+ * all-reduced column statistics) and all-gather the shards instead of each preparing all N. */
+struct exb_operand;   /* defined with the rep producers below */
+int exb_knn_sym_operand_slots(int64_t n, int dim, int k, int log_cap, int recv_cap,
+                              void* workspace, size_t workspace_bytes,
+                              struct exb_operand* slots, float** affine_slot);
 int exb_knn_sym_scatter_hits(int64_t n, int dim, int k, int log_cap, int recv_cap,
                              const exb_sym_hits* hits, void* workspace, exb_stream_t stream);
 

@@ -453,9 +453,31 @@ def test_symmetric_peer_routing_all_ranks_on_one_gpu(world):
         st = _lib.stream_ptr(DEV)
         for r in range(world):
             lo, hi, span_end, mid, extra = sym_span(tb, world, r)
+            ready = 0
+            if r % 2 == 1:
+                # odd "ranks": operand prepared by the caller in shards straight into the
+                # workspace's slots (what prepare_shard does across processes)
+                slots, aff_p = _lib.Operand(), ctypes.c_void_p()
+                _lib.check(lib.exb_knn_sym_operand_slots(n, dim, k, log_cap, recv_cap,
+                                                         _lib.ptr(ws[r]), need,
+                                                         ctypes.byref(slots), ctypes.byref(aff_p)))
+                base = ws[r].data_ptr()
+                dpad = -(-dim // 64) * 64
+                aff = ws[r][aff_p.value - base:aff_p.value - base + 4 * _lib.AFFINE_FLOATS].view(
+                    torch.float32)
+                from exorl_b200.rep import column_affine
+                aff.copy_(column_affine(xd))
+                for a, b in ((0, n // 3), (n // 3, n)):
+                    _lib.check(lib.exb_knn_prep_affine_f16(
+                        _lib.ptr(xd[a:b]), b - a, dim, _lib.ptr(aff),
+                        ctypes.c_void_p(slots.f16 + a * dpad * 2),
+                        ctypes.c_void_p(slots.half_norm + 4 * a),
+                        ctypes.c_void_p(slots.round_err + 4 * a),
+                        ctypes.c_void_p(slots.scalars), st))
+                ready = 1
             _lib.check(lib.exb_knn_sym_screen_peer_f32(
                 _lib.ptr(xd), n, dim, k, _lib.ptr(d_all), 1, log_cap, recv_cap, lo, hi, span_end,
-                mid, extra, world, hits, tl, _lib.ptr(ws[r]), need, st))
+                mid, extra, world, hits, tl, ready, _lib.ptr(ws[r]), need, st))
         torch.cuda.synchronize()
         total = 0
         for r in range(world):                      # every hit sits with the owner of its row
