@@ -280,6 +280,15 @@ def reps_from_host(rep_host, out=None, group=None):
     return out
 
 
+def sample_parts(n, world, stride):
+    """The rows 0, stride, 2 stride, ... of an n-row set split by the ranks' shards:
+    (first sample row, number of sample rows) inside shard_bounds(n, world, r) for every r."""
+    first = [-(-shard_bounds(n, world, r)[0] // stride) * stride for r in range(world)]
+    counts = [max(0, -(-(shard_bounds(n, world, r)[1] - first[r]) // stride))
+              for r in range(world)]
+    return first, counts
+
+
 class _HostFeed:
     """Rows of a pinned host matrix on their way to `rep_out` while the symmetric path already
     works (relabel_apt_reward_from_host): the sample (every stride-th row) goes first as one 2-D
@@ -306,9 +315,7 @@ class _HostFeed:
         """rep[::stride] on the device: every rank uploads the sample rows of ITS shard and the
         parts are all-gathered (padded to the largest part)."""
         lib, dev, world, dim = _lib.load(), self.dev, self.world, self.dim
-        first = [-(-shard_bounds(self.n, world, r)[0] // stride) * stride for r in range(world)]
-        counts = [max(0, -(-(shard_bounds(self.n, world, r)[1] - first[r]) // stride))
-                  for r in range(world)]
+        first, counts = sample_parts(self.n, world, stride)
         s_max = max(counts)
         buf = torch.empty((world, s_max, dim), dtype=torch.float32, device=dev)
         mine = buf[self.rank]

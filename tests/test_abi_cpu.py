@@ -144,3 +144,19 @@ def test_symmetric_rate_balanced_blocks_cover_once_and_equalise_time():
             lo, hi, span_end, mid, extra = sym_span(eq_tb, world, r)
             t_eq.append(sum(span_end - u + (extra if u >= mid else 0) for u in range(lo, hi)) * ms[r])
         assert max(t_bal) <= max(t_eq) * 1.005, (tiles, world, max(t_bal), max(t_eq))
+
+
+def test_sample_parts_partition_the_strided_sample():
+    """relabel.sample_parts: the per-rank pieces of rep[::stride] (each rank uploads the sample
+    rows of its own shard, the pieces are all-gathered) are disjoint, ordered and complete."""
+    from exorl_b200.relabel import sample_parts, shard_bounds
+    for n, world, stride in ((1_000_000, 8, 16), (150_000, 2, 16), (160_000, 8, 16), (1000, 4, 7),
+                             (999, 3, 16), (64, 8, 16), (10, 1, 3)):
+        first, counts = sample_parts(n, world, stride)
+        rows = []
+        for r in range(world):
+            lo, hi = shard_bounds(n, world, r)
+            part = [first[r] + j * stride for j in range(counts[r])]
+            assert all(lo <= x < hi for x in part), (n, world, stride, r)
+            rows += part
+        assert rows == list(range(0, n, stride)), (n, world, stride)
