@@ -160,3 +160,15 @@ def test_sample_parts_partition_the_strided_sample():
             assert all(lo <= x < hi for x in part), (n, world, stride, r)
             rows += part
         assert rows == list(range(0, n, stride)), (n, world, stride)
+
+
+def test_feed_chunk_cuts_cover_the_rows():
+    from exorl_b200.relabel import feed_chunk_cuts
+    for rows in (1, 5000, 119999, 120000, 125000, 130000, 250000, 500000, 1_000_000, 3_000_001):
+        cuts = feed_chunk_cuts(rows)
+        assert cuts[0] == 0 and cuts[-1] == rows and all(b > a for a, b in zip(cuts, cuts[1:]))
+        assert len(cuts) <= 2 + rows // 32768
+        if rows >= 120000:
+            assert cuts[1] == 32768 and max(b - a for a, b in zip(cuts, cuts[1:])) <= 2 * 262144
+            # growth <= 1.4 (the last chunk takes the remainder: up to 1.5 of its nominal size)
+            assert all(c - b <= 2.1 * (b - a) + 1 for a, b, c in zip(cuts, cuts[1:], cuts[2:]))
